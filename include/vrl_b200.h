@@ -1,0 +1,231 @@
+/*
+ * vrl_b200.h -- C ABI of the B200-native virtual-ray-light (VRL) volumetric gather.
+ *
+ * This is the drop-in boundary for the hot path of the `vrl` integrator of
+ * VincentiusIV/mitsuba-NLVRL (reference paths below are relative to the
+ * reference checkout).  The reference has no FFI on this path: everything is
+ * C++ virtual calls inside one process.  The entry
+ * points declared here are what a Mitsuba-side plugin shim `plugins/vrl.so`
+ * (class VRLIntegrator, src/integrators/vrl/vrl.cpp:20-859) binds instead of
+ * running the scalar CPU code; INTEGRATION.md shows that shim.
+ *
+ * Plain C: opaque handle, POD structs, fp32 arrays, explicit sizes.  No C++
+ * or torch types cross this boundary.  All functions return VRLB_OK (0) or a
+ * negative error code; vrlb_last_error() gives the message.  There is no CPU
+ * fallback: every compute entry point fails with VRLB_ERR_CUDA when no
+ * sm_100 device is usable.
+ */
+#ifndef VRL_B200_H
+#define VRL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VRLB_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------ */
+enum {
+    VRLB_OK            = 0,
+    VRLB_ERR_INVALID   = -1,  /* bad argument (mirrors Throw(...) in Properties / xml.cpp:1050-1068) */
+    VRLB_ERR_CUDA      = -2,  /* CUDA runtime failure or no device                                 */
+    VRLB_ERR_STATE     = -3,  /* call order violated (e.g. gather before a VRL set is resident)   */
+    VRLB_ERR_CANCELLED = -4,  /* vrlb_cancel() observed; mirrors Integrator::cancel, integrator.h:148 */
+    VRLB_ERR_NOMEM     = -5
+};
+
+/* ---- surfaces ---------------------------------------------------------- */
+/* One uint32 per triangle.  Restates what the hot path asks of a surface:
+ * BSDFFlags::Null (vrl_struct.h:529), BSDFFlags::Smooth (vrl.cpp:671),
+ * Shape::is_emitter (vrl.cpp:664), is_medium_transition/target_medium
+ * (vrl_struct.h:552-557, vrl.cpp:713-714). */
+#define VRLB_SURF_BSDF_MASK      0x3u
+#define VRLB_SURF_BSDF_SMOOTH    0x0u   /* diffuse & co: ends the camera path, occludes          */
+#define VRLB_SURF_BSDF_NULL      0x1u   /* index-matched boundary: passed through                */
+#define VRLB_SURF_EMITTER        0x4u   /* area emitter attached                                 */
+#define VRLB_SURF_INTERIOR(m)    ((((uint32_t)(m)) + 1u) << 8)   /* medium id m on the -n side  */
+#define VRLB_SURF_EXTERIOR(m)    ((((uint32_t)(m)) + 1u) << 16)  /* medium id m on the +n side  */
+#define VRLB_SURF_EMITTER_ID(e)  (((uint32_t)(e)) << 24)
+#define VRLB_SURF_GET_INTERIOR(f) ((int)(((f) >> 8) & 0xffu) - 1)   /* -1 = none */
+#define VRLB_SURF_GET_EXTERIOR(f) ((int)(((f) >> 16) & 0xffu) - 1)
+#define VRLB_SURF_GET_EMITTER(f)  ((int)(((f) >> 24) & 0xffu))
+
+/* ---- media ------------------------------------------------------------- */
+enum { VRLB_MEDIUM_HOMOGENEOUS = 0,   /* src/media/homogeneous.cpp   */
+       VRLB_MEDIUM_GRID        = 1,   /* src/media/heterogeneous.cpp + src/textures/grid3d.cpp */
+       VRLB_MEDIUM_NONLINEAR   = 2 }; /* src/media/nonlinear.cpp (homogeneous coefficients + IOR cell grid) */
+enum { VRLB_PHASE_ISOTROPIC = 0,      /* src/phase/isotropic.cpp:40-44 */
+       VRLB_PHASE_HG        = 1 };    /* src/phase/hg.cpp:51-54,77-81  */
+
+typedef struct vrlb_medium {
+    int32_t kind;
+    int32_t phase;
+    float   g;                 /* HG asymmetry                                         */
+    float   scale;             /* `scale` property                                     */
+    float   sigma_t[3];        /* constant sigma_t (homogeneous / nonlinear)            */
+    float   albedo[3];         /* constant albedo                                      */
+    /* grid medium (kind == VRLB_MEDIUM_GRID): scalar sigma_t grid, x fastest
+     * ((z*ny + y)*nx + x, grid3d.cpp:291), `.vol` bbox (volume_data.h:42-107)   */
+    const float *grid;         /* host pointer, nx*ny*nz floats; copied on scene_set    */
+    int32_t grid_res[3];
+    float   grid_bbox_min[3];
+    float   grid_bbox_max[3];
+    float   grid_max;          /* `m_sigmat->max()` of the grid (majorant before scale) */
+    /* nonlinear medium (kind == VRLB_MEDIUM_NONLINEAR), nonlinear.cpp:40-89,129-153   */
+    int32_t nl_res[3];
+    float   nl_bbox_min[3];
+    float   nl_bbox_max[3];
+    float   top_ior, bottom_ior;
+    int32_t ior_method;        /* only 0 (linear in height) is on the path             */
+    int32_t from_bottom;
+} vrlb_medium;
+
+typedef struct vrlb_emitter {
+    float radiance[3];         /* area emitter radiance (src/emitters/area.cpp)         */
+    float pad;
+} vrlb_emitter;
+
+typedef struct vrlb_scene_desc {
+    const float       *tri_verts;   /* n_tris * 9 floats: p0 p1 p2                      */
+    const uint32_t    *tri_flags;   /* n_tris surface words (VRLB_SURF_*)               */
+    uint32_t           n_tris;
+    const vrlb_medium *media;
+    uint32_t           n_media;
+    const vrlb_emitter*emitters;
+    uint32_t           n_emitters;
+} vrlb_scene_desc;
+
+/* ---- sensor ------------------------------------------------------------ */
+/* What PerspectiveCamera::sample_ray_differential (src/sensors/perspective.cpp:183-216)
+ * reads: m_sample_to_camera, the to_world transform, clip planes; the film size. Row-major 4x4. */
+typedef struct vrlb_camera {
+    float   sample_to_camera[16];
+    float   to_world[16];
+    float   near_clip, far_clip;
+    int32_t width, height;
+    int32_t medium;            /* sensor->medium(): medium id the camera sits in, -1 = none */
+    int32_t pad;
+} vrlb_camera;
+
+/* ---- integrator options ------------------------------------------------ */
+/* Subset of VRLIntegrator's Properties that drives the gather (vrl.cpp:33-73) plus the
+ * SamplingIntegrator / sampler state that addresses the PCG32 streams
+ * (integrator.cpp:187-297, sampler.cpp:83-96). */
+typedef struct vrlb_options {
+    int32_t  spp;                   /* sampler sample_count                               */
+    int32_t  block_size;            /* image block size (pin to 32 for parity, quirk 4)   */
+    uint64_t base_seed;             /* sampler `seed` property                            */
+    int32_t  samples_per_query;     /* q                                                  */
+    int32_t  use_uniform_sampling;  /* sampleMC instead of importance sampling            */
+    int32_t  rr_vrl;                /* distance Russian roulette (vrl_map.h:171-190)      */
+    float    scale_rr;
+    int32_t  max_depth;
+    int32_t  use_non_linear_camera; /* split camera rays at IOR cell faces (vrl.cpp:550)  */
+    int32_t  use_nl_atomic_query;   /* one query over the whole NLRay (vrl.cpp:613-617)   */
+    int32_t  visibility;            /* 1: trace shadow segments through the BVH; 0: scene has no
+                                       occluder between medium points (Tr_vis = medium Tr) */
+    int32_t  hide_emitters;
+    int32_t  math_mode;             /* 0: exact (IEEE op order of the oracle), 1: fast intrinsics */
+    int32_t  reserved[2];
+} vrlb_options;
+
+/* ---- VRL set ----------------------------------------------------------- */
+/* SoA of 10 fp32 columns, each n long, in this order:
+ *   ox oy oz  dx dy dz  length  flux_r flux_g flux_b        (struct VRL, vrl_struct.h:664-677)
+ * i.e. column c of VRL j is soa10[c*n + j].  `medium` (may be NULL = all 0) is the medium id.
+ * `scale` is VRLMap::m_scale = 1/volumePathCount (vrl.cpp:404,423).
+ * `first_index`/`total` place this set inside a larger exported set: PCG32 stream addressing
+ * uses the GLOBAL VRL index, so a rank holding a shard passes its offset here. */
+typedef struct vrlb_vrlset_desc {
+    const float    *soa10;
+    const uint16_t *medium;
+    uint64_t        n;
+    uint64_t        first_index;
+    uint64_t        total;
+    float           scale;
+    float           pad;
+} vrlb_vrlset_desc;
+
+/* ---- camera segments --------------------------------------------------- */
+/* One straight part of a camera path inside a medium: an NLRay part (vrl_struct.h:10-57)
+ * together with what VRLIntegrator::sample carries around its query (vrl.cpp:613-631). 64 bytes. */
+typedef struct vrlb_segment {
+    float    o[3];  float    maxt;
+    float    d[3];  uint32_t pixel;       /* y*width + x of the film pixel the sample lands in */
+    float    weight[3];                   /* throughput outside the query (vrlThroughput)      */
+    int32_t  medium;
+    uint64_t rng_state;                   /* PCG32 state at the first draw of this part's query */
+    uint32_t sample;                      /* sample index within the pixel                     */
+    uint32_t part;                        /* part index within the NLRay                       */
+} vrlb_segment;
+
+/* ---- timings of the last render, CUDA events on the library's stream --- */
+typedef struct vrlb_timing {
+    float    ms_upload;      /* host->device copies issued by the call         */
+    float    ms_segments;    /* camera-segment kernel(s)                       */
+    float    ms_gather;      /* gather kernel(s) incl. visibility              */
+    float    ms_film;        /* film conversion                                */
+    float    ms_download;    /* device->host copy                              */
+    uint32_t gather_launches;
+    uint32_t total_launches;
+    uint64_t n_evals;        /* P*S*q*N getContrib calls (vrl_struct.h:584)    */
+    uint64_t n_segments;
+} vrlb_timing;
+
+typedef struct vrlb_context vrlb_context;
+
+/* ---- lifetime ---------------------------------------------------------- */
+int  vrlb_abi_version(void);
+/* Creates a context on CUDA device `device` (one context per GPU; one process per GPU under
+ * torchrun).  Replaces the VRLIntegrator constructor's allocations, vrl.cpp:75-79. */
+int  vrlb_create(int device, vrlb_context **out);
+void vrlb_destroy(vrlb_context *ctx);
+const char *vrlb_last_error(const vrlb_context *ctx);   /* ctx may be NULL: last create error */
+/* Run the library's work on an existing CUDA stream (cudaStream_t as void*); NULL = own stream. */
+int  vrlb_set_stream(vrlb_context *ctx, void *cuda_stream);
+
+/* ---- scene: replaces Scene::ray_intersect + ShapeKDTree (scene.cpp:114-131, kdtree.h:2069-2172),
+ *      the media plugins and phase functions -------------------------------------------------- */
+int  vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *scene);
+
+/* ---- VRL set: replaces VRLMap::push_back/build/setScaleFactor (vrl_map.h:43-53,80-102,220) --- */
+int  vrlb_vrls_upload(vrlb_context *ctx, const vrlb_vrlset_desc *set);
+int  vrlb_vrls_download(vrlb_context *ctx, float *soa10, uint16_t *medium, uint64_t cap, uint64_t *n_out);
+uint64_t vrlb_vrls_count(const vrlb_context *ctx);
+
+/* ---- camera segments: replaces the medium branch of VRLIntegrator::sample up to the query
+ *      (vrl.cpp:443-631) driven by SamplingIntegrator::render_block/render_sample
+ *      (integrator.cpp:187-297) ----------------------------------------------------------------- */
+int  vrlb_segments_build(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_options *opt);
+int  vrlb_segments_upload(vrlb_context *ctx, const vrlb_segment *segs, uint64_t n, int32_t width, int32_t height, int32_t spp);
+int  vrlb_segments_download(vrlb_context *ctx, vrlb_segment *segs, uint64_t cap, uint64_t *n_out);
+uint64_t vrlb_segments_count(const vrlb_context *ctx);
+
+/* ---- gather: replaces VRLMap::query -> VRL::getContrib (vrl_map.h:133-211, vrl_struct.h:584-662)
+ *      for every resident camera segment against every resident VRL.  Accumulates
+ *      weight * Li into the device radiance buffer (fp32 RGB, width*height*3). ----------------- */
+int  vrlb_film_clear(vrlb_context *ctx);
+int  vrlb_gather(vrlb_context *ctx, const vrlb_options *opt);
+/* Device pointer of the fp32 RGB radiance accumulation buffer (width*height*3 floats) so that a
+ * multi-GPU host can sum VRL shards with NCCL without a host round trip. */
+int  vrlb_film_device_ptr(vrlb_context *ctx, void **dev_ptr, uint64_t *n_floats);
+/* Film contract of SamplingIntegrator::render_sample / ImageBlock::put (integrator.cpp:282-294,
+ * imageblock.cpp:162-169): 5 fp32 channels X,Y,Z,A,W per pixel, weighted sums (box filter). */
+int  vrlb_film_download_xyzaw(vrlb_context *ctx, float *xyzaw);
+int  vrlb_film_download_rgb(vrlb_context *ctx, float *rgb);
+
+/* ---- whole frame from host buffers: Integrator::render (integrator.cpp:51-183) --------------- */
+int  vrlb_render(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_options *opt,
+                 const vrlb_vrlset_desc *vrls /* NULL: keep resident set */, float *xyzaw_out);
+
+int  vrlb_cancel(vrlb_context *ctx);
+int  vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out);
+int  vrlb_synchronize(vrlb_context *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VRL_B200_H */

@@ -1,0 +1,76 @@
+"""ctypes mirror of include/vrl_b200.h (the C ABI PODs).  Field order and types must match the header."""
+import ctypes as C
+
+OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CANCELLED, ERR_NOMEM = 0, -1, -2, -3, -4, -5
+
+SURF_BSDF_SMOOTH, SURF_BSDF_NULL, SURF_EMITTER = 0x0, 0x1, 0x4
+MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_NONLINEAR = 0, 1, 2
+PHASE_ISOTROPIC, PHASE_HG = 0, 1
+
+
+def surf_interior(m): return (m + 1) << 8
+def surf_exterior(m): return (m + 1) << 16
+def surf_emitter_id(e): return e << 24
+
+
+class Medium(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("phase", C.c_int32), ("g", C.c_float), ("scale", C.c_float),
+                ("sigma_t", C.c_float * 3), ("albedo", C.c_float * 3),
+                ("grid", C.POINTER(C.c_float)), ("grid_res", C.c_int32 * 3),
+                ("grid_bbox_min", C.c_float * 3), ("grid_bbox_max", C.c_float * 3), ("grid_max", C.c_float),
+                ("nl_res", C.c_int32 * 3), ("nl_bbox_min", C.c_float * 3), ("nl_bbox_max", C.c_float * 3),
+                ("top_ior", C.c_float), ("bottom_ior", C.c_float), ("ior_method", C.c_int32), ("from_bottom", C.c_int32)]
+
+
+class Emitter(C.Structure):
+    _fields_ = [("radiance", C.c_float * 3), ("pad", C.c_float)]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("tri_verts", C.POINTER(C.c_float)), ("tri_flags", C.POINTER(C.c_uint32)), ("n_tris", C.c_uint32),
+                ("media", C.POINTER(Medium)), ("n_media", C.c_uint32),
+                ("emitters", C.POINTER(Emitter)), ("n_emitters", C.c_uint32)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("sample_to_camera", C.c_float * 16), ("to_world", C.c_float * 16),
+                ("near_clip", C.c_float), ("far_clip", C.c_float), ("width", C.c_int32), ("height", C.c_int32),
+                ("medium", C.c_int32), ("pad", C.c_int32)]
+
+
+class Options(C.Structure):
+    _fields_ = [("spp", C.c_int32), ("block_size", C.c_int32), ("base_seed", C.c_uint64),
+                ("samples_per_query", C.c_int32), ("use_uniform_sampling", C.c_int32), ("rr_vrl", C.c_int32),
+                ("scale_rr", C.c_float), ("max_depth", C.c_int32), ("use_non_linear_camera", C.c_int32),
+                ("use_nl_atomic_query", C.c_int32), ("visibility", C.c_int32), ("hide_emitters", C.c_int32),
+                ("math_mode", C.c_int32), ("reserved", C.c_int32 * 2)]
+
+
+class VrlSetDesc(C.Structure):
+    _fields_ = [("soa10", C.POINTER(C.c_float)), ("medium", C.POINTER(C.c_uint16)), ("n", C.c_uint64),
+                ("first_index", C.c_uint64), ("total", C.c_uint64), ("scale", C.c_float), ("pad", C.c_float)]
+
+
+class Segment(C.Structure):
+    _fields_ = [("o", C.c_float * 3), ("maxt", C.c_float), ("d", C.c_float * 3), ("pixel", C.c_uint32),
+                ("weight", C.c_float * 3), ("medium", C.c_int32), ("rng_state", C.c_uint64),
+                ("sample", C.c_uint32), ("part", C.c_uint32)]
+
+
+class Timing(C.Structure):
+    _fields_ = [("ms_upload", C.c_float), ("ms_segments", C.c_float), ("ms_gather", C.c_float), ("ms_film", C.c_float),
+                ("ms_download", C.c_float), ("gather_launches", C.c_uint32), ("total_launches", C.c_uint32),
+                ("n_evals", C.c_uint64), ("n_segments", C.c_uint64)]
+
+
+assert C.sizeof(Segment) == 64
+
+import numpy as _np
+SEGMENT_DTYPE = _np.dtype([("o", "<f4", 3), ("maxt", "<f4"), ("d", "<f4", 3), ("pixel", "<u4"),
+                           ("weight", "<f4", 3), ("medium", "<i4"), ("rng_state", "<u8"),
+                           ("sample", "<u4"), ("part", "<u4")])
+assert SEGMENT_DTYPE.itemsize == 64
+
+
+def fptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))

@@ -1,0 +1,282 @@
+"""Host-side scene description for the VRL gather: sensor matrices, triangle soups, media and seeded
+synthetic VRL sets of the shape SURVEY.md 8(d) names ("box-fog").  Pure numpy; produces the PODs of
+include/vrl_b200.h.  Matrix construction restates the reference's sensor set-up
+(include/mitsuba/render/sensor.h:195-231, src/librender/sensor.cpp parse_fov,
+include/mitsuba/core/transform.h look_at / perspective) in float64 and rounds once to fp32 -- the
+oracle and the CUDA path both consume the resulting fp32 matrices, so parity does not depend on how
+they were built."""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import abi
+
+
+# --------------------------------------------------------------------------- sensor
+def look_at(origin, target, up):
+    """Transform::look_at (transform.h): columns left, new_up, dir, origin."""
+    o, t, u = (np.asarray(v, np.float64) for v in (origin, target, up))
+    d = (t - o) / np.linalg.norm(t - o)
+    left = np.cross(u, d)
+    left /= np.linalg.norm(left)
+    new_up = np.cross(d, left)
+    m = np.eye(4)
+    m[:3, 0], m[:3, 1], m[:3, 2], m[:3, 3] = left, new_up, d, o
+    return m
+
+
+def _perspective(fov_deg, near, far):
+    recip = 1.0 / (far - near)
+    cot = 1.0 / math.tan(math.radians(fov_deg * 0.5))
+    m = np.zeros((4, 4))
+    m[0, 0] = cot
+    m[1, 1] = cot
+    m[2, 2] = far * recip
+    m[2, 3] = -near * far * recip
+    m[3, 2] = 1.0
+    return m
+
+
+def _scale(x, y, z):
+    return np.diag([x, y, z, 1.0])
+
+
+def _translate(x, y, z):
+    m = np.eye(4)
+    m[:3, 3] = (x, y, z)
+    return m
+
+
+def parse_fov(fov, fov_axis, aspect):
+    """parse_fov (src/librender/sensor.cpp): returns the x field of view in degrees."""
+    if fov_axis == "smaller":
+        fov_axis = "y" if aspect > 1 else "x"
+    elif fov_axis == "larger":
+        fov_axis = "x" if aspect > 1 else "y"
+    if fov_axis == "x":
+        return fov
+    if fov_axis == "y":
+        return math.degrees(2 * math.atan(math.tan(0.5 * math.radians(fov)) * aspect))
+    if fov_axis == "diagonal":
+        diag = 2 * math.tan(0.5 * math.radians(fov))
+        width = diag / math.sqrt(1 + 1 / (aspect * aspect))
+        return math.degrees(2 * math.atan(width * 0.5))
+    raise ValueError("fov_axis must be x, y, diagonal, smaller or larger")
+
+
+def make_camera(width, height, origin, target, up=(0, 1, 0), fov=39.3077, fov_axis="x",
+                near_clip=1e-2, far_clip=1e4, medium=-1):
+    aspect = width / float(height)
+    x_fov = parse_fov(fov, fov_axis, aspect)
+    # perspective_projection (sensor.h:195-231) with crop == film
+    c2s = _scale(-0.5, -0.5 * aspect, 1.0) @ _translate(-1.0, -1.0 / aspect, 0.0) @ _perspective(x_fov, near_clip, far_clip)
+    s2c = np.linalg.inv(c2s)
+    cam = abi.Camera()
+    cam.sample_to_camera[:] = s2c.astype(np.float32).reshape(-1).tolist()
+    cam.to_world[:] = look_at(origin, target, up).astype(np.float32).reshape(-1).tolist()
+    cam.near_clip, cam.far_clip = near_clip, far_clip
+    cam.width, cam.height, cam.medium = width, height, medium
+    return cam
+
+
+# --------------------------------------------------------------------------- geometry helpers
+def box_tris(lo, hi, faces="xXyYzZ", inward=False):
+    """Axis-aligned box as triangles (outward normals unless inward). faces picks which sides."""
+    lo, hi = np.asarray(lo, np.float32), np.asarray(hi, np.float32)
+    c = [np.array([lo[0] if i & 1 == 0 else hi[0], lo[1] if i & 2 == 0 else hi[1], lo[2] if i & 4 == 0 else hi[2]], np.float32)
+         for i in range(8)]
+    quads = {"x": (0, 4, 6, 2), "X": (1, 3, 7, 5), "y": (0, 1, 5, 4), "Y": (2, 6, 7, 3), "z": (0, 2, 3, 1), "Z": (4, 5, 7, 6)}
+    tris = []
+    for f in faces:
+        a, b, cc, d = quads[f]
+        q = [(a, b, cc), (a, cc, d)]
+        for t in q:
+            t = t[::-1] if inward else t
+            tris.append(np.stack([c[t[0]], c[t[1]], c[t[2]]]))
+    return np.stack(tris).astype(np.float32)
+
+
+def transform_tris(tris, m):
+    m = np.asarray(m, np.float64)
+    p = tris.reshape(-1, 3).astype(np.float64)
+    p = p @ m[:3, :3].T + m[:3, 3]
+    return p.reshape(-1, 3, 3).astype(np.float32)
+
+
+def rotation(axis, deg):
+    a = np.asarray(axis, np.float64)
+    a /= np.linalg.norm(a)
+    t = math.radians(deg)
+    K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    m = np.eye(4)
+    m[:3, :3] = np.eye(3) + math.sin(t) * K + (1 - math.cos(t)) * (K @ K)
+    return m
+
+
+def sphere_tris(center, radius, n_lat=20, n_lon=32):
+    """UV sphere: 2*n_lon*(n_lat-1) triangles (20x32 -> 1216; SURVEY's 1280 is an icosphere; same order of size)."""
+    c = np.asarray(center, np.float64)
+    tris = []
+
+    def p(i, j):
+        th = math.pi * i / n_lat
+        ph = 2 * math.pi * j / n_lon
+        return c + radius * np.array([math.sin(th) * math.cos(ph), math.cos(th), math.sin(th) * math.sin(ph)])
+    for i in range(n_lat):
+        for j in range(n_lon):
+            a, b, cc, d = p(i, j), p(i + 1, j), p(i + 1, j + 1), p(i, j + 1)
+            if i != 0:
+                tris.append(np.stack([a, b, d]))
+            if i != n_lat - 1:
+                tris.append(np.stack([b, cc, d]))
+    return np.stack(tris).astype(np.float32)
+
+
+# --------------------------------------------------------------------------- scene container
+def make_medium(kind=abi.MEDIUM_HOMOGENEOUS, sigma_t=(1, 1, 1), albedo=(0.75, 0.75, 0.75), scale=1.0,
+                phase=abi.PHASE_ISOTROPIC, g=0.8):
+    m = abi.Medium()
+    m.kind, m.phase, m.g, m.scale = kind, phase, g, scale
+    m.sigma_t[:] = list(sigma_t)
+    m.albedo[:] = list(albedo)
+    return m
+
+
+class Scene:
+    """Owns the numpy buffers behind a vrlb_scene_desc."""
+
+    def __init__(self):
+        self._tris, self._flags, self.media, self.emitters, self._grids = [], [], [], [], []
+
+    def add_tris(self, tris, flags):
+        tris = np.asarray(tris, np.float32).reshape(-1, 3, 3)
+        self._tris.append(tris)
+        self._flags.append(np.full(len(tris), flags, np.uint32))
+        return self
+
+    def add_medium(self, medium, grid=None):
+        if grid is not None:
+            g = np.ascontiguousarray(grid, np.float32)   # [nz, ny, nx]
+            self._grids.append(g)
+            medium.grid = abi.fptr(g)
+            medium.grid_res[:] = [g.shape[2], g.shape[1], g.shape[0]]
+            medium.grid_max = float(g.max())
+        self.media.append(medium)
+        return len(self.media) - 1
+
+    def add_emitter(self, radiance):
+        e = abi.Emitter()
+        e.radiance[:] = list(radiance)
+        self.emitters.append(e)
+        return len(self.emitters) - 1
+
+    @property
+    def tri_verts(self):
+        return np.ascontiguousarray(np.concatenate(self._tris), np.float32) if self._tris else np.zeros((0, 3, 3), np.float32)
+
+    @property
+    def tri_flags(self):
+        return np.ascontiguousarray(np.concatenate(self._flags), np.uint32) if self._flags else np.zeros(0, np.uint32)
+
+    def desc(self):
+        self._v, self._f = self.tri_verts, self.tri_flags
+        self._m = (abi.Medium * max(len(self.media), 1))(*self.media)
+        self._e = (abi.Emitter * max(len(self.emitters), 1))(*self.emitters)
+        d = abi.SceneDesc()
+        d.tri_verts = abi.fptr(self._v)
+        d.tri_flags = self._f.ctypes.data_as(C.POINTER(C.c_uint32))
+        d.n_tris = len(self._f)
+        d.media, d.n_media = self._m, len(self.media)
+        d.emitters, d.n_emitters = self._e, len(self.emitters)
+        return d
+
+
+def default_options(**kw):
+    o = abi.Options()
+    o.spp, o.block_size, o.base_seed = 1, 32, 0
+    o.samples_per_query, o.use_uniform_sampling, o.rr_vrl, o.scale_rr = 1, 0, 0, 0.5
+    o.max_depth, o.use_non_linear_camera, o.use_nl_atomic_query = 512, 1, 0
+    o.visibility, o.hide_emitters, o.math_mode = 1, 0, 0
+    for k, v in kw.items():
+        if not hasattr(o, k):
+            raise AttributeError(k)
+        setattr(o, k, v)
+    return o
+
+
+# --------------------------------------------------------------------------- the synthetic "box-fog" scene
+BOX = 10.0
+
+
+def box_fog_scene(occluders=True, phase=abi.PHASE_ISOTROPIC, g=0.8, sigma_s=0.1, sigma_a=0.01):
+    """Fog box [-10.01,10.01]^3 (null BSDF, interior medium 0) around five diffuse walls at +-10 (front
+    face open towards the camera), optional sphere r=4 and rotated cuboid as occluders inside."""
+    sc = Scene()
+    st = sigma_s + sigma_a
+    med = sc.add_medium(make_medium(sigma_t=(st,) * 3, albedo=(sigma_s / st,) * 3, scale=1.0, phase=phase, g=g))
+    e = BOX + 0.01
+    sc.add_tris(box_tris((-e,) * 3, (e,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(med))
+    sc.add_tris(box_tris((-BOX,) * 3, (BOX,) * 3, faces="xXyYZ", inward=True), abi.SURF_BSDF_SMOOTH)
+    if occluders:
+        sc.add_tris(sphere_tris((4.5, -2.0, -1.0), 4.0), abi.SURF_BSDF_SMOOTH)
+        cub = box_tris((-2.0, -3.0, -1.5), (2.0, 3.0, 1.5))
+        m = _translate(-4.0, -1.0, 2.0) @ rotation((0.3, 1.0, 0.2), 35.0)
+        sc.add_tris(transform_tris(cub, m), abi.SURF_BSDF_SMOOTH)
+    return sc
+
+
+def box_fog_camera(width=1920, height=1080):
+    return make_camera(width, height, origin=(0, 0, -40), target=(0, 0, -39), up=(0, 1, 0), fov=36.0, fov_axis="x",
+                       near_clip=0.1, far_clip=1000.0)
+
+
+def _seeded_floats(seed, n):
+    """n deterministic uniforms in [0,1) from a counter-based splitmix64 (VRL sets are synthetic inputs: any
+    seeded generator will do; parity only needs the oracle and the GPU to read the SAME exported set)."""
+    x = (np.arange(n, dtype=np.uint64) + np.uint64(seed) * np.uint64(0x9E3779B97F4A7C15)) & np.uint64(0xFFFFFFFFFFFFFFFF)
+    with np.errstate(over="ignore"):
+        x = (x + np.uint64(0x9E3779B97F4A7C15))
+        z = x
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return ((z >> np.uint64(40)).astype(np.float64) / float(1 << 24)).astype(np.float32)
+
+
+def synthetic_vrls(n, seed=1, sigma_t=0.11, albedo=0.909, box=BOX):
+    """Seeded VRL set of SURVEY 8(d): origins uniform in the box, directions uniform on the sphere, lengths
+    ~Exp(mean 1/sigma_t) clipped to the box, flux (1,1,1)*albedo^k with k~Geom(0.5).  Returns soa10 [10, n] fp32."""
+    u = _seeded_floats(seed, 7 * n).reshape(7, n).astype(np.float64)
+    o = (u[0:3] * 2 - 1) * (box * 0.999)
+    z = 1 - 2 * u[3]
+    r = np.sqrt(np.maximum(0, 1 - z * z))
+    ph = 2 * np.pi * u[4]
+    d = np.stack([r * np.cos(ph), r * np.sin(ph), z])
+    d32 = d.astype(np.float32)
+    d32 /= np.sqrt((d32 * d32).sum(0, dtype=np.float32))          # unit to fp32 rounding
+    d = d32.astype(np.float64)
+    length = -np.log(1 - u[5]) / sigma_t
+    # clip to the box: largest t with o + t d inside
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t1 = (box - o) / d
+        t2 = (-box - o) / d
+    tmax = np.where(d > 0, t1, np.where(d < 0, t2, np.inf)).min(0)
+    length = np.minimum(length, 0.999 * tmax)
+    k = np.floor(np.log2(1.0 / np.maximum(1 - u[6], 2.0 ** -24)))  # Geom(0.5)
+    flux = albedo ** k
+    soa = np.empty((10, n), np.float32)
+    soa[0:3], soa[3:6], soa[6], soa[7:10] = o, d32, length, flux
+    return np.ascontiguousarray(soa)
+
+
+def vrlset_desc(soa10, scale=None, first_index=0, total=None, medium=None):
+    """Builds a vrlb_vrlset_desc over a [10, n] fp32 array (kept alive by the caller)."""
+    assert soa10.dtype == np.float32 and soa10.flags["C_CONTIGUOUS"] and soa10.shape[0] == 10
+    n = soa10.shape[1]
+    d = abi.VrlSetDesc()
+    d.soa10 = abi.fptr(soa10)
+    d.medium = medium.ctypes.data_as(C.POINTER(C.c_uint16)) if medium is not None else None
+    d.n, d.first_index, d.total = n, first_index, (total if total is not None else n)
+    d.scale = (1.0 / d.total) if scale is None else scale
+    return d

@@ -1,0 +1,1106 @@
+/*
+ * vrl_oracle.cpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE (see vrl_oracle.h).
+ *
+ * Scalar fp32 CPU restatement of the reference's VRL gather.  Build:
+ *   g++ -O2 -std=c++17 -ffp-contract=off -fno-fast-math -fPIC -shared -pthread
+ * -ffp-contract=off matters: every '+', '-', '*', '/', sqrt below is exactly one IEEE binary32
+ * operation in the written order, which is the arithmetic the CUDA kernels reproduce
+ * (they are built with -fmad=false -prec-div=true -prec-sqrt=true).  Transcendentals go to the
+ * platform libm, as the reference's do through Enoki's scalar fallbacks.
+ *
+ * Every function cites the reference lines it follows (paths relative to the reference root).
+ */
+#include "vrl_oracle.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <thread>
+#include <vector>
+
+namespace {
+
+/* ------------------------------------------------------------------------------------------ */
+/*  small vector type; every operation is componentwise scalar fp32                           */
+/* ------------------------------------------------------------------------------------------ */
+struct V3 {
+    float x, y, z;
+    V3() : x(0), y(0), z(0) {}
+    V3(float a) : x(a), y(a), z(a) {}
+    V3(float a, float b, float c) : x(a), y(b), z(c) {}
+    explicit V3(const float *p) : x(p[0]), y(p[1]), z(p[2]) {}
+    float operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
+};
+inline V3 operator+(V3 a, V3 b) { return V3(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline V3 operator-(V3 a, V3 b) { return V3(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline V3 operator-(V3 a) { return V3(-a.x, -a.y, -a.z); }
+inline V3 operator*(V3 a, float s) { return V3(a.x * s, a.y * s, a.z * s); }
+inline V3 operator*(float s, V3 a) { return V3(a.x * s, a.y * s, a.z * s); }
+inline V3 operator*(V3 a, V3 b) { return V3(a.x * b.x, a.y * b.y, a.z * b.z); }
+inline V3 operator/(V3 a, float s) { return V3(a.x / s, a.y / s, a.z / s); }
+/* dot = (x*x' + y*y') + z*z' : defined summation order of this oracle */
+inline float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline V3 cross(V3 a, V3 b) {
+    return V3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+inline float squared_norm(V3 a) { return dot(a, a); }
+inline float norm(V3 a) { return std::sqrt(dot(a, a)); }
+inline V3 normalize(V3 a) { return a / norm(a); }
+inline float safe_sqrt(float x) { return std::sqrt(std::max(x, 0.0f)); }
+/* enoki::lerp = fmadd(b, t, fnmadd(a, t, a)) (array_math.h:1352); same order, uncontracted */
+inline float lerp(float a, float b, float t) { return b * t + (a - a * t); }
+inline float clampf(float v, float lo, float hi) { return std::min(std::max(v, lo), hi); }
+inline float hmax_abs(V3 p) { return std::max(std::fabs(p.x), std::max(std::fabs(p.y), std::fabs(p.z))); }
+
+constexpr float kEpsilon       = 5.9604644775390625e-08f;   /* math::Epsilon<float> = eps/2, math.h:36 */
+constexpr float kRayEpsilon    = kEpsilon * 1500.0f;        /* math.h:37 */
+constexpr float kShadowEpsilon = kRayEpsilon * 10.0f;       /* math.h:38 */
+constexpr float kInf           = std::numeric_limits<float>::infinity();
+constexpr float kInvFourPi     = 0.07957747154594766788f;
+
+/* ------------------------------------------------------------------------------------------ */
+/*  PCG32 -- ext/enoki/include/enoki/random.h:62-77 (seed), 69-77 (next_uint32),              */
+/*  117-119 (next_float32), 265-286 (advance)                                                  */
+/* ------------------------------------------------------------------------------------------ */
+constexpr uint64_t PCG32_DEFAULT_STATE  = 0x853c49e6748fea9bULL;
+constexpr uint64_t PCG32_DEFAULT_STREAM = 0xda3e39cb94b95bdbULL;
+constexpr uint64_t PCG32_MULT           = 0x5851f42d4c957f2dULL;
+
+struct Pcg32 {
+    uint64_t state, inc;
+    void seed(uint64_t initstate, uint64_t initseq) {
+        state = 0;
+        inc   = (initseq << 1) | 1u;
+        next_u32();
+        state += initstate;
+        next_u32();
+    }
+    uint32_t next_u32() {
+        uint64_t old = state;
+        state        = old * PCG32_MULT + inc;
+        uint32_t xorshifted = (uint32_t) (((old >> 18) ^ old) >> 27);
+        uint32_t rot        = (uint32_t) (old >> 59);
+        return (xorshifted >> rot) | (xorshifted << ((32 - rot) & 31));
+    }
+    float next_f32() {
+        uint32_t bits = (next_u32() >> 9) | 0x3f800000u;
+        float f;
+        std::memcpy(&f, &bits, 4);
+        return f - 1.0f;
+    }
+    void advance(int64_t delta_) {
+        uint64_t cur_mult = PCG32_MULT, cur_plus = inc, acc_mult = 1, acc_plus = 0;
+        uint64_t delta = (uint64_t) delta_;
+        while (delta != 0) {
+            if (delta & 1) {
+                acc_mult *= cur_mult;
+                acc_plus = acc_plus * cur_mult + cur_plus;
+            }
+            cur_plus = (cur_mult + 1) * cur_plus;
+            cur_mult *= cur_mult;
+            delta >>= 1;
+        }
+        state = acc_mult * state + acc_plus;
+    }
+};
+
+/* IndependentSampler over PCG32Sampler::seed (sampler.cpp:83-96): scalar variant seeds
+ * m_rng.seed(base_seed + seed_offset, PCG32_DEFAULT_STREAM). */
+struct Sampler {
+    Pcg32 rng;
+    void seed(uint64_t base_seed, uint64_t seed_offset) { rng.seed(base_seed + seed_offset, PCG32_DEFAULT_STREAM); }
+    float next_1d() { return rng.next_f32(); }
+};
+
+/* enoki::morton_decode<Point2u> (ext/enoki/include/enoki/morton.h:148-155): x = even bits, y = odd bits */
+inline uint32_t compact_bits(uint32_t v) {
+    v &= 0x55555555u;
+    v = (v | (v >> 1)) & 0x33333333u;
+    v = (v | (v >> 2)) & 0x0f0f0f0fu;
+    v = (v | (v >> 4)) & 0x00ff00ffu;
+    v = (v | (v >> 8)) & 0x0000ffffu;
+    return v;
+}
+
+/* Spiral::Spiral/reset/next_block (src/librender/spiral.cpp:8-72): ids in spiral order from the centre */
+std::vector<uint32_t> spiral_ids(int w, int h, int bs, int &nbx, int &nby) {
+    nbx = (w + bs - 1) / bs;
+    nby = (h + bs - 1) / bs;
+    int count = nbx * nby;
+    std::vector<uint32_t> ids((size_t) count, 0u);
+    int px = nbx / 2, py = nby / 2, dir = 0 /* Right */, steps_left = 1, steps = 1;
+    for (int counter = 0; counter < count; ++counter) {
+        ids[(size_t) py * nbx + px] = (uint32_t) counter;
+        if (counter + 1 != count) {
+            do {
+                switch (dir) {
+                    case 0: ++px; break;   /* Right */
+                    case 1: ++py; break;   /* Down  */
+                    case 2: --px; break;   /* Left  */
+                    case 3: --py; break;   /* Up    */
+                }
+                if (--steps_left == 0) {
+                    dir = (dir + 1) % 4;
+                    if (dir == 2 || dir == 0)
+                        ++steps;
+                    steps_left = steps;
+                }
+            } while (px < 0 || py < 0 || px >= nbx || py >= nby);
+        }
+    }
+    return ids;
+}
+
+}  // namespace
+
+extern "C" {
+
+void vrlo_pcg32_seed(uint64_t initstate, uint64_t initseq, uint64_t *state, uint64_t *inc) {
+    Pcg32 r; r.seed(initstate, initseq); *state = r.state; *inc = r.inc;
+}
+uint32_t vrlo_pcg32_next_u32(uint64_t *state, uint64_t inc) {
+    Pcg32 r{ *state, inc }; uint32_t v = r.next_u32(); *state = r.state; return v;
+}
+float vrlo_pcg32_next_f32(uint64_t *state, uint64_t inc) {
+    Pcg32 r{ *state, inc }; float v = r.next_f32(); *state = r.state; return v;
+}
+void vrlo_pcg32_advance(uint64_t *state, uint64_t inc, int64_t delta) {
+    Pcg32 r{ *state, inc }; r.advance(delta); *state = r.state;
+}
+void vrlo_sampler_stream(uint64_t base_seed, uint64_t seed_offset, uint32_t n, float *out_f, uint32_t *out_u) {
+    Sampler s; s.seed(base_seed, seed_offset);
+    for (uint32_t i = 0; i < n; ++i) {
+        Pcg32 copy = s.rng;
+        if (out_u) out_u[i] = copy.next_u32();
+        float f = s.next_1d();
+        if (out_f) out_f[i] = f;
+    }
+}
+uint32_t vrlo_spiral_block_ids(int32_t width, int32_t height, int32_t block_size, uint32_t *block_id, uint32_t cap) {
+    int nbx, nby;
+    std::vector<uint32_t> ids = spiral_ids(width, height, block_size, nbx, nby);
+    for (size_t i = 0; i < ids.size() && i < cap; ++i) block_id[i] = ids[i];
+    return (uint32_t) ids.size();
+}
+void vrlo_morton_decode(uint32_t i, uint32_t *x, uint32_t *y) {
+    *x = compact_bits(i);
+    *y = compact_bits(i >> 1);
+}
+
+}  // extern "C"
+
+namespace {
+
+/* ------------------------------------------------------------------------------------------ */
+/*  Scene: triangle soup + a conservative BVH (stands in for ShapeKDTree, kdtree.h:2069-2172;  */
+/*  only the set of triangle hits matters, and that is decided by the exact test below).      */
+/* ------------------------------------------------------------------------------------------ */
+struct Tri { V3 p0, p1, p2; uint32_t flags; };
+
+struct BvhNode { float lo[3], hi[3]; int left, right, first, count, axis; };
+
+struct Hit { float t, u, v; int prim; bool valid() const { return prim >= 0; } };
+
+}  // namespace
+
+struct vrlo_scene {
+    std::vector<Tri> tris;
+    std::vector<vrlb_medium> media;
+    std::vector<std::vector<float>> grids;
+    std::vector<vrlb_emitter> emitters;
+    std::vector<BvhNode> nodes;
+    std::vector<int> order;
+    float pad = 0.f;
+};
+
+namespace {
+
+/* Mesh::ray_intersect_triangle, include/mitsuba/render/mesh.h:195-225 (Moeller-Trumbore) */
+inline bool intersect_tri(const Tri &tr, V3 o, V3 d, float mint, float maxt, float &t, float &u, float &v) {
+    V3 e1 = tr.p1 - tr.p0, e2 = tr.p2 - tr.p0;
+    V3 pvec       = cross(d, e2);
+    float inv_det = 1.0f / dot(e1, pvec);
+    V3 tvec       = o - tr.p0;
+    u             = dot(tvec, pvec) * inv_det;
+    if (!(u >= 0.f && u <= 1.f)) return false;
+    V3 qvec = cross(tvec, e1);
+    v       = dot(d, qvec) * inv_det;
+    if (!(v >= 0.f && u + v <= 1.f)) return false;
+    t = dot(e2, qvec) * inv_det;
+    if (!(t >= mint && t <= maxt)) return false;
+    return true;
+}
+
+void build_bvh(vrlo_scene &s) {
+    size_t n = s.tris.size();
+    s.order.resize(n);
+    for (size_t i = 0; i < n; ++i) s.order[i] = (int) i;
+    s.nodes.clear();
+    if (n == 0) return;
+    float diag_lo[3] = { kInf, kInf, kInf }, diag_hi[3] = { -kInf, -kInf, -kInf };
+    for (auto &t : s.tris)
+        for (int k = 0; k < 3; ++k) {
+            float a = std::min(t.p0[k], std::min(t.p1[k], t.p2[k])), b = std::max(t.p0[k], std::max(t.p1[k], t.p2[k]));
+            diag_lo[k] = std::min(diag_lo[k], a); diag_hi[k] = std::max(diag_hi[k], b);
+        }
+    float ext = 0.f;
+    for (int k = 0; k < 3; ++k) ext = std::max(ext, std::max(std::fabs(diag_lo[k]), std::fabs(diag_hi[k])));
+    s.pad = 1e-4f * ext + 1e-6f;   /* conservative: boxes only ever admit more triangles to the exact test */
+
+    struct Item { int begin, end, node; };
+    std::vector<Item> stack;
+    s.nodes.push_back(BvhNode());
+    stack.push_back({ 0, (int) n, 0 });
+    while (!stack.empty()) {
+        Item it = stack.back(); stack.pop_back();
+        BvhNode nd;
+        float clo[3] = { kInf, kInf, kInf }, chi[3] = { -kInf, -kInf, -kInf };
+        for (int k = 0; k < 3; ++k) { nd.lo[k] = kInf; nd.hi[k] = -kInf; }
+        for (int i = it.begin; i < it.end; ++i) {
+            const Tri &t = s.tris[s.order[i]];
+            for (int k = 0; k < 3; ++k) {
+                float a = std::min(t.p0[k], std::min(t.p1[k], t.p2[k])), b = std::max(t.p0[k], std::max(t.p1[k], t.p2[k]));
+                nd.lo[k] = std::min(nd.lo[k], a); nd.hi[k] = std::max(nd.hi[k], b);
+                float c = (t.p0[k] + t.p1[k] + t.p2[k]) / 3.0f;
+                clo[k] = std::min(clo[k], c); chi[k] = std::max(chi[k], c);
+            }
+        }
+        for (int k = 0; k < 3; ++k) { nd.lo[k] -= s.pad; nd.hi[k] += s.pad; }
+        nd.left = nd.right = -1; nd.first = it.begin; nd.count = it.end - it.begin; nd.axis = 0;
+        if (nd.count > 4) {
+            /* binned SAH over the three axes (16 bins on centroids); falls back to the median */
+            auto tri_lohi = [&](int idx, int k, float &a, float &b) {
+                const Tri &t = s.tris[idx];
+                a = std::min(t.p0[k], std::min(t.p1[k], t.p2[k])); b = std::max(t.p0[k], std::max(t.p1[k], t.p2[k]));
+            };
+            auto centroid = [&](int idx, int k) { const Tri &t = s.tris[idx]; return (t.p0[k] + t.p1[k] + t.p2[k]) / 3.0f; };
+            const int NB = 16;
+            int axis = -1, best_bin = -1; float best_cost = kInf;
+            for (int k = 0; k < 3; ++k) {
+                float ext = chi[k] - clo[k];
+                if (!(ext > 0.f)) continue;
+                int cnt[NB] = { 0 }; float blo[NB][3], bhi[NB][3];
+                for (int b = 0; b < NB; ++b) for (int c = 0; c < 3; ++c) { blo[b][c] = kInf; bhi[b][c] = -kInf; }
+                for (int i = it.begin; i < it.end; ++i) {
+                    int idx = s.order[i];
+                    int b = std::min(NB - 1, (int) ((centroid(idx, k) - clo[k]) / ext * NB));
+                    cnt[b]++;
+                    for (int c = 0; c < 3; ++c) { float a, bb; tri_lohi(idx, c, a, bb); blo[b][c] = std::min(blo[b][c], a); bhi[b][c] = std::max(bhi[b][c], bb); }
+                }
+                auto area = [](const float *lo, const float *hi) {
+                    float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+                    return (dx < 0 || dy < 0 || dz < 0) ? 0.f : 2.f * (dx * dy + dy * dz + dz * dx);
+                };
+                float la[NB], ra[NB]; int lc[NB], rc[NB];
+                float lo3[3] = { kInf, kInf, kInf }, hi3[3] = { -kInf, -kInf, -kInf }; int c0 = 0;
+                for (int b = 0; b < NB; ++b) { for (int c = 0; c < 3; ++c) { lo3[c] = std::min(lo3[c], blo[b][c]); hi3[c] = std::max(hi3[c], bhi[b][c]); } c0 += cnt[b]; la[b] = area(lo3, hi3); lc[b] = c0; }
+                for (int c = 0; c < 3; ++c) { lo3[c] = kInf; hi3[c] = -kInf; } c0 = 0;
+                for (int b = NB - 1; b >= 0; --b) { for (int c = 0; c < 3; ++c) { lo3[c] = std::min(lo3[c], blo[b][c]); hi3[c] = std::max(hi3[c], bhi[b][c]); } c0 += cnt[b]; ra[b] = area(lo3, hi3); rc[b] = c0; }
+                for (int b = 0; b + 1 < NB; ++b) {
+                    if (lc[b] == 0 || rc[b + 1] == 0) continue;
+                    float cost = la[b] * lc[b] + ra[b + 1] * rc[b + 1];
+                    if (cost < best_cost) { best_cost = cost; axis = k; best_bin = b; }
+                }
+            }
+            int mid;
+            if (axis >= 0) {
+                float ext = chi[axis] - clo[axis];
+                auto bin_of = [&](int idx) { return std::min(NB - 1, (int) ((centroid(idx, axis) - clo[axis]) / ext * NB)); };
+                auto itp = std::stable_partition(s.order.begin() + it.begin, s.order.begin() + it.end, [&](int idx) { return bin_of(idx) <= best_bin; });
+                mid = (int) (itp - s.order.begin());
+            } else {
+                axis = 0; mid = (it.begin + it.end) / 2;
+            }
+            nd.count = 0; nd.axis = axis;
+            nd.left  = (int) s.nodes.size(); s.nodes.push_back(BvhNode());
+            nd.right = (int) s.nodes.size(); s.nodes.push_back(BvhNode());
+            stack.push_back({ it.begin, mid, nd.left });
+            stack.push_back({ mid, it.end, nd.right });
+        }
+        s.nodes[it.node] = nd;
+    }
+}
+
+inline bool slab(const BvhNode &nd, V3 o, V3 inv, float mint, float maxt) {
+    float t0 = mint, t1 = maxt;
+    for (int k = 0; k < 3; ++k) {
+        float a = (nd.lo[k] - o[k]) * inv[k], b = (nd.hi[k] - o[k]) * inv[k];
+        float tn = std::fmin(a, b), tf = std::fmax(a, b);   /* fmin/fmax drop NaNs (0 * inf) */
+        t0 = std::fmax(t0, tn); t1 = std::fmin(t1, tf);
+    }
+    return t0 <= t1 * 1.00001f + 1e-6f;
+}
+
+/* Scene::ray_intersect (scene.cpp:114-131): closest hit in [mint, maxt]; ties -> lowest prim index */
+Hit ray_intersect(const vrlo_scene &s, V3 o, V3 d, float mint, float maxt) {
+    Hit best{ kInf, 0.f, 0.f, -1 };
+    if (s.nodes.empty()) return best;
+    V3 inv(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    int stack[128], sp = 0;
+    stack[sp++] = 0;
+    while (sp) {
+        const BvhNode &nd = s.nodes[stack[--sp]];
+        float far = best.valid() ? best.t : maxt;
+        if (!slab(nd, o, inv, mint, far)) continue;
+        if (nd.left < 0) {
+            for (int i = nd.first; i < nd.first + nd.count; ++i) {
+                int prim = s.order[i];
+                float t, u, v;
+                if (intersect_tri(s.tris[prim], o, d, mint, maxt, t, u, v)) {
+                    if (t < best.t || (t == best.t && prim < best.prim)) best = Hit{ t, u, v, prim };
+                }
+            }
+        } else {
+            /* near child last on the stack = visited first (left holds the smaller centroids) */
+            if (d[nd.axis] >= 0.f) { stack[sp++] = nd.right; stack[sp++] = nd.left; }
+            else                   { stack[sp++] = nd.left;  stack[sp++] = nd.right; }
+        }
+    }
+    return best;
+}
+
+/* geometric normal of Mesh::compute_surface_interaction (mesh.cpp:477-487) */
+inline V3 tri_normal(const Tri &t) { return normalize(cross(t.p1 - t.p0, t.p2 - t.p0)); }
+/* si.p re-interpolated from barycentrics (mesh.cpp:467-484) */
+inline V3 tri_point(const Tri &t, float b1, float b2) {
+    float b0 = 1.f - b1 - b2;
+    return t.p0 * b0 + t.p1 * b1 + t.p2 * b2;
+}
+/* SurfaceInteraction::target_medium (interaction.h:186-200): exterior when cos > 0 else interior */
+inline int target_medium(const Tri &t, V3 d) {
+    return dot(d, tri_normal(t)) > 0.f ? VRLB_SURF_GET_EXTERIOR(t.flags) : VRLB_SURF_GET_INTERIOR(t.flags);
+}
+inline bool is_medium_transition(const Tri &t) {
+    return VRLB_SURF_GET_EXTERIOR(t.flags) >= 0 || VRLB_SURF_GET_INTERIOR(t.flags) >= 0;
+}
+inline bool is_null(const Tri &t) { return (t.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_NULL; }
+
+/* ------------------------------------------------------------------------------------------ */
+/*  Media and phase functions                                                                 */
+/* ------------------------------------------------------------------------------------------ */
+/* ConstVolume::max() returns the MEAN of the colour (constant3d.cpp:37, srgb.h mean) and
+ * m_max_density = scale * sigma_t->max() (homogeneous.cpp:26, nonlinear.cpp:53): grey extinction */
+inline float max_density(const vrlb_medium &m) {
+    if (m.kind == VRLB_MEDIUM_GRID) return m.scale * m.grid_max;             /* heterogeneous.cpp:29 */
+    float mean = (m.sigma_t[0] + m.sigma_t[1] + m.sigma_t[2]) / 3.0f;        /* hmean */
+    return m.scale * mean;
+}
+inline bool is_homogeneous(const vrlb_medium &m) { return m.kind != VRLB_MEDIUM_GRID; }
+
+/* Medium::evalTransmittance, homogeneous branch (medium.h:112-117) and homoEvalTransmittance (103-107) */
+inline float homo_transmittance(const vrlb_medium &m, float mint, float maxt) {
+    float md        = max_density(m);
+    float negLength = mint - maxt;
+    float val       = std::exp(md * negLength);
+    return md != 0.f ? val : 1.0f;
+}
+
+/* get_scattering_coefficients: sigma_s = scale*sigma_t*albedo (homogeneous.cpp:42-50, nonlinear.cpp:414-420) */
+inline V3 sigma_s_const(const vrlb_medium &m) {
+    V3 sigmat = V3(m.sigma_t) * m.scale;
+    return sigmat * V3(m.albedo);
+}
+
+/* IsotropicPhaseFunction::eval = square_to_uniform_sphere_pdf = 1/(4 pi) (isotropic.cpp:40-44);
+ * HGPhaseFunction::eval = eval_hg(dot(wo, mi.wi)) (hg.cpp:51-54, 77-81) */
+inline float phase_eval(const vrlb_medium &m, V3 wi, V3 wo) {
+    if (m.phase == VRLB_PHASE_ISOTROPIC) return kInvFourPi;
+    float g = m.g, cos_theta = dot(wo, wi);
+    float temp = 1.0f + g * g + 2.0f * g * cos_theta;
+    return kInvFourPi * (1 - g * g) / (temp * std::sqrt(temp));
+}
+
+}  // namespace
+
+namespace {
+
+/* ------------------------------------------------------------------------------------------ */
+/*  VRL (vrl_struct.h:60-86, 664-677) and camera ray part                                     */
+/* ------------------------------------------------------------------------------------------ */
+struct Vrl { V3 origin, direction; float length; V3 flux; int medium; };
+struct Ray { V3 o, d; float maxt; };
+
+struct ClosestPointInfo { float tCam, tVRL; };
+
+/* VRL::findClosetPoint, vrl_struct.h:163-228 */
+ClosestPointInfo find_closest_point(const Vrl &vrl, const Ray &r) {
+    V3 u = vrl.direction * vrl.length;
+    V3 v = r.d * r.maxt;
+    V3 w = vrl.origin - r.o;
+
+    float a = dot(u, u), b = dot(u, v), c = dot(v, v), d = dot(u, w), e = dot(v, w);
+    float D = a * c - b * b;
+    float sc, sN, sD = D;
+    float tc, tN, tD = D;
+
+    if (D < 0.0001f) {
+        sN = 0.0f; sD = 1.0f; tN = e; tD = c;
+    } else {
+        sN = (b * e - c * d);
+        tN = (a * e - b * d);
+        if (sN < 0.0f) {
+            sN = 0.0f; tN = e; tD = c;
+        } else if (sN > sD) {
+            sN = sD; tN = e + b; tD = c;
+        }
+    }
+
+    if (tN < 0.0f) {
+        tN = 0.0f;
+        if (-d < 0.0f)      sN = 0.0f;
+        else if (-d > a)    sN = sD;
+        else { sN = -d; sD = a; }
+    } else if (tN > tD) {
+        tN = tD;
+        if ((-d + b) < 0.0f)    sN = 0;
+        else if ((-d + b) > a)  sN = sD;
+        else { sN = (-d + b); sD = a; }
+    }
+
+    sc = (std::fabs(sN) < 0.0001f ? 0.0f : sN / sD);
+    tc = (std::fabs(tN) < 0.0001f ? 0.0f : tN / tD);
+    return ClosestPointInfo{ tc * r.maxt, sc * vrl.length };
+}
+
+struct SamplingInfo { V3 pCam; float tCam; V3 pVRL; float tVRL; float invPDF; bool valid; };
+inline SamplingInfo sampling_invalid() { return SamplingInfo{ V3(0.f), 0.f, V3(0.f), 0.f, 0.f, false }; }
+
+/* VRL::sampleMC, vrl_struct.h:239-243, with NLRay::at (44-56) for a single part */
+SamplingInfo sample_mc(const Vrl &vrl, const Ray &ray, float u1, float u2) {
+    float tCam = u1 * ray.maxt;
+    float tVRL = u2 * vrl.length;
+    return SamplingInfo{ ray.o + ray.d * tCam, tCam, vrl.origin + vrl.direction * tVRL, tVRL, vrl.length * ray.maxt, true };
+}
+
+/* Source of the two uniforms: draws lazily so that the sequential mode consumes exactly what the
+ * reference consumes (no draw before the early-outs at vrl_struct.h:264, 275). */
+struct DrawSrc {
+    Pcg32 *rng;        /* non-null: draw from the stream */
+    float u[2];        /* else: explicit uniforms        */
+    int k;
+    float next() { return rng ? rng->next_f32() : u[k++]; }
+};
+
+/* VRL::samplingVRL importance branch, vrl_struct.h:251-360 (the `if (true)` arm) */
+SamplingInfo sampling_vrl(const Vrl &vrl, const Ray &ray, bool uniform, DrawSrc &draws) {
+    if (uniform) {
+        float u1 = draws.next(), u2 = draws.next();
+        return sample_mc(vrl, ray, u1, u2);
+    }
+    ClosestPointInfo cp = find_closest_point(vrl, ray);
+    float h;
+    {
+        V3 vh = vrl.origin + vrl.direction * cp.tVRL;
+        V3 uh = ray.o + ray.d * cp.tCam;
+        h     = squared_norm(uh - vh);
+    }
+    if (h == 0.0f) return sampling_invalid();
+    h = safe_sqrt(h);
+
+    float v0Hat = -cp.tVRL;
+    float v1Hat = vrl.length + v0Hat;
+
+    float sinTheta = squared_norm(cross(vrl.direction, ray.d));
+    if (sinTheta == 0) return sampling_invalid();
+    sinTheta = safe_sqrt(sinTheta);
+
+    /* inverseCDF_A, vrl_struct.h:293-310 */
+    auto A = [](float x, float h, float sinTheta) -> float {
+        float value = (x / h) * sinTheta;
+        return std::log(value + std::sqrt(value * value + 1));
+    };
+    float r  = draws.next();
+    float a0 = A(v0Hat, h, sinTheta);
+    float a1 = A(v1Hat, h, sinTheta);
+    float vHat = (h * std::sinh(lerp(a0, a1, r))) / sinTheta;
+    float invPDF_A = (a1 - a0) * std::sqrt(h * h + vHat * vHat * sinTheta * sinTheta);
+    invPDF_A /= sinTheta;
+
+    float tVRL = (vHat + cp.tVRL);
+    V3 pVRL    = vrl.origin + vrl.direction * tVRL;
+
+    /* Kulla-Fajardo equi-angular on the camera ray, vrl_struct.h:318-336 */
+    float uHat  = dot(ray.d, (pVRL - ray.o));
+    float u0Hat = -uHat;
+    float u1Hat = ray.maxt + u0Hat;
+    float hPoint = norm(ray.o + ray.d * uHat - pVRL);
+    float eps    = draws.next();
+    float thetaA = std::atan(u0Hat / hPoint);
+    float thetaB = std::atan(u1Hat / hPoint);
+    float uS     = hPoint * std::tan(lerp(thetaA, thetaB, eps));
+    float invPDF_B = (thetaB - thetaA) * (hPoint * hPoint + uS * uS) / hPoint;
+    float tCam = (uS - u0Hat);
+    V3 pCam    = ray.o + ray.d * tCam;
+
+    tCam = clampf(tCam, 0.0f, ray.maxt);      /* vrl_struct.h:340-341 */
+    tVRL = clampf(tVRL, 0.0f, vrl.length);
+    return SamplingInfo{ pCam, tCam, pVRL, tVRL, invPDF_A * invPDF_B, true };
+}
+
+/* Medium::evalTransmittance over [0, t] along a ray (medium.h:109-155).  Homogeneous / nonlinear
+ * media: analytic grey exponential.  Grid media: see grid_transmittance() (part 5). */
+float grid_transmittance(const vrlo_scene &s, const vrlb_medium &m, int medium_id, V3 o, V3 d, float maxt, Pcg32 *sub);
+
+inline float medium_transmittance(const vrlo_scene &s, int medium_id, V3 o, V3 d, float maxt, Pcg32 *sub) {
+    const vrlb_medium &m = s.media[(size_t) medium_id];
+    if (is_homogeneous(m)) return homo_transmittance(m, 0.f, maxt);
+    return grid_transmittance(s, m, medium_id, o, d, maxt, sub);
+}
+
+/* VRL::evalTransmittance (static), vrl_struct.h:509-572, called with p1OnSurface = p2OnSurface =
+ * false and interactions = -1 (vrl_struct.h:630-632).  Grey result (all media return grey Tr).
+ * Note Null::eval returns 0 (src/bsdfs/null.cpp:59-62): crossing ANY surface zeroes the result. */
+float eval_transmittance(const vrlo_scene &s, bool trace, V3 p1, V3 p2, int medium_, Pcg32 *sub) {
+    V3 d            = p2 - p1;
+    float remaining = norm(d);
+    d               = normalize(d);
+    float lengthFactor = 1.f;
+    V3 ro = p1; float mint = 0.f, maxt = remaining * lengthFactor;
+    float transmittance = 1.0f;
+    int interactions = 0;
+    int medium = medium_;
+    while (remaining > 0) {
+        Hit si = trace ? ray_intersect(s, ro, d, mint, maxt) : Hit{ kInf, 0, 0, -1 };
+        bool surface = si.valid();
+        if (surface && !is_null(s.tris[(size_t) si.prim])) return 0.0f;
+        if (medium >= 0)
+            transmittance *= medium_transmittance(s, medium, ro, d, std::min(si.t, remaining), sub);
+        if (!surface || transmittance == 0.0f) break;
+        const Tri &tr = s.tris[(size_t) si.prim];
+        transmittance *= 0.0f;                       /* bsdf->eval of the Null BSDF, null.cpp:59-62 */
+        if (is_medium_transition(tr)) {
+            if (medium != target_medium(tr, -d)) return 0.0f;
+            medium = target_medium(tr, d);
+        }
+        if (++interactions > 100) break;
+        ro = ro + d * si.t;
+        remaining -= si.t;
+        maxt = remaining * lengthFactor;
+        mint = kEpsilon;
+    }
+    return transmittance;
+}
+
+/* VRL::getContrib, vrl_struct.h:584-662.  `wi` is NLRay::wi: the reference leaves it unset on the
+ * importance path (quirk 1); defined here as -part.d, the commented-out intent (:611). */
+V3 get_contrib(const vrlo_scene &s, bool trace, const Vrl &vrl, const Ray &ray, bool uniform, DrawSrc &draws, Pcg32 *sub) {
+    SamplingInfo sampling = sampling_vrl(vrl, ray, uniform, draws);
+    /* invalid() has pCam == pVRL == 0 -> lengthPtoP == 0 -> 0 */
+    V3 dir           = sampling.pVRL - sampling.pCam;
+    float lengthPtoP = norm(dir);
+    if (lengthPtoP == 0) return V3(0.f);
+    if (std::isnan(sampling.invPDF)) return V3(0.f);
+    dir = dir / lengthPtoP;
+
+    const vrlb_medium &m = s.media[(size_t) vrl.medium];
+    V3 wi       = -ray.d;
+    float rayPF = phase_eval(m, wi, dir);
+    if (rayPF == 0) return V3(0.f);
+    V3 sigmaSRay = sigma_s_const(m);
+
+    float vrlPF = phase_eval(m, -vrl.direction, -dir);
+    if (vrlPF == 0) return V3(0.f);
+    V3 sigmaSVRL = sigma_s_const(m);
+
+    float vrlToRayTrans = eval_transmittance(s, trace, sampling.pCam, sampling.pVRL, vrl.medium, sub);
+    if (vrlToRayTrans == 0.0f) return V3(0.f);
+    float rayTrans = medium_transmittance(s, vrl.medium, ray.o, ray.d, sampling.tCam, sub);
+    if (rayTrans == 0.0f) return V3(0.f);
+    float vrlTrans = medium_transmittance(s, vrl.medium, vrl.origin, vrl.direction, sampling.tVRL, sub);
+    if (vrlTrans == 0.0f) return V3(0.f);
+
+    float fallOff = 1.0f / (lengthPtoP * lengthPtoP);
+    V3 result = vrl.flux * fallOff * vrlPF * rayPF * V3(vrlTrans) * V3(rayTrans) * V3(vrlToRayTrans)
+                * sigmaSRay * sigmaSVRL * sampling.invPDF;
+    return result;
+}
+
+inline Vrl load_vrl(const vrlb_vrlset_desc &set, uint64_t j) {
+    const float *c = set.soa10; uint64_t n = set.n;
+    Vrl v;
+    v.origin    = V3(c[0 * n + j], c[1 * n + j], c[2 * n + j]);
+    v.direction = V3(c[3 * n + j], c[4 * n + j], c[5 * n + j]);
+    v.length    = c[6 * n + j];
+    v.flux      = V3(c[7 * n + j], c[8 * n + j], c[9 * n + j]);
+    v.medium    = set.medium ? (int) set.medium[j] : 0;
+    return v;
+}
+
+}  // namespace
+
+namespace {
+
+/* VRLMap::query, no-acceleration branch, vrl_map.h:133-211, for ONE camera part.
+ * `rng` is the pixel's stream positioned at the first draw of this query.  In sequential mode it
+ * is consumed exactly as the reference consumes it; in addressed mode eval (s, j) uses the draws at
+ * offset ((s*total + first_index + j) * dpe) and the stream is left after q*total*dpe draws.
+ * Li32: reference's sequential fp32 sum.  Li64: same fp32 contributions summed in fp64. */
+uint64_t query(const vrlo_scene &s, const vrlb_vrlset_desc &set, const Ray &ray, const vrlb_options &opt,
+               int rng_mode, Pcg32 &rng, V3 &Li32, double Li64[3]) {
+    Li32 = V3(0.f); Li64[0] = Li64[1] = Li64[2] = 0.0;
+    if (set.n == 0) return 0;
+    const bool uniform = opt.use_uniform_sampling != 0, rr = opt.rr_vrl != 0, trace = opt.visibility != 0;
+    const uint32_t q   = (uint32_t) std::max(opt.samples_per_query, 1);
+    const uint64_t dpe = rr ? 3u : 2u;
+    const uint64_t total = set.total ? set.total : set.n;
+    const Pcg32 base = rng;
+    uint64_t evals = 0;
+
+    for (uint32_t i = 0; i < q; ++i) {
+        Pcg32 cursor = base;
+        if (rng_mode == VRLO_RNG_ADDRESSED)
+            cursor.advance((int64_t) (((uint64_t) i * total + set.first_index) * dpe));
+        for (uint64_t j = 0; j < set.n; ++j) {
+            Vrl vrl = load_vrl(set, j);
+            Pcg32 eval_rng = cursor;
+            Pcg32 *r;
+            if (rng_mode == VRLO_RNG_ADDRESSED) {
+                eval_rng = cursor;
+                for (uint64_t k = 0; k < dpe; ++k) cursor.next_u32();
+                r = &eval_rng;
+            } else {
+                r = &rng;
+            }
+            /* grid-medium transmittance sub-stream (addressed mode only): keyed by the eval */
+            Pcg32 sub; sub.seed(eval_rng.state, PCG32_DEFAULT_STREAM + 1);
+            Pcg32 *subp = (rng_mode == VRLO_RNG_ADDRESSED) ? &sub : r;
+            DrawSrc draws{ r, { 0.f, 0.f }, 0 };
+            V3 contrib;
+            if (!rr) {
+                contrib = get_contrib(s, trace, vrl, ray, uniform, draws, subp) * set.scale;
+            } else {
+                /* EDistanceRoulette, vrl_map.h:171-190 */
+                ClosestPointInfo res = find_closest_point(vrl, ray);
+                float d2 = squared_norm((ray.o + ray.d * res.tCam) - (vrl.origin + vrl.direction * res.tVRL));
+                float min_distance = std::sqrt(d2);
+                float rrWeight     = std::min(1 / (min_distance * opt.scale_rr), 1.0f);
+                if (rrWeight > r->next_f32())
+                    contrib = (get_contrib(s, trace, vrl, ray, uniform, draws, subp) / rrWeight) * set.scale;
+                else
+                    continue;   /* pruned */
+            }
+            ++evals;
+            if (std::isnan(contrib.x) || std::isnan(contrib.y) || std::isnan(contrib.z) ||
+                std::isinf(contrib.x) || std::isinf(contrib.y) || std::isinf(contrib.z))
+                continue;
+            Li32 = Li32 + contrib;
+            Li64[0] += (double) contrib.x; Li64[1] += (double) contrib.y; Li64[2] += (double) contrib.z;
+        }
+    }
+    if (rng_mode == VRLO_RNG_ADDRESSED) {
+        rng = base;
+        rng.advance((int64_t) ((uint64_t) q * total * dpe));
+    }
+    if (q > 1) {
+        Li32 = Li32 / (float) q;
+        for (int k = 0; k < 3; ++k) Li64[k] /= (double) q;
+    }
+    return evals;
+}
+
+template <typename F> void parallel_for(uint64_t n, int n_threads, F &&fn) {
+    if (n_threads <= 1 || n < 2) { for (uint64_t i = 0; i < n; ++i) fn(i); return; }
+    std::atomic<uint64_t> next{ 0 };
+    std::vector<std::thread> pool;
+    for (int t = 0; t < n_threads; ++t)
+        pool.emplace_back([&]() {
+            for (;;) {
+                uint64_t i = next.fetch_add(1);
+                if (i >= n) break;
+                fn(i);
+            }
+        });
+    for (auto &th : pool) th.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+void vrlo_find_closest_point(const float vrl_o[3], const float vrl_d[3], float vrl_len,
+                             const float ray_o[3], const float ray_d[3], float ray_maxt, float *tCam, float *tVRL) {
+    Vrl v{ V3(vrl_o), V3(vrl_d), vrl_len, V3(0.f), 0 };
+    Ray r{ V3(ray_o), V3(ray_d), ray_maxt };
+    ClosestPointInfo c = find_closest_point(v, r);
+    *tCam = c.tCam; *tVRL = c.tVRL;
+}
+
+int vrlo_sampling_vrl(const float vrl_o[3], const float vrl_d[3], float vrl_len,
+                      const float ray_o[3], const float ray_d[3], float ray_maxt,
+                      int uniform, float u1, float u2, float *out9) {
+    Vrl v{ V3(vrl_o), V3(vrl_d), vrl_len, V3(0.f), 0 };
+    Ray r{ V3(ray_o), V3(ray_d), ray_maxt };
+    DrawSrc draws{ nullptr, { u1, u2 }, 0 };
+    SamplingInfo si = sampling_vrl(v, r, uniform != 0, draws);
+    out9[0] = si.pCam.x; out9[1] = si.pCam.y; out9[2] = si.pCam.z; out9[3] = si.tCam;
+    out9[4] = si.pVRL.x; out9[5] = si.pVRL.y; out9[6] = si.pVRL.z; out9[7] = si.tVRL; out9[8] = si.invPDF;
+    return si.valid ? 1 : 0;
+}
+
+float vrlo_phase_eval(const vrlb_medium *m, const float wi[3], const float wo[3]) {
+    return phase_eval(*m, V3(wi), V3(wo));
+}
+
+void vrlo_get_contrib(const vrlb_scene_desc *scene, const vrlb_medium *m, const float vrl10[10],
+                      const float ray_o[3], const float ray_d[3], float ray_maxt,
+                      int uniform, float u1, float u2, float out_rgb[3]) {
+    vrlo_scene *s = nullptr;
+    vrlo_scene local;
+    if (scene) s = vrlo_scene_create(scene);
+    else { local.media.push_back(*m); }
+    const vrlo_scene &sc = s ? *s : local;
+    Vrl v{ V3(vrl10), V3(vrl10 + 3), vrl10[6], V3(vrl10 + 7), 0 };
+    Ray r{ V3(ray_o), V3(ray_d), ray_maxt };
+    DrawSrc draws{ nullptr, { u1, u2 }, 0 };
+    Pcg32 sub; sub.seed(0, PCG32_DEFAULT_STREAM + 1);
+    V3 c = get_contrib(sc, s != nullptr, v, r, uniform != 0, draws, &sub);
+    out_rgb[0] = c.x; out_rgb[1] = c.y; out_rgb[2] = c.z;
+    if (s) vrlo_scene_destroy(s);
+}
+
+vrlo_scene *vrlo_scene_create(const vrlb_scene_desc *desc) {
+    vrlo_scene *s = new vrlo_scene();
+    s->tris.resize(desc->n_tris);
+    for (uint32_t i = 0; i < desc->n_tris; ++i) {
+        const float *p = desc->tri_verts + (size_t) i * 9;
+        s->tris[i] = Tri{ V3(p), V3(p + 3), V3(p + 6), desc->tri_flags ? desc->tri_flags[i] : 0u };
+    }
+    s->media.assign(desc->media, desc->media + desc->n_media);
+    s->grids.resize(desc->n_media);
+    for (uint32_t i = 0; i < desc->n_media; ++i) {
+        vrlb_medium &m = s->media[i];
+        if (m.kind == VRLB_MEDIUM_GRID && m.grid) {
+            size_t n = (size_t) m.grid_res[0] * m.grid_res[1] * m.grid_res[2];
+            s->grids[i].assign(m.grid, m.grid + n);
+            m.grid = s->grids[i].data();
+        }
+    }
+    if (desc->emitters) s->emitters.assign(desc->emitters, desc->emitters + desc->n_emitters);
+    build_bvh(*s);
+    return s;
+}
+void vrlo_scene_destroy(vrlo_scene *s) { delete s; }
+
+int vrlo_ray_intersect(const vrlo_scene *s, const float o[3], const float d[3], float mint, float maxt,
+                       float *t, float *u, float *v) {
+    Hit h = ray_intersect(*s, V3(o), V3(d), mint, maxt);
+    *t = h.t; *u = h.u; *v = h.v;
+    return h.prim;
+}
+
+void vrlo_eval_transmittance(const vrlo_scene *s, const float p1[3], const float p2[3], int medium, float out_rgb[3]) {
+    Pcg32 sub; sub.seed(0, PCG32_DEFAULT_STREAM + 1);
+    float tr = eval_transmittance(*s, true, V3(p1), V3(p2), medium, &sub);
+    out_rgb[0] = out_rgb[1] = out_rgb[2] = tr;
+}
+
+uint64_t vrlo_gather_segments(const vrlo_scene *s, const vrlb_vrlset_desc *vrls, const vrlb_segment *segs,
+                              uint64_t n_segs, const vrlb_options *opt, int rng_mode, int n_threads,
+                              float *out_rgb32, double *out_rgb64) {
+    std::atomic<uint64_t> evals{ 0 };
+    parallel_for(n_segs, n_threads, [&](uint64_t i) {
+        const vrlb_segment &sg = segs[i];
+        Ray ray{ V3(sg.o), V3(sg.d), sg.maxt };
+        Pcg32 rng{ sg.rng_state, (PCG32_DEFAULT_STREAM << 1) | 1u };
+        V3 li; double li64[3];
+        evals += query(*s, *vrls, ray, *opt, rng_mode, rng, li, li64);
+        if (out_rgb32) { out_rgb32[i * 3 + 0] = li.x; out_rgb32[i * 3 + 1] = li.y; out_rgb32[i * 3 + 2] = li.z; }
+        if (out_rgb64) { out_rgb64[i * 3 + 0] = li64[0]; out_rgb64[i * 3 + 1] = li64[1]; out_rgb64[i * 3 + 2] = li64[2]; }
+    });
+    return evals.load();
+}
+
+}  // extern "C"
+
+namespace {
+
+/* ------------------------------------------------------------------------------------------ */
+/*  Grid ("heterogeneous") medium                                                             */
+/* ------------------------------------------------------------------------------------------ */
+/* BoundingBox::ray_intersect, include/mitsuba/core/bbox.h:302-325 */
+inline bool bbox_ray_intersect(const float lo[3], const float hi[3], V3 o, V3 d, float &mint, float &maxt) {
+    bool active = true;
+    float t1p[3], t2p[3];
+    for (int k = 0; k < 3; ++k) {
+        active = active && ((d[k] != 0.f) || ((o[k] > lo[k]) || (o[k] < hi[k])));
+        float rcp = 1.0f / d[k];
+        float t1 = (lo[k] - o[k]) * rcp, t2 = (hi[k] - o[k]) * rcp;
+        t1p[k] = std::fmin(t1, t2); t2p[k] = std::fmax(t1, t2);
+    }
+    mint = std::max(t1p[0], std::max(t1p[1], t1p[2]));
+    maxt = std::min(t2p[0], std::min(t2p[1], t2p[2]));
+    return active && maxt >= mint;
+}
+
+/* Medium::evalTransmittance, non-homogeneous branch, include/mitsuba/render/medium.h:119-154,
+ * with Medium::sample_interaction (src/librender/medium.cpp:36-75) and eval_tr_and_pdf (77-89)
+ * inlined.  Stochastic product of majorant transmittances over accepted free-flight steps (a8).
+ * Consumes 1 + (#steps + 1) draws from `sub`. */
+float grid_transmittance(const vrlo_scene &, const vrlb_medium &m, int, V3 o_, V3 d, float maxt_, Pcg32 *sub) {
+    float t = 0.f, maxt = maxt_;
+    float majorant = max_density(m);
+    (void) std::min(sub->next_f32() * 3.f, 2.f);   /* channel draw; the majorant is grey */
+    float si_t = maxt_;
+    float throughput = 1.0f;
+    V3 ro = o_; float rmint = 0.f, rmaxt = maxt_;
+    while (t < maxt) {
+        float sample = sub->next_f32();
+        float bmin, bmax;
+        bool active = bbox_ray_intersect(m.grid_bbox_min, m.grid_bbox_max, ro, d, bmin, bmax);
+        active = active && (std::isfinite(bmin) || std::isfinite(bmax));
+        if (!active) { bmin = 0.f; bmax = kInf; }
+        float mint = std::max(rmint, bmin), mx = std::min(rmaxt, bmax);
+        float sampled_t = mint + (-std::log(1 - sample) / majorant);
+        bool valid_mi   = active && (sampled_t <= mx);
+        float mi_t      = valid_mi ? sampled_t : kInf;
+        V3 mi_p         = ro + d * sampled_t;
+        if (!(mi_t < kInf)) break;                       /* !mi.is_valid() */
+        if (si_t < mi_t) mi_t = kInf;
+        float tt = std::min(mi_t, si_t) - mint;
+        throughput *= std::exp(-tt * majorant);
+        t += mi_t;
+        si_t -= mi_t;
+        ro    = mi_p;                                    /* mi.spawn_ray(_ray.d), interaction.h:58-61 */
+        rmint = (1.f + hmax_abs(mi_p)) * kRayEpsilon;
+        rmaxt = std::max(0.0f, maxt - t);
+    }
+    return throughput;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/*  Sensor: PerspectiveCamera::sample_ray_differential, src/sensors/perspective.cpp:183-216   */
+/*  Transform * Point / * Vector: include/mitsuba/core/transform.h:105-127 (column accumulate) */
+/* ------------------------------------------------------------------------------------------ */
+inline void camera_ray(const vrlb_camera &c, float sx, float sy, V3 &o, V3 &d, float &mint, float &maxt) {
+    const float *m = c.sample_to_camera;   /* row-major: m[r*4+c] */
+    float r[4];
+    for (int k = 0; k < 4; ++k) r[k] = m[k * 4 + 3];
+    for (int k = 0; k < 4; ++k) r[k] = m[k * 4 + 0] * sx + r[k];
+    for (int k = 0; k < 4; ++k) r[k] = m[k * 4 + 1] * sy + r[k];
+    for (int k = 0; k < 4; ++k) r[k] = m[k * 4 + 2] * 0.f + r[k];
+    V3 near_p(r[0] / r[3], r[1] / r[3], r[2] / r[3]);
+    V3 dl = normalize(near_p);
+    float inv_z = 1.0f / dl.z;
+    mint = c.near_clip * inv_z;
+    maxt = c.far_clip * inv_z;
+    const float *w = c.to_world;
+    o = V3(w[3], w[7], w[11]);
+    float q[3];
+    for (int k = 0; k < 3; ++k) q[k] = w[k * 4 + 0] * dl.x;
+    for (int k = 0; k < 3; ++k) q[k] = w[k * 4 + 1] * dl.y + q[k];
+    for (int k = 0; k < 3; ++k) q[k] = w[k * 4 + 2] * dl.z + q[k];
+    d = V3(q[0], q[1], q[2]);
+}
+
+/* What one camera sample hands to the VRL query */
+struct PartOut { Ray ray; V3 weight; int medium; uint32_t part; };
+
+struct SampleResult { V3 radiance; bool valid_ray; };
+
+/* VRLIntegrator::sample, src/integrators/vrl/vrl.cpp:443-732, for the surface classes of the
+ * ABI (null / smooth / emitter).  Photon-map terms (vrl.cpp:600-611, 671-680) are SURVEY 8f rank 3
+ * and contribute 0 here.  `on_query(part, rng)` is called once per NLRay part in reference order
+ * (vrl.cpp:613-629) with the sampler positioned at the query's first draw; it returns Li and must
+ * leave the sampler after the query. */
+template <typename OnQuery>
+SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler &sampler, V3 ro, V3 rd,
+                          float rmint, float rmaxt, int sensor_medium, OnQuery &&on_query) {
+    V3 radiance(0.f), throughput(1.f);
+    int medium = sensor_medium;
+    Hit si{ kInf, 0, 0, -1 };
+    bool valid_ray = false;                         /* no environment emitter in the ABI */
+    bool specular_chain = !opt.hide_emitters;
+    bool needs_intersection = true;
+    uint32_t depth = 1;
+    /* channel draw, vrl.cpp:476-479 */
+    (void) std::min(sampler.next_1d() * 3.f, 2.f);
+
+    for (int bounce = 0;; ++bounce) {
+        bool active = !(throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f);
+        if (!active || depth >= (uint32_t) opt.max_depth) break;
+        bool active_medium = medium >= 0, active_surface = !active_medium;
+        if (bounce > 100000) break;
+
+        if (active_medium) {
+            if (!si.valid()) break;    /* reference spins to the 100k-bounce guard doing nothing (vrl.cpp:500-510,523) */
+            valid_ray = true;
+            /* radius jitter draw, vrl.cpp:527 (value only feeds the photon gather) */
+            (void) sampler.next_1d();
+            const vrlb_medium &m = s.media[(size_t) medium];
+            /* linear camera ray: a single part [ray.o, si.t] (vrl.cpp:539-540, 595).  Non-linear
+             * splitting (vrl.cpp:550-578) is added by trace_nl_parts() when the medium asks for it. */
+            Ray part{ ro, rd, si.t };
+            V3 indirect(0.f);
+            V3 vrlThroughput = throughput;
+            V3 Li = on_query(PartOut{ part, vrlThroughput, medium, 0u }, sampler);
+            indirect = indirect + Li * vrlThroughput;
+            vrlThroughput = vrlThroughput * homo_transmittance(m, 0.f, part.maxt);   /* vrl.cpp:627 */
+            throughput = throughput * homo_transmittance(m, 0.f, part.maxt);         /* vrl.cpp:631 */
+            radiance = radiance + indirect;
+            active_surface = true;
+        }
+
+        /* surface interactions, vrl.cpp:645-717 */
+        if (active_surface && needs_intersection)
+            si = ray_intersect(s, ro, rd, rmint, rmaxt);
+        if (active_surface && si.valid() && specular_chain) {
+            const Tri &tr = s.tris[(size_t) si.prim];
+            if (tr.flags & VRLB_SURF_EMITTER) {
+                /* AreaLight::eval: radiance where cos_theta(si.wi) > 0 (area.cpp:64-72) */
+                if (dot(-rd, tri_normal(tr)) > 0.f) {
+                    int e = VRLB_SURF_GET_EMITTER(tr.flags);
+                    V3 Le = (size_t) e < s.emitters.size() ? V3(s.emitters[(size_t) e].radiance) : V3(0.f);
+                    radiance = radiance + throughput * Le;
+                }
+            }
+        }
+        active_surface = active_surface && si.valid();
+        if (active_surface) {
+            const Tri &tr = s.tris[(size_t) si.prim];
+            if (tr.flags & VRLB_SURF_EMITTER) break;            /* vrl.cpp:664-665 */
+            valid_ray = true;
+            if (!is_null(tr)) break;                            /* smooth BSDF: photon-map estimates, then break (vrl.cpp:671-680) */
+            /* Null::sample (null.cpp:38-52): consumes next_1d + next_2d, weight 1, wo = -wi */
+            (void) sampler.next_1d(); (void) sampler.next_1d(); (void) sampler.next_1d();
+            V3 p  = tri_point(tr, si.u, si.v);
+            ro    = p;                                          /* si.spawn_ray, interaction.h:58-61 */
+            rmint = (1.f + hmax_abs(p)) * kRayEpsilon;
+            rmaxt = kInf;
+            Hit si_new = ray_intersect(s, ro, rd, rmint, rmaxt);  /* vrl.cpp:707-711 */
+            needs_intersection = false;
+            if (is_medium_transition(tr)) medium = target_medium(tr, rd);   /* vrl.cpp:713-714 */
+            si = si_new;
+        }
+        if (!(active_surface || active_medium)) break;          /* vrl.cpp:719 */
+    }
+    return SampleResult{ radiance, valid_ray };
+}
+
+/* srgb_to_xyz, include/mitsuba/core/spectrum.h:221-227 */
+inline V3 srgb_to_xyz(V3 c) {
+    return V3(0.412453f * c.x + 0.357580f * c.y + 0.180423f * c.z,
+              0.212671f * c.x + 0.715160f * c.y + 0.072169f * c.z,
+              0.019334f * c.x + 0.119193f * c.y + 0.950227f * c.z);
+}
+
+/* SamplingIntegrator::render_block + render_sample (integrator.cpp:187-297) for one pixel:
+ * seeds the sampler, runs spp samples, calls put(px, py, rgb, alpha) per sample. */
+template <typename OnQuery, typename Put>
+void render_pixel(const vrlo_scene &s, const vrlb_camera &cam, const vrlb_options &opt, uint32_t block_id,
+                  uint32_t morton_i, int bx0, int by0, int bw, int bh, OnQuery &&on_query, Put &&put) {
+    uint32_t lx = compact_bits(morton_i), ly = compact_bits(morton_i >> 1);
+    if ((int) lx >= bw || (int) ly >= bh) return;
+    Sampler sampler;
+    uint32_t pixel_count = (uint32_t) (opt.block_size * opt.block_size);
+    sampler.seed(opt.base_seed, (uint64_t) block_id * pixel_count + morton_i);   /* integrator.cpp:204 */
+    int px = bx0 + (int) lx, py = by0 + (int) ly;
+    for (int j = 0; j < opt.spp; ++j) {
+        float ax = 0.5f, ay = 0.5f;
+        if (opt.spp > 1) { ax = sampler.next_1d(); ay = sampler.next_1d(); }    /* integrator.cpp:249 */
+        float posx = (float) px + ax, posy = (float) py + ay;
+        (void) sampler.next_1d();                                                /* wavelength sample, :261 */
+        float sx = posx / (float) cam.width, sy = posy / (float) cam.height;     /* :263-265, no crop */
+        V3 o, d; float mint, maxt;
+        camera_ray(cam, sx, sy, o, d, mint, maxt);
+        auto q = [&](const PartOut &p, Sampler &smp) { return on_query(p, smp, px, py, j); };
+        SampleResult r = trace_sample(s, opt, sampler, o, d, mint, maxt, cam.medium, q);
+        /* ImageBlock::put, box filter branch (imageblock.cpp:162-169): pixel = ceil(pos - 1) inside the block */
+        int fx = (int) std::ceil(posx - (float) bx0 - 1.0f), fy = (int) std::ceil(posy - (float) by0 - 1.0f);
+        if (fx >= 0 && fy >= 0 && fx < bw && fy < bh)
+            put(bx0 + fx, by0 + fy, r.radiance, r.valid_ray ? 1.f : 0.f);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt,
+                             uint64_t n_vrls_total, int rng_mode, vrlb_segment *segs, uint64_t cap,
+                             float *direct_rgb, float *alpha_w) {
+    (void) rng_mode;   /* stream positions after the first query are only defined in addressed mode */
+    int nbx, nby;
+    std::vector<uint32_t> ids = spiral_ids(cam->width, cam->height, opt->block_size, nbx, nby);
+    const uint64_t dpe = opt->rr_vrl ? 3u : 2u;
+    const uint32_t q = (uint32_t) std::max(opt->samples_per_query, 1);
+    uint64_t n = 0;
+    if (direct_rgb) std::memset(direct_rgb, 0, sizeof(float) * 3 * (size_t) cam->width * cam->height);
+    if (alpha_w) std::memset(alpha_w, 0, sizeof(float) * 2 * (size_t) cam->width * cam->height);
+    /* emit in film order of blocks (row-major over blocks, Morton inside): the GPU builder uses the same order */
+    for (int by = 0; by < nby; ++by)
+        for (int bx = 0; bx < nbx; ++bx) {
+            int bx0 = bx * opt->block_size, by0 = by * opt->block_size;
+            int bw = std::min(opt->block_size, cam->width - bx0), bh = std::min(opt->block_size, cam->height - by0);
+            uint32_t bid = ids[(size_t) by * nbx + bx];
+            for (uint32_t i = 0; i < (uint32_t) (opt->block_size * opt->block_size); ++i) {
+                auto on_query = [&](const PartOut &p, Sampler &smp, int px, int py, int j) {
+                    if (n < cap) {
+                        vrlb_segment &g = segs[n];
+                        g.o[0] = p.ray.o.x; g.o[1] = p.ray.o.y; g.o[2] = p.ray.o.z; g.maxt = p.ray.maxt;
+                        g.d[0] = p.ray.d.x; g.d[1] = p.ray.d.y; g.d[2] = p.ray.d.z;
+                        g.pixel = (uint32_t) (py * cam->width + px);
+                        g.weight[0] = p.weight.x; g.weight[1] = p.weight.y; g.weight[2] = p.weight.z;
+                        g.medium = p.medium; g.rng_state = smp.rng.state; g.sample = (uint32_t) j; g.part = p.part;
+                    }
+                    ++n;
+                    smp.rng.advance((int64_t) ((uint64_t) q * n_vrls_total * dpe));
+                    return V3(0.f);
+                };
+                auto put = [&](int x, int y, V3 rad, float alpha) {
+                    size_t p = (size_t) y * cam->width + x;
+                    if (direct_rgb) { direct_rgb[p * 3] += rad.x; direct_rgb[p * 3 + 1] += rad.y; direct_rgb[p * 3 + 2] += rad.z; }
+                    if (alpha_w) { alpha_w[p * 2] += alpha; alpha_w[p * 2 + 1] += 1.f; }
+                };
+                render_pixel(*s, *cam, *opt, bid, i, bx0, by0, bw, bh, on_query, put);
+            }
+        }
+    return n;
+}
+
+uint64_t vrlo_render(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt,
+                     const vrlb_vrlset_desc *vrls, int rng_mode, int n_threads, const int32_t *crop,
+                     float *xyzaw, float *rgb) {
+    int nbx, nby;
+    std::vector<uint32_t> ids = spiral_ids(cam->width, cam->height, opt->block_size, nbx, nby);
+    size_t npix = (size_t) cam->width * cam->height;
+    if (xyzaw) std::memset(xyzaw, 0, sizeof(float) * 5 * npix);
+    if (rgb) std::memset(rgb, 0, sizeof(float) * 3 * npix);
+    std::atomic<uint64_t> evals{ 0 };
+    int cx0 = crop ? crop[0] : 0, cy0 = crop ? crop[1] : 0, cx1 = crop ? crop[2] : cam->width, cy1 = crop ? crop[3] : cam->height;
+    /* one task per block, as tbb::parallel_for over blocks (integrator.cpp:111-142); blocks own
+     * disjoint pixels with the box filter, so no film mutex is needed */
+    parallel_for((uint64_t) nbx * nby, n_threads, [&](uint64_t b) {
+        int bx = (int) (b % nbx), by = (int) (b / nbx);
+        int bx0 = bx * opt->block_size, by0 = by * opt->block_size;
+        int bw = std::min(opt->block_size, cam->width - bx0), bh = std::min(opt->block_size, cam->height - by0);
+        if (bx0 >= cx1 || by0 >= cy1 || bx0 + bw <= cx0 || by0 + bh <= cy0) return;
+        uint64_t local = 0;
+        for (uint32_t i = 0; i < (uint32_t) (opt->block_size * opt->block_size); ++i) {
+            uint32_t lx = compact_bits(i), ly = compact_bits(i >> 1);
+            int px = bx0 + (int) lx, py = by0 + (int) ly;
+            if (px < cx0 || py < cy0 || px >= cx1 || py >= cy1) continue;
+            auto on_query = [&](const PartOut &p, Sampler &smp, int, int, int) {
+                V3 li; double li64[3];
+                local += query(*s, *vrls, p.ray, *opt, rng_mode, smp.rng, li, li64);
+                return li;
+            };
+            auto put = [&](int x, int y, V3 rad, float alpha) {
+                size_t p = (size_t) y * cam->width + x;
+                if (rgb) { rgb[p * 3] += rad.x; rgb[p * 3 + 1] += rad.y; rgb[p * 3 + 2] += rad.z; }
+                if (xyzaw) {
+                    V3 xyz = srgb_to_xyz(rad);
+                    xyzaw[p * 5 + 0] += xyz.x; xyzaw[p * 5 + 1] += xyz.y; xyzaw[p * 5 + 2] += xyz.z;
+                    xyzaw[p * 5 + 3] += alpha; xyzaw[p * 5 + 4] += 1.f;
+                }
+            };
+            render_pixel(*s, *cam, *opt, ids[(size_t) by * nbx + bx], i, bx0, by0, bw, bh, on_query, put);
+        }
+        evals += local;
+    });
+    return evals.load();
+}
+
+}  // extern "C"

@@ -1,0 +1,92 @@
+/*
+ * vrl_oracle.h -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * CPU restatement (scalar fp32, one IEEE operation per written operation, built with
+ * -ffp-contract=off) of the VRL gather hot path of VincentiusIV/mitsuba-NLVRL.  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this.
+ *
+ * PARITY STATUS: the reference ships no golden vector or test for the VRL path.
+ * Pins that DO exist and are checked in tests/: the PCG32 stream (against Enoki's own
+ * random.h compiled into oracle/_ref), isotropic eval == 1/(4 pi), and the reference's own
+ * vrl_struct.h functions compiled against a mock Mitsuba (oracle/_ref/refprobe, see
+ * oracle/ref_probe.cpp).  Everything else is "parity unpinned" in the sense of the task text.
+ *
+ * Input structs are the public ABI PODs of include/vrl_b200.h (interface only).
+ */
+#ifndef VRL_ORACLE_H
+#define VRL_ORACLE_H
+#include "../include/vrl_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* rng addressing modes (SURVEY 8d "PCG32 stream addressing") */
+enum { VRLO_RNG_ADDRESSED = 0,   /* fixed draws per (part, sample, VRL); what the GPU implements */
+       VRLO_RNG_SEQUENTIAL = 1 };/* bit-faithful to the reference: early-outs consume fewer draws */
+
+/* -- PCG32 / sampler (ext/enoki/include/enoki/random.h:62-119,265-286; sampler.cpp:83-96) -- */
+void     vrlo_pcg32_seed(uint64_t initstate, uint64_t initseq, uint64_t *state, uint64_t *inc);
+uint32_t vrlo_pcg32_next_u32(uint64_t *state, uint64_t inc);
+float    vrlo_pcg32_next_f32(uint64_t *state, uint64_t inc);
+void     vrlo_pcg32_advance(uint64_t *state, uint64_t inc, int64_t delta);
+/* n floats of the stream of IndependentSampler::seed(seed_offset) with base seed `base_seed` */
+void     vrlo_sampler_stream(uint64_t base_seed, uint64_t seed_offset, uint32_t n, float *out_f, uint32_t *out_u);
+
+/* -- block / pixel order (spiral.cpp:27-72, integrator.cpp:203-206) -- */
+/* fills block_id[by*nbx+bx] with the spiral id of every block; returns number of blocks */
+uint32_t vrlo_spiral_block_ids(int32_t width, int32_t height, int32_t block_size, uint32_t *block_id, uint32_t cap);
+void     vrlo_morton_decode(uint32_t i, uint32_t *x, uint32_t *y);
+
+/* -- single-eval probes (vrl_struct.h:163-228, 239-360, 584-662) -- */
+void  vrlo_find_closest_point(const float vrl_o[3], const float vrl_d[3], float vrl_len,
+                              const float ray_o[3], const float ray_d[3], float ray_maxt,
+                              float *tCam, float *tVRL);
+/* returns 1 if valid; out9 = pCam(3) tCam pVRL(3) tVRL invPDF */
+int   vrlo_sampling_vrl(const float vrl_o[3], const float vrl_d[3], float vrl_len,
+                        const float ray_o[3], const float ray_d[3], float ray_maxt,
+                        int uniform, float u1, float u2, float *out9);
+float vrlo_phase_eval(const vrlb_medium *m, const float wi[3], const float wo[3]);
+/* one getContrib with explicit uniforms, homogeneous media; visibility through `scene` if non-NULL */
+void  vrlo_get_contrib(const vrlb_scene_desc *scene, const vrlb_medium *m,
+                       const float vrl10[10], const float ray_o[3], const float ray_d[3], float ray_maxt,
+                       int uniform, float u1, float u2, float out_rgb[3]);
+
+/* -- scene queries (scene.cpp:114-131, mesh.h:195-225) -- */
+typedef struct vrlo_scene vrlo_scene;
+vrlo_scene *vrlo_scene_create(const vrlb_scene_desc *desc);
+void        vrlo_scene_destroy(vrlo_scene *s);
+/* closest hit; returns prim index or -1; t/u/v written */
+int   vrlo_ray_intersect(const vrlo_scene *s, const float o[3], const float d[3], float mint, float maxt,
+                         float *t, float *u, float *v);
+/* VRL::evalTransmittance (vrl_struct.h:509-572) for p1->p2 starting in medium `medium` */
+void  vrlo_eval_transmittance(const vrlo_scene *s, const float p1[3], const float p2[3], int medium, float out_rgb[3]);
+
+/* -- camera segments: VRLIntegrator::sample up to the query (vrl.cpp:443-631) -- */
+/* returns number of segments written (<= cap); n_vrls_total fixes the draws a query consumes in
+ * addressed mode.  direct_rgb (width*height*3, may be NULL) receives emitter radiance seen on the
+ * specular chain (vrl.cpp:651-657); alpha_w (width*height*2, may be NULL) receives sum(alpha), sum(w). */
+uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt,
+                             uint64_t n_vrls_total, int rng_mode,
+                             vrlb_segment *segs, uint64_t cap, float *direct_rgb, float *alpha_w);
+
+/* -- gather: VRLMap::query over explicit segments (vrl_map.h:133-211) -- */
+/* out_rgb32: per segment Li with the reference's sequential fp32 sum; out_rgb64: same fp32
+ * per-eval contributions summed in fp64 (either may be NULL). Returns the number of evals.
+ * Multi-threaded over segments when n_threads > 1. */
+uint64_t vrlo_gather_segments(const vrlo_scene *s, const vrlb_vrlset_desc *vrls,
+                              const vrlb_segment *segs, uint64_t n_segs, const vrlb_options *opt,
+                              int rng_mode, int n_threads, float *out_rgb32, double *out_rgb64);
+
+/* -- whole frame: SamplingIntegrator::render (integrator.cpp:51-183) in 32x32 blocks over
+ *    n_threads std::threads; film = XYZAW fp32 (imageblock.cpp:162-169).  crop = {x0,y0,x1,y1}
+ *    restricts the rendered pixels (NULL = full frame) for bounded CPU-baseline samples.
+ *    Returns evals performed. -- */
+uint64_t vrlo_render(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt,
+                     const vrlb_vrlset_desc *vrls, int rng_mode, int n_threads,
+                     const int32_t *crop, float *xyzaw, float *rgb);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,121 @@
+"""TEST-SIDE loader for the CPU oracle (oracle/libvrl_oracle.so).  Product code never imports this."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+import mitsuba_nlvrl_b200 as pkg
+from mitsuba_nlvrl_b200 import abi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+RNG_ADDRESSED, RNG_SEQUENTIAL = 0, 1
+
+
+def _build():
+    so = os.path.join(ORACLE_DIR, "libvrl_oracle.so")
+    src = os.path.join(ORACLE_DIR, "vrl_oracle.cpp")
+    if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "libvrl_oracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(_build())
+        f3 = C.POINTER(C.c_float)
+        L.vrlo_sampler_stream.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, f3, C.POINTER(C.c_uint32)]
+        L.vrlo_pcg32_seed.argtypes = [C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.vrlo_pcg32_next_u32.argtypes = [C.POINTER(C.c_uint64), C.c_uint64]
+        L.vrlo_pcg32_next_u32.restype = C.c_uint32
+        L.vrlo_pcg32_advance.argtypes = [C.POINTER(C.c_uint64), C.c_uint64, C.c_int64]
+        L.vrlo_spiral_block_ids.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_uint32), C.c_uint32]
+        L.vrlo_spiral_block_ids.restype = C.c_uint32
+        L.vrlo_morton_decode.argtypes = [C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        L.vrlo_find_closest_point.argtypes = [f3, f3, C.c_float, f3, f3, C.c_float, f3, f3]
+        L.vrlo_sampling_vrl.argtypes = [f3, f3, C.c_float, f3, f3, C.c_float, C.c_int, C.c_float, C.c_float, f3]
+        L.vrlo_sampling_vrl.restype = C.c_int
+        L.vrlo_phase_eval.argtypes = [C.POINTER(abi.Medium), f3, f3]
+        L.vrlo_phase_eval.restype = C.c_float
+        L.vrlo_get_contrib.argtypes = [C.POINTER(abi.SceneDesc), C.POINTER(abi.Medium), f3, f3, f3, C.c_float,
+                                       C.c_int, C.c_float, C.c_float, f3]
+        L.vrlo_scene_create.argtypes = [C.POINTER(abi.SceneDesc)]
+        L.vrlo_scene_create.restype = C.c_void_p
+        L.vrlo_scene_destroy.argtypes = [C.c_void_p]
+        L.vrlo_ray_intersect.argtypes = [C.c_void_p, f3, f3, C.c_float, C.c_float, f3, f3, f3]
+        L.vrlo_ray_intersect.restype = C.c_int
+        L.vrlo_eval_transmittance.argtypes = [C.c_void_p, f3, f3, C.c_int, f3]
+        L.vrlo_build_segments.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.c_uint64, C.c_int,
+                                          C.c_void_p, C.c_uint64, f3, f3]
+        L.vrlo_build_segments.restype = C.c_uint64
+        L.vrlo_gather_segments.argtypes = [C.c_void_p, C.POINTER(abi.VrlSetDesc), C.c_void_p, C.c_uint64,
+                                           C.POINTER(abi.Options), C.c_int, C.c_int, f3, C.POINTER(C.c_double)]
+        L.vrlo_gather_segments.restype = C.c_uint64
+        L.vrlo_render.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.POINTER(abi.VrlSetDesc),
+                                  C.c_int, C.c_int, C.POINTER(C.c_int32), f3, f3]
+        L.vrlo_render.restype = C.c_uint64
+        _lib = L
+    return _lib
+
+
+def f32(a):
+    return np.ascontiguousarray(a, np.float32)
+
+
+def fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+class OracleScene:
+    def __init__(self, scene):
+        self.scene = scene
+        self._desc = scene.desc()
+        self.h = lib().vrlo_scene_create(C.byref(self._desc))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().vrlo_scene_destroy(self.h)
+            self.h = None
+
+    def intersect(self, o, d, mint=0.0, maxt=np.inf):
+        o, d = f32(o), f32(d)
+        t, u, v = (C.c_float(), C.c_float(), C.c_float())
+        prim = lib().vrlo_ray_intersect(self.h, fp(o), fp(d), mint, maxt, C.byref(t), C.byref(u), C.byref(v))
+        return prim, t.value, u.value, v.value
+
+    def transmittance(self, p1, p2, medium=0):
+        p1, p2, out = f32(p1), f32(p2), np.zeros(3, np.float32)
+        lib().vrlo_eval_transmittance(self.h, fp(p1), fp(p2), medium, fp(out))
+        return out
+
+    def build_segments(self, cam, opt, n_vrls_total, rng_mode=RNG_ADDRESSED, cap=None):
+        npix = cam.width * cam.height
+        cap = cap or npix * opt.spp * 4
+        segs = np.zeros(cap, abi.SEGMENT_DTYPE)
+        direct = np.zeros((cam.height, cam.width, 3), np.float32)
+        aw = np.zeros((cam.height, cam.width, 2), np.float32)
+        n = lib().vrlo_build_segments(self.h, C.byref(cam), C.byref(opt), n_vrls_total, rng_mode,
+                                      segs.ctypes.data, cap, fp(direct), fp(aw))
+        assert n <= cap, "segment capacity exceeded"
+        return segs[:n].copy(), direct, aw
+
+    def gather(self, vrl_desc, segs, opt, rng_mode=RNG_ADDRESSED, n_threads=None):
+        n = len(segs)
+        segs = np.ascontiguousarray(segs)
+        o32, o64 = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float64)
+        ev = lib().vrlo_gather_segments(self.h, C.byref(vrl_desc), segs.ctypes.data, n, C.byref(opt), rng_mode,
+                                        n_threads or os.cpu_count(), fp(o32), o64.ctypes.data_as(C.POINTER(C.c_double)))
+        return o32, o64, ev
+
+    def render(self, cam, opt, vrl_desc, rng_mode=RNG_ADDRESSED, n_threads=None, crop=None):
+        xyzaw = np.zeros((cam.height, cam.width, 5), np.float32)
+        rgb = np.zeros((cam.height, cam.width, 3), np.float32)
+        cr = (C.c_int32 * 4)(*crop) if crop is not None else None
+        ev = lib().vrlo_render(self.h, C.byref(cam), C.byref(opt), C.byref(vrl_desc), rng_mode,
+                               n_threads or os.cpu_count(), cr, fp(xyzaw), fp(rgb))
+        return xyzaw, rgb, ev
