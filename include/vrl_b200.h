@@ -209,6 +209,9 @@ uint64_t vrlb_segments_count(const vrlb_context *ctx);
  *      weight * Li into the device radiance buffer (fp32 RGB, width*height*3). ----------------- */
 int  vrlb_film_clear(vrlb_context *ctx);
 int  vrlb_gather(vrlb_context *ctx, const vrlb_options *opt);
+/* Same, and additionally returns Li per resident segment BEFORE the weight (host, n_segments*3 fp32):
+ * exactly the `color` VRLMap::query returns (vrl_map.h:210), for per-segment parity checks. */
+int  vrlb_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *li_out);
 /* Device pointer of the fp32 RGB radiance accumulation buffer (width*height*3 floats) so that a
  * multi-GPU host can sum VRL shards with NCCL without a host round trip. */
 int  vrlb_film_device_ptr(vrlb_context *ctx, void **dev_ptr, uint64_t *n_floats);

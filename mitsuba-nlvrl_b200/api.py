@@ -1,0 +1,179 @@
+"""ctypes binding of libvrl_b200.so (include/vrl_b200.h).  This is the host-side mirror the tests, the
+bench and the integrator front-end use; it adds no computation.  The library must exist in-tree
+(csrc/libvrl_b200.so, built by `make -C mitsuba-nlvrl_b200/csrc` or __graft_entry__.build()); there is no
+fallback of any kind: a missing library or a missing GPU raises."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libvrl_b200.so")
+
+# every symbol include/vrl_b200.h declares
+EXPORTS = [
+    "vrlb_abi_version", "vrlb_create", "vrlb_destroy", "vrlb_last_error", "vrlb_set_stream", "vrlb_scene_set",
+    "vrlb_vrls_upload", "vrlb_vrls_download", "vrlb_vrls_count", "vrlb_segments_build", "vrlb_segments_upload",
+    "vrlb_segments_download", "vrlb_segments_count", "vrlb_film_clear", "vrlb_gather", "vrlb_gather_segments",
+    "vrlb_film_device_ptr", "vrlb_film_download_xyzaw", "vrlb_film_download_rgb", "vrlb_render", "vrlb_cancel",
+    "vrlb_get_timing", "vrlb_synchronize",
+]
+
+
+class VrlbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libvrl_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load_library():
+    """Loads the in-tree shared library and declares prototypes.  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(f"{LIB_PATH} is missing: build it with `make -C {os.path.dirname(LIB_PATH)}` "
+                                "(the CUDA extension is mandatory, there is no CPU path)")
+    L = C.CDLL(LIB_PATH)
+    vp, f32p = C.c_void_p, C.POINTER(C.c_float)
+    L.vrlb_abi_version.restype = C.c_int
+    L.vrlb_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.vrlb_destroy.argtypes = [vp]
+    L.vrlb_destroy.restype = None
+    L.vrlb_last_error.argtypes = [vp]
+    L.vrlb_last_error.restype = C.c_char_p
+    L.vrlb_set_stream.argtypes = [vp, vp]
+    L.vrlb_scene_set.argtypes = [vp, C.POINTER(abi.SceneDesc)]
+    L.vrlb_vrls_upload.argtypes = [vp, C.POINTER(abi.VrlSetDesc)]
+    L.vrlb_vrls_download.argtypes = [vp, f32p, C.POINTER(C.c_uint16), C.c_uint64, C.POINTER(C.c_uint64)]
+    L.vrlb_vrls_count.argtypes = [vp]
+    L.vrlb_vrls_count.restype = C.c_uint64
+    L.vrlb_segments_build.argtypes = [vp, C.POINTER(abi.Camera), C.POINTER(abi.Options)]
+    L.vrlb_segments_upload.argtypes = [vp, vp, C.c_uint64, C.c_int32, C.c_int32, C.c_int32]
+    L.vrlb_segments_download.argtypes = [vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.vrlb_segments_count.argtypes = [vp]
+    L.vrlb_segments_count.restype = C.c_uint64
+    L.vrlb_film_clear.argtypes = [vp]
+    L.vrlb_gather.argtypes = [vp, C.POINTER(abi.Options)]
+    L.vrlb_gather_segments.argtypes = [vp, C.POINTER(abi.Options), f32p]
+    L.vrlb_film_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
+    L.vrlb_film_download_xyzaw.argtypes = [vp, f32p]
+    L.vrlb_film_download_rgb.argtypes = [vp, f32p]
+    L.vrlb_render.argtypes = [vp, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.POINTER(abi.VrlSetDesc), f32p]
+    L.vrlb_cancel.argtypes = [vp]
+    L.vrlb_get_timing.argtypes = [vp, C.POINTER(abi.Timing)]
+    L.vrlb_synchronize.argtypes = [vp]
+    for name in EXPORTS:
+        fn = getattr(L, name)
+        if fn.restype is C.c_int and name not in ("vrlb_abi_version",):
+            pass
+    _lib = L
+    return L
+
+
+class Context:
+    """One GPU context (one per process/GPU).  Thin object wrapper over the C handle."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.vrlb_create(device, C.byref(h))
+        if rc != abi.OK:
+            raise VrlbError(rc, self.lib.vrlb_last_error(None).decode())
+        self.h = h
+        self.device = device
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vrlb_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _check(self, rc):
+        if rc != abi.OK:
+            raise VrlbError(rc, self.lib.vrlb_last_error(self.h).decode())
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self.lib.vrlb_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def set_scene(self, scene):
+        d = scene.desc()
+        self._check(self.lib.vrlb_scene_set(self.h, C.byref(d)))
+
+    def upload_vrls(self, vrl_desc):
+        self._check(self.lib.vrlb_vrls_upload(self.h, C.byref(vrl_desc)))
+
+    def download_vrls(self):
+        n = int(self.lib.vrlb_vrls_count(self.h))
+        soa = np.zeros((10, max(n, 1)), np.float32)
+        med = np.zeros(max(n, 1), np.uint16)
+        got = C.c_uint64()
+        self._check(self.lib.vrlb_vrls_download(self.h, abi.fptr(soa), med.ctypes.data_as(C.POINTER(C.c_uint16)), n, C.byref(got)))
+        return soa[:, :n], med[:n]
+
+    def build_segments(self, cam, opt):
+        self._check(self.lib.vrlb_segments_build(self.h, C.byref(cam), C.byref(opt)))
+        return int(self.lib.vrlb_segments_count(self.h))
+
+    def upload_segments(self, segs, width, height, spp=1):
+        segs = np.ascontiguousarray(segs, abi.SEGMENT_DTYPE)
+        self._check(self.lib.vrlb_segments_upload(self.h, segs.ctypes.data, len(segs), width, height, spp))
+
+    def download_segments(self):
+        n = int(self.lib.vrlb_segments_count(self.h))
+        segs = np.zeros(max(n, 1), abi.SEGMENT_DTYPE)
+        got = C.c_uint64()
+        self._check(self.lib.vrlb_segments_download(self.h, segs.ctypes.data, n, C.byref(got)))
+        return segs[:n]
+
+    def clear_film(self):
+        self._check(self.lib.vrlb_film_clear(self.h))
+
+    def gather(self, opt):
+        self._check(self.lib.vrlb_gather(self.h, C.byref(opt)))
+
+    def gather_segments(self, opt):
+        n = int(self.lib.vrlb_segments_count(self.h))
+        out = np.zeros((max(n, 1), 3), np.float32)
+        self._check(self.lib.vrlb_gather_segments(self.h, C.byref(opt), abi.fptr(out)))
+        return out[:n]
+
+    def film_device_ptr(self):
+        p, n = C.c_void_p(), C.c_uint64()
+        self._check(self.lib.vrlb_film_device_ptr(self.h, C.byref(p), C.byref(n)))
+        return p.value, int(n.value)
+
+    def film_xyzaw(self, width, height):
+        out = np.zeros((height, width, 5), np.float32)
+        self._check(self.lib.vrlb_film_download_xyzaw(self.h, abi.fptr(out)))
+        return out
+
+    def film_rgb(self, width, height):
+        out = np.zeros((height, width, 3), np.float32)
+        self._check(self.lib.vrlb_film_download_rgb(self.h, abi.fptr(out)))
+        return out
+
+    def render(self, cam, opt, vrl_desc=None, out=None):
+        if out is None:
+            out = np.zeros((cam.height, cam.width, 5), np.float32)
+        self._check(self.lib.vrlb_render(self.h, C.byref(cam), C.byref(opt), C.byref(vrl_desc) if vrl_desc is not None else None,
+                                         abi.fptr(out)))
+        return out
+
+    def cancel(self):
+        self._check(self.lib.vrlb_cancel(self.h))
+
+    def synchronize(self):
+        self._check(self.lib.vrlb_synchronize(self.h))
+
+    def timing(self):
+        t = abi.Timing()
+        self._check(self.lib.vrlb_get_timing(self.h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in abi.Timing._fields_}

@@ -1,0 +1,483 @@
+// vrlb_api.cpp -- implementation of the C ABI declared in include/vrl_b200.h.
+//
+// Host side of libvrl_b200.so: owns device memory, the CUDA stream and events, builds the BVH,
+// mirrors the control flow of Integrator::render (src/librender/integrator.cpp:51-183) and
+// VRLIntegrator::preprocess/render (src/integrators/vrl/vrl.cpp) around the kernels of gather.cu and
+// segments.cu.  No CPU compute fallback: without a usable CUDA device every entry point fails.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/vrl_b200.h"
+#include "bvh_build.h"
+#include "vrlb_kernels.h"
+
+using namespace vrlb;
+
+namespace {
+
+std::string g_create_error;
+
+template <typename T> struct DevBuf {
+    T *ptr = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc((void **) &ptr, std::max<size_t>(n, 1) * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct vrlb_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    std::string error;
+    std::atomic<int> cancel{ 0 };
+
+    // scene
+    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DMedium> media; DevBuf<float> emitters;
+    DScene scene{};
+    bool have_scene = false;
+    std::vector<vrlb_medium> host_media;
+
+    // VRL set
+    DevBuf<DVrl> vrls; DevBuf<float> stage_soa; DevBuf<uint16_t> stage_med;
+    uint64_t n_vrls = 0, vrl_first = 0, vrl_total = 0; float vrl_scale = 1.f;
+
+    // segments
+    DevBuf<vrlb_segment> segs; uint64_t n_segs = 0;
+    DevBuf<unsigned long long> counter;
+    DevBuf<uint32_t> block_ids; std::vector<uint32_t> host_block_ids; int bid_w = 0, bid_h = 0, bid_bs = 0;
+
+    // film
+    DevBuf<float> film_rgb, film_aw, film_xyzaw;
+    int width = 0, height = 0;
+
+    // pinned staging for host<->device copies of the e2e path
+    void *pinned = nullptr; size_t pinned_cap = 0;
+
+    cudaEvent_t ev[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
+    vrlb_timing timing{};
+};
+
+namespace {
+
+int fail(vrlb_context *ctx, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (ctx) ctx->error = buf; else g_create_error = buf;
+    return code;
+}
+#define CU(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, VRLB_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
+
+int ensure_pinned(vrlb_context *ctx, size_t bytes) {
+    if (bytes <= ctx->pinned_cap) return VRLB_OK;
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    ctx->pinned = nullptr; ctx->pinned_cap = 0;
+    CU(ctx, cudaMallocHost(&ctx->pinned, bytes));
+    ctx->pinned_cap = bytes;
+    return VRLB_OK;
+}
+
+// Spiral block ids, src/librender/spiral.cpp:8-72 (ids in spiral order from the film centre)
+std::vector<uint32_t> spiral_ids(int w, int h, int bs, int &nbx, int &nby) {
+    nbx = (w + bs - 1) / bs; nby = (h + bs - 1) / bs;
+    int count = nbx * nby;
+    std::vector<uint32_t> ids((size_t) count, 0u);
+    int px = nbx / 2, py = nby / 2, dir = 0, steps_left = 1, steps = 1;
+    for (int c = 0; c < count; ++c) {
+        ids[(size_t) py * nbx + px] = (uint32_t) c;
+        if (c + 1 != count) {
+            do {
+                switch (dir) { case 0: ++px; break; case 1: ++py; break; case 2: --px; break; default: --py; break; }
+                if (--steps_left == 0) {
+                    dir = (dir + 1) % 4;
+                    if (dir == 0 || dir == 2) ++steps;
+                    steps_left = steps;
+                }
+            } while (px < 0 || py < 0 || px >= nbx || py >= nby);
+        }
+    }
+    return ids;
+}
+
+int ensure_film(vrlb_context *ctx, int w, int h) {
+    if (w <= 0 || h <= 0) return fail(ctx, VRLB_ERR_INVALID, "film size %dx%d", w, h);
+    size_t np = (size_t) w * h;
+    bool fresh = (w != ctx->width || h != ctx->height);
+    CU(ctx, ctx->film_rgb.reserve(np * 3));
+    CU(ctx, ctx->film_aw.reserve(np * 2));
+    CU(ctx, ctx->film_xyzaw.reserve(np * 5));
+    ctx->width = w; ctx->height = h;
+    if (fresh) {
+        CU(ctx, cudaMemsetAsync(ctx->film_rgb.ptr, 0, np * 3 * sizeof(float), ctx->stream));
+        CU(ctx, cudaMemsetAsync(ctx->film_aw.ptr, 0, np * 2 * sizeof(float), ctx->stream));
+    }
+    return VRLB_OK;
+}
+
+float elapsed(cudaEvent_t a, cudaEvent_t b) { float ms = 0.f; cudaEventElapsedTime(&ms, a, b); return ms; }
+
+}  // namespace
+
+extern "C" {
+
+int vrlb_abi_version(void) { return VRLB_ABI_VERSION; }
+
+int vrlb_create(int device, vrlb_context **out) {
+    if (!out) return fail(nullptr, VRLB_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, VRLB_ERR_CUDA, "no CUDA device (%s); libvrl_b200 has no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(nullptr, VRLB_ERR_INVALID, "device %d out of range [0,%d)", device, n);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail(nullptr, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
+    if (prop.major < 10)
+        return fail(nullptr, VRLB_ERR_CUDA, "device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(nullptr, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
+    vrlb_context *ctx = new vrlb_context();
+    ctx->device = device;
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        delete ctx; return fail(nullptr, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
+    }
+    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    cudaMalloc((void **) &ctx->counter.ptr, sizeof(unsigned long long)); ctx->counter.cap = 1;
+    *out = ctx;
+    return VRLB_OK;
+}
+
+void vrlb_destroy(vrlb_context *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->media.release(); ctx->emitters.release();
+    ctx->vrls.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
+    ctx->block_ids.release(); ctx->film_rgb.release(); ctx->film_aw.release(); ctx->film_xyzaw.release();
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *vrlb_last_error(const vrlb_context *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int vrlb_set_stream(vrlb_context *ctx, void *cuda_stream) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (cuda_stream) { ctx->stream = (cudaStream_t) cuda_stream; ctx->own_stream = false; }
+    else { CU(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true; }
+    return VRLB_OK;
+}
+
+int vrlb_synchronize(vrlb_context *ctx) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return VRLB_OK;
+}
+
+int vrlb_cancel(vrlb_context *ctx) { if (!ctx) return VRLB_ERR_INVALID; ctx->cancel.store(1); return VRLB_OK; }
+
+int vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out) {
+    if (!ctx || !out) return VRLB_ERR_INVALID;
+    *out = ctx->timing;
+    return VRLB_OK;
+}
+
+// ---- scene -----------------------------------------------------------------------------------------
+int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
+    if (!ctx || !sc) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (sc->n_tris && !sc->tri_verts) return fail(ctx, VRLB_ERR_INVALID, "tri_verts is NULL");
+    if (sc->n_media == 0 || !sc->media) return fail(ctx, VRLB_ERR_INVALID, "a scene needs at least one medium");
+    if (sc->n_media > 255 || sc->n_emitters > 255) return fail(ctx, VRLB_ERR_INVALID, "at most 255 media / emitters");
+    for (uint32_t i = 0; i < sc->n_tris; ++i) {
+        uint32_t f = sc->tri_flags ? sc->tri_flags[i] : 0u;
+        if (VRLB_SURF_GET_INTERIOR(f) >= (int) sc->n_media || VRLB_SURF_GET_EXTERIOR(f) >= (int) sc->n_media)
+            return fail(ctx, VRLB_ERR_INVALID, "triangle %u references medium out of range", i);
+        if ((f & VRLB_SURF_BSDF_MASK) > VRLB_SURF_BSDF_NULL)
+            return fail(ctx, VRLB_ERR_INVALID, "triangle %u: BSDF class %u not supported on this path", i, f & VRLB_SURF_BSDF_MASK);
+    }
+    std::vector<DMedium> dm(sc->n_media);
+    for (uint32_t i = 0; i < sc->n_media; ++i) {
+        const vrlb_medium &m = sc->media[i];
+        if (m.kind != VRLB_MEDIUM_HOMOGENEOUS && m.kind != VRLB_MEDIUM_NONLINEAR)
+            return fail(ctx, VRLB_ERR_INVALID, "medium %u: kind %d is not implemented on the CUDA path yet", i, m.kind);
+        if (m.phase != VRLB_PHASE_ISOTROPIC && m.phase != VRLB_PHASE_HG) return fail(ctx, VRLB_ERR_INVALID, "medium %u: unknown phase %d", i, m.phase);
+        if (m.phase == VRLB_PHASE_HG && !(m.g > -1.f && m.g < 1.f))
+            return fail(ctx, VRLB_ERR_INVALID, "The asymmetry parameter must lie in the interval (-1, 1)!");   // hg.cpp:45-46
+        DMedium d{};
+        float mean = (m.sigma_t[0] + m.sigma_t[1] + m.sigma_t[2]) / 3.0f;      // ConstVolume::max() = mean, constant3d.cpp:37
+        d.max_density = m.scale * mean;                                          // homogeneous.cpp:26
+        for (int k = 0; k < 3; ++k) d.sigma_s[k] = (m.sigma_t[k] * m.scale) * m.albedo[k];   // homogeneous.cpp:42-50
+        d.g = m.g; d.phase = m.phase; d.kind = m.kind;
+        dm[i] = d;
+    }
+    std::vector<DNode> nodes; std::vector<DTri> tris;
+    build_bvh(sc->tri_verts, sc->tri_flags, sc->n_tris, nodes, tris);
+    CU(ctx, ctx->tris.reserve(tris.size())); CU(ctx, ctx->nodes.reserve(nodes.size()));
+    CU(ctx, ctx->verts.reserve((size_t) sc->n_tris * 9)); CU(ctx, ctx->media.reserve(dm.size()));
+    CU(ctx, ctx->emitters.reserve((size_t) sc->n_emitters * 4));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    if (!tris.empty()) {
+        CU(ctx, cudaMemcpy(ctx->tris.ptr, tris.data(), tris.size() * sizeof(DTri), cudaMemcpyHostToDevice));
+        CU(ctx, cudaMemcpy(ctx->nodes.ptr, nodes.data(), nodes.size() * sizeof(DNode), cudaMemcpyHostToDevice));
+        CU(ctx, cudaMemcpy(ctx->verts.ptr, sc->tri_verts, (size_t) sc->n_tris * 9 * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    CU(ctx, cudaMemcpy(ctx->media.ptr, dm.data(), dm.size() * sizeof(DMedium), cudaMemcpyHostToDevice));
+    if (sc->n_emitters) CU(ctx, cudaMemcpy(ctx->emitters.ptr, sc->emitters, (size_t) sc->n_emitters * sizeof(vrlb_emitter), cudaMemcpyHostToDevice));
+    ctx->scene.tris = ctx->tris.ptr; ctx->scene.verts = ctx->verts.ptr; ctx->scene.nodes = ctx->nodes.ptr;
+    ctx->scene.n_tris = (int32_t) tris.size(); ctx->scene.n_nodes = (int32_t) nodes.size();
+    ctx->scene.media = ctx->media.ptr; ctx->scene.n_media = (int32_t) dm.size();
+    ctx->scene.emitters = ctx->emitters.ptr; ctx->scene.n_emitters = (int32_t) sc->n_emitters;
+    ctx->host_media.assign(sc->media, sc->media + sc->n_media);
+    ctx->have_scene = true;
+    return VRLB_OK;
+}
+
+// ---- VRL set ---------------------------------------------------------------------------------------
+int vrlb_vrls_upload(vrlb_context *ctx, const vrlb_vrlset_desc *set) {
+    if (!ctx || !set) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (set->n && !set->soa10) return fail(ctx, VRLB_ERR_INVALID, "soa10 is NULL");
+    uint64_t total = set->total ? set->total : set->n;
+    if (set->first_index + set->n > total) return fail(ctx, VRLB_ERR_INVALID, "VRL shard [%llu,+%llu) exceeds total %llu",
+                                                        (unsigned long long) set->first_index, (unsigned long long) set->n, (unsigned long long) total);
+    uint64_t n = set->n;
+    CU(ctx, ctx->vrls.reserve(n)); CU(ctx, ctx->stage_soa.reserve(n * 10));
+    if (set->medium) CU(ctx, ctx->stage_med.reserve(n));
+    size_t soa_bytes = n * 10 * sizeof(float), med_bytes = set->medium ? n * sizeof(uint16_t) : 0;
+    int rc = ensure_pinned(ctx, soa_bytes + med_bytes + 64);
+    if (rc) return rc;
+    cudaEventRecord(ctx->ev[0], ctx->stream);
+    if (n) {
+        // pageable -> pinned on the host, then one async H2D per array (no batched memcpy API)
+        std::memcpy(ctx->pinned, set->soa10, soa_bytes);
+        CU(ctx, cudaMemcpyAsync(ctx->stage_soa.ptr, ctx->pinned, soa_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        if (set->medium) {
+            std::memcpy((char *) ctx->pinned + soa_bytes, set->medium, med_bytes);
+            CU(ctx, cudaMemcpyAsync(ctx->stage_med.ptr, (char *) ctx->pinned + soa_bytes, med_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        }
+        CU(ctx, launch_pack_vrls(ctx->stage_soa.ptr, set->medium ? ctx->stage_med.ptr : nullptr, n, ctx->vrls.ptr, ctx->stream));
+    }
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->timing.ms_upload = elapsed(ctx->ev[0], ctx->ev[1]);
+    ctx->n_vrls = n; ctx->vrl_first = set->first_index; ctx->vrl_total = total; ctx->vrl_scale = set->scale;
+    return VRLB_OK;
+}
+
+uint64_t vrlb_vrls_count(const vrlb_context *ctx) { return ctx ? ctx->n_vrls : 0; }
+
+int vrlb_vrls_download(vrlb_context *ctx, float *soa10, uint16_t *medium, uint64_t cap, uint64_t *n_out) {
+    if (!ctx || !soa10) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    uint64_t n = ctx->n_vrls;
+    if (n_out) *n_out = n;
+    if (cap < n) return fail(ctx, VRLB_ERR_INVALID, "capacity %llu < %llu VRLs", (unsigned long long) cap, (unsigned long long) n);
+    if (n == 0) return VRLB_OK;
+    CU(ctx, ctx->stage_soa.reserve(n * 10)); CU(ctx, ctx->stage_med.reserve(n));
+    CU(ctx, launch_unpack_vrls(ctx->vrls.ptr, n, ctx->stage_soa.ptr, ctx->stage_med.ptr, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(soa10, ctx->stage_soa.ptr, n * 10 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (medium) CU(ctx, cudaMemcpyAsync(medium, ctx->stage_med.ptr, n * sizeof(uint16_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return VRLB_OK;
+}
+
+// ---- camera segments -------------------------------------------------------------------------------
+int vrlb_segments_build(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_options *opt) {
+    if (!ctx || !cam || !opt) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_segments_build");
+    if (opt->spp < 1 || opt->block_size < 1 || opt->block_size > 1024) return fail(ctx, VRLB_ERR_INVALID, "spp/block_size out of range");
+    if (cam->medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "camera medium out of range");
+    int rc = ensure_film(ctx, cam->width, cam->height);
+    if (rc) return rc;
+    if (ctx->bid_w != cam->width || ctx->bid_h != cam->height || ctx->bid_bs != opt->block_size) {
+        int nbx, nby;
+        ctx->host_block_ids = spiral_ids(cam->width, cam->height, opt->block_size, nbx, nby);
+        CU(ctx, ctx->block_ids.reserve(ctx->host_block_ids.size()));
+        CU(ctx, cudaMemcpyAsync(ctx->block_ids.ptr, ctx->host_block_ids.data(), ctx->host_block_ids.size() * sizeof(uint32_t),
+                                cudaMemcpyHostToDevice, ctx->stream));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->bid_w = cam->width; ctx->bid_h = cam->height; ctx->bid_bs = opt->block_size;
+    }
+    // linear camera rays: at most one in-medium part per null-bounded medium region crossed; start with
+    // 2 per sample and grow on overflow (the kernel counts what it needed)
+    uint64_t samples = (uint64_t) cam->width * cam->height * (uint64_t) opt->spp;
+    uint64_t cap = std::max<uint64_t>(ctx->segs.cap, samples + samples / 8 + 1024);
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        CU(ctx, ctx->segs.reserve(cap));
+        SegmentParams p{};
+        p.scene = ctx->scene; p.cam = *cam; p.opt = *opt;
+        p.block_ids = ctx->block_ids.ptr;
+        p.nbx = (cam->width + opt->block_size - 1) / opt->block_size; p.nby = (cam->height + opt->block_size - 1) / opt->block_size;
+        p.n_vrls_total = ctx->vrl_total; p.segs = ctx->segs.ptr; p.cap = ctx->segs.cap; p.counter = ctx->counter.ptr;
+        p.film_rgb = ctx->film_rgb.ptr; p.film_aw = ctx->film_aw.ptr;
+        size_t np = (size_t) cam->width * cam->height;
+        cudaEventRecord(ctx->ev[0], ctx->stream);
+        CU(ctx, cudaMemsetAsync(ctx->counter.ptr, 0, sizeof(unsigned long long), ctx->stream));
+        CU(ctx, cudaMemsetAsync(ctx->film_rgb.ptr, 0, np * 3 * sizeof(float), ctx->stream));
+        CU(ctx, cudaMemsetAsync(ctx->film_aw.ptr, 0, np * 2 * sizeof(float), ctx->stream));
+        CU(ctx, launch_segments(p, ctx->stream));
+        cudaEventRecord(ctx->ev[1], ctx->stream);
+        unsigned long long n = 0;
+        CU(ctx, cudaMemcpyAsync(&n, ctx->counter.ptr, sizeof n, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->timing.ms_segments = elapsed(ctx->ev[0], ctx->ev[1]);
+        ctx->timing.total_launches += 1;
+        if (n <= ctx->segs.cap) { ctx->n_segs = n; ctx->timing.n_segments = n; return VRLB_OK; }
+        cap = n;
+    }
+    return fail(ctx, VRLB_ERR_NOMEM, "segment buffer overflow");
+}
+
+int vrlb_segments_upload(vrlb_context *ctx, const vrlb_segment *segs, uint64_t n, int32_t width, int32_t height, int32_t spp) {
+    if (!ctx || (n && !segs)) return VRLB_ERR_INVALID;
+    (void) spp;
+    cudaSetDevice(ctx->device);
+    int rc = ensure_film(ctx, width, height);
+    if (rc) return rc;
+    for (uint64_t i = 0; i < n; ++i)
+        if (segs[i].pixel >= (uint64_t) width * height) return fail(ctx, VRLB_ERR_INVALID, "segment %llu: pixel out of range", (unsigned long long) i);
+    CU(ctx, ctx->segs.reserve(n));
+    if (n) CU(ctx, cudaMemcpyAsync(ctx->segs.ptr, segs, n * sizeof(vrlb_segment), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->n_segs = n; ctx->timing.n_segments = n;
+    return VRLB_OK;
+}
+
+int vrlb_segments_download(vrlb_context *ctx, vrlb_segment *segs, uint64_t cap, uint64_t *n_out) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (n_out) *n_out = ctx->n_segs;
+    if (!segs) return VRLB_OK;
+    if (cap < ctx->n_segs) return fail(ctx, VRLB_ERR_INVALID, "capacity too small");
+    if (ctx->n_segs) CU(ctx, cudaMemcpyAsync(segs, ctx->segs.ptr, ctx->n_segs * sizeof(vrlb_segment), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return VRLB_OK;
+}
+
+uint64_t vrlb_segments_count(const vrlb_context *ctx) { return ctx ? ctx->n_segs : 0; }
+
+// ---- gather ----------------------------------------------------------------------------------------
+int vrlb_film_clear(vrlb_context *ctx) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no film yet");
+    size_t np = (size_t) ctx->width * ctx->height;
+    CU(ctx, cudaMemsetAsync(ctx->film_rgb.ptr, 0, np * 3 * sizeof(float), ctx->stream));
+    CU(ctx, cudaMemsetAsync(ctx->film_aw.ptr, 0, np * 2 * sizeof(float), ctx->stream));
+    return VRLB_OK;
+}
+
+static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_out_dev) {
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "no scene resident");
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no camera segments resident");
+    if (opt->samples_per_query < 1) return fail(ctx, VRLB_ERR_INVALID, "samples_per_query must be >= 1");
+    if (opt->math_mode != 0) return fail(ctx, VRLB_ERR_INVALID, "math_mode %d not available in this build", opt->math_mode);
+    if (ctx->cancel.exchange(0)) return fail(ctx, VRLB_ERR_CANCELLED, "cancelled");
+    GatherParams p{};
+    p.scene = ctx->scene; p.segs = ctx->segs.ptr; p.n_segs = ctx->n_segs;
+    p.vrls = ctx->vrls.ptr; p.n_vrls = ctx->n_vrls; p.first_index = ctx->vrl_first; p.total = ctx->vrl_total;
+    p.scale = ctx->vrl_scale; p.scale_rr = opt->scale_rr; p.q = (uint32_t) opt->samples_per_query;
+    p.film_rgb = ctx->film_rgb.ptr; p.seg_out = seg_out_dev;
+    cudaEventRecord(ctx->ev[2], ctx->stream);
+    CU(ctx, launch_gather(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, opt->visibility != 0 && ctx->scene.n_tris > 0, ctx->stream));
+    cudaEventRecord(ctx->ev[3], ctx->stream);
+    bool launched = p.n_segs && p.n_vrls;
+    ctx->timing.gather_launches = launched ? 1 : 0;
+    ctx->timing.total_launches += launched ? 1 : 0;
+    ctx->timing.n_evals = p.n_segs * p.n_vrls * p.q;
+    return VRLB_OK;
+}
+
+int vrlb_gather(vrlb_context *ctx, const vrlb_options *opt) {
+    if (!ctx || !opt) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    return gather_impl(ctx, opt, nullptr);
+}
+
+/* Test/diagnostic entry: gather and also return Li per resident segment (before the weight), host buffer n_segs*3. */
+int vrlb_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *li_out) {
+    if (!ctx || !opt || !li_out) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    DevBuf<float> tmp;
+    CU(ctx, tmp.reserve(ctx->n_segs * 3 + 1));
+    CU(ctx, cudaMemsetAsync(tmp.ptr, 0, (ctx->n_segs * 3 + 1) * sizeof(float), ctx->stream));
+    int rc = gather_impl(ctx, opt, tmp.ptr);
+    if (rc == VRLB_OK) {
+        cudaError_t e = cudaMemcpyAsync(li_out, tmp.ptr, ctx->n_segs * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = fail(ctx, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
+        else ctx->timing.ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
+    }
+    tmp.release();
+    return rc;
+}
+
+int vrlb_film_device_ptr(vrlb_context *ctx, void **dev_ptr, uint64_t *n_floats) {
+    if (!ctx || !dev_ptr) return VRLB_ERR_INVALID;
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no film yet");
+    *dev_ptr = ctx->film_rgb.ptr;
+    if (n_floats) *n_floats = (uint64_t) ctx->width * ctx->height * 3;
+    return VRLB_OK;
+}
+
+int vrlb_film_download_xyzaw(vrlb_context *ctx, float *xyzaw) {
+    if (!ctx || !xyzaw) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no film yet");
+    size_t np = (size_t) ctx->width * ctx->height;
+    cudaEventRecord(ctx->ev[4], ctx->stream);
+    CU(ctx, launch_film_xyzaw(ctx->film_rgb.ptr, ctx->film_aw.ptr, ctx->film_xyzaw.ptr, np, ctx->stream));
+    cudaEventRecord(ctx->ev[5], ctx->stream);
+    int rc = ensure_pinned(ctx, np * 5 * sizeof(float));
+    if (rc) return rc;
+    CU(ctx, cudaMemcpyAsync(ctx->pinned, ctx->film_xyzaw.ptr, np * 5 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    std::memcpy(xyzaw, ctx->pinned, np * 5 * sizeof(float));
+    ctx->timing.ms_film = elapsed(ctx->ev[4], ctx->ev[5]);
+    ctx->timing.ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
+    ctx->timing.total_launches += 1;
+    return VRLB_OK;
+}
+
+int vrlb_film_download_rgb(vrlb_context *ctx, float *rgb) {
+    if (!ctx || !rgb) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no film yet");
+    size_t np = (size_t) ctx->width * ctx->height;
+    CU(ctx, cudaMemcpyAsync(rgb, ctx->film_rgb.ptr, np * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->timing.ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
+    return VRLB_OK;
+}
+
+// ---- whole frame (Integrator::render, integrator.cpp:51-183): upload -> segments -> gather -> film ----
+int vrlb_render(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_options *opt, const vrlb_vrlset_desc *vrls, float *xyzaw_out) {
+    if (!ctx || !cam || !opt || !xyzaw_out) return VRLB_ERR_INVALID;
+    ctx->timing = vrlb_timing{};
+    int rc;
+    if (vrls && (rc = vrlb_vrls_upload(ctx, vrls)) != VRLB_OK) return rc;
+    if (ctx->vrl_total == 0 && ctx->n_vrls == 0) { /* empty map: VRLMap::query returns 0 (vrl_map.h:134-137) */ }
+    if ((rc = vrlb_segments_build(ctx, cam, opt)) != VRLB_OK) return rc;
+    if ((rc = vrlb_gather(ctx, opt)) != VRLB_OK) return rc;
+    return vrlb_film_download_xyzaw(ctx, xyzaw_out);
+}
+
+}  // extern "C"

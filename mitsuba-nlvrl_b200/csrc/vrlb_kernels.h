@@ -1,0 +1,49 @@
+// vrlb_kernels.h -- host-visible launch interface of the CUDA kernels (internal to libvrl_b200.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/vrl_b200.h"
+#include "vrlb_device.cuh"
+
+namespace vrlb {
+
+struct GatherParams {
+    DScene              scene;
+    const vrlb_segment *segs;        // device, 64 B records
+    uint64_t            n_segs;
+    const DVrl         *vrls;        // device, 48 B records (this rank's shard)
+    uint64_t            n_vrls;
+    uint64_t            first_index; // global index of vrls[0] (PCG32 stream addressing)
+    uint64_t            total;       // size of the whole exported set
+    float               scale;       // VRLMap::m_scale
+    float               scale_rr;
+    uint32_t            q;           // samples_per_query
+    float              *film_rgb;    // device, width*height*3 fp32, accumulated with RED.ADD (may be null)
+    float              *seg_out;     // device, n_segs*3: Li per segment before the weight (may be null)
+};
+
+cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis, cudaStream_t stream);
+
+struct SegmentParams {
+    DScene        scene;
+    vrlb_camera   cam;
+    vrlb_options  opt;
+    const uint32_t *block_ids;   // device: spiral id per block, row-major over blocks
+    int32_t       nbx, nby;
+    uint64_t      n_vrls_total;
+    vrlb_segment *segs;          // device output, capacity `cap`
+    uint64_t      cap;
+    unsigned long long *counter; // device: number of segments appended (may exceed cap -> overflow)
+    float        *film_rgb;      // device: emitter radiance seen directly is added here
+    float        *film_aw;       // device: width*height*2: sum(alpha), sum(weight)
+};
+cudaError_t launch_segments(const SegmentParams &p, cudaStream_t stream);
+
+// XYZAW film from the RGB accumulation buffer (integrator.cpp:282-294)
+cudaError_t launch_film_xyzaw(const float *film_rgb, const float *film_aw, float *xyzaw, uint64_t n_pixels, cudaStream_t stream);
+// SoA10 (+ medium ids) -> 48 B records, and back
+cudaError_t launch_pack_vrls(const float *soa10, const uint16_t *medium, uint64_t n, DVrl *out, cudaStream_t stream);
+cudaError_t launch_unpack_vrls(const DVrl *in, uint64_t n, float *soa10, uint16_t *medium, cudaStream_t stream);
+
+}  // namespace vrlb

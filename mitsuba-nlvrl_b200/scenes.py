@@ -234,8 +234,8 @@ def box_fog_camera(width=1920, height=1080):
 def _seeded_floats(seed, n):
     """n deterministic uniforms in [0,1) from a counter-based splitmix64 (VRL sets are synthetic inputs: any
     seeded generator will do; parity only needs the oracle and the GPU to read the SAME exported set)."""
-    x = (np.arange(n, dtype=np.uint64) + np.uint64(seed) * np.uint64(0x9E3779B97F4A7C15)) & np.uint64(0xFFFFFFFFFFFFFFFF)
     with np.errstate(over="ignore"):
+        x = np.arange(n, dtype=np.uint64) + np.uint64((int(seed) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF)
         x = (x + np.uint64(0x9E3779B97F4A7C15))
         z = x
         z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
