@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py -- camera-segment x VRL evaluations per second and ms/frame at 1080p (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (config.workload): the synthetic "box-fog" scene of SURVEY.md 8(d), variant V2 (sphere + cuboid
+occluders inside a homogeneous isotropic fog box, shadow query through the BVH per eval), 1920x1080, spp 1,
+block_size 32, samples_per_query 1, importance sampling, 100k seeded VRLs: BASELINE.json configs[3]/[4]
+shape, 2.07e11 evals per frame.  One step = one frame: camera-segment kernel + gather kernel (+ NCCL film
+all-reduce when N > 1) + XYZAW film kernel.  N > 1: the VRL set is sharded across ranks (strong scaling: the
+frame is fixed, each rank gathers all pixels against N_vrl/N VRLs), films summed with NCCL.
+
+`value`   : whole-job evals/s with the VRL set, scene and camera resident on the device (CUDA events on the
+            library's stream, max over ranks).
+`e2e`     : same metric through vrlb_render() from HOST buffers: per step the VRL set is copied host->device
+            and the XYZAW film device->host inside the timed region (wall clock around synchronised calls).
+`roofline`: the gather kernel against the FP32 FMA issue peak measured on this GPU by the library's FFMA
+            microkernel (MEASURED_PEAKS.json has no FP32 entry; the path is FP32/SFU-issue bound, not HBM).
+`cpu_baseline` / --impl reference: the CPU restatement of the reference's scalar gather (oracle/, kind
+            "port": the MSVC-only reference cannot be compiled here) on all host cores, on a crop of the frame.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+FLOPS_PER_EVAL = 210.0        # homogeneous + isotropic + importance sampling, visibility excluded
+METRIC = "camera-seg x VRL evals/sec (1080p, 100k VRLs)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--vrls", type=int, default=100000)
+    ap.add_argument("--q", type=int, default=1)
+    ap.add_argument("--no-occluders", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload(args):
+    import mitsuba_nlvrl_b200 as pkg
+    sc = pkg.scenes.box_fog_scene(occluders=not args.no_occluders)
+    cam = pkg.scenes.box_fog_camera(args.width, args.height)
+    opt = pkg.scenes.default_options(samples_per_query=args.q, visibility=0 if args.no_occluders else 1)
+    soa = pkg.scenes.synthetic_vrls(args.vrls, seed=1)
+    name = (f"box-fog {'V1 no occluders' if args.no_occluders else 'V2 occluders+BVH visibility'} "
+            f"{args.width}x{args.height} spp1 q{args.q} N_vrl={args.vrls} homogeneous isotropic importance-sampled")
+    return sc, cam, opt, soa, name
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, pw, reasons = [], [], [], set()
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 8:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); pw.append(float(c[3]))
+            except ValueError:
+                continue
+            for name, v in zip(self.NAMES, c[4:8]):
+                if v == "Active":
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # "under load": samples whose power draw is above the midpoint of the observed range
+        lo, hi = min(pw), max(pw)
+        load = [s for s, w in zip(sm, pw) if w >= lo + 0.5 * (hi - lo)] or sm
+        return {"sm_mhz": float(np.median(load)), "sm_max_mhz": float(max(mx)), "power_w_max": float(hi),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+def cpu_sample(sc, cam, opt, soa, seconds, n_threads=None):
+    """Times the CPU oracle (restatement of the reference's scalar gather) on a centred crop of the same frame
+    sized for ~`seconds` of work on all host cores.  Returns (evals_per_s, cores, sample description)."""
+    import oracle
+    import mitsuba_nlvrl_b200 as pkg
+    n_threads = n_threads or os.cpu_count()
+    vd = pkg.scenes.vrlset_desc(soa)
+    osc = oracle.OracleScene(sc)
+    cx, cy = cam.width // 2, cam.height // 2
+
+    def run(crop):
+        t0 = time.perf_counter()
+        _, _, ev = osc.render(cam, opt, vd, n_threads=n_threads, crop=crop)
+        return ev, time.perf_counter() - t0
+    bs = opt.block_size
+    nbx = (cam.width + bs - 1) // bs
+    # the oracle parallelises over 32x32 blocks like the reference (integrator.cpp:111-142): calibrate one
+    # thread on 4 pixels, then time a band that gives every thread the same number of pixel rows of a block
+    bx, by = (cx // bs) * bs, (cy // bs) * bs
+    ev, dt = run((bx, by, min(bx + 4, cam.width), by + 1))
+    per_thread = ev / max(dt, 1e-9)
+    per_px = max(soa.shape[1] * opt.samples_per_query, 1)
+    tb = min(n_threads, nbx)                       # blocks side by side
+    two_rows = n_threads > nbx and by >= bs        # straddle a block-row boundary to feed more threads
+    rows = int(max(1, min(bs, round(per_thread * seconds / per_px / bs))))
+    x0 = max(0, min(bx - (tb // 2) * bs, cam.width - tb * bs))
+    crop = (x0, by - rows if two_rows else by, min(x0 + tb * bs, cam.width), by + rows)
+    ev, dt = run(crop)
+    rate = ev / max(dt, 1e-9)
+    desc = (f"crop x[{crop[0]},{crop[2]}) y[{crop[1]},{crop[3]}) of the frame = {ev:.3e} evals in {dt:.1f} s, "
+            f"{n_threads} std::threads over 32x32 blocks")
+    return rate, n_threads, desc, ev, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    sc, cam, opt, soa, name = workload(args)
+    per_step = max(args.cpu_seconds / max(args.steps, 1), 2.0)
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample(sc, cam, opt, soa, 1.0)
+    tot_ev, tot_t, desc, cores = 0, 0.0, "", os.cpu_count()
+    for _ in range(args.steps):
+        rate, cores, desc, ev, dt = cpu_sample(sc, cam, opt, soa, per_step)
+        tot_ev += ev
+        tot_t += dt
+    value = tot_ev / tot_t
+    frame_evals = cam.width * cam.height * soa.shape[1] * opt.samples_per_query
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "ms_per_frame_extrapolated": 1e3 * frame_evals / value,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": name, "note": "each step = a bounded crop of the frame on the host cores"},
+            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc},
+            "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import mitsuba_nlvrl_b200 as pkg
+    api, scenes = pkg.api, pkg.scenes
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the VRL gather has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sc, cam, opt, soa, name = workload(args)
+    n_total = soa.shape[1]
+    lo, hi = rank * n_total // world, (rank + 1) * n_total // world
+    shard = np.ascontiguousarray(soa[:, lo:hi])
+    vd = scenes.vrlset_desc(shard, scale=1.0 / n_total, first_index=lo, total=n_total)
+
+    ctx = api.Context(local)
+    stream = torch.cuda.Stream()
+    ctx.set_stream(stream.cuda_stream)
+    if world > 1:
+        ids = [api.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(ids[0], rank, world)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(vd)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    gather_ms = []
+
+    def step():
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        n_segs = ctx.build_segments(cam, opt)
+        ctx.gather(opt)
+        if world > 1:
+            ctx.film_allreduce()
+        ctx.film_resolve()
+        return n_segs
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        n_segs = step()
+    barrier()
+    fp32_peak = ctx.measure_fp32_peak()
+    l0 = ctx.timing()["launches_lifetime"]
+    clocks = ClockSampler()
+    if rank == 0:
+        clocks.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        n_segs = step()
+        ctx.synchronize()
+        gather_ms.append(ctx.timing()["ms_gather"])
+    e1.record(stream)
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    launches = ctx.timing()["launches_lifetime"] - l0
+    frame_evals = n_segs * n_total * opt.samples_per_query
+    value = frame_evals * args.steps / (total_ms * 1e-3)
+
+    # ---- end to end through vrlb_render() from host buffers --------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        out = np.zeros((cam.height, cam.width, 5), np.float32) if rank == 0 else False
+        ctx.render(cam, opt, vd, out)                      # warm-up (allocations, pinned staging)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ctx.render(cam, opt, vd, out)
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": frame_evals * args.steps / float(dt.item()), "unit": "evals/s",
+               "h2d_bytes_per_step": int(shard.nbytes) * world, "d2h_bytes_per_step": int(cam.width * cam.height * 5 * 4),
+               "ms_per_frame": 1e3 * float(dt.item()) / args.steps}
+
+    if rank == 0:
+        g_ms = float(np.mean(gather_ms))
+        shard_evals = n_segs * (hi - lo) * opt.samples_per_query
+        achieved = shard_evals * FLOPS_PER_EVAL / (g_ms * 1e-3) * 1e-12
+        traffic = None
+        tr_file = os.path.join(ROOT, "profiles", "gather_traffic.json")
+        if os.path.exists(tr_file):
+            try:
+                traffic = json.load(open(tr_file)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {"metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": total_ms / args.steps, "ms_per_frame": total_ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": name, "n_segments": int(n_segs), "evals_per_frame": int(frame_evals),
+                           "parallelism": f"vrl-shard x{world} + NCCL fp32 film all-reduce" if world > 1 else "single GPU",
+                           "l2": "256 MB flush buffer written between steps; segment buffer 133 MB > L2"},
+                "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
+                             "frac": achieved / fp32_peak if fp32_peak else None, "traffic": traffic,
+                             "kernel": "gather_kernel", "ms_per_launch": g_ms, "flops_per_eval": FLOPS_PER_EVAL,
+                             "peak_source": "FFMA microkernel measured in this run (vrlb_measure_fp32_peak); "
+                                            "MEASURED_PEAKS.json has no FP32 entry"},
+                "clocks": clk, "gpu_launches": int(launches), "e2e": e2e}
+        if world == 1 and not args.no_cpu_baseline:
+            rate, cores, desc, _, _ = cpu_sample(sc, cam, opt, soa, args.cpu_seconds)
+            line["cpu_baseline"] = {"value": rate, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc}
+        print(json.dumps(line))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define VRLB_ABI_VERSION 1
+#define VRLB_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -173,6 +173,9 @@ typedef struct vrlb_timing {
     uint32_t total_launches;
     uint64_t n_evals;        /* P*S*q*N getContrib calls (vrl_struct.h:584)    */
     uint64_t n_segments;
+    uint64_t launches_lifetime; /* kernels of this library launched since vrlb_create (never reset) */
+    float    ms_reduce;      /* NCCL film all-reduce (0 when single GPU)       */
+    float    pad;
 } vrlb_timing;
 
 typedef struct vrlb_context vrlb_context;
@@ -223,6 +226,25 @@ int  vrlb_film_download_rgb(vrlb_context *ctx, float *rgb);
 /* ---- whole frame from host buffers: Integrator::render (integrator.cpp:51-183) --------------- */
 int  vrlb_render(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_options *opt,
                  const vrlb_vrlset_desc *vrls /* NULL: keep resident set */, float *xyzaw_out);
+
+/* ---- multi-GPU: VRLs are sharded across ranks (one context per GPU / process), every rank gathers all
+ *      pixels against its shard, and the fp32 RGB film buffers are summed with one NCCL all-reduce over
+ *      NVLink.  Replaces the mutex-protected HDRFilm::put merge (hdrfilm.cpp:210-214).
+ *      NCCL is bound at run time (dlopen of libnccl.so.2), so single-GPU users need no NCCL at all. ---- */
+#define VRLB_COMM_ID_BYTES 128
+int  vrlb_comm_unique_id(void *id /* VRLB_COMM_ID_BYTES, filled on the calling rank */);
+int  vrlb_comm_init(vrlb_context *ctx, const void *id, int rank, int n_ranks);
+int  vrlb_comm_destroy(vrlb_context *ctx);
+/* Sum the radiance film over all ranks in place, on the context's stream.  Emitter radiance seen
+ * directly (vrl.cpp:651-657) and the A/W channels are written by rank 0 only / replicated, so the
+ * sum counts them once. */
+int  vrlb_film_allreduce(vrlb_context *ctx);
+/* XYZAW conversion on the device only (no download); device pointer to width*height*5 floats. */
+int  vrlb_film_resolve(vrlb_context *ctx, void **dev_xyzaw);
+
+/* ---- measurement helper: FP32 FMA issue peak of this device, measured by an FFMA-saturating
+ *      microkernel (roofline denominator of the gather).  tflops = 2 flops per FMA. ---- */
+int  vrlb_measure_fp32_peak(vrlb_context *ctx, float *tflops);
 
 int  vrlb_cancel(vrlb_context *ctx);
 int  vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out);

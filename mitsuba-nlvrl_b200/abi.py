@@ -1,6 +1,7 @@
 """ctypes mirror of include/vrl_b200.h (the C ABI PODs).  Field order and types must match the header."""
 import ctypes as C
 
+COMM_ID_BYTES = 128
 OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CANCELLED, ERR_NOMEM = 0, -1, -2, -3, -4, -5
 
 SURF_BSDF_SMOOTH, SURF_BSDF_NULL, SURF_EMITTER = 0x0, 0x1, 0x4
@@ -60,7 +61,8 @@ class Segment(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("ms_upload", C.c_float), ("ms_segments", C.c_float), ("ms_gather", C.c_float), ("ms_film", C.c_float),
                 ("ms_download", C.c_float), ("gather_launches", C.c_uint32), ("total_launches", C.c_uint32),
-                ("n_evals", C.c_uint64), ("n_segments", C.c_uint64)]
+                ("n_evals", C.c_uint64), ("n_segments", C.c_uint64),
+                ("launches_lifetime", C.c_uint64), ("ms_reduce", C.c_float), ("pad", C.c_float)]
 
 
 assert C.sizeof(Segment) == 64

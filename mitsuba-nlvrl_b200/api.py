@@ -18,7 +18,8 @@ EXPORTS = [
     "vrlb_vrls_upload", "vrlb_vrls_download", "vrlb_vrls_count", "vrlb_segments_build", "vrlb_segments_upload",
     "vrlb_segments_download", "vrlb_segments_count", "vrlb_film_clear", "vrlb_gather", "vrlb_gather_segments",
     "vrlb_film_device_ptr", "vrlb_film_download_xyzaw", "vrlb_film_download_rgb", "vrlb_render", "vrlb_cancel",
-    "vrlb_get_timing", "vrlb_synchronize",
+    "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
+    "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak",
 ]
 
 
@@ -68,10 +69,12 @@ def load_library():
     L.vrlb_cancel.argtypes = [vp]
     L.vrlb_get_timing.argtypes = [vp, C.POINTER(abi.Timing)]
     L.vrlb_synchronize.argtypes = [vp]
-    for name in EXPORTS:
-        fn = getattr(L, name)
-        if fn.restype is C.c_int and name not in ("vrlb_abi_version",):
-            pass
+    L.vrlb_comm_unique_id.argtypes = [vp]
+    L.vrlb_comm_init.argtypes = [vp, vp, C.c_int, C.c_int]
+    L.vrlb_comm_destroy.argtypes = [vp]
+    L.vrlb_film_allreduce.argtypes = [vp]
+    L.vrlb_film_resolve.argtypes = [vp, C.POINTER(vp)]
+    L.vrlb_measure_fp32_peak.argtypes = [vp, f32p]
     _lib = L
     return L
 
@@ -164,8 +167,37 @@ class Context:
         if out is None:
             out = np.zeros((cam.height, cam.width, 5), np.float32)
         self._check(self.lib.vrlb_render(self.h, C.byref(cam), C.byref(opt), C.byref(vrl_desc) if vrl_desc is not None else None,
-                                         abi.fptr(out)))
+                                         abi.fptr(out) if out is not False else None))
         return out
+
+    # ---- multi-GPU film reduce (one Context per rank) ----
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(abi.COMM_ID_BYTES)
+        rc = load_library().vrlb_comm_unique_id(buf)
+        if rc != abi.OK:
+            raise VrlbError(rc, load_library().vrlb_last_error(None).decode())
+        return buf.raw
+
+    def comm_init(self, unique_id, rank, n_ranks):
+        buf = C.create_string_buffer(bytes(unique_id), abi.COMM_ID_BYTES)
+        self._check(self.lib.vrlb_comm_init(self.h, buf, rank, n_ranks))
+
+    def comm_destroy(self):
+        self._check(self.lib.vrlb_comm_destroy(self.h))
+
+    def film_allreduce(self):
+        self._check(self.lib.vrlb_film_allreduce(self.h))
+
+    def film_resolve(self):
+        p = C.c_void_p()
+        self._check(self.lib.vrlb_film_resolve(self.h, C.byref(p)))
+        return p.value
+
+    def measure_fp32_peak(self):
+        t = C.c_float()
+        self._check(self.lib.vrlb_measure_fp32_peak(self.h, C.byref(t)))
+        return float(t.value)
 
     def cancel(self):
         self._check(self.lib.vrlb_cancel(self.h))

@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
             if (!(active_surface || active_medium)) break;                            // vrl.cpp:719
         }
         if (on_film) {
-            if (radiance.x != 0.f || radiance.y != 0.f || radiance.z != 0.f) {
+            if (p.add_direct && (radiance.x != 0.f || radiance.y != 0.f || radiance.z != 0.f)) {
                 atomicAdd(p.film_rgb + (size_t) film_pixel * 3 + 0, radiance.x);
                 atomicAdd(p.film_rgb + (size_t) film_pixel * 3 + 1, radiance.y);
                 atomicAdd(p.film_rgb + (size_t) film_pixel * 3 + 2, radiance.z);

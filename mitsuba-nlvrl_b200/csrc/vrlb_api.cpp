@@ -5,6 +5,7 @@
 // VRLIntegrator::preprocess/render (src/integrators/vrl/vrl.cpp) around the kernels of gather.cu and
 // segments.cu.  No CPU compute fallback: without a usable CUDA device every entry point fails.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <atomic>
 #include <cstdarg>
@@ -22,6 +23,7 @@ using namespace vrlb;
 namespace {
 
 std::string g_create_error;
+int (*g_nccl_destroy)(void *) = nullptr;   // set once NCCL is bound (vrlb_comm_*)
 
 template <typename T> struct DevBuf {
     T *ptr = nullptr; size_t cap = 0;
@@ -67,8 +69,12 @@ struct vrlb_context {
     // pinned staging for host<->device copies of the e2e path
     void *pinned = nullptr; size_t pinned_cap = 0;
 
-    cudaEvent_t ev[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
+    cudaEvent_t ev[8] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
     vrlb_timing timing{};
+    uint64_t launches = 0;       // lifetime kernel-launch count of this library
+
+    // multi-GPU film reduce
+    void *nccl_comm = nullptr; int rank = 0, n_ranks = 1;
 };
 
 namespace {
@@ -165,6 +171,7 @@ void vrlb_destroy(vrlb_context *ctx) {
     cudaStreamSynchronize(ctx->stream);
     ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->media.release(); ctx->emitters.release();
     ctx->vrls.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
+    if (ctx->nccl_comm && g_nccl_destroy) g_nccl_destroy(ctx->nccl_comm);
     ctx->block_ids.release(); ctx->film_rgb.release(); ctx->film_aw.release(); ctx->film_xyzaw.release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -195,6 +202,9 @@ int vrlb_cancel(vrlb_context *ctx) { if (!ctx) return VRLB_ERR_INVALID; ctx->can
 int vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out) {
     if (!ctx || !out) return VRLB_ERR_INVALID;
     *out = ctx->timing;
+    out->launches_lifetime = ctx->launches;
+    // kernel durations from the CUDA events recorded around them on the library's stream, once complete
+    if (ctx->timing.gather_launches && cudaEventQuery(ctx->ev[3]) == cudaSuccess) out->ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
     return VRLB_OK;
 }
 
@@ -273,6 +283,7 @@ int vrlb_vrls_upload(vrlb_context *ctx, const vrlb_vrlset_desc *set) {
             CU(ctx, cudaMemcpyAsync(ctx->stage_med.ptr, (char *) ctx->pinned + soa_bytes, med_bytes, cudaMemcpyHostToDevice, ctx->stream));
         }
         CU(ctx, launch_pack_vrls(ctx->stage_soa.ptr, set->medium ? ctx->stage_med.ptr : nullptr, n, ctx->vrls.ptr, ctx->stream));
+        ctx->timing.total_launches += 1; ctx->launches += 1;
     }
     cudaEventRecord(ctx->ev[1], ctx->stream);
     CU(ctx, cudaStreamSynchronize(ctx->stream));
@@ -292,6 +303,7 @@ int vrlb_vrls_download(vrlb_context *ctx, float *soa10, uint16_t *medium, uint64
     if (n == 0) return VRLB_OK;
     CU(ctx, ctx->stage_soa.reserve(n * 10)); CU(ctx, ctx->stage_med.reserve(n));
     CU(ctx, launch_unpack_vrls(ctx->vrls.ptr, n, ctx->stage_soa.ptr, ctx->stage_med.ptr, ctx->stream));
+    ctx->launches += 1;
     CU(ctx, cudaMemcpyAsync(soa10, ctx->stage_soa.ptr, n * 10 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     if (medium) CU(ctx, cudaMemcpyAsync(medium, ctx->stage_med.ptr, n * sizeof(uint16_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
@@ -328,6 +340,7 @@ int vrlb_segments_build(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_op
         p.nbx = (cam->width + opt->block_size - 1) / opt->block_size; p.nby = (cam->height + opt->block_size - 1) / opt->block_size;
         p.n_vrls_total = ctx->vrl_total; p.segs = ctx->segs.ptr; p.cap = ctx->segs.cap; p.counter = ctx->counter.ptr;
         p.film_rgb = ctx->film_rgb.ptr; p.film_aw = ctx->film_aw.ptr;
+        p.add_direct = ctx->rank == 0 ? 1 : 0;   // emitter radiance is counted once across VRL shards
         size_t np = (size_t) cam->width * cam->height;
         cudaEventRecord(ctx->ev[0], ctx->stream);
         CU(ctx, cudaMemsetAsync(ctx->counter.ptr, 0, sizeof(unsigned long long), ctx->stream));
@@ -339,7 +352,7 @@ int vrlb_segments_build(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_op
         CU(ctx, cudaMemcpyAsync(&n, ctx->counter.ptr, sizeof n, cudaMemcpyDeviceToHost, ctx->stream));
         CU(ctx, cudaStreamSynchronize(ctx->stream));
         ctx->timing.ms_segments = elapsed(ctx->ev[0], ctx->ev[1]);
-        ctx->timing.total_launches += 1;
+        ctx->timing.total_launches += 1; ctx->launches += 1;
         if (n <= ctx->segs.cap) { ctx->n_segs = n; ctx->timing.n_segments = n; return VRLB_OK; }
         cap = n;
     }
@@ -401,7 +414,7 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     cudaEventRecord(ctx->ev[3], ctx->stream);
     bool launched = p.n_segs && p.n_vrls;
     ctx->timing.gather_launches = launched ? 1 : 0;
-    ctx->timing.total_launches += launched ? 1 : 0;
+    ctx->timing.total_launches += launched ? 1 : 0; ctx->launches += launched ? 1 : 0;
     ctx->timing.n_evals = p.n_segs * p.n_vrls * p.q;
     return VRLB_OK;
 }
@@ -438,22 +451,34 @@ int vrlb_film_device_ptr(vrlb_context *ctx, void **dev_ptr, uint64_t *n_floats) 
     return VRLB_OK;
 }
 
-int vrlb_film_download_xyzaw(vrlb_context *ctx, float *xyzaw) {
-    if (!ctx || !xyzaw) return VRLB_ERR_INVALID;
+int vrlb_film_resolve(vrlb_context *ctx, void **dev_xyzaw) {
+    if (!ctx) return VRLB_ERR_INVALID;
     cudaSetDevice(ctx->device);
     if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no film yet");
     size_t np = (size_t) ctx->width * ctx->height;
     cudaEventRecord(ctx->ev[4], ctx->stream);
     CU(ctx, launch_film_xyzaw(ctx->film_rgb.ptr, ctx->film_aw.ptr, ctx->film_xyzaw.ptr, np, ctx->stream));
     cudaEventRecord(ctx->ev[5], ctx->stream);
-    int rc = ensure_pinned(ctx, np * 5 * sizeof(float));
+    ctx->timing.total_launches += 1; ctx->launches += 1;
+    if (dev_xyzaw) *dev_xyzaw = ctx->film_xyzaw.ptr;
+    return VRLB_OK;
+}
+
+int vrlb_film_download_xyzaw(vrlb_context *ctx, float *xyzaw) {
+    if (!ctx || !xyzaw) return VRLB_ERR_INVALID;
+    int rc = vrlb_film_resolve(ctx, nullptr);
     if (rc) return rc;
+    size_t np = (size_t) ctx->width * ctx->height;
+    rc = ensure_pinned(ctx, np * 5 * sizeof(float));
+    if (rc) return rc;
+    cudaEventRecord(ctx->ev[6], ctx->stream);
     CU(ctx, cudaMemcpyAsync(ctx->pinned, ctx->film_xyzaw.ptr, np * 5 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    cudaEventRecord(ctx->ev[7], ctx->stream);
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     std::memcpy(xyzaw, ctx->pinned, np * 5 * sizeof(float));
     ctx->timing.ms_film = elapsed(ctx->ev[4], ctx->ev[5]);
-    ctx->timing.ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
-    ctx->timing.total_launches += 1;
+    ctx->timing.ms_download = elapsed(ctx->ev[6], ctx->ev[7]);
+    if (ctx->timing.gather_launches) ctx->timing.ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
     return VRLB_OK;
 }
 
@@ -470,14 +495,109 @@ int vrlb_film_download_rgb(vrlb_context *ctx, float *rgb) {
 
 // ---- whole frame (Integrator::render, integrator.cpp:51-183): upload -> segments -> gather -> film ----
 int vrlb_render(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_options *opt, const vrlb_vrlset_desc *vrls, float *xyzaw_out) {
-    if (!ctx || !cam || !opt || !xyzaw_out) return VRLB_ERR_INVALID;
+    if (!ctx || !cam || !opt) return VRLB_ERR_INVALID;
+    if (!xyzaw_out && ctx->rank == 0) return fail(ctx, VRLB_ERR_INVALID, "xyzaw_out is NULL (only ranks > 0 may skip the film download)");
     ctx->timing = vrlb_timing{};
     int rc;
     if (vrls && (rc = vrlb_vrls_upload(ctx, vrls)) != VRLB_OK) return rc;
-    if (ctx->vrl_total == 0 && ctx->n_vrls == 0) { /* empty map: VRLMap::query returns 0 (vrl_map.h:134-137) */ }
     if ((rc = vrlb_segments_build(ctx, cam, opt)) != VRLB_OK) return rc;
+    /* an empty map is fine: VRLMap::query returns 0 (vrl_map.h:134-137) */
     if ((rc = vrlb_gather(ctx, opt)) != VRLB_OK) return rc;
-    return vrlb_film_download_xyzaw(ctx, xyzaw_out);
+    if (ctx->n_ranks > 1 && (rc = vrlb_film_allreduce(ctx)) != VRLB_OK) return rc;
+    if (xyzaw_out) return vrlb_film_download_xyzaw(ctx, xyzaw_out);
+    return vrlb_synchronize(ctx);
+}
+
+// ---- multi-GPU film reduce: NCCL bound at run time ---------------------------------------------------
+struct Id128 { char bytes[VRLB_COMM_ID_BYTES]; };   // ncclUniqueId is passed by value
+namespace {
+struct NcclApi {
+    void *lib = nullptr;
+    int (*GetUniqueId)(void *) = nullptr;
+    int (*CommInitRank)(void **, int, Id128, int) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+const char *load_nccl() {
+    if (g_nccl.lib) return nullptr;
+    // the soname first: inside a process that already loaded NCCL (e.g. torch) this binds to that copy
+    const char *names[] = { "libnccl.so.2", "libnccl.so" };
+    void *h = nullptr;
+    for (const char *n : names) if ((h = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+    if (!h) return "libnccl.so.2 not found (dlopen)";
+    g_nccl.GetUniqueId   = (decltype(g_nccl.GetUniqueId)) dlsym(h, "ncclGetUniqueId");
+    g_nccl.CommInitRank  = (decltype(g_nccl.CommInitRank)) dlsym(h, "ncclCommInitRank");
+    g_nccl.CommDestroy   = (decltype(g_nccl.CommDestroy)) dlsym(h, "ncclCommDestroy");
+    g_nccl.AllReduce     = (decltype(g_nccl.AllReduce)) dlsym(h, "ncclAllReduce");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString)) dlsym(h, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce) return "NCCL symbols missing";
+    g_nccl.lib = h; g_nccl_destroy = g_nccl.CommDestroy;
+    return nullptr;
+}
+const char *nccl_err(int rc) { return g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error"; }
+}  // namespace
+
+int vrlb_comm_unique_id(void *id) {
+    if (!id) return VRLB_ERR_INVALID;
+    if (const char *e = load_nccl()) return fail(nullptr, VRLB_ERR_STATE, "%s", e);
+    int rc = g_nccl.GetUniqueId(id);
+    if (rc != 0) return fail(nullptr, VRLB_ERR_CUDA, "ncclGetUniqueId: %s", nccl_err(rc));
+    return VRLB_OK;
+}
+
+int vrlb_comm_init(vrlb_context *ctx, const void *id, int rank, int n_ranks) {
+    if (!ctx || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->nccl_comm) return fail(ctx, VRLB_ERR_STATE, "communicator already initialised");
+    if (const char *e = load_nccl()) return fail(ctx, VRLB_ERR_STATE, "%s", e);
+    Id128 uid; std::memcpy(uid.bytes, id, sizeof uid.bytes);
+    int rc = g_nccl.CommInitRank(&ctx->nccl_comm, n_ranks, uid, rank);
+    if (rc != 0) { ctx->nccl_comm = nullptr; return fail(ctx, VRLB_ERR_CUDA, "ncclCommInitRank: %s", nccl_err(rc)); }
+    ctx->rank = rank; ctx->n_ranks = n_ranks;
+    return VRLB_OK;
+}
+
+int vrlb_comm_destroy(vrlb_context *ctx) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    if (ctx->nccl_comm) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); g_nccl.CommDestroy(ctx->nccl_comm); }
+    ctx->nccl_comm = nullptr; ctx->rank = 0; ctx->n_ranks = 1;
+    return VRLB_OK;
+}
+
+int vrlb_film_allreduce(vrlb_context *ctx) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no film yet");
+    if (ctx->n_ranks == 1) return VRLB_OK;
+    if (!ctx->nccl_comm) return fail(ctx, VRLB_ERR_STATE, "vrlb_comm_init must precede vrlb_film_allreduce");
+    size_t n = (size_t) ctx->width * ctx->height * 3;
+    int rc = g_nccl.AllReduce(ctx->film_rgb.ptr, ctx->film_rgb.ptr, n, /* ncclFloat32 */ 7, /* ncclSum */ 0, ctx->nccl_comm, ctx->stream);
+    if (rc != 0) return fail(ctx, VRLB_ERR_CUDA, "ncclAllReduce: %s", nccl_err(rc));   // NCCL errors abort the render
+    return VRLB_OK;
+}
+
+int vrlb_measure_fp32_peak(vrlb_context *ctx, float *tflops) {
+    if (!ctx || !tflops) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaDeviceProp prop; CU(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+    DevBuf<float> scratch; CU(ctx, scratch.reserve(4));
+    const int blocks = prop.multiProcessorCount * 8, iters = 4096;
+    float best = 0.f;
+    for (int rep = 0; rep < 6; ++rep) {
+        cudaEventRecord(ctx->ev[0], ctx->stream);
+        CU(ctx, launch_fp32_peak(scratch.ptr, blocks, iters, ctx->stream));
+        cudaEventRecord(ctx->ev[1], ctx->stream);
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->launches += 1;
+        double flops = (double) blocks * 256.0 * iters * 64.0 * 2.0;
+        float t = (float) (flops / (elapsed(ctx->ev[0], ctx->ev[1]) * 1e-3) * 1e-12);
+        if (rep > 0 && t > best) best = t;
+    }
+    scratch.release();
+    *tflops = best;
+    return VRLB_OK;
 }
 
 }  // extern "C"

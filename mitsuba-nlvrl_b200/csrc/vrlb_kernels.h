@@ -37,6 +37,7 @@ struct SegmentParams {
     unsigned long long *counter; // device: number of segments appended (may exceed cap -> overflow)
     float        *film_rgb;      // device: emitter radiance seen directly is added here
     float        *film_aw;       // device: width*height*2: sum(alpha), sum(weight)
+    int32_t       add_direct;    // 0 on ranks > 0 of a VRL-sharded render: emitter radiance is counted once
 };
 cudaError_t launch_segments(const SegmentParams &p, cudaStream_t stream);
 
@@ -45,5 +46,8 @@ cudaError_t launch_film_xyzaw(const float *film_rgb, const float *film_aw, float
 // SoA10 (+ medium ids) -> 48 B records, and back
 cudaError_t launch_pack_vrls(const float *soa10, const uint16_t *medium, uint64_t n, DVrl *out, cudaStream_t stream);
 cudaError_t launch_unpack_vrls(const DVrl *in, uint64_t n, float *soa10, uint16_t *medium, cudaStream_t stream);
+
+// FFMA-saturating microkernel (peak.cu)
+cudaError_t launch_fp32_peak(float *scratch, int blocks, int iters, cudaStream_t stream);
 
 }  // namespace vrlb

@@ -1,0 +1,282 @@
+"""CPU suite (-m "not gpu"): pins the oracle against the golden vectors generated from the reference's own
+Enoki headers (tests/golden/enoki_pcg32.json, oracle/enoki_probe.cpp), the known answers the reference's
+tests hold for this path (src/samplers/tests/test_independent.py:28-33, src/phase/tests/test_isotropic.py:14-26)
+and closed-form properties of the sampling routines ("closed-form checks")."""
+import ctypes as C
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from mitsuba_nlvrl_b200 import abi, api, scenes
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+DEFAULT_STATE, DEFAULT_STREAM = 0x853c49e6748fea9b, 0xda3e39cb94b95bdb
+
+
+@pytest.fixture(scope="module")
+def gold():
+    with open(os.path.join(GOLD, "enoki_pcg32.json")) as f:
+        return json.load(f)
+
+
+def _pcg(initstate, initseq=DEFAULT_STREAM):
+    st, inc = C.c_uint64(), C.c_uint64()
+    oracle.lib().vrlo_pcg32_seed(initstate, initseq, C.byref(st), C.byref(inc))
+    return st, inc
+
+
+def test_pcg32_default_stream_matches_enoki(gold):
+    st, inc = _pcg(DEFAULT_STATE)
+    got = [oracle.lib().vrlo_pcg32_next_u32(C.byref(st), inc.value) for _ in range(30)]
+    assert got == gold["default_u32"]
+    f = np.array([((u >> 9) | 0x3f800000) for u in got], np.uint32).view(np.float32) - np.float32(1.0)
+    assert np.array_equal(f, np.array(gold["default_f32"], np.float32))
+
+
+def test_sampler_seeding_matches_enoki(gold):
+    for seed, want in gold["seeded"].items():
+        out_f, out_u = np.zeros(16, np.float32), np.zeros(16, np.uint32)
+        oracle.lib().vrlo_sampler_stream(0, int(seed), 16, oracle.fp(out_f), out_u.ctypes.data_as(C.POINTER(C.c_uint32)))
+        assert out_u.tolist() == want, seed
+        # base_seed + offset is what is seeded (sampler.cpp:87-94)
+        oracle.lib().vrlo_sampler_stream(int(seed), 0, 16, oracle.fp(out_f), out_u.ctypes.data_as(C.POINTER(C.c_uint32)))
+        assert out_u.tolist() == want, seed
+
+
+def test_pcg32_advance_matches_enoki(gold):
+    for delta, state, nxt in gold["advance"]:
+        st, inc = _pcg(42)
+        oracle.lib().vrlo_pcg32_advance(C.byref(st), inc.value, delta)
+        # the probe's printf evaluates its arguments right to left: `state` is the state AFTER the draw
+        assert oracle.lib().vrlo_pcg32_next_u32(C.byref(st), inc.value) == nxt, delta
+        assert st.value == int(state), delta
+
+
+def test_morton_matches_enoki(gold):
+    for i, x, y in gold["morton"]:
+        gx, gy = C.c_uint32(), C.c_uint32()
+        oracle.lib().vrlo_morton_decode(i, C.byref(gx), C.byref(gy))
+        assert (gx.value, gy.value) == (x, y)
+
+
+def test_spiral_ids_are_a_permutation_starting_at_centre():
+    w, h, bs = 1920, 1080, 32
+    nbx, nby = (w + bs - 1) // bs, (h + bs - 1) // bs
+    ids = np.zeros(nbx * nby, np.uint32)
+    n = oracle.lib().vrlo_spiral_block_ids(w, h, bs, ids.ctypes.data_as(C.POINTER(C.c_uint32)), len(ids))
+    assert n == nbx * nby and sorted(ids.tolist()) == list(range(n))
+    assert ids.reshape(nby, nbx)[nby // 2, nbx // 2] == 0          # spiral.cpp:27-33 starts at the centre block
+
+
+def test_isotropic_known_answer():
+    """src/phase/tests/test_isotropic.py:14-26: eval == 1/(4 pi) for any directions."""
+    m = scenes.make_medium(phase=abi.PHASE_ISOTROPIC)
+    rng = np.random.default_rng(0)
+    for _ in range(20):
+        wi, wo = (oracle.f32(v / np.linalg.norm(v)) for v in rng.normal(size=(2, 3)))
+        assert oracle.lib().vrlo_phase_eval(C.byref(m), oracle.fp(wi), oracle.fp(wo)) == pytest.approx(1 / (4 * math.pi), rel=1e-7)
+
+
+def test_hg_normalised_and_matches_formula():
+    """hg.cpp:51-54: 1/4pi (1-g^2) / (1+g^2+2g cos)^1.5, integrates to one over the sphere (chi2 pin of test_hg.py)."""
+    g = 0.6
+    m = scenes.make_medium(phase=abi.PHASE_HG, g=g)
+    wi = oracle.f32([0, 0, 1])
+    mu = np.linspace(-1, 1, 4001)
+    vals = []
+    for c in mu:
+        wo = oracle.f32([math.sqrt(max(0, 1 - c * c)), 0, c])
+        vals.append(oracle.lib().vrlo_phase_eval(C.byref(m), oracle.fp(wi), oracle.fp(wo)))
+    vals = np.array(vals, np.float64)
+    want = (1 - g * g) / (4 * math.pi * (1 + g * g + 2 * g * mu) ** 1.5)
+    assert np.allclose(vals, want, rtol=2e-6)
+    assert 2 * math.pi * np.trapezoid(vals, mu) == pytest.approx(1.0, rel=1e-4)
+
+
+def _closest(vo, vd, vl, ro, rd, rl):
+    tc, tv = C.c_float(), C.c_float()
+    a = [oracle.f32(x) for x in (vo, vd, ro, rd)]
+    oracle.lib().vrlo_find_closest_point(oracle.fp(a[0]), oracle.fp(a[1]), vl, oracle.fp(a[2]), oracle.fp(a[3]), rl,
+                                         C.cast(C.byref(tc), C.POINTER(C.c_float)), C.cast(C.byref(tv), C.POINTER(C.c_float)))
+    return tc.value, tv.value
+
+
+def test_find_closest_point_vs_brute_force():
+    rng = np.random.default_rng(1)
+    for _ in range(50):
+        vo, ro = rng.uniform(-5, 5, (2, 3))
+        vd, rd = (v / np.linalg.norm(v) for v in rng.normal(size=(2, 3)))
+        vl, rl = rng.uniform(0.5, 8, 2)
+        tc, tv = _closest(vo, vd, vl, ro, rd, rl)
+        s = np.linspace(0, vl, 801)[:, None, None]
+        t = np.linspace(0, rl, 801)[None, :, None]
+        d2 = (((vo + s * vd) - (ro + t * rd)) ** 2).sum(-1)
+        got = np.linalg.norm((vo + tv * vd) - (ro + tc * rd))
+        assert got <= math.sqrt(d2.min()) * (1 + 1e-4) + 1e-4
+        assert -1e-6 <= tc <= rl * (1 + 1e-6) and -1e-6 <= tv <= vl * (1 + 1e-6)
+
+
+def test_find_closest_point_perpendicular_skew():
+    tc, tv = _closest([0, 0, 0], [1, 0, 0], 4.0, [2, 3, -2], [0, 0, 1], 4.0)
+    assert (tc, tv) == pytest.approx((2.0, 2.0))
+
+
+def _sample(vrl, ray, uniform, u1, u2):
+    out = np.zeros(9, np.float32)
+    a = [oracle.f32(x) for x in (vrl[0], vrl[1], ray[0], ray[1])]
+    ok = oracle.lib().vrlo_sampling_vrl(oracle.fp(a[0]), oracle.fp(a[1]), vrl[2], oracle.fp(a[2]), oracle.fp(a[3]), ray[2],
+                                        uniform, u1, u2, oracle.fp(out))
+    return ok, out
+
+
+def test_importance_and_uniform_sampling_estimate_the_same_integral():
+    """E[f * invPDF] must equal the double integral of f = 1/d^2 over both segments for both strategies
+    (vrl_struct.h:239-243 vs 251-360); checked against midpoint quadrature."""
+    vrl = (np.array([0.0, 0, 0]), np.array([1.0, 0, 0]), 3.0)
+    ray = (np.array([1.0, 2.0, -2.0]), np.array([0.0, 0.0, 1.0]), 5.0)
+    n = 400
+    s = (np.arange(n) + 0.5) / n * vrl[2]
+    t = (np.arange(n) + 0.5) / n * ray[2]
+    P = vrl[0] + s[:, None, None] * vrl[1]
+    Q = ray[0] + t[None, :, None] * ray[1]
+    quad = (1.0 / ((P - Q) ** 2).sum(-1)).mean() * vrl[2] * ray[2]
+    m = 96
+    us = (np.arange(m) + 0.5) / m
+    for uniform in (0, 1):
+        acc = 0.0
+        for u1 in us:
+            for u2 in us:
+                ok, o = _sample(vrl, ray, uniform, float(u1), float(u2))
+                assert ok
+                d2 = ((o[0:3].astype(np.float64) - o[4:7]) ** 2).sum()
+                acc += o[8] / d2
+        assert acc / (m * m) == pytest.approx(quad, rel=2e-3 if not uniform else 2e-2)
+
+
+def test_sampling_early_outs():
+    # parallel segments: sin(theta) == 0 -> invalid (vrl_struct.h:275-278)
+    ok, _ = _sample((np.zeros(3), np.array([0, 0, 1.0]), 2.0), (np.array([1.0, 0, 0]), np.array([0, 0, 1.0]), 2.0), 0, 0.3, 0.6)
+    assert ok == 0
+    # intersecting segments: h == 0 -> invalid (vrl_struct.h:264-265)
+    ok, _ = _sample((np.array([-1.0, 0, 0]), np.array([1.0, 0, 0]), 2.0), (np.array([0, -1.0, 0]), np.array([0, 1.0, 0]), 2.0), 0, 0.3, 0.6)
+    assert ok == 0
+
+
+def test_homogeneous_transmittance_is_grey_mean_sigma_t():
+    """medium.h:103-117 + constant3d.cpp:37: exp(-scale * mean(sigma_t) * t), the same for the three channels."""
+    sc = scenes.Scene()
+    sc.add_medium(scenes.make_medium(sigma_t=(0.3, 0.6, 0.9), albedo=(0.5,) * 3, scale=2.0))
+    osc = oracle.OracleScene(sc)
+    tr = osc.transmittance([0, 0, 0], [0, 0, 1.5], medium=0)
+    assert np.allclose(tr, math.exp(-2.0 * 0.6 * 1.5), rtol=1e-6) and tr[0] == tr[1] == tr[2]
+
+
+def test_shadow_query_occluder_and_null_boundary():
+    """vrl_struct.h:525-569: a non-null surface zeroes the transmittance; Null::eval returns 0 (null.cpp:59-62),
+    so does an index-matched boundary."""
+    sc = scenes.box_fog_scene(occluders=True)
+    osc = oracle.OracleScene(sc)
+    assert np.all(osc.transmittance([4.5, -2, -9], [4.5, -2, 9]) == 0)           # through the sphere
+    free = osc.transmittance([-8, 8, -8], [-8, 8, 8])
+    assert np.allclose(free, math.exp(-0.11 * 16), rtol=1e-5)
+    assert np.all(osc.transmittance([0, 0, -9], [0, 0, -10.5]) == 0)             # across the null fog boundary
+
+
+def test_oracle_ray_intersect_vs_naive():
+    """kd-tree vs naive (src/librender/tests/test_kdtrees.py): the oracle's BVH must return the brute-force closest hit."""
+    sc = scenes.box_fog_scene(occluders=True)
+    osc = oracle.OracleScene(sc)
+    V = sc.tri_verts.astype(np.float64)
+    rng = np.random.default_rng(5)
+    for _ in range(60):
+        o = rng.uniform(-9, 9, 3)
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        e1, e2 = V[:, 1] - V[:, 0], V[:, 2] - V[:, 0]
+        p = np.cross(d, e2)
+        det = (e1 * p).sum(1)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            inv = 1 / det
+            tv = o - V[:, 0]
+            u = (tv * p).sum(1) * inv
+            q = np.cross(tv, e1)
+            v = (q * d).sum(1) * inv
+            t = (e2 * q).sum(1) * inv
+        okm = (u >= 0) & (v >= 0) & (u + v <= 1) & (t > 1e-4) & np.isfinite(t)
+        prim, tt, _, _ = osc.intersect(o, d, 1e-4)
+        if okm.any():
+            assert prim >= 0 and tt == pytest.approx(t[okm].min(), rel=1e-4, abs=1e-4)
+        else:
+            assert prim < 0
+
+
+def test_sequential_and_addressed_streams_agree_without_early_outs():
+    """the addressed PCG32 convention equals the reference's sequential consumption whenever no
+    eval takes an early-out before its draws (the generic case)."""
+    sc = scenes.box_fog_scene(occluders=True)
+    cam = scenes.box_fog_camera(16, 9)
+    opt = scenes.default_options()
+    soa = scenes.synthetic_vrls(300, seed=9)
+    vd = scenes.vrlset_desc(soa)
+    osc = oracle.OracleScene(sc)
+    a, _, ev_a = osc.render(cam, opt, vd, rng_mode=oracle.RNG_ADDRESSED)
+    b, _, ev_b = osc.render(cam, opt, vd, rng_mode=oracle.RNG_SEQUENTIAL)
+    assert ev_a == ev_b == 16 * 9 * 300
+    assert np.array_equal(a, b)
+
+
+def test_film_contract_xyzaw():
+    """integrator.cpp:282-294 / imageblock.cpp:162-169: XYZ = srgb_to_xyz(rgb), A = valid ray, W = 1 per sample."""
+    sc = scenes.box_fog_scene(occluders=False)
+    cam = scenes.box_fog_camera(16, 9)
+    opt = scenes.default_options(visibility=0, spp=2)
+    soa = scenes.synthetic_vrls(64, seed=2)
+    xyzaw, rgb, _ = oracle.OracleScene(sc).render(cam, opt, scenes.vrlset_desc(soa))
+    assert np.all(xyzaw[..., 4] <= 2.0) and xyzaw[..., 4].sum() == pytest.approx(16 * 9 * 2, abs=8)   # jitter may splat next door
+    M = np.array([[0.412453, 0.357580, 0.180423], [0.212671, 0.715160, 0.072169], [0.019334, 0.119193, 0.950227]])
+    one = scenes.default_options(visibility=0, spp=1)
+    xyzaw1, rgb1, _ = oracle.OracleScene(sc).render(cam, one, scenes.vrlset_desc(soa))
+    assert np.allclose(xyzaw1[..., :3], rgb1 @ M.T, rtol=1e-5, atol=1e-12)
+    assert np.all(xyzaw1[..., 4] == 1.0)
+
+
+# ------------------------------------------------------------------------------------------ C ABI (no GPU)
+def test_library_exports_every_declared_symbol():
+    import re
+    hdr = open(os.path.join(os.path.dirname(GOLD), "..", "include", "vrl_b200.h")).read()
+    declared = set(re.findall(r"\b(vrlb_[a-z0-9_]+)\s*\(", hdr))
+    lib = api.load_library()
+    missing = [s for s in sorted(declared) if not hasattr(lib, s)]
+    assert not missing, missing
+    assert declared == set(api.EXPORTS), declared ^ set(api.EXPORTS)
+    assert lib.vrlb_abi_version() == 2
+
+
+def test_pod_layouts_match_header(tmp_path):
+    """sizeof of every POD as the C compiler lays out include/vrl_b200.h == the ctypes mirror."""
+    import subprocess
+    names = {"vrlb_segment": abi.Segment, "vrlb_options": abi.Options, "vrlb_camera": abi.Camera, "vrlb_vrlset_desc": abi.VrlSetDesc,
+             "vrlb_timing": abi.Timing, "vrlb_medium": abi.Medium, "vrlb_scene_desc": abi.SceneDesc, "vrlb_emitter": abi.Emitter}
+    src = tmp_path / "sz.c"
+    body = "".join(f'printf("{n} %zu\\n", sizeof({n}));' for n in names)
+    src.write_text('#include <stdio.h>\n#include "vrl_b200.h"\nint main(void){' + body + "return 0;}")
+    exe = tmp_path / "sz"
+    inc = os.path.join(os.path.dirname(GOLD), "..", "include")
+    subprocess.check_call(["gcc", "-std=c99", "-I", inc, "-o", str(exe), str(src)])      # the header is plain C
+    for line in subprocess.check_output([str(exe)]).decode().splitlines():
+        n, sz = line.split()
+        assert C.sizeof(names[n]) == int(sz), n
+    assert C.sizeof(abi.Segment) == 64 and abi.SEGMENT_DTYPE.itemsize == 64
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(api.VrlbError) as e:
+        api.Context(0)
+    assert e.value.code == abi.ERR_CUDA
