@@ -128,8 +128,12 @@ typedef struct vrlb_options {
     int32_t  visibility;            /* 1: trace shadow segments through the BVH; 0: scene has no
                                        occluder between medium points (Tr_vis = medium Tr) */
     int32_t  hide_emitters;
-    int32_t  math_mode;             /* 0: exact (IEEE op order of the oracle), 1: fast intrinsics */
-    int32_t  reserved[2];
+    int32_t  math_mode;             /* 0: exact (the reference's IEEE operation order, every eval);
+                                       1: production: fast arithmetic (FMA, MUFU) with a conditioning guard that
+                                          sends near-singular evals (VRL closer than 0.2 to the camera part, or
+                                          asinh argument < -8) through the exact path; parity <= 1e-4 per pixel;
+                                       2: fast arithmetic without the guard (diagnostic: perf ceiling) */
+    int32_t  reserved[2];           /* 0.  (development: override guard thresholds, [0] = h in 1e-3 units, [1] = z) */
 } vrlb_options;
 
 /* ---- VRL set ----------------------------------------------------------- */

@@ -8,6 +8,7 @@
 #include "bvh_build.h"
 
 #include <algorithm>
+#include <cstring>
 #include <cmath>
 #include <limits>
 
@@ -109,6 +110,109 @@ void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vecto
         for (int k = 0; k < 3; ++k) { t.p0[k] = p[k]; t.e1[k] = p[3 + k] - p[k]; t.e2[k] = p[6 + k] - p[k]; }
         t.prim = prim; t.flags = flags ? flags[prim] : 0u; t.pad = 0;
         tris[i] = t;
+    }
+}
+
+void build_wide_nodes(const std::vector<DNode> &nodes, std::vector<DWNode> &wnodes) {
+    wnodes.clear();
+    if (nodes.empty() || nodes[0].b < 0) return;
+    std::vector<int32_t> windex(nodes.size(), -1);
+    int32_t n_inner = 0;
+    for (size_t i = 0; i < nodes.size(); ++i) if (nodes[i].b >= 0) windex[i] = n_inner++;   // root (node 0) -> wide node 0
+    wnodes.resize((size_t) n_inner);
+    auto ref = [&](int32_t child) -> uint32_t {
+        const DNode &c = nodes[(size_t) child];
+        if (c.b >= 0) return (uint32_t) windex[(size_t) child];
+        return 0x80000000u | ((uint32_t) c.a << 12) | ((uint32_t) (-c.b) << 7);      // leaf: first tri, count (<= 16)
+    };
+    for (size_t i = 0; i < nodes.size(); ++i) {
+        if (nodes[i].b < 0) continue;
+        DWNode w{};
+        const DNode &l = nodes[(size_t) nodes[i].a], &r = nodes[(size_t) nodes[i].b];
+        for (int k = 0; k < 3; ++k) { w.lo0[k] = l.lo[k]; w.hi0[k] = l.hi[k]; w.lo1[k] = r.lo[k]; w.hi1[k] = r.hi[k]; }
+        w.c0 = ref(nodes[i].a); w.c1 = ref(nodes[i].b);
+        wnodes[(size_t) windex[i]] = w;
+    }
+}
+
+// ---- shadow structure: main BVH + "shell" components -------------------------------------------------------
+// A connected component whose every triangle lies in a face plane of the component's own AABB (a fog container
+// box, the walls of a room) cannot be hit by a segment whose two end points are strictly inside that AABB, so
+// such components get their own small BVH which the shadow query enters only when an end point is within
+// `margin` of (or outside) the box.  Everything else goes into the main BVH, whose SAH is then no longer
+// dominated by scene-sized triangles.  Exactness: skipped triangles are at least `margin` away from the segment.
+void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, ShadowAccel &out) {
+    out = ShadowAccel();
+    if (n == 0) return;
+    // union-find over triangles sharing a vertex position (exact fp32 equality)
+    std::vector<uint32_t> parent(n);
+    for (uint32_t i = 0; i < n; ++i) parent[i] = i;
+    auto find = [&](uint32_t x) { while (parent[x] != x) { parent[x] = parent[parent[x]]; x = parent[x]; } return x; };
+    struct VKey { uint32_t x, y, z; uint32_t tri; };
+    std::vector<VKey> keys; keys.reserve((size_t) n * 3);
+    auto bits = [](float f) { if (f == 0.f) f = 0.f; uint32_t u; std::memcpy(&u, &f, 4); return u; };
+    for (uint32_t i = 0; i < n; ++i)
+        for (int v = 0; v < 3; ++v) {
+            const float *p = verts + (size_t) i * 9 + v * 3;
+            keys.push_back({ bits(p[0]), bits(p[1]), bits(p[2]), i });
+        }
+    std::sort(keys.begin(), keys.end(), [](const VKey &a, const VKey &b) {
+        if (a.x != b.x) return a.x < b.x; if (a.y != b.y) return a.y < b.y; if (a.z != b.z) return a.z < b.z; return a.tri < b.tri; });
+    for (size_t i = 1; i < keys.size(); ++i)
+        if (keys[i].x == keys[i - 1].x && keys[i].y == keys[i - 1].y && keys[i].z == keys[i - 1].z) {
+            uint32_t a = find(keys[i].tri), b = find(keys[i - 1].tri);
+            if (a != b) parent[std::max(a, b)] = std::min(a, b);
+        }
+    // component boxes
+    std::vector<Box> cbox(n);
+    for (uint32_t i = 0; i < n; ++i) { uint32_t r = find(i); const float *p = verts + (size_t) i * 9; cbox[r].grow(p); cbox[r].grow(p + 3); cbox[r].grow(p + 6); }
+    std::vector<char> is_shell(n, 0);
+    for (uint32_t i = 0; i < n; ++i) if (find(i) == i) is_shell[i] = 1;
+    for (uint32_t i = 0; i < n; ++i) {
+        uint32_t r = find(i); const Box &b = cbox[r]; const float *p = verts + (size_t) i * 9;
+        bool on_face = false;
+        for (int k = 0; k < 3 && !on_face; ++k)
+            on_face = (p[k] == b.lo[k] && p[3 + k] == b.lo[k] && p[6 + k] == b.lo[k]) || (p[k] == b.hi[k] && p[3 + k] == b.hi[k] && p[6 + k] == b.hi[k]);
+        if (!on_face) is_shell[r] = 0;
+    }
+    std::vector<uint32_t> shell_roots;
+    for (uint32_t i = 0; i < n; ++i) if (find(i) == i && is_shell[i] && shell_roots.size() < VRLB_MAX_SHELLS) shell_roots.push_back(i);
+    auto shell_of = [&](uint32_t tri) -> int { uint32_t r = find(tri); for (size_t s = 0; s < shell_roots.size(); ++s) if (shell_roots[s] == r) return (int) s; return -1; };
+    // gather subsets
+    std::vector<std::vector<uint32_t>> subsets(1 + shell_roots.size());
+    for (uint32_t i = 0; i < n; ++i) subsets[(size_t) (1 + shell_of(i))].push_back(i);
+    float ext = 0.f;
+    for (uint32_t i = 0; i < n * 9; ++i) ext = std::max(ext, std::fabs(verts[i]));
+    const float margin = 1e-3f * ext + 1e-6f;
+    for (size_t s = 0; s < subsets.size(); ++s) {
+        const std::vector<uint32_t> &sub = subsets[s];
+        uint32_t root_ref = 0x80000000u;          // empty leaf
+        if (!sub.empty()) {
+            std::vector<float> v((size_t) sub.size() * 9); std::vector<uint32_t> f(sub.size());
+            for (size_t i = 0; i < sub.size(); ++i) { std::memcpy(&v[i * 9], verts + (size_t) sub[i] * 9, 36); f[i] = flags ? flags[sub[i]] : 0u; }
+            std::vector<DNode> nodes; std::vector<DTri> tris; std::vector<DWNode> w;
+            build_bvh(v.data(), f.data(), (uint32_t) sub.size(), nodes, tris);
+            build_wide_nodes(nodes, w);
+            const uint32_t tri0 = (uint32_t) out.tris.size(), node0 = (uint32_t) out.wnodes.size();
+            for (DTri &t : tris) { t.prim = sub[t.prim]; out.tris.push_back(t); }
+            auto fix = [&](uint32_t ref) -> uint32_t {
+                if (ref & 0x80000000u) return 0x80000000u | ((((ref & 0x7fffffffu) >> 12) + tri0) << 12) | (ref & 0xf80u);
+                return ref + node0;
+            };
+            for (DWNode &wn : w) { wn.c0 = fix(wn.c0); wn.c1 = fix(wn.c1); out.wnodes.push_back(wn); }
+            root_ref = w.empty() ? (0x80000000u | (tri0 << 12) | ((uint32_t) tris.size() << 7)) : node0;
+        }
+        if (s == 0) {
+            out.main_root = root_ref; out.has_main = !sub.empty();
+            Box mb; for (uint32_t t : sub) { const float *p = verts + (size_t) t * 9; mb.grow(p); mb.grow(p + 3); mb.grow(p + 6); }
+            if (!sub.empty()) for (int k = 0; k < 3; ++k) { out.main_lo[k] = mb.lo[k] - margin; out.main_hi[k] = mb.hi[k] + margin; }
+        }
+        else {
+            DShell sh{}; const Box &b = cbox[shell_roots[s - 1]];
+            for (int k = 0; k < 3; ++k) { sh.lo[k] = b.lo[k] + margin; sh.hi[k] = b.hi[k] - margin; }
+            sh.root = root_ref;
+            out.shells.push_back(sh);
+        }
     }
 }
 

@@ -9,4 +9,17 @@ namespace vrlb {
 // verts: n*9 floats (p0 p1 p2 per triangle), flags: n surface words (may be null).
 // Produces the flattened binary BVH (root = node 0) and the triangles in leaf order.
 void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vector<DNode> &nodes, std::vector<DTri> &tris);
+// Re-packs the binary BVH for the shadow traversal: one DWNode per inner node holding both children's boxes.
+// Empty when the root is a leaf.
+void build_wide_nodes(const std::vector<DNode> &nodes, std::vector<DWNode> &wnodes);
+// Shadow (any-hit) structure: main BVH over ordinary geometry + per-shell BVHs (see bvh_build.cpp).
+struct ShadowAccel {
+    std::vector<DTri>   tris;      // own triangle order (prim = original index)
+    std::vector<DWNode> wnodes;
+    std::vector<DShell> shells;
+    uint32_t main_root = 0x80000000u;
+    float    main_lo[3] = { 0, 0, 0 }, main_hi[3] = { 0, 0, 0 };
+    bool     has_main = false;
+};
+void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, ShadowAccel &out);
 }  // namespace vrlb

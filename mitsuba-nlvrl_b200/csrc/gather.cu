@@ -13,149 +13,9 @@
 // PCG32 addressing: eval (sample s, global VRL j) of a segment uses the draws at offset
 // ((s*total + j) * dpe) from the segment's rng_state (dpe = 2, or 3 with distance roulette); a thread
 // jumps to its shard's first draw with PCG32::advance and then steps the LCG.
-#include "vrlb_device.cuh"
-#include "vrlb_kernels.h"
+#include "gather_exact.cuh"
 
 namespace vrlb {
-
-constexpr int GATHER_THREADS = 256;
-constexpr int TILE           = 256;   // VRL records per shared-memory tile (12 KB)
-
-// ---- mbarrier / TMA bulk-copy PTX (sm_90+; SASS: UBLKCP + SYNCS) -----------------------------------
-__device__ inline uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
-__device__ inline void mbar_init(uint64_t *bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ inline void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ inline void mbar_wait(uint64_t *bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ inline void tma_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-
-// ---- VRL::findClosetPoint, vrl_struct.h:163-228 -----------------------------------------------------
-__device__ inline void find_closest_point(V3 vo, V3 vd, float vlen, V3 ro, V3 rd, float rmaxt, float &tCam, float &tVRL) {
-    V3 u = vd * vlen;
-    V3 v = rd * rmaxt;
-    V3 w = vo - ro;
-    float a = dot(u, u), b = dot(u, v), c = dot(v, v), d = dot(u, w), e = dot(v, w);
-    float D = a * c - b * b;
-    float sN, sD = D, tN, tD = D;
-    if (D < 0.0001f) {
-        sN = 0.0f; sD = 1.0f; tN = e; tD = c;
-    } else {
-        sN = (b * e - c * d);
-        tN = (a * e - b * d);
-        if (sN < 0.0f) { sN = 0.0f; tN = e; tD = c; }
-        else if (sN > sD) { sN = sD; tN = e + b; tD = c; }
-    }
-    if (tN < 0.0f) {
-        tN = 0.0f;
-        if (-d < 0.0f) sN = 0.0f;
-        else if (-d > a) sN = sD;
-        else { sN = -d; sD = a; }
-    } else if (tN > tD) {
-        tN = tD;
-        if ((-d + b) < 0.0f) sN = 0;
-        else if ((-d + b) > a) sN = sD;
-        else { sN = (-d + b); sD = a; }
-    }
-    float sc = (fabsf(sN) < 0.0001f ? 0.0f : sN / sD);
-    float tc = (fabsf(tN) < 0.0001f ? 0.0f : tN / tD);
-    tCam = tc * rmaxt;
-    tVRL = sc * vlen;
-}
-
-struct SegRegs { V3 o, d; float maxt; };
-
-// ---- VRL::getContrib (vrl_struct.h:584-662) with samplingVRL (239-360) inlined.  Returns the scalar
-//      factor that multiplies flux * sigma_s(cam) * sigma_s(vrl); 0 when the reference returns 0. ----
-template <bool UNIFORM, bool VIS>
-__device__ inline float eval_contrib(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
-                                     float max_density, int phase, float g, float u1, float u2) {
-    V3 pCam, pVRL; float tCam, tVRL, invPDF;
-    if (UNIFORM) {
-        // VRL::sampleMC, vrl_struct.h:239-243 (single-part NLRay::at, :44-56)
-        tCam = u1 * ray.maxt;
-        tVRL = u2 * vlen;
-        pCam = ray.o + ray.d * tCam;
-        pVRL = vo + vd * tVRL;
-        invPDF = vlen * ray.maxt;
-    } else {
-        float cpCam, cpVRL;
-        find_closest_point(vo, vd, vlen, ray.o, ray.d, ray.maxt, cpCam, cpVRL);
-        V3 vh = vo + vd * cpVRL;
-        V3 uh = ray.o + ray.d * cpCam;
-        float h = squared_norm(uh - vh);
-        if (h == 0.0f) return 0.f;                               // vrl_struct.h:264
-        h = safe_sqrt(h);
-        float v0Hat = -cpVRL;
-        float v1Hat = vlen + v0Hat;
-        float sinTheta = squared_norm(cross(vd, ray.d));
-        if (sinTheta == 0) return 0.f;                           // vrl_struct.h:275
-        sinTheta = safe_sqrt(sinTheta);
-        // inverseCDF_A, vrl_struct.h:293-310 (Novak et al. 2012, eq. 10-13)
-        float z0 = (v0Hat / h) * sinTheta, z1 = (v1Hat / h) * sinTheta;
-        float a0 = logf(z0 + sqrtf(z0 * z0 + 1));
-        float a1 = logf(z1 + sqrtf(z1 * z1 + 1));
-        float vHat = (h * sinhf(lerpf(a0, a1, u1))) / sinTheta;
-        float invPDF_A = (a1 - a0) * sqrtf(h * h + vHat * vHat * sinTheta * sinTheta);
-        invPDF_A /= sinTheta;
-        tVRL = (vHat + cpVRL);
-        pVRL = vo + vd * tVRL;
-        // equi-angular sampling of the camera part, vrl_struct.h:318-336 (Kulla & Fajardo 2012)
-        float uHat  = dot(ray.d, (pVRL - ray.o));
-        float u0Hat = -uHat;
-        float u1Hat = ray.maxt + u0Hat;
-        float hPoint = norm(ray.o + ray.d * uHat - pVRL);
-        float thetaA = atanf(u0Hat / hPoint);
-        float thetaB = atanf(u1Hat / hPoint);
-        float uS     = hPoint * tanf(lerpf(thetaA, thetaB, u2));
-        float invPDF_B = (thetaB - thetaA) * (hPoint * hPoint + uS * uS) / hPoint;
-        tCam = (uS - u0Hat);
-        pCam = ray.o + ray.d * tCam;
-        tCam = fminf(fmaxf(tCam, 0.0f), ray.maxt);               // vrl_struct.h:340-341
-        tVRL = fminf(fmaxf(tVRL, 0.0f), vlen);
-        invPDF = invPDF_A * invPDF_B;
-    }
-    V3 dir = pVRL - pCam;
-    float lengthPtoP = norm(dir);
-    if (lengthPtoP == 0) return 0.f;                             // vrl_struct.h:589
-    if (isnan(invPDF)) return 0.f;                               // vrl_struct.h:594
-    dir = dir / lengthPtoP;
-    float rayPF = phase_eval(phase, g, -ray.d, dir);             // wi = -part.d (quirk 1)
-    if (rayPF == 0) return 0.f;
-    float vrlPF = phase_eval(phase, g, -vd, -dir);
-    if (vrlPF == 0) return 0.f;
-    // VRL::evalTransmittance pCam -> pVRL, vrl_struct.h:509-572
-    float vrlToRayTrans;
-    {
-        V3 dd = pVRL - pCam;
-        float remaining = norm(dd);
-        dd = normalize(dd);
-        if (VIS && remaining > 0 && any_hit(scene, pCam, dd, 0.f, remaining)) return 0.f;
-        vrlToRayTrans = remaining > 0 ? homo_transmittance(max_density, remaining) : 1.0f;
-    }
-    if (vrlToRayTrans == 0.0f) return 0.f;
-    float rayTrans = homo_transmittance(max_density, tCam);
-    if (rayTrans == 0.0f) return 0.f;
-    float vrlTrans = homo_transmittance(max_density, tVRL);
-    if (vrlTrans == 0.0f) return 0.f;
-    float fallOff = 1.0f / (lengthPtoP * lengthPtoP);
-    return fallOff * vrlPF * rayPF * vrlTrans * rayTrans * vrlToRayTrans * invPDF;
-}
 
 // compensated (Kahan) fp32 accumulation: the per-pixel sum over up to 1e6 VRLs stays at fp64-sum
 // quality without fp64 issue slots ("FP32 accumulation order")

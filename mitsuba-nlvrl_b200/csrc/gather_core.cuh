@@ -1,0 +1,36 @@
+// gather_core.cuh -- pieces shared by the exact-arithmetic gather (gather.cu) and the fast-math gather
+// (gather_fast.cu): mbarrier / TMA bulk-copy PTX wrappers and the VRL tile geometry.
+#pragma once
+#include "vrlb_device.cuh"
+#include "vrlb_kernels.h"
+
+namespace vrlb {
+
+constexpr int GATHER_THREADS = 256;
+constexpr int TILE           = 256;   // VRL records per shared-memory tile (12 KB)
+
+// ---- mbarrier / TMA bulk-copy PTX (sm_90+; SASS: UBLKCP + SYNCS) -----------------------------------
+__device__ inline uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ inline void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ inline void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ inline void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ inline void tma_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+}  // namespace vrlb

@@ -1,0 +1,738 @@
+// gather_fast.cu -- the camera-segment x VRL gather, production arithmetic (vrlb_options::math_mode = 1).
+//
+// Same algorithm, stream addressing and tile pipeline as gather.cu (which restates the reference's IEEE
+// operation order for bit-level comparison with the oracle); here every well-conditioned step uses the
+// issue-cheapest sm_100a form: FMA contraction, MUFU.RCP / RSQ / LG2 / EX2 instead of IEEE division, sqrt,
+// logf, sinhf, expf, and two short polynomials for atan / tan (tools/fit_polys.py, <= 1.5e-7 relative).
+// What stays exactly rounded, because the reference's own formula is ill-conditioned there and a
+// different rounding would produce a different (equally noisy) value:
+//   * asinh(z) = log(z + sqrt(z*z + 1)) for z < 0 (vrl_struct.h:297-301): z*z, +1, sqrt and the sum are
+//     single IEEE operations, only the final log is MUFU.LG2;
+//   * the Moeller-Trumbore shadow test (vrlb_device.cuh::intersect_tri).
+// Parity: tests/test_gather_gpu.py checks this kernel against the oracle at the north-star tolerance
+// (per-pixel relative error <= 1e-4); per-eval relative error is ~1e-6.
+//
+// Per-eval cost drops from ~710 to ~260 warp instructions (profiles/), which is what moves the FP32-issue-bound
+// kernel; the VRL records are pre-multiplied (flux * sigma_s^2 * m_scale, extinction in the pad lane) by
+// prep_fast_vrls so the inner loop reads no medium table when every medium is isotropic.
+#include "gather_exact.cuh"
+
+namespace vrlb {
+
+__device__ __forceinline__ float f_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float f_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float f_rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float f_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float f_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+constexpr float kLn2 = 0.693147180559945309f, kLog2e = 1.44269504088896341f, kHalfPi = 1.57079632679489662f;
+
+// atan(x): |x| <= 1 -> x P(x^2); else +-pi/2 - atan(1/x)
+__device__ __forceinline__ float f_atan(float x) {
+    float ax = fabsf(x);
+    bool big = ax > 1.0f;
+    float t = big ? f_rcp(ax) : ax;
+    float s = t * t;
+    float p = 0.002849772f;
+    p = fmaf(p, s, -0.01606816f); p = fmaf(p, s, 0.042690758f); p = fmaf(p, s, -0.07504231f);
+    p = fmaf(p, s, 0.10640904f);  p = fmaf(p, s, -0.14203636f); p = fmaf(p, s, 0.19992618f);
+    p = fmaf(p, s, -0.33333072f);
+    float r = fmaf(p * s, t, t);
+    r = big ? kHalfPi - r : r;
+    return copysignf(r, x);
+}
+// tan(x) for |x| < pi/2: |x| <= pi/4 -> x Q(x^2); else 1 / tan(pi/2 - |x|)
+__device__ __forceinline__ float f_tan(float x) {
+    float ax = fabsf(x);
+    bool big = ax > 0.78539816339744831f;
+    float t = big ? kHalfPi - ax : ax;
+    float s = t * t;
+    float q = 0.009499237f;
+    q = fmaf(q, s, 0.0028941673f); q = fmaf(q, s, 0.02460186f); q = fmaf(q, s, 0.05334885f);
+    q = fmaf(q, s, 0.13339895f);   q = fmaf(q, s, 0.33333075f);
+    float r = fmaf(q * s, t, t);
+    r = big ? f_rcp(r) : r;
+    return copysignf(r, x);
+}
+
+// This translation unit is compiled with -fmad=false (the exact slow path lives here too), so the fast
+// path spells its FMAs out.
+__device__ __forceinline__ float fdot(V3 a, V3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ V3 fmad3(V3 o, V3 d, float t) { return V3(fmaf(d.x, t, o.x), fmaf(d.y, t, o.y), fmaf(d.z, t, o.z)); }
+__device__ __forceinline__ V3 fcross(V3 a, V3 b) {
+    return V3(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
+}
+
+struct FastSeg {
+    V3 o, d;          // part origin / direction
+    float maxt;
+    V3 v;             // d * maxt
+    float c;          // dot(v, v)
+};
+
+// VRL::findClosetPoint, vrl_struct.h:163-228 (v, c hoisted per camera segment)
+__device__ __forceinline__ void closest_fast(V3 vo, V3 vd, float vlen, const FastSeg &r, float &tCam, float &tVRL) {
+    V3 u = vd * vlen;
+    V3 w = vo - r.o;
+    float a = fdot(u, u), b = fdot(u, r.v), c = r.c, d = fdot(u, w), e = fdot(r.v, w);
+    float D = fmaf(a, c, -(b * b));
+    float sN, sD = D, tN, tD = D;
+    if (D < 0.0001f) {
+        sN = 0.0f; sD = 1.0f; tN = e; tD = c;
+    } else {
+        sN = fmaf(b, e, -(c * d));
+        tN = fmaf(a, e, -(b * d));
+        if (sN < 0.0f) { sN = 0.0f; tN = e; tD = c; }
+        else if (sN > sD) { sN = sD; tN = e + b; tD = c; }
+    }
+    if (tN < 0.0f) {
+        tN = 0.0f;
+        if (-d < 0.0f) sN = 0.0f;
+        else if (-d > a) sN = sD;
+        else { sN = -d; sD = a; }
+    } else if (tN > tD) {
+        tN = tD;
+        if ((-d + b) < 0.0f) sN = 0;
+        else if ((-d + b) > a) sN = sD;
+        else { sN = (-d + b); sD = a; }
+    }
+    float sc = (fabsf(sN) < 0.0001f ? 0.0f : sN * f_rcp(sD));
+    float tc = (fabsf(tN) < 0.0001f ? 0.0f : tN * f_rcp(tD));
+    tCam = tc * r.maxt;
+    tVRL = sc * vlen;
+}
+
+__device__ __forceinline__ float hg_fast(float g, float cos_theta) {
+    float temp = fmaf(2.0f * g, cos_theta, fmaf(g, g, 1.0f));
+    float rs = f_rsqrt(temp);
+    return kInvFourPi * (1.0f - g * g) * (rs * rs * rs);
+}
+
+// Conditioning guard.  The estimator is ill-conditioned when the VRL passes close to the camera part: the
+// reference's asinh(z) = log(z + sqrt(z*z + 1)) cancels for z << 0 (relative noise 2 z^2 eps, an exact 0 -> NaN ->
+// rejected eval beyond |z| ~ 4096), and the equi-angular pdf ~ 1/hPoint amplifies any position error by
+// 1/h.  Those evals carry the largest weights of their pixel, so they are evaluated by the exactly-rounded path
+// (gather_exact.cuh), which reproduces the reference's rounding; everything else takes the fast path, whose
+// per-eval relative error (~1e-6) is then not amplified.  Thresholds come from GatherParams.
+struct Guard { float h2min, zmax; };
+
+// VRL::getContrib (vrl_struct.h:584-662) with samplingVRL (239-360) inlined; returns the scalar that multiplies
+// flux * sigma_s(cam) * sigma_s(vrl) * m_scale BEFORE the shadow test (the segment to trace is returned in so / sd /
+// sdist when VIS), 0 where the reference returns 0.  `slow` is set (and nothing
+// else computed) when the guard wants the exact path.
+template <bool UNIFORM, bool VIS, bool ISO, bool GUARD>
+__device__ __forceinline__ float contrib_fast(const DScene &scene, const FastSeg &ray, V3 vo, V3 vd, float vlen,
+                                              float max_density, float g, float u1, float u2, Guard guard, bool &slow,
+                                              V3 &so, V3 &sd, float &sdist) {
+    V3 pCam, pVRL; float tCam, tVRL, invPDF;
+    slow = false;
+    if (UNIFORM) {
+        tCam = u1 * ray.maxt;                                    // VRL::sampleMC, vrl_struct.h:239-243
+        tVRL = u2 * vlen;
+        pCam = fmad3(ray.o, ray.d, tCam);
+        pVRL = fmad3(vo, vd, tVRL);
+        invPDF = vlen * ray.maxt;
+    } else {
+        float cpCam, cpVRL;
+        closest_fast(vo, vd, vlen, ray, cpCam, cpVRL);
+        V3 vh = fmad3(vo, vd, cpVRL);
+        V3 uh = fmad3(ray.o, ray.d, cpCam);
+        V3 dh = uh - vh;
+        float h2 = fdot(dh, dh);
+        V3 cr = fcross(vd, ray.d);
+        float st2 = fdot(cr, cr);
+        float rh = f_rsqrt(h2);
+        float rst = f_rsqrt(st2);
+        float k  = st2 * rst * rh;                               // sin(theta) / h
+        float z0 = -cpVRL * k, z1 = (vlen - cpVRL) * k;
+        if (GUARD && !(h2 >= guard.h2min && z0 >= -guard.zmax && st2 > 1e-6f)) { slow = true; return 0.f; }
+        if (h2 == 0.0f) return 0.f;                              // vrl_struct.h:264
+        if (st2 == 0.f) return 0.f;                              // vrl_struct.h:275
+        float h  = h2 * rh;
+        // inverseCDF_A, vrl_struct.h:293-310; asinh(z) = log(z + sqrt(z^2 + 1)), cancellation-free for z < 0
+        float r0 = f_sqrt(fmaf(z0, z0, 1.0f)), r1 = f_sqrt(fmaf(z1, z1, 1.0f));
+        float e0 = z0 < 0.f ? f_rcp(r0 - z0) : z0 + r0;
+        float e1 = z1 < 0.f ? f_rcp(r1 - z1) : z1 + r1;
+        float l0 = f_lg2(e0), l1 = f_lg2(e1);                    // a = l * ln2
+        float E  = f_ex2(fmaf(l1 - l0, u1, l0));                 // exp(lerp(a0, a1, u1))
+        float sh = 0.5f * (E - f_rcp(E));                        // sinh
+        float vHat = h * sh * rst;
+        float invPDF_A = (l1 - l0) * kLn2 * f_sqrt(fmaf(vHat * vHat, st2, h2)) * rst;
+        tVRL = vHat + cpVRL;
+        pVRL = fmad3(vo, vd, tVRL);
+        // equi-angular sampling of the camera part, vrl_struct.h:318-336
+        float uHat  = fdot(ray.d, pVRL - ray.o);
+        float u0Hat = -uHat;
+        float u1Hat = ray.maxt + u0Hat;
+        V3 perp = fmad3(ray.o, ray.d, uHat) - pVRL;
+        float hp2 = fdot(perp, perp);
+        float rhp = f_rsqrt(hp2);
+        float hPoint = hp2 * rhp;
+        float thetaA = f_atan(u0Hat * rhp);
+        float thetaB = f_atan(u1Hat * rhp);
+        float uS     = hPoint * f_tan(fmaf(thetaB - thetaA, u2, thetaA));
+        float invPDF_B = (thetaB - thetaA) * fmaf(uS, uS, hp2) * rhp;
+        tCam = uS - u0Hat;
+        pCam = fmad3(ray.o, ray.d, tCam);
+        tCam = fminf(fmaxf(tCam, 0.0f), ray.maxt);               // vrl_struct.h:340-341
+        tVRL = fminf(fmaxf(tVRL, 0.0f), vlen);
+        invPDF = invPDF_A * invPDF_B;
+    }
+    V3 dir = pVRL - pCam;
+    float d2 = fdot(dir, dir);
+    if (d2 == 0.f) return 0.f;                                   // vrl_struct.h:589
+    if (isnan(invPDF)) return 0.f;                               // vrl_struct.h:594
+    float rd = f_rsqrt(d2);
+    float dist = d2 * rd;
+    float pf = kInvFourPi * kInvFourPi;
+    if (!ISO) {
+        V3 dn = dir * rd;
+        float rayPF = hg_fast(g, -fdot(dn, ray.d));              // wi = -part.d (quirk 1), wo = dir
+        float vrlPF = hg_fast(g, fdot(dn, vd));                  // wi = -vrl.dir, wo = -dir
+        pf = rayPF * vrlPF;
+        if (pf == 0.f) return 0.f;
+    }
+    if (VIS) { so = pCam; sd = dir * rd; sdist = dist; }          // shadow segment, traced by the caller (vrl_struct.h:509-572)
+    // three homogeneous transmittances, medium.h:112-117: exp(-sigma (dist + tCam + tVRL)) in one MUFU.EX2
+    float tr = f_ex2(-(max_density * kLog2e) * (dist + tCam + tVRL));
+    if (tr == 0.f) return 0.f;
+    return (rd * rd) * pf * tr * invPDF;
+}
+
+// ---- kernel: one thread per camera segment, VRL tiles through shared memory by TMA (as gather.cu) ----
+template <bool UNIFORM, bool RR, bool VIS, bool ISO, bool GUARD>
+__global__ void __launch_bounds__(GATHER_THREADS)
+gather_fast_kernel(GatherParams p) {
+    __shared__ alignas(128) DVrl tile[2][TILE];
+    __shared__ alignas(8) uint64_t full_bar[2];
+
+    const uint32_t tid = threadIdx.x;
+    const uint64_t seg_i = (uint64_t) blockIdx.x * GATHER_THREADS + tid;
+    const bool live = seg_i < p.n_segs;
+
+    FastSeg ray; uint64_t rng0 = 0; uint32_t pixel = 0; float w[3] = { 0.f, 0.f, 0.f };
+    if (live) {
+        const float4 *sp = reinterpret_cast<const float4 *>(p.segs + seg_i);
+        float4 r0 = __ldg(sp), r1 = __ldg(sp + 1), r2 = __ldg(sp + 2);
+        ulonglong2 r3 = __ldg(reinterpret_cast<const ulonglong2 *>(sp + 3));
+        ray.o = V3(r0.x, r0.y, r0.z); ray.maxt = r0.w;
+        ray.d = V3(r1.x, r1.y, r1.z); pixel = __float_as_uint(r1.w);
+        w[0] = r2.x; w[1] = r2.y; w[2] = r2.z;
+        rng0 = r3.x;
+    } else {
+        ray.o = V3(0.f); ray.d = V3(0.f, 0.f, 1.f); ray.maxt = 1.f;
+    }
+    ray.v = ray.d * ray.maxt;
+    ray.c = fdot(ray.v, ray.v);
+
+    const uint32_t n_tiles = (uint32_t) ((p.n_vrls + TILE - 1) / TILE);
+    const uint32_t total_tiles = n_tiles * p.q;
+    constexpr uint32_t DPE = RR ? 3u : 2u;
+
+    if (tid == 0) {
+        mbar_init(&full_bar[0], 1);
+        mbar_init(&full_bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](uint32_t it) {
+        uint32_t t = it % n_tiles, buf = it & 1u;
+        uint64_t first = (uint64_t) t * TILE;
+        uint32_t cnt = (uint32_t) min((uint64_t) TILE, p.n_vrls - first);
+        uint32_t bytes = cnt * (uint32_t) sizeof(DVrl);
+        mbar_expect_tx(&full_bar[buf], bytes);
+        tma_bulk_g2s(&tile[buf][0], p.vrls_fast + first, bytes, &full_bar[buf]);
+    };
+    if (tid == 0) {
+        if (total_tiles > 0) issue(0);
+        if (total_tiles > 1) issue(1);
+    }
+
+    const DMedium *media = p.scene.media;
+    const Guard guard = { p.guard_h * p.guard_h, p.guard_z };
+    float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
+    Pcg32 rng; rng.state = rng0;
+
+    for (uint32_t it = 0; it < total_tiles; ++it) {
+        const uint32_t t = it % n_tiles, s = it / n_tiles, buf = it & 1u;
+        if (t == 0) {
+            rng.state = rng0;
+            rng.advance(((uint64_t) s * p.total + p.first_index) * DPE);
+        }
+        mbar_wait(&full_bar[buf], (it >> 1) & 1u);
+        const uint32_t cnt = (uint32_t) min((uint64_t) TILE, p.n_vrls - (uint64_t) t * TILE);
+        float pr = 0.f, pg = 0.f, pb = 0.f;                               // plain fp32 inside a tile
+        if (live) {
+#pragma unroll 2
+            for (uint32_t j = 0; j < cnt; ++j) {
+                const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
+                float4 a = vp[0], b = vp[1], c = vp[2];
+                V3 vo(a.x, a.y, a.z), vd(b.x, b.y, b.z);
+                float vlen = a.w;
+                float rrWeight = 1.f; bool survive = true;
+                if (RR) {
+                    float cc, cv;                                         // EDistanceRoulette, vrl_map.h:171-190
+                    closest_fast(vo, vd, vlen, ray, cc, cv);
+                    float d2 = squared_norm((ray.o + ray.d * cc) - (vo + vd * cv));
+                    rrWeight = fminf(f_rcp(f_sqrt(d2) * p.scale_rr), 1.0f);
+                    survive  = rrWeight > rng.next_f32();
+                }
+                float u1 = rng.next_f32(), u2 = rng.next_f32();
+                if (!survive) continue;
+                float g = 0.f;
+                if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
+                bool slow;
+                V3 so, sd; float sdist;
+                float f = contrib_fast<UNIFORM, false, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, sdist);
+                if (GUARD && slow) {                                      // ill-conditioned eval: exactly-rounded path
+                    const DMedium &m = media[__float_as_uint(b.w)];
+                    SegRegs er; er.o = ray.o; er.d = ray.d; er.maxt = ray.maxt;
+                    f = eval_contrib<UNIFORM, false>(p.scene, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2);
+                }
+                if (RR) f = f * f_rcp(rrWeight);
+                float cr = c.x * f, cg = c.y * f, cb = c.z * f;           // flux pre-multiplied by sigma_s^2 * m_scale
+                if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { pr += cr; pg += cg; pb += cb; }   // vrl_map.h:162
+            }
+        }
+        float part[3] = { pr, pg, pb };
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float y = xsub(part[k], comp[k]);
+            float tt = xadd(sum[k], y);
+            comp[k] = xsub(xsub(tt, sum[k]), y);
+            sum[k] = tt;
+        }
+        __syncthreads();
+        if (tid == 0 && it + 2 < total_tiles) issue(it + 2);
+    }
+
+    if (live) {
+        float inv_q = 1.0f / (float) p.q;
+        float lr = sum[0] * inv_q, lg = sum[1] * inv_q, lb = sum[2] * inv_q;
+        if (p.seg_out) { p.seg_out[seg_i * 3 + 0] = lr; p.seg_out[seg_i * 3 + 1] = lg; p.seg_out[seg_i * 3 + 2] = lb; }
+        if (p.film_rgb) {
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 0, lr * w[0]);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 1, lg * w[1]);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 2, lb * w[2]);
+        }
+    }
+}
+
+// ---- shadow phase: in-warp ray queue with persistent lanes ------------------------------------------------
+// The shadow query is the divergent part of an eval (traversal length varies 2..80 node visits per ray).  Done
+// inline, every lane waits for the slowest ray of its warp at every VRL (measured: 9.8 of 32 lanes active,
+// profiles/r01b_gather_v2_fast.txt).  Instead a warp shades NB VRLs for its 32 camera segments in lock step
+// (phase A, fully converged), parks the NB*32 shadow segments in shared memory, and then traces them with
+// persistent lanes: whenever a lane finishes a ray it pulls the next one from the queue (phase B), so lanes stay
+// busy until the queue runs dry.  Phase C adds the surviving contributions in VRL order (lane-private slots,
+// deterministic).  B200 has no RT cores: this is plain SIMT traversal with warp-level ray compaction.
+constexpr int NB    = 4;                 // VRLs shaded per batch
+constexpr int VTILE = 64, NBUF = 4;     // VRL ring of the visibility kernel: NBUF tiles of VTILE records
+constexpr int QCAP  = NB * 32;           // shadow-segment slots per warp
+constexpr int QF    = 8;                 // floats per slot: o(3) d(3) dist f
+constexpr float Q_RESOLVED = -1.f, Q_REDO = -2.f;   // dist markers: no trace needed / re-evaluate exactly
+
+struct WarpQueue {
+    float    v[QF][QCAP];                // SoA: consecutive lanes -> consecutive banks
+    uint16_t roots[QCAP];                // per slot: which roots to visit (roots_mask)
+    uint16_t list[QCAP];                 // compacted slot indices that need tracing
+    uint32_t lq[128];                    // pending leaf entries: (first triangle << 12) | (count << 7) | slot
+};
+
+struct RayState {
+    V3 o, d, inv; float dist;
+    uint32_t cur;        // current wide node
+    int sp;              // stack pointer
+    uint32_t roots;      // bit 0: main BVH pending, bit 1 + i: shell i pending (decided in phase A)
+};
+
+__device__ __forceinline__ bool shell_inside(const DShell &sh, V3 o, V3 e) {
+    return o.x > sh.lo[0] && o.x < sh.hi[0] && o.y > sh.lo[1] && o.y < sh.hi[1] && o.z > sh.lo[2] && o.z < sh.hi[2] &&
+           e.x > sh.lo[0] && e.x < sh.hi[0] && e.y > sh.lo[1] && e.y < sh.hi[1] && e.z > sh.lo[2] && e.z < sh.hi[2];
+}
+
+// which roots the shadow segment has to visit: bit 0 = main BVH (its root box is hit), bit 1 + i = shell i (an end
+// point is not strictly inside it).  Evaluated in phase A with all lanes converged.
+__device__ __forceinline__ uint32_t roots_mask(const DScene &s, V3 o, V3 d, float dist) {
+    uint32_t m = 0;
+    V3 e = fmad3(o, d, dist);
+    if (s.main_root != 0x80000000u) {
+        V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
+        if (slab2(s.main_lo[0], s.main_lo[1], s.main_lo[2], s.main_hi[0], s.main_hi[1], s.main_hi[2], inv, o, 0.f, dist)) m |= 1u;
+    }
+    for (int i = 0; i < s.n_shells; ++i) if (!shell_inside(s.shells[i], o, e)) m |= 2u << i;
+    return m;
+}
+__device__ __forceinline__ bool next_root(const DScene &s, RayState &r, uint32_t &root) {
+    if (r.roots == 0) return false;
+    int i = __ffs((int) r.roots) - 1;
+    r.roots &= r.roots - 1;
+    root = i == 0 ? s.main_root : s.shells[i - 1].root;
+    return true;
+}
+
+// Phase B.  `cnt` listed slots; on return q.v[7][slot] = 0 for occluded segments and q.v[6][slot] = Q_REDO for
+// segments whose hit decision fell inside the graze margins.  Two kinds of work, each done by all 32 lanes at
+// once: node steps (one DWNode visit per active lane; lanes that finish a ray pull the next from q.list) and
+// leaf entries (slot, leaf) that the node steps append to q.lq -- as soon as 32 are pending every lane tests one
+// leaf's triangles.  Triangle tests at 1-3 active lanes were what held the inline traversal at 10 of 32 lanes.
+__device__ __forceinline__ void process_leaves(const DScene &s, WarpQueue &q, int first, int n, unsigned lane) {
+    if ((int) lane < n) {
+        uint32_t ent = q.lq[first + lane];
+        int slot = (int) (ent & 127u);
+        uint32_t cntl = (ent >> 7) & 31u, tri0 = (ent & 0x7fffffffu) >> 12;
+        V3 o(q.v[0][slot], q.v[1][slot], q.v[2][slot]), d(q.v[3][slot], q.v[4][slot], q.v[5][slot]);
+        float dist = q.v[6][slot];
+        if (dist > 0.f) {                                     // not already marked for exact re-evaluation
+            int res = 0;
+            for (uint32_t i = tri0; i < tri0 + cntl; ++i) {
+                int h = intersect_tri_graze(s.stris[i], o, d, 0.f, dist);
+                res |= h;
+                if (h == 1) break;
+            }
+            if (res & 1) q.v[7][slot] = 0.f;                  // certain hit: contribution is 0 (benign same-value races)
+            else if (res & 2) q.v[6][slot] = Q_REDO;
+        }
+    }
+}
+
+__device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int cnt) {
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    int head = 0, slot = 0, lqn = 0;
+    bool active = false;
+    RayState r;
+    uint32_t stack[24];
+    r.sp = 0; r.cur = 0; r.roots = 0; r.dist = 0.f;
+    while (true) {
+        // (1) leaf work: a full warp's worth pending
+        while (lqn >= 32) {
+            lqn -= 32;
+            __syncwarp();
+            process_leaves(s, q, lqn, 32, lane);
+            __syncwarp();
+        }
+        // (2) retire rays found occluded, refill idle lanes
+        if (active && q.v[7][slot] == 0.f) active = false;
+        unsigned idle = __ballot_sync(0xffffffffu, !active);
+        uint32_t leaf0 = 0, leaf1 = 0;                        // leaf entries produced by this step
+        if (idle) {
+            int avail = cnt - head;
+            if (avail > 0) {
+                int rank = __popc(idle & lt);
+                if (!active && rank < avail) {
+                    slot = q.list[head + rank];
+                    r.o = V3(q.v[0][slot], q.v[1][slot], q.v[2][slot]);
+                    r.d = V3(q.v[3][slot], q.v[4][slot], q.v[5][slot]);
+                    r.dist = q.v[6][slot];
+                    r.inv = V3(f_rcp(r.d.x), f_rcp(r.d.y), f_rcp(r.d.z));      // conservative slabs: approximate reciprocal is enough
+                    r.sp = 0; r.roots = q.roots[slot];
+                    uint32_t root;
+                    active = false;
+                    while (next_root(s, r, root)) {
+                        if (root & 0x80000000u) { stack[r.sp++] = root; continue; }      // single-leaf component
+                        r.cur = root; active = true; break;
+                    }
+                    if (!active && r.sp) { r.cur = stack[--r.sp]; active = true; }
+                }
+                head += min(__popc(idle), avail);
+            } else if (idle == 0xffffffffu) break;
+        }
+        // (3) one node step per active lane
+        if (active) {
+            if (r.cur & 0x80000000u) {                        // a leaf reference popped from the stack (root leaves)
+                leaf0 = r.cur;
+                bool more = true;
+                if (r.sp) r.cur = stack[--r.sp];
+                else {
+                    uint32_t root; more = false;
+                    while (next_root(s, r, root)) {
+                        if (root & 0x80000000u) { stack[r.sp++] = root; continue; }
+                        r.cur = root; more = true; break;
+                    }
+                    if (!more && r.sp) { r.cur = stack[--r.sp]; more = true; }
+                }
+                active = more;
+            } else {
+                const float4 *np = reinterpret_cast<const float4 *>(s.wnodes + r.cur);
+                float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2), e = __ldg(np + 3);
+                bool h0 = slab2(a.x, a.y, a.z, a.w, b.x, b.y, r.inv, r.o, 0.f, r.dist);
+                bool h1 = slab2(b.z, b.w, c.x, c.y, c.z, c.w, r.inv, r.o, 0.f, r.dist);
+                uint32_t c0 = __float_as_uint(e.x), c1 = __float_as_uint(e.y);
+                if (h0 && (c0 & 0x80000000u)) { leaf0 = c0; h0 = false; }
+                if (h1 && (c1 & 0x80000000u)) { leaf1 = c1; h1 = false; }
+                bool more = true;
+                if (h0) { if (h1) stack[r.sp++] = c1; r.cur = c0; }
+                else if (h1) r.cur = c1;
+                else if (r.sp) r.cur = stack[--r.sp];
+                else {
+                    uint32_t root; more = false;
+                    while (next_root(s, r, root)) {
+                        if (root & 0x80000000u) { stack[r.sp++] = root; continue; }
+                        r.cur = root; more = true; break;
+                    }
+                    if (!more && r.sp) { r.cur = stack[--r.sp]; more = true; }
+                }
+                active = more;
+            }
+        }
+        // append leaf entries: leaf reference | slot
+        {
+            unsigned m0 = __ballot_sync(0xffffffffu, leaf0 != 0);
+            if (leaf0) q.lq[lqn + __popc(m0 & lt)] = leaf0 | (uint32_t) slot;
+            lqn += __popc(m0);
+            unsigned m1 = __ballot_sync(0xffffffffu, leaf1 != 0);
+            if (leaf1) q.lq[lqn + __popc(m1 & lt)] = leaf1 | (uint32_t) slot;
+            lqn += __popc(m1);
+        }
+    }
+    __syncwarp();
+    if (lqn > 0) process_leaves(s, q, 0, lqn, lane);
+}
+
+// the exactly-rounded eval with its inline shadow traversal, out of line: it runs for < 1 % of the evals and would
+// otherwise be inlined twice into the kernel (instruction-cache misses were 2.7 stalled warps per issue)
+template <bool UNIFORM>
+__device__ __noinline__ float exact_eval_vis(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
+                                             float max_density, int phase, float g, float u1, float u2) {
+    return eval_contrib<UNIFORM, true>(scene, ray, vo, vd, vlen, max_density, phase, g, u1, u2);
+}
+
+// ---- kernel with visibility: phases A (shade NB VRLs) / B (trace the queue) / C (accumulate) per warp ----
+template <bool UNIFORM, bool RR, bool ISO, bool GUARD>
+__global__ void __launch_bounds__(GATHER_THREADS)
+gather_fast_vis_kernel(GatherParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    DVrl (*tile)[VTILE] = reinterpret_cast<DVrl (*)[VTILE]>(smem_raw);                              // [NBUF][VTILE]
+    WarpQueue *queues = reinterpret_cast<WarpQueue *>(smem_raw + NBUF * VTILE * sizeof(DVrl));      // [warps]
+    __shared__ alignas(8) uint64_t full_bar[NBUF];
+    __shared__ int done_cnt[NBUF];                 // warps that have finished the tile in each ring slot
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, lt = (1u << lane) - 1u;
+    WarpQueue &q = queues[tid >> 5];
+    const uint64_t seg_i = (uint64_t) blockIdx.x * GATHER_THREADS + tid;
+    const bool live = seg_i < p.n_segs;
+
+    FastSeg ray; uint64_t rng0 = 0; uint32_t pixel = 0; float w[3] = { 0.f, 0.f, 0.f };
+    if (live) {
+        const float4 *sp = reinterpret_cast<const float4 *>(p.segs + seg_i);
+        float4 r0 = __ldg(sp), r1 = __ldg(sp + 1), r2 = __ldg(sp + 2);
+        ulonglong2 r3 = __ldg(reinterpret_cast<const ulonglong2 *>(sp + 3));
+        ray.o = V3(r0.x, r0.y, r0.z); ray.maxt = r0.w;
+        ray.d = V3(r1.x, r1.y, r1.z); pixel = __float_as_uint(r1.w);
+        w[0] = r2.x; w[1] = r2.y; w[2] = r2.z;
+        rng0 = r3.x;
+    } else {
+        ray.o = V3(0.f); ray.d = V3(0.f, 0.f, 1.f); ray.maxt = 1.f;
+    }
+    ray.v = ray.d * ray.maxt;
+    ray.c = fdot(ray.v, ray.v);
+    SegRegs er; er.o = ray.o; er.d = ray.d; er.maxt = ray.maxt;
+
+    const uint32_t n_tiles = (uint32_t) ((p.n_vrls + VTILE - 1) / VTILE);
+    const uint32_t total_tiles = n_tiles * p.q;
+    constexpr uint32_t DPE = RR ? 3u : 2u;
+
+    if (tid == 0) {
+        for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); done_cnt[b] = 0; }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](uint32_t it) {
+        uint32_t t = it % n_tiles, buf = it % NBUF;
+        uint64_t first = (uint64_t) t * VTILE;
+        uint32_t cnt = (uint32_t) min((uint64_t) VTILE, p.n_vrls - first);
+        uint32_t bytes = cnt * (uint32_t) sizeof(DVrl);
+        mbar_expect_tx(&full_bar[buf], bytes);
+        tma_bulk_g2s(&tile[buf][0], p.vrls_fast + first, bytes, &full_bar[buf]);
+    };
+    if (tid == 0) {
+        for (uint32_t b = 0; b < NBUF && b < total_tiles; ++b) issue(b);
+    }
+
+    const DMedium *media = p.scene.media;
+    const Guard guard = { p.guard_h * p.guard_h, p.guard_z };
+    float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
+    Pcg32 rng; rng.state = rng0;
+
+    for (uint32_t it = 0; it < total_tiles; ++it) {
+        const uint32_t t = it % n_tiles, s = it / n_tiles, buf = it % NBUF;
+        if (t == 0) {
+            rng.state = rng0;
+            rng.advance(((uint64_t) s * p.total + p.first_index) * DPE);
+        }
+        mbar_wait(&full_bar[buf], (it / NBUF) & 1u);
+        const uint32_t cnt = (uint32_t) min((uint64_t) VTILE, p.n_vrls - (uint64_t) t * VTILE);
+        float pr = 0.f, pg = 0.f, pb = 0.f;
+        for (uint32_t jb = 0; jb < cnt; jb += NB) {
+            // ---- phase A: shade NB VRLs, park the shadow segments ----
+            int qn = 0;
+            const uint64_t rng_batch = rng.state;          // to regenerate (u1, u2) of a slot on the rare re-evaluation
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+                const uint32_t j = jb + i;
+                const int slot = i * 32 + (int) lane;
+                float f = 0.f, sdist = Q_RESOLVED, u1 = 0.f, u2 = 0.f; uint32_t roots = 0;
+                V3 so(0.f), sd(0.f);
+                if (j < cnt) {
+                    const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
+                    float4 a = vp[0], b = vp[1], c = vp[2];
+                    V3 vo(a.x, a.y, a.z), vd(b.x, b.y, b.z);
+                    float vlen = a.w;
+                    float rrWeight = 1.f; bool survive = live;
+                    if (RR) {
+                        float cc, cv;                                     // EDistanceRoulette, vrl_map.h:171-190
+                        closest_fast(vo, vd, vlen, ray, cc, cv);
+                        V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(vo, vd, cv);
+                        rrWeight = fminf(f_rcp(f_sqrt(fdot(dd, dd)) * p.scale_rr), 1.0f);
+                        survive  = survive && rrWeight > rng.next_f32();
+                    }
+                    u1 = rng.next_f32(); u2 = rng.next_f32();
+                    if (survive) {
+                        float g = 0.f;
+                        if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
+                        bool slow; float dist;
+                        f = contrib_fast<UNIFORM, true, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, dist);
+                        if (GUARD && slow) {                              // ill-conditioned eval: exact path, traced inline
+                            const DMedium &m = media[__float_as_uint(b.w)];
+                            f = exact_eval_vis<UNIFORM>(p.scene, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2);
+                        } else if (f != 0.f) { sdist = dist; roots = roots_mask(p.scene, so, sd, dist); if (roots == 0) sdist = Q_RESOLVED; }
+                        if (RR) f = f * f_rcp(rrWeight);
+                    }
+                }
+                q.v[0][slot] = so.x; q.v[1][slot] = so.y; q.v[2][slot] = so.z;
+                q.v[3][slot] = sd.x; q.v[4][slot] = sd.y; q.v[5][slot] = sd.z;
+                q.v[6][slot] = sdist; q.v[7][slot] = f; q.roots[slot] = (uint16_t) roots;
+                const bool need = sdist > 0.f;
+                const unsigned m = __ballot_sync(0xffffffffu, need);
+                if (need) q.list[qn + __popc(m & lt)] = (uint16_t) slot;
+                qn += __popc(m);
+            }
+            __syncwarp();
+            // ---- phase B: persistent-lane traversal of the queue ----
+            trace_queue(p.scene, q, qn);
+            __syncwarp();
+            // ---- phase C: accumulate in VRL order ----
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+                const uint32_t j = jb + i;
+                if (j >= cnt) break;
+                const int slot = i * 32 + (int) lane;
+                float f = q.v[7][slot];
+                const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
+                float4 c = vp[2];
+                if (q.v[6][slot] == Q_REDO) {                             // graze margin: exactly-rounded eval + exact trace
+                    float4 a = vp[0], b = vp[1];
+                    const DMedium &m = media[__float_as_uint(b.w)];
+                    Pcg32 rr; rr.state = rng_batch;
+                    for (int k = 0; k < i * (int) DPE + (RR ? 1 : 0); ++k) rr.next_u32();
+                    float ru1 = rr.next_f32(), ru2 = rr.next_f32();
+                    float fe = exact_eval_vis<UNIFORM>(p.scene, er, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, m.max_density, m.phase, m.g, ru1, ru2);
+                    if (RR) {
+                        float cc, cv;
+                        closest_fast(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, ray, cc, cv);
+                        V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), cv);
+                        fe = fe * f_rcp(fminf(f_rcp(f_sqrt(fdot(dd, dd)) * p.scale_rr), 1.0f));
+                    }
+                    f = fe;
+                }
+                float cr = c.x * f, cg = c.y * f, cb = c.z * f;           // flux pre-multiplied by sigma_s^2 * m_scale
+                if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { pr += cr; pg += cg; pb += cb; }   // vrl_map.h:162
+            }
+            __syncwarp();
+        }
+        float part[3] = { pr, pg, pb };
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float y = xsub(part[k], comp[k]);
+            float tt = xadd(sum[k], y);
+            comp[k] = xsub(xsub(tt, sum[k]), y);
+            sum[k] = tt;
+        }
+        // ring hand-over without a CTA barrier: the last warp to finish a slot refills it (warps drift up to NBUF - 1 tiles apart)
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();
+            int old = atomicAdd(&done_cnt[buf], 1);
+            if (old == GATHER_THREADS / 32 - 1) {
+                done_cnt[buf] = 0;
+                if (it + NBUF < total_tiles) issue(it + NBUF);
+            }
+        }
+    }
+
+    if (live) {
+        float inv_q = 1.0f / (float) p.q;
+        float lr = sum[0] * inv_q, lg = sum[1] * inv_q, lb = sum[2] * inv_q;
+        if (p.seg_out) { p.seg_out[seg_i * 3 + 0] = lr; p.seg_out[seg_i * 3 + 1] = lg; p.seg_out[seg_i * 3 + 2] = lb; }
+        if (p.film_rgb) {
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 0, lr * w[0]);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 1, lg * w[1]);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 2, lb * w[2]);
+        }
+    }
+}
+
+// ---- VRL records for the fast kernel: flux * sigma_s(medium)^2 * m_scale, extinction in the pad lane ----
+__global__ void prep_fast_vrls_kernel(const DVrl *in, uint64_t n, const DMedium *media, float scale, DVrl *out) {
+    uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    DVrl v = in[j];
+    const DMedium m = media[v.medium];
+    v.fr = v.fr * m.sigma_s[0] * m.sigma_s[0] * scale;      // vrl_struct.h:652-659, vrl_map.h:160
+    v.fg = v.fg * m.sigma_s[1] * m.sigma_s[1] * scale;
+    v.fb = v.fb * m.sigma_s[2] * m.sigma_s[2] * scale;
+    v.pad = m.max_density;
+    out[j] = v;
+}
+cudaError_t launch_prep_fast_vrls(const DVrl *in, uint64_t n, const DMedium *media, float scale, DVrl *out, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    prep_fast_vrls_kernel<<<(uint32_t) ((n + 255) / 256), 256, 0, stream>>>(in, n, media, scale, out);
+    return cudaGetLastError();
+}
+
+template <bool U, bool R, bool I, bool P>
+static cudaError_t launch_f(const GatherParams &p, cudaStream_t stream) {
+    uint32_t grid = (uint32_t) ((p.n_segs + GATHER_THREADS - 1) / GATHER_THREADS);
+    if (grid == 0 || p.n_vrls == 0) return cudaSuccess;
+    gather_fast_kernel<U, R, false, I, P><<<grid, GATHER_THREADS, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+template <bool U, bool R, bool I, bool P>
+static cudaError_t launch_fv(const GatherParams &p, cudaStream_t stream) {
+    uint32_t grid = (uint32_t) ((p.n_segs + GATHER_THREADS - 1) / GATHER_THREADS);
+    if (grid == 0 || p.n_vrls == 0) return cudaSuccess;
+    constexpr size_t smem = NBUF * VTILE * sizeof(DVrl) + (GATHER_THREADS / 32) * sizeof(WarpQueue);
+    static bool configured = false;       // per instantiation; the attribute is sticky for the process
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(gather_fast_vis_kernel<U, R, I, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    gather_fast_vis_kernel<U, R, I, P><<<grid, GATHER_THREADS, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+template <bool U, bool R, bool V>
+static cudaError_t launch_f2(const GatherParams &p, bool iso, bool guard, cudaStream_t stream) {
+    if (V) {
+        if (iso) return guard ? launch_fv<U, R, true, true>(p, stream) : launch_fv<U, R, true, false>(p, stream);
+        return guard ? launch_fv<U, R, false, true>(p, stream) : launch_fv<U, R, false, false>(p, stream);
+    }
+    if (iso) return guard ? launch_f<U, R, true, true>(p, stream) : launch_f<U, R, true, false>(p, stream);
+    return guard ? launch_f<U, R, false, true>(p, stream) : launch_f<U, R, false, false>(p, stream);
+}
+
+cudaError_t launch_gather_fast(const GatherParams &p, bool uniform, bool rr, bool vis, bool iso, bool guard, cudaStream_t stream) {
+    int key = (uniform ? 4 : 0) | (rr ? 2 : 0) | (vis ? 1 : 0);
+    switch (key) {
+        case 0: return launch_f2<false, false, false>(p, iso, guard, stream);
+        case 1: return launch_f2<false, false, true>(p, iso, guard, stream);
+        case 2: return launch_f2<false, true, false>(p, iso, guard, stream);
+        case 3: return launch_f2<false, true, true>(p, iso, guard, stream);
+        case 4: return launch_f2<true, false, false>(p, iso, guard, stream);
+        case 5: return launch_f2<true, false, true>(p, iso, guard, stream);
+        case 6: return launch_f2<true, true, false>(p, iso, guard, stream);
+        default: return launch_f2<true, true, true>(p, iso, guard, stream);
+    }
+}
+
+}  // namespace vrlb

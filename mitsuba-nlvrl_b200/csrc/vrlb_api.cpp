@@ -48,13 +48,14 @@ struct vrlb_context {
     std::atomic<int> cancel{ 0 };
 
     // scene
-    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DMedium> media; DevBuf<float> emitters;
+    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters;
     DScene scene{};
     bool have_scene = false;
     std::vector<vrlb_medium> host_media;
 
     // VRL set
-    DevBuf<DVrl> vrls; DevBuf<float> stage_soa; DevBuf<uint16_t> stage_med;
+    DevBuf<DVrl> vrls, vrls_fast; bool fast_dirty = true; bool all_iso = true;
+    DevBuf<float> stage_soa; DevBuf<uint16_t> stage_med;
     uint64_t n_vrls = 0, vrl_first = 0, vrl_total = 0; float vrl_scale = 1.f;
 
     // segments
@@ -169,8 +170,8 @@ void vrlb_destroy(vrlb_context *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->media.release(); ctx->emitters.release();
-    ctx->vrls.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
+    ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->wnodes.release(); ctx->stris.release(); ctx->media.release(); ctx->emitters.release();
+    ctx->vrls.release(); ctx->vrls_fast.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
     if (ctx->nccl_comm && g_nccl_destroy) g_nccl_destroy(ctx->nccl_comm);
     ctx->block_ids.release(); ctx->film_rgb.release(); ctx->film_aw.release(); ctx->film_xyzaw.release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
@@ -214,6 +215,7 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     cudaSetDevice(ctx->device);
     if (sc->n_tris && !sc->tri_verts) return fail(ctx, VRLB_ERR_INVALID, "tri_verts is NULL");
     if (sc->n_media == 0 || !sc->media) return fail(ctx, VRLB_ERR_INVALID, "a scene needs at least one medium");
+    if (sc->n_tris >= (1u << 19)) return fail(ctx, VRLB_ERR_INVALID, "at most 2^19 - 1 triangles on this path (shadow leaf-queue packing)");
     if (sc->n_media > 255 || sc->n_emitters > 255) return fail(ctx, VRLB_ERR_INVALID, "at most 255 media / emitters");
     for (uint32_t i = 0; i < sc->n_tris; ++i) {
         uint32_t f = sc->tri_flags ? sc->tri_flags[i] : 0u;
@@ -239,6 +241,8 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     }
     std::vector<DNode> nodes; std::vector<DTri> tris;
     build_bvh(sc->tri_verts, sc->tri_flags, sc->n_tris, nodes, tris);
+    ShadowAccel sa; build_shadow_accel(sc->tri_verts, sc->tri_flags, sc->n_tris, sa);
+    CU(ctx, ctx->wnodes.reserve(sa.wnodes.size())); CU(ctx, ctx->stris.reserve(sa.tris.size()));
     CU(ctx, ctx->tris.reserve(tris.size())); CU(ctx, ctx->nodes.reserve(nodes.size()));
     CU(ctx, ctx->verts.reserve((size_t) sc->n_tris * 9)); CU(ctx, ctx->media.reserve(dm.size()));
     CU(ctx, ctx->emitters.reserve((size_t) sc->n_emitters * 4));
@@ -246,16 +250,24 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     if (!tris.empty()) {
         CU(ctx, cudaMemcpy(ctx->tris.ptr, tris.data(), tris.size() * sizeof(DTri), cudaMemcpyHostToDevice));
         CU(ctx, cudaMemcpy(ctx->nodes.ptr, nodes.data(), nodes.size() * sizeof(DNode), cudaMemcpyHostToDevice));
+        if (!sa.wnodes.empty()) CU(ctx, cudaMemcpy(ctx->wnodes.ptr, sa.wnodes.data(), sa.wnodes.size() * sizeof(DWNode), cudaMemcpyHostToDevice));
+        CU(ctx, cudaMemcpy(ctx->stris.ptr, sa.tris.data(), sa.tris.size() * sizeof(DTri), cudaMemcpyHostToDevice));
         CU(ctx, cudaMemcpy(ctx->verts.ptr, sc->tri_verts, (size_t) sc->n_tris * 9 * sizeof(float), cudaMemcpyHostToDevice));
     }
     CU(ctx, cudaMemcpy(ctx->media.ptr, dm.data(), dm.size() * sizeof(DMedium), cudaMemcpyHostToDevice));
     if (sc->n_emitters) CU(ctx, cudaMemcpy(ctx->emitters.ptr, sc->emitters, (size_t) sc->n_emitters * sizeof(vrlb_emitter), cudaMemcpyHostToDevice));
     ctx->scene.tris = ctx->tris.ptr; ctx->scene.verts = ctx->verts.ptr; ctx->scene.nodes = ctx->nodes.ptr;
+    ctx->scene.wnodes = ctx->wnodes.ptr; ctx->scene.stris = ctx->stris.ptr; ctx->scene.main_root = sa.main_root;
+    for (int k = 0; k < 3; ++k) { ctx->scene.main_lo[k] = sa.main_lo[k]; ctx->scene.main_hi[k] = sa.main_hi[k]; }
+    ctx->scene.n_shells = (int32_t) sa.shells.size();
+    for (size_t i = 0; i < sa.shells.size(); ++i) ctx->scene.shells[i] = sa.shells[i];
     ctx->scene.n_tris = (int32_t) tris.size(); ctx->scene.n_nodes = (int32_t) nodes.size();
     ctx->scene.media = ctx->media.ptr; ctx->scene.n_media = (int32_t) dm.size();
     ctx->scene.emitters = ctx->emitters.ptr; ctx->scene.n_emitters = (int32_t) sc->n_emitters;
     ctx->host_media.assign(sc->media, sc->media + sc->n_media);
-    ctx->have_scene = true;
+    ctx->have_scene = true; ctx->fast_dirty = true;
+    ctx->all_iso = true;
+    for (const DMedium &d : dm) if (d.phase != VRLB_PHASE_ISOTROPIC) ctx->all_iso = false;
     return VRLB_OK;
 }
 
@@ -288,6 +300,7 @@ int vrlb_vrls_upload(vrlb_context *ctx, const vrlb_vrlset_desc *set) {
     cudaEventRecord(ctx->ev[1], ctx->stream);
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->timing.ms_upload = elapsed(ctx->ev[0], ctx->ev[1]);
+    ctx->fast_dirty = true;
     ctx->n_vrls = n; ctx->vrl_first = set->first_index; ctx->vrl_total = total; ctx->vrl_scale = set->scale;
     return VRLB_OK;
 }
@@ -402,15 +415,25 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "no scene resident");
     if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no camera segments resident");
     if (opt->samples_per_query < 1) return fail(ctx, VRLB_ERR_INVALID, "samples_per_query must be >= 1");
-    if (opt->math_mode != 0) return fail(ctx, VRLB_ERR_INVALID, "math_mode %d not available in this build", opt->math_mode);
+    if (opt->math_mode < 0 || opt->math_mode > 2) return fail(ctx, VRLB_ERR_INVALID, "math_mode %d unknown (0 exact, 1 fast + conditioning guard, 2 fast unguarded)", opt->math_mode);
     if (ctx->cancel.exchange(0)) return fail(ctx, VRLB_ERR_CANCELLED, "cancelled");
     GatherParams p{};
     p.scene = ctx->scene; p.segs = ctx->segs.ptr; p.n_segs = ctx->n_segs;
     p.vrls = ctx->vrls.ptr; p.n_vrls = ctx->n_vrls; p.first_index = ctx->vrl_first; p.total = ctx->vrl_total;
     p.scale = ctx->vrl_scale; p.scale_rr = opt->scale_rr; p.q = (uint32_t) opt->samples_per_query;
     p.film_rgb = ctx->film_rgb.ptr; p.seg_out = seg_out_dev;
+    const bool vis = opt->visibility != 0 && ctx->scene.n_tris > 0;
+    if (opt->math_mode != 0 && ctx->fast_dirty && ctx->n_vrls) {
+        CU(ctx, ctx->vrls_fast.reserve(ctx->n_vrls));
+        CU(ctx, launch_prep_fast_vrls(ctx->vrls.ptr, ctx->n_vrls, ctx->media.ptr, ctx->vrl_scale, ctx->vrls_fast.ptr, ctx->stream));
+        ctx->fast_dirty = false; ctx->timing.total_launches += 1; ctx->launches += 1;
+    }
+    p.vrls_fast = ctx->vrls_fast.ptr;
+    p.guard_h = opt->reserved[0] ? (float) opt->reserved[0] * 1e-3f : 0.2f;   // dev knobs (milli-units); 0 = shipped defaults
+    p.guard_z = opt->reserved[1] ? (float) opt->reserved[1] : 8.0f;
     cudaEventRecord(ctx->ev[2], ctx->stream);
-    CU(ctx, launch_gather(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, opt->visibility != 0 && ctx->scene.n_tris > 0, ctx->stream));
+    if (opt->math_mode == 0) CU(ctx, launch_gather(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, vis, ctx->stream));
+    else CU(ctx, launch_gather_fast(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, vis, ctx->all_iso, opt->math_mode == 1, ctx->stream));
     cudaEventRecord(ctx->ev[3], ctx->stream);
     bool launched = p.n_segs && p.n_vrls;
     ctx->timing.gather_launches = launched ? 1 : 0;

@@ -84,6 +84,17 @@ struct DNode {           // 32 B.  inner: a = left child, b = right child; leaf:
     float lo[3]; int32_t a;
     float hi[3]; int32_t b;
 };
+struct DWNode {          // 64 B: the boxes of BOTH children of an inner node, for the shadow (any-hit) traversal.
+    float lo0[3], hi0[3], lo1[3], hi1[3];
+    uint32_t c0, c1;     // child reference: inner node index, or leaf = 0x80000000 | first_tri << 12 | count << 7 (low 7 bits free)
+    uint32_t pad[2];
+};
+#define VRLB_MAX_SHELLS 8
+struct DShell {          // a component lying in the faces of its own AABB (fog container, room walls)
+    float lo[3], hi[3];  // AABB shrunk by the safety margin
+    uint32_t root;       // child reference as in DWNode
+    uint32_t pad;
+};
 struct DMedium {         // what the gather needs of a medium (homogeneous / nonlinear coefficients)
     float max_density;   // scale * mean(sigma_t): grey extinction (homogeneous.cpp:26, constant3d.cpp:37)
     float sigma_s[3];    // scale * sigma_t * albedo (homogeneous.cpp:42-50)
@@ -102,6 +113,13 @@ struct DScene {
     const DTri  *tris;
     const float *verts;      // n_tris * 9, ORIGINAL order and values (si.p re-interpolation, mesh.cpp:484)
     const DNode *nodes;
+    // shadow structure (bvh_build.cpp::build_shadow_accel)
+    const DTri   *stris;
+    const DWNode *wnodes;
+    uint32_t     main_root;  // child reference; 0x80000000 = no main geometry
+    float        main_lo[3], main_hi[3];   // root box of the main BVH
+    int32_t      n_shells;
+    DShell       shells[VRLB_MAX_SHELLS];
     int32_t      n_tris;
     int32_t      n_nodes;
     const DMedium *media;
@@ -110,19 +128,51 @@ struct DScene {
     int32_t      n_emitters;
 };
 
+// Exactly-rounded fp32 building blocks: one IEEE operation each, immune to FMA contraction whatever the
+// translation unit's -fmad setting.  Hit / no-hit decisions (and the exact-mode gather) are built from these so
+// they agree with the oracle's -ffp-contract=off arithmetic.
+__device__ __forceinline__ float xmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float xadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float xsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float xdot(V3 a, V3 b) { return xadd(xadd(xmul(a.x, b.x), xmul(a.y, b.y)), xmul(a.z, b.z)); }
+__device__ __forceinline__ V3 xcross(V3 a, V3 b) {
+    return V3(xsub(xmul(a.y, b.z), xmul(a.z, b.y)), xsub(xmul(a.z, b.x), xmul(a.x, b.z)), xsub(xmul(a.x, b.y), xmul(a.y, b.x)));
+}
+__device__ __forceinline__ V3 xsub3(V3 a, V3 b) { return V3(xsub(a.x, b.x), xsub(a.y, b.y), xsub(a.z, b.z)); }
+
 // Mesh::ray_intersect_triangle, include/mitsuba/render/mesh.h:195-225
 __device__ inline bool intersect_tri(const DTri &tr, V3 o, V3 d, float mint, float maxt, float &t, float &u, float &v) {
     V3 p0(tr.p0[0], tr.p0[1], tr.p0[2]), e1(tr.e1[0], tr.e1[1], tr.e1[2]), e2(tr.e2[0], tr.e2[1], tr.e2[2]);
-    V3 pvec       = cross(d, e2);
-    float inv_det = 1.0f / dot(e1, pvec);
-    V3 tvec       = o - p0;
-    u             = dot(tvec, pvec) * inv_det;
+    V3 pvec       = xcross(d, e2);
+    float inv_det = __fdiv_rn(1.0f, xdot(e1, pvec));
+    V3 tvec       = xsub3(o, p0);
+    u             = xmul(xdot(tvec, pvec), inv_det);
     if (!(u >= 0.f && u <= 1.f)) return false;
-    V3 qvec = cross(tvec, e1);
-    v       = dot(d, qvec) * inv_det;
-    if (!(v >= 0.f && u + v <= 1.f)) return false;
-    t = dot(e2, qvec) * inv_det;
+    V3 qvec = xcross(tvec, e1);
+    v       = xmul(xdot(d, qvec), inv_det);
+    if (!(v >= 0.f && xadd(u, v) <= 1.f)) return false;
+    t = xmul(xdot(e2, qvec), inv_det);
     return (t >= mint && t <= maxt);
+}
+
+// Shadow-test variant for rays whose end points carry fast-arithmetic error (~1e-5 absolute): 0 = certain miss,
+// 1 = certain hit, 2 = within the margins of an edge / end point: the caller re-evaluates that eval with the
+// exactly-rounded path, whose ray matches the oracle's.
+__device__ inline int intersect_tri_graze(const DTri &tr, V3 o, V3 d, float mint, float maxt) {
+    const float eu = 1e-4f, et = 2e-4f + 1e-5f * maxt;
+    V3 p0(tr.p0[0], tr.p0[1], tr.p0[2]), e1(tr.e1[0], tr.e1[1], tr.e1[2]), e2(tr.e2[0], tr.e2[1], tr.e2[2]);
+    V3 pvec       = xcross(d, e2);
+    float inv_det = __fdiv_rn(1.0f, xdot(e1, pvec));
+    V3 tvec       = xsub3(o, p0);
+    float u       = xmul(xdot(tvec, pvec), inv_det);
+    if (!(u >= -eu && u <= 1.f + eu)) return 0;
+    V3 qvec = xcross(tvec, e1);
+    float v = xmul(xdot(d, qvec), inv_det);
+    if (!(v >= -eu && xadd(u, v) <= 1.f + eu)) return 0;
+    float t = xmul(xdot(e2, qvec), inv_det);
+    if (!(t >= mint - et && t <= maxt + et)) return 0;
+    bool sure = u >= eu && v >= eu && xadd(u, v) <= 1.f - eu && t >= mint + et && t <= maxt - et;
+    return sure ? 1 : 2;
 }
 
 // conservative slab test (boxes are padded on the host); NaNs from 0*inf are dropped by fminf/fmaxf
@@ -169,24 +219,56 @@ __device__ inline Hit closest_hit(const DScene &s, V3 o, V3 d, float mint, float
 // Shadow query of VRL::evalTransmittance (vrl_struct.h:509-572).  Null::eval() returns 0
 // (src/bsdfs/null.cpp:59-62), so crossing ANY surface -- occluder or index-matched boundary -- zeroes
 // the transmittance: the reference's closest-hit loop reduces to "is there any hit in [0, maxt]".
+// Traversal over DWNode: one 64 B fetch gives both children's boxes; the slab tests are conservative (padded
+// boxes, FMA form), the triangle test is the exactly-rounded one, so hit / no-hit equals the oracle's.
+__device__ __forceinline__ bool slab2(float lox, float loy, float loz, float hix, float hiy, float hiz,
+                                      V3 inv, V3 o, float mint, float maxt) {
+    // (plane - o) * inv, not fma(plane, inv, -o * inv): the latter loses |o * inv| * eps absolutely when a
+    // direction component is tiny, enough to skip a box that is hit
+    float ax = (lox - o.x) * inv.x, bx = (hix - o.x) * inv.x;
+    float ay = (loy - o.y) * inv.y, by = (hiy - o.y) * inv.y;
+    float az = (loz - o.z) * inv.z, bz = (hiz - o.z) * inv.z;
+    float t0 = fmaxf(fmaxf(mint, fminf(ax, bx)), fmaxf(fminf(ay, by), fminf(az, bz)));
+    float t1 = fminf(fminf(maxt, fmaxf(ax, bx)), fminf(fmaxf(ay, by), fmaxf(az, bz)));
+    return t0 <= fmaf(t1, 1.00001f, 1e-5f);
+}
+__device__ __forceinline__ bool leaf_any_hit(const DScene &s, uint32_t ref, V3 o, V3 d, float mint, float maxt) {
+    uint32_t first = (ref & 0x7fffffffu) >> 12, cnt = (ref >> 7) & 31u;
+    for (uint32_t i = first; i < first + cnt; ++i) {
+        float t, u, v;
+        if (intersect_tri(s.stris[i], o, d, mint, maxt, t, u, v)) return true;
+    }
+    return false;
+}
+__device__ inline bool traverse_any_hit(const DScene &s, uint32_t root, V3 o, V3 d, V3 inv, float mint, float maxt) {
+    if (root & 0x80000000u) return leaf_any_hit(s, root, o, d, mint, maxt);
+    // 0 * inf = NaN when a direction component is 0 and the origin lies on a slab plane: fminf/fmaxf drop NaNs,
+    // which only widens the interval (conservative)
+    uint32_t stack[32]; int sp = 0;
+    uint32_t cur = root;
+    while (true) {
+        const float4 *np = reinterpret_cast<const float4 *>(s.wnodes + cur);
+        float4 a = __ldg(np), b = __ldg(np + 1), c = __ldg(np + 2), e = __ldg(np + 3);
+        bool h0 = slab2(a.x, a.y, a.z, a.w, b.x, b.y, inv, o, mint, maxt);
+        bool h1 = slab2(b.z, b.w, c.x, c.y, c.z, c.w, inv, o, mint, maxt);
+        uint32_t c0 = __float_as_uint(e.x), c1 = __float_as_uint(e.y);
+        if (h0 && (c0 & 0x80000000u)) { if (leaf_any_hit(s, c0, o, d, mint, maxt)) return true; h0 = false; }
+        if (h1 && (c1 & 0x80000000u)) { if (leaf_any_hit(s, c1, o, d, mint, maxt)) return true; h1 = false; }
+        if (h0) { if (h1) stack[sp++] = c1; cur = c0; }
+        else if (h1) cur = c1;
+        else { if (sp == 0) return false; cur = stack[--sp]; }
+    }
+}
 __device__ inline bool any_hit(const DScene &s, V3 o, V3 d, float mint, float maxt) {
-    if (s.n_nodes == 0) return false;
+    if (s.n_tris == 0) return false;
     V3 inv(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    int stack[48]; int sp = 0; stack[sp++] = 0;
-    while (sp) {
-        int ni = stack[--sp];
-        const float4 *np = reinterpret_cast<const float4 *>(s.nodes + ni);
-        float4 lo = __ldg(np), hi = __ldg(np + 1);
-        if (!slab(lo, hi, o, inv, mint, maxt)) continue;
-        int a = __float_as_int(lo.w), b = __float_as_int(hi.w);
-        if (b < 0) {
-            for (int i = a; i < a - b; ++i) {
-                float t, u, v;
-                if (intersect_tri(s.tris[i], o, d, mint, maxt, t, u, v)) return true;
-            }
-        } else {
-            stack[sp++] = a; stack[sp++] = b;
-        }
+    if (s.main_root != 0x80000000u && traverse_any_hit(s, s.main_root, o, d, inv, mint, maxt)) return true;
+    V3 e = o + d * maxt;
+    for (int i = 0; i < s.n_shells; ++i) {
+        const DShell &sh = s.shells[i];
+        bool inside = o.x > sh.lo[0] && o.x < sh.hi[0] && o.y > sh.lo[1] && o.y < sh.hi[1] && o.z > sh.lo[2] && o.z < sh.hi[2] &&
+                      e.x > sh.lo[0] && e.x < sh.hi[0] && e.y > sh.lo[1] && e.y < sh.hi[1] && e.z > sh.lo[2] && e.z < sh.hi[2];
+        if (!inside && traverse_any_hit(s, sh.root, o, d, inv, mint, maxt)) return true;
     }
     return false;
 }

@@ -13,17 +13,22 @@ struct GatherParams {
     const vrlb_segment *segs;        // device, 64 B records
     uint64_t            n_segs;
     const DVrl         *vrls;        // device, 48 B records (this rank's shard)
+    const DVrl         *vrls_fast;   // same records pre-multiplied for the fast kernel (launch_prep_fast_vrls)
     uint64_t            n_vrls;
     uint64_t            first_index; // global index of vrls[0] (PCG32 stream addressing)
     uint64_t            total;       // size of the whole exported set
     float               scale;       // VRLMap::m_scale
     float               scale_rr;
+    float               guard_h, guard_z; // fast gather: evals with closest distance < guard_h or asinh argument < -guard_z take the exact path
     uint32_t            q;           // samples_per_query
     float              *film_rgb;    // device, width*height*3 fp32, accumulated with RED.ADD (may be null)
     float              *seg_out;     // device, n_segs*3: Li per segment before the weight (may be null)
 };
 
 cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis, cudaStream_t stream);
+// math_mode 1 / 2 (gather_fast.cu): iso = every medium isotropic, guard = route ill-conditioned evals to the exact path
+cudaError_t launch_gather_fast(const GatherParams &p, bool uniform, bool rr, bool vis, bool iso, bool guard, cudaStream_t stream);
+cudaError_t launch_prep_fast_vrls(const DVrl *in, uint64_t n, const DMedium *media, float scale, DVrl *out, cudaStream_t stream);
 
 struct SegmentParams {
     DScene        scene;

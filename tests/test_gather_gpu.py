@@ -34,8 +34,9 @@ def _setup(occluders, phase=abi.PHASE_ISOTROPIC, n_vrls=2000, w=48, h=32, **optk
 
 @pytest.mark.parametrize("occluders,vis", [(False, 0), (True, 1)])
 @pytest.mark.parametrize("uniform", [0, 1])
-def test_segments_and_gather_match_oracle(ctx, occluders, vis, uniform):
-    sc, cam, opt, soa = _setup(occluders, visibility=vis, use_uniform_sampling=uniform)
+@pytest.mark.parametrize("math_mode", [0, 1])
+def test_segments_and_gather_match_oracle(ctx, occluders, vis, uniform, math_mode):
+    sc, cam, opt, soa = _setup(occluders, visibility=vis, use_uniform_sampling=uniform, math_mode=math_mode)
     vd = scenes.vrlset_desc(soa)
     osc = oracle.OracleScene(sc)
     ref_segs, ref_direct, ref_aw = osc.build_segments(cam, opt, soa.shape[1])
@@ -66,8 +67,9 @@ def test_segments_and_gather_match_oracle(ctx, occluders, vis, uniform):
     assert np.array_equal(xyzaw[..., 3:], ref_aw)
 
 
-def test_hg_rr_q2_match_oracle(ctx):
-    sc, cam, opt, soa = _setup(True, phase=abi.PHASE_HG, n_vrls=1500, visibility=1, rr_vrl=1, samples_per_query=2)
+@pytest.mark.parametrize("math_mode", [0, 1])
+def test_hg_rr_q2_match_oracle(ctx, math_mode):
+    sc, cam, opt, soa = _setup(True, phase=abi.PHASE_HG, n_vrls=1500, visibility=1, rr_vrl=1, samples_per_query=2, math_mode=math_mode)
     vd = scenes.vrlset_desc(soa)
     osc = oracle.OracleScene(sc)
     ctx.set_scene(sc)
