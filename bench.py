@@ -41,7 +41,7 @@ METRIC = "camera-seg x VRL evals/sec (1080p, 100k VRLs)"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--width", type=int, default=1920)
@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true")
     return ap.parse_args()
 
 
@@ -194,17 +195,14 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sc, cam, opt, soa, name = workload(args)
     n_total = soa.shape[1]
-    lo, hi = rank * n_total // world, (rank + 1) * n_total // world
-    shard = np.ascontiguousarray(soa[:, lo:hi])
-    vd = scenes.vrlset_desc(shard, scale=1.0 / n_total, first_index=lo, total=n_total)
+    lo, hi = pkg.sharding.shard_bounds(n_total, rank, world)
+    shard, vd = pkg.sharding.shard_desc(soa, rank, world)
 
     ctx = api.Context(local)
     stream = torch.cuda.Stream()
     ctx.set_stream(stream.cuda_stream)
     if world > 1:
-        ids = [api.Context.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(ids, src=0)
-        ctx.comm_init(ids[0], rank, world)
+        ctx.comm_init(pkg.sharding.broadcast_comm_id(dist, api.Context.comm_unique_id, rank), rank, world)
     ctx.set_scene(sc)
     ctx.upload_vrls(vd)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
@@ -269,6 +267,26 @@ def run_ours(args):
                "h2d_bytes_per_step": int(shard.nbytes) * world, "d2h_bytes_per_step": int(cam.width * cam.height * 5 * 4),
                "ms_per_frame": 1e3 * float(dt.item()) / args.steps}
 
+    # ---- secondary figure: the same frame without occluders (variant V1: visibility == medium transmittance), the
+    #      pure sample+shade rate of the gather kernel that the FP32-issue roofline describes -------------------
+    secondary = None
+    if not args.no_occluders and not args.no_secondary:
+        sc1 = scenes.box_fog_scene(occluders=False)
+        opt1 = scenes.default_options(samples_per_query=args.q, visibility=0)
+        ctx.set_scene(sc1)
+        ctx.upload_vrls(vd)
+        n1 = ctx.build_segments(cam, opt1)
+        g1 = []
+        for i in range(3):
+            ctx.gather(opt1); ctx.synchronize()
+            g1.append(ctx.timing()["ms_gather"])
+        g1 = float(np.mean(g1[1:]))
+        ev1 = n1 * (hi - lo) * opt1.samples_per_query
+        secondary = {"workload": "same frame, variant V1 (no occluders, no shadow traversal), gather kernel only, this rank's shard",
+                     "evals_per_s_per_gpu": ev1 / (g1 * 1e-3), "ms_per_launch": g1,
+                     "fp32_tflops": ev1 * FLOPS_PER_EVAL / (g1 * 1e-3) * 1e-12,
+                     "frac_of_fp32_peak": ev1 * FLOPS_PER_EVAL / (g1 * 1e-3) * 1e-12 / fp32_peak if fp32_peak else None}
+
     if rank == 0:
         g_ms = float(np.mean(gather_ms))
         shard_evals = n_segs * (hi - lo) * opt.samples_per_query
@@ -288,10 +306,10 @@ def run_ours(args):
                            "l2": "256 MB flush buffer written between steps; segment buffer 133 MB > L2"},
                 "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                              "frac": achieved / fp32_peak if fp32_peak else None, "traffic": traffic,
-                             "kernel": "gather_kernel", "ms_per_launch": g_ms, "flops_per_eval": FLOPS_PER_EVAL,
+                             "kernel": "gather_fast_vis_kernel" if not args.no_occluders else "gather_fast_kernel", "ms_per_launch": g_ms, "flops_per_eval": FLOPS_PER_EVAL,
                              "peak_source": "FFMA microkernel measured in this run (vrlb_measure_fp32_peak); "
                                             "MEASURED_PEAKS.json has no FP32 entry"},
-                "clocks": clk, "gpu_launches": int(launches), "e2e": e2e}
+                "clocks": clk, "gpu_launches": int(launches), "e2e": e2e, "secondary": secondary}
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, desc, _, _ = cpu_sample(sc, cam, opt, soa, args.cpu_seconds)
             line["cpu_baseline"] = {"value": rate, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc}

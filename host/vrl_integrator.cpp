@@ -1,0 +1,212 @@
+// vrl_integrator.cpp -- see vrl_integrator.h.  Host logic only; all computation happens in libvrl_b200.so.
+#include "vrl_integrator.h"
+
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+
+namespace vrlhost {
+
+namespace {
+[[noreturn]] void Throw(const std::string &msg) { throw std::runtime_error(msg); }   // Throw(...) of mitsuba/core/logger.h
+}
+
+// ---- Properties ---------------------------------------------------------------------------------------------
+bool Properties::bool_(const std::string &k, bool def) const {
+    auto it = m_values.find(k);
+    if (it == m_values.end()) return def;
+    m_queried.insert(k);
+    if (auto p = std::get_if<bool>(&it->second)) return *p;
+    Throw("The property \"" + k + "\" has the wrong type (expected <boolean>).");
+}
+int64_t Properties::int_(const std::string &k, int64_t def) const {
+    auto it = m_values.find(k);
+    if (it == m_values.end()) return def;
+    m_queried.insert(k);
+    if (auto p = std::get_if<int64_t>(&it->second)) return *p;
+    Throw("The property \"" + k + "\" has the wrong type (expected <integer>).");
+}
+double Properties::float_(const std::string &k, double def) const {
+    auto it = m_values.find(k);
+    if (it == m_values.end()) return def;
+    m_queried.insert(k);
+    if (auto p = std::get_if<double>(&it->second)) return *p;
+    if (auto p = std::get_if<int64_t>(&it->second)) return (double) *p;
+    Throw("The property \"" + k + "\" has the wrong type (expected <float>).");
+}
+Vec3 Properties::vector3f(const std::string &k, Vec3 def) const {
+    auto it = m_values.find(k);
+    if (it == m_values.end()) return def;
+    m_queried.insert(k);
+    if (auto p = std::get_if<Vec3>(&it->second)) return *p;
+    Throw("The property \"" + k + "\" has the wrong type (expected <vector>).");
+}
+std::vector<std::string> Properties::unqueried() const {
+    std::vector<std::string> out;
+    for (auto &kv : m_values) if (!m_queried.count(kv.first)) out.push_back(kv.first);
+    return out;
+}
+
+// ---- VRL set file: "VRLB" | u32 version | u64 n | f32 scale | u32 pad | 10*n f32 (SoA) | n u16 -----------------
+void VrlSet::save(const std::string &path) const {
+    std::ofstream f(path, std::ios::binary);
+    if (!f) Throw("cannot write " + path);
+    uint32_t ver = 1, pad = 0;
+    f.write("VRLB", 4); f.write((const char *) &ver, 4); f.write((const char *) &n, 8);
+    f.write((const char *) &scale, 4); f.write((const char *) &pad, 4);
+    f.write((const char *) soa10.data(), (std::streamsize) (soa10.size() * 4));
+    std::vector<uint16_t> m = medium; m.resize(n, 0);
+    f.write((const char *) m.data(), (std::streamsize) (n * 2));
+}
+void VrlSet::load(const std::string &path) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) Throw("cannot read " + path);
+    char magic[4]; uint32_t ver = 0, pad = 0;
+    f.read(magic, 4); f.read((char *) &ver, 4); f.read((char *) &n, 8); f.read((char *) &scale, 4); f.read((char *) &pad, 4);
+    if (!f || std::memcmp(magic, "VRLB", 4) != 0 || ver != 1) Throw(path + ": not a VRLB version 1 file");
+    soa10.resize((size_t) n * 10); medium.resize((size_t) n);
+    f.read((char *) soa10.data(), (std::streamsize) (soa10.size() * 4));
+    f.read((char *) medium.data(), (std::streamsize) (n * 2));
+    if (!f) Throw(path + ": truncated VRLB file");
+}
+
+// ---- VRLIntegrator ------------------------------------------------------------------------------------------
+VRLIntegrator::VRLIntegrator(const Properties &props) {
+    // Integrator / SamplingIntegrator base, integrator.cpp:26-38
+    m_blockSize      = props.int_("block_size", 0);
+    if (m_blockSize < 0) Throw("\"block_size\" must be >= 0");                       // integrator.cpp:28-29
+    m_samplesPerPass = props.int_("samples_per_pass", -1);
+    m_timeout        = props.float_("timeout", -1.0);
+    m_hideEmitters   = props.bool_("hide_emitters", false);
+    // vrl.cpp:33-73 (the later global/caustic defaults win)
+    m_globalPhotons  = props.int_("global_photons", 250000);
+    m_causticPhotons = props.int_("caustic_photons", 250000);
+    m_volumePhotons  = props.int_("volume_photons", 1000);
+    m_maxDepth       = props.int_("max_depth", 512);
+    m_targetVRLs     = props.int_("target_vrls", 1000);
+    m_volumeLookupRadiusRelative  = props.float_("volume_lookup_radius_relative", 0.005);
+    m_globalLookupRadiusRelative  = props.float_("global_lookup_radius_relative", 0.05);
+    m_causticLookupRadiusRelative = props.float_("caustic_lookup_radius_relative", 0.0125);
+    m_globalLookupSize  = props.int_("global_lookup_size", 120);
+    m_causticLookupSize = props.int_("caustic_lookup_size", 120);
+    m_samplesPerQuery   = props.int_("samples_per_query", 2);
+    m_rrDepth           = props.int_("rr_depth", 5);
+    m_useLaser          = props.bool_("use_laser", false);
+    laserOrigin         = props.vector3f("laser_origin", Vec3());
+    laserDirection      = props.vector3f("laser_direction", Vec3());
+    m_useNonLinear            = props.bool_("use_non_linear", true);
+    m_useNonLinearCameraRays  = props.bool_("use_non_linear_camera", true);
+    m_useNLAtomicQuery        = props.bool_("use_nl_atomic_query", false);
+    m_useDirectIllum          = props.bool_("use_direct_illum", true);
+    m_diceVRL                 = props.int_("dice_vrl", 1);
+    m_longVRL                 = props.bool_("long_vrl", false);
+    m_useUniformSampling      = props.bool_("use_uniform_sampling", false) || (m_useNLAtomicQuery && m_useNonLinearCameraRays);
+    minVRLLength              = props.float_("min_vrl_length", 5);
+    m_useLightCut             = props.bool_("use_light_cut", false);
+    m_stochasticLightcut      = props.bool_("stochastic_lightcut", false);
+    m_lightcutSamples         = props.int_("lightcut_samples", 1);
+    m_RRVRL                   = props.bool_("rr_vrl", false);
+    m_scaleRR                 = props.float_("scale_rr", 0.5);
+    m_thresholdBetterDist     = props.int_("threshold_better_dist", 8);
+    m_thresholdError          = props.float_("threshold_error", 0.02);
+    m_shootCenter             = props.bool_("shoot_center", true);
+    // additions of this implementation
+    m_device   = props.int_("device", 0);
+    m_mathMode = props.int_("math_mode", 1);
+    // the XML loader's check, xml.cpp:1050-1068
+    auto rest = props.unqueried();
+    if (!rest.empty()) {
+        std::string msg = "Error while loading \"<integrator type=\\\"" + props.plugin_name() + "\\\">\": unreferenced propert" +
+                          (rest.size() > 1 ? "ies " : "y ");
+        for (size_t i = 0; i < rest.size(); ++i) msg += (i ? ", \"" : "\"") + rest[i] + "\"";
+        Throw(msg);
+    }
+    if (m_useLightCut) Throw("use_light_cut: the lightcut accelerator is not on the B200 path yet (DESIGN.md section 7)");
+    if (m_samplesPerQuery < 1) Throw("\"samples_per_query\" must be >= 1");
+}
+
+VRLIntegrator::~VRLIntegrator() { if (m_ctx) vrlb_destroy(m_ctx); }
+
+void VRLIntegrator::check(int rc, const char *what) const {
+    if (rc == VRLB_OK) return;
+    std::string msg = std::string(what) + ": " + (m_ctx ? vrlb_last_error(m_ctx) : vrlb_last_error(nullptr));
+    Throw(msg);
+}
+
+void VRLIntegrator::sample() const { Throw("VRLIntegrator::sample(): not implemented on the host; the B200 path has no CPU fallback"); }
+
+vrlb_options VRLIntegrator::make_options(const HostSensor &sensor) const {
+    vrlb_options o{};
+    o.spp = sensor.spp;
+    // integrator.cpp:91-99: 32 unless `block_size` is given (the thread-count dependent halving is a CPU detail;
+    // parity runs pin block_size = 32)
+    o.block_size = m_blockSize > 0 ? (int32_t) m_blockSize : 32;
+    o.base_seed = sensor.sampler_seed;
+    o.samples_per_query = (int32_t) m_samplesPerQuery;
+    o.use_uniform_sampling = m_useUniformSampling;
+    o.rr_vrl = m_RRVRL; o.scale_rr = (float) m_scaleRR;
+    o.max_depth = (int32_t) m_maxDepth;
+    o.use_non_linear_camera = m_useNonLinearCameraRays; o.use_nl_atomic_query = m_useNLAtomicQuery;
+    o.visibility = 1; o.hide_emitters = m_hideEmitters; o.math_mode = (int32_t) m_mathMode;
+    return o;
+}
+
+void VRLIntegrator::set_vrls(const VrlSet &set) {
+    if (!m_ctx) check(vrlb_create((int) m_device, &m_ctx), "vrlb_create");
+    vrlb_vrlset_desc d{};
+    d.soa10 = set.soa10.data(); d.medium = set.medium.empty() ? nullptr : set.medium.data();
+    d.n = set.n; d.first_index = 0; d.total = set.n; d.scale = set.scale;
+    check(vrlb_vrls_upload(m_ctx, &d), "vrlb_vrls_upload");
+    m_have_vrls = true;
+}
+
+void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
+    if (!m_ctx) check(vrlb_create((int) m_device, &m_ctx), "vrlb_create");
+    vrlb_scene_desc sd{};
+    sd.tri_verts = scene.tri_verts.data(); sd.tri_flags = scene.tri_flags.data(); sd.n_tris = (uint32_t) scene.tri_flags.size();
+    sd.media = scene.media.data(); sd.n_media = (uint32_t) scene.media.size();
+    sd.emitters = scene.emitters.data(); sd.n_emitters = (uint32_t) scene.emitters.size();
+    check(vrlb_scene_set(m_ctx, &sd), "vrlb_scene_set");
+    if (!m_have_vrls)
+        Throw("preprocess(): VRL generation on the device is the next row (DESIGN.md section 7); supply the exported set with set_vrls()");
+    m_preprocessed = true;
+}
+
+bool VRLIntegrator::render(const HostScene &scene, const HostSensor &sensor, std::vector<float> &xyzaw) {
+    if (!m_preprocessed) preprocess(scene, sensor);          // Python callers never call preprocess
+    vrlb_options o = make_options(sensor);
+    xyzaw.assign((size_t) sensor.camera.width * sensor.camera.height * 5, 0.f);
+    int rc = vrlb_render(m_ctx, &sensor.camera, &o, nullptr, xyzaw.data());
+    if (rc == VRLB_ERR_CANCELLED) return false;              // render() returns !m_stop, integrator.cpp:182
+    check(rc, "vrlb_render");
+    vrlb_get_timing(m_ctx, &m_timing);
+    postprocess();
+    return true;
+}
+
+void VRLIntegrator::cancel() { if (m_ctx) vrlb_cancel(m_ctx); }
+
+void VRLIntegrator::postprocess() const {
+    // vrl.cpp:734-749 logs query counters; same information from the device timings
+    std::fprintf(stderr, "[VRLIntegrator] %llu camera segments x %llu VRLs: %llu evals, gather %.3f ms (%.3g evals/s), %u launches\n",
+                 (unsigned long long) m_timing.n_segments, (unsigned long long) (m_ctx ? vrlb_vrls_count(m_ctx) : 0),
+                 (unsigned long long) m_timing.n_evals, m_timing.ms_gather,
+                 m_timing.ms_gather > 0 ? m_timing.n_evals / (m_timing.ms_gather * 1e-3) : 0.0, m_timing.total_launches);
+}
+
+std::string VRLIntegrator::to_string() const {
+    std::ostringstream o;
+    o << "VRLIntegrator[\n  max_depth = " << m_maxDepth << ",\n  rr_depth = " << m_rrDepth << ",\n  target_vrls = " << m_targetVRLs
+      << ",\n  samples_per_query = " << m_samplesPerQuery << ",\n  use_uniform_sampling = " << m_useUniformSampling
+      << ",\n  rr_vrl = " << m_RRVRL << ",\n  backend = libvrl_b200 (sm_100a), math_mode = " << m_mathMode << "\n]";
+    return o.str();
+}
+
+}  // namespace vrlhost
+
+// ---- plugin discovery symbols (include/mitsuba/core/class.h:206-211, plugin.cpp:84-118) -------------------------
+extern "C" {
+const char *plugin_name() { return "VRLIntegrator"; }
+const char *plugin_descr() { return "Virtual ray lights, B200 gather (libvrl_b200)"; }
+}

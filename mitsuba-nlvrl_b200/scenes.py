@@ -280,3 +280,41 @@ def vrlset_desc(soa10, scale=None, first_index=0, total=None, medium=None):
     d.n, d.first_index, d.total = n, first_index, (total if total is not None else n)
     d.scale = (1.0 / d.total) if scale is None else scale
     return d
+
+
+# --------------------------------------------------------------------------- files (INTEGRATION.md "File formats")
+def save_vrlb(path, soa10, scale=None, medium=None):
+    """Exported VRL set: "VRLB" | u32 version | u64 n | f32 scale | u32 pad | 10*n f32 (SoA) | n u16 medium ids."""
+    import struct
+    n = soa10.shape[1]
+    scale = (1.0 / n) if scale is None else scale
+    med = np.zeros(n, np.uint16) if medium is None else np.ascontiguousarray(medium, np.uint16)
+    with open(path, "wb") as f:
+        f.write(b"VRLB" + struct.pack("<IQfI", 1, n, scale, 0))
+        f.write(np.ascontiguousarray(soa10, np.float32).tobytes())
+        f.write(med.tobytes())
+
+
+def load_vrlb(path):
+    import struct
+    with open(path, "rb") as f:
+        hdr = f.read(24)
+        if hdr[:4] != b"VRLB":
+            raise ValueError(f"{path}: not a VRLB file")
+        ver, n, scale, _ = struct.unpack("<IQfI", hdr[4:])
+        if ver != 1:
+            raise ValueError(f"{path}: VRLB version {ver}")
+        soa = np.frombuffer(f.read(40 * n), np.float32).reshape(10, n).copy()
+        med = np.frombuffer(f.read(2 * n), np.uint16).copy()
+    return soa, scale, med
+
+
+def save_scene_dump(path, scene, cam, spp=1, seed=0):
+    """Test-harness scene dump read by host/vrl_host (vrl_host_main.cpp)."""
+    import struct
+    v, fl = scene.tri_verts, scene.tri_flags
+    with open(path, "wb") as f:
+        f.write(struct.pack("<I", len(fl)) + v.tobytes() + fl.tobytes())
+        f.write(struct.pack("<I", len(scene.media)) + b"".join(bytes(m) for m in scene.media))
+        f.write(struct.pack("<I", len(scene.emitters)) + b"".join(bytes(e) for e in scene.emitters))
+        f.write(bytes(cam) + struct.pack("<iQ", spp, seed))

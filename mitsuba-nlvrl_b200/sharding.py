@@ -1,0 +1,27 @@
+"""Host-side multi-GPU protocol: contiguous VRL shards with GLOBAL stream addressing and the film sum.
+Used by bench.py under torchrun; the arithmetic is testable on CPU with the gloo backend (tests/test_multi_gpu_host.py)."""
+import numpy as np
+
+from . import scenes
+
+
+def shard_bounds(n_total, rank, world):
+    """Rank r owns VRLs [r*N/W, (r+1)*N/W): contiguous, so eval (s, j) keeps its PCG32 offset (s*N + j)*dpe."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside [0, {world})")
+    return rank * n_total // world, (rank + 1) * n_total // world
+
+
+def shard_desc(soa10, rank, world):
+    """(shard array kept alive by the caller, vrlb_vrlset_desc with first_index/total/scale of the WHOLE set)."""
+    n = soa10.shape[1]
+    lo, hi = shard_bounds(n, rank, world)
+    shard = np.ascontiguousarray(soa10[:, lo:hi])
+    return shard, scenes.vrlset_desc(shard, scale=1.0 / n, first_index=lo, total=n)
+
+
+def broadcast_comm_id(dist, make_id, rank, src=0):
+    """Rank `src` creates the NCCL unique id (vrlb_comm_unique_id), everyone receives the 128 bytes."""
+    box = [make_id() if rank == src else None]
+    dist.broadcast_object_list(box, src=src)
+    return box[0]
