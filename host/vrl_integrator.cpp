@@ -168,8 +168,20 @@ void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
     sd.media = scene.media.data(); sd.n_media = (uint32_t) scene.media.size();
     sd.emitters = scene.emitters.data(); sd.n_emitters = (uint32_t) scene.emitters.size();
     check(vrlb_scene_set(m_ctx, &sd), "vrlb_scene_set");
-    if (!m_have_vrls)
-        Throw("preprocess(): VRL generation on the device is the next row (DESIGN.md section 7); supply the exported set with set_vrls()");
+    if (!m_have_vrls) {
+        // light tracing on the device (vrl.cpp:117-374 -> generate.cu); scale = 1 / particles traced (vrl.cpp:404,423)
+        vrlb_generate_desc g{};
+        g.target_vrls = (uint64_t) m_targetVRLs; g.seed = 0;                       // sampler->seed(0), vrl.cpp:98
+        g.max_depth = (int32_t) m_maxDepth; g.rr_depth = (int32_t) m_rrDepth; g.min_vrl_length = (float) minVRLLength;
+        g.use_non_linear = m_useNonLinear; g.use_laser = m_useLaser;
+        const float lo[3] = { laserOrigin.x, laserOrigin.y, laserOrigin.z }, ld[3] = { laserDirection.x, laserDirection.y, laserDirection.z };
+        for (int k = 0; k < 3; ++k) { g.laser_origin[k] = lo[k]; g.laser_direction[k] = ld[k]; g.laser_power[k] = scene.laser_power[k]; }
+        g.start_medium = scene.emission_medium;
+        uint64_t n = 0, particles = 0;
+        check(vrlb_vrls_generate(m_ctx, &g, &n, &particles), "vrlb_vrls_generate");
+        std::fprintf(stderr, "[VRLIntegrator] VRL Map Created: %llu VRLs from %llu particles\n", (unsigned long long) n, (unsigned long long) particles);
+        m_have_vrls = true;
+    }
     m_preprocessed = true;
 }
 

@@ -58,6 +58,8 @@ struct HostScene {
     std::vector<uint32_t>     tri_flags;   // VRLB_SURF_*
     std::vector<vrlb_medium>  media;
     std::vector<vrlb_emitter> emitters;
+    int32_t emission_medium = -1;              // medium at the emitters / laser origin (-1 = none)
+    float   laser_power[3] = { 1.f, 1.f, 1.f };  // flux of the laser when `use_laser` (the reference takes it from the sampled emitter)
 };
 // ... and from mitsuba::Sensor / Film / Sampler
 struct HostSensor {

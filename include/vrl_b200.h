@@ -203,6 +203,28 @@ int  vrlb_vrls_upload(vrlb_context *ctx, const vrlb_vrlset_desc *set);
 int  vrlb_vrls_download(vrlb_context *ctx, float *soa10, uint16_t *medium, uint64_t cap, uint64_t *n_out);
 uint64_t vrlb_vrls_count(const vrlb_context *ctx);
 
+/* ---- VRL generation on the device: replaces the light tracer of VRLIntegrator::preprocess (vrl.cpp:117-374) and
+ *      NonLinearMedia::sampleNonLinearInteraction / handleNonLinearInteraction (nonlinear.cpp:244-405).  Particles are
+ *      marched through graded-IOR media with a fixed-step eikonal integrator (step = one IOR layer, height / res_y) and
+ *      emit piecewise-linear VRLs.  The resident set is replaced; m_scale = 1 / (particles traced) (vrl.cpp:404,423). */
+typedef struct vrlb_generate_desc {
+    uint64_t target_vrls;          /* `target_vrls`: generation stops at the particle that reaches it            */
+    uint64_t seed;                 /* particle i uses PCG32 seed(seed + i)                                       */
+    int32_t  max_depth, rr_depth;  /* vrl.cpp:36,46                                                              */
+    float    min_vrl_length;       /* vrl.cpp:64                                                                 */
+    int32_t  use_non_linear;       /* vrl.cpp:53: 0 = straight flights even in a nonlinear medium                */
+    int32_t  use_laser;            /* vrl.cpp:50,156-162; otherwise the scene's area emitters (VRLB_SURF_EMITTER) */
+    float    laser_origin[3], laser_direction[3], laser_power[3];
+    int32_t  start_medium;         /* medium id at the emission point, -1 = outside all media                    */
+    int32_t  max_steps;            /* eikonal step budget per flight (0 = 100000)                                */
+    int32_t  reserved[2];
+} vrlb_generate_desc;
+/* m_scale of the resident set, and the scatter depth of every resident VRL (VRL::m_scatterDepth, vrl_struct.h:675;
+ * 0 for uploaded sets) */
+float vrlb_vrls_scale(const vrlb_context *ctx);
+int  vrlb_vrls_download_depth(vrlb_context *ctx, int32_t *depth, uint64_t cap);
+int  vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t *n_vrls_out, uint64_t *n_particles_out);
+
 /* ---- camera segments: replaces the medium branch of VRLIntegrator::sample up to the query
  *      (vrl.cpp:443-631) driven by SamplingIntegrator::render_block/render_sample
  *      (integrator.cpp:187-297) ----------------------------------------------------------------- */

@@ -52,6 +52,13 @@ class VrlSetDesc(C.Structure):
                 ("first_index", C.c_uint64), ("total", C.c_uint64), ("scale", C.c_float), ("pad", C.c_float)]
 
 
+class GenerateDesc(C.Structure):
+    _fields_ = [("target_vrls", C.c_uint64), ("seed", C.c_uint64), ("max_depth", C.c_int32), ("rr_depth", C.c_int32),
+                ("min_vrl_length", C.c_float), ("use_non_linear", C.c_int32), ("use_laser", C.c_int32),
+                ("laser_origin", C.c_float * 3), ("laser_direction", C.c_float * 3), ("laser_power", C.c_float * 3),
+                ("start_medium", C.c_int32), ("max_steps", C.c_int32), ("reserved", C.c_int32 * 2)]
+
+
 class Segment(C.Structure):
     _fields_ = [("o", C.c_float * 3), ("maxt", C.c_float), ("d", C.c_float * 3), ("pixel", C.c_uint32),
                 ("weight", C.c_float * 3), ("medium", C.c_int32), ("rng_state", C.c_uint64),

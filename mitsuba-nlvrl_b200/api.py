@@ -19,7 +19,8 @@ EXPORTS = [
     "vrlb_segments_download", "vrlb_segments_count", "vrlb_film_clear", "vrlb_gather", "vrlb_gather_segments",
     "vrlb_film_device_ptr", "vrlb_film_download_xyzaw", "vrlb_film_download_rgb", "vrlb_render", "vrlb_cancel",
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
-    "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak",
+    "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
+    "vrlb_vrls_download_depth",
 ]
 
 
@@ -75,6 +76,10 @@ def load_library():
     L.vrlb_film_allreduce.argtypes = [vp]
     L.vrlb_film_resolve.argtypes = [vp, C.POINTER(vp)]
     L.vrlb_measure_fp32_peak.argtypes = [vp, f32p]
+    L.vrlb_vrls_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.vrlb_vrls_scale.argtypes = [vp]
+    L.vrlb_vrls_scale.restype = C.c_float
+    L.vrlb_vrls_download_depth.argtypes = [vp, C.POINTER(C.c_int32), C.c_uint64]
     _lib = L
     return L
 
@@ -120,6 +125,21 @@ class Context:
         got = C.c_uint64()
         self._check(self.lib.vrlb_vrls_download(self.h, abi.fptr(soa), med.ctypes.data_as(C.POINTER(C.c_uint16)), n, C.byref(got)))
         return soa[:, :n], med[:n]
+
+    def generate_vrls(self, gen):
+        """Light tracing on the device (vrlb_vrls_generate); returns (n_vrls, n_particles)."""
+        n, pcount = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.vrlb_vrls_generate(self.h, C.byref(gen), C.byref(n), C.byref(pcount)))
+        return int(n.value), int(pcount.value)
+
+    def vrls_scale(self):
+        return float(self.lib.vrlb_vrls_scale(self.h))
+
+    def download_vrl_depths(self):
+        n = int(self.lib.vrlb_vrls_count(self.h))
+        d = np.zeros(max(n, 1), np.int32)
+        self._check(self.lib.vrlb_vrls_download_depth(self.h, d.ctypes.data_as(C.POINTER(C.c_int32)), n))
+        return d[:n]
 
     def build_segments(self, cam, opt):
         self._check(self.lib.vrlb_segments_build(self.h, C.byref(cam), C.byref(opt)))

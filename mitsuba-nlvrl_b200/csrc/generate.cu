@@ -1,0 +1,198 @@
+// generate.cu -- VRL generation by GPU light tracing (north-star subsystem 1).
+//
+// Replaces the single-threaded light tracer of VRLIntegrator::preprocess (src/integrators/vrl/vrl.cpp:117-374)
+// and the cell-by-cell Snell refraction of NonLinearMedia (src/media/nonlinear.cpp:244-405): one thread per emitted
+// particle, each with its own PCG32 stream seed(base_seed + particle index) (the reference runs one serial stream;
+// generation is compared statistically).  Inside a graded-IOR ("nonlinear") medium the particle is
+// marched with a FIXED-STEP EIKONAL integrator
+//        v = n * dir,   dv/ds = grad n,   dx/ds = v / n          (semi-implicit Euler, step = one IOR layer)
+// through n(y) = lerp(bottom_ior, top_ior, (y - y0) / height) (nonlinear.cpp:129-153, method 0) and the curved path is
+// emitted as piecewise-linear VRLs: a segment is cut when the direction has changed and the segment is longer than
+// min_vrl_length (vrl.cpp:215-223), at every real scattering event (vrl.cpp:278-284) and at every surface
+// (vrl.cpp:313-314).  Homogeneous media take one straight flight per event.
+//
+// Events (vrl.cpp:180-357): Russian roulette after rr_depth; free-flight distance t = -log(1 - u) / sigma_maj with the
+// grey majorant (medium.cpp:36-75; tr/pdf cancels for a homogeneous extinction); real scatter: throughput *= albedo,
+// new direction from the phase function (isotropic.cpp / hg.cpp); null-BSDF surfaces are crossed and switch the
+// medium; other surfaces END the particle (surface BSDF sampling is outside the hot path).
+// Flux: laser = power; area emitter = Le * pi * area * pi (the second pi is vrl.cpp:151-152).
+//
+// Output is deterministic for a given (seed, particle count): pass 1 counts the VRLs of every particle, an exclusive
+// scan gives each particle its slot range, pass 2 re-traces and writes.  Records are written as 48 B DVrl.
+#include "vrlb_device.cuh"
+#include "vrlb_kernels.h"
+
+namespace vrlb {
+
+constexpr float kPi = 3.14159265358979323846f;
+
+__device__ inline float ior_at(const DMedium &m, float y) {
+    float h = m.nl_hi[1] - m.nl_lo[1];
+    float t = fminf(fmaxf((y - m.nl_lo[1]) / h, 0.f), 1.f);
+    return m.ior_bottom + (m.ior_top - m.ior_bottom) * t;
+}
+__device__ inline float ior_grad_y(const DMedium &m, V3 p) {
+    bool in = p.x >= m.nl_lo[0] && p.x <= m.nl_hi[0] && p.y >= m.nl_lo[1] && p.y <= m.nl_hi[1] && p.z >= m.nl_lo[2] && p.z <= m.nl_hi[2];
+    return in ? (m.ior_top - m.ior_bottom) / (m.nl_hi[1] - m.nl_lo[1]) : 0.f;
+}
+// one eikonal step of length ds: bends `dir` towards increasing n, returns the new direction (unit)
+__device__ inline V3 eikonal_bend(const DMedium &m, V3 p, V3 dir, float ds) {
+    float n = ior_at(m, p.y);
+    V3 v = dir * n;
+    v.y = v.y + ds * ior_grad_y(m, p);
+    return normalize(v);
+}
+
+__device__ inline V3 sample_uniform_sphere(float u1, float u2) {         // warp::square_to_uniform_sphere
+    float z = 1.f - 2.f * u2, r = sqrtf(fmaxf(1.f - z * z, 0.f));
+    float s, c; sincosf(2.f * kPi * u1, &s, &c);
+    return V3(r * c, r * s, z);
+}
+__device__ inline void frame(V3 n, V3 &s, V3 &t) {                        // coordinate_system, core/vector.h
+    float sign = copysignf(1.f, n.z), a = -1.f / (sign + n.z), b = n.x * n.y * a;
+    s = V3(1.f + sign * n.x * n.x * a, sign * b, -sign * n.x);
+    t = V3(b, sign + n.y * n.y * a, -n.y);
+}
+__device__ inline V3 sample_phase(const DMedium &m, V3 wi /* direction of travel */, float u1, float u2) {
+    if (m.phase == VRLB_PHASE_ISOTROPIC) return sample_uniform_sphere(u1, u2);
+    // Henyey-Greenstein about the direction of travel (hg.cpp:56-75: cos_theta relative to -wi = travel direction)
+    float g = m.g, cos_theta;
+    if (fabsf(g) < 1e-3f) cos_theta = 1.f - 2.f * u1;
+    else { float sq = (1.f - g * g) / (1.f - g + 2.f * g * u1); cos_theta = (1.f + g * g - sq * sq) / (2.f * g); }
+    float sin_theta = sqrtf(fmaxf(1.f - cos_theta * cos_theta, 0.f));
+    float s, c; sincosf(2.f * kPi * u2, &s, &c);
+    V3 a, b; frame(wi, a, b);
+    return normalize(a * (sin_theta * c) + b * (sin_theta * s) + wi * cos_theta);
+}
+
+struct Emit {
+    V3 o, d, flux; int medium;
+};
+
+__device__ inline Emit emit_particle(const GenParams &p, Pcg32 &rng) {
+    Emit e; e.medium = p.start_medium;
+    float u0 = rng.next_f32(), u1 = rng.next_f32(), u2 = rng.next_f32(), u3 = rng.next_f32(), u4 = rng.next_f32();
+    if (p.use_laser || p.n_emit_tris == 0) {                               // vrl.cpp:156-162
+        e.o = V3(p.laser_o[0], p.laser_o[1], p.laser_o[2]);
+        e.d = normalize(V3(p.laser_d[0], p.laser_d[1], p.laser_d[2]));
+        e.flux = V3(p.laser_power[0], p.laser_power[1], p.laser_power[2]);
+        return e;
+    }
+    // area emitter (area.cpp:74-117): triangle proportional to area (cdf), uniform point, cosine direction
+    int lo = 0, hi = p.n_emit_tris - 1;
+    float target = u0 * p.emit_area;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (p.emit_cdf[mid] < target) lo = mid + 1; else hi = mid; }
+    const DTri &t = p.scene.tris[p.emit_tris[lo]];
+    float su = sqrtf(u1), b0 = 1.f - su, b1 = u2 * su;                      // warp::square_to_uniform_triangle
+    V3 p0(t.p0[0], t.p0[1], t.p0[2]), e1(t.e1[0], t.e1[1], t.e1[2]), e2(t.e2[0], t.e2[1], t.e2[2]);
+    V3 n = tri_normal(t);
+    e.o = p0 + e1 * b1 + e2 * (1.f - b0 - b1);
+    float r = sqrtf(u3), s, c; sincosf(2.f * kPi * u4, &s, &c);           // cosine hemisphere
+    V3 a, b; frame(n, a, b);
+    e.d = normalize(a * (r * c) + b * (r * s) + n * sqrtf(fmaxf(1.f - u3, 0.f)));
+    int id = VRLB_SURF_GET_EMITTER(t.flags);
+    V3 Le(p.scene.emitters[id * 4], p.scene.emitters[id * 4 + 1], p.scene.emitters[id * 4 + 2]);
+    e.flux = Le * (kPi * p.emit_area * kPi);                               // Le * pi / pdf_pos, then * pi (vrl.cpp:151-152)
+    e.o = e.o + e.d * ((1.f + hmax_abs(e.o)) * kRayEpsilon);
+    return e;
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
+    uint64_t pi = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (pi >= p.n_particles) return;
+    const DScene &s = p.scene;
+    Pcg32 rng; rng.seed(p.base_seed + p.first_particle + pi);
+    uint32_t count = 0;
+    uint64_t slot = WRITE ? p.offsets[pi] : 0;
+    const uint64_t slot_end = WRITE ? p.offsets[pi + 1] : 0;
+
+    Emit e = emit_particle(p, rng);
+    V3 pos = e.o, dir = e.d, throughput(1.f);
+    int medium = e.medium, depth = 0;
+    V3 vrl_o = pos, vrl_d0 = dir; bool vrl_open = medium >= 0;
+    auto push = [&](V3 end, int med, V3 flux) {                             // VRL::setEndPoint + VRLMap::push_back
+        V3 dd = end - vrl_o; float len = norm(dd);
+        if (!(len > 0.f) || med < 0 || (flux.x == 0.f && flux.y == 0.f && flux.z == 0.f)) return;
+        if (WRITE && slot < slot_end) {
+            DVrl v; V3 dn = dd / len;
+            v.ox = vrl_o.x; v.oy = vrl_o.y; v.oz = vrl_o.z; v.length = len;
+            v.dx = dn.x; v.dy = dn.y; v.dz = dn.z; v.medium = (uint32_t) med;
+            v.fr = flux.x; v.fg = flux.y; v.fb = flux.z; v.pad = __int_as_float(depth);
+            p.out[slot++] = v;
+        }
+        ++count;
+    };
+
+    for (int bounce = 0; bounce < p.max_depth && count < p.max_per_particle; ++bounce) {
+        if (depth > p.rr_depth) {                                          // Russian roulette, vrl.cpp:181-185
+            float q = fminf(fmaxf(throughput.x, fmaxf(throughput.y, throughput.z)), 0.95f);
+            if (rng.next_f32() >= q) break;
+            throughput = throughput * (1.f / q);
+        }
+        // distance to the next medium event
+        float t_event = VRLB_INF;
+        const DMedium *m = medium >= 0 ? &s.media[medium] : nullptr;
+        if (m) {
+            (void) rng.next_f32();                                         // channel draw (grey majorant)
+            float u = rng.next_f32();
+            t_event = m->max_density > 0.f ? -logf(1.f - u) / m->max_density : VRLB_INF;
+        }
+        const bool curved = m && m->kind == VRLB_MEDIUM_NONLINEAR && m->nl_step > 0.f && p.use_non_linear;
+        // flight: straight (one closest-hit) or marched in eikonal steps
+        bool surface = false; Hit si; si.tri = -1; si.t = VRLB_INF;
+        float travelled = 0.f;
+        if (!curved) {
+            si = closest_hit(s, pos, dir, 0.f, t_event);
+            surface = si.tri >= 0;
+            float t = surface ? si.t : t_event;
+            if (!(t < VRLB_INF)) break;                                    // escaped
+            pos = pos + dir * t; travelled = t;
+        } else {
+            for (int step = 0; step < p.max_steps; ++step) {
+                float ds = fminf(m->nl_step, t_event - travelled);
+                si = closest_hit(s, pos, dir, 0.f, ds);
+                if (si.tri >= 0) { pos = pos + dir * si.t; travelled += si.t; surface = true; break; }
+                pos = pos + dir * ds; travelled += ds;
+                if (travelled >= t_event) break;
+                V3 nd = eikonal_bend(*m, pos, dir, ds);
+                // cut a VRL when the direction has changed and the piece is long enough (vrl.cpp:215-223)
+                if (vrl_open && dot(nd, vrl_d0) < 1.f - 1e-7f && norm(pos - vrl_o) > p.min_vrl_length) {
+                    push(pos, medium, throughput * e.flux);
+                    vrl_o = pos; vrl_d0 = nd;
+                }
+                dir = nd;
+            }
+            if (!surface && travelled < t_event) break;                     // step budget exhausted
+        }
+        if (surface) {
+            const DTri &tr = s.tris[si.tri];
+            if (vrl_open) push(pos, medium, throughput * e.flux);          // vrl.cpp:313-314
+            if ((tr.flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL) break;   // opaque surface: particle ends
+            (void) rng.next_f32(); (void) rng.next_f32(); (void) rng.next_f32();  // bsdf->sample draws, vrl.cpp:318
+            if (VRLB_SURF_GET_EXTERIOR(tr.flags) >= 0 || VRLB_SURF_GET_INTERIOR(tr.flags) >= 0) medium = target_medium(tr, dir);
+            pos = pos + dir * ((1.f + hmax_abs(pos)) * kRayEpsilon);        // spawn_ray offset
+            vrl_o = pos; vrl_d0 = dir; vrl_open = medium >= 0;
+            continue;
+        }
+        // real scattering event (homogeneous extinction: no null collisions), vrl.cpp:246-294
+        push(pos, medium, throughput * e.flux);
+        throughput = throughput * V3(m->albedo[0], m->albedo[1], m->albedo[2]);
+        ++depth;
+        float u1 = rng.next_f32(), u2 = rng.next_f32();
+        dir = sample_phase(*m, dir, u1, u2);
+        vrl_o = pos; vrl_d0 = dir; vrl_open = true;
+        if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+    }
+    if (!WRITE) p.counts[pi] = count;
+}
+
+cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream) {
+    if (p.n_particles == 0) return cudaSuccess;
+    uint32_t grid = (uint32_t) ((p.n_particles + 127) / 128);
+    if (write) generate_kernel<true><<<grid, 128, 0, stream>>>(p);
+    else generate_kernel<false><<<grid, 128, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace vrlb

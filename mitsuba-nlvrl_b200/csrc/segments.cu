@@ -49,13 +49,6 @@ __device__ inline void camera_ray(const vrlb_camera &c, float sx, float sy, V3 &
     d = V3(q[0], q[1], q[2]);
 }
 
-__device__ inline V3 tri_normal(const DTri &t) {
-    return normalize(cross(V3(t.e1[0], t.e1[1], t.e1[2]), V3(t.e2[0], t.e2[1], t.e2[2])));
-}
-__device__ inline int target_medium(const DTri &t, V3 d) {      // interaction.h:186-200
-    return dot(d, tri_normal(t)) > 0.f ? VRLB_SURF_GET_EXTERIOR(t.flags) : VRLB_SURF_GET_INTERIOR(t.flags);
-}
-
 __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
     const int bs = p.opt.block_size;
     const uint32_t pixel_count = (uint32_t) (bs * bs);

@@ -8,6 +8,7 @@
 #include <dlfcn.h>
 
 #include <atomic>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -52,6 +53,7 @@ struct vrlb_context {
     DScene scene{};
     bool have_scene = false;
     std::vector<vrlb_medium> host_media;
+    std::vector<DTri> host_tris;      // BVH order, for the emitter table of vrlb_vrls_generate
 
     // VRL set
     DevBuf<DVrl> vrls, vrls_fast; bool fast_dirty = true; bool all_iso = true;
@@ -237,6 +239,14 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
         d.max_density = m.scale * mean;                                          // homogeneous.cpp:26
         for (int k = 0; k < 3; ++k) d.sigma_s[k] = (m.sigma_t[k] * m.scale) * m.albedo[k];   // homogeneous.cpp:42-50
         d.g = m.g; d.phase = m.phase; d.kind = m.kind;
+        for (int k = 0; k < 3; ++k) { d.albedo[k] = m.albedo[k]; d.nl_lo[k] = m.nl_bbox_min[k]; d.nl_hi[k] = m.nl_bbox_max[k]; }
+        d.ior_bottom = m.bottom_ior; d.ior_top = m.top_ior; d.nl_step = 0.f;
+        if (m.kind == VRLB_MEDIUM_NONLINEAR) {
+            if (m.ior_method != 0) return fail(ctx, VRLB_ERR_INVALID, "medium %u: only ior_method 0 (linear in height) is on the path", i);
+            if (!(m.nl_bbox_max[1] > m.nl_bbox_min[1]) || m.nl_res[1] < 1) return fail(ctx, VRLB_ERR_INVALID, "medium %u: nonlinear medium needs nl_bbox and nl_res", i);
+            if (!(m.bottom_ior > 0.f && m.top_ior > 0.f)) return fail(ctx, VRLB_ERR_INVALID, "medium %u: IOR must be positive", i);
+            d.nl_step = (m.nl_bbox_max[1] - m.nl_bbox_min[1]) / (float) m.nl_res[1];
+        }
         dm[i] = d;
     }
     std::vector<DNode> nodes; std::vector<DTri> tris;
@@ -265,6 +275,7 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     ctx->scene.media = ctx->media.ptr; ctx->scene.n_media = (int32_t) dm.size();
     ctx->scene.emitters = ctx->emitters.ptr; ctx->scene.n_emitters = (int32_t) sc->n_emitters;
     ctx->host_media.assign(sc->media, sc->media + sc->n_media);
+    ctx->host_tris = tris;
     ctx->have_scene = true; ctx->fast_dirty = true;
     ctx->all_iso = true;
     for (const DMedium &d : dm) if (d.phase != VRLB_PHASE_ISOTROPIC) ctx->all_iso = false;
@@ -320,6 +331,99 @@ int vrlb_vrls_download(vrlb_context *ctx, float *soa10, uint16_t *medium, uint64
     CU(ctx, cudaMemcpyAsync(soa10, ctx->stage_soa.ptr, n * 10 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     if (medium) CU(ctx, cudaMemcpyAsync(medium, ctx->stage_med.ptr, n * sizeof(uint16_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return VRLB_OK;
+}
+
+float vrlb_vrls_scale(const vrlb_context *ctx) { return ctx ? ctx->vrl_scale : 0.f; }
+
+int vrlb_vrls_download_depth(vrlb_context *ctx, int32_t *depth, uint64_t cap) {
+    if (!ctx || !depth) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (cap < ctx->n_vrls) return fail(ctx, VRLB_ERR_INVALID, "capacity too small");
+    std::vector<DVrl> tmp((size_t) ctx->n_vrls);
+    if (ctx->n_vrls) CU(ctx, cudaMemcpy(tmp.data(), ctx->vrls.ptr, tmp.size() * sizeof(DVrl), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < tmp.size(); ++i) std::memcpy(&depth[i], &tmp[i].pad, 4);
+    return VRLB_OK;
+}
+
+int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t *n_vrls_out, uint64_t *n_particles_out) {
+    if (!ctx || !gen) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_vrls_generate");
+    if (gen->target_vrls == 0) return fail(ctx, VRLB_ERR_INVALID, "target_vrls must be > 0");
+    if (gen->start_medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "start_medium out of range");
+    // emitter table: triangles flagged VRLB_SURF_EMITTER, area cdf
+    std::vector<int32_t> etris; std::vector<float> ecdf; double area = 0.0;
+    if (!gen->use_laser) {
+        for (size_t i = 0; i < ctx->host_tris.size(); ++i) {
+            const DTri &t = ctx->host_tris[i];
+            if (!(t.flags & VRLB_SURF_EMITTER)) continue;
+            double cx = (double) t.e1[1] * t.e2[2] - (double) t.e1[2] * t.e2[1], cy = (double) t.e1[2] * t.e2[0] - (double) t.e1[0] * t.e2[2],
+                   cz = (double) t.e1[0] * t.e2[1] - (double) t.e1[1] * t.e2[0];
+            area += 0.5 * std::sqrt(cx * cx + cy * cy + cz * cz);
+            etris.push_back((int32_t) i); ecdf.push_back((float) area);
+        }
+        if (etris.empty()) return fail(ctx, VRLB_ERR_INVALID, "no emitter: the scene has no VRLB_SURF_EMITTER triangle and use_laser is 0");
+    }
+    DevBuf<int32_t> d_etris; DevBuf<float> d_ecdf; DevBuf<uint32_t> d_counts; DevBuf<uint64_t> d_offsets;
+    if (!etris.empty()) {
+        CU(ctx, d_etris.reserve(etris.size())); CU(ctx, d_ecdf.reserve(ecdf.size()));
+        CU(ctx, cudaMemcpy(d_etris.ptr, etris.data(), etris.size() * 4, cudaMemcpyHostToDevice));
+        CU(ctx, cudaMemcpy(d_ecdf.ptr, ecdf.data(), ecdf.size() * 4, cudaMemcpyHostToDevice));
+    }
+    GenParams p{};
+    p.scene = ctx->scene; p.base_seed = gen->seed;
+    p.max_depth = gen->max_depth > 0 ? gen->max_depth : 512; p.rr_depth = gen->rr_depth; p.max_steps = gen->max_steps > 0 ? gen->max_steps : 100000;
+    p.use_non_linear = gen->use_non_linear; p.use_laser = gen->use_laser; p.start_medium = gen->start_medium;
+    p.max_per_particle = 4096; p.min_vrl_length = gen->min_vrl_length;
+    for (int k = 0; k < 3; ++k) { p.laser_o[k] = gen->laser_origin[k]; p.laser_d[k] = gen->laser_direction[k]; p.laser_power[k] = gen->laser_power[k]; }
+    p.emit_tris = d_etris.ptr; p.emit_cdf = d_ecdf.ptr; p.n_emit_tris = (int32_t) etris.size(); p.emit_area = (float) area;
+
+    const uint64_t target = gen->target_vrls;
+    uint64_t have = 0, particles = 0;
+    uint64_t wave = std::min<uint64_t>(std::max<uint64_t>(target / 4, 4096), 1u << 22);
+    std::vector<uint32_t> counts; std::vector<uint64_t> offsets;
+    bool done = false;
+    for (int iter = 0; iter < 64 && !done; ++iter) {
+        if (ctx->cancel.exchange(0)) return fail(ctx, VRLB_ERR_CANCELLED, "cancelled");
+        CU(ctx, d_counts.reserve(wave)); CU(ctx, d_offsets.reserve(wave + 1));
+        p.n_particles = wave; p.first_particle = particles; p.counts = d_counts.ptr;
+        CU(ctx, launch_generate(p, false, ctx->stream)); ctx->launches += 1;
+        counts.resize(wave);
+        CU(ctx, cudaMemcpyAsync(counts.data(), d_counts.ptr, wave * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        offsets.assign(wave + 1, 0);
+        uint64_t used = wave;
+        for (uint64_t i = 0; i < wave; ++i) {
+            offsets[i + 1] = offsets[i] + counts[i];
+            if (have + offsets[i + 1] >= target) { used = i + 1; done = true; break; }       // the particle that fills the map is the last one
+        }
+        const uint64_t add = offsets[used];
+        if (add) {
+            // grow the record buffer, keeping what earlier waves wrote
+            if (have + add > ctx->vrls.cap) {
+                DevBuf<DVrl> bigger; CU(ctx, bigger.reserve(std::max<uint64_t>(have + add, target + target / 8 + 4096)));
+                if (have) CU(ctx, cudaMemcpy(bigger.ptr, ctx->vrls.ptr, have * sizeof(DVrl), cudaMemcpyDeviceToDevice));
+                ctx->vrls.release(); ctx->vrls = bigger;
+            }
+            CU(ctx, cudaMemcpyAsync(d_offsets.ptr, offsets.data(), (used + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+            p.n_particles = used; p.offsets = d_offsets.ptr; p.out = ctx->vrls.ptr + have;
+            CU(ctx, launch_generate(p, true, ctx->stream)); ctx->launches += 1;
+            CU(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+        have += add; particles += used;
+        if (!done) {
+            if (have == 0 && iter >= 3) break;                                  // nothing scatters: give up below
+            double per = have ? (double) have / (double) particles : 0.05;
+            wave = (uint64_t) std::min<double>(std::max<double>(1.2 * (double) (target - have) / per, 1024.0), (double) (1u << 22));
+        }
+    }
+    d_etris.release(); d_ecdf.release(); d_counts.release(); d_offsets.release();
+    if (have == 0) return fail(ctx, VRLB_ERR_STATE, "light tracing produced no VRL (no particle reached a medium)");
+    ctx->n_vrls = have; ctx->vrl_first = 0; ctx->vrl_total = have; ctx->vrl_scale = 1.0f / (float) particles;   // vrl.cpp:404,423
+    ctx->fast_dirty = true;
+    if (n_vrls_out) *n_vrls_out = have;
+    if (n_particles_out) *n_particles_out = particles;
     return VRLB_OK;
 }
 

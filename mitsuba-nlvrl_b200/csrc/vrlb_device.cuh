@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/vrl_b200.h"
+
 namespace vrlb {
 
 // ------------------------------------------------------------------------------------------------
@@ -102,6 +104,12 @@ struct DMedium {         // what the gather needs of a medium (homogeneous / non
     int32_t phase;
     int32_t kind;
     int32_t pad;
+    // graded refractive index (VRLB_MEDIUM_NONLINEAR, nonlinear.cpp:129-153 method 0): n(y) = lerp(bottom, top, (y - y0) / height)
+    float nl_lo[3], nl_hi[3];
+    float ior_bottom, ior_top;
+    float nl_step;       // eikonal step length = height / res_y (one IOR layer of the reference's cell grid)
+    float albedo[3];
+    float pad2[2];
 };
 struct DVrl {            // 48 B record: three 16-byte rows, staged tile-wise into shared memory by TMA
     float ox, oy, oz, length;
@@ -271,6 +279,13 @@ __device__ inline bool any_hit(const DScene &s, V3 o, V3 d, float mint, float ma
         if (!inside && traverse_any_hit(s, sh.root, o, d, inv, mint, maxt)) return true;
     }
     return false;
+}
+
+__device__ inline V3 tri_normal(const DTri &t) {
+    return normalize(cross(V3(t.e1[0], t.e1[1], t.e1[2]), V3(t.e2[0], t.e2[1], t.e2[2])));
+}
+__device__ inline int target_medium(const DTri &t, V3 d) {      // interaction.h:186-200
+    return dot(d, tri_normal(t)) > 0.f ? VRLB_SURF_GET_EXTERIOR(t.flags) : VRLB_SURF_GET_INTERIOR(t.flags);
 }
 
 // Medium::evalTransmittance homogeneous branch (include/mitsuba/render/medium.h:112-117)

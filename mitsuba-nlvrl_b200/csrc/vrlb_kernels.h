@@ -52,6 +52,24 @@ cudaError_t launch_film_xyzaw(const float *film_rgb, const float *film_aw, float
 cudaError_t launch_pack_vrls(const float *soa10, const uint16_t *medium, uint64_t n, DVrl *out, cudaStream_t stream);
 cudaError_t launch_unpack_vrls(const DVrl *in, uint64_t n, float *soa10, uint16_t *medium, cudaStream_t stream);
 
+// VRL generation by light tracing (generate.cu)
+struct GenParams {
+    DScene    scene;
+    uint64_t  n_particles, first_particle, base_seed;
+    int32_t   max_depth, rr_depth, max_steps, use_non_linear, use_laser, start_medium;
+    uint32_t  max_per_particle;
+    float     min_vrl_length;
+    float     laser_o[3], laser_d[3], laser_power[3];
+    const int32_t *emit_tris;     // device: indices (BVH order) of emitter triangles
+    const float   *emit_cdf;      // device: inclusive area cdf over emit_tris
+    int32_t   n_emit_tris;
+    float     emit_area;
+    uint32_t *counts;             // device, per particle (count pass)
+    const uint64_t *offsets;      // device, n_particles + 1 (write pass)
+    DVrl     *out;                // device, VRL records
+};
+cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream);
+
 // FFMA-saturating microkernel (peak.cu)
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int iters, cudaStream_t stream);
 

@@ -205,6 +205,27 @@ def default_options(**kw):
     return o
 
 
+def generate_desc(target_vrls, seed=0, max_depth=512, rr_depth=5, min_vrl_length=5.0, use_non_linear=1, laser=None,
+                  start_medium=-1, max_steps=0):
+    """vrlb_generate_desc from the integrator properties of vrl.cpp:33-73; laser = (origin, direction, power) or None."""
+    g = abi.GenerateDesc()
+    g.target_vrls, g.seed, g.max_depth, g.rr_depth = target_vrls, seed, max_depth, rr_depth
+    g.min_vrl_length, g.use_non_linear, g.start_medium, g.max_steps = min_vrl_length, use_non_linear, start_medium, max_steps
+    if laser is not None:
+        g.use_laser = 1
+        g.laser_origin[:], g.laser_direction[:], g.laser_power[:] = list(laser[0]), list(laser[1]), list(laser[2])
+    return g
+
+
+def make_nonlinear_medium(lo, hi, res_y, bottom_ior=1.0, top_ior=0.95, **kw):
+    """`nonlinear` medium (src/media/nonlinear.cpp:40-60): homogeneous coefficients + IOR linear in height over [lo, hi]."""
+    m = make_medium(kind=abi.MEDIUM_NONLINEAR, **kw)
+    m.nl_bbox_min[:], m.nl_bbox_max[:] = list(lo), list(hi)
+    m.nl_res[:] = [1, res_y, 1]
+    m.bottom_ior, m.top_ior, m.ior_method, m.from_bottom = bottom_ior, top_ior, 0, 1
+    return m
+
+
 # --------------------------------------------------------------------------- the synthetic "box-fog" scene (SURVEY 8d)
 BOX = 10.0
 

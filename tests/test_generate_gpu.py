@@ -1,0 +1,138 @@
+"""VRL generation on the device (vrlb_vrls_generate, generate.cu).  The north star replaces the reference's
+cell-refraction light tracer by an eikonal marcher, so generation is checked statistically:
+free-flight statistics and energy in a homogeneous medium, Snell's invariant along marched paths in a graded-IOR
+medium, cosine emission from area emitters, determinism."""
+import numpy as np
+import pytest
+
+from mitsuba_nlvrl_b200 import abi, api, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = api.Context(0)
+    yield c
+    c.close()
+
+
+def _fog(size, medium):
+    sc = scenes.Scene()
+    mid = sc.add_medium(medium)
+    sc.add_tris(scenes.box_tris((-size,) * 3, (size,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(mid))
+    return sc
+
+
+def test_homogeneous_free_flight_statistics(ctx):
+    sigma_t, albedo = 1.0, 0.8
+    sc = _fog(200.0, scenes.make_medium(sigma_t=(sigma_t,) * 3, albedo=(albedo,) * 3))
+    ctx.set_scene(sc)
+    gen = scenes.generate_desc(40000, seed=11, max_depth=100000, rr_depth=5, laser=((0, 0, 0), (0, 0, 1), (2.0, 1.0, 0.5)), start_medium=0)
+    n, particles = ctx.generate_vrls(gen)
+    assert 40000 <= n < 40000 + 4096 and ctx.vrls_scale() == pytest.approx(1.0 / particles)
+    soa, med = ctx.download_vrls()
+    depth = ctx.download_vrl_depths()
+    length = soa[6].astype(np.float64)
+    # every flight in an unbounded homogeneous medium is Exp(sigma_t): mean 1/sigma_t, variance 1/sigma_t^2
+    assert length.mean() == pytest.approx(1 / sigma_t, abs=5 / np.sqrt(n))
+    assert length.var() == pytest.approx(1 / sigma_t ** 2, rel=0.08)
+    # energy: E[sum of VRL flux per particle] = power * sum_k albedo^k = power / (1 - albedo) (Russian roulette after
+    # rr_depth is unbiased); below the roulette depth the flux of a depth-k VRL is exactly power * albedo^k
+    assert soa[7].astype(np.float64).sum() / particles == pytest.approx(2.0 / (1 - albedo), rel=0.05)
+    early = depth <= 5
+    assert np.allclose(soa[7, early], 2.0 * albedo ** depth[early], rtol=1e-4) and np.allclose(soa[9, early], 0.5 * albedo ** depth[early], rtol=1e-4)
+    assert np.allclose(np.linalg.norm(soa[3:6], axis=0), 1.0, atol=1e-5)
+    first = depth == 0
+    assert first.sum() == particles and np.allclose(soa[3:6, first], np.array([[0], [0], [1]]), atol=1e-6)
+    # isotropic phase: scattered directions have zero mean
+    assert np.abs(soa[3:6, ~first].mean(axis=1)).max() < 0.02
+
+
+def test_generation_is_deterministic_and_seed_dependent(ctx):
+    sc = _fog(50.0, scenes.make_medium(sigma_t=(0.5,) * 3, albedo=(0.7,) * 3, phase=abi.PHASE_HG, g=0.6))
+    ctx.set_scene(sc)
+    gen = scenes.generate_desc(5000, seed=3, laser=((0, 0, -40), (0, 0.1, 1), (1, 1, 1)), start_medium=0)
+    ctx.generate_vrls(gen)
+    a, _ = ctx.download_vrls()
+    a = a.copy()
+    ctx.generate_vrls(gen)
+    b, _ = ctx.download_vrls()
+    assert np.array_equal(a, b)
+    gen.seed = 4
+    ctx.generate_vrls(gen)
+    c, _ = ctx.download_vrls()
+    assert c.shape != a.shape or not np.array_equal(a, c)
+    # HG g = 0.6: mean cosine between consecutive flights of a particle is g; checked through the depth-1 VRLs
+    soa, _ = ctx.download_vrls()
+    depth = ctx.download_vrl_depths()
+    d0 = np.array([0, 0.1, 1.0]) / np.linalg.norm([0, 0.1, 1.0])
+    cos1 = (soa[3:6, depth == 1] * d0[:, None]).sum(0)
+    assert cos1.mean() == pytest.approx(0.6, abs=0.05)
+
+
+def test_eikonal_path_keeps_snell_invariant(ctx):
+    """In n(y) the horizontal optical momentum n * d_x, n * d_z is conserved and the ray bends towards larger n."""
+    lo, hi = (-10.0, -10.0, -10.0), (10.0, 10.0, 10.0)
+    med = scenes.make_nonlinear_medium(lo, hi, res_y=2000, bottom_ior=1.0, top_ior=0.8, sigma_t=(1e-5,) * 3, albedo=(0.9,) * 3)
+    sc = _fog(10.0, med)
+    ctx.set_scene(sc)
+    d = np.array([1.0, 0.45, 0.2]); d /= np.linalg.norm(d)
+    gen = scenes.generate_desc(40, seed=1, min_vrl_length=0.25, laser=((-9.5, -6.0, 0.0), d, (1, 1, 1)), start_medium=0)
+    n, particles = ctx.generate_vrls(gen)
+    soa, _ = ctx.download_vrls()
+    # the first particle's polyline: consecutive segments until the chain breaks (next particle restarts at the laser)
+    o, dd, ln = soa[0:3].T.astype(np.float64), soa[3:6].T.astype(np.float64), soa[6].astype(np.float64)
+    k = 1
+    while k < n and np.allclose(o[k], o[k - 1] + dd[k - 1] * ln[k - 1], atol=1e-4):
+        k += 1
+    assert k >= 10, "the curved flight must be cut into several VRLs"
+    mid_y = o[:k, 1] + 0.5 * dd[:k, 1] * ln[:k]
+    n_mid = 1.0 + (0.8 - 1.0) * (mid_y + 10.0) / 20.0
+    inv_x, inv_z = n_mid * dd[:k, 0], n_mid * dd[:k, 2]
+    n0 = 1.0 + (0.8 - 1.0) * (-6.0 + 10.0) / 20.0
+    assert np.allclose(inv_x, n0 * d[0], rtol=3e-3) and np.allclose(inv_z, n0 * d[2], rtol=3e-3)
+    assert np.all(np.diff(dd[:k, 1]) < 0)                  # n decreases upwards: the ray curves back down
+    # with use_non_linear = 0 the same particle flies straight: one VRL from the laser to the far boundary
+    gen.use_non_linear = 0
+    ctx.generate_vrls(gen)
+    soa2, _ = ctx.download_vrls()
+    assert np.allclose(soa2[3:6, 0], d, atol=1e-6) and soa2[6, 0] > 15
+
+
+def test_area_emitter_cosine_emission(ctx):
+    sc = scenes.Scene()
+    mid = sc.add_medium(scenes.make_medium(sigma_t=(0.05,) * 3, albedo=(0.5,) * 3))
+    sc.add_tris(scenes.box_tris((-100,) * 3, (100,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(mid))
+    e = sc.add_emitter((3.0, 2.0, 1.0))
+    quad = np.array([[[-1, -1, 0], [1, -1, 0], [1, 1, 0]], [[-1, -1, 0], [1, 1, 0], [-1, 1, 0]]], np.float32)   # normal +z, area 4
+    sc.add_tris(quad, abi.SURF_BSDF_SMOOTH | abi.SURF_EMITTER | abi.surf_emitter_id(e))
+    ctx.set_scene(sc)
+    gen = scenes.generate_desc(20000, seed=5, start_medium=0)
+    n, particles = ctx.generate_vrls(gen)
+    soa, _ = ctx.download_vrls()
+    depth = ctx.download_vrl_depths()
+    f = depth == 0
+    assert soa[5, f].mean() == pytest.approx(2.0 / 3.0, abs=0.01)          # E[cos] of a cosine lobe
+    assert np.all(np.abs(soa[0, f]) <= 1.001) and np.all(np.abs(soa[1, f]) <= 1.001)
+    assert np.allclose(soa[7, f], 3.0 * np.pi * 4.0 * np.pi, rtol=1e-5)     # Le * pi * area * pi (vrl.cpp:151-152)
+
+
+def test_generated_set_feeds_the_gather(ctx):
+    sc = scenes.box_fog_scene(occluders=True)
+    ctx.set_scene(sc)
+    gen = scenes.generate_desc(3000, seed=2, laser=((0, 9.5, 0), (0.1, -1, 0.05), (50, 50, 50)), start_medium=0)
+    n, particles = ctx.generate_vrls(gen)
+    cam = scenes.box_fog_camera(32, 18)
+    opt = scenes.default_options()
+    ctx.build_segments(cam, opt)
+    ctx.gather(opt)
+    rgb = ctx.film_rgb(32, 18)
+    assert np.isfinite(rgb).all() and rgb.max() > 0
+    # the same exported set through upload gives the same image (export -> import round trip of the parity protocol)
+    soa, med = ctx.download_vrls()
+    soa = np.ascontiguousarray(soa)
+    ctx.upload_vrls(scenes.vrlset_desc(soa, scale=1.0 / particles))
+    ctx.build_segments(cam, opt)
+    ctx.gather(opt)
+    assert np.allclose(ctx.film_rgb(32, 18), rgb, rtol=1e-5, atol=1e-12)
