@@ -49,6 +49,20 @@ __device__ inline void camera_ray(const vrlb_camera &c, float sx, float sy, V3 &
     d = V3(q[0], q[1], q[2]);
 }
 
+// cosine of the turning angle after which a curved camera path starts a new straight part (0.25 degrees)
+constexpr float NL_PART_COS = 0.99999048f;
+// one eikonal step (see generate.cu): v = n dir, v.y += ds * dn/dy inside the IOR box, dir = v / |v|
+__device__ inline V3 nl_bend(const DMedium &m, V3 p, V3 dir, float ds) {
+    float h = m.nl_hi[1] - m.nl_lo[1];
+    float t = fminf(fmaxf((p.y - m.nl_lo[1]) / h, 0.f), 1.f);
+    float n = m.ior_bottom + (m.ior_top - m.ior_bottom) * t;
+    bool in = p.x >= m.nl_lo[0] && p.x <= m.nl_hi[0] && p.y >= m.nl_lo[1] && p.y <= m.nl_hi[1] && p.z >= m.nl_lo[2] && p.z <= m.nl_hi[2];
+    float g = in ? (m.ior_top - m.ior_bottom) / h : 0.f;
+    V3 v = dir * n;
+    v.y = v.y + ds * g;
+    return normalize(v);
+}
+
 __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
     const int bs = p.opt.block_size;
     const uint32_t pixel_count = (uint32_t) (bs * bs);
@@ -98,19 +112,50 @@ __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
                 valid_ray = true;
                 (void) rng.next_f32();             // photon-gather radius jitter, vrl.cpp:527
                 const DMedium &m = s.media[medium];
-                if (on_film) {
-                    unsigned long long slot = atomicAdd(p.counter, 1ull);
-                    if (slot < p.cap) {
-                        vrlb_segment g;
-                        g.o[0] = ro.x; g.o[1] = ro.y; g.o[2] = ro.z; g.maxt = si.t;
-                        g.d[0] = rd.x; g.d[1] = rd.y; g.d[2] = rd.z; g.pixel = film_pixel;
-                        g.weight[0] = throughput.x; g.weight[1] = throughput.y; g.weight[2] = throughput.z;
-                        g.medium = medium; g.rng_state = rng.state; g.sample = (uint32_t) j; g.part = 0;
-                        p.segs[slot] = g;
+                auto emit = [&](V3 po, V3 pd, float pmaxt, V3 weight, uint32_t part) {
+                    if (on_film) {
+                        unsigned long long slot = atomicAdd(p.counter, 1ull);
+                        if (slot < p.cap) {
+                            vrlb_segment g;
+                            g.o[0] = po.x; g.o[1] = po.y; g.o[2] = po.z; g.maxt = pmaxt;
+                            g.d[0] = pd.x; g.d[1] = pd.y; g.d[2] = pd.z; g.pixel = film_pixel;
+                            g.weight[0] = weight.x; g.weight[1] = weight.y; g.weight[2] = weight.z;
+                            g.medium = medium; g.rng_state = rng.state; g.sample = (uint32_t) j; g.part = part;
+                            p.segs[slot] = g;
+                        }
                     }
+                    rng.advance(query_draws);
+                };
+                if (m.kind == VRLB_MEDIUM_NONLINEAR && m.nl_step > 0.f && p.opt.use_non_linear_camera) {
+                    // curved camera path (vrl.cpp:550-629): marched with the eikonal integrator of generate.cu, cut into
+                    // straight parts when the direction has turned by more than NL_PART_COS; one query per part, the
+                    // preceding parts' transmittance carried in the weight (vrl.cpp:619-628)
+                    V3 pstart = ro, pos = ro, dir = rd, dir0 = rd, vrlThroughput = throughput;
+                    float total = 0.f, step_mint = rmint; uint32_t part = 0; bool found = false; Hit hit; hit.tri = -1; hit.t = VRLB_INF; hit.u = hit.v = 0.f;
+                    for (int step = 0; step < 100000; ++step) {
+                        hit = closest_hit(s, pos, dir, step_mint, m.nl_step);
+                        step_mint = 0.f;
+                        if (hit.tri >= 0) { pos = pos + dir * hit.t; found = true; break; }
+                        pos = pos + dir * m.nl_step;
+                        V3 nd = nl_bend(m, pos, dir, m.nl_step);
+                        if (dot(nd, dir0) < NL_PART_COS) {
+                            V3 chord = pos - pstart; float len = norm(chord);
+                            emit(pstart, chord / len, len, vrlThroughput, part++);
+                            vrlThroughput = vrlThroughput * homo_transmittance(m.max_density, len);
+                            total = total + len;
+                            pstart = pos; dir0 = nd;
+                        }
+                        dir = nd;
+                    }
+                    if (!found) { si.tri = -1; break; }
+                    V3 chord = pos - pstart; float len = norm(chord);
+                    if (len > 0.f) { emit(pstart, chord / len, len, vrlThroughput, part++); total = total + len; }
+                    throughput = throughput * homo_transmittance(m.max_density, total);        // vrl.cpp:631
+                    si = hit; rd = dir; needs_intersection = false;
+                } else {
+                    emit(ro, rd, si.t, throughput, 0u);
+                    throughput = throughput * homo_transmittance(m.max_density, si.t);      // vrl.cpp:631
                 }
-                rng.advance(query_draws);
-                throughput = throughput * homo_transmittance(m.max_density, si.t);      // vrl.cpp:631
                 active_surface = true;
             }
             if (active_surface && needs_intersection) si = closest_hit(s, ro, rd, rmint, rmaxt);

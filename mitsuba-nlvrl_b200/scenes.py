@@ -247,6 +247,21 @@ def box_fog_scene(occluders=True, phase=abi.PHASE_ISOTROPIC, g=0.8, sigma_s=0.1,
     return sc
 
 
+def nl_fog_scene(occluders=True, res_y=320, bottom_ior=1.0, top_ior=0.95, sigma_s=0.1, sigma_a=0.01):
+    """box-fog variant V4: the fog is a graded-IOR `nonlinear` medium, IOR(y) = lerp(bottom, top) over the
+    box height in res_y layers (cbox-nonlinear-homo.xml uses 640), so camera paths are curved."""
+    sc = Scene()
+    st = sigma_s + sigma_a
+    e = BOX + 0.01
+    med = sc.add_medium(make_nonlinear_medium((-e,) * 3, (e,) * 3, res_y, bottom_ior, top_ior,
+                                              sigma_t=(st,) * 3, albedo=(sigma_s / st,) * 3))
+    sc.add_tris(box_tris((-e,) * 3, (e,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(med))
+    sc.add_tris(box_tris((-BOX,) * 3, (BOX,) * 3, faces="xXyYZ", inward=True), abi.SURF_BSDF_SMOOTH)
+    if occluders:
+        sc.add_tris(sphere_tris((4.5, -2.0, -1.0), 4.0), abi.SURF_BSDF_SMOOTH)
+    return sc
+
+
 def box_fog_camera(width=1920, height=1080):
     return make_camera(width, height, origin=(0, 0, -40), target=(0, 0, -39), up=(0, 1, 0), fov=36.0, fov_axis="x",
                        near_clip=0.1, far_clip=1000.0)

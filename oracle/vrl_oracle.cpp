@@ -895,6 +895,24 @@ inline void camera_ray(const vrlb_camera &c, float sx, float sy, V3 &o, V3 &d, f
     d = V3(q[0], q[1], q[2]);
 }
 
+/* graded-IOR profile of the `nonlinear` medium (nonlinear.cpp:129-153, method 0) and one eikonal step */
+constexpr float kNlPartCos = 0.99999048f;     /* cos(0.25 deg) */
+inline float nl_step(const vrlb_medium &m) {
+    if (m.kind != VRLB_MEDIUM_NONLINEAR || m.nl_res[1] < 1) return 0.f;
+    return (m.nl_bbox_max[1] - m.nl_bbox_min[1]) / (float) m.nl_res[1];
+}
+inline V3 nl_bend(const vrlb_medium &m, V3 p, V3 dir, float ds) {
+    float h = m.nl_bbox_max[1] - m.nl_bbox_min[1];
+    float t = std::fmin(std::fmax((p.y - m.nl_bbox_min[1]) / h, 0.f), 1.f);
+    float n = m.bottom_ior + (m.top_ior - m.bottom_ior) * t;
+    bool in = p.x >= m.nl_bbox_min[0] && p.x <= m.nl_bbox_max[0] && p.y >= m.nl_bbox_min[1] && p.y <= m.nl_bbox_max[1] &&
+              p.z >= m.nl_bbox_min[2] && p.z <= m.nl_bbox_max[2];
+    float g = in ? (m.top_ior - m.bottom_ior) / h : 0.f;
+    V3 v = dir * n;
+    v.y = v.y + ds * g;
+    return normalize(v);
+}
+
 /* What one camera sample hands to the VRL query */
 struct PartOut { Ray ray; V3 weight; int medium; uint32_t part; };
 
@@ -932,13 +950,47 @@ SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler 
             const vrlb_medium &m = s.media[(size_t) medium];
             /* linear camera ray: a single part [ray.o, si.t] (vrl.cpp:539-540, 595).  Non-linear
              * splitting (vrl.cpp:550-578) is added by trace_nl_parts() when the medium asks for it. */
-            Ray part{ ro, rd, si.t };
             V3 indirect(0.f);
             V3 vrlThroughput = throughput;
-            V3 Li = on_query(PartOut{ part, vrlThroughput, medium, 0u }, sampler);
-            indirect = indirect + Li * vrlThroughput;
-            vrlThroughput = vrlThroughput * homo_transmittance(m, 0.f, part.maxt);   /* vrl.cpp:627 */
-            throughput = throughput * homo_transmittance(m, 0.f, part.maxt);         /* vrl.cpp:631 */
+            if (m.kind == VRLB_MEDIUM_NONLINEAR && nl_step(m) > 0.f && opt.use_non_linear_camera) {
+                /* curved camera path (vrl.cpp:550-629).  The north star replaces the reference's cell-face refraction
+                 * by a fixed-step eikonal marcher (step = one IOR layer); parts are cut when the direction has turned
+                 * by more than kNlPartCos; one query per part with the preceding parts' transmittance (vrl.cpp:619-628) */
+                V3 pstart = ro, pos = ro, dir = rd, dir0 = rd;
+                float total = 0.f, step_mint = rmint, ds = nl_step(m); uint32_t part = 0; bool found = false;
+                Hit hit{ kInf, 0, 0, -1 };
+                for (int step = 0; step < 100000; ++step) {
+                    hit = ray_intersect(s, pos, dir, step_mint, ds);
+                    step_mint = 0.f;
+                    if (hit.valid()) { pos = pos + dir * hit.t; found = true; break; }
+                    pos = pos + dir * ds;
+                    V3 nd = nl_bend(m, pos, dir, ds);
+                    if (dot(nd, dir0) < kNlPartCos) {
+                        V3 chord = pos - pstart; float len = norm(chord);
+                        V3 Li = on_query(PartOut{ Ray{ pstart, chord / len, len }, vrlThroughput, medium, part++ }, sampler);
+                        indirect = indirect + Li * vrlThroughput;
+                        vrlThroughput = vrlThroughput * homo_transmittance(m, 0.f, len);
+                        total = total + len;
+                        pstart = pos; dir0 = nd;
+                    }
+                    dir = nd;
+                }
+                if (!found) { si = Hit{ kInf, 0, 0, -1 }; radiance = radiance + indirect; break; }
+                V3 chord = pos - pstart; float len = norm(chord);
+                if (len > 0.f) {
+                    V3 Li = on_query(PartOut{ Ray{ pstart, chord / len, len }, vrlThroughput, medium, part++ }, sampler);
+                    indirect = indirect + Li * vrlThroughput;
+                    total = total + len;
+                }
+                throughput = throughput * homo_transmittance(m, 0.f, total);             /* vrl.cpp:631 */
+                si = hit; rd = dir; needs_intersection = false;
+            } else {
+                /* linear camera ray: a single part [ray.o, si.t] (vrl.cpp:539-540, 595) */
+                Ray part{ ro, rd, si.t };
+                V3 Li = on_query(PartOut{ part, vrlThroughput, medium, 0u }, sampler);
+                indirect = indirect + Li * vrlThroughput;
+                throughput = throughput * homo_transmittance(m, 0.f, part.maxt);         /* vrl.cpp:631 */
+            }
             radiance = radiance + indirect;
             active_surface = true;
         }

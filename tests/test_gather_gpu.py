@@ -110,3 +110,45 @@ def test_render_end_to_end_matches_oracle(ctx):
     assert rel_err(out[..., :3].astype(np.float64), ref_xyzaw[..., :3].astype(np.float64)).max() <= 2e-4  # fp32-sequential oracle film
     t = ctx.timing()
     assert t["n_evals"] == ev and t["gather_launches"] == 1
+
+
+@pytest.mark.parametrize("math_mode", [0, 1])
+def test_nonlinear_camera_parts_match_oracle(ctx, math_mode):
+    """Graded-IOR medium (config 3): curved camera paths are marched with the eikonal integrator and split into
+    straight parts, one query per part with the preceding parts' transmittance in the weight (vrl.cpp:550-629)."""
+    sc = scenes.nl_fog_scene(occluders=True, res_y=160, top_ior=0.8)
+    cam = scenes.box_fog_camera(32, 18)
+    opt = scenes.default_options(visibility=1, math_mode=math_mode)
+    soa = scenes.synthetic_vrls(600, seed=12)
+    vd = scenes.vrlset_desc(soa)
+    osc = oracle.OracleScene(sc)
+    ref_segs, ref_direct, ref_aw = osc.build_segments(cam, opt, soa.shape[1], cap=32 * 18 * 200)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(vd)
+    n = ctx.build_segments(cam, opt)
+    assert n == len(ref_segs) and n > 3 * 32 * 18, "camera paths must split into several parts"
+    segs = ctx.download_segments()
+    key = lambda s: np.lexsort((s["part"], s["sample"], s["pixel"]))
+    a, b = segs[key(segs)], ref_segs[key(ref_segs)]
+    for f in ("pixel", "sample", "part", "medium", "rng_state", "o", "d", "maxt"):
+        assert np.array_equal(a[f], b[f]), f                 # same IEEE operation order: bit-exact parts
+    assert np.allclose(a["weight"], b["weight"], rtol=2e-6, atol=0)   # products of exp(): CUDA expf vs glibc differ by ulps
+    li = ctx.gather_segments(opt).astype(np.float64)
+    o32, o64, ev = osc.gather(vd, segs, opt)
+    # the north-star tolerance is per PIXEL: sum over the parts of weight * Li.  (A part can be arbitrarily short --
+    # the piece between the last cut and the surface -- and then theta_B - theta_A of the equi-angular pdf cancels, so
+    # single parts are only held to a loose bound; they carry a negligible share of their pixel.)
+    got, ref = np.zeros((32 * 18, 3)), np.zeros((32 * 18, 3))
+    np.add.at(got, segs["pixel"], li * segs["weight"])
+    np.add.at(ref, segs["pixel"], o64 * segs["weight"])
+    assert rel_err(got, ref).max() <= REL_TOL
+    assert rel_err(li, o64).max() <= 2e-2 and np.quantile(rel_err(li, o64), 0.99) <= REL_TOL
+    # straight rays when the option is off (vrl.cpp:550 m_useNonLinearCameraRays)
+    opt.use_non_linear_camera = 0
+    assert ctx.build_segments(cam, opt) == 32 * 18
+    # whole frame
+    opt.use_non_linear_camera = 1
+    out = ctx.render(cam, opt, vd)
+    ref_xyzaw, _, _ = osc.render(cam, opt, vd)
+    assert np.array_equal(out[..., 3:], ref_xyzaw[..., 3:])
+    assert rel_err(out[..., :3].astype(np.float64), ref_xyzaw[..., :3].astype(np.float64)).max() <= 2e-4
