@@ -224,8 +224,15 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def note(msg):
+        if rank == 0:
+            print(f"[bench {time.strftime('%H:%M:%S')}] {msg}", file=sys.stderr, flush=True)
+
+    note(f"scene + {hi - lo} VRLs resident; warm-up")
     for _ in range(args.warmup):
         n_segs = step()
+        ctx.synchronize()
+        note(f"warm-up step done: gather {ctx.timing()['ms_gather']:.1f} ms")
     barrier()
     fp32_peak = ctx.measure_fp32_peak()
     l0 = ctx.timing()["launches_lifetime"]
@@ -241,6 +248,7 @@ def run_ours(args):
         gather_ms.append(ctx.timing()["ms_gather"])
     e1.record(stream)
     barrier()
+    note("timed steps done")
     clk = clocks.stop() if rank == 0 else None
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
     if world > 1:
@@ -269,6 +277,7 @@ def run_ours(args):
 
     # ---- secondary figure: the same frame without occluders (variant V1: visibility == medium transmittance), the
     #      pure sample+shade rate of the gather kernel that the FP32-issue roofline describes -------------------
+    note("e2e done")
     secondary = None
     if not args.no_occluders and not args.no_secondary:
         sc1 = scenes.box_fog_scene(occluders=False)
@@ -287,6 +296,7 @@ def run_ours(args):
                      "fp32_tflops": ev1 * FLOPS_PER_EVAL / (g1 * 1e-3) * 1e-12,
                      "frac_of_fp32_peak": ev1 * FLOPS_PER_EVAL / (g1 * 1e-3) * 1e-12 / fp32_peak if fp32_peak else None}
 
+    note("secondary done")
     if rank == 0:
         g_ms = float(np.mean(gather_ms))
         shard_evals = n_segs * (hi - lo) * opt.samples_per_query
@@ -321,6 +331,9 @@ def run_ours(args):
 
 
 def main():
+    import faulthandler
+    import signal
+    faulthandler.register(signal.SIGUSR1, all_threads=True)       # `kill -USR1 <pid>` dumps the Python stacks to stderr
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -30,7 +30,7 @@ struct Kahan3 {
     }
 };
 
-template <bool UNIFORM, bool RR, bool VIS>
+template <bool UNIFORM, bool RR, bool VIS, bool GRID>
 __global__ void __launch_bounds__(GATHER_THREADS)
 gather_kernel(GatherParams p) {
     __shared__ alignas(128) DVrl tile[2][TILE];
@@ -96,6 +96,7 @@ gather_kernel(GatherParams p) {
                 float vlen = a.w;
                 const DMedium &m = media[__float_as_uint(b.w)];
                 float rrWeight = 1.f; bool survive = true;
+                const uint64_t eval_state = rng.state;      // keys the grid-medium sub-stream
                 if (RR) {
                     // EDistanceRoulette, vrl_map.h:171-190
                     float cc, cv;
@@ -107,12 +108,21 @@ gather_kernel(GatherParams p) {
                 }
                 float u1 = rng.next_f32(), u2 = rng.next_f32();
                 if (!survive) continue;
-                float f = eval_contrib<UNIFORM, VIS>(p.scene, ray, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2);
+                float st2 = 0.f;
+                float f = eval_contrib<UNIFORM, VIS, GRID>(p.scene, ray, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2,
+                                                           &m, eval_state, &st2);
                 if (RR) f = f / rrWeight;
                 // flux * f * sigma_s(cam) * sigma_s(vrl) * m_scale (vrl_struct.h:652-659, vrl_map.h:160)
-                float cr = c.x * f * m.sigma_s[0] * m.sigma_s[0] * p.scale;
-                float cg = c.y * f * m.sigma_s[1] * m.sigma_s[1] * p.scale;
-                float cb = c.z * f * m.sigma_s[2] * m.sigma_s[2] * p.scale;
+                float cr, cg, cb;
+                if (GRID && m.kind == VRLB_MEDIUM_GRID) {
+                    cr = c.x * f * (m.albedo[0] * m.albedo[0]) * st2 * p.scale;
+                    cg = c.y * f * (m.albedo[1] * m.albedo[1]) * st2 * p.scale;
+                    cb = c.z * f * (m.albedo[2] * m.albedo[2]) * st2 * p.scale;
+                } else {
+                    cr = c.x * f * m.sigma_s[0] * m.sigma_s[0] * p.scale;
+                    cg = c.y * f * m.sigma_s[1] * m.sigma_s[1] * p.scale;
+                    cb = c.z * f * m.sigma_s[2] * m.sigma_s[2] * p.scale;
+                }
                 // NaN / Inf rejection, vrl_map.h:162
                 if (isfinite(cr) && isfinite(cg) && isfinite(cb)) { acc.add(0, cr); acc.add(1, cg); acc.add(2, cb); }
             }
@@ -136,26 +146,30 @@ gather_kernel(GatherParams p) {
     }
 }
 
-template <bool U, bool R, bool V>
+template <bool U, bool R, bool V, bool G>
 static cudaError_t launch_t(const GatherParams &p, cudaStream_t stream) {
     uint32_t grid = (uint32_t) ((p.n_segs + GATHER_THREADS - 1) / GATHER_THREADS);
     if (grid == 0 || p.n_vrls == 0) return cudaSuccess;
-    gather_kernel<U, R, V><<<grid, GATHER_THREADS, 0, stream>>>(p);
+    gather_kernel<U, R, V, G><<<grid, GATHER_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
 }
-
-cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis, cudaStream_t stream) {
+template <bool G>
+static cudaError_t launch_g(const GatherParams &p, bool uniform, bool rr, bool vis, cudaStream_t stream) {
     int key = (uniform ? 4 : 0) | (rr ? 2 : 0) | (vis ? 1 : 0);
     switch (key) {
-        case 0: return launch_t<false, false, false>(p, stream);
-        case 1: return launch_t<false, false, true>(p, stream);
-        case 2: return launch_t<false, true, false>(p, stream);
-        case 3: return launch_t<false, true, true>(p, stream);
-        case 4: return launch_t<true, false, false>(p, stream);
-        case 5: return launch_t<true, false, true>(p, stream);
-        case 6: return launch_t<true, true, false>(p, stream);
-        default: return launch_t<true, true, true>(p, stream);
+        case 0: return launch_t<false, false, false, G>(p, stream);
+        case 1: return launch_t<false, false, true, G>(p, stream);
+        case 2: return launch_t<false, true, false, G>(p, stream);
+        case 3: return launch_t<false, true, true, G>(p, stream);
+        case 4: return launch_t<true, false, false, G>(p, stream);
+        case 5: return launch_t<true, false, true, G>(p, stream);
+        case 6: return launch_t<true, true, false, G>(p, stream);
+        default: return launch_t<true, true, true, G>(p, stream);
     }
+}
+
+cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis, bool grid, cudaStream_t stream) {
+    return grid ? launch_g<true>(p, uniform, rr, vis, stream) : launch_g<false>(p, uniform, rr, vis, stream);
 }
 
 }  // namespace vrlb

@@ -44,9 +44,12 @@ struct SegRegs { V3 o, d; float maxt; };
 
 // ---- VRL::getContrib (vrl_struct.h:584-662) with samplingVRL (239-360) inlined.  Returns the scalar
 //      factor that multiplies flux * sigma_s(cam) * sigma_s(vrl); 0 when the reference returns 0. ----
-template <bool UNIFORM, bool VIS>
+//      GRID: the VRL's medium may be a grid medium; then `sub_seed` keys the eval's transmittance sub-stream and
+//      `st2` receives sigma_t(pCam) * sigma_t(pVRL) (the caller multiplies albedo^2; heterogeneous.cpp:43-51). ----
+template <bool UNIFORM, bool VIS, bool GRID = false>
 __device__ inline float eval_contrib(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
-                                     float max_density, int phase, float g, float u1, float u2) {
+                                     float max_density, int phase, float g, float u1, float u2,
+                                     const DMedium *gm = nullptr, uint64_t sub_seed = 0, float *st2 = nullptr) {
     V3 pCam, pVRL; float tCam, tVRL, invPDF;
     if (UNIFORM) {
         // VRL::sampleMC, vrl_struct.h:239-243 (single-part NLRay::at, :44-56)
@@ -102,19 +105,30 @@ __device__ inline float eval_contrib(const DScene &scene, const SegRegs &ray, V3
     float vrlPF = phase_eval(phase, g, -vd, -dir);
     if (vrlPF == 0) return 0.f;
     // VRL::evalTransmittance pCam -> pVRL, vrl_struct.h:509-572
-    float vrlToRayTrans;
-    {
-        V3 dd = pVRL - pCam;
-        float remaining = norm(dd);
-        dd = normalize(dd);
-        if (VIS && remaining > 0 && any_hit(scene, pCam, dd, 0.f, remaining)) return 0.f;
+    float vrlToRayTrans, rayTrans, vrlTrans;
+    V3 dd = pVRL - pCam;
+    float remaining = norm(dd);
+    dd = normalize(dd);
+    if (VIS && remaining > 0 && any_hit(scene, pCam, dd, 0.f, remaining)) return 0.f;
+    if (GRID && gm->kind == VRLB_MEDIUM_GRID) {
+        // get_scattering_coefficients at both points (vrl_struct.h:616, 624), then the three stochastic
+        // transmittances in the reference's call order (:632, :641, :647) on the eval's sub-stream
+        *st2 = (gm->scale * grid_eval(*gm, pCam)) * (gm->scale * grid_eval(*gm, pVRL));
+        Pcg32s sub; sub.seed(sub_seed, PCG32_DEFAULT_STREAM + 1u);
+        vrlToRayTrans = remaining > 0 ? grid_transmittance(*gm, pCam, dd, remaining, sub) : 1.0f;
+        if (vrlToRayTrans == 0.0f) return 0.f;
+        rayTrans = grid_transmittance(*gm, ray.o, ray.d, tCam, sub);
+        if (rayTrans == 0.0f) return 0.f;
+        vrlTrans = grid_transmittance(*gm, vo, vd, tVRL, sub);
+        if (vrlTrans == 0.0f) return 0.f;
+    } else {
         vrlToRayTrans = remaining > 0 ? homo_transmittance(max_density, remaining) : 1.0f;
+        if (vrlToRayTrans == 0.0f) return 0.f;
+        rayTrans = homo_transmittance(max_density, tCam);
+        if (rayTrans == 0.0f) return 0.f;
+        vrlTrans = homo_transmittance(max_density, tVRL);
+        if (vrlTrans == 0.0f) return 0.f;
     }
-    if (vrlToRayTrans == 0.0f) return 0.f;
-    float rayTrans = homo_transmittance(max_density, tCam);
-    if (rayTrans == 0.0f) return 0.f;
-    float vrlTrans = homo_transmittance(max_density, tVRL);
-    if (vrlTrans == 0.0f) return 0.f;
     float fallOff = 1.0f / (lengthPtoP * lengthPtoP);
     return fallOff * vrlPF * rayPF * vrlTrans * rayTrans * vrlToRayTrans * invPDF;
 }

@@ -396,14 +396,18 @@ __device__ __forceinline__ void process_leaves(const DScene &s, WarpQueue &q, in
     }
 }
 
-__device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int cnt) {
+__device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int cnt, uint32_t *wd) {
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
     int head = 0, slot = 0, lqn = 0;
     bool active = false;
     RayState r;
     uint32_t stack[24];
     r.sp = 0; r.cur = 0; r.roots = 0; r.dist = 0.f;
-    while (true) {
+    for (uint32_t steps = 0; ; ++steps) {
+        if (steps > (1u << 22)) {                                  // watchdog: a batch takes a few hundred steps
+            if (wd && atomicCAS(wd, 0u, 2u) == 0u) { wd[1] = blockIdx.x; wd[2] = threadIdx.x; wd[3] = (uint32_t) cnt; wd[4] = (uint32_t) head; wd[5] = r.cur; wd[6] = (uint32_t) r.sp; __threadfence_system(); }
+            __trap();
+        }
         // (1) leaf work: a full warp's worth pending
         while (lqn >= 32) {
             lqn -= 32;
@@ -497,6 +501,31 @@ __device__ __noinline__ float exact_eval_vis(const DScene &scene, const SegRegs 
     return eval_contrib<UNIFORM, true>(scene, ray, vo, vd, vlen, max_density, phase, g, u1, u2);
 }
 
+// Watchdog for the ring: a wait that outlasts ~2 s (a tile takes ~0.1 ms) writes the CTA's ring state to pinned host
+// memory and traps, so that a lost hand-over surfaces as an error with evidence instead of a silent hang.
+__device__ __noinline__ void ring_watchdog_trip(uint32_t *wd, uint32_t code, uint32_t it, uint32_t buf,
+                                                const uint32_t *warp_it, const uint64_t *bars) {
+    if (wd && atomicCAS(wd, 0u, code) == 0u) {
+        wd[1] = blockIdx.x; wd[2] = threadIdx.x; wd[3] = it; wd[4] = buf;
+        for (int b = 0; b < 8; ++b) { wd[5 + 2 * b] = (uint32_t) bars[b]; wd[6 + 2 * b] = (uint32_t) (bars[b] >> 32); }   // full[0..3], empty[0..3]
+        for (int w = 0; w < 8; ++w) wd[21 + w] = warp_it[w];
+        __threadfence_system();
+    }
+    __trap();
+}
+__device__ __forceinline__ void mbar_wait_wd(uint64_t *bar, uint32_t parity, uint32_t *wd, uint32_t code, uint32_t it, uint32_t buf,
+                                             const uint32_t *warp_it, const uint64_t *bars) {
+    uint32_t ok = 0;
+    long long t0 = 0;
+    for (uint32_t spins = 0; ; ++spins) {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) return;
+        if (spins == 64) t0 = clock64();
+        else if (spins > 64 && (spins & 1023u) == 0 && clock64() - t0 > 4000000000LL) ring_watchdog_trip(wd, code, it, buf, warp_it, bars);
+    }
+}
+
 // ---- kernel with visibility: phases A (shade NB VRLs) / B (trace the queue) / C (accumulate) per warp ----
 template <bool UNIFORM, bool RR, bool ISO, bool GUARD>
 __global__ void __launch_bounds__(GATHER_THREADS)
@@ -504,8 +533,9 @@ gather_fast_vis_kernel(GatherParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     DVrl (*tile)[VTILE] = reinterpret_cast<DVrl (*)[VTILE]>(smem_raw);                              // [NBUF][VTILE]
     WarpQueue *queues = reinterpret_cast<WarpQueue *>(smem_raw + NBUF * VTILE * sizeof(DVrl));      // [warps]
-    __shared__ alignas(8) uint64_t full_bar[NBUF];
-    __shared__ int done_cnt[NBUF];                 // warps that have finished the tile in each ring slot
+    __shared__ alignas(8) uint64_t ring_bar[2 * NBUF];  // [0, NBUF): "full" (TMA complete_tx); [NBUF, 2 NBUF): "empty" (one arrive per warp)
+    uint64_t *full_bar = ring_bar, *empty_bar = ring_bar + NBUF;
+    __shared__ uint32_t warp_it[GATHER_THREADS / 32];   // watchdog evidence: the tile each warp is on
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, lt = (1u << lane) - 1u;
     WarpQueue &q = queues[tid >> 5];
@@ -533,7 +563,7 @@ gather_fast_vis_kernel(GatherParams p) {
     constexpr uint32_t DPE = RR ? 3u : 2u;
 
     if (tid == 0) {
-        for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); done_cnt[b] = 0; }
+        for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], GATHER_THREADS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -560,7 +590,15 @@ gather_fast_vis_kernel(GatherParams p) {
             rng.state = rng0;
             rng.advance(((uint64_t) s * p.total + p.first_index) * DPE);
         }
-        mbar_wait(&full_bar[buf], (it / NBUF) & 1u);
+        if (lane == 0) warp_it[tid >> 5] = it;
+        // producer (thread 0): tile it + 2 goes into the slot that tile it - 2 vacated, once every warp has released it.
+        // Warps may drift up to 2 tiles apart in either direction of warp 0 without anyone waiting.
+        if (tid == 0 && it >= 2 && it + 2 < total_tiles) {
+            mbar_wait_wd(&empty_bar[(it - 2) % NBUF], ((it - 2) / NBUF) & 1u, p.wd, 3u, it, (it - 2) % NBUF, warp_it, ring_bar);
+            issue(it + 2);
+        }
+        __syncwarp();
+        mbar_wait_wd(&full_bar[buf], (it / NBUF) & 1u, p.wd, 1u, it, buf, warp_it, ring_bar);
         const uint32_t cnt = (uint32_t) min((uint64_t) VTILE, p.n_vrls - (uint64_t) t * VTILE);
         float pr = 0.f, pg = 0.f, pb = 0.f;
         for (uint32_t jb = 0; jb < cnt; jb += NB) {
@@ -609,7 +647,7 @@ gather_fast_vis_kernel(GatherParams p) {
             }
             __syncwarp();
             // ---- phase B: persistent-lane traversal of the queue ----
-            trace_queue(p.scene, q, qn);
+            trace_queue(p.scene, q, qn, p.wd);
             __syncwarp();
             // ---- phase C: accumulate in VRL order ----
 #pragma unroll
@@ -648,16 +686,9 @@ gather_fast_vis_kernel(GatherParams p) {
             comp[k] = xsub(xsub(tt, sum[k]), y);
             sum[k] = tt;
         }
-        // ring hand-over without a CTA barrier: the last warp to finish a slot refills it (warps drift up to NBUF - 1 tiles apart)
+        // release the slot (consumer side of the full/empty mbarrier pipeline; no CTA barrier in the loop)
         __syncwarp();
-        if (lane == 0) {
-            __threadfence_block();
-            int old = atomicAdd(&done_cnt[buf], 1);
-            if (old == GATHER_THREADS / 32 - 1) {
-                done_cnt[buf] = 0;
-                if (it + NBUF < total_tiles) issue(it + NBUF);
-            }
-        }
+        if (lane == 0) mbar_arrive(&empty_bar[buf]);
     }
 
     if (live) {

@@ -49,7 +49,7 @@ struct vrlb_context {
     std::atomic<int> cancel{ 0 };
 
     // scene
-    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters;
+    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters; DevBuf<float> grids; bool any_grid = false;
     DScene scene{};
     bool have_scene = false;
     std::vector<vrlb_medium> host_media;
@@ -71,6 +71,7 @@ struct vrlb_context {
 
     // pinned staging for host<->device copies of the e2e path
     void *pinned = nullptr; size_t pinned_cap = 0;
+    uint32_t *wd = nullptr;           // pinned, 32 words: in-kernel watchdog record (gather_fast.cu)
 
     cudaEvent_t ev[8] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
     vrlb_timing timing{};
@@ -88,7 +89,17 @@ int fail(vrlb_context *ctx, int code, const char *fmt, ...) {
     if (ctx) ctx->error = buf; else g_create_error = buf;
     return code;
 }
-#define CU(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, VRLB_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
+// CUDA failure: message + the in-kernel watchdog's record when it is the one that trapped (gather_fast.cu)
+int fail_cuda(vrlb_context *ctx, const char *what, cudaError_t e) {
+    const uint32_t *w = ctx->wd;
+    if (w && w[0]) {
+        char rec[512]; int n = 0;
+        for (int i = 0; i < 25 && n < 480; ++i) n += std::snprintf(rec + n, sizeof(rec) - (size_t) n, "%s%x", i ? " " : "", w[i]);
+        return fail(ctx, VRLB_ERR_CUDA, "%s: %s [gather watchdog code %u: %s]", what, cudaGetErrorString(e), w[0], rec);
+    }
+    return fail(ctx, VRLB_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+#define CU(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(ctx, #call, e_); } while (0)
 
 int ensure_pinned(vrlb_context *ctx, size_t bytes) {
     if (bytes <= ctx->pinned_cap) return VRLB_OK;
@@ -227,10 +238,11 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
             return fail(ctx, VRLB_ERR_INVALID, "triangle %u: BSDF class %u not supported on this path", i, f & VRLB_SURF_BSDF_MASK);
     }
     std::vector<DMedium> dm(sc->n_media);
+    std::vector<float> grid_host; std::vector<std::pair<uint32_t, size_t>> grid_off;
     for (uint32_t i = 0; i < sc->n_media; ++i) {
         const vrlb_medium &m = sc->media[i];
-        if (m.kind != VRLB_MEDIUM_HOMOGENEOUS && m.kind != VRLB_MEDIUM_NONLINEAR)
-            return fail(ctx, VRLB_ERR_INVALID, "medium %u: kind %d is not implemented on the CUDA path yet", i, m.kind);
+        if (m.kind != VRLB_MEDIUM_HOMOGENEOUS && m.kind != VRLB_MEDIUM_NONLINEAR && m.kind != VRLB_MEDIUM_GRID)
+            return fail(ctx, VRLB_ERR_INVALID, "medium %u: unknown kind %d", i, m.kind);
         if (m.phase != VRLB_PHASE_ISOTROPIC && m.phase != VRLB_PHASE_HG) return fail(ctx, VRLB_ERR_INVALID, "medium %u: unknown phase %d", i, m.phase);
         if (m.phase == VRLB_PHASE_HG && !(m.g > -1.f && m.g < 1.f))
             return fail(ctx, VRLB_ERR_INVALID, "The asymmetry parameter must lie in the interval (-1, 1)!");   // hg.cpp:45-46
@@ -238,7 +250,17 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
         float mean = (m.sigma_t[0] + m.sigma_t[1] + m.sigma_t[2]) / 3.0f;      // ConstVolume::max() = mean, constant3d.cpp:37
         d.max_density = m.scale * mean;                                          // homogeneous.cpp:26
         for (int k = 0; k < 3; ++k) d.sigma_s[k] = (m.sigma_t[k] * m.scale) * m.albedo[k];   // homogeneous.cpp:42-50
-        d.g = m.g; d.phase = m.phase; d.kind = m.kind;
+        d.g = m.g; d.phase = m.phase; d.kind = m.kind; d.scale = m.scale;
+        if (m.kind == VRLB_MEDIUM_GRID) {
+            if (!m.grid || m.grid_res[0] < 1 || m.grid_res[1] < 1 || m.grid_res[2] < 1) return fail(ctx, VRLB_ERR_INVALID, "medium %u: grid medium needs grid and grid_res", i);
+            for (int k = 0; k < 3; ++k)
+                if (!(m.grid_bbox_max[k] > m.grid_bbox_min[k])) return fail(ctx, VRLB_ERR_INVALID, "medium %u: empty grid_bbox", i);
+            if (!(m.grid_max > 0.f)) return fail(ctx, VRLB_ERR_INVALID, "medium %u: grid_max (the majorant before scale) must be positive", i);
+            d.max_density = m.scale * m.grid_max;                                // heterogeneous.cpp:29
+            for (int k = 0; k < 3; ++k) { d.sigma_s[k] = 0.f; d.g_res[k] = m.grid_res[k]; d.g_lo[k] = m.grid_bbox_min[k]; d.g_hi[k] = m.grid_bbox_max[k]; }
+            grid_off.push_back({ i, grid_host.size() });
+            grid_host.insert(grid_host.end(), m.grid, m.grid + (size_t) m.grid_res[0] * m.grid_res[1] * m.grid_res[2]);
+        }
         for (int k = 0; k < 3; ++k) { d.albedo[k] = m.albedo[k]; d.nl_lo[k] = m.nl_bbox_min[k]; d.nl_hi[k] = m.nl_bbox_max[k]; }
         d.ior_bottom = m.bottom_ior; d.ior_top = m.top_ior; d.nl_step = 0.f;
         if (m.kind == VRLB_MEDIUM_NONLINEAR) {
@@ -264,6 +286,12 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
         CU(ctx, cudaMemcpy(ctx->stris.ptr, sa.tris.data(), sa.tris.size() * sizeof(DTri), cudaMemcpyHostToDevice));
         CU(ctx, cudaMemcpy(ctx->verts.ptr, sc->tri_verts, (size_t) sc->n_tris * 9 * sizeof(float), cudaMemcpyHostToDevice));
     }
+    if (!grid_host.empty()) {
+        CU(ctx, ctx->grids.reserve(grid_host.size()));
+        CU(ctx, cudaMemcpy(ctx->grids.ptr, grid_host.data(), grid_host.size() * sizeof(float), cudaMemcpyHostToDevice));
+        for (auto &go : grid_off) dm[go.first].grid = ctx->grids.ptr + go.second;
+    }
+    ctx->any_grid = !grid_off.empty();
     CU(ctx, cudaMemcpy(ctx->media.ptr, dm.data(), dm.size() * sizeof(DMedium), cudaMemcpyHostToDevice));
     if (sc->n_emitters) CU(ctx, cudaMemcpy(ctx->emitters.ptr, sc->emitters, (size_t) sc->n_emitters * sizeof(vrlb_emitter), cudaMemcpyHostToDevice));
     ctx->scene.tris = ctx->tris.ptr; ctx->scene.verts = ctx->verts.ptr; ctx->scene.nodes = ctx->nodes.ptr;
@@ -526,8 +554,13 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     p.vrls = ctx->vrls.ptr; p.n_vrls = ctx->n_vrls; p.first_index = ctx->vrl_first; p.total = ctx->vrl_total;
     p.scale = ctx->vrl_scale; p.scale_rr = opt->scale_rr; p.q = (uint32_t) opt->samples_per_query;
     p.film_rgb = ctx->film_rgb.ptr; p.seg_out = seg_out_dev;
+    if (!ctx->wd) { CU(ctx, cudaHostAlloc((void **) &ctx->wd, 32 * sizeof(uint32_t), cudaHostAllocMapped)); std::memset(ctx->wd, 0, 32 * sizeof(uint32_t)); }
+    p.wd = ctx->wd;
     const bool vis = opt->visibility != 0 && ctx->scene.n_tris > 0;
-    if (opt->math_mode != 0 && ctx->fast_dirty && ctx->n_vrls) {
+    // grid media run on the exactly-rounded kernel in every math mode (their stochastic transmittance is a chain of
+    // accept/reject decisions on logf results; a fast variant would flip decisions against the oracle)
+    const bool fast = opt->math_mode != 0 && !ctx->any_grid;
+    if (fast && ctx->fast_dirty && ctx->n_vrls) {
         CU(ctx, ctx->vrls_fast.reserve(ctx->n_vrls));
         CU(ctx, launch_prep_fast_vrls(ctx->vrls.ptr, ctx->n_vrls, ctx->media.ptr, ctx->vrl_scale, ctx->vrls_fast.ptr, ctx->stream));
         ctx->fast_dirty = false; ctx->timing.total_launches += 1; ctx->launches += 1;
@@ -536,7 +569,7 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     p.guard_h = opt->reserved[0] ? (float) opt->reserved[0] * 1e-3f : 0.2f;   // dev knobs (milli-units); 0 = shipped defaults
     p.guard_z = opt->reserved[1] ? (float) opt->reserved[1] : 8.0f;
     cudaEventRecord(ctx->ev[2], ctx->stream);
-    if (opt->math_mode == 0) CU(ctx, launch_gather(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, vis, ctx->stream));
+    if (!fast) CU(ctx, launch_gather(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, vis, ctx->any_grid, ctx->stream));
     else CU(ctx, launch_gather_fast(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, vis, ctx->all_iso, opt->math_mode == 1, ctx->stream));
     cudaEventRecord(ctx->ev[3], ctx->stream);
     bool launched = p.n_segs && p.n_vrls;

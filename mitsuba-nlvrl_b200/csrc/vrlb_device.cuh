@@ -48,7 +48,8 @@ constexpr float kInvFourPi  = 0.07957747154594766788f;
 // PCG32, ext/enoki/include/enoki/random.h:62-119, 265-286.  All pixel streams share the default
 // stream constant (sampler.cpp:93), so `inc` is a compile-time constant.
 constexpr uint64_t PCG32_MULT = 0x5851f42d4c957f2dULL;
-constexpr uint64_t PCG32_INC  = (0xda3e39cb94b95bdbULL << 1) | 1ULL;
+constexpr uint64_t PCG32_DEFAULT_STREAM = 0xda3e39cb94b95bdbULL;
+constexpr uint64_t PCG32_INC  = (PCG32_DEFAULT_STREAM << 1) | 1ULL;
 
 struct Pcg32 {
     uint64_t state;
@@ -72,6 +73,22 @@ struct Pcg32 {
             delta >>= 1;
         }
         state = acc_mult * state + acc_plus;
+    }
+};
+
+// PCG32 on an arbitrary stream (the grid-medium transmittance sub-stream, SURVEY 8d "addressed" mode)
+struct Pcg32s {
+    uint64_t state, inc;
+    __device__ inline uint32_t next_u32() {
+        uint64_t old = state;
+        state        = old * PCG32_MULT + inc;
+        uint32_t xs  = (uint32_t) (((old >> 18) ^ old) >> 27);
+        uint32_t rot = (uint32_t) (old >> 59);
+        return (xs >> rot) | (xs << ((32 - rot) & 31));
+    }
+    __device__ inline float next_f32() { return __uint_as_float((next_u32() >> 9) | 0x3f800000u) - 1.0f; }
+    __device__ inline void seed(uint64_t initstate, uint64_t initseq) {      // enoki/random.h:79-86
+        state = 0; inc = (initseq << 1u) | 1u; next_u32(); state += initstate; next_u32();
     }
 };
 
@@ -109,7 +126,12 @@ struct DMedium {         // what the gather needs of a medium (homogeneous / non
     float ior_bottom, ior_top;
     float nl_step;       // eikonal step length = height / res_y (one IOR layer of the reference's cell grid)
     float albedo[3];
-    float pad2[2];
+    float scale;         // medium `scale`
+    // grid medium (VRLB_MEDIUM_GRID, heterogeneous.cpp + grid3d.cpp): scalar sigma_t grid, x fastest; max_density = scale * grid max
+    const float *grid;   // device copy, one allocation per scene
+    int32_t g_res[3];
+    float   g_lo[3], g_hi[3];
+    float   pad2[2];
 };
 struct DVrl {            // 48 B record: three 16-byte rows, staged tile-wise into shared memory by TMA
     float ox, oy, oz, length;
@@ -292,6 +314,86 @@ __device__ inline int target_medium(const DTri &t, V3 d) {      // interaction.h
 __device__ inline float homo_transmittance(float max_density, float maxt) {
     float val = expf(max_density * (0.f - maxt));
     return max_density != 0.f ? val : 1.0f;
+}
+
+// ---- grid ("heterogeneous") medium ------------------------------------------------------------------
+// GridVolume::eval, 1 channel, trilinear, clamp wrap (src/textures/grid3d.cpp:219-340); no domain test, as there
+__device__ inline float grid_eval(const DMedium &m, V3 p) {
+    float pw[3] = { p.x, p.y, p.z }, w1[3], w0[3];
+    int i0[3], i1[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float l  = __fmul_rn(__fsub_rn(pw[k], m.g_lo[k]), __fdiv_rn(1.0f, __fsub_rn(m.g_hi[k], m.g_lo[k])));
+        float q  = fmaf(l, (float) m.g_res[k], -.5f);
+        float fl = floorf(q);
+        int   i  = (int) fl;
+        w1[k] = __fsub_rn(q, fl); w0[k] = __fsub_rn(1.f, w1[k]);
+        i0[k] = min(max(i, 0), m.g_res[k] - 1);
+        i1[k] = min(max(i + 1, 0), m.g_res[k] - 1);
+    }
+    const float *g = m.grid;
+    const size_t nx = (size_t) m.g_res[0], ny = (size_t) m.g_res[1];
+    const size_t r00 = ((size_t) i0[2] * ny + i0[1]) * nx, r10 = ((size_t) i0[2] * ny + i1[1]) * nx,
+                 r01 = ((size_t) i1[2] * ny + i0[1]) * nx, r11 = ((size_t) i1[2] * ny + i1[1]) * nx;
+    float d000 = __ldg(g + r00 + i0[0]), d100 = __ldg(g + r00 + i1[0]), d010 = __ldg(g + r10 + i0[0]), d110 = __ldg(g + r10 + i1[0]);
+    float d001 = __ldg(g + r01 + i0[0]), d101 = __ldg(g + r01 + i1[0]), d011 = __ldg(g + r11 + i0[0]), d111 = __ldg(g + r11 + i1[0]);
+    float v00 = fmaf(w0[0], d000, __fmul_rn(w1[0], d100)), v01 = fmaf(w0[0], d001, __fmul_rn(w1[0], d101)),
+          v10 = fmaf(w0[0], d010, __fmul_rn(w1[0], d110)), v11 = fmaf(w0[0], d011, __fmul_rn(w1[0], d111));
+    float v0 = fmaf(w0[1], v00, __fmul_rn(w1[1], v10)), v1 = fmaf(w0[1], v01, __fmul_rn(w1[1], v11));
+    return fmaf(w0[2], v0, __fmul_rn(w1[2], v1));
+}
+
+// BoundingBox::ray_intersect, include/mitsuba/core/bbox.h:302-325
+__device__ inline bool bbox_ray_intersect(const float lo[3], const float hi[3], V3 o, V3 d, float &mint, float &maxt) {
+    float oo[3] = { o.x, o.y, o.z }, dd[3] = { d.x, d.y, d.z };
+    bool active = true;
+    float t1p[3], t2p[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        active = active && ((dd[k] != 0.f) || ((oo[k] > lo[k]) || (oo[k] < hi[k])));
+        float rcp = __fdiv_rn(1.0f, dd[k]);
+        float t1 = __fmul_rn(__fsub_rn(lo[k], oo[k]), rcp), t2 = __fmul_rn(__fsub_rn(hi[k], oo[k]), rcp);
+        t1p[k] = fminf(t1, t2); t2p[k] = fmaxf(t1, t2);
+    }
+    mint = fmaxf(t1p[0], fmaxf(t1p[1], t1p[2]));
+    maxt = fminf(t2p[0], fminf(t2p[1], t2p[2]));
+    return active && maxt >= mint;
+}
+
+// Medium::evalTransmittance, non-homogeneous branch (include/mitsuba/render/medium.h:119-154) with
+// Medium::sample_interaction (src/librender/medium.cpp:36-75) and eval_tr_and_pdf (:77-89) inlined: the product of
+// majorant transmittances over the accepted free-flight steps (the grid values do not enter).
+// Draws: 1 channel + one per step, from the eval's sub-stream.
+__device__ inline float grid_transmittance(const DMedium &m, V3 o_, V3 d, float maxt_, Pcg32s &sub) {
+    const float kInfF = __int_as_float(0x7f800000);
+    float t = 0.f, maxt = maxt_;
+    const float majorant = m.max_density;
+    (void) sub.next_u32();                             // channel draw; the majorant is grey
+    float si_t = maxt_;
+    float throughput = 1.0f;
+    V3 ro = o_; float rmint = 0.f, rmaxt = maxt_;
+    while (t < maxt) {
+        float sample = sub.next_f32();
+        float bmin, bmax;
+        bool active = bbox_ray_intersect(m.g_lo, m.g_hi, ro, d, bmin, bmax);
+        active = active && (isfinite(bmin) || isfinite(bmax));
+        if (!active) { bmin = 0.f; bmax = kInfF; }
+        float mint = fmaxf(rmint, bmin), mx = fminf(rmaxt, bmax);
+        float sampled_t = __fadd_rn(mint, __fdiv_rn(-logf(__fsub_rn(1.f, sample)), majorant));
+        bool valid_mi   = active && (sampled_t <= mx);
+        float mi_t      = valid_mi ? sampled_t : kInfF;
+        V3 mi_p         = ro + d * sampled_t;
+        if (!(mi_t < kInfF)) break;                    // !mi.is_valid()
+        if (si_t < mi_t) mi_t = kInfF;
+        float tt = __fsub_rn(fminf(mi_t, si_t), mint);
+        throughput = __fmul_rn(throughput, expf(__fmul_rn(-tt, majorant)));
+        t = __fadd_rn(t, mi_t);
+        si_t = __fsub_rn(si_t, mi_t);
+        ro    = mi_p;                                  // mi.spawn_ray(_ray.d), interaction.h:58-61
+        rmint = __fmul_rn(__fadd_rn(1.f, fmaxf(fabsf(mi_p.x), fmaxf(fabsf(mi_p.y), fabsf(mi_p.z)))), kRayEpsilon);
+        rmaxt = fmaxf(0.0f, __fsub_rn(maxt, t));
+    }
+    return throughput;
 }
 
 // IsotropicPhaseFunction::eval (src/phase/isotropic.cpp:40-44) / HGPhaseFunction::eval (src/phase/hg.cpp:51-54,77-81)

@@ -23,9 +23,10 @@ struct GatherParams {
     uint32_t            q;           // samples_per_query
     float              *film_rgb;    // device, width*height*3 fp32, accumulated with RED.ADD (may be null)
     float              *seg_out;     // device, n_segs*3: Li per segment before the weight (may be null)
+    uint32_t           *wd;          // pinned host memory, 32 words: record left by the in-kernel watchdog before it traps
 };
 
-cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis, cudaStream_t stream);
+cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis, bool grid, cudaStream_t stream);
 // math_mode 1 / 2 (gather_fast.cu): iso = every medium isotropic, guard = route ill-conditioned evals to the exact path
 cudaError_t launch_gather_fast(const GatherParams &p, bool uniform, bool rr, bool vis, bool iso, bool guard, cudaStream_t stream);
 cudaError_t launch_prep_fast_vrls(const DVrl *in, uint64_t n, const DMedium *media, float scale, DVrl *out, cudaStream_t stream);

@@ -262,6 +262,38 @@ def nl_fog_scene(occluders=True, res_y=320, bottom_ior=1.0, top_ior=0.95, sigma_
     return sc
 
 
+def smoke_grid(res=(64, 50, 64), seed=7, blobs=24):
+    """Synthetic density grid [nz, ny, nx] in [0, 1] with the look of data/hetvol/smoke.vol (a few soft plumes over a
+    thin background): the sum of seeded Gaussian blobs.  Deterministic (numpy PCG64 with a fixed seed)."""
+    nx, ny, nz = res
+    rng = np.random.Generator(np.random.PCG64(seed))
+    z, y, x = np.meshgrid((np.arange(nz) + .5) / nz, (np.arange(ny) + .5) / ny, (np.arange(nx) + .5) / nx, indexing="ij")
+    g = np.full((nz, ny, nx), 0.02)
+    for _ in range(blobs):
+        c = rng.uniform(0.15, 0.85, 3)
+        s = rng.uniform(0.05, 0.18)
+        a = rng.uniform(0.3, 1.0)
+        g += a * np.exp(-((x - c[0]) ** 2 + (y - c[1]) ** 2 + (z - c[2]) ** 2) / (2 * s * s))
+    return (g / g.max()).astype(np.float32)
+
+
+def grid_fog_scene(occluders=True, res=(64, 50, 64), majorant=0.4, albedo=0.909, phase=abi.PHASE_HG, g=0.8):
+    """box-fog variant V3: the fog is a grid (`heterogeneous`) medium; `scale` is chosen so that the
+    majorant scale * max(grid) is `majorant` (a handful of free-flight steps per transmittance at this box size)."""
+    sc = Scene()
+    e = BOX + 0.01
+    grid = smoke_grid(res)
+    m = make_medium(kind=abi.MEDIUM_GRID, sigma_t=(1, 1, 1), albedo=(albedo,) * 3, scale=majorant / float(grid.max()), phase=phase, g=g)
+    m.grid_bbox_min[:] = [-e] * 3
+    m.grid_bbox_max[:] = [e] * 3
+    med = sc.add_medium(m, grid=grid)
+    sc.add_tris(box_tris((-e,) * 3, (e,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(med))
+    sc.add_tris(box_tris((-BOX,) * 3, (BOX,) * 3, faces="xXyYZ", inward=True), abi.SURF_BSDF_SMOOTH)
+    if occluders:
+        sc.add_tris(sphere_tris((4.5, -2.0, -1.0), 4.0), abi.SURF_BSDF_SMOOTH)
+    return sc
+
+
 def box_fog_camera(width=1920, height=1080):
     return make_camera(width, height, origin=(0, 0, -40), target=(0, 0, -39), up=(0, 1, 0), fov=36.0, fov_axis="x",
                        near_clip=0.1, far_clip=1000.0)

@@ -404,6 +404,40 @@ inline V3 sigma_s_const(const vrlb_medium &m) {
     return sigmat * V3(m.albedo);
 }
 
+/* GridVolume::eval for a 1-channel grid: world -> [0,1]^3 by the `.vol` bbox (volume_data.h:25-33, 79-81; applied
+ * here as (p - min) * rcp(extent)), then trilinear interpolation with clamp wrap (grid3d.cpp:236-340: fmadd(p, shape,
+ * -.5), floor2int, the eight taps at ((z*ny + y)*nx + x), fmadd lerps in x, y, z order).  The reference does not test
+ * the domain (eval_impl, grid3d.cpp:219-230): points outside see the clamped border values. */
+inline float grid_eval(const vrlb_medium &m, V3 p) {
+    const int n[3] = { m.grid_res[0], m.grid_res[1], m.grid_res[2] };
+    float pw[3] = { p.x, p.y, p.z }, w1[3], w0[3];
+    int i0[3], i1[3];
+    for (int k = 0; k < 3; ++k) {
+        float l  = (pw[k] - m.grid_bbox_min[k]) * (1.0f / (m.grid_bbox_max[k] - m.grid_bbox_min[k]));
+        float q  = std::fma(l, (float) n[k], -.5f);
+        float fl = std::floor(q);
+        int   i  = (int) fl;
+        w1[k] = q - fl; w0[k] = 1.f - w1[k];
+        i0[k] = std::min(std::max(i, 0), n[k] - 1);
+        i1[k] = std::min(std::max(i + 1, 0), n[k] - 1);
+    }
+    auto at = [&](int x, int y, int z) { return m.grid[((size_t) z * n[1] + y) * n[0] + x]; };
+    float d000 = at(i0[0], i0[1], i0[2]), d100 = at(i1[0], i0[1], i0[2]), d010 = at(i0[0], i1[1], i0[2]),
+          d110 = at(i1[0], i1[1], i0[2]), d001 = at(i0[0], i0[1], i1[2]), d101 = at(i1[0], i0[1], i1[2]),
+          d011 = at(i0[0], i1[1], i1[2]), d111 = at(i1[0], i1[1], i1[2]);
+    float v00 = std::fma(w0[0], d000, w1[0] * d100), v01 = std::fma(w0[0], d001, w1[0] * d101),
+          v10 = std::fma(w0[0], d010, w1[0] * d110), v11 = std::fma(w0[0], d011, w1[0] * d111);
+    float v0 = std::fma(w0[1], v00, w1[1] * v10), v1 = std::fma(w0[1], v01, w1[1] * v11);
+    return std::fma(w0[2], v0, w1[2] * v1);
+}
+/* get_scattering_coefficients at a point: heterogeneous.cpp:43-51 for the grid medium (sigma_t = scale * grid(p),
+ * sigma_s = sigma_t * albedo with a constant albedo volume), else the constant coefficients */
+inline V3 sigma_s_at(const vrlb_medium &m, V3 p) {
+    if (m.kind != VRLB_MEDIUM_GRID) return sigma_s_const(m);
+    float sigmat = m.scale * grid_eval(m, p);
+    return V3(m.albedo) * sigmat;
+}
+
 /* IsotropicPhaseFunction::eval = square_to_uniform_sphere_pdf = 1/(4 pi) (isotropic.cpp:40-44);
  * HGPhaseFunction::eval = eval_hg(dot(wo, mi.wi)) (hg.cpp:51-54, 77-81) */
 inline float phase_eval(const vrlb_medium &m, V3 wi, V3 wo) {
@@ -599,11 +633,11 @@ V3 get_contrib(const vrlo_scene &s, bool trace, const Vrl &vrl, const Ray &ray, 
     V3 wi       = -ray.d;
     float rayPF = phase_eval(m, wi, dir);
     if (rayPF == 0) return V3(0.f);
-    V3 sigmaSRay = sigma_s_const(m);
+    V3 sigmaSRay = sigma_s_at(m, sampling.pCam);
 
     float vrlPF = phase_eval(m, -vrl.direction, -dir);
     if (vrlPF == 0) return V3(0.f);
-    V3 sigmaSVRL = sigma_s_const(m);
+    V3 sigmaSVRL = sigma_s_at(m, sampling.pVRL);
 
     float vrlToRayTrans = eval_transmittance(s, trace, sampling.pCam, sampling.pVRL, vrl.medium, sub);
     if (vrlToRayTrans == 0.0f) return V3(0.f);
@@ -795,6 +829,13 @@ void vrlo_eval_transmittance(const vrlo_scene *s, const float p1[3], const float
     Pcg32 sub; sub.seed(0, PCG32_DEFAULT_STREAM + 1);
     float tr = eval_transmittance(*s, true, V3(p1), V3(p2), medium, &sub);
     out_rgb[0] = out_rgb[1] = out_rgb[2] = tr;
+}
+
+/* probes for the grid medium (tests/test_oracle_cpu.py) */
+float vrlo_grid_eval(const vrlo_scene *s, int medium, const float p[3]) { return grid_eval(s->media[(size_t) medium], V3(p)); }
+float vrlo_grid_transmittance(const vrlo_scene *s, int medium, const float o[3], const float d[3], float maxt, uint64_t seed) {
+    Pcg32 sub; sub.seed(seed, PCG32_DEFAULT_STREAM + 1);
+    return grid_transmittance(*s, s->media[(size_t) medium], medium, V3(o), V3(d), maxt, &sub);
 }
 
 uint64_t vrlo_gather_segments(const vrlo_scene *s, const vrlb_vrlset_desc *vrls, const vrlb_segment *segs,

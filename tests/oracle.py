@@ -50,6 +50,10 @@ def lib():
         L.vrlo_ray_intersect.argtypes = [C.c_void_p, f3, f3, C.c_float, C.c_float, f3, f3, f3]
         L.vrlo_ray_intersect.restype = C.c_int
         L.vrlo_eval_transmittance.argtypes = [C.c_void_p, f3, f3, C.c_int, f3]
+        L.vrlo_grid_eval.argtypes = [C.c_void_p, C.c_int, f3]
+        L.vrlo_grid_eval.restype = C.c_float
+        L.vrlo_grid_transmittance.argtypes = [C.c_void_p, C.c_int, f3, f3, C.c_float, C.c_uint64]
+        L.vrlo_grid_transmittance.restype = C.c_float
         L.vrlo_build_segments.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.c_uint64, C.c_int,
                                           C.c_void_p, C.c_uint64, f3, f3]
         L.vrlo_build_segments.restype = C.c_uint64
@@ -92,6 +96,14 @@ class OracleScene:
         p1, p2, out = f32(p1), f32(p2), np.zeros(3, np.float32)
         lib().vrlo_eval_transmittance(self.h, fp(p1), fp(p2), medium, fp(out))
         return out
+
+    def grid_eval(self, p, medium=0):
+        p = f32(p)
+        return lib().vrlo_grid_eval(self.h, medium, fp(p))
+
+    def grid_transmittance(self, o, d, maxt, seed, medium=0):
+        o, d = f32(o), f32(d)
+        return lib().vrlo_grid_transmittance(self.h, medium, fp(o), fp(d), maxt, seed)
 
     def build_segments(self, cam, opt, n_vrls_total, rng_mode=RNG_ADDRESSED, cap=None):
         npix = cam.width * cam.height

@@ -175,6 +175,45 @@ def test_homogeneous_transmittance_is_grey_mean_sigma_t():
     assert np.allclose(tr, math.exp(-2.0 * 0.6 * 1.5), rtol=1e-6) and tr[0] == tr[1] == tr[2]
 
 
+def test_grid_volume_trilinear_known_answers():
+    """GridVolume::eval (grid3d.cpp:236-340), as src/textures/tests/test_texture3d.py checks it: voxel centres return
+    the stored value, a grid that is linear in x is reproduced between centres, outside points see the clamped border."""
+    res = (8, 5, 6)
+    sc = scenes.grid_fog_scene(occluders=False, res=res)
+    grid = scenes.smoke_grid(res)
+    osc = oracle.OracleScene(sc)
+    e = scenes.BOX + 0.01
+    ext = 2 * e
+    for (ix, iy, iz) in [(0, 0, 0), (3, 2, 4), (7, 4, 5)]:
+        p = [-e + (ix + .5) / res[0] * ext, -e + (iy + .5) / res[1] * ext, -e + (iz + .5) / res[2] * ext]
+        assert abs(osc.grid_eval(p) - grid[iz, iy, ix]) <= 2e-6
+    assert abs(osc.grid_eval([-e - 3.0, -e - 1.0, -e - 2.0]) - grid[0, 0, 0]) <= 1e-7
+    lin = scenes.Scene()
+    g = np.broadcast_to(np.arange(8, dtype=np.float32)[None, None, :], (6, 5, 8))
+    m = scenes.make_medium(kind=abi.MEDIUM_GRID, scale=1.0)
+    m.grid_bbox_min[:] = [0, 0, 0]
+    m.grid_bbox_max[:] = [8, 5, 6]
+    lin.add_medium(m, grid=g)
+    ol = oracle.OracleScene(lin)
+    for x in (0.5, 1.25, 3.9, 7.5):
+        assert abs(ol.grid_eval([x, 2.2, 3.3]) - (x - 0.5)) <= 1e-5
+
+
+def test_grid_transmittance_is_the_references_biased_majorant_estimator():
+    """medium.h:119-154: the product of exp(-majorant * step) over the ACCEPTED free-flight steps only, i.e.
+    exp(-majorant * T_last) with T_last the last Poisson arrival before L.  Closed form of its mean:
+    E = exp(-mu L) (1 + mu L)  (the true transmittance would be exp(-mu L)); every sample lies in [exp(-mu L), 1]."""
+    sc = scenes.grid_fog_scene(occluders=False, res=(8, 5, 6), majorant=0.4)
+    osc = oracle.OracleScene(sc)
+    mu, L = 0.4, 6.0
+    o, d = [-3.0, 0.5, -1.0], [1.0, 0.0, 0.0]
+    v = np.array([osc.grid_transmittance(o, d, L, seed) for seed in range(20000)])
+    assert v.min() >= np.exp(-mu * L) * (1 - 1e-5) and v.max() <= 1.0
+    want = np.exp(-mu * L) * (1 + mu * L)
+    assert abs(v.mean() - want) <= 4 * v.std() / np.sqrt(len(v))
+    assert osc.grid_transmittance(o, d, L, 5) == osc.grid_transmittance(o, d, L, 5)
+
+
 def test_shadow_query_occluder_and_null_boundary():
     """vrl_struct.h:525-569: a non-null surface zeroes the transmittance; Null::eval returns 0 (null.cpp:59-62),
     so does an index-matched boundary."""
