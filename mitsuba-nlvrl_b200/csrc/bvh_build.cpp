@@ -177,10 +177,31 @@ void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, S
     }
     std::vector<uint32_t> shell_roots;
     for (uint32_t i = 0; i < n; ++i) if (find(i) == i && is_shell[i] && shell_roots.size() < VRLB_MAX_SHELLS) shell_roots.push_back(i);
-    auto shell_of = [&](uint32_t tri) -> int { uint32_t r = find(tri); for (size_t s = 0; s < shell_roots.size(); ++s) if (shell_roots[s] == r) return (int) s; return -1; };
+    // "solids": the largest remaining components (by box area, at least 12 triangles) get their own BVH + proxies
+    std::vector<uint32_t> solid_roots;
+    {
+        std::vector<uint32_t> ccount(n, 0);
+        for (uint32_t i = 0; i < n; ++i) ccount[find(i)]++;
+        std::vector<std::pair<float, uint32_t>> cand;
+        for (uint32_t i = 0; i < n; ++i) {
+            if (find(i) != i || is_shell[i] || ccount[i] < 12) continue;
+            const Box &b = cbox[i]; float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+            cand.push_back({ -(dx * dy + dy * dz + dz * dx), i });
+        }
+        std::sort(cand.begin(), cand.end());
+        for (size_t i = 0; i < cand.size() && i < VRLB_MAX_SOLIDS; ++i) solid_roots.push_back(cand[i].second);
+    }
+    const size_t n_sh = shell_roots.size();
+    // subset index: 0 = main, 1 .. n_sh = shells, n_sh + 1 .. = solids
+    auto subset_of = [&](uint32_t tri) -> size_t {
+        uint32_t r = find(tri);
+        for (size_t s = 0; s < shell_roots.size(); ++s) if (shell_roots[s] == r) return 1 + s;
+        for (size_t s = 0; s < solid_roots.size(); ++s) if (solid_roots[s] == r) return 1 + n_sh + s;
+        return 0;
+    };
     // gather subsets
-    std::vector<std::vector<uint32_t>> subsets(1 + shell_roots.size());
-    for (uint32_t i = 0; i < n; ++i) subsets[(size_t) (1 + shell_of(i))].push_back(i);
+    std::vector<std::vector<uint32_t>> subsets(1 + shell_roots.size() + solid_roots.size());
+    for (uint32_t i = 0; i < n; ++i) subsets[subset_of(i)].push_back(i);
     float ext = 0.f;
     for (uint32_t i = 0; i < n * 9; ++i) ext = std::max(ext, std::fabs(verts[i]));
     const float margin = 1e-3f * ext + 1e-6f;
@@ -207,11 +228,15 @@ void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, S
             Box mb; for (uint32_t t : sub) { const float *p = verts + (size_t) t * 9; mb.grow(p); mb.grow(p + 3); mb.grow(p + 6); }
             if (!sub.empty()) for (int k = 0; k < 3; ++k) { out.main_lo[k] = mb.lo[k] - margin; out.main_hi[k] = mb.hi[k] + margin; }
         }
-        else {
+        else if (s <= n_sh) {
             DShell sh{}; const Box &b = cbox[shell_roots[s - 1]];
             for (int k = 0; k < 3; ++k) { sh.lo[k] = b.lo[k] + margin; sh.hi[k] = b.hi[k] - margin; }
             sh.root = root_ref;
             out.shells.push_back(sh);
+        } else {
+            DSolid so; build_solid_proxies(verts, sub, margin, so);
+            so.root = root_ref;
+            out.solids.push_back(so);
         }
     }
 }

@@ -17,9 +17,12 @@ struct ShadowAccel {
     std::vector<DTri>   tris;      // own triangle order (prim = original index)
     std::vector<DWNode> wnodes;
     std::vector<DShell> shells;
+    std::vector<DSolid> solids;    // largest non-shell components, each with its own BVH + proxies (occluder_proxies.cpp)
     uint32_t main_root = 0x80000000u;
     float    main_lo[3] = { 0, 0, 0 }, main_hi[3] = { 0, 0, 0 };
     bool     has_main = false;
 };
+// proxies of one component (triangle indices `sub` into verts); fills everything but `root`
+void build_solid_proxies(const float *verts, const std::vector<uint32_t> &sub, float margin, DSolid &out);
 void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, ShadowAccel &out);
 }  // namespace vrlb

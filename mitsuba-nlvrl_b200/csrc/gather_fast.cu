@@ -326,16 +326,17 @@ gather_fast_kernel(GatherParams p) {
 // persistent lanes: whenever a lane finishes a ray it pulls the next one from the queue (phase B), so lanes stay
 // busy until the queue runs dry.  Phase C adds the surviving contributions in VRL order (lane-private slots,
 // deterministic).  B200 has no RT cores: this is plain SIMT traversal with warp-level ray compaction.
-constexpr int NB    = 4;                 // VRLs shaded per batch
+constexpr int NB    = 4;                 // pending shadow segments a lane may park before the warp traces
 constexpr int VTILE = 64, NBUF = 4;     // VRL ring of the visibility kernel: NBUF tiles of VTILE records
 constexpr int QCAP  = NB * 32;           // shadow-segment slots per warp
-constexpr int QF    = 8;                 // floats per slot: o(3) d(3) dist f
+constexpr int QF    = 11;                // floats per slot: o(3) d(3) dist alive r g b
 constexpr float Q_RESOLVED = -1.f, Q_REDO = -2.f;   // dist markers: no trace needed / re-evaluate exactly
 
 struct WarpQueue {
     float    v[QF][QCAP];                // SoA: consecutive lanes -> consecutive banks
     uint16_t roots[QCAP];                // per slot: which roots to visit (roots_mask)
     uint16_t list[QCAP];                 // compacted slot indices that need tracing
+    uint16_t vj[QCAP];                   // per slot: index of the VRL in the current tile (exact re-evaluation)
     uint32_t lq[128];                    // pending leaf entries: (first triangle << 12) | (count << 7) | slot
 };
 
@@ -351,15 +352,60 @@ __device__ __forceinline__ bool shell_inside(const DShell &sh, V3 o, V3 e) {
            e.x > sh.lo[0] && e.x < sh.hi[0] && e.y > sh.lo[1] && e.y < sh.hi[1] && e.z > sh.lo[2] && e.z < sh.hi[2];
 }
 
-// which roots the shadow segment has to visit: bit 0 = main BVH (its root box is hit), bit 1 + i = shell i (an end
-// point is not strictly inside it).  Evaluated in phase A with all lanes converged.
-__device__ __forceinline__ uint32_t roots_mask(const DScene &s, V3 o, V3 d, float dist) {
-    uint32_t m = 0;
-    V3 e = fmad3(o, d, dist);
-    if (s.main_root != 0x80000000u) {
-        V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
-        if (slab2(s.main_lo[0], s.main_lo[1], s.main_lo[2], s.main_hi[0], s.main_hi[1], s.main_hi[2], inv, o, 0.f, dist)) m |= 1u;
+// One solid against the shadow segment o + t d, t in [0, dist] (d unit, inv = 1/d, e = end point):
+// 0 = cannot hit it, 1 = undecided (traverse its BVH), 2 = certainly occluded by it.  See occluder_proxies.cpp.
+__device__ __forceinline__ int solid_test(const DSolid &S, V3 o, V3 d, V3 inv, V3 e, float dist) {
+    if (!slab2(S.lo[0], S.lo[1], S.lo[2], S.hi[0], S.hi[1], S.hi[2], inv, o, 0.f, dist)) return 0;
+    {   // bounding sphere: closest approach of the segment to the centre
+        V3 oc(S.c[0] - o.x, S.c[1] - o.y, S.c[2] - o.z);
+        float t = fminf(fmaxf(fdot(oc, d), 0.f), dist);
+        V3 q = fmad3(oc, d, -t);
+        if (fdot(q, q) > S.r_out2) return 0;
     }
+    // inner proxies count only when an end point is outside the (grown) AABB: then the segment enters from outside
+    const bool o_out = o.x < S.lo[0] || o.x > S.hi[0] || o.y < S.lo[1] || o.y > S.hi[1] || o.z < S.lo[2] || o.z > S.hi[2];
+    const bool e_out = e.x < S.lo[0] || e.x > S.hi[0] || e.y < S.lo[1] || e.y > S.hi[1] || e.z < S.lo[2] || e.z > S.hi[2];
+    const bool enters = o_out || e_out;
+    if (enters && (S.flags & VRLB_SOLID_INNER_SPHERE)) {
+        V3 oc(S.ci[0] - o.x, S.ci[1] - o.y, S.ci[2] - o.z);
+        float t = fminf(fmaxf(fdot(oc, d), 0.f), dist);
+        V3 q = fmad3(oc, d, -t);
+        if (fdot(q, q) <= S.r_in2) return 2;
+    }
+    if (S.flags & (VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB)) {
+        V3 r(o.x - S.oc[0], o.y - S.oc[1], o.z - S.oc[2]);
+        V3 ol(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), r), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), r), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), r));
+        V3 dl(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), d), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), d), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), d));
+        V3 il(f_rcp(dl.x), f_rcp(dl.y), f_rcp(dl.z));
+        if ((S.flags & VRLB_SOLID_OUTER_OBB) &&
+            !slab2(-S.h_out[0], -S.h_out[1], -S.h_out[2], S.h_out[0], S.h_out[1], S.h_out[2], il, ol, 0.f, dist)) return 0;
+        if (enters && (S.flags & VRLB_SOLID_INNER_OBB)) {
+            float ax = (-S.h_in[0] - ol.x) * il.x, bx = (S.h_in[0] - ol.x) * il.x;
+            float ay = (-S.h_in[1] - ol.y) * il.y, by = (S.h_in[1] - ol.y) * il.y;
+            float az = (-S.h_in[2] - ol.z) * il.z, bz = (S.h_in[2] - ol.z) * il.z;
+            float t0 = fmaxf(fmaxf(0.f, fminf(ax, bx)), fmaxf(fminf(ay, by), fminf(az, bz)));
+            float t1 = fminf(fminf(dist, fmaxf(ax, bx)), fminf(fmaxf(ay, by), fmaxf(az, bz)));
+            if (t0 <= t1) return 2;                       // strict: the box is already pulled in by the margin
+        }
+    }
+    return 1;
+}
+
+// which roots the shadow segment has to visit: bit 0 = main BVH (its root box is hit), bit 1 + i = shell i (an end
+// point is not strictly inside it), bit 9 + i = solid i (undecided by its proxies).  `occluded` = a solid's inner proxy
+// already decides the query.  Evaluated in phase A with all lanes converged.
+__device__ __forceinline__ uint32_t roots_mask(const DScene &s, V3 o, V3 d, float dist, bool &occluded) {
+    uint32_t m = 0;
+    occluded = false;
+    V3 e = fmad3(o, d, dist);
+    V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
+    for (int i = 0; i < s.n_solids; ++i) {
+        int r = solid_test(s.solids[i], o, d, inv, e, dist);
+        if (r == 2) occluded = true;
+        if (r == 1) m |= 512u << i;
+    }
+    if (s.main_root != 0x80000000u &&
+        slab2(s.main_lo[0], s.main_lo[1], s.main_lo[2], s.main_hi[0], s.main_hi[1], s.main_hi[2], inv, o, 0.f, dist)) m |= 1u;
     for (int i = 0; i < s.n_shells; ++i) if (!shell_inside(s.shells[i], o, e)) m |= 2u << i;
     return m;
 }
@@ -367,7 +413,7 @@ __device__ __forceinline__ bool next_root(const DScene &s, RayState &r, uint32_t
     if (r.roots == 0) return false;
     int i = __ffs((int) r.roots) - 1;
     r.roots &= r.roots - 1;
-    root = i == 0 ? s.main_root : s.shells[i - 1].root;
+    root = i == 0 ? s.main_root : (i <= VRLB_MAX_SHELLS ? s.shells[i - 1].root : s.solids[i - 1 - VRLB_MAX_SHELLS].root);
     return true;
 }
 
@@ -601,68 +647,31 @@ gather_fast_vis_kernel(GatherParams p) {
         mbar_wait_wd(&full_bar[buf], (it / NBUF) & 1u, p.wd, 1u, it, buf, warp_it, ring_bar);
         const uint32_t cnt = (uint32_t) min((uint64_t) VTILE, p.n_vrls - (uint64_t) t * VTILE);
         float pr = 0.f, pg = 0.f, pb = 0.f;
-        for (uint32_t jb = 0; jb < cnt; jb += NB) {
-            // ---- phase A: shade NB VRLs, park the shadow segments ----
+        const uint64_t rng_tile = rng.state;               // to regenerate (u1, u2) of a VRL on the rare re-evaluation
+        int npend = 0;                                     // shadow segments this lane has parked (slot = k * 32 + lane)
+        // trace what is parked and add the survivors (lane-private slots: deterministic order)
+        auto flush = [&]() {
             int qn = 0;
-            const uint64_t rng_batch = rng.state;          // to regenerate (u1, u2) of a slot on the rare re-evaluation
 #pragma unroll
-            for (int i = 0; i < NB; ++i) {
-                const uint32_t j = jb + i;
-                const int slot = i * 32 + (int) lane;
-                float f = 0.f, sdist = Q_RESOLVED, u1 = 0.f, u2 = 0.f; uint32_t roots = 0;
-                V3 so(0.f), sd(0.f);
-                if (j < cnt) {
-                    const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
-                    float4 a = vp[0], b = vp[1], c = vp[2];
-                    V3 vo(a.x, a.y, a.z), vd(b.x, b.y, b.z);
-                    float vlen = a.w;
-                    float rrWeight = 1.f; bool survive = live;
-                    if (RR) {
-                        float cc, cv;                                     // EDistanceRoulette, vrl_map.h:171-190
-                        closest_fast(vo, vd, vlen, ray, cc, cv);
-                        V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(vo, vd, cv);
-                        rrWeight = fminf(f_rcp(f_sqrt(fdot(dd, dd)) * p.scale_rr), 1.0f);
-                        survive  = survive && rrWeight > rng.next_f32();
-                    }
-                    u1 = rng.next_f32(); u2 = rng.next_f32();
-                    if (survive) {
-                        float g = 0.f;
-                        if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
-                        bool slow; float dist;
-                        f = contrib_fast<UNIFORM, true, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, dist);
-                        if (GUARD && slow) {                              // ill-conditioned eval: exact path, traced inline
-                            const DMedium &m = media[__float_as_uint(b.w)];
-                            f = exact_eval_vis<UNIFORM>(p.scene, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2);
-                        } else if (f != 0.f) { sdist = dist; roots = roots_mask(p.scene, so, sd, dist); if (roots == 0) sdist = Q_RESOLVED; }
-                        if (RR) f = f * f_rcp(rrWeight);
-                    }
-                }
-                q.v[0][slot] = so.x; q.v[1][slot] = so.y; q.v[2][slot] = so.z;
-                q.v[3][slot] = sd.x; q.v[4][slot] = sd.y; q.v[5][slot] = sd.z;
-                q.v[6][slot] = sdist; q.v[7][slot] = f; q.roots[slot] = (uint16_t) roots;
-                const bool need = sdist > 0.f;
+            for (int k = 0; k < NB; ++k) {
+                const bool need = k < npend;
                 const unsigned m = __ballot_sync(0xffffffffu, need);
-                if (need) q.list[qn + __popc(m & lt)] = (uint16_t) slot;
+                if (need) q.list[qn + __popc(m & lt)] = (uint16_t) (k * 32 + (int) lane);
                 qn += __popc(m);
             }
             __syncwarp();
-            // ---- phase B: persistent-lane traversal of the queue ----
             trace_queue(p.scene, q, qn, p.wd);
             __syncwarp();
-            // ---- phase C: accumulate in VRL order ----
-#pragma unroll
-            for (int i = 0; i < NB; ++i) {
-                const uint32_t j = jb + i;
-                if (j >= cnt) break;
-                const int slot = i * 32 + (int) lane;
-                float f = q.v[7][slot];
-                const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
-                float4 c = vp[2];
-                if (q.v[6][slot] == Q_REDO) {                             // graze margin: exactly-rounded eval + exact trace
-                    float4 a = vp[0], b = vp[1];
+            for (int k = 0; k < npend; ++k) {
+                const int slot = k * 32 + (int) lane;
+                float cr = q.v[8][slot], cg = q.v[9][slot], cb = q.v[10][slot];
+                if (q.v[6][slot] == Q_REDO) {              // graze margin: exactly-rounded eval + exact trace
+                    const uint32_t j = q.vj[slot];
+                    const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
+                    float4 a = vp[0], b = vp[1], c = vp[2];
                     const DMedium &m = media[__float_as_uint(b.w)];
-                    Pcg32 rr; rr.state = rng_batch;
-                    for (int k = 0; k < i * (int) DPE + (RR ? 1 : 0); ++k) rr.next_u32();
+                    Pcg32 rr; rr.state = rng_tile;
+                    for (uint32_t d = 0; d < j * DPE + (RR ? 1u : 0u); ++d) rr.next_u32();
                     float ru1 = rr.next_f32(), ru2 = rr.next_f32();
                     float fe = exact_eval_vis<UNIFORM>(p.scene, er, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, m.max_density, m.phase, m.g, ru1, ru2);
                     if (RR) {
@@ -671,13 +680,58 @@ gather_fast_vis_kernel(GatherParams p) {
                         V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), cv);
                         fe = fe * f_rcp(fminf(f_rcp(f_sqrt(fdot(dd, dd)) * p.scale_rr), 1.0f));
                     }
-                    f = fe;
-                }
-                float cr = c.x * f, cg = c.y * f, cb = c.z * f;           // flux pre-multiplied by sigma_s^2 * m_scale
+                    cr = c.x * fe; cg = c.y * fe; cb = c.z * fe;
+                } else if (q.v[7][slot] == 0.f) continue;  // occluded
                 if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { pr += cr; pg += cg; pb += cb; }   // vrl_map.h:162
             }
+            npend = 0;
             __syncwarp();
+        };
+        for (uint32_t j = 0; j < cnt; ++j) {
+            // shade VRL j for the warp's 32 camera segments (converged); only undecided shadow segments are parked
+            const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
+            float4 a = vp[0], b = vp[1], c = vp[2];
+            V3 vo(a.x, a.y, a.z), vd(b.x, b.y, b.z);
+            float vlen = a.w;
+            float rrWeight = 1.f; bool survive = live;
+            if (RR) {
+                float cc, cv;                                     // EDistanceRoulette, vrl_map.h:171-190
+                closest_fast(vo, vd, vlen, ray, cc, cv);
+                V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(vo, vd, cv);
+                rrWeight = fminf(f_rcp(f_sqrt(fdot(dd, dd)) * p.scale_rr), 1.0f);
+                survive  = survive && rrWeight > rng.next_f32();
+            }
+            float u1 = rng.next_f32(), u2 = rng.next_f32();
+            float f = 0.f; bool pend = false; uint32_t roots = 0; V3 so(0.f), sd(0.f); float dist = 0.f;
+            if (survive) {
+                float g = 0.f;
+                if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
+                bool slow;
+                f = contrib_fast<UNIFORM, true, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, dist);
+                if (GUARD && slow) {                              // ill-conditioned eval: exact path, traced inline
+                    const DMedium &m = media[__float_as_uint(b.w)];
+                    f = exact_eval_vis<UNIFORM>(p.scene, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2);
+                } else if (f != 0.f) {
+                    bool occluded;
+                    roots = roots_mask(p.scene, so, sd, dist, occluded);
+                    if (occluded) f = 0.f;                        // an inner proxy of a closed solid decides it
+                    else pend = roots != 0;
+                }
+                if (RR) f = f * f_rcp(rrWeight);
+            }
+            const float cr = c.x * f, cg = c.y * f, cb = c.z * f; // flux pre-multiplied by sigma_s^2 * m_scale
+            if (pend) {
+                const int slot = npend * 32 + (int) lane;
+                q.v[0][slot] = so.x; q.v[1][slot] = so.y; q.v[2][slot] = so.z;
+                q.v[3][slot] = sd.x; q.v[4][slot] = sd.y; q.v[5][slot] = sd.z;
+                q.v[6][slot] = dist; q.v[7][slot] = 1.f;
+                q.v[8][slot] = cr; q.v[9][slot] = cg; q.v[10][slot] = cb;
+                q.roots[slot] = (uint16_t) roots; q.vj[slot] = (uint16_t) j;
+                ++npend;
+            } else if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { pr += cr; pg += cg; pb += cb; }   // vrl_map.h:162
+            if (__any_sync(0xffffffffu, npend == NB)) flush();
         }
+        if (__any_sync(0xffffffffu, npend > 0)) flush();
         float part[3] = { pr, pg, pb };
 #pragma unroll
         for (int k = 0; k < 3; ++k) {

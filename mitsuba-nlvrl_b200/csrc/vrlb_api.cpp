@@ -49,7 +49,7 @@ struct vrlb_context {
     std::atomic<int> cancel{ 0 };
 
     // scene
-    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters; DevBuf<float> grids; bool any_grid = false;
+    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters; DevBuf<float> grids; bool any_grid = false; DevBuf<DSolid> solids;
     DScene scene{};
     bool have_scene = false;
     std::vector<vrlb_medium> host_media;
@@ -183,7 +183,7 @@ void vrlb_destroy(vrlb_context *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->wnodes.release(); ctx->stris.release(); ctx->media.release(); ctx->emitters.release();
+    ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->wnodes.release(); ctx->stris.release(); ctx->media.release(); ctx->emitters.release(); ctx->grids.release(); ctx->solids.release();
     ctx->vrls.release(); ctx->vrls_fast.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
     if (ctx->nccl_comm && g_nccl_destroy) g_nccl_destroy(ctx->nccl_comm);
     ctx->block_ids.release(); ctx->film_rgb.release(); ctx->film_aw.release(); ctx->film_xyzaw.release();
@@ -299,6 +299,10 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     for (int k = 0; k < 3; ++k) { ctx->scene.main_lo[k] = sa.main_lo[k]; ctx->scene.main_hi[k] = sa.main_hi[k]; }
     ctx->scene.n_shells = (int32_t) sa.shells.size();
     for (size_t i = 0; i < sa.shells.size(); ++i) ctx->scene.shells[i] = sa.shells[i];
+    ctx->scene.n_solids = (int32_t) sa.solids.size();
+    CU(ctx, ctx->solids.reserve(std::max<size_t>(sa.solids.size(), 1)));
+    if (!sa.solids.empty()) CU(ctx, cudaMemcpy(ctx->solids.ptr, sa.solids.data(), sa.solids.size() * sizeof(DSolid), cudaMemcpyHostToDevice));
+    ctx->scene.solids = ctx->solids.ptr;
     ctx->scene.n_tris = (int32_t) tris.size(); ctx->scene.n_nodes = (int32_t) nodes.size();
     ctx->scene.media = ctx->media.ptr; ctx->scene.n_media = (int32_t) dm.size();
     ctx->scene.emitters = ctx->emitters.ptr; ctx->scene.n_emitters = (int32_t) sc->n_emitters;

@@ -114,6 +114,24 @@ struct DShell {          // a component lying in the faces of its own AABB (fog 
     uint32_t root;       // child reference as in DWNode
     uint32_t pad;
 };
+// A connected component with its own BVH and conservative proxies (occluder_proxies.cpp): outer = bounding sphere +
+// oriented box (a segment missing one misses the mesh); inner = inscribed sphere + oriented box of a CLOSED component
+// (a segment with an end point outside the AABB that meets one crosses the surface).
+#define VRLB_MAX_SOLIDS 6
+#define VRLB_SOLID_OUTER_OBB    1u
+#define VRLB_SOLID_INNER_SPHERE 2u
+#define VRLB_SOLID_INNER_OBB    4u
+struct DSolid {
+    float lo[3], hi[3];      // AABB grown by the safety margin
+    uint32_t root;           // child reference as in DWNode
+    uint32_t flags;
+    float c[3], r_out2;      // bounding sphere: centre, (radius + margin)^2
+    float ci[3], r_in2;      // inscribed sphere: centre, (radius - margin)^2
+    float ax[9];             // oriented-box frame, rows = unit axes
+    float oc[3];             // oriented-box centre
+    float h_out[3];          // outer half extents (+ margin)
+    float h_in[3];           // inscribed half extents (- margin)
+};
 struct DMedium {         // what the gather needs of a medium (homogeneous / nonlinear coefficients)
     float max_density;   // scale * mean(sigma_t): grey extinction (homogeneous.cpp:26, constant3d.cpp:37)
     float sigma_s[3];    // scale * sigma_t * albedo (homogeneous.cpp:42-50)
@@ -150,6 +168,8 @@ struct DScene {
     float        main_lo[3], main_hi[3];   // root box of the main BVH
     int32_t      n_shells;
     DShell       shells[VRLB_MAX_SHELLS];
+    int32_t      n_solids;
+    const DSolid *solids;    // device array (dynamic indexing of a by-value parameter array would go through local memory)
     int32_t      n_tris;
     int32_t      n_nodes;
     const DMedium *media;
@@ -299,6 +319,11 @@ __device__ inline bool any_hit(const DScene &s, V3 o, V3 d, float mint, float ma
         bool inside = o.x > sh.lo[0] && o.x < sh.hi[0] && o.y > sh.lo[1] && o.y < sh.hi[1] && o.z > sh.lo[2] && o.z < sh.hi[2] &&
                       e.x > sh.lo[0] && e.x < sh.hi[0] && e.y > sh.lo[1] && e.y < sh.hi[1] && e.z > sh.lo[2] && e.z < sh.hi[2];
         if (!inside && traverse_any_hit(s, sh.root, o, d, inv, mint, maxt)) return true;
+    }
+    // solids: exact traversal only (the proxies are the fast path's business; this is the parity anchor)
+    for (int i = 0; i < s.n_solids; ++i) {
+        const DSolid &so = s.solids[i];
+        if (slab(make_float4(so.lo[0], so.lo[1], so.lo[2], 0.f), make_float4(so.hi[0], so.hi[1], so.hi[2], 0.f), o, inv, mint, maxt) && traverse_any_hit(s, so.root, o, d, inv, mint, maxt)) return true;
     }
     return false;
 }
