@@ -330,7 +330,7 @@ constexpr int NB    = 4;                 // pending shadow segments a lane may p
 constexpr int VTILE = 64, NBUF = 4;     // VRL ring of the visibility kernel: NBUF tiles of VTILE records
 constexpr int QCAP  = NB * 32;           // shadow-segment slots per warp
 constexpr int QF    = 11;                // floats per slot: o(3) d(3) dist alive r g b
-constexpr float Q_RESOLVED = -1.f, Q_REDO = -2.f;   // dist markers: no trace needed / re-evaluate exactly
+constexpr float Q_RESOLVED = -1.f, Q_REDO = -2.f, Q_SLOW = -3.f;   // dist markers: no trace needed / re-evaluate exactly / exact eval pending
 
 struct WarpQueue {
     float    v[QF][QCAP];                // SoA: consecutive lanes -> consecutive banks
@@ -352,25 +352,22 @@ __device__ __forceinline__ bool shell_inside(const DShell &sh, V3 o, V3 e) {
            e.x > sh.lo[0] && e.x < sh.hi[0] && e.y > sh.lo[1] && e.y < sh.hi[1] && e.z > sh.lo[2] && e.z < sh.hi[2];
 }
 
-// One solid against the shadow segment o + t d, t in [0, dist] (d unit, inv = 1/d, e = end point):
+// One solid against the shadow segment o + t d, t in [0, dist] (d unit, e = end point):
 // 0 = cannot hit it, 1 = undecided (traverse its BVH), 2 = certainly occluded by it.  See occluder_proxies.cpp.
-__device__ __forceinline__ int solid_test(const DSolid &S, V3 o, V3 d, V3 inv, V3 e, float dist) {
-    if (!slab2(S.lo[0], S.lo[1], S.lo[2], S.hi[0], S.hi[1], S.hi[2], inv, o, 0.f, dist)) return 0;
-    {   // bounding sphere: closest approach of the segment to the centre
-        V3 oc(S.c[0] - o.x, S.c[1] - o.y, S.c[2] - o.z);
-        float t = fminf(fmaxf(fdot(oc, d), 0.f), dist);
-        V3 q = fmad3(oc, d, -t);
-        if (fdot(q, q) > S.r_out2) return 0;
-    }
-    // inner proxies count only when an end point is outside the (grown) AABB: then the segment enters from outside
-    const bool o_out = o.x < S.lo[0] || o.x > S.hi[0] || o.y < S.lo[1] || o.y > S.hi[1] || o.z < S.lo[2] || o.z > S.hi[2];
-    const bool e_out = e.x < S.lo[0] || e.x > S.hi[0] || e.y < S.lo[1] || e.y > S.hi[1] || e.z < S.lo[2] || e.z > S.hi[2];
-    const bool enters = o_out || e_out;
+// Cheapest rejection first: most segments miss the bounding sphere and leave after ~15 instructions.
+__device__ __forceinline__ int solid_test(const DSolid &S, V3 o, V3 d, V3 e, float dist) {
+    V3 oc(S.c[0] - o.x, S.c[1] - o.y, S.c[2] - o.z);
+    const float t = fminf(fmaxf(fdot(oc, d), 0.f), dist);        // closest approach of the segment to the centre
+    V3 q = fmad3(oc, d, -t);
+    if (fdot(q, q) > S.r_out2) return 0;
+    // inner proxies count only for a segment that enters from outside: an end point outside the bounding sphere
+    V3 ec(S.c[0] - e.x, S.c[1] - e.y, S.c[2] - e.z);
+    const bool enters = fdot(oc, oc) > S.r_out2 || fdot(ec, ec) > S.r_out2;
     if (enters && (S.flags & VRLB_SOLID_INNER_SPHERE)) {
-        V3 oc(S.ci[0] - o.x, S.ci[1] - o.y, S.ci[2] - o.z);
-        float t = fminf(fmaxf(fdot(oc, d), 0.f), dist);
-        V3 q = fmad3(oc, d, -t);
-        if (fdot(q, q) <= S.r_in2) return 2;
+        V3 oi(S.ci[0] - o.x, S.ci[1] - o.y, S.ci[2] - o.z);
+        const float ti = fminf(fmaxf(fdot(oi, d), 0.f), dist);
+        V3 qi = fmad3(oi, d, -ti);
+        if (fdot(qi, qi) <= S.r_in2) return 2;
     }
     if (S.flags & (VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB)) {
         V3 r(o.x - S.oc[0], o.y - S.oc[1], o.z - S.oc[2]);
@@ -394,19 +391,24 @@ __device__ __forceinline__ int solid_test(const DSolid &S, V3 o, V3 d, V3 inv, V
 // which roots the shadow segment has to visit: bit 0 = main BVH (its root box is hit), bit 1 + i = shell i (an end
 // point is not strictly inside it), bit 9 + i = solid i (undecided by its proxies).  `occluded` = a solid's inner proxy
 // already decides the query.  Evaluated in phase A with all lanes converged.
-__device__ __forceinline__ uint32_t roots_mask(const DScene &s, V3 o, V3 d, float dist, bool &occluded) {
+__device__ __forceinline__ uint32_t roots_mask(const DScene &s, const DSolid *solids, const float (&safe)[6], V3 o, V3 d, float dist, bool &occluded) {
     uint32_t m = 0;
     occluded = false;
     V3 e = fmad3(o, d, dist);
-    V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
     for (int i = 0; i < s.n_solids; ++i) {
-        int r = solid_test(s.solids[i], o, d, inv, e, dist);
-        if (r == 2) occluded = true;
+        int r = solid_test(solids[i], o, d, e, dist);
+        if (r == 2) { occluded = true; return 0; }
         if (r == 1) m |= 512u << i;
     }
+    V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
     if (s.main_root != 0x80000000u &&
         slab2(s.main_lo[0], s.main_lo[1], s.main_lo[2], s.main_hi[0], s.main_hi[1], s.main_hi[2], inv, o, 0.f, dist)) m |= 1u;
-    for (int i = 0; i < s.n_shells; ++i) if (!shell_inside(s.shells[i], o, e)) m |= 2u << i;
+    // shells: `safe` is the intersection of all shell boxes (registers); only a segment with an end point outside it
+    // has to look at the individual shells
+    const bool in_safe = o.x > safe[0] && o.x < safe[3] && o.y > safe[1] && o.y < safe[4] && o.z > safe[2] && o.z < safe[5] &&
+                         e.x > safe[0] && e.x < safe[3] && e.y > safe[1] && e.y < safe[4] && e.z > safe[2] && e.z < safe[5];
+    if (!in_safe)
+        for (int i = 0; i < s.n_shells; ++i) if (!shell_inside(s.shells[i], o, e)) m |= 2u << i;
     return m;
 }
 __device__ __forceinline__ bool next_root(const DScene &s, RayState &r, uint32_t &root) {
@@ -541,6 +543,13 @@ __device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int c
 
 // the exactly-rounded eval with its inline shadow traversal, out of line: it runs for < 1 % of the evals and would
 // otherwise be inlined twice into the kernel (instruction-cache misses were 2.7 stalled warps per issue)
+// the exactly-rounded eval without its shadow query: seg[0..6] = pCam, direction, length of the connection
+template <bool UNIFORM>
+__device__ __noinline__ float exact_eval_seg(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
+                                             float max_density, int phase, float g, float u1, float u2, float *seg) {
+    seg[6] = 0.f;
+    return eval_contrib<UNIFORM, false>(scene, ray, vo, vd, vlen, max_density, phase, g, u1, u2, nullptr, 0, nullptr, seg);
+}
 template <bool UNIFORM>
 __device__ __noinline__ float exact_eval_vis(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
                                              float max_density, int phase, float g, float u1, float u2) {
@@ -574,7 +583,7 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t *bar, uint32_t parity, uin
 
 // ---- kernel with visibility: phases A (shade NB VRLs) / B (trace the queue) / C (accumulate) per warp ----
 template <bool UNIFORM, bool RR, bool ISO, bool GUARD>
-__global__ void __launch_bounds__(GATHER_THREADS)
+__global__ void __launch_bounds__(GATHER_THREADS, 2)
 gather_fast_vis_kernel(GatherParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     DVrl (*tile)[VTILE] = reinterpret_cast<DVrl (*)[VTILE]>(smem_raw);                              // [NBUF][VTILE]
@@ -582,6 +591,7 @@ gather_fast_vis_kernel(GatherParams p) {
     __shared__ alignas(8) uint64_t ring_bar[2 * NBUF];  // [0, NBUF): "full" (TMA complete_tx); [NBUF, 2 NBUF): "empty" (one arrive per warp)
     uint64_t *full_bar = ring_bar, *empty_bar = ring_bar + NBUF;
     __shared__ uint32_t warp_it[GATHER_THREADS / 32];   // watchdog evidence: the tile each warp is on
+    __shared__ DSolid sol[VRLB_MAX_SOLIDS];             // the solids' proxies, read by every eval
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, lt = (1u << lane) - 1u;
     WarpQueue &q = queues[tid >> 5];
@@ -608,6 +618,8 @@ gather_fast_vis_kernel(GatherParams p) {
     const uint32_t total_tiles = n_tiles * p.q;
     constexpr uint32_t DPE = RR ? 3u : 2u;
 
+    for (uint32_t i = tid; i < (uint32_t) p.scene.n_solids * (sizeof(DSolid) / 4); i += GATHER_THREADS)
+        reinterpret_cast<uint32_t *>(sol)[i] = reinterpret_cast<const uint32_t *>(p.scene.solids)[i];
     if (tid == 0) {
         for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], GATHER_THREADS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -629,6 +641,9 @@ gather_fast_vis_kernel(GatherParams p) {
     const Guard guard = { p.guard_h * p.guard_h, p.guard_z };
     float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
     Pcg32 rng; rng.state = rng0;
+    float safe[6] = { -VRLB_INF, -VRLB_INF, -VRLB_INF, VRLB_INF, VRLB_INF, VRLB_INF };   // intersection of the shell boxes
+    for (int i = 0; i < p.scene.n_shells; ++i)
+        for (int k = 0; k < 3; ++k) { safe[k] = fmaxf(safe[k], p.scene.shells[i].lo[k]); safe[3 + k] = fminf(safe[3 + k], p.scene.shells[i].hi[k]); }
 
     for (uint32_t it = 0; it < total_tiles; ++it) {
         const uint32_t t = it % n_tiles, s = it / n_tiles, buf = it % NBUF;
@@ -708,12 +723,16 @@ gather_fast_vis_kernel(GatherParams p) {
                 if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
                 bool slow;
                 f = contrib_fast<UNIFORM, true, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, dist);
-                if (GUARD && slow) {                              // ill-conditioned eval: exact path, traced inline
-                    const DMedium &m = media[__float_as_uint(b.w)];
-                    f = exact_eval_vis<UNIFORM>(p.scene, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2);
-                } else if (f != 0.f) {
+                if (GUARD && slow) {                              // ill-conditioned eval: exactly-rounded arithmetic; its
+                    const DMedium &m = media[__float_as_uint(b.w)];       // connection segment is traced like any other
+                    float seg[7];
+                    f = exact_eval_seg<UNIFORM>(p.scene, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2, seg);
+                    so = V3(seg[0], seg[1], seg[2]); sd = V3(seg[3], seg[4], seg[5]); dist = seg[6];
+                    if (!(dist > 0.f)) f = 0.f;
+                }
+                if (f != 0.f) {
                     bool occluded;
-                    roots = roots_mask(p.scene, so, sd, dist, occluded);
+                    roots = roots_mask(p.scene, sol, safe, so, sd, dist, occluded);
                     if (occluded) f = 0.f;                        // an inner proxy of a closed solid decides it
                     else pend = roots != 0;
                 }

@@ -11,7 +11,8 @@ n = 5000
 soa = scenes.synthetic_vrls(n, seed=1)
 cam = scenes.box_fog_camera(1920, 1080)
 ctx = api.Context(0)
-for name, occ, vis, mode in (("no occluders, vis off (V1 kernel)", False, 0, 1), ("no occluders, vis on (shells only)", False, 1, 1),
+for name, occ, vis, mode in (("no occluders, vis off (V1 kernel)", False, 0, 1), ("no occluders, vis off, unguarded", False, 0, 2),
+                             ("no occluders, vis on (shells only)", False, 1, 1), ("no occluders, vis on, unguarded", False, 1, 2),
                              ("occluders, vis on, guard (bench)", True, 1, 1), ("occluders, vis on, unguarded", True, 1, 2),
                              ("occluders, vis on, exact kernel", True, 1, 0)):
     sc = scenes.box_fog_scene(occluders=occ)
