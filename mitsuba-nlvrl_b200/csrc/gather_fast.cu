@@ -581,9 +581,57 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t *bar, uint32_t parity, uin
     }
 }
 
+// Trace what the warp has parked and return the sum of the surviving contributions of this lane (lane-private slots,
+// deterministic order).  Out of line: the flush runs once per few dozen VRLs, and keeping the traversal's registers
+// out of the shading loop is worth a third CTA per SM.
+struct Acc3 { float r, g, b; };
+template <bool UNIFORM, bool RR>
+__device__ __noinline__ Acc3 flush_queue(const DScene &S, WarpQueue &q, const DVrl *tile_buf, const DMedium *media, int npend,
+                                         uint64_t rng_tile, const SegRegs &er, float scale_rr, uint32_t *wd) {
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    constexpr uint32_t DPE = RR ? 3u : 2u;
+    Acc3 acc = { 0.f, 0.f, 0.f };
+    int qn = 0;
+#pragma unroll
+    for (int k = 0; k < NB; ++k) {
+        const bool need = k < npend;
+        const unsigned m = __ballot_sync(0xffffffffu, need);
+        if (need) q.list[qn + __popc(m & lt)] = (uint16_t) (k * 32 + (int) lane);
+        qn += __popc(m);
+    }
+    __syncwarp();
+    trace_queue(S, q, qn, wd);
+    __syncwarp();
+    for (int k = 0; k < npend; ++k) {
+        const int slot = k * 32 + (int) lane;
+        float cr = q.v[8][slot], cg = q.v[9][slot], cb = q.v[10][slot];
+        if (q.v[6][slot] == Q_REDO) {              // graze margin: exactly-rounded eval + exact trace
+            const uint32_t j = q.vj[slot];
+            const float4 *vp = reinterpret_cast<const float4 *>(tile_buf + j);
+            float4 a = vp[0], b = vp[1], c = vp[2];
+            const DMedium &m = media[__float_as_uint(b.w)];
+            Pcg32 rr; rr.state = rng_tile;
+            for (uint32_t d = 0; d < j * DPE + (RR ? 1u : 0u); ++d) rr.next_u32();
+            float ru1 = rr.next_f32(), ru2 = rr.next_f32();
+            float fe = exact_eval_vis<UNIFORM>(S, er, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, m.max_density, m.phase, m.g, ru1, ru2);
+            if (RR) {
+                FastSeg ray; ray.o = er.o; ray.d = er.d; ray.maxt = er.maxt; ray.v = er.d * er.maxt; ray.c = fdot(ray.v, ray.v);
+                float cc, cv;
+                closest_fast(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, ray, cc, cv);
+                V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), cv);
+                fe = fe * f_rcp(fminf(f_rcp(f_sqrt(fdot(dd, dd)) * scale_rr), 1.0f));
+            }
+            cr = c.x * fe; cg = c.y * fe; cb = c.z * fe;
+        } else if (q.v[7][slot] == 0.f) continue;  // occluded
+        if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { acc.r += cr; acc.g += cg; acc.b += cb; }   // vrl_map.h:162
+    }
+    __syncwarp();
+    return acc;
+}
+
 // ---- kernel with visibility: phases A (shade NB VRLs) / B (trace the queue) / C (accumulate) per warp ----
 template <bool UNIFORM, bool RR, bool ISO, bool GUARD>
-__global__ void __launch_bounds__(GATHER_THREADS, 2)
+__global__ void __launch_bounds__(GATHER_THREADS, 3)
 gather_fast_vis_kernel(GatherParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     DVrl (*tile)[VTILE] = reinterpret_cast<DVrl (*)[VTILE]>(smem_raw);                              // [NBUF][VTILE]
@@ -592,6 +640,10 @@ gather_fast_vis_kernel(GatherParams p) {
     uint64_t *full_bar = ring_bar, *empty_bar = ring_bar + NBUF;
     __shared__ uint32_t warp_it[GATHER_THREADS / 32];   // watchdog evidence: the tile each warp is on
     __shared__ DSolid sol[VRLB_MAX_SOLIDS];             // the solids' proxies, read by every eval
+    __shared__ DScene s_scene;                          // the out-of-line helpers take the scene by reference: shared, not a local copy
+    if (threadIdx.x == 0) s_scene = p.scene;
+    __syncthreads();
+    const DScene &S = s_scene;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, lt = (1u << lane) - 1u;
     WarpQueue &q = queues[tid >> 5];
@@ -618,8 +670,8 @@ gather_fast_vis_kernel(GatherParams p) {
     const uint32_t total_tiles = n_tiles * p.q;
     constexpr uint32_t DPE = RR ? 3u : 2u;
 
-    for (uint32_t i = tid; i < (uint32_t) p.scene.n_solids * (sizeof(DSolid) / 4); i += GATHER_THREADS)
-        reinterpret_cast<uint32_t *>(sol)[i] = reinterpret_cast<const uint32_t *>(p.scene.solids)[i];
+    for (uint32_t i = tid; i < (uint32_t) S.n_solids * (sizeof(DSolid) / 4); i += GATHER_THREADS)
+        reinterpret_cast<uint32_t *>(sol)[i] = reinterpret_cast<const uint32_t *>(S.solids)[i];
     if (tid == 0) {
         for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], GATHER_THREADS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -637,13 +689,13 @@ gather_fast_vis_kernel(GatherParams p) {
         for (uint32_t b = 0; b < NBUF && b < total_tiles; ++b) issue(b);
     }
 
-    const DMedium *media = p.scene.media;
+    const DMedium *media = S.media;
     const Guard guard = { p.guard_h * p.guard_h, p.guard_z };
     float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
     Pcg32 rng; rng.state = rng0;
     float safe[6] = { -VRLB_INF, -VRLB_INF, -VRLB_INF, VRLB_INF, VRLB_INF, VRLB_INF };   // intersection of the shell boxes
-    for (int i = 0; i < p.scene.n_shells; ++i)
-        for (int k = 0; k < 3; ++k) { safe[k] = fmaxf(safe[k], p.scene.shells[i].lo[k]); safe[3 + k] = fminf(safe[3 + k], p.scene.shells[i].hi[k]); }
+    for (int i = 0; i < S.n_shells; ++i)
+        for (int k = 0; k < 3; ++k) { safe[k] = fmaxf(safe[k], S.shells[i].lo[k]); safe[3 + k] = fminf(safe[3 + k], S.shells[i].hi[k]); }
 
     for (uint32_t it = 0; it < total_tiles; ++it) {
         const uint32_t t = it % n_tiles, s = it / n_tiles, buf = it % NBUF;
@@ -664,43 +716,10 @@ gather_fast_vis_kernel(GatherParams p) {
         float pr = 0.f, pg = 0.f, pb = 0.f;
         const uint64_t rng_tile = rng.state;               // to regenerate (u1, u2) of a VRL on the rare re-evaluation
         int npend = 0;                                     // shadow segments this lane has parked (slot = k * 32 + lane)
-        // trace what is parked and add the survivors (lane-private slots: deterministic order)
         auto flush = [&]() {
-            int qn = 0;
-#pragma unroll
-            for (int k = 0; k < NB; ++k) {
-                const bool need = k < npend;
-                const unsigned m = __ballot_sync(0xffffffffu, need);
-                if (need) q.list[qn + __popc(m & lt)] = (uint16_t) (k * 32 + (int) lane);
-                qn += __popc(m);
-            }
-            __syncwarp();
-            trace_queue(p.scene, q, qn, p.wd);
-            __syncwarp();
-            for (int k = 0; k < npend; ++k) {
-                const int slot = k * 32 + (int) lane;
-                float cr = q.v[8][slot], cg = q.v[9][slot], cb = q.v[10][slot];
-                if (q.v[6][slot] == Q_REDO) {              // graze margin: exactly-rounded eval + exact trace
-                    const uint32_t j = q.vj[slot];
-                    const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
-                    float4 a = vp[0], b = vp[1], c = vp[2];
-                    const DMedium &m = media[__float_as_uint(b.w)];
-                    Pcg32 rr; rr.state = rng_tile;
-                    for (uint32_t d = 0; d < j * DPE + (RR ? 1u : 0u); ++d) rr.next_u32();
-                    float ru1 = rr.next_f32(), ru2 = rr.next_f32();
-                    float fe = exact_eval_vis<UNIFORM>(p.scene, er, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, m.max_density, m.phase, m.g, ru1, ru2);
-                    if (RR) {
-                        float cc, cv;
-                        closest_fast(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, ray, cc, cv);
-                        V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), cv);
-                        fe = fe * f_rcp(fminf(f_rcp(f_sqrt(fdot(dd, dd)) * p.scale_rr), 1.0f));
-                    }
-                    cr = c.x * fe; cg = c.y * fe; cb = c.z * fe;
-                } else if (q.v[7][slot] == 0.f) continue;  // occluded
-                if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { pr += cr; pg += cg; pb += cb; }   // vrl_map.h:162
-            }
+            Acc3 r = flush_queue<UNIFORM, RR>(S, q, &tile[buf][0], media, npend, rng_tile, er, p.scale_rr, p.wd);
+            pr += r.r; pg += r.g; pb += r.b;
             npend = 0;
-            __syncwarp();
         };
         for (uint32_t j = 0; j < cnt; ++j) {
             // shade VRL j for the warp's 32 camera segments (converged); only undecided shadow segments are parked
@@ -722,17 +741,17 @@ gather_fast_vis_kernel(GatherParams p) {
                 float g = 0.f;
                 if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
                 bool slow;
-                f = contrib_fast<UNIFORM, true, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, dist);
+                f = contrib_fast<UNIFORM, true, ISO, GUARD>(S, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, dist);
                 if (GUARD && slow) {                              // ill-conditioned eval: exactly-rounded arithmetic; its
                     const DMedium &m = media[__float_as_uint(b.w)];       // connection segment is traced like any other
                     float seg[7];
-                    f = exact_eval_seg<UNIFORM>(p.scene, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2, seg);
+                    f = exact_eval_seg<UNIFORM>(S, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2, seg);
                     so = V3(seg[0], seg[1], seg[2]); sd = V3(seg[3], seg[4], seg[5]); dist = seg[6];
                     if (!(dist > 0.f)) f = 0.f;
                 }
                 if (f != 0.f) {
                     bool occluded;
-                    roots = roots_mask(p.scene, sol, safe, so, sd, dist, occluded);
+                    roots = roots_mask(S, sol, safe, so, sd, dist, occluded);
                     if (occluded) f = 0.f;                        // an inner proxy of a closed solid decides it
                     else pend = roots != 0;
                 }
