@@ -573,11 +573,12 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t *bar, uint32_t parity, uin
     uint32_t ok = 0;
     long long t0 = 0;
     for (uint32_t spins = 0; ; ++spins) {
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
-                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        // try_wait with a suspend-time hint: a waiting warp sleeps in the barrier unit instead of burning issue slots
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(20000u) : "memory");
         if (ok) return;
-        if (spins == 64) t0 = clock64();
-        else if (spins > 64 && (spins & 1023u) == 0 && clock64() - t0 > 4000000000LL) ring_watchdog_trip(wd, code, it, buf, warp_it, bars);
+        if (spins == 4) t0 = clock64();
+        else if (spins > 4 && (spins & 15u) == 0 && clock64() - t0 > 4000000000LL) ring_watchdog_trip(wd, code, it, buf, warp_it, bars);
     }
 }
 
