@@ -162,7 +162,8 @@ typedef struct vrlb_segment {
     float    weight[3];                   /* throughput outside the query (vrlThroughput)      */
     int32_t  medium;
     uint64_t rng_state;                   /* PCG32 state at the first draw of this part's query */
-    uint32_t sample;                      /* sample index within the pixel                     */
+    uint32_t sample;                      /* sample index within the pixel; with use_nl_atomic_query the high
+                                           * 16 bits hold n_parts of the NLRay and its parts are consecutive */
     uint32_t part;                        /* part index within the NLRay                       */
 } vrlb_segment;
 

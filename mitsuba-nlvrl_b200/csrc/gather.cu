@@ -52,6 +52,19 @@ gather_kernel(GatherParams p) {
     } else {
         ray.o = V3(0.f); ray.d = V3(0.f, 0.f, 1.f); ray.maxt = 1.f;
     }
+    // use_nl_atomic_query (vrl.cpp:613-617): this part's place in its NLRay and the first part (distance roulette)
+    float nla_off = 0.f, nla_total = -1.f; SegRegs ray0 = ray;
+    if (UNIFORM && p.nla && live) {
+        const vrlb_segment &me = p.segs[seg_i];
+        const uint32_t n_all = me.sample >> 16, part = me.part;
+        if (n_all > 0) {
+            const vrlb_segment *g0 = p.segs + (seg_i - part);
+            float tot = 0.f;
+            for (uint32_t k = 0; k < n_all; ++k) { if (k == part) nla_off = tot; tot = tot + __ldg(&g0[k].maxt); }   // NLRay::push_back order
+            nla_total = tot;
+            ray0.o = V3(g0->o[0], g0->o[1], g0->o[2]); ray0.d = V3(g0->d[0], g0->d[1], g0->d[2]); ray0.maxt = g0->maxt;
+        }
+    }
 
     const uint32_t n_tiles = (uint32_t) ((p.n_vrls + TILE - 1) / TILE);
     const uint32_t total_tiles = n_tiles * p.q;     // the tile sequence repeats once per query sample
@@ -100,8 +113,8 @@ gather_kernel(GatherParams p) {
                 if (RR) {
                     // EDistanceRoulette, vrl_map.h:171-190
                     float cc, cv;
-                    find_closest_point(vo, vd, vlen, ray.o, ray.d, ray.maxt, cc, cv);
-                    float d2 = squared_norm((ray.o + ray.d * cc) - (vo + vd * cv));
+                    find_closest_point(vo, vd, vlen, ray0.o, ray0.d, ray0.maxt, cc, cv);
+                    float d2 = squared_norm((ray0.o + ray0.d * cc) - (vo + vd * cv));
                     float min_distance = sqrtf(d2);
                     rrWeight = fminf(1 / (min_distance * p.scale_rr), 1.0f);
                     survive  = rrWeight > rng.next_f32();
@@ -110,7 +123,7 @@ gather_kernel(GatherParams p) {
                 if (!survive) continue;
                 float st2 = 0.f;
                 float f = eval_contrib<UNIFORM, VIS, GRID>(p.scene, ray, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2,
-                                                           &m, eval_state, &st2);
+                                                           &m, eval_state, &st2, nullptr, nla_off, nla_total);
                 if (RR) f = f / rrWeight;
                 // flux * f * sigma_s(cam) * sigma_s(vrl) * m_scale (vrl_struct.h:652-659, vrl_map.h:160)
                 float cr, cg, cb;

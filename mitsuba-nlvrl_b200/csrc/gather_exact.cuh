@@ -51,15 +51,26 @@ struct SegRegs { V3 o, d; float maxt; };
 template <bool UNIFORM, bool VIS, bool GRID = false>
 __device__ inline float eval_contrib(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
                                      float max_density, int phase, float g, float u1, float u2,
-                                     const DMedium *gm = nullptr, uint64_t sub_seed = 0, float *st2 = nullptr, float *seg_out = nullptr) {
+                                     const DMedium *gm = nullptr, uint64_t sub_seed = 0, float *st2 = nullptr, float *seg_out = nullptr,
+                                     float nla_off = 0.f, float nla_total = -1.f) {
     V3 pCam, pVRL; float tCam, tVRL, invPDF;
     if (UNIFORM) {
         // VRL::sampleMC, vrl_struct.h:239-243 (single-part NLRay::at, :44-56)
-        tCam = u1 * ray.maxt;
+        if (nla_total >= 0.f) {
+            // use_nl_atomic_query: `ray` is one part of a longer NLRay of length nla_total that starts nla_off before it;
+            // the eval belongs to the part NLRay::at lands on, every other part's thread contributes 0
+            tCam = u1 * nla_total;
+            float local = tCam - nla_off;
+            if (!(local >= 0.f && local < ray.maxt)) return 0.f;
+            pCam = ray.o + ray.d * local;
+            invPDF = vlen * nla_total;
+        } else {
+            tCam = u1 * ray.maxt;
+            pCam = ray.o + ray.d * tCam;
+            invPDF = vlen * ray.maxt;
+        }
         tVRL = u2 * vlen;
-        pCam = ray.o + ray.d * tCam;
         pVRL = vo + vd * tVRL;
-        invPDF = vlen * ray.maxt;
     } else {
         float cpCam, cpVRL;
         find_closest_point(vo, vd, vlen, ray.o, ray.d, ray.maxt, cpCam, cpVRL);

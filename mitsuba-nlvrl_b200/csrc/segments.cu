@@ -130,26 +130,59 @@ __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
                     // curved camera path (vrl.cpp:550-629): marched with the eikonal integrator of generate.cu, cut into
                     // straight parts when the direction has turned by more than NL_PART_COS; one query per part, the
                     // preceding parts' transmittance carried in the weight (vrl.cpp:619-628)
-                    V3 pstart = ro, pos = ro, dir = rd, dir0 = rd, vrlThroughput = throughput;
-                    float total = 0.f, step_mint = rmint; uint32_t part = 0; bool found = false; Hit hit; hit.tri = -1; hit.t = VRLB_INF; hit.u = hit.v = 0.f;
-                    for (int step = 0; step < 100000; ++step) {
-                        hit = closest_hit(s, pos, dir, step_mint, m.nl_step);
-                        step_mint = 0.f;
-                        if (hit.tri >= 0) { pos = pos + dir * hit.t; found = true; break; }
-                        pos = pos + dir * m.nl_step;
-                        V3 nd = nl_bend(m, pos, dir, m.nl_step);
-                        if (dot(nd, dir0) < NL_PART_COS) {
-                            V3 chord = pos - pstart; float len = norm(chord);
-                            emit(pstart, chord / len, len, vrlThroughput, part++);
-                            vrlThroughput = vrlThroughput * homo_transmittance(m.max_density, len);
-                            total = total + len;
-                            pstart = pos; dir0 = nd;
+                    V3 pos = ro, dir = rd; float total = 0.f; bool found = false; Hit hit; hit.tri = -1; hit.t = VRLB_INF; hit.u = hit.v = 0.f;
+                    // the march; on_part(origin, direction, length, index) is called for every straight part in order
+                    auto march = [&](auto &&on_part) -> uint32_t {
+                        V3 pstart = ro, dir0 = rd; pos = ro; dir = rd; total = 0.f; found = false;
+                        float step_mint = rmint; uint32_t part = 0;
+                        for (int step = 0; step < 100000; ++step) {
+                            hit = closest_hit(s, pos, dir, step_mint, m.nl_step);
+                            step_mint = 0.f;
+                            if (hit.tri >= 0) { pos = pos + dir * hit.t; found = true; break; }
+                            pos = pos + dir * m.nl_step;
+                            V3 nd = nl_bend(m, pos, dir, m.nl_step);
+                            if (dot(nd, dir0) < NL_PART_COS) {
+                                V3 chord = pos - pstart; float len = norm(chord);
+                                on_part(pstart, chord / len, len, part++);
+                                total = total + len;
+                                pstart = pos; dir0 = nd;
+                            }
+                            dir = nd;
                         }
-                        dir = nd;
+                        if (!found) return part;
+                        V3 chord = pos - pstart; float len = norm(chord);
+                        if (len > 0.f) { on_part(pstart, chord / len, len, part++); total = total + len; }
+                        return part;
+                    };
+                    if (p.opt.use_nl_atomic_query) {
+                        // one query over the whole curved path (vrl.cpp:613-617): count the parts, reserve consecutive
+                        // records, write them with the query's stream position and sample = j | n_parts << 16
+                        const uint32_t n_parts = march([&](V3, V3, float, uint32_t) {});
+                        if (!found) { si.tri = -1; break; }
+                        if (n_parts > 0) {
+                            unsigned long long slot0 = on_film ? atomicAdd(p.counter, (unsigned long long) n_parts) : 0ull;
+                            if (on_film)
+                                march([&](V3 po, V3 pd, float pmaxt, uint32_t part) {
+                                    unsigned long long slot = slot0 + part;
+                                    if (slot < p.cap) {
+                                        vrlb_segment g;
+                                        g.o[0] = po.x; g.o[1] = po.y; g.o[2] = po.z; g.maxt = pmaxt;
+                                        g.d[0] = pd.x; g.d[1] = pd.y; g.d[2] = pd.z; g.pixel = film_pixel;
+                                        g.weight[0] = throughput.x; g.weight[1] = throughput.y; g.weight[2] = throughput.z;
+                                        g.medium = medium; g.rng_state = rng.state; g.sample = (uint32_t) j | (n_parts << 16); g.part = part;
+                                        p.segs[slot] = g;
+                                    }
+                                });
+                            rng.advance(query_draws);
+                        }
+                    } else {
+                        V3 vrlThroughput = throughput;
+                        march([&](V3 po, V3 pd, float pmaxt, uint32_t part) {
+                            emit(po, pd, pmaxt, vrlThroughput, part);
+                            vrlThroughput = vrlThroughput * homo_transmittance(m.max_density, pmaxt);
+                        });
+                        if (!found) { si.tri = -1; break; }
                     }
-                    if (!found) { si.tri = -1; break; }
-                    V3 chord = pos - pstart; float len = norm(chord);
-                    if (len > 0.f) { emit(pstart, chord / len, len, vrlThroughput, part++); total = total + len; }
                     throughput = throughput * homo_transmittance(m.max_density, total);        // vrl.cpp:631
                     si = hit; rd = dir; needs_intersection = false;
                 } else {

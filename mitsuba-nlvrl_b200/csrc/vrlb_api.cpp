@@ -563,7 +563,11 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     const bool vis = opt->visibility != 0 && ctx->scene.n_tris > 0;
     // grid media run on the exactly-rounded kernel in every math mode (their stochastic transmittance is a chain of
     // accept/reject decisions on logf results; a fast variant would flip decisions against the oracle)
-    const bool fast = opt->math_mode != 0 && !ctx->any_grid;
+    // use_nl_atomic_query && use_non_linear_camera forces uniform sampling (vrl.cpp:62) and runs on the exact kernel
+    const bool nla = opt->use_nl_atomic_query != 0 && opt->use_non_linear_camera != 0;
+    const bool uniform = opt->use_uniform_sampling != 0 || nla;
+    p.nla = nla ? 1 : 0;
+    const bool fast = opt->math_mode != 0 && !ctx->any_grid && !nla;
     if (fast && ctx->fast_dirty && ctx->n_vrls) {
         CU(ctx, ctx->vrls_fast.reserve(ctx->n_vrls));
         CU(ctx, launch_prep_fast_vrls(ctx->vrls.ptr, ctx->n_vrls, ctx->media.ptr, ctx->vrl_scale, ctx->vrls_fast.ptr, ctx->stream));
@@ -573,8 +577,8 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     p.guard_h = opt->reserved[0] ? (float) opt->reserved[0] * 1e-3f : 0.2f;   // dev knobs (milli-units); 0 = shipped defaults
     p.guard_z = opt->reserved[1] ? (float) opt->reserved[1] : 8.0f;
     cudaEventRecord(ctx->ev[2], ctx->stream);
-    if (!fast) CU(ctx, launch_gather(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, vis, ctx->any_grid, ctx->stream));
-    else CU(ctx, launch_gather_fast(p, opt->use_uniform_sampling != 0, opt->rr_vrl != 0, vis, ctx->all_iso, opt->math_mode == 1, ctx->stream));
+    if (!fast) CU(ctx, launch_gather(p, uniform, opt->rr_vrl != 0, vis, ctx->any_grid, ctx->stream));
+    else CU(ctx, launch_gather_fast(p, uniform, opt->rr_vrl != 0, vis, ctx->all_iso, opt->math_mode == 1, ctx->stream));
     cudaEventRecord(ctx->ev[3], ctx->stream);
     bool launched = p.n_segs && p.n_vrls;
     ctx->timing.gather_launches = launched ? 1 : 0;

@@ -21,6 +21,7 @@ struct GatherParams {
     float               scale_rr;
     float               guard_h, guard_z; // fast gather: evals with closest distance < guard_h or asinh argument < -guard_z take the exact path
     uint32_t            q;           // samples_per_query
+    int32_t             nla;         // use_nl_atomic_query: records with sample >> 16 = n_parts form one NLRay (exact kernel only)
     float              *film_rgb;    // device, width*height*3 fp32, accumulated with RED.ADD (may be null)
     float              *seg_out;     // device, n_segs*3: Li per segment before the weight (may be null)
     uint32_t           *wd;          // pinned host memory, 32 words: record left by the in-kernel watchdog before it traps

@@ -13,6 +13,7 @@
 #include "vrl_oracle.h"
 
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -620,8 +621,14 @@ float eval_transmittance(const vrlo_scene &s, bool trace, V3 p1, V3 p2, int medi
 
 /* VRL::getContrib, vrl_struct.h:584-662.  `wi` is NLRay::wi: the reference leaves it unset on the
  * importance path (quirk 1); defined here as -part.d, the commented-out intent (:611). */
+V3 get_contrib_sampled(const vrlo_scene &s, bool trace, const Vrl &vrl, const Ray &ray, const SamplingInfo &sampling, Pcg32 *sub);
 V3 get_contrib(const vrlo_scene &s, bool trace, const Vrl &vrl, const Ray &ray, bool uniform, DrawSrc &draws, Pcg32 *sub) {
     SamplingInfo sampling = sampling_vrl(vrl, ray, uniform, draws);
+    return get_contrib_sampled(s, trace, vrl, ray, sampling, sub);
+}
+/* `ray` supplies wi = -ray.d (the part NLRay::at selected, vrl_struct.h:49) and the origin/direction of the
+ * camera-side transmittance ray (ray.first(), vrl_struct.h:637-641; direction is irrelevant to the homogeneous Tr) */
+V3 get_contrib_sampled(const vrlo_scene &s, bool trace, const Vrl &vrl, const Ray &ray, const SamplingInfo &sampling, Pcg32 *sub) {
     /* invalid() has pCam == pVRL == 0 -> lengthPtoP == 0 -> 0 */
     V3 dir           = sampling.pVRL - sampling.pCam;
     float lengthPtoP = norm(dir);
@@ -735,6 +742,74 @@ uint64_t query(const vrlo_scene &s, const vrlb_vrlset_desc &set, const Ray &ray,
     return evals;
 }
 
+/* VRLMap::query for a whole multi-part NLRay, `use_nl_atomic_query` (vrl.cpp:613-617): uniform sampling over the total
+ * length (VRL::sampleMC, vrl_struct.h:239-243, with NLRay::at walking the parts by sequential subtraction, :44-56),
+ * distance roulette measured from the first part (vrl_map.h:141, 172-176).  Addressed draws as in query().  The
+ * contributions are returned per part (the part `at` landed on), so that a caller can compare part-wise partial sums;
+ * their sum over the parts is the reference's Li. */
+uint64_t query_atomic(const vrlo_scene &s, const vrlb_vrlset_desc &set, const Ray *parts, int n_parts, const vrlb_options &opt,
+                      int rng_mode, Pcg32 &rng, V3 *Li32, double (*Li64)[3]) {
+    for (int k = 0; k < n_parts; ++k) { Li32[k] = V3(0.f); Li64[k][0] = Li64[k][1] = Li64[k][2] = 0.0; }
+    if (set.n == 0 || n_parts == 0) return 0;
+    const bool rr = opt.rr_vrl != 0, trace = opt.visibility != 0;
+    const uint32_t q   = (uint32_t) std::max(opt.samples_per_query, 1);
+    const uint64_t dpe = rr ? 3u : 2u;
+    const uint64_t total = set.total ? set.total : set.n;
+    float maxt = 0.f;
+    for (int k = 0; k < n_parts; ++k) maxt += parts[k].maxt;                 /* NLRay::push_back, vrl_struct.h:23-26 */
+    const Ray first = parts[0];
+    const Pcg32 base = rng;
+    uint64_t evals = 0;
+    for (uint32_t i = 0; i < q; ++i) {
+        Pcg32 cursor = base;
+        if (rng_mode == VRLO_RNG_ADDRESSED) cursor.advance((int64_t) (((uint64_t) i * total + set.first_index) * dpe));
+        for (uint64_t j = 0; j < set.n; ++j) {
+            Vrl vrl = load_vrl(set, j);
+            Pcg32 eval_rng = cursor;
+            Pcg32 *r;
+            if (rng_mode == VRLO_RNG_ADDRESSED) { for (uint64_t k = 0; k < dpe; ++k) cursor.next_u32(); r = &eval_rng; }
+            else r = &rng;
+            Pcg32 sub; sub.seed(eval_rng.state, PCG32_DEFAULT_STREAM + 1);
+            Pcg32 *subp = (rng_mode == VRLO_RNG_ADDRESSED) ? &sub : r;
+            float rrWeight = 1.f;
+            if (rr) {
+                ClosestPointInfo res = find_closest_point(vrl, first);
+                float d2 = squared_norm((first.o + first.d * res.tCam) - (vrl.origin + vrl.direction * res.tVRL));
+                rrWeight = std::min(1 / (std::sqrt(d2) * opt.scale_rr), 1.0f);
+                if (!(rrWeight > r->next_f32())) continue;
+            }
+            /* sampleMC + NLRay::at */
+            float u1 = r->next_f32(), u2 = r->next_f32();
+            float tCam = u1 * maxt, tVRL = u2 * vrl.length;
+            int hit = n_parts - 1; V3 pCam;
+            {
+                float dist = tCam; bool found = false;
+                if (dist < maxt)
+                    for (int k = 0; k < n_parts; ++k) {
+                        if (dist < parts[k].maxt) { hit = k; pCam = parts[k].o + parts[k].d * dist; found = true; break; }
+                        dist -= parts[k].maxt;
+                    }
+                if (!found) { hit = n_parts - 1; pCam = parts[hit].o + parts[hit].d * tCam; }
+            }
+            SamplingInfo si{ pCam, tCam, vrl.origin + vrl.direction * tVRL, tVRL, vrl.length * maxt, true };
+            Ray wi_ray{ first.o, parts[hit].d, first.maxt };
+            V3 contrib = get_contrib_sampled(s, trace, vrl, wi_ray, si, subp);
+            if (rr) contrib = contrib / rrWeight;
+            contrib = contrib * set.scale;
+            ++evals;
+            if (std::isnan(contrib.x) || std::isnan(contrib.y) || std::isnan(contrib.z) ||
+                std::isinf(contrib.x) || std::isinf(contrib.y) || std::isinf(contrib.z))
+                continue;
+            Li32[hit] = Li32[hit] + contrib;
+            Li64[hit][0] += (double) contrib.x; Li64[hit][1] += (double) contrib.y; Li64[hit][2] += (double) contrib.z;
+        }
+    }
+    if (rng_mode == VRLO_RNG_ADDRESSED) { rng = base; rng.advance((int64_t) ((uint64_t) q * total * dpe)); }
+    if (q > 1)
+        for (int k = 0; k < n_parts; ++k) { Li32[k] = Li32[k] / (float) q; for (int c = 0; c < 3; ++c) Li64[k][c] /= (double) q; }
+    return evals;
+}
+
 template <typename F> void parallel_for(uint64_t n, int n_threads, F &&fn) {
     if (n_threads <= 1 || n < 2) { for (uint64_t i = 0; i < n; ++i) fn(i); return; }
     std::atomic<uint64_t> next{ 0 };
@@ -844,6 +919,21 @@ uint64_t vrlo_gather_segments(const vrlo_scene *s, const vrlb_vrlset_desc *vrls,
     std::atomic<uint64_t> evals{ 0 };
     parallel_for(n_segs, n_threads, [&](uint64_t i) {
         const vrlb_segment &sg = segs[i];
+        const uint32_t n_all = sg.sample >> 16;
+        if (n_all > 0) {
+            /* atomic query (use_nl_atomic_query): the record with part 0 evaluates the whole group */
+            if (sg.part != 0) return;
+            std::vector<Ray> parts(n_all);
+            for (uint32_t k = 0; k < n_all; ++k) parts[k] = Ray{ V3(segs[i + k].o), V3(segs[i + k].d), segs[i + k].maxt };
+            std::vector<V3> l32(n_all); std::vector<std::array<double, 3>> l64(n_all);
+            Pcg32 rng{ sg.rng_state, (PCG32_DEFAULT_STREAM << 1) | 1u };
+            evals += query_atomic(*s, *vrls, parts.data(), (int) n_all, *opt, rng_mode, rng, l32.data(), reinterpret_cast<double (*)[3]>(l64.data()));
+            for (uint32_t k = 0; k < n_all; ++k) {
+                if (out_rgb32) { out_rgb32[(i + k) * 3 + 0] = l32[k].x; out_rgb32[(i + k) * 3 + 1] = l32[k].y; out_rgb32[(i + k) * 3 + 2] = l32[k].z; }
+                if (out_rgb64) { out_rgb64[(i + k) * 3 + 0] = l64[k][0]; out_rgb64[(i + k) * 3 + 1] = l64[k][1]; out_rgb64[(i + k) * 3 + 2] = l64[k][2]; }
+            }
+            return;
+        }
         Ray ray{ V3(sg.o), V3(sg.d), sg.maxt };
         Pcg32 rng{ sg.rng_state, (PCG32_DEFAULT_STREAM << 1) | 1u };
         V3 li; double li64[3];
@@ -955,7 +1045,7 @@ inline V3 nl_bend(const vrlb_medium &m, V3 p, V3 dir, float ds) {
 }
 
 /* What one camera sample hands to the VRL query */
-struct PartOut { Ray ray; V3 weight; int medium; uint32_t part; };
+struct PartOut { Ray ray; V3 weight; int medium; uint32_t part; const Ray *all = nullptr; int n_all = 0; };   /* n_all > 0: one query over the whole NLRay (use_nl_atomic_query) */
 
 struct SampleResult { V3 radiance; bool valid_ray; };
 
@@ -1000,6 +1090,8 @@ SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler 
                 V3 pstart = ro, pos = ro, dir = rd, dir0 = rd;
                 float total = 0.f, step_mint = rmint, ds = nl_step(m); uint32_t part = 0; bool found = false;
                 Hit hit{ kInf, 0, 0, -1 };
+                const bool atomic = opt.use_nl_atomic_query != 0;      /* vrl.cpp:613-617: one query over all parts */
+                std::vector<Ray> all;
                 for (int step = 0; step < 100000; ++step) {
                     hit = ray_intersect(s, pos, dir, step_mint, ds);
                     step_mint = 0.f;
@@ -1008,8 +1100,11 @@ SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler 
                     V3 nd = nl_bend(m, pos, dir, ds);
                     if (dot(nd, dir0) < kNlPartCos) {
                         V3 chord = pos - pstart; float len = norm(chord);
-                        V3 Li = on_query(PartOut{ Ray{ pstart, chord / len, len }, vrlThroughput, medium, part++ }, sampler);
-                        indirect = indirect + Li * vrlThroughput;
+                        if (atomic) all.push_back(Ray{ pstart, chord / len, len });
+                        else {
+                            V3 Li = on_query(PartOut{ Ray{ pstart, chord / len, len }, vrlThroughput, medium, part++ }, sampler);
+                            indirect = indirect + Li * vrlThroughput;
+                        }
                         vrlThroughput = vrlThroughput * homo_transmittance(m, 0.f, len);
                         total = total + len;
                         pstart = pos; dir0 = nd;
@@ -1019,9 +1114,16 @@ SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler 
                 if (!found) { si = Hit{ kInf, 0, 0, -1 }; radiance = radiance + indirect; break; }
                 V3 chord = pos - pstart; float len = norm(chord);
                 if (len > 0.f) {
-                    V3 Li = on_query(PartOut{ Ray{ pstart, chord / len, len }, vrlThroughput, medium, part++ }, sampler);
-                    indirect = indirect + Li * vrlThroughput;
+                    if (atomic) all.push_back(Ray{ pstart, chord / len, len });
+                    else {
+                        V3 Li = on_query(PartOut{ Ray{ pstart, chord / len, len }, vrlThroughput, medium, part++ }, sampler);
+                        indirect = indirect + Li * vrlThroughput;
+                    }
                     total = total + len;
+                }
+                if (atomic && !all.empty()) {
+                    V3 Li = on_query(PartOut{ all[0], throughput, medium, 0u, all.data(), (int) all.size() }, sampler);
+                    indirect = indirect + Li * throughput;                                /* vrl.cpp:617 */
                 }
                 throughput = throughput * homo_transmittance(m, 0.f, total);             /* vrl.cpp:631 */
                 si = hit; rd = dir; needs_intersection = false;
@@ -1130,6 +1232,22 @@ uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const 
             uint32_t bid = ids[(size_t) by * nbx + bx];
             for (uint32_t i = 0; i < (uint32_t) (opt->block_size * opt->block_size); ++i) {
                 auto on_query = [&](const PartOut &p, Sampler &smp, int px, int py, int j) {
+                    if (p.n_all > 0) {
+                        /* atomic query: the parts as consecutive records sharing the query's stream position;
+                         * sample = j | n_parts << 16 (include/vrl_b200.h, vrlb_segment) */
+                        for (int k = 0; k < p.n_all; ++k, ++n) {
+                            if (n >= cap) continue;
+                            vrlb_segment &g = segs[n]; const Ray &r = p.all[k];
+                            g.o[0] = r.o.x; g.o[1] = r.o.y; g.o[2] = r.o.z; g.maxt = r.maxt;
+                            g.d[0] = r.d.x; g.d[1] = r.d.y; g.d[2] = r.d.z;
+                            g.pixel = (uint32_t) (py * cam->width + px);
+                            g.weight[0] = p.weight.x; g.weight[1] = p.weight.y; g.weight[2] = p.weight.z;
+                            g.medium = p.medium; g.rng_state = smp.rng.state;
+                            g.sample = (uint32_t) j | ((uint32_t) p.n_all << 16); g.part = (uint32_t) k;
+                        }
+                        smp.rng.advance((int64_t) ((uint64_t) q * n_vrls_total * dpe));
+                        return V3(0.f);
+                    }
                     if (n < cap) {
                         vrlb_segment &g = segs[n];
                         g.o[0] = p.ray.o.x; g.o[1] = p.ray.o.y; g.o[2] = p.ray.o.z; g.maxt = p.ray.maxt;
@@ -1177,6 +1295,14 @@ uint64_t vrlo_render(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_opt
             if (px < cx0 || py < cy0 || px >= cx1 || py >= cy1) continue;
             auto on_query = [&](const PartOut &p, Sampler &smp, int, int, int) {
                 V3 li; double li64[3];
+                if (p.n_all > 0) {
+                    std::vector<V3> l32((size_t) p.n_all); std::vector<std::array<double, 3>> l64((size_t) p.n_all);
+                    local += query_atomic(*s, *vrls, p.all, p.n_all, *opt, rng_mode, smp.rng, l32.data(),
+                                          reinterpret_cast<double (*)[3]>(l64.data()));
+                    li = V3(0.f);
+                    for (const V3 &v : l32) li = li + v;
+                    return li;
+                }
                 local += query(*s, *vrls, p.ray, *opt, rng_mode, smp.rng, li, li64);
                 return li;
             };

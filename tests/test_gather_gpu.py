@@ -82,6 +82,45 @@ def test_hg_rr_q2_match_oracle(ctx, math_mode):
     assert err.max() <= REL_TOL, f"{err.max():.3e}"
 
 
+@pytest.mark.parametrize("rr,q", [(0, 1), (1, 2)])
+def test_nl_atomic_query_matches_oracle(ctx, rr, q):
+    """use_nl_atomic_query (vrl.cpp:613-617): ONE uniform-sampled query over the whole curved camera path.  The parts
+    of a sample are consecutive records that share the query's stream position (sample = j | n_parts << 16); every
+    eval lands on exactly one part (NLRay::at), the distance roulette is measured from the first part."""
+    sc = scenes.nl_fog_scene(occluders=True, res_y=160, top_ior=0.8)
+    cam = scenes.box_fog_camera(32, 18)
+    opt = scenes.default_options(visibility=1, use_nl_atomic_query=1, rr_vrl=rr, samples_per_query=q)
+    soa = scenes.synthetic_vrls(600, seed=12)
+    vd = scenes.vrlset_desc(soa)
+    osc = oracle.OracleScene(sc)
+    ref_segs, _, _ = osc.build_segments(cam, opt, soa.shape[1], cap=32 * 18 * 200)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(vd)
+    n = ctx.build_segments(cam, opt)
+    assert n == len(ref_segs) and n > 3 * 32 * 18
+    segs = ctx.download_segments()
+    key = lambda s: np.lexsort((s["part"], s["sample"], s["pixel"]))
+    a, b = segs[key(segs)], ref_segs[key(ref_segs)]
+    for f in ("pixel", "sample", "part", "medium", "rng_state", "o", "d", "maxt", "weight"):
+        assert np.array_equal(a[f], b[f]), f
+    assert (segs["sample"] >> 16).min() >= 1
+    first = segs["part"] == 0
+    groups = np.cumsum(first) - 1                                # records of a sample are consecutive, part 0 first
+    assert np.array_equal(segs["rng_state"], segs["rng_state"][first][groups])
+    assert np.array_equal(np.bincount(groups), (segs["sample"] >> 16)[first])
+    li = ctx.gather_segments(opt).astype(np.float64)
+    o32, o64, ev = osc.gather(vd, segs, opt)
+    assert o64.max() > 0
+    got, ref = np.zeros((32 * 18, 3)), np.zeros((32 * 18, 3))
+    np.add.at(got, segs["pixel"], li * segs["weight"])
+    np.add.at(ref, segs["pixel"], o64 * segs["weight"])
+    assert rel_err(got, ref).max() <= REL_TOL
+    assert np.quantile(rel_err(li, o64), 0.99) <= REL_TOL       # an eval on a part boundary may land on the neighbour
+    out = ctx.render(cam, opt, vd)
+    ref_xyzaw, _, _ = osc.render(cam, opt, vd)
+    assert rel_err(out[..., :3].astype(np.float64), ref_xyzaw[..., :3].astype(np.float64)).max() <= 2e-4
+
+
 @pytest.mark.parametrize("occluders,vis,uniform,rr,math_mode", [(False, 0, 0, 0, 0), (True, 1, 0, 0, 1), (True, 1, 1, 1, 0)])
 def test_grid_medium_matches_oracle(ctx, occluders, vis, uniform, rr, math_mode):
     """Grid (heterogeneous) medium, SURVEY 8a a8-a10: trilinear sigma_s at both points and the reference's stochastic
