@@ -339,7 +339,7 @@ def synthetic_vrls(n, seed=1, sigma_t=0.11, albedo=0.909, box=BOX):
 
 
 def vrlset_desc(soa10, scale=None, first_index=0, total=None, medium=None):
-    """Builds a vrlb_vrlset_desc over a [10, n] fp32 array (kept alive by the caller)."""
+    """Builds a vrlb_vrlset_desc over a [10, n] fp32 array; the descriptor keeps the arrays alive."""
     assert soa10.dtype == np.float32 and soa10.flags["C_CONTIGUOUS"] and soa10.shape[0] == 10
     n = soa10.shape[1]
     d = abi.VrlSetDesc()
@@ -347,6 +347,7 @@ def vrlset_desc(soa10, scale=None, first_index=0, total=None, medium=None):
     d.medium = medium.ctypes.data_as(C.POINTER(C.c_uint16)) if medium is not None else None
     d.n, d.first_index, d.total = n, first_index, (total if total is not None else n)
     d.scale = (1.0 / d.total) if scale is None else scale
+    d._keep = (soa10, medium)          # the C struct only holds raw pointers
     return d
 
 
