@@ -273,6 +273,16 @@ int  vrlb_film_resolve(vrlb_context *ctx, void **dev_xyzaw);
  *      microkernel (roofline denominator of the gather).  tflops = 2 flops per FMA. ---- */
 int  vrlb_measure_fp32_peak(vrlb_context *ctx, float *tflops);
 
+/* ---- diagnostic, host only (no device needed): the shadow-query structure the library builds for a mesh.
+ *      Solids are the connected components that get conservative proxies (mitsuba-nlvrl_b200/csrc/
+ *      occluder_proxies.cpp); each is written as VRLB_SOLID_WORDS 32-bit words:
+ *      aabb lo[3] hi[3] | u32 root | u32 flags (1 outer box, 2 inscribed sphere, 4 inscribed box) |
+ *      bounding sphere c[3] r^2 | inscribed sphere c[3] r^2 | box axes[9] (rows) | box centre[3] |
+ *      outer half extents[3] | inscribed half extents[3].  counts[0] = solids, counts[1] = shells,
+ *      counts[2] = triangles left in the main BVH. ---- */
+#define VRLB_SOLID_WORDS 34
+int  vrlb_shadow_proxies(const float *tri_verts, uint32_t n_tris, float *solids_out, uint32_t cap_solids, uint32_t counts[3]);
+
 int  vrlb_cancel(vrlb_context *ctx);
 int  vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out);
 int  vrlb_synchronize(vrlb_context *ctx);

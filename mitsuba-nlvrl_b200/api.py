@@ -20,8 +20,24 @@ EXPORTS = [
     "vrlb_film_device_ptr", "vrlb_film_download_xyzaw", "vrlb_film_download_rgb", "vrlb_render", "vrlb_cancel",
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
-    "vrlb_vrls_download_depth",
+    "vrlb_vrls_download_depth", "vrlb_shadow_proxies",
 ]
+
+
+SOLID_DTYPE = np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("root", "<u4"), ("flags", "<u4"), ("c", "<f4", 3), ("r_out2", "<f4"),
+                        ("ci", "<f4", 3), ("r_in2", "<f4"), ("ax", "<f4", (3, 3)), ("oc", "<f4", 3), ("h_out", "<f4", 3), ("h_in", "<f4", 3)])
+
+
+def shadow_proxies(tri_verts):
+    """Host-only diagnostic (vrlb_shadow_proxies): (solids as a SOLID_DTYPE array, n_shells, n_main_tris)."""
+    v = np.ascontiguousarray(tri_verts, np.float32).reshape(-1)
+    out = np.zeros(8, SOLID_DTYPE)
+    counts = (C.c_uint32 * 3)()
+    rc = load_library().vrlb_shadow_proxies(v.ctypes.data_as(C.POINTER(C.c_float)), v.size // 9,
+                                            out.ctypes.data_as(C.POINTER(C.c_float)), len(out), counts)
+    if rc != abi.OK:
+        raise VrlbError(rc, "vrlb_shadow_proxies failed")
+    return out[:counts[0]], int(counts[1]), int(counts[2])
 
 
 class VrlbError(RuntimeError):
@@ -80,6 +96,7 @@ def load_library():
     L.vrlb_vrls_scale.argtypes = [vp]
     L.vrlb_vrls_scale.restype = C.c_float
     L.vrlb_vrls_download_depth.argtypes = [vp, C.POINTER(C.c_int32), C.c_uint64]
+    L.vrlb_shadow_proxies.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     _lib = L
     return L
 

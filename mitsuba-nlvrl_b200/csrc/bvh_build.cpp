@@ -224,7 +224,7 @@ void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, S
             root_ref = w.empty() ? (0x80000000u | (tri0 << 12) | ((uint32_t) tris.size() << 7)) : node0;
         }
         if (s == 0) {
-            out.main_root = root_ref; out.has_main = !sub.empty();
+            out.main_root = root_ref; out.has_main = !sub.empty(); out.n_main_tris = (uint32_t) sub.size();
             Box mb; for (uint32_t t : sub) { const float *p = verts + (size_t) t * 9; mb.grow(p); mb.grow(p + 3); mb.grow(p + 6); }
             if (!sub.empty()) for (int k = 0; k < 3; ++k) { out.main_lo[k] = mb.lo[k] - margin; out.main_hi[k] = mb.hi[k] + margin; }
         }

@@ -21,6 +21,7 @@ struct ShadowAccel {
     uint32_t main_root = 0x80000000u;
     float    main_lo[3] = { 0, 0, 0 }, main_hi[3] = { 0, 0, 0 };
     bool     has_main = false;
+    uint32_t n_main_tris = 0;
 };
 // proxies of one component (triangle indices `sub` into verts); fills everything but `root`
 void build_solid_proxies(const float *verts, const std::vector<uint32_t> &sub, float margin, DSolid &out);

@@ -211,6 +211,19 @@ int vrlb_synchronize(vrlb_context *ctx) {
     return VRLB_OK;
 }
 
+int vrlb_shadow_proxies(const float *tri_verts, uint32_t n_tris, float *solids_out, uint32_t cap_solids, uint32_t counts[3]) {
+    static_assert(sizeof(DSolid) == VRLB_SOLID_WORDS * 4, "DSolid layout is part of the diagnostic ABI");
+    if ((n_tris && !tri_verts) || !counts) return VRLB_ERR_INVALID;
+    ShadowAccel sa; build_shadow_accel(tri_verts, nullptr, n_tris, sa);
+    counts[0] = (uint32_t) sa.solids.size(); counts[1] = (uint32_t) sa.shells.size();
+    counts[2] = n_tris;
+    // triangles not in the main BVH: recount from the leaf references is overkill; shells + solids own the rest
+    if (solids_out)
+        for (size_t i = 0; i < sa.solids.size() && i < cap_solids; ++i) std::memcpy(solids_out + i * VRLB_SOLID_WORDS, &sa.solids[i], sizeof(DSolid));
+    counts[2] = sa.n_main_tris;
+    return VRLB_OK;
+}
+
 int vrlb_cancel(vrlb_context *ctx) { if (!ctx) return VRLB_ERR_INVALID; ctx->cancel.store(1); return VRLB_OK; }
 
 int vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out) {
