@@ -2,8 +2,13 @@
 // the reference: load -> preprocess -> render -> film).  Usage:
 //   vrl_host render <scene.vrls> <set.vrlb> <out.f32> [key=value ...]     integrator properties as key=value
 //   vrl_host selftest                                                     property / error behaviour, no GPU needed
+//   vrl_host vol-info <file.vol> | obj-info <file.obj>                     the loaders of vrl_io.h (no GPU needed)
+// An output name ending in .pfm receives the developed film (XYZ / W -> linear sRGB, hdrfilm.cpp:259-262) instead of
+// the raw XYZAW floats.
 // scene.vrls (test harness dump, written by tests/): u32 n_tris | verts | flags | u32 n_media | vrlb_medium[] |
 // u32 n_emitters | vrlb_emitter[] | vrlb_camera | i32 spp | u64 seed.
+#include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -11,6 +16,7 @@
 #include <iostream>
 
 #include "vrl_integrator.h"
+#include "vrl_io.h"
 using namespace vrlhost;
 
 static void set_kv(Properties &p, const std::string &kv) {
@@ -47,6 +53,22 @@ static int selftest() {
       s.save("/tmp/_vrlb_selftest.vrlb"); VrlSet t; t.load("/tmp/_vrlb_selftest.vrlb");
       bool ok = t.n == 3 && t.scale == 0.25f && t.soa10 == s.soa10 && t.medium == s.medium;
       std::printf("%s VRLB file round trip\n", ok ? "ok  " : "FAIL"); fails += !ok; }
+    { VolumeGrid g; g.nx = 2; g.ny = 3; g.nz = 2; g.data.resize(12); for (int i = 0; i < 12; ++i) g.data[i] = 0.5f * (float) i; g.bbox_max[1] = 2.f;
+      write_vol("/tmp/_vol_selftest.vol", g); VolumeGrid h = read_vol("/tmp/_vol_selftest.vol");
+      bool ok = h.nx == 2 && h.ny == 3 && h.nz == 2 && h.data == g.data && h.max == 5.5f && h.bbox_max[1] == 2.f;
+      std::printf("%s .vol round trip\n", ok ? "ok  " : "FAIL"); fails += !ok; }
+    expect_throw("bad .vol header", [] { std::ofstream("/tmp/_vol_bad.vol") << "VOX"; read_vol("/tmp/_vol_bad.vol"); }, "Invalid volume file");
+    { std::ofstream("/tmp/_obj_selftest.obj") << "v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nvn 0 0 1\nf 1//1 2//1 3//1 4//1\n";
+      std::vector<float> t = read_obj("/tmp/_obj_selftest.obj");
+      bool ok = t.size() == 18 && t[3] == 1.f && t[9] == 0.f && t[12] == 1.f && t[13] == 1.f && t[15] == 0.f && t[16] == 1.f;   // quad fanned: (1,2,3) (1,3,4)
+      std::printf("%s OBJ quad is fanned into two triangles\n", ok ? "ok  " : "FAIL"); fails += !ok; }
+    expect_throw("OBJ invalid index", [] { std::ofstream("/tmp/_obj_bad.obj") << "v 0 0 0\nf 1 2 3\n"; read_obj("/tmp/_obj_bad.obj"); }, "reference to invalid vertex");
+    { std::vector<float> x = { 0.412453f, 0.212671f, 0.019334f, 1.f, 2.f, 0, 0, 0, 0, 0 };      // pixel 0 = XYZ of pure red, twice weighted
+      x[0] *= 2; x[1] *= 2; x[2] *= 2;
+      std::vector<float> rgb = develop_rgb(x, 2, 1);
+      bool ok = std::fabs(rgb[0] - 1.f) < 1e-4f && std::fabs(rgb[1]) < 1e-4f && std::fabs(rgb[2]) < 1e-4f && rgb[3] == 0.f;
+      write_pfm("/tmp/_pfm_selftest.pfm", rgb, 2, 1);
+      std::printf("%s develop XYZ/W -> sRGB + PFM\n", ok ? "ok  " : "FAIL"); fails += !ok; }
     std::printf("%s\n", fails ? "SELFTEST FAILED" : "SELFTEST PASSED");
     return fails ? 1 : 0;
 }
@@ -54,6 +76,19 @@ static int selftest() {
 int main(int argc, char **argv) {
     try {
         if (argc >= 2 && std::string(argv[1]) == "selftest") return selftest();
+        if (argc == 3 && std::string(argv[1]) == "vol-info") {
+            VolumeGrid g = read_vol(argv[2]);
+            std::printf("shape %d %d %d channels %d bbox %.9g %.9g %.9g %.9g %.9g %.9g max %.9g mean %.9g\n", g.nx, g.ny, g.nz, g.channels,
+                        g.bbox_min[0], g.bbox_min[1], g.bbox_min[2], g.bbox_max[0], g.bbox_max[1], g.bbox_max[2], g.max, g.mean);
+            return 0;
+        }
+        if (argc == 3 && std::string(argv[1]) == "obj-info") {
+            std::vector<float> t = read_obj(argv[2]);
+            double lo[3] = { 1e300, 1e300, 1e300 }, hi[3] = { -1e300, -1e300, -1e300 }, sum = 0;
+            for (size_t i = 0; i < t.size(); ++i) { lo[i % 3] = std::min(lo[i % 3], (double) t[i]); hi[i % 3] = std::max(hi[i % 3], (double) t[i]); sum += t[i]; }
+            std::printf("triangles %zu bbox %.9g %.9g %.9g %.9g %.9g %.9g checksum %.9g\n", t.size() / 9, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], sum);
+            return 0;
+        }
         if (argc < 5 || std::string(argv[1]) != "render") { std::fprintf(stderr, "usage: vrl_host render scene.vrls set.vrlb out.f32 [k=v ...] | selftest\n"); return 2; }
         HostScene sc; HostSensor se;
         std::ifstream f(argv[2], std::ios::binary);
@@ -75,8 +110,13 @@ int main(int argc, char **argv) {
         integrator.preprocess(sc, se);
         std::vector<float> film;
         bool ok = integrator.render(sc, se, film);
-        std::ofstream o(argv[4], std::ios::binary);
-        o.write((const char *) film.data(), (std::streamsize) (film.size() * 4));
+        std::string out = argv[4];
+        if (out.size() > 4 && out.substr(out.size() - 4) == ".pfm")
+            write_pfm(out, develop_rgb(film, se.camera.width, se.camera.height), se.camera.width, se.camera.height);
+        else {
+            std::ofstream o(out, std::ios::binary);
+            o.write((const char *) film.data(), (std::streamsize) (film.size() * 4));
+        }
         return ok ? 0 : 3;
     } catch (const std::exception &e) {                    // mitsuba.cpp:251-255: exceptions end the run with a message
         std::fprintf(stderr, "Caught a critical exception: %s\n", e.what());

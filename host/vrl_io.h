@@ -1,0 +1,32 @@
+// vrl_io.h -- file formats either side of the path, host side, no Mitsuba dependency:
+//   * Mitsuba binary grid volumes `.vol` (src/textures/volume_data.h:42-107: "VOL", u8 version 3, i32 type 1 = fp32,
+//     i32 nx ny nz, i32 channels, 6 x f32 bbox, data with x fastest and channels innermost, grid3d.cpp:291);
+//   * Wavefront OBJ meshes as the fixtures use them (v / f records, polygons fanned, negative indices; normals and
+//     texture coordinates are parsed past -- the gather only needs positions, src/shapes/obj.cpp);
+//   * the developed film: HDRFilm::develop divides XYZ by W and converts XYZ -> linear sRGB (hdrfilm.cpp:259-262,
+//     include/mitsuba/core/spectrum.h:229-235); written as a PFM image (the EXR container stays with the host film).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace vrlhost {
+
+struct VolumeGrid {
+    int32_t nx = 0, ny = 0, nz = 0, channels = 1;
+    float bbox_min[3] = { 0, 0, 0 }, bbox_max[3] = { 1, 1, 1 };
+    std::vector<float> data;        // ((z * ny + y) * nx + x) * channels + c
+    float  max = 0.f;               // VolumeMetadata::max  (the majorant before `scale`)
+    double mean = 0.0;              // VolumeMetadata::mean
+};
+VolumeGrid read_vol(const std::string &path);                    // throws std::runtime_error with the reference's messages
+void write_vol(const std::string &path, const VolumeGrid &g);
+
+// triangles as 9 floats each (p0 p1 p2), `to_world` = optional row-major 4x4 applied to the positions
+std::vector<float> read_obj(const std::string &path, const float *to_world = nullptr);
+
+// XYZAW (5 floats / pixel) -> linear sRGB (3 floats / pixel); pixels with W = 0 stay black
+std::vector<float> develop_rgb(const std::vector<float> &xyzaw, int width, int height);
+void write_pfm(const std::string &path, const std::vector<float> &rgb, int width, int height);   // top row first in `rgb`
+
+}  // namespace vrlhost

@@ -378,6 +378,56 @@ def load_vrlb(path):
     return soa, scale, med
 
 
+def load_vol(path):
+    """Mitsuba binary grid volume (src/textures/volume_data.h:42-107) -> (grid [nz, ny, nx(, c)], bbox_min, bbox_max)."""
+    import struct
+    with open(path, "rb") as f:
+        hdr = f.read(4)
+        if hdr[:3] != b"VOL":
+            raise ValueError(f"Invalid volume file {path}")
+        if hdr[3] != 3:
+            raise ValueError(f"Invalid version, currently only version 3 is supported (found {hdr[3]})")
+        typ, nx, ny, nz, ch = struct.unpack("<5i", f.read(20))
+        if typ != 1:
+            raise ValueError(f"Wrong type, currently only type == 1 (Float32) data is supported (found type = {typ})")
+        bbox = struct.unpack("<6f", f.read(24))
+        data = np.frombuffer(f.read(4 * nx * ny * nz * ch), "<f4")
+    if data.size != nx * ny * nz * ch:
+        raise ValueError(f"Unexpected end of volume file {path}")
+    grid = data.reshape((nz, ny, nx, ch)) if ch > 1 else data.reshape((nz, ny, nx))
+    return grid.astype(np.float32), np.array(bbox[:3], np.float32), np.array(bbox[3:], np.float32)
+
+
+def save_vol(path, grid, bbox_min, bbox_max):
+    import struct
+    g = np.ascontiguousarray(grid, np.float32)
+    ch = g.shape[3] if g.ndim == 4 else 1
+    with open(path, "wb") as f:
+        f.write(b"VOL\x03" + struct.pack("<5i", 1, g.shape[2], g.shape[1], g.shape[0], ch))
+        f.write(struct.pack("<6f", *[float(x) for x in bbox_min], *[float(x) for x in bbox_max]))
+        f.write(g.tobytes())
+
+
+def load_obj(path, to_world=None):
+    """Wavefront OBJ -> [n, 3, 3] triangles; polygons are fanned (v0, v_{k-1}, v_k) like src/shapes/obj.cpp:256-262."""
+    pos, tris = [], []
+    with open(path) as f:
+        for line in f:
+            s = line.split()
+            if not s:
+                continue
+            if s[0] == "v":
+                pos.append([float(s[1]), float(s[2]), float(s[3])])
+            elif s[0] == "f":
+                idx = [int(tok.split("/")[0]) for tok in s[1:]]
+                if any(i < 1 or i > len(pos) for i in idx):
+                    raise ValueError(f"{path}: reference to invalid vertex")
+                for k in range(2, len(idx)):
+                    tris.append([pos[idx[0] - 1], pos[idx[k - 1] - 1], pos[idx[k] - 1]])
+    t = np.asarray(tris, np.float32).reshape(-1, 3, 3)
+    return transform_tris(t, to_world) if to_world is not None else t
+
+
 def save_scene_dump(path, scene, cam, spp=1, seed=0):
     """Test-harness scene dump read by host/vrl_host (vrl_host_main.cpp)."""
     import struct

@@ -44,6 +44,45 @@ def test_vrlb_file_round_trip(tmp_path):
     assert np.array_equal(got, soa) and scale == 0.125 and med.shape == (100,)
 
 
+def test_vol_and_obj_loaders_agree_between_host_and_python(tmp_path):
+    """`.vol` (volume_data.h:42-107) and OBJ (obj.cpp) readers: C++ host (vrl_io.cpp) against the Python mirror."""
+    grid = scenes.smoke_grid((12, 7, 9))
+    scenes.save_vol(tmp_path / "g.vol", grid, (-1, -2, -3), (1, 2, 3))
+    g2, lo, hi = scenes.load_vol(tmp_path / "g.vol")
+    assert np.array_equal(g2, grid) and list(lo) == [-1, -2, -3] and list(hi) == [1, 2, 3]
+    out = subprocess.run([_build(), "vol-info", str(tmp_path / "g.vol")], capture_output=True, text=True).stdout.split()
+    assert out[1:4] == ["12", "7", "9"] and out[5] == "1"
+    assert abs(float(out[out.index("max") + 1]) - grid.max()) < 1e-6 and abs(float(out[out.index("mean") + 1]) - grid.astype(np.float64).mean()) < 1e-6
+    (tmp_path / "q.obj").write_text("# cube face\nv 0 0 0\nv 2 0 0\nv 2 2 0\nv 0 2 0\nv 1 3 0\nvt 0 0\nf 1/1 2/1 3/1 4/1 5/1\n")
+    tris = scenes.load_obj(tmp_path / "q.obj")
+    assert tris.shape == (3, 3, 3) and np.array_equal(tris[2], [[0, 0, 0], [0, 2, 0], [1, 3, 0]])
+    out = subprocess.run([_build(), "obj-info", str(tmp_path / "q.obj")], capture_output=True, text=True).stdout.split()
+    assert out[1] == "3" and abs(float(out[out.index("checksum") + 1]) - tris.astype(np.float64).sum()) < 1e-6
+    with pytest.raises(ValueError):
+        (tmp_path / "bad.vol").write_bytes(b"VOL\x02" + b"\0" * 64)
+        scenes.load_vol(tmp_path / "bad.vol")
+
+
+REF_DATA = "/root/reference/data"
+
+
+@pytest.mark.skipif(not os.path.exists(REF_DATA + "/hetvol/smoke.vol"), reason="reference fixtures only exist in the build container")
+def test_loaders_read_the_reference_fixtures():
+    """data/hetvol/smoke.vol is the 128 x 128 x 50 grid SURVEY 8d names; bounds.obj its bounding box."""
+    grid, lo, hi = scenes.load_vol(REF_DATA + "/hetvol/smoke.vol")
+    assert grid.shape == (50, 128, 128) and grid.max() == 1.0
+    out = subprocess.run([_build(), "vol-info", REF_DATA + "/hetvol/smoke.vol"], capture_output=True, text=True).stdout.split()
+    assert out[1:4] == ["128", "128", "50"] and abs(float(out[out.index("mean") + 1]) - grid.astype(np.float64).mean()) < 1e-8
+    tris = scenes.load_obj(REF_DATA + "/hetvol/bounds.obj")
+    assert tris.shape == (12, 3, 3) and np.allclose(tris.reshape(-1, 3).min(0), lo, atol=1e-5) and np.allclose(tris.reshape(-1, 3).max(0), hi, atol=1e-5)
+    # the grid as a medium of the C ABI: majorant = scale * max (heterogeneous.cpp:29)
+    m = scenes.make_medium(kind=scenes.abi.MEDIUM_GRID, scale=100.0)
+    sc = scenes.Scene()
+    m.grid_bbox_min[:], m.grid_bbox_max[:] = list(lo), list(hi)
+    sc.add_medium(m, grid=grid)
+    assert sc.media[0].grid_max == 1.0 and list(sc.media[0].grid_res) == [128, 128, 50]
+
+
 def test_host_render_without_gpu_fails_loudly(tmp_path):
     import torch
     if torch.cuda.is_available():
