@@ -20,7 +20,7 @@ def main():
         data = json.loads(out)
         with open(os.path.join(GOLD, "ref_vrl_struct.json"), "w") as f:
             json.dump(data, f)
-        print("wrote ref_vrl_struct.json:", {k: len(v) for k, v in data.items()})
+        print("wrote ref_vrl_struct.json:", {k: (len(v) if hasattr(v, "__len__") else v) for k, v in data.items()})
 
 if __name__ == "__main__":
     sys.exit(main())

@@ -5,11 +5,14 @@
  * -ffp-contract=off) of the VRL gather hot path of VincentiusIV/mitsuba-NLVRL.  Only tests/,
  * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this.
  *
- * PARITY STATUS: the reference ships no golden vector or test for the VRL path.
- * Pins that DO exist and are checked in tests/: the PCG32 stream (against Enoki's own
- * random.h compiled into oracle/_ref), isotropic eval == 1/(4 pi), and the reference's own
- * vrl_struct.h functions compiled against a mock Mitsuba (oracle/_ref/refprobe, see
- * oracle/ref_probe.cpp).  Everything else is "parity unpinned" in the sense of the task text.
+ * PARITY STATUS: pinned for the homogeneous-medium gather.  The reference's own vrl_struct.h is compiled in
+ * place against a mock Mitsuba (oracle/ref_probe.cpp + ref_mock.h -> oracle/_ref/refprobe) and its outputs
+ * for findClosetPoint / samplingVRL / evalTransmittance / getContrib / sequential-stream query sums are the
+ * fixture tests/golden/ref_vrl_struct.json, which tests/test_ref_golden_cpu.py holds this file to (closest
+ * point bit-exact, getContrib within 3.5e-7).  The PCG32 stream is pinned by tests/golden/enoki_pcg32.json
+ * (Enoki's random.h compiled into oracle/_ref/enoki_probe).  "Parity unpinned" still applies to the grid-medium
+ * stochastic transmittance, the camera-segment construction and VRL generation: no reference code could be
+ * run for those.
  *
  * Input structs are the public ABI PODs of include/vrl_b200.h (interface only).
  */

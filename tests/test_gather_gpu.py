@@ -218,3 +218,45 @@ def test_nonlinear_camera_parts_match_oracle(ctx, math_mode):
     ref_xyzaw, _, _ = osc.render(cam, opt, vd)
     assert np.array_equal(out[..., 3:], ref_xyzaw[..., 3:])
     assert rel_err(out[..., :3].astype(np.float64), ref_xyzaw[..., :3].astype(np.float64)).max() <= 2e-4
+
+
+@pytest.mark.parametrize("math_mode", [0, 1])
+def test_gather_matches_reference_compiled_golden(ctx, math_mode):
+    """CUDA gather against outputs of the REFERENCE'S OWN getContrib (tests/golden/ref_vrl_struct.json, made by
+    oracle/_ref/refprobe = src/integrators/vrl/vrl_struct.h compiled in place): 96 VRLs, q = 1/2, importance and
+    uniform sampling, with and without occluders.  Only the golden queries whose sequential stream consumed the full
+    2 draws per eval are used (no early-out), where addressed == sequential stream positions."""
+    import ctypes as C
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_vrl_struct.json")) as f:
+        gold = json.load(f)
+    soa = np.ascontiguousarray(np.array(gold["query_vrls"], np.float32).T)
+    vd = scenes.vrlset_desc(soa, scale=gold["query_scale"])
+    m = gold["medium"]
+    used = 0
+    for c in gold["query"]:
+        if c["draws"] != 2 * c["samples"] * soa.shape[1]:
+            continue
+        used += 1
+        sc = scenes.Scene()
+        sc.add_medium(scenes.make_medium(sigma_t=m["sigma_t"], albedo=m["albedo"], scale=m["scale"]))
+        if c["vis"]:
+            sc.add_tris(np.array(gold["triangles"], np.float32).reshape(-1, 3, 3), abi.SURF_BSDF_SMOOTH)
+        opt = scenes.default_options(samples_per_query=c["samples"], use_uniform_sampling=c["uniform"],
+                                     visibility=c["vis"], math_mode=math_mode)
+        st, inc = C.c_uint64(), C.c_uint64()
+        oracle.lib().vrlo_pcg32_seed(c["seed"], 0xda3e39cb94b95bdb, C.byref(st), C.byref(inc))
+        seg = np.zeros(1, abi.SEGMENT_DTYPE)
+        r = np.array(c["ray"], np.float32)
+        seg["o"][0], seg["d"][0], seg["maxt"][0] = r[0:3], r[3:6], r[6]
+        seg["weight"][0] = 1.0
+        seg["rng_state"][0] = st.value
+        ctx.set_scene(sc)
+        ctx.upload_vrls(vd)
+        ctx.upload_segments(seg, 1, 1)
+        li = ctx.gather_segments(opt)
+        want = np.array(c["out"], np.float64)
+        err = np.abs(li[0] - want) / np.abs(want)
+        assert err.max() <= REL_TOL, (c["seed"], math_mode, li[0], want)
+    assert used >= 6

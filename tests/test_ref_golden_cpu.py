@@ -1,0 +1,155 @@
+"""CPU suite (-m "not gpu"): pins the oracle's VRL maths against outputs of the REFERENCE'S OWN code.
+
+tests/golden/ref_vrl_struct.json was produced by oracle/_ref/refprobe = the reference's
+src/integrators/vrl/vrl_struct.h compiled where it lies (against the mock Mitsuba of oracle/ref_mock.h and the
+reference's vendored Enoki; generator oracle/ref_probe.cpp + oracle/make_golden.py).  It holds, with their inputs:
+  closest        VRL::findClosetPoint      vrl_struct.h:163-228
+  sampling       VRL::samplingVRL          vrl_struct.h:239-360   (+ how many sampler draws each call consumed)
+  transmittance  VRL::evalTransmittance    vrl_struct.h:509-572
+  contrib        VRL::getContrib           vrl_struct.h:584-662
+  query          getContrib summed over a VRL list on one sequential stream (vrl_map.h:151-169)
+
+Tolerances: findClosetPoint is pure +,*,/ in the same order -> bit-exact.  Everything that goes through
+log/sinh/atan/tan/exp is compared at 2e-5 relative: the reference evaluates Enoki's polynomial approximations,
+the oracle glibc's correctly-rounded-ish libm, and the inverse CDFs amplify an ulp of difference (the north-star
+tolerance on the image is 1e-4)."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from mitsuba_nlvrl_b200 import abi, scenes
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_vrl_struct.json")
+RTOL = 2e-5
+
+
+def _num(x):
+    return float(x) if not isinstance(x, str) else float(x.replace("nan", "nan"))
+
+
+def _arr(xs):
+    return np.array([_num(x) for x in xs], np.float32)
+
+
+@pytest.fixture(scope="module")
+def gold():
+    with open(GOLD) as f:
+        return json.load(f)
+
+
+def _medium(gold, hg=False):
+    m = gold["medium"]
+    return scenes.make_medium(sigma_t=m["sigma_t"], albedo=m["albedo"], scale=m["scale"],
+                              phase=abi.PHASE_HG if hg else abi.PHASE_ISOTROPIC, g=m["g"])
+
+
+def _scene(gold, occluders, hg=False):
+    sc = scenes.Scene()
+    sc.add_medium(_medium(gold, hg))
+    if occluders:
+        sc.add_tris(np.array(gold["triangles"], np.float32).reshape(-1, 3, 3), abi.SURF_BSDF_SMOOTH)
+    return sc
+
+
+def _close(got, want, rtol=RTOL, atol=0.0):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    return np.all(np.abs(got - want) <= rtol * np.abs(want) + atol)
+
+
+def test_find_closest_point_bit_exact(gold):
+    L = oracle.lib()
+    for c in gold["closest"]:
+        v, r = oracle.f32(c["vrl"]), oracle.f32(c["ray"])
+        tc, tv = C.c_float(), C.c_float()
+        L.vrlo_find_closest_point(oracle.fp(v[0:3]), oracle.fp(v[3:6]), v[6], oracle.fp(r[0:3]), oracle.fp(r[3:6]), r[6],
+                                  C.byref(tc), C.byref(tv))
+        want = np.array(c["out"], np.float32)
+        assert np.float32(tc.value) == want[0] and np.float32(tv.value) == want[1], c
+
+
+def test_sampling_vrl_matches_reference(gold):
+    L = oracle.lib()
+    n_invalid = n_nan = 0
+    for c in gold["sampling"]:
+        v, r = oracle.f32(c["vrl"]), oracle.f32(c["ray"])
+        out = np.zeros(9, np.float32)
+        valid = L.vrlo_sampling_vrl(oracle.fp(v[0:3]), oracle.fp(v[3:6]), v[6], oracle.fp(r[0:3]), oracle.fp(r[3:6]), r[6],
+                                    c["uniform"], c["u"][0], c["u"][1], oracle.fp(out))
+        want = _arr(c["out"])
+        # the early-outs (h == 0, parallel) return before any draw: vrl_struct.h:264-265, 275-278
+        assert (c["draws"] == 0) == (valid == 0), c
+        if not valid:
+            n_invalid += 1
+            assert np.all(want == 0)
+            continue
+        if np.isnan(want[8]):
+            # asinh by log(z + sqrt(z*z+1)) cancelling -> NaN pdf; getContrib rejects it (vrl_struct.h:594)
+            n_nan += 1
+            assert np.isnan(out[8]), c
+            continue
+        scale = max(1.0, float(np.abs(want[:8]).max()))
+        assert _close(out[:8], want[:8], atol=RTOL * scale), (c, out)
+        assert _close(out[8], want[8], rtol=5e-5), (c, out)
+    assert n_invalid >= 10      # the fixture does exercise the early-outs
+
+
+def test_eval_transmittance_matches_reference(gold):
+    sc = oracle.OracleScene(_scene(gold, True))
+    blocked = 0
+    for c in gold["transmittance"]:
+        got = sc.transmittance(c["p1"], c["p2"], 0)
+        want = _arr(c["out"])
+        blocked += int(want[0] == 0)
+        assert (got[0] == 0) == (want[0] == 0), c
+        assert _close(got, want), (c, got)
+    assert blocked >= 10
+
+
+@pytest.mark.parametrize("hg", [0, 1])
+def test_get_contrib_matches_reference(gold, hg):
+    L = oracle.lib()
+    med = _medium(gold, bool(hg))
+    sc_occ = _scene(gold, True, bool(hg))
+    desc = sc_occ.desc()
+    nz = 0
+    for c in gold["contrib"]:
+        if c["hg"] != hg:
+            continue
+        v, r = oracle.f32(c["vrl"]), oracle.f32(c["ray"])
+        out = np.zeros(3, np.float32)
+        L.vrlo_get_contrib(C.byref(desc) if c["vis"] else None, C.byref(med), oracle.fp(v), oracle.fp(r[0:3]),
+                           oracle.fp(r[3:6]), r[6], c["uniform"], c["u"][0], c["u"][1], oracle.fp(out))
+        want = _arr(c["out"])
+        if np.any(np.isnan(want)):
+            assert np.any(np.isnan(out)) or np.all(out == 0), (c, out)
+            continue
+        nz += int(np.any(want != 0))
+        assert np.all((out == 0) == (want == 0)), (c, out)
+        assert _close(out, want, rtol=5e-6), (c, out)   # measured max 3.5e-7
+    assert nz >= 50
+
+
+def test_query_sum_matches_reference_sequential_stream(gold):
+    """VRLMap::query over 96 VRLs, q = 1 or 2, on the reference's one sequential PCG32 stream per pixel: the
+    oracle in VRLO_RNG_SEQUENTIAL mode must consume the same draws (early-outs consume none) and sum the same Li."""
+    L = oracle.lib()
+    soa = np.ascontiguousarray(np.array(gold["query_vrls"], np.float32).T)
+    vd = scenes.vrlset_desc(soa, scale=gold["query_scale"])
+    for c in gold["query"]:
+        sc = oracle.OracleScene(_scene(gold, bool(c["vis"])))
+        opt = scenes.default_options(samples_per_query=c["samples"], use_uniform_sampling=c["uniform"],
+                                     visibility=c["vis"], math_mode=0)
+        st, inc = C.c_uint64(), C.c_uint64()
+        L.vrlo_pcg32_seed(c["seed"], 0xda3e39cb94b95bdb, C.byref(st), C.byref(inc))
+        seg = np.zeros(1, abi.SEGMENT_DTYPE)
+        r = oracle.f32(c["ray"])
+        seg["o"][0], seg["d"][0], seg["maxt"][0] = r[0:3], r[3:6], r[6]
+        seg["weight"][0] = 1.0
+        seg["rng_state"][0] = st.value
+        o32, o64, ev = sc.gather(vd, seg, opt, rng_mode=oracle.RNG_SEQUENTIAL, n_threads=1)
+        want = _arr(c["out"])
+        assert _close(o32[0], want, rtol=5e-6), (c, o32[0])
