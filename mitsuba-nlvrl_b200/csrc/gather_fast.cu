@@ -68,13 +68,24 @@ struct FastSeg {
     float maxt;
     V3 v;             // d * maxt
     float c;          // dot(v, v)
+    __device__ __forceinline__ float dotv(V3 x) const { return fmaf(v.x, x.x, fmaf(v.y, x.y, v.z * x.z)); }
+    __device__ __forceinline__ float cc() const { return c; }
+};
+// The same without the hoisted v and c: four registers fewer across the VRL loop for three more multiplies per eval
+// (the visibility kernel sits at its register cap; d is unit length, so dot(v, v) = maxt^2 to fp32 rounding).
+struct FastSegC {
+    V3 o, d;
+    float maxt;
+    __device__ __forceinline__ float dotv(V3 x) const { return maxt * fmaf(d.x, x.x, fmaf(d.y, x.y, d.z * x.z)); }
+    __device__ __forceinline__ float cc() const { return maxt * maxt; }
 };
 
 // VRL::findClosetPoint, vrl_struct.h:163-228 (v, c hoisted per camera segment)
-__device__ __forceinline__ void closest_fast(V3 vo, V3 vd, float vlen, const FastSeg &r, float &tCam, float &tVRL) {
+template <class Seg>
+__device__ __forceinline__ void closest_fast(V3 vo, V3 vd, float vlen, const Seg &r, float &tCam, float &tVRL) {
     V3 u = vd * vlen;
     V3 w = vo - r.o;
-    float a = fdot(u, u), b = fdot(u, r.v), c = r.c, d = fdot(u, w), e = fdot(r.v, w);
+    float a = fdot(u, u), b = r.dotv(u), c = r.cc(), d = fdot(u, w), e = r.dotv(w);
     float D = fmaf(a, c, -(b * b));
     float sN, sD = D, tN, tD = D;
     if (D < 0.0001f) {
@@ -120,8 +131,8 @@ struct Guard { float h2min, zmax; };
 // flux * sigma_s(cam) * sigma_s(vrl) * m_scale BEFORE the shadow test (the segment to trace is returned in so / sd /
 // sdist when VIS), 0 where the reference returns 0.  `slow` is set (and nothing
 // else computed) when the guard wants the exact path.
-template <bool UNIFORM, bool VIS, bool ISO, bool GUARD>
-__device__ __forceinline__ float contrib_fast(const DScene &scene, const FastSeg &ray, V3 vo, V3 vd, float vlen,
+template <bool UNIFORM, bool VIS, bool ISO, bool GUARD, class Seg>
+__device__ __forceinline__ float contrib_fast(const DScene &scene, const Seg &ray, V3 vo, V3 vd, float vlen,
                                               float max_density, float g, float u1, float u2, Guard guard, bool &slow,
                                               V3 &so, V3 &sd, float &sdist) {
     V3 pCam, pVRL; float tCam, tVRL, invPDF;
@@ -249,7 +260,7 @@ gather_fast_kernel(GatherParams p) {
     }
 
     const DMedium *media = p.scene.media;
-    const Guard guard = { p.guard_h * p.guard_h, p.guard_z };
+    const Guard guard = { p.guard_h2, p.guard_z };
     float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
     Pcg32 rng; rng.state = rng0;
 
@@ -311,9 +322,12 @@ gather_fast_kernel(GatherParams p) {
         float lr = sum[0] * inv_q, lg = sum[1] * inv_q, lb = sum[2] * inv_q;
         if (p.seg_out) { p.seg_out[seg_i * 3 + 0] = lr; p.seg_out[seg_i * 3 + 1] = lg; p.seg_out[seg_i * 3 + 2] = lb; }
         if (p.film_rgb) {
-            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 0, lr * w[0]);
-            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 1, lg * w[1]);
-            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 2, lb * w[2]);
+            const float4 *sp = reinterpret_cast<const float4 *>(p.segs + seg_i);
+            const uint32_t pixel = __float_as_uint(__ldg(sp + 1).w);
+            const float4 w = __ldg(sp + 2);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 0, lr * w.x);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 1, lg * w.y);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 2, lb * w.z);
         }
     }
 }
@@ -355,28 +369,28 @@ __device__ __forceinline__ bool shell_inside(const DShell &sh, V3 o, V3 e) {
 // One solid against the shadow segment o + t d, t in [0, dist] (d unit, e = end point):
 // 0 = cannot hit it, 1 = undecided (traverse its BVH), 2 = certainly occluded by it.  See occluder_proxies.cpp.
 // Cheapest rejection first: most segments miss the bounding sphere and leave after ~15 instructions.
-__device__ __forceinline__ int solid_test(const DSolid &S, V3 o, V3 d, V3 e, float dist) {
-    V3 oc(S.c[0] - o.x, S.c[1] - o.y, S.c[2] - o.z);
+__device__ __forceinline__ int solid_test(const DSolid &S, float4 bs, uint32_t flags, V3 o, V3 d, V3 e, float dist) {
+    V3 oc(bs.x - o.x, bs.y - o.y, bs.z - o.z);
     const float t = fminf(fmaxf(fdot(oc, d), 0.f), dist);        // closest approach of the segment to the centre
     V3 q = fmad3(oc, d, -t);
-    if (fdot(q, q) > S.r_out2) return 0;
+    if (fdot(q, q) > bs.w) return 0;
     // inner proxies count only for a segment that enters from outside: an end point outside the bounding sphere
-    V3 ec(S.c[0] - e.x, S.c[1] - e.y, S.c[2] - e.z);
-    const bool enters = fdot(oc, oc) > S.r_out2 || fdot(ec, ec) > S.r_out2;
-    if (enters && (S.flags & VRLB_SOLID_INNER_SPHERE)) {
+    V3 ec(bs.x - e.x, bs.y - e.y, bs.z - e.z);
+    const bool enters = fdot(oc, oc) > bs.w || fdot(ec, ec) > bs.w;
+    if (enters && (flags & VRLB_SOLID_INNER_SPHERE)) {
         V3 oi(S.ci[0] - o.x, S.ci[1] - o.y, S.ci[2] - o.z);
         const float ti = fminf(fmaxf(fdot(oi, d), 0.f), dist);
         V3 qi = fmad3(oi, d, -ti);
         if (fdot(qi, qi) <= S.r_in2) return 2;
     }
-    if (S.flags & (VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB)) {
+    if (flags & (VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB)) {
         V3 r(o.x - S.oc[0], o.y - S.oc[1], o.z - S.oc[2]);
         V3 ol(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), r), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), r), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), r));
         V3 dl(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), d), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), d), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), d));
         V3 il(f_rcp(dl.x), f_rcp(dl.y), f_rcp(dl.z));
-        if ((S.flags & VRLB_SOLID_OUTER_OBB) &&
+        if ((flags & VRLB_SOLID_OUTER_OBB) &&
             !slab2(-S.h_out[0], -S.h_out[1], -S.h_out[2], S.h_out[0], S.h_out[1], S.h_out[2], il, ol, 0.f, dist)) return 0;
-        if (enters && (S.flags & VRLB_SOLID_INNER_OBB)) {
+        if (enters && (flags & VRLB_SOLID_INNER_OBB)) {
             float ax = (-S.h_in[0] - ol.x) * il.x, bx = (S.h_in[0] - ol.x) * il.x;
             float ay = (-S.h_in[1] - ol.y) * il.y, by = (S.h_in[1] - ol.y) * il.y;
             float az = (-S.h_in[2] - ol.z) * il.z, bz = (S.h_in[2] - ol.z) * il.z;
@@ -391,24 +405,30 @@ __device__ __forceinline__ int solid_test(const DSolid &S, V3 o, V3 d, V3 e, flo
 // which roots the shadow segment has to visit: bit 0 = main BVH (its root box is hit), bit 1 + i = shell i (an end
 // point is not strictly inside it), bit 9 + i = solid i (undecided by its proxies).  `occluded` = a solid's inner proxy
 // already decides the query.  Evaluated in phase A with all lanes converged.
-__device__ __forceinline__ uint32_t roots_mask(const DScene &s, const DSolid *solids, const float (&safe)[6], V3 o, V3 d, float dist, bool &occluded) {
+// `cs` is the scene as the kernel PARAMETER (constant bank: its counts and root box cost no load and no register);
+// `bsph` / `sflags` are the solids' bounding spheres (one LDS.128 each) and their proxy flags, 3 bits per solid.
+__device__ __forceinline__ uint32_t roots_mask(const DScene &cs, const DSolid *solids, const float4 *bsph, uint32_t sflags,
+                                               const float (&safe)[6], V3 o, V3 d, float dist, bool &occluded) {   // safe = p.safe
     uint32_t m = 0;
     occluded = false;
     V3 e = fmad3(o, d, dist);
-    for (int i = 0; i < s.n_solids; ++i) {
-        int r = solid_test(solids[i], o, d, e, dist);
+    const int n_solids = cs.n_solids;
+#pragma unroll 1
+    for (int i = 0; i < n_solids; ++i) {
+        int r = solid_test(solids[i], bsph[i], (sflags >> (3 * i)) & 7u, o, d, e, dist);
         if (r == 2) { occluded = true; return 0; }
         if (r == 1) m |= 512u << i;
     }
-    V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
-    if (s.main_root != 0x80000000u &&
-        slab2(s.main_lo[0], s.main_lo[1], s.main_lo[2], s.main_hi[0], s.main_hi[1], s.main_hi[2], inv, o, 0.f, dist)) m |= 1u;
+    if (cs.main_root != 0x80000000u) {
+        V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
+        if (slab2(cs.main_lo[0], cs.main_lo[1], cs.main_lo[2], cs.main_hi[0], cs.main_hi[1], cs.main_hi[2], inv, o, 0.f, dist)) m |= 1u;
+    }
     // shells: `safe` is the intersection of all shell boxes (registers); only a segment with an end point outside it
     // has to look at the individual shells
     const bool in_safe = o.x > safe[0] && o.x < safe[3] && o.y > safe[1] && o.y < safe[4] && o.z > safe[2] && o.z < safe[5] &&
                          e.x > safe[0] && e.x < safe[3] && e.y > safe[1] && e.y < safe[4] && e.z > safe[2] && e.z < safe[5];
     if (!in_safe)
-        for (int i = 0; i < s.n_shells; ++i) if (!shell_inside(s.shells[i], o, e)) m |= 2u << i;
+        for (int i = 0; i < cs.n_shells; ++i) if (!shell_inside(cs.shells[i], o, e)) m |= 2u << i;
     return m;
 }
 __device__ __forceinline__ bool next_root(const DScene &s, RayState &r, uint32_t &root) {
@@ -577,6 +597,9 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t *bar, uint32_t parity, uin
         asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}\n"
                      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(20000u) : "memory");
         if (ok) return;
+        // a warp that ran ahead of the producer waits here for a tile (~0.1 ms of work): sleep instead of spinning, the
+        // spin loop was 5 % of all issued instructions (profiles/r01k_gather_v2_lines.txt)
+        __nanosleep(spins < 8 ? 256u : 2048u);
         if (spins == 4) t0 = clock64();
         else if (spins > 4 && (spins & 15u) == 0 && clock64() - t0 > 4000000000LL) ring_watchdog_trip(wd, code, it, buf, warp_it, bars);
     }
@@ -616,7 +639,7 @@ __device__ __noinline__ Acc3 flush_queue(const DScene &S, WarpQueue &q, const DV
             float ru1 = rr.next_f32(), ru2 = rr.next_f32();
             float fe = exact_eval_vis<UNIFORM>(S, er, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, m.max_density, m.phase, m.g, ru1, ru2);
             if (RR) {
-                FastSeg ray; ray.o = er.o; ray.d = er.d; ray.maxt = er.maxt; ray.v = er.d * er.maxt; ray.c = fdot(ray.v, ray.v);
+                FastSegC ray; ray.o = er.o; ray.d = er.d; ray.maxt = er.maxt;
                 float cc, cv;
                 closest_fast(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, ray, cc, cv);
                 V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), cv);
@@ -641,6 +664,8 @@ gather_fast_vis_kernel(GatherParams p) {
     uint64_t *full_bar = ring_bar, *empty_bar = ring_bar + NBUF;
     __shared__ uint32_t warp_it[GATHER_THREADS / 32];   // watchdog evidence: the tile each warp is on
     __shared__ DSolid sol[VRLB_MAX_SOLIDS];             // the solids' proxies, read by every eval
+    __shared__ float4 bsph[VRLB_MAX_SOLIDS];            // their bounding spheres (centre, r^2): the first test of every eval, one LDS.128
+    __shared__ uint32_t s_sflags;                       // proxy flags, 3 bits per solid
     __shared__ DScene s_scene;                          // the out-of-line helpers take the scene by reference: shared, not a local copy
     if (threadIdx.x == 0) s_scene = p.scene;
     __syncthreads();
@@ -651,20 +676,18 @@ gather_fast_vis_kernel(GatherParams p) {
     const uint64_t seg_i = (uint64_t) blockIdx.x * GATHER_THREADS + tid;
     const bool live = seg_i < p.n_segs;
 
-    FastSeg ray; uint64_t rng0 = 0; uint32_t pixel = 0; float w[3] = { 0.f, 0.f, 0.f };
+    // Only what every eval needs stays in registers (origin, direction, maxt, the stream); pixel, weight and the
+    // stream's start are re-read from the segment record where they are used (the kernel sits at its register cap).
+    FastSegC ray; uint64_t rng0 = 0;
     if (live) {
         const float4 *sp = reinterpret_cast<const float4 *>(p.segs + seg_i);
-        float4 r0 = __ldg(sp), r1 = __ldg(sp + 1), r2 = __ldg(sp + 2);
-        ulonglong2 r3 = __ldg(reinterpret_cast<const ulonglong2 *>(sp + 3));
+        float4 r0 = __ldg(sp), r1 = __ldg(sp + 1);
         ray.o = V3(r0.x, r0.y, r0.z); ray.maxt = r0.w;
-        ray.d = V3(r1.x, r1.y, r1.z); pixel = __float_as_uint(r1.w);
-        w[0] = r2.x; w[1] = r2.y; w[2] = r2.z;
-        rng0 = r3.x;
+        ray.d = V3(r1.x, r1.y, r1.z);
+        rng0 = __ldg(reinterpret_cast<const ulonglong2 *>(sp + 3)).x;
     } else {
         ray.o = V3(0.f); ray.d = V3(0.f, 0.f, 1.f); ray.maxt = 1.f;
     }
-    ray.v = ray.d * ray.maxt;
-    ray.c = fdot(ray.v, ray.v);
     SegRegs er; er.o = ray.o; er.d = ray.d; er.maxt = ray.maxt;
 
     const uint32_t n_tiles = (uint32_t) ((p.n_vrls + VTILE - 1) / VTILE);
@@ -673,6 +696,12 @@ gather_fast_vis_kernel(GatherParams p) {
 
     for (uint32_t i = tid; i < (uint32_t) S.n_solids * (sizeof(DSolid) / 4); i += GATHER_THREADS)
         reinterpret_cast<uint32_t *>(sol)[i] = reinterpret_cast<const uint32_t *>(S.solids)[i];
+    if (tid < (uint32_t) S.n_solids) bsph[tid] = make_float4(S.solids[tid].c[0], S.solids[tid].c[1], S.solids[tid].c[2], S.solids[tid].r_out2);
+    if (tid == 32) {
+        uint32_t f = 0;
+        for (int i = 0; i < S.n_solids; ++i) f |= (S.solids[i].flags & 7u) << (3 * i);
+        s_sflags = f;
+    }
     if (tid == 0) {
         for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], GATHER_THREADS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -691,17 +720,15 @@ gather_fast_vis_kernel(GatherParams p) {
     }
 
     const DMedium *media = S.media;
-    const Guard guard = { p.guard_h * p.guard_h, p.guard_z };
+    const Guard guard = { p.guard_h2, p.guard_z };
+    const uint32_t sflags = s_sflags;
     float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
     Pcg32 rng; rng.state = rng0;
-    float safe[6] = { -VRLB_INF, -VRLB_INF, -VRLB_INF, VRLB_INF, VRLB_INF, VRLB_INF };   // intersection of the shell boxes
-    for (int i = 0; i < S.n_shells; ++i)
-        for (int k = 0; k < 3; ++k) { safe[k] = fmaxf(safe[k], S.shells[i].lo[k]); safe[3 + k] = fminf(safe[3 + k], S.shells[i].hi[k]); }
 
     for (uint32_t it = 0; it < total_tiles; ++it) {
         const uint32_t t = it % n_tiles, s = it / n_tiles, buf = it % NBUF;
         if (t == 0) {
-            rng.state = rng0;
+            rng.state = live ? __ldg(reinterpret_cast<const ulonglong2 *>(p.segs + seg_i) + 3).x : 0ull;
             rng.advance(((uint64_t) s * p.total + p.first_index) * DPE);
         }
         if (lane == 0) warp_it[tid >> 5] = it;
@@ -722,19 +749,24 @@ gather_fast_vis_kernel(GatherParams p) {
             pr += r.r; pg += r.g; pb += r.b;
             npend = 0;
         };
-        for (uint32_t j = 0; j < cnt; ++j) {
+        // The (out-of-line) flush is called from the OUTER of two loops: the inner loop shades VRLs until some lane's
+        // slots are full and contains no call, so its state stays in registers instead of being re-read from the
+        // spill area at every VRL (12 LDL per eval before, profiles/r01k_gather_v2_lines.txt).
+        for (uint32_t j = 0; ; ) {
+          for (; j < cnt; ++j) {
             // shade VRL j for the warp's 32 camera segments (converged); only undecided shadow segments are parked
             const float4 *vp = reinterpret_cast<const float4 *>(&tile[buf][j]);
-            float4 a = vp[0], b = vp[1], c = vp[2];
+            float4 a = vp[0], b = vp[1];
             V3 vo(a.x, a.y, a.z), vd(b.x, b.y, b.z);
             float vlen = a.w;
-            float rrWeight = 1.f; bool survive = live;
+            const float max_density = reinterpret_cast<const float *>(vp)[11];   // the flux is read after the eval (registers)
+            float rrWeight = 1.f; bool survive = true;           // lanes past the last segment shade a dummy segment, never written
             if (RR) {
                 float cc, cv;                                     // EDistanceRoulette, vrl_map.h:171-190
                 closest_fast(vo, vd, vlen, ray, cc, cv);
                 V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(vo, vd, cv);
                 rrWeight = fminf(f_rcp(f_sqrt(fdot(dd, dd)) * p.scale_rr), 1.0f);
-                survive  = survive && rrWeight > rng.next_f32();
+                survive  = rrWeight > rng.next_f32();
             }
             float u1 = rng.next_f32(), u2 = rng.next_f32();
             float f = 0.f; bool pend = false; uint32_t roots = 0; V3 so(0.f), sd(0.f); float dist = 0.f;
@@ -742,7 +774,7 @@ gather_fast_vis_kernel(GatherParams p) {
                 float g = 0.f;
                 if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
                 bool slow;
-                f = contrib_fast<UNIFORM, true, ISO, GUARD>(S, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, dist);
+                f = contrib_fast<UNIFORM, true, ISO, GUARD>(S, ray, vo, vd, vlen, max_density, g, u1, u2, guard, slow, so, sd, dist);
                 if (GUARD && slow) {                              // ill-conditioned eval: exactly-rounded arithmetic; its
                     const DMedium &m = media[__float_as_uint(b.w)];       // connection segment is traced like any other
                     float seg[7];
@@ -752,13 +784,16 @@ gather_fast_vis_kernel(GatherParams p) {
                 }
                 if (f != 0.f) {
                     bool occluded;
-                    roots = roots_mask(S, sol, safe, so, sd, dist, occluded);
+                    roots = roots_mask(p.scene, sol, bsph, sflags, p.safe, so, sd, dist, occluded);
                     if (occluded) f = 0.f;                        // an inner proxy of a closed solid decides it
                     else pend = roots != 0;
                 }
                 if (RR) f = f * f_rcp(rrWeight);
             }
-            const float cr = c.x * f, cg = c.y * f, cb = c.z * f; // flux pre-multiplied by sigma_s^2 * m_scale
+            float4 c;                                             // flux pre-multiplied by sigma_s^2 * m_scale; read here, not
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"    // at the top: four registers fewer across the eval
+                         : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w) : "r"(smem_u32(vp + 2)));
+            const float cr = c.x * f, cg = c.y * f, cb = c.z * f;
             if (pend) {
                 const int slot = npend * 32 + (int) lane;
                 q.v[0][slot] = so.x; q.v[1][slot] = so.y; q.v[2][slot] = so.z;
@@ -768,9 +803,11 @@ gather_fast_vis_kernel(GatherParams p) {
                 q.roots[slot] = (uint16_t) roots; q.vj[slot] = (uint16_t) j;
                 ++npend;
             } else if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { pr += cr; pg += cg; pb += cb; }   // vrl_map.h:162
-            if (__any_sync(0xffffffffu, npend == NB)) flush();
+            if (__any_sync(0xffffffffu, npend == NB)) { ++j; break; }
+          }
+          if (__any_sync(0xffffffffu, npend > 0)) flush();
+          if (j >= cnt) break;
         }
-        if (__any_sync(0xffffffffu, npend > 0)) flush();
         float part[3] = { pr, pg, pb };
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
@@ -789,9 +826,12 @@ gather_fast_vis_kernel(GatherParams p) {
         float lr = sum[0] * inv_q, lg = sum[1] * inv_q, lb = sum[2] * inv_q;
         if (p.seg_out) { p.seg_out[seg_i * 3 + 0] = lr; p.seg_out[seg_i * 3 + 1] = lg; p.seg_out[seg_i * 3 + 2] = lb; }
         if (p.film_rgb) {
-            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 0, lr * w[0]);
-            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 1, lg * w[1]);
-            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 2, lb * w[2]);
+            const float4 *sp = reinterpret_cast<const float4 *>(p.segs + seg_i);
+            const uint32_t pixel = __float_as_uint(__ldg(sp + 1).w);
+            const float4 w = __ldg(sp + 2);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 0, lr * w.x);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 1, lg * w.y);
+            atomicAdd(p.film_rgb + (size_t) pixel * 3 + 2, lb * w.z);
         }
     }
 }
@@ -818,7 +858,9 @@ template <bool U, bool R, bool I, bool P>
 static cudaError_t launch_f(const GatherParams &p, cudaStream_t stream) {
     uint32_t grid = (uint32_t) ((p.n_segs + GATHER_THREADS - 1) / GATHER_THREADS);
     if (grid == 0 || p.n_vrls == 0) return cudaSuccess;
-    gather_fast_kernel<U, R, false, I, P><<<grid, GATHER_THREADS, 0, stream>>>(p);
+    GatherParams pp = p;
+    pp.guard_h2 = p.guard_h * p.guard_h;
+    gather_fast_kernel<U, R, false, I, P><<<grid, GATHER_THREADS, 0, stream>>>(pp);
     return cudaGetLastError();
 }
 template <bool U, bool R, bool I, bool P>
@@ -826,13 +868,18 @@ static cudaError_t launch_fv(const GatherParams &p, cudaStream_t stream) {
     uint32_t grid = (uint32_t) ((p.n_segs + GATHER_THREADS - 1) / GATHER_THREADS);
     if (grid == 0 || p.n_vrls == 0) return cudaSuccess;
     constexpr size_t smem = NBUF * VTILE * sizeof(DVrl) + (GATHER_THREADS / 32) * sizeof(WarpQueue);
+    GatherParams pp = p;                   // intersection of the shell boxes: a segment with both ends strictly inside it meets no shell
+    pp.guard_h2 = p.guard_h * p.guard_h;
+    for (int k = 0; k < 3; ++k) { pp.safe[k] = -INFINITY; pp.safe[3 + k] = INFINITY; }
+    for (int i = 0; i < p.scene.n_shells; ++i)
+        for (int k = 0; k < 3; ++k) { pp.safe[k] = fmaxf(pp.safe[k], p.scene.shells[i].lo[k]); pp.safe[3 + k] = fminf(pp.safe[3 + k], p.scene.shells[i].hi[k]); }
     static bool configured = false;       // per instantiation; the attribute is sticky for the process
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(gather_fast_vis_kernel<U, R, I, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    gather_fast_vis_kernel<U, R, I, P><<<grid, GATHER_THREADS, smem, stream>>>(p);
+    gather_fast_vis_kernel<U, R, I, P><<<grid, GATHER_THREADS, smem, stream>>>(pp);
     return cudaGetLastError();
 }
 template <bool U, bool R, bool V>

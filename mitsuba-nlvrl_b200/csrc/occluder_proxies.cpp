@@ -280,6 +280,22 @@ void build_solid_proxies(const float *verts, const std::vector<uint32_t> &sub, f
             }
         }
     }
+    // Every proxy is conservative on its own, so dropping one only sends a few more segments to the traversal.  Keep the
+    // per-eval test short where a proxy adds nothing (a warp pays for the longest path any of its 32 lanes takes):
+    //  * sphere-like solid: the layer between the inscribed and the bounding sphere is thin -> no oriented boxes;
+    //  * box-like solid: the inscribed sphere lies (nearly) inside the inscribed box -> no inscribed sphere.
+    if ((out.flags & VRLB_SOLID_INNER_SPHERE) && out.r_in2 >= 0.85f * out.r_out2)
+        out.flags &= ~(VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB);
+    if ((out.flags & VRLB_SOLID_INNER_SPHERE) && (out.flags & VRLB_SOLID_INNER_OBB)) {
+        const double rin = std::sqrt((double) out.r_in2);
+        bool inside_box = true;
+        for (int k = 0; k < 3; ++k) {
+            double off = 0;
+            for (int c = 0; c < 3; ++c) off += ((double) out.ci[c] - (double) out.oc[c]) * (double) out.ax[3 * k + c];
+            inside_box = inside_box && std::fabs(off) + 0.9 * rin <= (double) out.h_in[k];
+        }
+        if (inside_box) out.flags &= ~VRLB_SOLID_INNER_SPHERE;
+    }
 }
 
 }  // namespace vrlb

@@ -25,6 +25,8 @@ struct GatherParams {
     float              *film_rgb;    // device, width*height*3 fp32, accumulated with RED.ADD (may be null)
     float              *seg_out;     // device, n_segs*3: Li per segment before the weight (may be null)
     uint32_t           *wd;          // pinned host memory, 32 words: record left by the in-kernel watchdog before it traps
+    float               guard_h2;    // guard_h^2, filled by launch_gather_fast
+    float               safe[6];     // intersection of the shell boxes (lo, hi), filled by launch_gather_fast: compare operands from the constant bank
 };
 
 cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis, bool grid, cudaStream_t stream);
