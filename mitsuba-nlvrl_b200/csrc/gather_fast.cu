@@ -599,7 +599,7 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t *bar, uint32_t parity, uin
         if (ok) return;
         // a warp that ran ahead of the producer waits here for a tile (~0.1 ms of work): sleep instead of spinning, the
         // spin loop was 5 % of all issued instructions (profiles/r01k_gather_v2_lines.txt)
-        __nanosleep(spins < 8 ? 256u : 2048u);
+        __nanosleep(spins < 4 ? 512u : 4096u);
         if (spins == 4) t0 = clock64();
         else if (spins > 4 && (spins & 15u) == 0 && clock64() - t0 > 4000000000LL) ring_watchdog_trip(wd, code, it, buf, warp_it, bars);
     }
