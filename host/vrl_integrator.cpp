@@ -182,6 +182,13 @@ void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
         std::fprintf(stderr, "[VRLIntegrator] VRL Map Created: %llu VRLs from %llu particles\n", (unsigned long long) n, (unsigned long long) particles);
         m_have_vrls = true;
     }
+    // vrl.cpp:408-415: the map may be turned into long beams and / or diced before it is used
+    if (m_longVRL) check(vrlb_vrls_to_long(m_ctx), "vrlb_vrls_to_long");
+    if (m_diceVRL > 1) {
+        uint64_t n = 0;
+        check(vrlb_vrls_dice(m_ctx, (uint32_t) m_diceVRL, &n), "vrlb_vrls_dice");
+        std::fprintf(stderr, "[VRLIntegrator] Dicing the VRL... Number of VRLs: %llu\n", (unsigned long long) n);
+    }
     m_preprocessed = true;
 }
 

@@ -225,6 +225,14 @@ typedef struct vrlb_generate_desc {
 float vrlb_vrls_scale(const vrlb_context *ctx);
 int  vrlb_vrls_download_depth(vrlb_context *ctx, int32_t *depth, uint64_t cap);
 int  vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t *n_vrls_out, uint64_t *n_particles_out);
+/* The two transforms VRLIntegrator::preprocess applies to the map before the gather (vrl.cpp:408-415), on the resident set:
+ *   vrlb_vrls_to_long: `long_vrl`  -- VRLMap::toLong / VRL::convertToLong (vrl_map.h:56-62, vrl_struct.h:146-154): every VRL is
+ *                      extended to the closest surface along its direction; VRLB_ERR_STATE if one sees none (the reference throws);
+ *   vrlb_vrls_dice:    `dice_vrl` > 1 -- VRLMap::dicingVRL / VRL::dice (vrl_map.h:104-128, vrl_struct.h:88-128): every VRL is cut
+ *                      into pieces of (mean length / avg_number_dice), flux attenuated by the medium transmittance up to the piece;
+ *                      the set keeps VRL-major order and its m_scale.  Homogeneous / nonlinear media only. */
+int  vrlb_vrls_to_long(vrlb_context *ctx);
+int  vrlb_vrls_dice(vrlb_context *ctx, uint32_t avg_number_dice, uint64_t *n_vrls_out);
 
 /* ---- camera segments: replaces the medium branch of VRLIntegrator::sample up to the query
  *      (vrl.cpp:443-631) driven by SamplingIntegrator::render_block/render_sample

@@ -20,7 +20,7 @@ EXPORTS = [
     "vrlb_film_device_ptr", "vrlb_film_download_xyzaw", "vrlb_film_download_rgb", "vrlb_render", "vrlb_cancel",
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
-    "vrlb_vrls_download_depth", "vrlb_shadow_proxies",
+    "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice",
 ]
 
 
@@ -93,6 +93,8 @@ def load_library():
     L.vrlb_film_resolve.argtypes = [vp, C.POINTER(vp)]
     L.vrlb_measure_fp32_peak.argtypes = [vp, f32p]
     L.vrlb_vrls_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.vrlb_vrls_to_long.argtypes = [vp]
+    L.vrlb_vrls_dice.argtypes = [vp, C.c_uint32, C.POINTER(C.c_uint64)]
     L.vrlb_vrls_scale.argtypes = [vp]
     L.vrlb_vrls_scale.restype = C.c_float
     L.vrlb_vrls_download_depth.argtypes = [vp, C.POINTER(C.c_int32), C.c_uint64]
@@ -148,6 +150,16 @@ class Context:
         n, pcount = C.c_uint64(), C.c_uint64()
         self._check(self.lib.vrlb_vrls_generate(self.h, C.byref(gen), C.byref(n), C.byref(pcount)))
         return int(n.value), int(pcount.value)
+
+    def vrls_to_long(self):
+        """`long_vrl`: extend every resident VRL to the next surface (VRLMap::toLong)."""
+        self._check(self.lib.vrlb_vrls_to_long(self.h))
+
+    def dice_vrls(self, avg_number_dice):
+        """`dice_vrl`: cut the resident VRLs into pieces of mean length / avg_number_dice (VRLMap::dicingVRL); returns the new count."""
+        n = C.c_uint64()
+        self._check(self.lib.vrlb_vrls_dice(self.h, int(avg_number_dice), C.byref(n)))
+        return int(n.value)
 
     def vrls_scale(self):
         return float(self.lib.vrlb_vrls_scale(self.h))

@@ -472,6 +472,65 @@ int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_
     return VRLB_OK;
 }
 
+// ---- VRL-set transforms (vrl_post.cu) ----------------------------------------------------------------
+int vrlb_vrls_to_long(vrlb_context *ctx) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_vrls_to_long");
+    if (ctx->n_vrls == 0) return VRLB_OK;
+    CU(ctx, ctx->counter.reserve(1));
+    CU(ctx, cudaMemsetAsync(ctx->counter.ptr, 0, sizeof(unsigned long long), ctx->stream));
+    CU(ctx, launch_vrls_to_long(ctx->scene, ctx->vrls.ptr, ctx->n_vrls, ctx->counter.ptr, ctx->stream)); ctx->launches += 1;
+    unsigned long long missed = 0;
+    CU(ctx, cudaMemcpyAsync(&missed, ctx->counter.ptr, sizeof missed, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->fast_dirty = true;
+    // VRL::convertToLong: Log(Error, ...) throws in the reference
+    if (missed) return fail(ctx, VRLB_ERR_STATE, "Impossible to convert to long vrl... (%llu VRLs see no surface)", missed);
+    return VRLB_OK;
+}
+
+int vrlb_vrls_dice(vrlb_context *ctx, uint32_t avg_number_dice, uint64_t *n_out) {
+    if (!ctx || avg_number_dice == 0) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_vrls_dice");
+    if (ctx->any_grid) return fail(ctx, VRLB_ERR_STATE, "dicing inside a grid medium draws the reference's stochastic transmittance from the "
+                                                        "preprocess sampler; only homogeneous / nonlinear media are diced on this path");
+    const uint64_t n = ctx->n_vrls;
+    if (n_out) *n_out = n;
+    if (n == 0) return VRLB_OK;
+    // average length: the reference's serial double sum over the map (vrl_map.h:106-110)
+    CU(ctx, ctx->stage_soa.reserve(n * 10)); CU(ctx, ctx->stage_med.reserve(n));
+    CU(ctx, launch_unpack_vrls(ctx->vrls.ptr, n, ctx->stage_soa.ptr, ctx->stage_med.ptr, ctx->stream)); ctx->launches += 1;
+    std::vector<float> len((size_t) n);
+    CU(ctx, cudaMemcpyAsync(len.data(), ctx->stage_soa.ptr + 6 * n, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    double avg = 0.0;
+    for (float l : len) avg += l;
+    avg /= (double) n;
+    const float dice_len = (float) (avg / (double) avg_number_dice);      // VRL::dice(scene, sampler, const Float avgLength)
+    if (!(dice_len > 0.f)) return fail(ctx, VRLB_ERR_STATE, "dicing needs a positive mean VRL length");
+    DevBuf<uint32_t> d_counts; DevBuf<uint64_t> d_offsets; DevBuf<DVrl> diced;
+    CU(ctx, d_counts.reserve(n)); CU(ctx, d_offsets.reserve(n + 1));
+    CU(ctx, launch_vrls_dice(ctx->vrls.ptr, n, ctx->media.ptr, dice_len, d_counts.ptr, nullptr, nullptr, ctx->stream)); ctx->launches += 1;
+    std::vector<uint32_t> counts((size_t) n); std::vector<uint64_t> offsets((size_t) n + 1, 0);
+    CU(ctx, cudaMemcpyAsync(counts.data(), d_counts.ptr, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    for (uint64_t i = 0; i < n; ++i) offsets[i + 1] = offsets[i] + counts[i];
+    const uint64_t total = offsets[n];
+    if (total == 0) return fail(ctx, VRLB_ERR_STATE, "dicing produced no VRL");
+    CU(ctx, diced.reserve(total));
+    CU(ctx, cudaMemcpyAsync(d_offsets.ptr, offsets.data(), (n + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, launch_vrls_dice(ctx->vrls.ptr, n, ctx->media.ptr, dice_len, d_counts.ptr, d_offsets.ptr, diced.ptr, ctx->stream)); ctx->launches += 1;
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->vrls.release(); ctx->vrls = diced; diced.ptr = nullptr; diced.cap = 0;
+    d_counts.release(); d_offsets.release();
+    ctx->n_vrls = total; ctx->vrl_first = 0; ctx->vrl_total = total;      // m_scale is untouched (vrl.cpp:412-423)
+    ctx->fast_dirty = true;
+    if (n_out) *n_out = total;
+    return VRLB_OK;
+}
+
 // ---- camera segments -------------------------------------------------------------------------------
 int vrlb_segments_build(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_options *opt) {
     if (!ctx || !cam || !opt) return VRLB_ERR_INVALID;

@@ -74,6 +74,11 @@ struct GenParams {
 };
 cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream);
 
+// VRL-set transforms between light tracing and the gather (vrl_post.cu): long beams, dicing (count pass when out == nullptr)
+cudaError_t launch_vrls_to_long(const DScene &s, DVrl *v, uint64_t n, unsigned long long *missed, cudaStream_t stream);
+cudaError_t launch_vrls_dice(const DVrl *in, uint64_t n, const DMedium *media, float dice_len, uint32_t *counts,
+                             const uint64_t *offsets, DVrl *out, cudaStream_t stream);
+
 // FFMA-saturating microkernel (peak.cu)
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int iters, cudaStream_t stream);
 

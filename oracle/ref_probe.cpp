@@ -179,6 +179,47 @@ int main() {
                (double) p.rmaxt, uniform, vis, samples, 20000 + k, (int) s.draws, nb);
         p3n(Li); printf("]}%s\n", k + 1 < NQ ? "," : "");
     }
-    printf(" ],\n \"warnings\": %d\n}\n", MockLog::warnings);
+    printf(" ],\n");
+
+    /* ---- dice: VRL::dice (vrl_struct.h:88-128) with the dice length VRLMap::dicingVRL derives (vrl_map.h:104-118,
+     *      double mean of the lengths / avgNumberDice, passed as a Float); long: VRL::convertToLong (146-154) ---- */
+    {
+        const int ND = 24, avgNumberDice = 3;
+        std::vector<Pair> dp(ND);
+        for (int j = 0; j < ND; ++j) { dp[j] = make_pair(j % 8 == 7 ? 5 : 0); }
+        dp[3].vlen = 0.f;                       /* zero-length VRL: one zero-length piece */
+        auto avg_length = 0.0;
+        for (int j = 0; j < ND; ++j) avg_length += dp[j].vlen;
+        avg_length /= ND;
+        printf(" \"dice_in\": [");
+        for (int j = 0; j < ND; ++j) { printf("%s[", j ? ", " : ""); p3(dp[j].vo); printf(", "); p3(dp[j].vd); printf(", %.9g, ", (double) dp[j].vlen); p3(dp[j].flux); printf("]"); }
+        printf("],\n \"dice_n\": %d,\n \"dice_out\": [\n", avgNumberDice);
+        MockSampler s; s.seed(0, 777);
+        bool first = true;
+        for (int j = 0; j < ND; ++j) {
+            VRLf v = make_vrl(dp[j], &med);
+            auto pieces = v.dice(&empty, &s, avg_length / avgNumberDice);
+            for (auto &q2 : pieces) {
+                printf("%s  [%d, ", first ? "" : ",\n", j); p3(q2.origin); printf(", "); p3(q2.direction); printf(", %.9g, ", (double) q2.length); p3(q2.flux); printf("]");
+                first = false;
+            }
+        }
+        printf("\n ],\n \"long\": [\n");
+        /* a closed room around the occluders so that every VRL sees a surface */
+        MockScene room = occl;
+        const float R = 12.f;
+        const float c8[8][3] = { {-R,-R,-R},{R,-R,-R},{R,R,-R},{-R,R,-R},{-R,-R,R},{R,-R,R},{R,R,R},{-R,R,R} };
+        const int f12[12][3] = { {0,1,2},{0,2,3},{4,6,5},{4,7,6},{0,4,5},{0,5,1},{3,2,6},{3,6,7},{0,3,7},{0,7,4},{1,5,6},{1,6,2} };
+        for (auto &f : f12) for (int k = 0; k < 3; ++k) room.tri.push_back(V3(c8[f[k]][0], c8[f[k]][1], c8[f[k]][2]));
+        for (int j = 0; j < ND; ++j) {
+            VRLf v = make_vrl(dp[j], &med);
+            v.convertToLong(&room);
+            printf("  %.9g%s\n", (double) v.length, j + 1 < ND ? "," : "");
+        }
+        printf(" ],\n \"room_triangles\": [");
+        for (size_t i = 0; i < room.tri.size(); ++i) { if (i) printf(", "); p3(room.tri[i]); }
+        printf("],\n");
+    }
+    printf(" \"warnings\": %d\n}\n", MockLog::warnings);
     return 0;
 }

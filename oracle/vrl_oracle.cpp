@@ -913,6 +913,55 @@ float vrlo_grid_transmittance(const vrlo_scene *s, int medium, const float o[3],
     return grid_transmittance(*s, s->media[(size_t) medium], medium, V3(o), V3(d), maxt, &sub);
 }
 
+/* VRLMap::toLong -> VRL::convertToLong (vrl_map.h:56-62, vrl_struct.h:146-154): Ray3f r(origin, direction, 0) keeps the
+ * default [RayEpsilon, inf) interval; length = si.t of the closest surface; a miss is Log(Error) = throw in the reference */
+uint64_t vrlo_vrls_to_long(const vrlo_scene *s, const float *soa10, uint64_t n, float *length_out) {
+    uint64_t missed = 0;
+    for (uint64_t j = 0; j < n; ++j) {
+        V3 o(soa10[0 * n + j], soa10[1 * n + j], soa10[2 * n + j]), d(soa10[3 * n + j], soa10[4 * n + j], soa10[5 * n + j]);
+        Hit h = ray_intersect(*s, o, d, kRayEpsilon, kInf);
+        if (!h.valid()) { ++missed; length_out[j] = soa10[6 * n + j]; }
+        else length_out[j] = h.t;
+    }
+    return missed;
+}
+
+/* VRLMap::dicingVRL -> VRL::dice (vrl_map.h:104-128, vrl_struct.h:88-128).  `avg_length` and `current_distance` are
+ * doubles in the reference (`auto x = 0.0`), the dice length is passed as a Float; origin + direction * current_distance
+ * is a float vector times a double, i.e. evaluated in fp64 and rounded once on assignment.  Homogeneous media only
+ * (grid media would draw from the preprocess sampler).  Returns the number of diced VRLs; writes min(count, cap). */
+uint64_t vrlo_vrls_dice(const vrlo_scene *s, const float *soa10, const uint16_t *medium, uint64_t n, uint32_t avg_number_dice,
+                        float *out_soa10, uint16_t *out_medium, uint64_t cap) {
+    double avg_length = 0.0;
+    for (uint64_t j = 0; j < n; ++j) avg_length += soa10[6 * n + j];
+    avg_length /= (double) n;
+    const float avgLength = (float) (avg_length / (double) avg_number_dice);
+    uint64_t w = 0;
+    for (uint64_t j = 0; j < n; ++j) {
+        const float length = soa10[6 * n + j];
+        const int med = medium ? medium[j] : 0;
+        const vrlb_medium &m = s->media[(size_t) med];
+        double current_distance = 0.0;
+        while (current_distance <= length) {
+            double next_length = std::min((double) length - current_distance, (double) avgLength);
+            float tr = 1.0f;
+            if (current_distance != 0.0) tr = homo_transmittance(m, 0.0f, (float) current_distance);
+            if (w < cap) {
+                for (int c = 0; c < 3; ++c) {
+                    out_soa10[(size_t) c * cap + w] = (float) ((double) soa10[c * n + j] + (double) soa10[(3 + c) * n + j] * current_distance);
+                    out_soa10[(size_t) (3 + c) * cap + w] = soa10[(3 + c) * n + j];
+                    out_soa10[(size_t) (7 + c) * cap + w] = soa10[(7 + c) * n + j] * tr;
+                }
+                out_soa10[(size_t) 6 * cap + w] = (float) next_length;
+                if (out_medium) out_medium[w] = (uint16_t) med;
+            }
+            ++w;
+            current_distance += avgLength;
+        }
+    }
+    return w;
+}
+
 uint64_t vrlo_gather_segments(const vrlo_scene *s, const vrlb_vrlset_desc *vrls, const vrlb_segment *segs,
                               uint64_t n_segs, const vrlb_options *opt, int rng_mode, int n_threads,
                               float *out_rgb32, double *out_rgb64) {

@@ -65,6 +65,13 @@ int   vrlo_ray_intersect(const vrlo_scene *s, const float o[3], const float d[3]
 /* VRL::evalTransmittance (vrl_struct.h:509-572) for p1->p2 starting in medium `medium` */
 void  vrlo_eval_transmittance(const vrlo_scene *s, const float p1[3], const float p2[3], int medium, float out_rgb[3]);
 
+/* -- VRL-set transforms of VRLIntegrator::preprocess (vrl.cpp:408-415) -- */
+/* VRLMap::toLong (vrl_map.h:56-62): new lengths; returns the number of VRLs that see no surface (the reference throws) */
+uint64_t vrlo_vrls_to_long(const vrlo_scene *s, const float *soa10, uint64_t n, float *length_out);
+/* VRLMap::dicingVRL (vrl_map.h:104-128): out_soa10 is [10][cap]; returns the diced count (may exceed cap: nothing lost but the tail) */
+uint64_t vrlo_vrls_dice(const vrlo_scene *s, const float *soa10, const uint16_t *medium, uint64_t n, uint32_t avg_number_dice,
+                        float *out_soa10, uint16_t *out_medium, uint64_t cap);
+
 /* -- camera segments: VRLIntegrator::sample up to the query (vrl.cpp:443-631) -- */
 /* returns number of segments written (<= cap); n_vrls_total fixes the draws a query consumes in
  * addressed mode.  direct_rgb (width*height*3, may be NULL) receives emitter radiance seen on the

@@ -54,6 +54,10 @@ def lib():
         L.vrlo_grid_eval.restype = C.c_float
         L.vrlo_grid_transmittance.argtypes = [C.c_void_p, C.c_int, f3, f3, C.c_float, C.c_uint64]
         L.vrlo_grid_transmittance.restype = C.c_float
+        L.vrlo_vrls_to_long.argtypes = [C.c_void_p, f3, C.c_uint64, f3]
+        L.vrlo_vrls_to_long.restype = C.c_uint64
+        L.vrlo_vrls_dice.argtypes = [C.c_void_p, f3, C.POINTER(C.c_uint16), C.c_uint64, C.c_uint32, f3, C.POINTER(C.c_uint16), C.c_uint64]
+        L.vrlo_vrls_dice.restype = C.c_uint64
         L.vrlo_build_segments.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.c_uint64, C.c_int,
                                           C.c_void_p, C.c_uint64, f3, f3]
         L.vrlo_build_segments.restype = C.c_uint64
@@ -104,6 +108,26 @@ class OracleScene:
     def grid_transmittance(self, o, d, maxt, seed, medium=0):
         o, d = f32(o), f32(d)
         return lib().vrlo_grid_transmittance(self.h, medium, fp(o), fp(d), maxt, seed)
+
+    def vrls_to_long(self, soa10):
+        """VRLMap::toLong: (new lengths, number of VRLs that see no surface)."""
+        soa10 = np.ascontiguousarray(soa10, np.float32)
+        n = soa10.shape[1]
+        out = np.zeros(n, np.float32)
+        missed = lib().vrlo_vrls_to_long(self.h, fp(soa10), n, fp(out))
+        return out, int(missed)
+
+    def vrls_dice(self, soa10, avg_number_dice, medium=None):
+        """VRLMap::dicingVRL: the diced [10, m] set (+ medium ids)."""
+        soa10 = np.ascontiguousarray(soa10, np.float32)
+        n = soa10.shape[1]
+        med = None if medium is None else np.ascontiguousarray(medium, np.uint16)
+        mp = None if med is None else med.ctypes.data_as(C.POINTER(C.c_uint16))
+        cap = int(lib().vrlo_vrls_dice(self.h, fp(soa10), mp, n, avg_number_dice, None, None, 0))
+        out, om = np.zeros((10, max(cap, 1)), np.float32), np.zeros(max(cap, 1), np.uint16)
+        m = int(lib().vrlo_vrls_dice(self.h, fp(soa10), mp, n, avg_number_dice, fp(out), om.ctypes.data_as(C.POINTER(C.c_uint16)), cap))
+        assert m == cap
+        return out[:, :m], om[:m]
 
     def build_segments(self, cam, opt, n_vrls_total, rng_mode=RNG_ADDRESSED, cap=None):
         npix = cam.width * cam.height

@@ -136,3 +136,84 @@ def test_generated_set_feeds_the_gather(ctx):
     ctx.build_segments(cam, opt)
     ctx.gather(opt)
     assert np.allclose(ctx.film_rgb(32, 18), rgb, rtol=1e-5, atol=1e-12)
+
+
+# ---- the two map transforms of VRLIntegrator::preprocess (vrl.cpp:408-415): long beams and dicing -------------------
+def _gold():
+    import json, os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_vrl_struct.json")) as f:
+        return json.load(f)
+
+
+def test_dice_matches_oracle_and_reference_golden():
+    """vrlb_vrls_dice against (a) the pieces VRL::dice of the reference produced (tests/golden/ref_vrl_struct.json, made by
+    oracle/_ref/refprobe) and (b) the oracle on a 5000-VRL set: count and order identical, origin / direction / length
+    bit-exact, flux within 2e-6 (CUDA expf vs Enoki / glibc exp); m_scale untouched."""
+    import oracle
+    gold = _gold()
+    m = gold["medium"]
+    sc = scenes.Scene()
+    sc.add_medium(scenes.make_medium(sigma_t=m["sigma_t"], albedo=m["albedo"], scale=m["scale"]))
+    ctx = api.Context(0)
+    ctx.set_scene(sc)
+    src = np.ascontiguousarray(np.array(gold["dice_in"], np.float32).T)
+    ctx.upload_vrls(scenes.vrlset_desc(src, scale=0.25))
+    n = ctx.dice_vrls(gold["dice_n"])
+    want = np.array(gold["dice_out"], np.float64)[:, 1:].T.astype(np.float32)
+    got, _ = ctx.download_vrls()
+    assert n == want.shape[1] == got.shape[1]
+    assert np.array_equal(got[0:7], want[0:7])
+    assert np.allclose(got[7:10], want[7:10], rtol=2e-6, atol=0)
+    assert ctx.vrls_scale() == 0.25
+    # larger set, against the oracle
+    sc2 = scenes.box_fog_scene(occluders=True)
+    ctx.set_scene(sc2)
+    soa = scenes.synthetic_vrls(5000, seed=21)
+    ctx.upload_vrls(scenes.vrlset_desc(soa))
+    n2 = ctx.dice_vrls(4)
+    ref, _ = oracle.OracleScene(sc2).vrls_dice(soa, 4)
+    got2, _ = ctx.download_vrls()
+    assert n2 == ref.shape[1] and n2 > 4 * 5000
+    assert np.array_equal(got2[0:7], ref[0:7])
+    assert np.allclose(got2[7:10], ref[7:10], rtol=2e-6, atol=0)
+    # energy: the pieces of one VRL carry flux * Tr(start of piece) -- the first piece keeps the flux
+    first = np.nonzero(np.all(got2[0:3] == soa[0:3, :1], axis=0))[0][0]
+    assert np.array_equal(got2[7:10, first], soa[7:10, 0])
+    ctx.close()
+
+
+def test_to_long_matches_oracle_and_reference_golden():
+    """vrlb_vrls_to_long against VRL::convertToLong of the reference (golden) and the oracle; a VRL that sees no surface is
+    an error like the reference's Log(Error)."""
+    import oracle
+    gold = _gold()
+    m = gold["medium"]
+    sc = scenes.Scene()
+    sc.add_medium(scenes.make_medium(sigma_t=m["sigma_t"], albedo=m["albedo"], scale=m["scale"]))
+    sc.add_tris(np.array(gold["room_triangles"], np.float32).reshape(-1, 3, 3), abi.SURF_BSDF_SMOOTH)
+    ctx = api.Context(0)
+    ctx.set_scene(sc)
+    src = np.ascontiguousarray(np.array(gold["dice_in"], np.float32).T)
+    ctx.upload_vrls(scenes.vrlset_desc(src))
+    ctx.vrls_to_long()
+    got, _ = ctx.download_vrls()
+    assert np.allclose(got[6], np.array(gold["long"], np.float32), rtol=2e-6, atol=0)
+    assert np.array_equal(got[0:6], src[0:6]) and np.array_equal(got[7:10], src[7:10])
+    # box-fog: every VRL inside the fog container ends on a surface (container, walls, sphere or cuboid)
+    sc2 = scenes.box_fog_scene(occluders=True)
+    ctx.set_scene(sc2)
+    soa = scenes.synthetic_vrls(4000, seed=22)
+    ctx.upload_vrls(scenes.vrlset_desc(soa))
+    ctx.vrls_to_long()
+    ref, missed = oracle.OracleScene(sc2).vrls_to_long(soa)
+    got2, _ = ctx.download_vrls()
+    assert missed == 0 and np.array_equal(got2[6], ref)          # same Moeller-Trumbore arithmetic: bit-exact
+    assert np.all(got2[6] >= soa[6] - 1e-3)                      # long beams only grow (short ones were clipped to the box)
+    # no surface at all -> error
+    empty = scenes.Scene()
+    empty.add_medium(scenes.make_medium())
+    ctx.set_scene(empty)
+    ctx.upload_vrls(scenes.vrlset_desc(soa))
+    with pytest.raises(api.VrlbError, match="Impossible to convert to long vrl"):
+        ctx.vrls_to_long()
+    ctx.close()

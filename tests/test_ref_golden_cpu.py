@@ -153,3 +153,31 @@ def test_query_sum_matches_reference_sequential_stream(gold):
         o32, o64, ev = sc.gather(vd, seg, opt, rng_mode=oracle.RNG_SEQUENTIAL, n_threads=1)
         want = _arr(c["out"])
         assert _close(o32[0], want, rtol=5e-6), (c, o32[0])
+
+
+def test_dice_matches_reference(gold):
+    """VRL::dice compiled from the reference (pieces of mean length / 3, flux attenuated by the medium transmittance):
+    piece count, origins and lengths bit-exact (fp64 position arithmetic rounded once), flux to 1e-6 (Enoki exp vs libm)."""
+    src = np.ascontiguousarray(np.array(gold["dice_in"], np.float32).T)
+    want = np.array(gold["dice_out"], np.float64)
+    sc = oracle.OracleScene(_scene(gold, False))
+    got, med = sc.vrls_dice(src, gold["dice_n"])
+    assert got.shape[1] == len(want)
+    w = want[:, 1:].T.astype(np.float32)
+    assert np.array_equal(got[0:7], w[0:7])
+    assert _close(got[7:10], w[7:10], rtol=1e-6)
+    # the reference emits a zero-length tail piece whenever the length is an exact multiple of the dice length, and one
+    # zero-length piece for a zero-length VRL (while (current_distance <= length))
+    counts = np.bincount(want[:, 0].astype(int), minlength=src.shape[1])
+    assert counts[3] == 1 and counts.min() >= 1
+
+
+def test_to_long_matches_reference(gold):
+    """VRL::convertToLong compiled from the reference against the brute-force mock scene: si.t of the closest surface."""
+    src = np.ascontiguousarray(np.array(gold["dice_in"], np.float32).T)
+    sc = scenes.Scene()
+    sc.add_medium(_medium(gold))
+    sc.add_tris(np.array(gold["room_triangles"], np.float32).reshape(-1, 3, 3), abi.SURF_BSDF_SMOOTH)
+    got, missed = oracle.OracleScene(sc).vrls_to_long(src)
+    assert missed == 0
+    assert _close(got, np.array(gold["long"], np.float32), rtol=2e-6)
