@@ -208,7 +208,9 @@ def test_to_long_matches_oracle_and_reference_golden():
     ref, missed = oracle.OracleScene(sc2).vrls_to_long(soa)
     got2, _ = ctx.download_vrls()
     assert missed == 0 and np.array_equal(got2[6], ref)          # same Moeller-Trumbore arithmetic: bit-exact
-    assert np.all(got2[6] >= soa[6] - 1e-3)                      # long beams only grow (short ones were clipped to the box)
+    assert np.all(got2[6] > 0) and np.all(got2[6] <= 20 * np.sqrt(3) + 1e-3)   # ends on the container, a wall or an occluder
+    inside = np.linalg.norm(soa[0:3].T + soa[3:6].T * got2[6][:, None], axis=1, ord=np.inf) <= 10.0 + 1e-3
+    assert inside.all()
     # no surface at all -> error
     empty = scenes.Scene()
     empty.add_medium(scenes.make_medium())
