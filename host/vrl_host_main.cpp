@@ -3,6 +3,11 @@
 //   vrl_host render <scene.vrls> <set.vrlb> <out.f32> [key=value ...]     integrator properties as key=value
 //   vrl_host selftest                                                     property / error behaviour, no GPU needed
 //   vrl_host vol-info <file.vol> | obj-info <file.obj>                     the loaders of vrl_io.h (no GPU needed)
+//   vrl_host xml-info <scene.xml> [-Dname=value ...]                       what the scene loader of vrl_xml.h sees (no GPU needed)
+//   vrl_host render-xml <scene.xml> <out.pfm|out.f32> [-Dname=value ...] [key=value ...]
+//                                                                         the role of `mitsuba scene.xml`: load -> VRLIntegrator ->
+//                                                                         preprocess (light tracing on the device) -> render -> film;
+//                                                                         key=value overrides integrator properties of the file
 // An output name ending in .pfm receives the developed film (XYZ / W -> linear sRGB, hdrfilm.cpp:259-262) instead of
 // the raw XYZAW floats.
 // scene.vrls (test harness dump, written by tests/): u32 n_tris | verts | flags | u32 n_media | vrlb_medium[] |
@@ -14,9 +19,11 @@
 #include <cstring>
 #include <fstream>
 #include <iostream>
+#include <map>
 
 #include "vrl_integrator.h"
 #include "vrl_io.h"
+#include "vrl_xml.h"
 using namespace vrlhost;
 
 static void set_kv(Properties &p, const std::string &kv) {
@@ -88,6 +95,65 @@ int main(int argc, char **argv) {
             for (size_t i = 0; i < t.size(); ++i) { lo[i % 3] = std::min(lo[i % 3], (double) t[i]); hi[i % 3] = std::max(hi[i % 3], (double) t[i]); sum += t[i]; }
             std::printf("triangles %zu bbox %.9g %.9g %.9g %.9g %.9g %.9g checksum %.9g\n", t.size() / 9, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], sum);
             return 0;
+        }
+        if (argc >= 3 && (std::string(argv[1]) == "xml-info" || std::string(argv[1]) == "render-xml")) {
+            const bool render = std::string(argv[1]) == "render-xml";
+            if (render && argc < 4) { std::fprintf(stderr, "usage: vrl_host render-xml scene.xml out.pfm [-Dname=value ...] [key=value ...]\n"); return 2; }
+            std::map<std::string, std::string> defs; std::vector<std::string> overrides;
+            for (int i = render ? 4 : 3; i < argc; ++i) {
+                std::string a = argv[i];
+                if (a.rfind("-D", 0) == 0) { auto eq = a.find('='); if (eq == std::string::npos) throw std::runtime_error("expected -Dname=value: " + a); defs[a.substr(2, eq - 2)] = a.substr(eq + 1); }
+                else overrides.push_back(a);
+            }
+            LoadedScene ls = load_scene_xml(argv[2], defs);
+            for (auto &w : ls.warnings) std::fprintf(stderr, "[xml] warning: %s\n", w.c_str());
+            if (!render) {
+                const vrlb_camera &c = ls.sensor.camera;
+                double lo[3] = { 1e300, 1e300, 1e300 }, hi[3] = { -1e300, -1e300, -1e300 };
+                for (size_t i = 0; i < ls.scene.tri_verts.size(); ++i) { lo[i % 3] = std::min(lo[i % 3], (double) ls.scene.tri_verts[i]); hi[i % 3] = std::max(hi[i % 3], (double) ls.scene.tri_verts[i]); }
+                size_t n_null = 0, n_emit = 0, n_int = 0;
+                for (uint32_t f : ls.scene.tri_flags) { n_null += (f & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_NULL; n_emit += (f & VRLB_SURF_EMITTER) != 0; n_int += VRLB_SURF_GET_INTERIOR(f) >= 0; }
+                std::printf("{\"triangles\": %zu, \"null_triangles\": %zu, \"emitter_triangles\": %zu, \"interior_triangles\": %zu,\n", ls.scene.tri_flags.size(), n_null, n_emit, n_int);
+                std::printf(" \"bbox\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g],\n", lo[0], lo[1], lo[2], hi[0], hi[1], hi[2]);
+                std::printf(" \"media\": [");
+                for (size_t i = 0; i < ls.scene.media.size(); ++i) {
+                    const vrlb_medium &m = ls.scene.media[i];
+                    std::printf("%s{\"id\": \"%s\", \"kind\": %d, \"phase\": %d, \"g\": %.9g, \"scale\": %.9g, \"sigma_t\": [%.9g, %.9g, %.9g], \"albedo\": [%.9g, %.9g, %.9g], "
+                                "\"grid_res\": [%d, %d, %d], \"grid_bbox\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g], \"grid_max\": %.9g, "
+                                "\"nl_res\": [%d, %d, %d], \"nl_bbox\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g], \"top_ior\": %.9g, \"bottom_ior\": %.9g}",
+                                i ? ", " : "", ls.media_ids[i].c_str(), m.kind, m.phase, m.g, m.scale, m.sigma_t[0], m.sigma_t[1], m.sigma_t[2], m.albedo[0], m.albedo[1], m.albedo[2],
+                                m.grid_res[0], m.grid_res[1], m.grid_res[2], m.grid_bbox_min[0], m.grid_bbox_min[1], m.grid_bbox_min[2], m.grid_bbox_max[0], m.grid_bbox_max[1], m.grid_bbox_max[2], m.grid_max,
+                                m.nl_res[0], m.nl_res[1], m.nl_res[2], m.nl_bbox_min[0], m.nl_bbox_min[1], m.nl_bbox_min[2], m.nl_bbox_max[0], m.nl_bbox_max[1], m.nl_bbox_max[2], m.top_ior, m.bottom_ior);
+                }
+                std::printf("],\n \"emitters\": [");
+                for (size_t i = 0; i < ls.scene.emitters.size(); ++i) std::printf("%s[%.9g, %.9g, %.9g]", i ? ", " : "", ls.scene.emitters[i].radiance[0], ls.scene.emitters[i].radiance[1], ls.scene.emitters[i].radiance[2]);
+                std::printf("],\n \"sensor\": {\"width\": %d, \"height\": %d, \"spp\": %d, \"seed\": %llu, \"medium\": %d, \"near_clip\": %.9g, \"far_clip\": %.9g,\n  \"sample_to_camera\": [",
+                            c.width, c.height, ls.sensor.spp, (unsigned long long) ls.sensor.sampler_seed, c.medium, c.near_clip, c.far_clip);
+                for (int i = 0; i < 16; ++i) std::printf("%s%.9g", i ? ", " : "", c.sample_to_camera[i]);
+                std::printf("],\n  \"to_world\": [");
+                for (int i = 0; i < 16; ++i) std::printf("%s%.9g", i ? ", " : "", c.to_world[i]);
+                std::printf("]},\n \"integrator\": \"%s\", \"warnings\": %zu}\n", ls.integrator_type.c_str(), ls.warnings.size());
+                if (ls.integrator_type == "vrl") {                         // the constructor is where property errors surface (xml.cpp:1050-1068)
+                    Properties props = ls.integrator;
+                    for (auto &kv : overrides) set_kv(props, kv);
+                    VRLIntegrator integrator(props);
+                    std::cerr << integrator.to_string() << std::endl;
+                }
+                return 0;
+            }
+            if (ls.integrator_type != "vrl") throw std::runtime_error("the scene's integrator is \"" + ls.integrator_type + "\"; this plugin is <integrator type=\"vrl\">");
+            Properties props = ls.integrator;
+            for (auto &kv : overrides) set_kv(props, kv);
+            VRLIntegrator integrator(props);
+            std::cerr << integrator.to_string() << std::endl;
+            integrator.preprocess(ls.scene, ls.sensor);
+            std::vector<float> film;
+            bool ok = integrator.render(ls.scene, ls.sensor, film);
+            std::string out = argv[3];
+            if (out.size() > 4 && out.substr(out.size() - 4) == ".pfm")
+                write_pfm(out, develop_rgb(film, ls.sensor.camera.width, ls.sensor.camera.height), ls.sensor.camera.width, ls.sensor.camera.height);
+            else { std::ofstream o(out, std::ios::binary); o.write((const char *) film.data(), (std::streamsize) (film.size() * 4)); }
+            return ok ? 0 : 3;
         }
         if (argc < 5 || std::string(argv[1]) != "render") { std::fprintf(stderr, "usage: vrl_host render scene.vrls set.vrlb out.f32 [k=v ...] | selftest\n"); return 2; }
         HostScene sc; HostSensor se;
