@@ -234,6 +234,24 @@ int  vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64
 int  vrlb_vrls_to_long(vrlb_context *ctx);
 int  vrlb_vrls_dice(vrlb_context *ctx, uint32_t avg_number_dice, uint64_t *n_vrls_out);
 
+/* ---- volume photon map: the direct in-scattering term of VRLIntegrator::sample (vrl.cpp:523-611) ----------------------
+ * A resident photon set switches the term on (`use_direct_illum`): vrlb_gather / vrlb_render then add, for every in-medium
+ * camera segment, sum over the gather points (every 2 r along the segment, r = lookup_radius * lerp(0.75, 1.25, u)) of
+ * throughput * Tr * PhotonMap::estimateRadianceVolume (photonmap.h:216-271) * scale.  Photons are what the light tracer
+ * deposits at a particle's first medium scattering (vrl.cpp:278-281, 785: position, propagation direction, power after the
+ * albedo).  pos / dir / power are n x 3 floats each; `scale` = 1 / directVolumePathCount (vrl.cpp:431); `lookup_radius` =
+ * volume_lookup_radius_relative * scene radius (vrl.cpp:451).  Curved (nonlinear-medium) camera paths skip the term. */
+typedef struct vrlb_photonset_desc {
+    const float *pos, *dir, *power;
+    uint64_t     n;
+    float        scale;
+    float        lookup_radius;
+} vrlb_photonset_desc;
+int  vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set);   /* n = 0 clears the set (term off) */
+uint64_t vrlb_photons_count(const vrlb_context *ctx);
+/* Test/diagnostic entry: the direct term per resident camera segment (throughput included), host buffer n_segs*3. */
+int  vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *direct_out);
+
 /* ---- camera segments: replaces the medium branch of VRLIntegrator::sample up to the query
  *      (vrl.cpp:443-631) driven by SamplingIntegrator::render_block/render_sample
  *      (integrator.cpp:187-297) ----------------------------------------------------------------- */

@@ -52,6 +52,11 @@ class VrlSetDesc(C.Structure):
                 ("first_index", C.c_uint64), ("total", C.c_uint64), ("scale", C.c_float), ("pad", C.c_float)]
 
 
+class PhotonSetDesc(C.Structure):
+    _fields_ = [("pos", C.POINTER(C.c_float)), ("dir", C.POINTER(C.c_float)), ("power", C.POINTER(C.c_float)), ("n", C.c_uint64),
+                ("scale", C.c_float), ("lookup_radius", C.c_float)]
+
+
 class GenerateDesc(C.Structure):
     _fields_ = [("target_vrls", C.c_uint64), ("seed", C.c_uint64), ("max_depth", C.c_int32), ("rr_depth", C.c_int32),
                 ("min_vrl_length", C.c_float), ("use_non_linear", C.c_int32), ("use_laser", C.c_int32),

@@ -21,6 +21,7 @@ EXPORTS = [
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
     "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice",
+    "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments",
 ]
 
 
@@ -95,6 +96,10 @@ def load_library():
     L.vrlb_vrls_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.vrlb_vrls_to_long.argtypes = [vp]
     L.vrlb_vrls_dice.argtypes = [vp, C.c_uint32, C.POINTER(C.c_uint64)]
+    L.vrlb_photons_upload.argtypes = [vp, C.POINTER(abi.PhotonSetDesc)]
+    L.vrlb_photons_count.argtypes = [vp]
+    L.vrlb_photons_count.restype = C.c_uint64
+    L.vrlb_photon_gather_segments.argtypes = [vp, C.POINTER(abi.Options), f32p]
     L.vrlb_vrls_scale.argtypes = [vp]
     L.vrlb_vrls_scale.restype = C.c_float
     L.vrlb_vrls_download_depth.argtypes = [vp, C.POINTER(C.c_int32), C.c_uint64]
@@ -160,6 +165,24 @@ class Context:
         n = C.c_uint64()
         self._check(self.lib.vrlb_vrls_dice(self.h, int(avg_number_dice), C.byref(n)))
         return int(n.value)
+
+    def upload_photons(self, photon_desc):
+        """Volume photon set (scenes.photonset_desc); a resident set switches the direct in-scattering term on, n = 0 off."""
+        self._check(self.lib.vrlb_photons_upload(self.h, C.byref(photon_desc)))
+
+    def clear_photons(self):
+        d = abi.PhotonSetDesc()
+        self._check(self.lib.vrlb_photons_upload(self.h, C.byref(d)))
+
+    def photons_count(self):
+        return int(self.lib.vrlb_photons_count(self.h))
+
+    def photon_gather_segments(self, opt):
+        """The direct term per resident camera segment (throughput included)."""
+        n = int(self.lib.vrlb_segments_count(self.h))
+        out = np.zeros((max(n, 1), 3), np.float32)
+        self._check(self.lib.vrlb_photon_gather_segments(self.h, C.byref(opt), abi.fptr(out)))
+        return out[:n]
 
     def vrls_scale(self):
         return float(self.lib.vrlb_vrls_scale(self.h))

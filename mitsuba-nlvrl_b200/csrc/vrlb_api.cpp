@@ -60,6 +60,10 @@ struct vrlb_context {
     DevBuf<float> stage_soa; DevBuf<uint16_t> stage_med;
     uint64_t n_vrls = 0, vrl_first = 0, vrl_total = 0; float vrl_scale = 1.f;
 
+    // volume photon map (photons.cu): sorted by grid cell
+    DevBuf<DPhoton> photons; DevBuf<uint32_t> photon_cells; uint64_t n_photons = 0;
+    float photon_scale = 0.f, photon_radius = 0.f, photon_lo[3] = { 0, 0, 0 }, photon_inv_cell = 0.f; int32_t photon_res[3] = { 1, 1, 1 };
+
     // segments
     DevBuf<vrlb_segment> segs; uint64_t n_segs = 0;
     DevBuf<unsigned long long> counter;
@@ -659,10 +663,93 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     return VRLB_OK;
 }
 
+// direct term from the resident photon set (no-op without one); film path when seg_out_dev is null
+static int photon_gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_out_dev) {
+    if (ctx->n_photons == 0 && !seg_out_dev) return VRLB_OK;
+    if (!seg_out_dev && ctx->n_ranks > 1 && ctx->rank != 0) return VRLB_OK;   // VRL shards: the films are summed, the direct term is rank 0's
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "no scene resident");
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no camera segments resident");
+    PhotonGatherParams p{};
+    p.scene = ctx->scene; p.segs = ctx->segs.ptr; p.n_segs = ctx->n_segs;
+    p.photons = ctx->photons.ptr; p.cell_start = ctx->photon_cells.ptr; p.n_photons = ctx->n_photons;
+    for (int k = 0; k < 3; ++k) { p.grid_lo[k] = ctx->photon_lo[k]; p.grid_res[k] = ctx->photon_res[k]; }
+    p.inv_cell = ctx->photon_inv_cell; p.lookup_radius = ctx->photon_radius; p.scale = ctx->photon_scale;
+    p.nl_camera = opt->use_non_linear_camera;
+    p.film_rgb = seg_out_dev ? nullptr : ctx->film_rgb.ptr; p.seg_out = seg_out_dev;
+    CU(ctx, launch_photon_gather(p, ctx->stream));
+    if (p.n_segs) { ctx->timing.total_launches += 1; ctx->launches += 1; }
+    return VRLB_OK;
+}
+
 int vrlb_gather(vrlb_context *ctx, const vrlb_options *opt) {
     if (!ctx || !opt) return VRLB_ERR_INVALID;
     cudaSetDevice(ctx->device);
-    return gather_impl(ctx, opt, nullptr);
+    int rc = gather_impl(ctx, opt, nullptr);
+    if (rc == VRLB_OK) rc = photon_gather_impl(ctx, opt, nullptr);
+    return rc;
+}
+
+int vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set) {
+    if (!ctx || !set) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (set->n == 0) { ctx->n_photons = 0; return VRLB_OK; }
+    if (!set->pos || !set->dir || !set->power) return fail(ctx, VRLB_ERR_INVALID, "photon arrays missing");
+    if (!(set->lookup_radius > 0.f)) return fail(ctx, VRLB_ERR_INVALID, "lookup_radius must be > 0");
+    if (set->n > 0xfffffff0ull) return fail(ctx, VRLB_ERR_INVALID, "too many photons");
+    const uint64_t n = set->n;
+    // uniform grid over the photons' bounds, cell = 2 r_max (r_max = 1.25 lookup_radius): a gather sphere meets <= 8 cells
+    float lo[3] = { set->pos[0], set->pos[1], set->pos[2] }, hi[3] = { lo[0], lo[1], lo[2] };
+    for (uint64_t i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) { float v = set->pos[i * 3 + k]; if (!(v == v)) return fail(ctx, VRLB_ERR_INVALID, "NaN photon position"); lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v); }
+    float cell = 2.5f * set->lookup_radius;
+    for (;;) {
+        double cells = 1;
+        for (int k = 0; k < 3; ++k) { ctx->photon_res[k] = std::max(1, (int) std::floor((hi[k] - lo[k]) / cell) + 1); cells *= ctx->photon_res[k]; }
+        if (cells <= 16.0e6) break;
+        cell *= 1.5f;
+    }
+    const size_t n_cells = (size_t) ctx->photon_res[0] * ctx->photon_res[1] * ctx->photon_res[2];
+    const float inv_cell = 1.0f / cell;
+    std::vector<uint32_t> cell_of((size_t) n), order((size_t) n), start(n_cells + 1, 0);
+    for (uint64_t i = 0; i < n; ++i) {
+        uint32_t c[3];
+        for (int k = 0; k < 3; ++k) c[k] = (uint32_t) std::min(ctx->photon_res[k] - 1, std::max(0, (int) std::floor((set->pos[i * 3 + k] - lo[k]) * inv_cell)));
+        cell_of[i] = (c[2] * (uint32_t) ctx->photon_res[1] + c[1]) * (uint32_t) ctx->photon_res[0] + c[0];
+        start[cell_of[i] + 1] += 1;
+    }
+    for (size_t c = 0; c < n_cells; ++c) start[c + 1] += start[c];
+    { std::vector<uint32_t> cur(start.begin(), start.end() - 1);
+      for (uint64_t i = 0; i < n; ++i) order[cur[cell_of[i]]++] = (uint32_t) i; }           // counting sort: set order inside a cell
+    std::vector<DPhoton> sorted((size_t) n);
+    for (uint64_t k = 0; k < n; ++k) {
+        const uint64_t i = order[k];
+        sorted[k] = DPhoton{ set->pos[i * 3], set->pos[i * 3 + 1], set->pos[i * 3 + 2], 0.f, set->dir[i * 3], set->dir[i * 3 + 1], set->dir[i * 3 + 2], 0.f,
+                             set->power[i * 3], set->power[i * 3 + 1], set->power[i * 3 + 2], 0.f };
+    }
+    CU(ctx, ctx->photons.reserve(n)); CU(ctx, ctx->photon_cells.reserve(n_cells + 1));
+    CU(ctx, cudaMemcpyAsync(ctx->photons.ptr, sorted.data(), n * sizeof(DPhoton), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(ctx->photon_cells.ptr, start.data(), (n_cells + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 3; ++k) ctx->photon_lo[k] = lo[k];
+    ctx->photon_inv_cell = inv_cell; ctx->photon_scale = set->scale; ctx->photon_radius = set->lookup_radius; ctx->n_photons = n;
+    return VRLB_OK;
+}
+
+uint64_t vrlb_photons_count(const vrlb_context *ctx) { return ctx ? ctx->n_photons : 0; }
+
+int vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *direct_out) {
+    if (!ctx || !opt || !direct_out) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    DevBuf<float> tmp;
+    CU(ctx, tmp.reserve(ctx->n_segs * 3 + 1));
+    CU(ctx, cudaMemsetAsync(tmp.ptr, 0, (ctx->n_segs * 3 + 1) * sizeof(float), ctx->stream));
+    int rc = photon_gather_impl(ctx, opt, tmp.ptr);
+    if (rc == VRLB_OK) {
+        cudaError_t e = cudaMemcpyAsync(direct_out, tmp.ptr, ctx->n_segs * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = fail(ctx, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
+    }
+    tmp.release();
+    return rc;
 }
 
 /* Test/diagnostic entry: gather and also return Li per resident segment (before the weight), host buffer n_segs*3. */

@@ -79,6 +79,25 @@ cudaError_t launch_vrls_to_long(const DScene &s, DVrl *v, uint64_t n, unsigned l
 cudaError_t launch_vrls_dice(const DVrl *in, uint64_t n, const DMedium *media, float dice_len, uint32_t *counts,
                              const uint64_t *offsets, DVrl *out, cudaStream_t stream);
 
+// Volume photon map and the direct in-scattering term (photons.cu; vrl.cpp:523-611, photonmap.h:216-271)
+struct DPhoton {             // 48 B: position, propagation direction, power (PhotonData, photonmapper/photon.h)
+    float px, py, pz, pad0;
+    float dx, dy, dz, pad1;
+    float wr, wg, wb, pad2;
+};
+struct PhotonGatherParams {
+    DScene              scene;
+    const vrlb_segment *segs; uint64_t n_segs;
+    const DPhoton      *photons;      // sorted by grid cell
+    const uint32_t     *cell_start;   // n_cells + 1
+    uint64_t            n_photons;
+    float               grid_lo[3], inv_cell; int32_t grid_res[3];
+    float               lookup_radius, scale;
+    int32_t             nl_camera;    // use_non_linear_camera: segments of nonlinear media are curved paths (skipped here)
+    float              *film_rgb, *seg_out;
+};
+cudaError_t launch_photon_gather(const PhotonGatherParams &p, cudaStream_t stream);
+
 // FFMA-saturating microkernel (peak.cu)
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int iters, cudaStream_t stream);
 

@@ -351,6 +351,29 @@ def vrlset_desc(soa10, scale=None, first_index=0, total=None, medium=None):
     return d
 
 
+def photonset_desc(pos, direction, power, scale, lookup_radius):
+    """Builds a vrlb_photonset_desc over three [n, 3] fp32 arrays; the descriptor keeps them alive."""
+    pos, direction, power = (np.ascontiguousarray(a, np.float32).reshape(-1, 3) for a in (pos, direction, power))
+    assert len(pos) == len(direction) == len(power)
+    d = abi.PhotonSetDesc()
+    d.pos, d.dir, d.power = abi.fptr(pos), abi.fptr(direction), abi.fptr(power)
+    d.n, d.scale, d.lookup_radius = len(pos), scale, lookup_radius
+    d._keep = (pos, direction, power)
+    return d
+
+
+def synthetic_photons(n, seed=9, box=BOX, albedo=0.909):
+    """Seeded volume photons for the box-fog scene: positions uniform in the box, unit directions, grey power."""
+    u = _seeded_floats(seed, n * 7).reshape(n, 7)
+    pos = ((u[:, 0:3] * 2.0 - 1.0) * box).astype(np.float32)
+    z = u[:, 3] * 2.0 - 1.0
+    phi = u[:, 4] * (2.0 * math.pi)
+    r = np.sqrt(np.maximum(0.0, 1.0 - z * z))
+    direction = np.stack([r * np.cos(phi), r * np.sin(phi), z], 1).astype(np.float32)
+    power = (albedo * (0.5 + u[:, 5:6]) * np.array([[1.0, 0.9, 0.8]])).astype(np.float32)
+    return pos, direction, power
+
+
 # --------------------------------------------------------------------------- files (INTEGRATION.md "File formats")
 def save_vrlb(path, soa10, scale=None, medium=None):
     """Exported VRL set: "VRLB" | u32 version | u64 n | f32 scale | u32 pad | 10*n f32 (SoA) | n u16 medium ids."""

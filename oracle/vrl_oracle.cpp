@@ -913,6 +913,51 @@ float vrlo_grid_transmittance(const vrlo_scene *s, int medium, const float o[3],
     return grid_transmittance(*s, s->media[(size_t) medium], medium, V3(o), V3(d), maxt, &sub);
 }
 
+/* The direct in-scattering term of VRLIntegrator::sample for one in-medium camera segment (vrl.cpp:523-611): radius jitter
+ * (the draw before the query position), gather points at r, 3r, 5r ... while gather_t <= maxt - step, grey transmittance
+ * from the previous gather point (homoEvalTransmittance, medium.h:103-107), PhotonMap::estimateRadianceVolume with the
+ * RadianceQueryVolume functor (photonmap.h:216-271) -- here a plain loop over the photon set, the reference's kd-tree
+ * only changes the visiting order -- and the map's scale factor (vrl.cpp:610). */
+void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc *set, const vrlb_segment *segs, uint64_t n_segs,
+                                 const vrlb_options *opt, float *out_rgb) {
+    for (uint64_t i = 0; i < n_segs; ++i) {
+        const vrlb_segment &sg = segs[i];
+        float *out = out_rgb + i * 3;
+        out[0] = out[1] = out[2] = 0.f;
+        const vrlb_medium &m = s->media[(size_t) sg.medium];
+        if (sg.part != 0 || set->n == 0 || (m.kind == VRLB_MEDIUM_NONLINEAR && opt->use_non_linear_camera)) continue;
+        Pcg32 rng; rng.state = sg.rng_state; rng.inc = (PCG32_DEFAULT_STREAM << 1) | 1u;
+        rng.advance(-1);
+        const float radius = set->lookup_radius * lerp(0.75f, 1.25f, rng.next_f32());
+        float stepSize = radius, leftOver = 0.0f, gather_t = 0.f;
+        const V3 o(sg.o), d(sg.d);
+        V3 last = o, tr(sg.weight), direct(0.f);
+        const float md = max_density(m);
+        while (gather_t <= (sg.maxt - (stepSize - leftOver))) {
+            gather_t += (stepSize - leftOver);
+            leftOver = 0.0f;
+            const V3 gp = o + d * gather_t;
+            stepSize = radius * 2;
+            const float val = std::exp(md * -norm(gp - last));
+            tr = tr * (md != 0.f ? val : 1.0f);
+            V3 result(0.f);
+            const float radiusSqr = radius * radius;
+            for (uint64_t k = 0; k < set->n; ++k) {
+                const V3 pp(set->pos + k * 3), pd(set->dir + k * 3), pw(set->power + k * 3);
+                const float lengthSqr = squared_norm(gp - pp);
+                if ((radiusSqr - lengthSqr) < 0) continue;
+                const float photonPF = phase_eval(m, -pd, d);
+                const float q1 = 1.0f - lengthSqr / radiusSqr;
+                result = result + pw * photonPF * (q1 * q1) / radiusSqr * 0.31830988618379067154f * 3.0f;
+            }
+            direct = direct + tr * result;
+            last = gp;
+        }
+        direct = direct * set->scale;
+        out[0] = direct.x; out[1] = direct.y; out[2] = direct.z;
+    }
+}
+
 /* VRLMap::toLong -> VRL::convertToLong (vrl_map.h:56-62, vrl_struct.h:146-154): Ray3f r(origin, direction, 0) keeps the
  * default [RayEpsilon, inf) interval; length = si.t of the closest surface; a miss is Log(Error) = throw in the reference */
 uint64_t vrlo_vrls_to_long(const vrlo_scene *s, const float *soa10, uint64_t n, float *length_out) {

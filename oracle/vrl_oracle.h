@@ -65,6 +65,10 @@ int   vrlo_ray_intersect(const vrlo_scene *s, const float o[3], const float d[3]
 /* VRL::evalTransmittance (vrl_struct.h:509-572) for p1->p2 starting in medium `medium` */
 void  vrlo_eval_transmittance(const vrlo_scene *s, const float p1[3], const float p2[3], int medium, float out_rgb[3]);
 
+/* -- direct in-scattering term from the volume photon map (vrl.cpp:523-611, photonmap.h:216-271), per segment, throughput included -- */
+void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc *set, const vrlb_segment *segs, uint64_t n_segs,
+                                 const vrlb_options *opt, float *out_rgb);
+
 /* -- VRL-set transforms of VRLIntegrator::preprocess (vrl.cpp:408-415) -- */
 /* VRLMap::toLong (vrl_map.h:56-62): new lengths; returns the number of VRLs that see no surface (the reference throws) */
 uint64_t vrlo_vrls_to_long(const vrlo_scene *s, const float *soa10, uint64_t n, float *length_out);

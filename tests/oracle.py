@@ -54,6 +54,7 @@ def lib():
         L.vrlo_grid_eval.restype = C.c_float
         L.vrlo_grid_transmittance.argtypes = [C.c_void_p, C.c_int, f3, f3, C.c_float, C.c_uint64]
         L.vrlo_grid_transmittance.restype = C.c_float
+        L.vrlo_photon_gather_segments.argtypes = [C.c_void_p, C.POINTER(abi.PhotonSetDesc), C.c_void_p, C.c_uint64, C.POINTER(abi.Options), f3]
         L.vrlo_vrls_to_long.argtypes = [C.c_void_p, f3, C.c_uint64, f3]
         L.vrlo_vrls_to_long.restype = C.c_uint64
         L.vrlo_vrls_dice.argtypes = [C.c_void_p, f3, C.POINTER(C.c_uint16), C.c_uint64, C.c_uint32, f3, C.POINTER(C.c_uint16), C.c_uint64]
@@ -108,6 +109,13 @@ class OracleScene:
     def grid_transmittance(self, o, d, maxt, seed, medium=0):
         o, d = f32(o), f32(d)
         return lib().vrlo_grid_transmittance(self.h, medium, fp(o), fp(d), maxt, seed)
+
+    def photon_gather(self, photon_desc, segs, opt):
+        """Direct in-scattering term per segment (vrl.cpp:523-611), throughput included."""
+        segs = np.ascontiguousarray(segs)
+        out = np.zeros((len(segs), 3), np.float32)
+        lib().vrlo_photon_gather_segments(self.h, C.byref(photon_desc), segs.ctypes.data, len(segs), C.byref(opt), fp(out))
+        return out
 
     def vrls_to_long(self, soa10):
         """VRLMap::toLong: (new lengths, number of VRLs that see no surface)."""

@@ -260,3 +260,39 @@ def test_gather_matches_reference_compiled_golden(ctx, math_mode):
         err = np.abs(li[0] - want) / np.abs(want)
         assert err.max() <= REL_TOL, (c["seed"], math_mode, li[0], want)
     assert used >= 6
+
+
+@pytest.mark.parametrize("phase", [abi.PHASE_ISOTROPIC, abi.PHASE_HG])
+def test_photon_direct_term_matches_oracle(ctx, phase):
+    """Direct in-scattering term from the volume photon map (vrl.cpp:523-611, photonmap.h:216-271): the grid-binned CUDA
+    gather against the oracle's loop over all photons, per segment; then the film: with a resident photon set
+    vrlb_gather adds the term on top of the VRL gather, without one it does not."""
+    sc = scenes.box_fog_scene(occluders=True, phase=phase, g=0.6)
+    cam = scenes.box_fog_camera(48, 32)
+    opt = scenes.default_options(visibility=1)
+    soa = scenes.synthetic_vrls(300, seed=3)
+    vd = scenes.vrlset_desc(soa)
+    pos, pdir, power = scenes.synthetic_photons(20000, seed=9)
+    pd = scenes.photonset_desc(pos, pdir, power, scale=1.0 / 19999, lookup_radius=0.7)
+    osc = oracle.OracleScene(sc)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(vd)
+    ctx.build_segments(cam, opt)
+    segs = ctx.download_segments()
+    ctx.upload_photons(pd)
+    assert ctx.photons_count() == 20000
+    got = ctx.photon_gather_segments(opt).astype(np.float64)
+    ref = osc.photon_gather(pd, segs, opt).astype(np.float64)
+    assert (ref > 0).mean() > 0.5                                       # most camera segments see photons
+    assert rel_err(got, ref).max() <= 2e-5                              # same fp32 operations, different photon visiting order
+    # film = VRL term + direct term (the direct term already carries the path throughput)
+    ctx.clear_film(); ctx.gather(opt)
+    with_direct = ctx.film_rgb(cam.width, cam.height).reshape(-1, 3).astype(np.float64)
+    ctx.clear_photons()
+    assert ctx.photons_count() == 0
+    ctx.clear_film(); ctx.gather(opt)
+    vrl_only = ctx.film_rgb(cam.width, cam.height).reshape(-1, 3).astype(np.float64)
+    want = vrl_only.copy()
+    np.add.at(want, segs["pixel"], ref)
+    assert rel_err(with_direct, want).max() <= REL_TOL
+    assert with_direct.sum() > 1.05 * vrl_only.sum()

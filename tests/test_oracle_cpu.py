@@ -319,3 +319,40 @@ def test_no_cpu_fallback_without_gpu():
     with pytest.raises(api.VrlbError) as e:
         api.Context(0)
     assert e.value.code == abi.ERR_CUDA
+
+
+def test_photon_direct_term_single_photon_closed_form():
+    """Direct in-scattering term (vrl.cpp:523-611): one photon sitting on the first gather point of a segment.  The radius
+    jitter is the draw just before the segment's query position; the first gather point is at t = r; the estimate is
+    power * pf * (1 - 0)^2 / r^2 * 3 / pi, weighted by the throughput, exp(-sigma r) and the map's scale."""
+    L = oracle.lib()
+    sc = scenes.Scene()
+    med = scenes.make_medium(sigma_t=(0.3, 0.3, 0.3), albedo=(0.8,) * 3, scale=2.0)
+    sc.add_medium(med)
+    osc = oracle.OracleScene(sc)
+    st, inc = _pcg(1234)
+    bits = L.vrlo_pcg32_next_u32(C.byref(st), inc.value)
+    u = np.array([(bits >> 9) | 0x3f800000], np.uint32).view(np.float32)[0] - np.float32(1.0)
+    R = np.float32(0.5)
+    r = R * (np.float32(1.25) * u + (np.float32(0.75) - np.float32(0.75) * u))
+    seg = np.zeros(1, abi.SEGMENT_DTYPE)
+    seg["o"][0], seg["d"][0], seg["maxt"][0] = (1, 2, 3), (0, 0, 1), 1.5 * r        # room for exactly one gather point
+    seg["weight"][0] = (0.5, 0.25, 1.0)
+    seg["rng_state"][0] = st.value                                                  # the query starts after the jitter draw
+    power = np.array([[2.0, 3.0, 4.0]], np.float32)
+    pd = scenes.photonset_desc([[1, 2, 3 + r]], [[0, 1, 0]], power, scale=0.125, lookup_radius=float(R))
+    opt = scenes.default_options()
+    got = osc.photon_gather(pd, seg, opt)[0]
+    want = np.array([0.5, 0.25, 1.0]) * math.exp(-0.6 * r) * power[0] / (4 * math.pi) * 3 / (math.pi * r * r) * 0.125
+    assert np.allclose(got, want, rtol=2e-6)
+    # a photon just outside the radius contributes nothing; a segment shorter than r has no gather point
+    pd2 = scenes.photonset_desc([[1 + 1.001 * r, 2, 3 + r]], [[0, 1, 0]], power, scale=0.125, lookup_radius=float(R))
+    assert np.all(osc.photon_gather(pd2, seg, opt) == 0)
+    seg["maxt"][0] = 0.99 * r
+    assert np.all(osc.photon_gather(pd, seg, opt) == 0)
+    # gather points at r, 3r, 5r ...: a photon at 3r is seen through exp(-sigma 3r) (two transmittance factors multiplied)
+    seg["maxt"][0] = 3.5 * r
+    pd3 = scenes.photonset_desc([[1, 2, 3 + 3 * r]], [[0, 1, 0]], power, scale=1.0, lookup_radius=float(R))
+    got3 = osc.photon_gather(pd3, seg, opt)[0]
+    want3 = np.array([0.5, 0.25, 1.0]) * math.exp(-0.6 * 3 * r) * power[0] / (4 * math.pi) * 3 / (math.pi * r * r)
+    assert np.allclose(got3, want3, rtol=1e-5)
