@@ -1,5 +1,7 @@
 // vrl_integrator.cpp -- see vrl_integrator.h.  Host logic only; all computation happens in libvrl_b200.so.
 #include "vrl_integrator.h"
+#include <algorithm>
+#include <cmath>
 
 #include <cstdio>
 #include <cstring>
@@ -181,6 +183,17 @@ void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
         check(vrlb_vrls_generate(m_ctx, &g, &n, &particles), "vrlb_vrls_generate");
         std::fprintf(stderr, "[VRLIntegrator] VRL Map Created: %llu VRLs from %llu particles\n", (unsigned long long) n, (unsigned long long) particles);
         m_have_vrls = true;
+        // the volume photon map of the direct in-scattering term (vrl.cpp:79: capacity volume_photons iff use_direct_illum;
+        // lookup radius = volume_lookup_radius_relative * |bbox.center - bbox.max|, vrl.cpp:449-451).  Same particles as above.
+        if (m_useDirectIllum && m_volumePhotons > 0 && !scene.tri_verts.empty()) {
+            double lo[3] = { 1e300, 1e300, 1e300 }, hi[3] = { -1e300, -1e300, -1e300 };
+            for (size_t i = 0; i < scene.tri_verts.size(); ++i) { lo[i % 3] = std::min(lo[i % 3], (double) scene.tri_verts[i]); hi[i % 3] = std::max(hi[i % 3], (double) scene.tri_verts[i]); }
+            const double radius = 0.5 * std::sqrt((hi[0] - lo[0]) * (hi[0] - lo[0]) + (hi[1] - lo[1]) * (hi[1] - lo[1]) + (hi[2] - lo[2]) * (hi[2] - lo[2]));
+            uint64_t np = 0, paths = 0;
+            check(vrlb_photons_generate(m_ctx, &g, (uint64_t) m_volumePhotons, (float) (m_volumeLookupRadiusRelative * radius), &np, &paths), "vrlb_photons_generate");
+            std::fprintf(stderr, "[VRLIntegrator] Building volume PM, size: %llu (%llu particles), lookup radius %g\n",
+                         (unsigned long long) np, (unsigned long long) paths, m_volumeLookupRadiusRelative * radius);
+        }
     }
     // vrl.cpp:408-415: the map may be turned into long beams and / or diced before it is used
     if (m_longVRL) check(vrlb_vrls_to_long(m_ctx), "vrlb_vrls_to_long");

@@ -249,6 +249,13 @@ typedef struct vrlb_photonset_desc {
 } vrlb_photonset_desc;
 int  vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set);   /* n = 0 clears the set (term off) */
 uint64_t vrlb_photons_count(const vrlb_context *ctx);
+/* Light tracing on the device for the photon set (generate.cu, the same particles as vrlb_vrls_generate): one photon at each
+ * particle's first medium scattering, in particle order, until `capacity` (`volume_photons`) are stored; scale as the reference
+ * counts its paths (vrl.cpp:372-373, 431).  capacity = 0 or a scene where nothing scatters leaves no set (term off). */
+int  vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
+                           uint64_t *n_photons_out, uint64_t *n_particles_out);
+/* pos / dir / power (n x 3 each, any may be NULL) of the resident set in grid order, and its scale */
+int  vrlb_photons_download(vrlb_context *ctx, float *pos, float *dir, float *power, uint64_t cap, float *scale_out);
 /* Test/diagnostic entry: the direct term per resident camera segment (throughput included), host buffer n_segs*3. */
 int  vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *direct_out);
 

@@ -21,7 +21,7 @@ EXPORTS = [
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
     "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice",
-    "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments",
+    "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments", "vrlb_photons_generate", "vrlb_photons_download",
 ]
 
 
@@ -98,6 +98,8 @@ def load_library():
     L.vrlb_vrls_dice.argtypes = [vp, C.c_uint32, C.POINTER(C.c_uint64)]
     L.vrlb_photons_upload.argtypes = [vp, C.POINTER(abi.PhotonSetDesc)]
     L.vrlb_photons_count.argtypes = [vp]
+    L.vrlb_photons_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.c_uint64, C.c_float, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.vrlb_photons_download.argtypes = [vp, f32p, f32p, f32p, C.c_uint64, f32p]
     L.vrlb_photons_count.restype = C.c_uint64
     L.vrlb_photon_gather_segments.argtypes = [vp, C.POINTER(abi.Options), f32p]
     L.vrlb_vrls_scale.argtypes = [vp]
@@ -169,6 +171,20 @@ class Context:
     def upload_photons(self, photon_desc):
         """Volume photon set (scenes.photonset_desc); a resident set switches the direct in-scattering term on, n = 0 off."""
         self._check(self.lib.vrlb_photons_upload(self.h, C.byref(photon_desc)))
+
+    def generate_photons(self, gen, capacity, lookup_radius):
+        """Volume photons by light tracing on the device (vrlb_photons_generate); returns (n_photons, n_particles)."""
+        n, pcount = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.vrlb_photons_generate(self.h, C.byref(gen), int(capacity), float(lookup_radius), C.byref(n), C.byref(pcount)))
+        return int(n.value), int(pcount.value)
+
+    def download_photons(self):
+        """(pos, dir, power, scale) of the resident photon set, in grid order."""
+        n = self.photons_count()
+        pos, direction, power = (np.zeros((max(n, 1), 3), np.float32) for _ in range(3))
+        scale = C.c_float()
+        self._check(self.lib.vrlb_photons_download(self.h, abi.fptr(pos), abi.fptr(direction), abi.fptr(power), n, C.byref(scale)))
+        return pos[:n], direction[:n], power[:n], float(scale.value)
 
     def clear_photons(self):
         d = abi.PhotonSetDesc()

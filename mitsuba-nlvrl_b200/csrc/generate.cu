@@ -178,6 +178,11 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
         // real scattering event (homogeneous extinction: no null collisions), vrl.cpp:246-294
         push(pos, medium, throughput * e.flux);
         throughput = throughput * V3(m->albedo[0], m->albedo[1], m->albedo[2]);
+        if (!WRITE && p.photon_out && depth == 0) {                        // mediumDepth == 0: handleMediumInteraction, vrl.cpp:278-281, 785
+            const V3 w = throughput * e.flux;                              // flux * throughput after the albedo
+            p.photon_out[pi] = DPhoton{ pos.x, pos.y, pos.z, 0.f, dir.x, dir.y, dir.z, 0.f, w.x, w.y, w.z, 0.f };
+            p.photon_flag[pi] = 1u;
+        }
         ++depth;
         float u1 = rng.next_f32(), u2 = rng.next_f32();
         dir = sample_phase(*m, dir, u1, u2);
@@ -185,6 +190,7 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
         if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
     }
     if (!WRITE) p.counts[pi] = count;
+    if (!WRITE && p.photon_out && depth == 0) p.photon_flag[pi] = 0u;      // never scattered in a medium
 }
 
 cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream) {

@@ -395,12 +395,9 @@ int vrlb_vrls_download_depth(vrlb_context *ctx, int32_t *depth, uint64_t cap) {
     return VRLB_OK;
 }
 
-int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t *n_vrls_out, uint64_t *n_particles_out) {
-    if (!ctx || !gen) return VRLB_ERR_INVALID;
-    cudaSetDevice(ctx->device);
-    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_vrls_generate");
-    if (gen->target_vrls == 0) return fail(ctx, VRLB_ERR_INVALID, "target_vrls must be > 0");
-    if (gen->start_medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "start_medium out of range");
+// light-tracer parameters shared by VRL and volume-photon generation: emitter table (triangles flagged VRLB_SURF_EMITTER,
+// area cdf) + the integrator properties of vrlb_generate_desc
+static int setup_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, GenParams &p, DevBuf<int32_t> &d_etris, DevBuf<float> &d_ecdf) {
     // emitter table: triangles flagged VRLB_SURF_EMITTER, area cdf
     std::vector<int32_t> etris; std::vector<float> ecdf; double area = 0.0;
     if (!gen->use_laser) {
@@ -414,13 +411,11 @@ int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_
         }
         if (etris.empty()) return fail(ctx, VRLB_ERR_INVALID, "no emitter: the scene has no VRLB_SURF_EMITTER triangle and use_laser is 0");
     }
-    DevBuf<int32_t> d_etris; DevBuf<float> d_ecdf; DevBuf<uint32_t> d_counts; DevBuf<uint64_t> d_offsets;
     if (!etris.empty()) {
         CU(ctx, d_etris.reserve(etris.size())); CU(ctx, d_ecdf.reserve(ecdf.size()));
         CU(ctx, cudaMemcpy(d_etris.ptr, etris.data(), etris.size() * 4, cudaMemcpyHostToDevice));
         CU(ctx, cudaMemcpy(d_ecdf.ptr, ecdf.data(), ecdf.size() * 4, cudaMemcpyHostToDevice));
     }
-    GenParams p{};
     p.scene = ctx->scene; p.base_seed = gen->seed;
     p.max_depth = gen->max_depth > 0 ? gen->max_depth : 512; p.rr_depth = gen->rr_depth; p.max_steps = gen->max_steps > 0 ? gen->max_steps : 100000;
     p.use_non_linear = gen->use_non_linear; p.use_laser = gen->use_laser; p.start_medium = gen->start_medium;
@@ -428,6 +423,18 @@ int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_
     for (int k = 0; k < 3; ++k) { p.laser_o[k] = gen->laser_origin[k]; p.laser_d[k] = gen->laser_direction[k]; p.laser_power[k] = gen->laser_power[k]; }
     p.emit_tris = d_etris.ptr; p.emit_cdf = d_ecdf.ptr; p.n_emit_tris = (int32_t) etris.size(); p.emit_area = (float) area;
 
+    return VRLB_OK;
+}
+
+int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t *n_vrls_out, uint64_t *n_particles_out) {
+    if (!ctx || !gen) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_vrls_generate");
+    if (gen->target_vrls == 0) return fail(ctx, VRLB_ERR_INVALID, "target_vrls must be > 0");
+    if (gen->start_medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "start_medium out of range");
+    DevBuf<int32_t> d_etris; DevBuf<float> d_ecdf; DevBuf<uint32_t> d_counts; DevBuf<uint64_t> d_offsets;
+    GenParams p{};
+    { int rc = setup_generate(ctx, gen, p, d_etris, d_ecdf); if (rc) return rc; }
     const uint64_t target = gen->target_vrls;
     uint64_t have = 0, particles = 0;
     uint64_t wave = std::min<uint64_t>(std::max<uint64_t>(target / 4, 4096), 1u << 22);
@@ -734,7 +741,76 @@ int vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set) {
     return VRLB_OK;
 }
 
+// Volume photons by light tracing: the same particles as vrlb_vrls_generate (particle i = PCG32 seed(seed + i)), one
+// photon at a particle's first medium scattering, in particle order until `capacity` photons are stored.  Scale factor
+// as the reference counts it (vrl.cpp:372-373, 431): a path is counted when it deposited AND the map is not full after
+// it, i.e. capacity - 1 paths for a filled map.
+int vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
+                          uint64_t *n_photons_out, uint64_t *n_particles_out) {
+    if (!ctx || !gen) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_photons_generate");
+    if (gen->start_medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "start_medium out of range");
+    if (n_photons_out) *n_photons_out = 0;
+    if (n_particles_out) *n_particles_out = 0;
+    if (capacity == 0) { ctx->n_photons = 0; return VRLB_OK; }            // PhotonMap(m_useDirectIllum ? m_volumePhotons : 0), vrl.cpp:79
+    DevBuf<int32_t> d_etris; DevBuf<float> d_ecdf; DevBuf<uint32_t> d_counts, d_flags; DevBuf<DPhoton> d_ph;
+    GenParams p{};
+    { int rc = setup_generate(ctx, gen, p, d_etris, d_ecdf); if (rc) return rc; }
+    std::vector<float> pos, dir, power;
+    std::vector<uint32_t> flags; std::vector<DPhoton> ph;
+    uint64_t have = 0, particles = 0;
+    uint64_t wave = std::min<uint64_t>(std::max<uint64_t>(capacity + capacity / 4, 4096), 1u << 20);
+    bool done = false;
+    for (int iter = 0; iter < 256 && !done; ++iter) {
+        if (ctx->cancel.exchange(0)) return fail(ctx, VRLB_ERR_CANCELLED, "cancelled");
+        CU(ctx, d_counts.reserve(wave)); CU(ctx, d_flags.reserve(wave)); CU(ctx, d_ph.reserve(wave));
+        CU(ctx, cudaMemsetAsync(d_flags.ptr, 0, wave * 4, ctx->stream));
+        p.n_particles = wave; p.first_particle = particles; p.counts = d_counts.ptr; p.photon_out = d_ph.ptr; p.photon_flag = d_flags.ptr;
+        CU(ctx, launch_generate(p, false, ctx->stream)); ctx->launches += 1;
+        flags.resize(wave); ph.resize(wave);
+        CU(ctx, cudaMemcpyAsync(flags.data(), d_flags.ptr, wave * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaMemcpyAsync(ph.data(), d_ph.ptr, wave * sizeof(DPhoton), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        uint64_t used = wave;
+        for (uint64_t i = 0; i < wave; ++i) {
+            if (!flags[i]) continue;
+            const DPhoton &q = ph[i];
+            pos.insert(pos.end(), { q.px, q.py, q.pz }); dir.insert(dir.end(), { q.dx, q.dy, q.dz }); power.insert(power.end(), { q.wr, q.wg, q.wb });
+            if (++have == capacity) { used = i + 1; done = true; break; }
+        }
+        particles += used;
+        if (!done && have == 0 && iter >= 3) break;                       // nothing scatters in a medium
+    }
+    d_etris.release(); d_ecdf.release(); d_counts.release(); d_flags.release(); d_ph.release();
+    if (n_photons_out) *n_photons_out = have;
+    if (n_particles_out) *n_particles_out = particles;
+    if (have == 0) { ctx->n_photons = 0; return VRLB_OK; }
+    const uint64_t counted = have == capacity ? capacity - 1 : have;     // paths counted while the map was not full
+    vrlb_photonset_desc d{};
+    d.pos = pos.data(); d.dir = dir.data(); d.power = power.data(); d.n = have;
+    d.scale = counted ? 1.0f / (float) counted : 1.0f; d.lookup_radius = lookup_radius;
+    return vrlb_photons_upload(ctx, &d);
+}
+
 uint64_t vrlb_photons_count(const vrlb_context *ctx) { return ctx ? ctx->n_photons : 0; }
+
+int vrlb_photons_download(vrlb_context *ctx, float *pos, float *dir, float *power, uint64_t cap, float *scale_out) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (scale_out) *scale_out = ctx->photon_scale;
+    const uint64_t n = ctx->n_photons;
+    if (cap < n) return fail(ctx, VRLB_ERR_INVALID, "capacity %llu < %llu photons", (unsigned long long) cap, (unsigned long long) n);
+    if (n == 0) return VRLB_OK;
+    std::vector<DPhoton> tmp((size_t) n);
+    CU(ctx, cudaMemcpy(tmp.data(), ctx->photons.ptr, n * sizeof(DPhoton), cudaMemcpyDeviceToHost));
+    for (uint64_t i = 0; i < n; ++i) {
+        if (pos)   { pos[i * 3] = tmp[i].px; pos[i * 3 + 1] = tmp[i].py; pos[i * 3 + 2] = tmp[i].pz; }
+        if (dir)   { dir[i * 3] = tmp[i].dx; dir[i * 3 + 1] = tmp[i].dy; dir[i * 3 + 2] = tmp[i].dz; }
+        if (power) { power[i * 3] = tmp[i].wr; power[i * 3 + 1] = tmp[i].wg; power[i * 3 + 2] = tmp[i].wb; }
+    }
+    return VRLB_OK;
+}
 
 int vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *direct_out) {
     if (!ctx || !opt || !direct_out) return VRLB_ERR_INVALID;

@@ -57,6 +57,7 @@ cudaError_t launch_pack_vrls(const float *soa10, const uint16_t *medium, uint64_
 cudaError_t launch_unpack_vrls(const DVrl *in, uint64_t n, float *soa10, uint16_t *medium, cudaStream_t stream);
 
 // VRL generation by light tracing (generate.cu)
+struct DPhoton;
 struct GenParams {
     DScene    scene;
     uint64_t  n_particles, first_particle, base_seed;
@@ -71,6 +72,8 @@ struct GenParams {
     uint32_t *counts;             // device, per particle (count pass)
     const uint64_t *offsets;      // device, n_particles + 1 (write pass)
     DVrl     *out;                // device, VRL records
+    DPhoton  *photon_out;     // device or null (count pass only): one slot per particle of the wave, the volume photon of
+    uint32_t *photon_flag;        //   its FIRST medium scattering (vrl.cpp:278-281) and whether it deposited one
 };
 cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream);
 

@@ -219,3 +219,31 @@ def test_to_long_matches_oracle_and_reference_golden():
     with pytest.raises(api.VrlbError, match="Impossible to convert to long vrl"):
         ctx.vrls_to_long()
     ctx.close()
+
+
+def test_volume_photons_are_the_first_scatterings_of_the_same_particles(ctx):
+    """vrlb_photons_generate traces the same particles as vrlb_vrls_generate: photon k sits at the end of the direct
+    (depth-0) VRL of a particle, travels in that VRL's direction and carries the flux of the VRL that starts there
+    (power after the albedo, vrl.cpp:270-281).  Capacity and the reference's path count (capacity - 1) are honoured."""
+    sigma_t, albedo = 1.0, 0.8
+    sc = _fog(200.0, scenes.make_medium(sigma_t=(sigma_t,) * 3, albedo=(albedo,) * 3))
+    ctx.set_scene(sc)
+    gen = scenes.generate_desc(20000, seed=11, max_depth=100000, rr_depth=5, laser=((0, 0, 0), (0, 0, 1), (2.0, 1.0, 0.5)), start_medium=0)
+    ctx.generate_vrls(gen)
+    soa, _ = ctx.download_vrls()
+    depth = ctx.download_vrl_depths()
+    n, particles = ctx.generate_photons(gen, 2000, 0.5)
+    assert n == 2000 and particles == 2000                       # every particle scatters in the unbounded fog
+    pos, pdir, power, scale = ctx.download_photons()
+    assert scale == pytest.approx(1.0 / 1999)
+    direct = np.nonzero(depth == 0)[0][:2000]                   # the direct VRLs of particles 0 .. 1999, in particle order
+    ends = (soa[0:3, direct] + soa[3:6, direct] * soa[6, direct]).T
+    # the resident set is in grid-cell order: match by position
+    key = lambda a: np.lexsort((a[:, 2], a[:, 1], a[:, 0]))
+    assert np.allclose(pos[key(pos)], ends[key(ends)], atol=2e-5)
+    assert np.allclose(pdir, [[0, 0, 1]], atol=1e-6)            # laser direction
+    assert np.allclose(power, np.array([[2.0, 1.0, 0.5]]) * albedo, rtol=1e-5)
+    # exponential free flight: mean distance of the photons from the laser origin
+    assert pos[:, 2].mean() == pytest.approx(1 / sigma_t, abs=5 / np.sqrt(2000))
+    # capacity 0 switches the term off (vrl.cpp:79)
+    assert ctx.generate_photons(gen, 0, 0.5) == (0, 0) and ctx.photons_count() == 0

@@ -200,3 +200,22 @@ def test_render_xml_end_to_end(host, tmp_path):
     pfm = os.path.join(str(tmp_path), "film.pfm")
     r3 = subprocess.run([host, "render-xml", path, pfm, "-Dspp=1", "target_vrls=200"], capture_output=True, text=True)
     assert r3.returncode == 0 and open(pfm, "rb").read(2) == b"PF"
+
+
+@pytest.mark.gpu
+def test_render_xml_direct_term_switch(host, tmp_path):
+    """use_direct_illum (default true, vrl.cpp:57): the plugin builds the volume photon map from the same light tracing and
+    adds the direct in-scattering term; with use_direct_illum=false the film holds the VRL term only and is darker."""
+    path = _write_scene(str(tmp_path))
+    txt = open(path).read().replace('<medium id="fog" type="nonlinear">', '<medium id="fog" type="homogeneous">')
+    open(path, "w").write(txt)
+    films = {}
+    for flag in ("true", "false"):
+        out = os.path.join(str(tmp_path), f"film_{flag}.f32")
+        r = subprocess.run([host, "render-xml", path, out, "-Dspp=1", f"use_direct_illum={flag}", "volume_photons=20000",
+                            "volume_lookup_radius_relative=0.05"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert ("Building volume PM" in r.stderr) == (flag == "true")
+        films[flag] = np.fromfile(out, np.float32).reshape(48, 64, 5)
+    a, b = films["true"][..., 1], films["false"][..., 1]
+    assert np.isfinite(a).all() and np.all(a >= b - 1e-7) and a.sum() > 1.02 * b.sum()
