@@ -124,7 +124,12 @@ VRLIntegrator::VRLIntegrator(const Properties &props) {
         for (size_t i = 0; i < rest.size(); ++i) msg += (i ? ", \"" : "\"") + rest[i] + "\"";
         Throw(msg);
     }
-    if (m_useLightCut) Throw("use_light_cut: the lightcut accelerator is not on the B200 path yet (DESIGN.md section 7)");
+    // The lightcut (vrl_lightcut.h) is the reference's way to make 32k-128k VRLs affordable on CPU cores: it replaces
+    // clusters of VRLs by a representative whenever a bound on the cluster's error is below `threshold_error`.  The B200
+    // gather evaluates every VRL (error 0 <= any threshold), so the option is accepted and the cut parameters are
+    // unused; images differ from the reference's lightcut images by the reference's own clustering error.
+    if (m_useLightCut)
+        std::fprintf(stderr, "[VRLIntegrator] use_light_cut: the B200 gather evaluates the full VRL set (exact; threshold_error = %g is met trivially)\n", m_thresholdError);
     if (m_samplesPerQuery < 1) Throw("\"samples_per_query\" must be >= 1");
 }
 
