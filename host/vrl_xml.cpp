@@ -133,9 +133,11 @@ void set_param(Params &params, const std::string &k, const std::string &v, bool 
     std::stable_sort(params.begin(), params.end(), [](auto &a, auto &b) { return a.first.size() > b.first.size(); });
 }
 
+bool upgrade_tree(Node &root, const std::string &path, std::vector<std::string> &notes);
+
 // Depth-first: <default> defines a parameter unless the caller already set it, <include> splices the children of the
 // included file's root in place (xml.cpp:651-690), every other tag gets its attributes substituted.
-void expand(Node &n, Params &params, const std::string &base_dir, int depth) {
+void expand(Node &n, Params &params, const std::string &base_dir, int depth, std::vector<std::string> &notes) {
     if (depth > 16) fail("Error while loading \"" + n.file + "\": includes nested too deeply");
     std::vector<Node> out;
     for (Node &c : n.children) {
@@ -146,14 +148,129 @@ void expand(Node &n, Params &params, const std::string &base_dir, int depth) {
             std::string text = read_text(path);
             Node root = Parser(text, path).document();
             if (root.name != "scene") fail("Error while loading \"" + path + "\": root element of an included file must be <scene>");
-            expand(root, params, dir_of(path), depth + 1);
+            upgrade_tree(root, path, notes);
+            expand(root, params, dir_of(path), depth + 1, notes);
             for (Node &g : root.children) out.push_back(std::move(g));
             continue;
         }
-        expand(c, params, base_dir, depth);
+        expand(c, params, base_dir, depth, notes);
         out.push_back(std::move(c));
     }
     n.children = std::move(out);
+}
+
+// ---- scene versions before 2.0 (xml.cpp:350-392 upgrade_tree, run per file like the reference does) ----
+// The reference's own in-memory upgrade: every name="..." except on <default> goes from camelCase to underscore_case,
+// <lookAt> becomes <lookat>, ids with a leading underscore are renamed, diffuse_reflectance of a diffuse BSDF becomes
+// reflectance.  On top of that, what the 0.x scenes of data/FBD15ALVRL_scenes need and no plugin of the fork provides
+// ("reusable after schema translation"), each reported in `notes`:
+//   medium sigma_s + sigma_a            -> sigma_t = sigma_s + sigma_a, albedo = sigma_s / sigma_t
+//   shape with a medium and no BSDF     -> index-matched boundary (0.x Shape::configure), i.e. <bsdf type="null"/>
+//   <integrator type="vrl"> properties  -> those of the LightSlice implementation these scenes were written for are dropped;
+//                                          VRLIntegrator then runs on its defaults (or the caller's overrides)
+int version_major(const Node &root, const std::string &path) {
+    const std::string v = root.get("version", "");
+    if (v.empty()) fail("Error while loading \"" + path + "\": missing version attribute in root element <scene>");
+    size_t used = 0; int major = -1;
+    try { major = std::stoi(v, &used); } catch (...) {}
+    if (major < 0 || (used < v.size() && v[used] != '.')) fail("Error while loading \"" + path + "\": could not parse scene version \"" + v + "\"");
+    return major;
+}
+std::string underscore_case(std::string name) {         // the loop of xml.cpp:365-375, including its skip after a hump
+    for (size_t i = 0; i + 1 < name.length(); ++i) {
+        if (std::islower((unsigned char) name[i]) && std::isupper((unsigned char) name[i + 1])) {
+            name = name.substr(0, i + 1) + "_" + name.substr(i + 1);
+            i += 2;
+            while (i < name.length() && std::isupper((unsigned char) name[i])) { name[i] = (char) std::tolower((unsigned char) name[i]); ++i; }
+        }
+    }
+    return name;
+}
+const char *const kVrlProps[] = {       // what VRLIntegrator's constructor queries (vrl_integrator.cpp <- vrl.cpp:38-104)
+    "block_size", "caustic_lookup_radius_relative", "caustic_lookup_size", "caustic_photons", "device", "dice_vrl",
+    "global_lookup_radius_relative", "global_lookup_size", "global_photons", "hide_emitters", "laser_direction", "laser_origin",
+    "lightcut_samples", "long_vrl", "math_mode", "max_depth", "min_vrl_length", "rr_depth", "rr_vrl", "samples_per_pass",
+    "samples_per_query", "scale_rr", "shoot_center", "stochastic_lightcut", "target_vrls", "threshold_better_dist", "threshold_error",
+    "timeout", "use_direct_illum", "use_laser", "use_light_cut", "use_nl_atomic_query", "use_non_linear", "use_non_linear_camera",
+    "use_uniform_sampling", "volume_lookup_radius_relative", "volume_photons" };
+void set_attr(Node &n, const char *k, const std::string &v) { for (auto &a : n.attrs) if (a.first == k) { a.second = v; return; } n.attrs.emplace_back(k, v); }
+void upgrade_names(Node &n, std::vector<std::string> &notes) {
+    if (n.name == "lookAt") n.name = "lookat";
+    if (n.name != "default") if (auto *nm = n.attr("name")) if (!nm->empty()) set_attr(n, "name", underscore_case(*nm));
+    if (auto *id = n.attr("id")) if (!id->empty() && (*id)[0] == '_') {
+        const std::string renamed = "ID" + *id + "__UPGR";
+        notes.push_back("changing identifier: \"" + *id + "\" -> \"" + renamed + "\"");
+        set_attr(n, "id", renamed);
+    }
+    if (n.name == "bsdf" && n.get("type", "") == "diffuse")
+        for (Node &c : n.children) if (c.get("name", "") == "diffuse_reflectance") set_attr(c, "name", "reflectance");
+    for (Node &c : n.children) upgrade_names(c, notes);
+}
+void translate_legacy(Node &n, std::vector<std::string> &notes) {
+    auto find = [&](const char *nm) -> Node * { for (Node &c : n.children) if (c.name != "ref" && c.get("name", "") == nm) return &c; return nullptr; };
+    if (n.name == "medium" && find("sigma_s") && find("sigma_a") && !find("sigma_t")) {
+        Node *ns = find("sigma_s"), *na = find("sigma_a");
+        auto comps = [&](const Node &c) {
+            const std::string v = c.get("value");
+            if (v.find(':') != std::string::npos) fail("Error while loading \"" + n.file + "\": medium coefficient \"" + c.get("name") + "\" is a wavelength table; only constants are translated");
+            std::vector<double> r; std::string tok;
+            for (char ch : v + ",") { if (ch == ',' || std::isspace((unsigned char) ch)) { if (!tok.empty()) { r.push_back(std::stod(tok)); tok.clear(); } } else tok += ch; }
+            if (r.size() == 1) r = { r[0], r[0], r[0] };
+            if (r.size() != 3) fail("Error while loading \"" + n.file + "\": medium coefficient \"" + c.get("name") + "\" needs 1 or 3 components");
+            return r;
+        };
+        const auto s = comps(*ns), a = comps(*na);
+        std::ostringstream st, al, note; st.precision(17); al.precision(17); note.precision(6);       // 17 digits: the double survives the round trip
+        for (int k = 0; k < 3; ++k) {
+            const double t = s[(size_t) k] + a[(size_t) k], alb = t > 0 ? s[(size_t) k] / t : 0.0;
+            st << (k ? ", " : "") << t; al << (k ? ", " : "") << alb;
+            note << (k ? ", " : "") << t << " / " << alb;
+        }
+        Node t; t.name = "rgb"; t.file = n.file; t.attrs = { { "name", "sigma_t" }, { "value", st.str() } };
+        Node b; b.name = "rgb"; b.file = n.file; b.attrs = { { "name", "albedo" }, { "value", al.str() } };
+        std::vector<Node> kept;
+        for (Node &c : n.children) if (&c != ns && &c != na) kept.push_back(std::move(c));
+        kept.push_back(std::move(t)); kept.push_back(std::move(b));
+        n.children = std::move(kept);
+        notes.push_back("medium \"" + n.get("id", "") + "\": sigma_s / sigma_a translated to sigma_t / albedo = " + note.str());
+    }
+    if (n.name == "shape") {
+        bool has_bsdf = false, has_medium = false, has_emitter = false;
+        for (const Node &c : n.children) {
+            if (c.name == "bsdf") has_bsdf = true;
+            else if (c.name == "medium") has_medium = true;
+            else if (c.name == "emitter") has_emitter = true;
+            else if (c.name == "ref") { const std::string nm = c.get("name", ""); if (nm == "interior" || nm == "exterior") has_medium = true; else has_bsdf = true; }
+        }
+        if (has_medium && !has_bsdf && !has_emitter) {
+            Node b; b.name = "bsdf"; b.file = n.file; b.attrs = { { "type", "null" } };
+            n.children.push_back(std::move(b));
+            notes.push_back("0.x shape with a medium and no BSDF: loaded as an index-matched boundary (null BSDF), as 0.x Shape::configure did");
+        }
+    }
+    if (n.name == "integrator" && n.get("type", "") == "vrl") {
+        std::vector<Node> kept;
+        std::string dropped;
+        for (Node &c : n.children) {
+            const std::string nm = c.get("name", "");
+            bool known = false;
+            for (const char *k : kVrlProps) known = known || nm == k;
+            if (known) kept.push_back(std::move(c));
+            else dropped += (dropped.empty() ? "" : ", ") + nm;
+        }
+        n.children = std::move(kept);
+        if (!dropped.empty()) notes.push_back("0.x <integrator type=\"vrl\"> properties of another VRL implementation are dropped: " + dropped);
+    }
+    for (Node &c : n.children) translate_legacy(c, notes);
+}
+// returns true when the file was upgraded
+bool upgrade_tree(Node &root, const std::string &path, std::vector<std::string> &notes) {
+    const int major = version_major(root, path);
+    if (major >= 2) return false;
+    notes.push_back("\"" + path + "\": in-memory version upgrade (v" + root.get("version") + " -> v2.0.0)");
+    upgrade_names(root, notes);
+    translate_legacy(root, notes);
+    return true;
 }
 
 // ---- numbers, vectors, transforms ----

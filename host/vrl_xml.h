@@ -13,7 +13,10 @@
 //            wrong-type errors are those of VRLIntegrator's constructor
 // What the hot path asks of a BSDF is one bit (BSDFFlags::Null or not, vrl_struct.h:529); delta BSDFs (dielectric,
 // conductor ...) have no specular chain on this path yet: they load as occluders and are listed in `warnings`.
-// Scene versions before 2.0 (the 0.x schemas of data/FBD15ALVRL_scenes) are refused like an unknown version.
+// Scene versions before 2.0 get the reference's in-memory upgrade (xml.cpp:350-392: camelCase -> underscore_case names,
+// lookAt) and, for the 0.x scenes of data/FBD15ALVRL_scenes, the schema translation of SURVEY.md 8c (sigma_s/sigma_a ->
+// sigma_t/albedo, medium boundary without BSDF -> null BSDF, the other implementation's integrator properties dropped);
+// every step is listed in `warnings`.
 #pragma once
 #include <map>
 #include <memory>

@@ -243,15 +243,14 @@ LoadedScene load_scene_xml(const std::string &path, const std::map<std::string, 
     std::string text = read_text(path);
     Node root = Parser(text, path).document();
     if (root.name != "scene") fail("Error while loading \"" + path + "\": root element must be <scene>");
-    const std::string version = root.get("version", "");
-    if (version.empty()) fail("Error while loading \"" + path + "\": missing version attribute in root element <scene>");
-    if (version.compare(0, 2, "2.") != 0 && version.compare(0, 2, "3.") != 0)
-        fail("Error while loading \"" + path + "\": scene version " + version + " needs the 0.x -> 2.0 upgrade of xml.cpp:357-392, which this loader does not perform");
+    std::vector<std::string> notes;
+    upgrade_tree(root, path, notes);              // scene versions before 2.0 (xml.cpp:350-392); checks the version attribute
     Params params;
     for (auto &p : params_in) set_param(params, p.first, p.second, false);
-    expand(root, params, dir_of(path), 0);
+    expand(root, params, dir_of(path), 0, notes);
 
     Builder b;
+    for (auto &w : notes) b.warn(w);
     b.base_dir = dir_of(path);
     b.index_ids(root);
     // media first (ids are referenced by shapes and the sensor), in document order so that ids are stable

@@ -148,11 +148,80 @@ def test_property_and_schema_errors(host, tmp_path):
     old = os.path.join(str(tmp_path), "old.xml")
     open(old, "w").write('<scene version="0.6.0"><integrator type="vrl"/></scene>')
     rc, info, err = _info(host, old)
-    assert rc != 0 and "0.6.0" in err and "upgrade" in err
+    assert rc != 0 and "no sensor" in err                                # 0.x files are upgraded now, not refused
+    open(old, "w").write('<scene><integrator type="vrl"/></scene>')
+    rc, info, err = _info(host, old)
+    assert rc != 0 and "missing version attribute" in err
     bad = os.path.join(str(tmp_path), "bad.xml")
     open(bad, "w").write('<scene version="2.0.0"><sensor type="perspective"></scene>')
     rc, info, err = _info(host, bad)
     assert rc != 0 and "mismatched closing tag" in err and "line 1" in err
+
+
+def _legacy(txt):
+    """The synthetic scene respelt the way the 0.x scenes of data/FBD15ALVRL_scenes are written: camelCase names, <lookAt>,
+    sigmaS / sigmaA, a medium boundary without BSDF, an integrator property of the LightSlice implementation."""
+    txt = txt.replace('<medium id="fog" type="nonlinear">', '<medium id="fog" type="homogeneous">')
+    txt = txt.replace('<scene version="2.0.0">', '<scene version="0.6.0">', 1)
+    for a, b in (("fov_axis", "fovAxis"), ("near_clip", "nearClip"), ("far_clip", "farClip"), ("to_world", "toWorld"),
+                 ("sample_count", "sampleCount"), ("<lookat", "<lookAt"), ("target_vrls", "targetVrls"),
+                 ("samples_per_query", "samplesPerQuery"), ("use_light_cut", "useLightCut"), ("min_vrl_length", "minVrlLength")):
+        txt = txt.replace(a, b)
+    txt = txt.replace('<rgb name="sigma_t" value="0.2, 0.22, 0.24"/>', '<spectrum name="sigmaS" value="0.18, 0.198, 0.216"/>'
+                      '<spectrum name="sigmaA" value="0.02, 0.022, 0.024"/>').replace('<rgb name="albedo" value="0.9"/>', "")
+    txt = txt.replace('<shape type="cube">\n        <bsdf type="null"/>', '<shape type="cube" name="fogBox">')
+    assert "sigmaS" in txt and "fogBox" in txt and "lookAt" in txt
+    return txt
+
+
+def test_legacy_schema_upgrade_equals_current_schema(host, tmp_path):
+    """xml.cpp:350-392 (camelCase -> underscore_case, lookAt) plus the FBD15 translation (sigma_s/sigma_a, boundary without
+    BSDF, foreign integrator properties): the 0.6-spelt scene loads to the same numbers as the 2.0-spelt one."""
+    path = _write_scene(str(tmp_path), extra='<integer name="vrlTargetNum" value="300"/>')
+    txt = open(path).read()
+    new = os.path.join(str(tmp_path), "new.xml")
+    open(new, "w").write(txt.replace('<medium id="fog" type="nonlinear">', '<medium id="fog" type="homogeneous">')
+                         .replace('<integer name="vrlTargetNum" value="300"/>', ""))
+    old = os.path.join(str(tmp_path), "old.xml")
+    open(old, "w").write(_legacy(txt))
+    rc_n, a, err_n = _info(host, new)
+    rc_o, b, err_o = _info(host, old)
+    assert rc_n == 0 and rc_o == 0, (err_n, err_o)
+    for w in ("in-memory version upgrade (v0.6.0", "vrl_target_num", "sigma_t / albedo = 0.2 / 0.9, 0.22 / 0.9, 0.24 / 0.9", "index-matched boundary"):
+        assert w in err_o, w
+    assert "upgrade" not in err_n
+    assert "target_vrls = 300" in err_o and "samples_per_query = 1" in err_o        # the renamed properties reached the plugin
+    for k in ("triangles", "null_triangles", "emitter_triangles", "interior_triangles", "bbox", "emitters", "integrator"):
+        assert a[k] == b[k], k
+    assert a["sensor"] == b["sensor"]
+    ma, mb = a["media"][0], b["media"][0]
+    assert np.allclose(ma["sigma_t"], mb["sigma_t"], rtol=1e-7) and np.allclose(ma["albedo"], mb["albedo"], rtol=1e-7)
+    assert {k: v for k, v in ma.items() if k not in ("sigma_t", "albedo")} == {k: v for k, v in mb.items() if k not in ("sigma_t", "albedo")}
+
+
+FBD15 = "/root/reference/data/FBD15ALVRL_scenes"
+
+
+@pytest.mark.skipif(not os.path.isdir(FBD15), reason="reference fixtures not mounted")
+def test_fbd15_benchmark_scenes_load(host):
+    """BASELINE config 4 names data/FBD15ALVRL_scenes: box.xml (Mitsuba 0.6 schema) loads after the upgrade + translation."""
+    rc, info, err = _info(host, os.path.join(FBD15, "box", "box.xml"))
+    assert rc == 0, err
+    assert info["triangles"] == 7 * 2 + (2 * 32 - 2) * 64 + 12 and info["emitter_triangles"] == 2 and info["null_triangles"] == 2
+    assert np.allclose(info["bbox"], [-10, -10, -10, 10, 10, 10], atol=1e-5) and info["emitters"] == [[20.0, 20.0, 20.0]]
+    m = info["media"][0]
+    assert m["id"] == "pm" and m["kind"] == abi.MEDIUM_HOMOGENEOUS and m["scale"] == 1.0
+    assert np.allclose(m["sigma_t"], [0.11] * 3, rtol=1e-6) and np.allclose(m["albedo"], [0.1 / 0.11] * 3, rtol=1e-6)
+    s = info["sensor"]
+    assert (s["width"], s["height"], s["spp"], s["medium"]) == (256, 256, 1, -1)
+    cam = scenes.make_camera(256, 256, (0, 0, -40), (0, 0, -39), fov=36, fov_axis="x", near_clip=0.1, far_clip=100)
+    assert np.allclose(s["sample_to_camera"], list(cam.sample_to_camera), rtol=2e-6, atol=1e-7)
+    assert np.allclose(s["to_world"], list(cam.to_world), rtol=2e-6, atol=1e-7)
+    assert "max_passes" in err and "conductor" in err
+    rc, info, err = _info(host, os.path.join(FBD15, "glass", "glass.xml"))
+    assert rc == 0, err
+    assert [m["id"] for m in info["media"]] == ["grapefruitJuiceIsotropic", "absorbingGlass"]
+    assert np.allclose(info["media"][0]["sigma_t"], [0.86, 1.27, 4.96], rtol=1e-6) and "envmap" in err
 
 
 @pytest.mark.skipif(not os.path.isdir(REF_SCENES), reason="reference fixtures not mounted")
@@ -200,6 +269,26 @@ def test_render_xml_end_to_end(host, tmp_path):
     pfm = os.path.join(str(tmp_path), "film.pfm")
     r3 = subprocess.run([host, "render-xml", path, pfm, "-Dspp=1", "target_vrls=200"], capture_output=True, text=True)
     assert r3.returncode == 0 and open(pfm, "rb").read(2) == b"PF"
+
+
+@pytest.mark.gpu
+def test_render_xml_legacy_schema_renders_the_same_film(host, tmp_path):
+    """The 0.6-spelt scene renders the film of the 2.0-spelt one (the translation is exact up to one float rounding of the
+    medium coefficients, so: same VRL count, film within 1e-5 relative)."""
+    path = _write_scene(str(tmp_path))
+    txt = open(path).read()
+    new, old = os.path.join(str(tmp_path), "new.xml"), os.path.join(str(tmp_path), "old.xml")
+    open(new, "w").write(txt.replace('<medium id="fog" type="nonlinear">', '<medium id="fog" type="homogeneous">'))
+    open(old, "w").write(_legacy(txt))
+    films = []
+    for p in (new, old):
+        out = p + ".f32"
+        r = subprocess.run([host, "render-xml", p, out, "-Dspp=1", "use_direct_illum=false"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        films.append(np.fromfile(out, np.float32).reshape(48, 64, 5))
+    a, b = films
+    assert a[..., 1].mean() > 0
+    assert np.allclose(a, b, rtol=1e-5, atol=1e-6 * float(a[..., :3].max()))
 
 
 @pytest.mark.gpu
