@@ -164,7 +164,9 @@ typedef struct vrlb_segment {
     uint64_t rng_state;                   /* PCG32 state at the first draw of this part's query */
     uint32_t sample;                      /* sample index within the pixel; with use_nl_atomic_query the high
                                            * 16 bits hold n_parts of the NLRay and its parts are consecutive */
-    uint32_t part;                        /* part index within the NLRay                       */
+    uint32_t part;                        /* low 16 bits: part index within the NLRay.  Curved paths queried part by
+                                           * part: high 16 bits = n_parts, the parts are consecutive records (the direct
+                                           * in-scattering term walks them in order, vrl.cpp:553-608) */
 } vrlb_segment;
 
 /* ---- timings of the last render, CUDA events on the library's stream --- */
@@ -240,7 +242,9 @@ int  vrlb_vrls_dice(vrlb_context *ctx, uint32_t avg_number_dice, uint64_t *n_vrl
  * throughput * Tr * PhotonMap::estimateRadianceVolume (photonmap.h:216-271) * scale.  Photons are what the light tracer
  * deposits at a particle's first medium scattering (vrl.cpp:278-281, 785: position, propagation direction, power after the
  * albedo).  pos / dir / power are n x 3 floats each; `scale` = 1 / directVolumePathCount (vrl.cpp:431); `lookup_radius` =
- * volume_lookup_radius_relative * scene radius (vrl.cpp:451).  Curved (nonlinear-medium) camera paths skip the term. */
+ * volume_lookup_radius_relative * scene radius (vrl.cpp:451).  On a curved (nonlinear-medium) camera path the gather
+ * points run over all its parts with the step phase carried from part to part (vrl.cpp:553-577), the transmittance taken
+ * over the straight distance between consecutive points and the phase function against the first part's direction. */
 typedef struct vrlb_photonset_desc {
     const float *pos, *dir, *power;
     uint64_t     n;

@@ -33,60 +33,75 @@ __global__ void photon_gather_kernel(PhotonGatherParams p) {
     const float maxt = r0.w;
     const uint32_t pixel = __float_as_uint(r1.w);
     const int medium = __float_as_int(r2.w);
-    const uint32_t part = (uint32_t) (r3.y >> 32);
+    const uint32_t part = (uint32_t) (r3.y >> 32), sample = (uint32_t) r3.y;
     float out[3] = { 0.f, 0.f, 0.f };
     const DMedium &m = p.scene.media[medium];
-    // the walk below is the single-part one (linear camera rays); curved paths carry their step phase across parts
-    // (vrl.cpp:553-577) and are left to the VRL term
-    if (part == 0 && p.n_photons > 0 && !(m.kind == VRLB_MEDIUM_NONLINEAR && p.nl_camera)) {
+    // A curved camera path (graded-IOR medium) is n_parts consecutive records (segments.cu; n_parts in the high half of
+    // `part`, or of `sample` under use_nl_atomic_query): the thread of its first record walks all of them in order, with
+    // the step phase carried from part to part (leftOver, vrl.cpp:553-577), the transmittance taken over the straight
+    // distance between consecutive gather points and the phase function against the first part's direction
+    // (mediumRay.d, vrl.cpp:530, 604-606).  A straight segment is the one-part case of the same walk.
+    if ((part & 0xffffu) == 0 && p.n_photons > 0) {
+        uint32_t n_parts = max(max(part >> 16, sample >> 16), 1u);
+        if (i + n_parts > p.n_segs) n_parts = (uint32_t) (p.n_segs - i);
         Pcg32 rng; rng.state = (r3.x - PCG32_INC) * PCG32_MULT_INV;      // one draw back: the radius jitter, vrl.cpp:527
         const float u = rng.next_f32();
         const float radius = xmul(p.lookup_radius, xadd(xmul(1.25f, u), xsub(0.75f, xmul(0.75f, u))));   // enoki::lerp(a, b, t) = b t + (a - a t)
         const float r2q = xmul(radius, radius);
-        float step = radius, left = 0.f, t = 0.f;
+        float step = radius, left = 0.f;
         V3 last = o;
-        float tr[3] = { r2.x, r2.y, r2.z };                               // throughput at the segment's start
+        float tr[3] = { r2.x, r2.y, r2.z };                               // throughput at the path's start
         float acc[3] = { 0.f, 0.f, 0.f };
-        for (int guard = 0; guard < 10000000 && t <= xsub(maxt, xsub(step, left)); ++guard) {
-            t = xadd(t, xsub(step, left));
-            left = 0.f;
-            const V3 gp(xadd(o.x, xmul(d.x, t)), xadd(o.y, xmul(d.y, t)), xadd(o.z, xmul(d.z, t)));     // gatherRay(gather_t), unfused like the oracle
-            step = xmul(radius, 2.0f);
-            const V3 dl(xsub(gp.x, last.x), xsub(gp.y, last.y), xsub(gp.z, last.z));
-            const float len = __fsqrt_rn(xdot(dl, dl));
-            const float T = m.max_density != 0.f ? expf(xmul(m.max_density, -len)) : 1.0f;   // homoEvalTransmittance
-            tr[0] = xmul(tr[0], T); tr[1] = xmul(tr[1], T); tr[2] = xmul(tr[2], T);
-            // estimateRadianceVolume(gatherPoint, mediumRay.d, medium, sampler, radius, M)
-            float est[3] = { 0.f, 0.f, 0.f };
-            int lo[3], hi[3];
-            const float g3[3] = { gp.x, gp.y, gp.z };
-            bool any = true;
-            for (int k = 0; k < 3; ++k) {
-                lo[k] = (int) floorf((g3[k] - radius - p.grid_lo[k]) * p.inv_cell);
-                hi[k] = (int) floorf((g3[k] + radius - p.grid_lo[k]) * p.inv_cell);
-                lo[k] = max(lo[k], 0); hi[k] = min(hi[k], p.grid_res[k] - 1);
-                any = any && lo[k] <= hi[k];
+        for (uint32_t k = 0; k < n_parts; ++k) {
+            V3 po = o, pd = d; float pmaxt = maxt;
+            if (k > 0) {
+                const float4 *sk = reinterpret_cast<const float4 *>(p.segs + i + k);
+                const float4 k0 = __ldg(sk), k1 = __ldg(sk + 1);
+                po = V3(k0.x, k0.y, k0.z); pd = V3(k1.x, k1.y, k1.z); pmaxt = k0.w;
             }
-            if (any)
-                for (int cz = lo[2]; cz <= hi[2]; ++cz) for (int cy = lo[1]; cy <= hi[1]; ++cy) for (int cx = lo[0]; cx <= hi[0]; ++cx) {
-                    const uint32_t c = ((uint32_t) cz * (uint32_t) p.grid_res[1] + (uint32_t) cy) * (uint32_t) p.grid_res[0] + (uint32_t) cx;
-                    for (uint32_t k = __ldg(p.cell_start + c); k < __ldg(p.cell_start + c + 1); ++k) {
-                        const float4 *pp = reinterpret_cast<const float4 *>(p.photons + k);
-                        const float4 a = __ldg(pp), b = __ldg(pp + 1), w = __ldg(pp + 2);
-                        const V3 dp(xsub(gp.x, a.x), xsub(gp.y, a.y), xsub(gp.z, a.z));
-                        const float l2 = xdot(dp, dp);
-                        if (xsub(r2q, l2) < 0.f) continue;                                     // photonmap.h:226-229
-                        const float pf = phase_iso_or_hg(m, V3(-b.x, -b.y, -b.z), d);       // mi1.wi = -photon.direction, wo = ray.d
-                        const float q1 = xsub(1.0f, __fdiv_rn(l2, r2q));
-                        // power * photonPF * sqr(1 - l2 / r2) / r2 * INV_PI * 3, left to right (photonmap.h:245)
-                        const float wgt = xmul(q1, q1);
-                        const float pw[3] = { w.x, w.y, w.z };
-                        for (int ch = 0; ch < 3; ++ch)
-                            est[ch] = xadd(est[ch], xmul(xmul(__fdiv_rn(xmul(xmul(pw[ch], pf), wgt), r2q), 0.31830988618379067154f), 3.0f));
-                    }
+            float t = 0.f;
+            for (int guard = 0; guard < 10000000 && t <= xsub(pmaxt, xsub(step, left)); ++guard) {
+                t = xadd(t, xsub(step, left));
+                left = 0.f;
+                const V3 gp(xadd(po.x, xmul(pd.x, t)), xadd(po.y, xmul(pd.y, t)), xadd(po.z, xmul(pd.z, t)));     // gatherRay(gather_t), unfused like the oracle
+                step = xmul(radius, 2.0f);
+                const V3 dl(xsub(gp.x, last.x), xsub(gp.y, last.y), xsub(gp.z, last.z));
+                const float len = __fsqrt_rn(xdot(dl, dl));
+                const float T = m.max_density != 0.f ? expf(xmul(m.max_density, -len)) : 1.0f;   // homoEvalTransmittance
+                tr[0] = xmul(tr[0], T); tr[1] = xmul(tr[1], T); tr[2] = xmul(tr[2], T);
+                // estimateRadianceVolume(gatherPoint, mediumRay.d, medium, sampler, radius, M)
+                float est[3] = { 0.f, 0.f, 0.f };
+                int lo[3], hi[3];
+                const float g3[3] = { gp.x, gp.y, gp.z };
+                bool any = true;
+                for (int c = 0; c < 3; ++c) {
+                    lo[c] = (int) floorf((g3[c] - radius - p.grid_lo[c]) * p.inv_cell);
+                    hi[c] = (int) floorf((g3[c] + radius - p.grid_lo[c]) * p.inv_cell);
+                    lo[c] = max(lo[c], 0); hi[c] = min(hi[c], p.grid_res[c] - 1);
+                    any = any && lo[c] <= hi[c];
                 }
-            for (int ch = 0; ch < 3; ++ch) acc[ch] = xadd(acc[ch], xmul(tr[ch], est[ch]));
-            last = gp;
+                if (any)
+                    for (int cz = lo[2]; cz <= hi[2]; ++cz) for (int cy = lo[1]; cy <= hi[1]; ++cy) for (int cx = lo[0]; cx <= hi[0]; ++cx) {
+                        const uint32_t c = ((uint32_t) cz * (uint32_t) p.grid_res[1] + (uint32_t) cy) * (uint32_t) p.grid_res[0] + (uint32_t) cx;
+                        for (uint32_t q = __ldg(p.cell_start + c); q < __ldg(p.cell_start + c + 1); ++q) {
+                            const float4 *pp = reinterpret_cast<const float4 *>(p.photons + q);
+                            const float4 a = __ldg(pp), b = __ldg(pp + 1), w = __ldg(pp + 2);
+                            const V3 dp(xsub(gp.x, a.x), xsub(gp.y, a.y), xsub(gp.z, a.z));
+                            const float l2 = xdot(dp, dp);
+                            if (xsub(r2q, l2) < 0.f) continue;                                     // photonmap.h:226-229
+                            const float pf = phase_iso_or_hg(m, V3(-b.x, -b.y, -b.z), d);       // mi1.wi = -photon.direction, wo = ray.d
+                            const float q1 = xsub(1.0f, __fdiv_rn(l2, r2q));
+                            // power * photonPF * sqr(1 - l2 / r2) / r2 * INV_PI * 3, left to right (photonmap.h:245)
+                            const float wgt = xmul(q1, q1);
+                            const float pw[3] = { w.x, w.y, w.z };
+                            for (int ch = 0; ch < 3; ++ch)
+                                est[ch] = xadd(est[ch], xmul(xmul(__fdiv_rn(xmul(xmul(pw[ch], pf), wgt), r2q), 0.31830988618379067154f), 3.0f));
+                        }
+                    }
+                for (int ch = 0; ch < 3; ++ch) acc[ch] = xadd(acc[ch], xmul(tr[ch], est[ch]));
+                last = gp;
+            }
+            if (k + 1 < n_parts) left = xadd(left, xsub(pmaxt, t));           // leftOver += nli.t - gather_t, vrl.cpp:570
         }
         for (int ch = 0; ch < 3; ++ch) out[ch] = xmul(acc[ch], p.scale);   // directIllum *= getScaleFactor()
     }

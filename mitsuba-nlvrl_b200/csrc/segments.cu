@@ -176,9 +176,24 @@ __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
                             rng.advance(query_draws);
                         }
                     } else {
+                        // one query per part (vrl.cpp:619-628).  The parts of one path are written as consecutive records
+                        // (count, reserve, write) with part = index | n_parts << 16, so that the direct in-scattering term
+                        // (photons.cu) can walk the path in order with the step phase it carries across parts
+                        const uint32_t n_parts = march([&](V3, V3, float, uint32_t) {});
+                        const uint32_t n_enc = min(n_parts, 0xffffu) << 16;
+                        unsigned long long slot0 = (on_film && n_parts > 0) ? atomicAdd(p.counter, (unsigned long long) n_parts) : 0ull;
                         V3 vrlThroughput = throughput;
                         march([&](V3 po, V3 pd, float pmaxt, uint32_t part) {
-                            emit(po, pd, pmaxt, vrlThroughput, part);
+                            unsigned long long slot = slot0 + part;
+                            if (on_film && slot < p.cap) {
+                                vrlb_segment g;
+                                g.o[0] = po.x; g.o[1] = po.y; g.o[2] = po.z; g.maxt = pmaxt;
+                                g.d[0] = pd.x; g.d[1] = pd.y; g.d[2] = pd.z; g.pixel = film_pixel;
+                                g.weight[0] = vrlThroughput.x; g.weight[1] = vrlThroughput.y; g.weight[2] = vrlThroughput.z;
+                                g.medium = medium; g.rng_state = rng.state; g.sample = (uint32_t) j; g.part = part | n_enc;
+                                p.segs[slot] = g;
+                            }
+                            rng.advance(query_draws);
                             vrlThroughput = vrlThroughput * homo_transmittance(m.max_density, pmaxt);
                         });
                         if (!found) { si.tri = -1; break; }

@@ -96,7 +96,7 @@ struct PhotonGatherParams {
     uint64_t            n_photons;
     float               grid_lo[3], inv_cell; int32_t grid_res[3];
     float               lookup_radius, scale;
-    int32_t             nl_camera;    // use_non_linear_camera: segments of nonlinear media are curved paths (skipped here)
+    int32_t             nl_camera;    // use_non_linear_camera (curved paths arrive as groups of consecutive parts)
     float              *film_rgb, *seg_out;
 };
 cudaError_t launch_photon_gather(const PhotonGatherParams &p, cudaStream_t stream);

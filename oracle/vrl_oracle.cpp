@@ -920,38 +920,49 @@ float vrlo_grid_transmittance(const vrlo_scene *s, int medium, const float o[3],
  * only changes the visiting order -- and the map's scale factor (vrl.cpp:610). */
 void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc *set, const vrlb_segment *segs, uint64_t n_segs,
                                  const vrlb_options *opt, float *out_rgb) {
+    (void) opt;
     for (uint64_t i = 0; i < n_segs; ++i) {
         const vrlb_segment &sg = segs[i];
         float *out = out_rgb + i * 3;
         out[0] = out[1] = out[2] = 0.f;
         const vrlb_medium &m = s->media[(size_t) sg.medium];
-        if (sg.part != 0 || set->n == 0 || (m.kind == VRLB_MEDIUM_NONLINEAR && opt->use_non_linear_camera)) continue;
+        if ((sg.part & 0xffffu) != 0 || set->n == 0) continue;
+        /* a curved path = n_parts consecutive records (n_parts in the high half of `part`, or of `sample` for the atomic
+         * query); the walk below is vrl.cpp:553-608 with the records standing for the NLRay's parts */
+        uint64_t n_parts = std::max<uint32_t>(std::max(sg.part >> 16, sg.sample >> 16), 1u);
+        n_parts = std::min(n_parts, n_segs - i);
         Pcg32 rng; rng.state = sg.rng_state; rng.inc = (PCG32_DEFAULT_STREAM << 1) | 1u;
         rng.advance(-1);
         const float radius = set->lookup_radius * lerp(0.75f, 1.25f, rng.next_f32());
-        float stepSize = radius, leftOver = 0.0f, gather_t = 0.f;
-        const V3 o(sg.o), d(sg.d);
-        V3 last = o, tr(sg.weight), direct(0.f);
+        float stepSize = radius, leftOver = 0.0f;
+        const V3 d0(sg.d);                                   /* mediumRay.d: the direction the path starts with */
+        V3 last(sg.o), tr(sg.weight), direct(0.f);
         const float md = max_density(m);
-        while (gather_t <= (sg.maxt - (stepSize - leftOver))) {
-            gather_t += (stepSize - leftOver);
-            leftOver = 0.0f;
-            const V3 gp = o + d * gather_t;
-            stepSize = radius * 2;
-            const float val = std::exp(md * -norm(gp - last));
-            tr = tr * (md != 0.f ? val : 1.0f);
-            V3 result(0.f);
-            const float radiusSqr = radius * radius;
-            for (uint64_t k = 0; k < set->n; ++k) {
-                const V3 pp(set->pos + k * 3), pd(set->dir + k * 3), pw(set->power + k * 3);
-                const float lengthSqr = squared_norm(gp - pp);
-                if ((radiusSqr - lengthSqr) < 0) continue;
-                const float photonPF = phase_eval(m, -pd, d);
-                const float q1 = 1.0f - lengthSqr / radiusSqr;
-                result = result + pw * photonPF * (q1 * q1) / radiusSqr * 0.31830988618379067154f * 3.0f;
+        for (uint64_t k = 0; k < n_parts; ++k) {
+            const V3 o(segs[i + k].o), d(segs[i + k].d);
+            const float maxt = segs[i + k].maxt;
+            float gather_t = 0.f;
+            while (gather_t <= (maxt - (stepSize - leftOver))) {
+                gather_t += (stepSize - leftOver);
+                leftOver = 0.0f;
+                const V3 gp = o + d * gather_t;
+                stepSize = radius * 2;
+                const float val = std::exp(md * -norm(gp - last));
+                tr = tr * (md != 0.f ? val : 1.0f);
+                V3 result(0.f);
+                const float radiusSqr = radius * radius;
+                for (uint64_t q = 0; q < set->n; ++q) {
+                    const V3 pp(set->pos + q * 3), pd(set->dir + q * 3), pw(set->power + q * 3);
+                    const float lengthSqr = squared_norm(gp - pp);
+                    if ((radiusSqr - lengthSqr) < 0) continue;
+                    const float photonPF = phase_eval(m, -pd, d0);
+                    const float q1 = 1.0f - lengthSqr / radiusSqr;
+                    result = result + pw * photonPF * (q1 * q1) / radiusSqr * 0.31830988618379067154f * 3.0f;
+                }
+                direct = direct + tr * result;
+                last = gp;
             }
-            direct = direct + tr * result;
-            last = gp;
+            if (k + 1 < n_parts) leftOver += maxt - gather_t;    /* vrl.cpp:570 */
         }
         direct = direct * set->scale;
         out[0] = direct.x; out[1] = direct.y; out[2] = direct.z;
@@ -1362,6 +1373,20 @@ uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const 
                 render_pixel(*s, *cam, *opt, bid, i, bx0, by0, bw, bh, on_query, put);
             }
         }
+    /* curved camera paths queried part by part: the records of one path are consecutive; each gets the path's part count
+     * in the high half of `part` (include/vrl_b200.h, vrlb_segment) -- the direct in-scattering term walks the group */
+    if (opt->use_non_linear_camera && !opt->use_nl_atomic_query) {
+        const uint64_t m = std::min(n, cap);
+        for (uint64_t a = 0; a < m;) {
+            uint64_t b = a + 1;
+            const vrlb_medium &med = s->media[(size_t) segs[a].medium];
+            if (!(med.kind == VRLB_MEDIUM_NONLINEAR && nl_step(med) > 0.f)) { a = b; continue; }
+            while (b < m && segs[b].part == segs[b - 1].part + 1 && segs[b].pixel == segs[a].pixel && segs[b].sample == segs[a].sample) ++b;
+            const uint32_t enc = (uint32_t) std::min<uint64_t>(b - a, 0xffffu) << 16;
+            for (uint64_t k = a; k < b; ++k) segs[k].part |= enc;
+            a = b;
+        }
+    }
     return n;
 }
 

@@ -296,3 +296,42 @@ def test_photon_direct_term_matches_oracle(ctx, phase):
     np.add.at(want, segs["pixel"], ref)
     assert rel_err(with_direct, want).max() <= REL_TOL
     assert with_direct.sum() > 1.05 * vrl_only.sum()
+
+
+@pytest.mark.parametrize("atomic", [0, 1])
+def test_photon_direct_term_on_curved_paths_matches_oracle(ctx, atomic):
+    """Direct in-scattering term along curved camera paths (vrl.cpp:553-608): the parts of a path are consecutive records
+    carrying the part count, the thread of the first record walks them with the step phase carried across parts; against
+    the oracle's walk over the same records, per path, then on the film."""
+    sc = scenes.nl_fog_scene(occluders=True, res_y=160, top_ior=0.8)
+    cam = scenes.box_fog_camera(32, 18)
+    opt = scenes.default_options(visibility=1, use_nl_atomic_query=atomic)
+    soa = scenes.synthetic_vrls(300, seed=12)
+    vd = scenes.vrlset_desc(soa)
+    pos, pdir, power = scenes.synthetic_photons(20000, seed=9)
+    pd = scenes.photonset_desc(pos, pdir, power, scale=1.0 / 19999, lookup_radius=0.7)
+    osc = oracle.OracleScene(sc)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(vd)
+    ctx.build_segments(cam, opt)
+    segs = ctx.download_segments()
+    idx, n_parts = segs["part"] & 0xffff, np.maximum(segs["part"] >> 16, segs["sample"] >> 16)
+    first = np.flatnonzero(idx == 0)
+    assert n_parts.min() >= 1 and n_parts[first].max() >= 3 and n_parts[first].sum() == len(segs)
+    for i in first[:: max(1, len(first) // 64)]:                      # the group of a first record follows it, in order
+        k = int(n_parts[i])
+        assert np.array_equal(idx[i:i + k], np.arange(k)) and np.all(segs["pixel"][i:i + k] == segs["pixel"][i])
+    ctx.upload_photons(pd)
+    got = ctx.photon_gather_segments(opt).astype(np.float64)
+    ref = osc.photon_gather(pd, segs, opt).astype(np.float64)
+    assert np.all(got[idx != 0] == 0) and (ref[first] > 0).mean() > 0.5
+    assert rel_err(got, ref).max() <= 2e-5
+    ctx.clear_film(); ctx.gather(opt)
+    with_direct = ctx.film_rgb(cam.width, cam.height).reshape(-1, 3).astype(np.float64)
+    ctx.clear_photons()
+    ctx.clear_film(); ctx.gather(opt)
+    vrl_only = ctx.film_rgb(cam.width, cam.height).reshape(-1, 3).astype(np.float64)
+    want = vrl_only.copy()
+    np.add.at(want, segs["pixel"], ref)
+    assert rel_err(with_direct, want).max() <= REL_TOL
+    assert with_direct.sum() > 1.05 * vrl_only.sum()

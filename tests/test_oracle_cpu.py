@@ -356,3 +356,59 @@ def test_photon_direct_term_single_photon_closed_form():
     got3 = osc.photon_gather(pd3, seg, opt)[0]
     want3 = np.array([0.5, 0.25, 1.0]) * math.exp(-0.6 * 3 * r) * power[0] / (4 * math.pi) * 3 / (math.pi * r * r)
     assert np.allclose(got3, want3, rtol=1e-5)
+
+
+def test_photon_direct_term_carries_step_phase_across_parts():
+    """Curved camera paths (vrl.cpp:553-608): a path is n consecutive part records, n in the high half of `part`.  Cutting a
+    straight segment into collinear parts must not move the gather points (the step phase `leftOver` is carried), and on
+    a bent path the transmittance runs over the straight distance between consecutive gather points."""
+    L = oracle.lib()
+    sc = scenes.Scene()
+    sc.add_medium(scenes.make_medium(sigma_t=(0.3, 0.3, 0.3), albedo=(0.8,) * 3, scale=2.0))
+    osc = oracle.OracleScene(sc)
+    st, inc = _pcg(99)
+    bits = L.vrlo_pcg32_next_u32(C.byref(st), inc.value)
+    u = np.array([(bits >> 9) | 0x3f800000], np.uint32).view(np.float32)[0] - np.float32(1.0)
+    R = 0.4
+    r = float(np.float32(R) * (np.float32(1.25) * u + (np.float32(0.75) - np.float32(0.75) * u)))
+    pos, pdir, power = scenes.synthetic_photons(4000, seed=4, box=3.0)
+    pd = scenes.photonset_desc(pos, pdir, power, scale=1.0 / 3999, lookup_radius=R)
+    opt = scenes.default_options()
+    whole = np.zeros(1, abi.SEGMENT_DTYPE)
+    whole["o"][0], whole["d"][0], whole["maxt"][0] = (-2.5, 0.2, -0.3), (1, 0, 0), 5.0
+    whole["weight"][0] = (1.0, 0.5, 0.25)
+    whole["rng_state"][0] = st.value
+    want = osc.photon_gather(pd, whole, opt)[0]
+    assert want.min() > 0
+    cuts = [0.0, 0.3 * r, 1.7 * r, 1.7 * r + 2.0, 5.0]              # a part shorter than r, one without any gather point
+    parts = np.zeros(len(cuts) - 1, abi.SEGMENT_DTYPE)
+    for k in range(len(parts)):
+        parts["o"][k] = (-2.5 + cuts[k], 0.2, -0.3)
+        parts["d"][k], parts["maxt"][k] = (1, 0, 0), cuts[k + 1] - cuts[k]
+        parts["part"][k] = k | (len(parts) << 16)
+    parts["weight"][:] = whole["weight"][0]
+    parts["weight"][1:] *= 0.123                                      # only the first part's throughput is read
+    parts["rng_state"][:] = st.value
+    got = osc.photon_gather(pd, parts, opt)
+    assert np.all(got[1:] == 0)                                       # the path's term sits on its first record
+    assert np.allclose(got[0], want, rtol=2e-5)
+    # without the group size every part would restart its own walk: the carried phase matters
+    solo = parts.copy(); solo["part"] = 0
+    assert not np.allclose(osc.photon_gather(pd, solo, opt).sum(0), want, rtol=1e-3)
+    # a right-angle bend at t = 2 r with one photon on the second gather point (1 r past the corner): it is seen through
+    # exp(-sigma (r + sqrt(2) r)), chord not arc length, and its phase function takes the FIRST part's direction
+    hg = scenes.Scene()
+    hg.add_medium(scenes.make_medium(sigma_t=(0.3, 0.3, 0.3), albedo=(0.8,) * 3, scale=2.0, phase=abi.PHASE_HG, g=0.5))
+    bend = np.zeros(2, abi.SEGMENT_DTYPE)
+    bend["o"][0], bend["d"][0], bend["maxt"][0] = (0, 0, 0), (0, 0, 1), 2 * r
+    bend["o"][1], bend["d"][1], bend["maxt"][1] = (0, 0, 2 * r), (1, 0, 0), 1.5 * r
+    bend["part"] = [0 | 2 << 16, 1 | 2 << 16]
+    bend["weight"][:] = 1.0
+    bend["rng_state"][:] = st.value
+    p1 = scenes.photonset_desc([[r, 0, 2 * r]], [[0, 0, -1]], [[1.0, 1.0, 1.0]], scale=1.0, lookup_radius=R)
+    got = oracle.OracleScene(hg).photon_gather(p1, bend, opt)[0]
+    g = 0.5
+    cos_theta = 1.0                                                   # wo = d0 = +z, wi = -photon.direction = +z
+    pf = (1 - g * g) / (4 * math.pi) / (1 + g * g + 2 * g * cos_theta) ** 1.5
+    want = math.exp(-0.6 * (r + math.sqrt(2.0) * r)) * pf * 3 / (math.pi * r * r)
+    assert np.allclose(got, want, rtol=1e-5)
