@@ -116,6 +116,14 @@ int main(int argc, char **argv) {
                 for (uint32_t f : ls.scene.tri_flags) { n_null += (f & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_NULL; n_emit += (f & VRLB_SURF_EMITTER) != 0; n_int += VRLB_SURF_GET_INTERIOR(f) >= 0; }
                 std::printf("{\"triangles\": %zu, \"null_triangles\": %zu, \"emitter_triangles\": %zu, \"interior_triangles\": %zu,\n", ls.scene.tri_flags.size(), n_null, n_emit, n_int);
                 std::printf(" \"bbox\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g],\n", lo[0], lo[1], lo[2], hi[0], hi[1], hi[2]);
+                {   // what the light tracer sees of the BSDFs: triangles that reflect particles, their mean reflectance
+                    size_t n_refl = 0; double mean[3] = { 0, 0, 0 };
+                    const auto &rf = ls.scene.tri_reflectance;
+                    for (size_t i = 0; i + 2 < rf.size(); i += 3) if (rf[i] > 0 || rf[i + 1] > 0 || rf[i + 2] > 0) { ++n_refl; for (int k = 0; k < 3; ++k) mean[k] += rf[i + (size_t) k]; }
+                    for (int k = 0; k < 3; ++k) mean[k] = n_refl ? mean[k] / (double) n_refl : 0.0;
+                    size_t n_two = 0; for (uint32_t f : ls.scene.tri_flags) n_two += (f & VRLB_SURF_TWOSIDED) != 0;
+                    std::printf(" \"reflecting_triangles\": %zu, \"twosided_triangles\": %zu, \"mean_reflectance\": [%.9g, %.9g, %.9g],\n", n_refl, n_two, mean[0], mean[1], mean[2]);
+                }
                 std::printf(" \"media\": [");
                 for (size_t i = 0; i < ls.scene.media.size(); ++i) {
                     const vrlb_medium &m = ls.scene.media[i];

@@ -174,6 +174,7 @@ void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
     sd.tri_verts = scene.tri_verts.data(); sd.tri_flags = scene.tri_flags.data(); sd.n_tris = (uint32_t) scene.tri_flags.size();
     sd.media = scene.media.data(); sd.n_media = (uint32_t) scene.media.size();
     sd.emitters = scene.emitters.data(); sd.n_emitters = (uint32_t) scene.emitters.size();
+    if (scene.tri_reflectance.size() == scene.tri_flags.size() * 3 && !scene.tri_reflectance.empty()) sd.tri_reflectance = scene.tri_reflectance.data();
     check(vrlb_scene_set(m_ctx, &sd), "vrlb_scene_set");
     if (!m_have_vrls) {
         // light tracing on the device (vrl.cpp:117-374 -> generate.cu); scale = 1 / particles traced (vrl.cpp:404,423)

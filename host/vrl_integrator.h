@@ -56,6 +56,7 @@ private:
 struct HostScene {
     std::vector<float>        tri_verts;   // 9 floats per triangle
     std::vector<uint32_t>     tri_flags;   // VRLB_SURF_*
+    std::vector<float>        tri_reflectance;   // 3 per triangle (diffuse reflectance, read by the light tracer) or empty
     std::vector<vrlb_medium>  media;
     std::vector<vrlb_emitter> emitters;
     int32_t emission_medium = -1;              // medium at the emitters / laser origin (-1 = none)

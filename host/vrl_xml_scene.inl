@@ -145,11 +145,44 @@ struct Builder {
         // surface word: BSDF kind, media on both sides, emitter
         uint32_t flags = VRLB_SURF_BSDF_SMOOTH;
         int interior = -1;
-        auto bsdf_kind = [&](const Node &b) {
-            std::string t = b.get("type");
-            if (t == "twosided" || t == "bumpmap" || t == "mask") { if (const Node *in = child_named(b, "bsdf", nullptr)) t = in->get("type"); }
-            if (t == "null") flags = (flags & ~VRLB_SURF_BSDF_MASK) | VRLB_SURF_BSDF_NULL;
-            else if (is_delta(t)) warn("bsdf type=\"" + t + "\": specular chains are not on the VRL path yet; the surface loads as an occluder");
+        float refl[3] = { 0.5f, 0.5f, 0.5f };                  // a shape without <bsdf> gets a diffuse one, reflectance 0.5 (shape.cpp, diffuse.cpp:71)
+        auto bsdf_kind = [&](const Node &b0) {
+            const Node *b = &b0;
+            std::string t = b->get("type");
+            for (int hop = 0; hop < 4 && (t == "twosided" || t == "bumpmap" || t == "mask"); ++hop) {
+                if (t == "twosided") flags |= VRLB_SURF_TWOSIDED;
+                const Node *in = child_named(*b, "bsdf", nullptr);
+                if (!in) for (const Node &c : b->children) if (c.name == "ref" && deref(c).name == "bsdf") in = &deref(c);
+                if (!in) break;
+                b = in; t = b->get("type");
+            }
+            if (t == "null") { flags = (flags & ~VRLB_SURF_BSDF_MASK) | VRLB_SURF_BSDF_NULL; return; }
+            if (is_delta(t)) {
+                warn("bsdf type=\"" + t + "\": specular chains are not on the VRL path yet; the surface loads as an occluder");
+                refl[0] = refl[1] = refl[2] = 0.f;              // light-tracing particles end there
+                return;
+            }
+            // what the light tracer needs of a smooth BSDF: the weight of SmoothDiffuse::sample = its reflectance
+            if (t != "diffuse") warn("bsdf type=\"" + t + "\": light-tracing particles are reflected with a diffuse lobe of its reflectance");
+            refl[0] = refl[1] = refl[2] = 0.5f;
+            const Node *r = prop(*b, "reflectance");
+            if (!r) r = prop(*b, "diffuse_reflectance");
+            if (!r) return;
+            const std::string v = r->get("value", "");
+            if ((r->name == "rgb" || r->name == "spectrum" || r->name == "float" || r->name == "color") && v.find(':') == std::string::npos && !v.empty()) prop_rgb(*b, r->get("name").c_str(), refl);
+            else if (r->name == "spectrum" && v.find(':') != std::string::npos) {
+                // wavelength:value table (the 0.x scenes): mean over the blue / green / red thirds of the visible range
+                double sum[3] = { 0, 0, 0 }; int cnt[3] = { 0, 0, 0 }; std::string tok;
+                for (char ch : v + ",") {
+                    if (ch != ',') { tok += ch; continue; }
+                    const size_t c = tok.find(':');
+                    if (c != std::string::npos) { const double wl = to_double(*r, tok.substr(0, c)), val = to_double(*r, tok.substr(c + 1));
+                                                  const int band = wl < 490 ? 2 : wl < 580 ? 1 : 0; sum[band] += val; ++cnt[band]; }
+                    tok.clear();
+                }
+                for (int k = 0; k < 3; ++k) refl[k] = cnt[k] ? (float) (sum[k] / cnt[k]) : 0.5f;
+                warn("reflectance given as a wavelength table: reduced to RGB by band means (no CIE integration)");
+            } else warn("bsdf \"" + b->get("id", t.c_str()) + "\": textured reflectance; light-tracing particles see the default 0.5");
         };
         for (const Node &c : s.children) {
             if (c.name == "bsdf") bsdf_kind(c);
@@ -168,7 +201,11 @@ struct Builder {
         // Emitter::medium() is the exterior medium of the shape the emitter sits on (shape.cpp: the area emitter inherits
         // it); particles start there (vrl.cpp:152)
         if ((flags & VRLB_SURF_EMITTER) && VRLB_SURF_GET_EXTERIOR(flags) >= 0) out.scene.emission_medium = VRLB_SURF_GET_EXTERIOR(flags);
-        for (size_t i = 0; i < v.size() / 9; ++i) out.scene.tri_flags.push_back(flags);
+        const bool reflects = (flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_SMOOTH && !(flags & VRLB_SURF_EMITTER);
+        for (size_t i = 0; i < v.size() / 9; ++i) {
+            out.scene.tri_flags.push_back(flags);
+            for (int k = 0; k < 3; ++k) out.scene.tri_reflectance.push_back(reflects ? refl[k] : 0.f);
+        }
         out.scene.tri_verts.insert(out.scene.tri_verts.end(), v.begin(), v.end());
         if (interior >= 0) {                                   // NonLinearMedia::build(bbox of the shape), nonlinear.cpp:62-89
             auto &bx = nl_boxes[(size_t) interior]; nl_box_set[(size_t) interior] = true;

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define VRLB_ABI_VERSION 2
+#define VRLB_ABI_VERSION 3
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -46,6 +46,7 @@ enum {
 #define VRLB_SURF_BSDF_SMOOTH    0x0u   /* diffuse & co: ends the camera path, occludes          */
 #define VRLB_SURF_BSDF_NULL      0x1u   /* index-matched boundary: passed through                */
 #define VRLB_SURF_EMITTER        0x4u   /* area emitter attached                                 */
+#define VRLB_SURF_TWOSIDED       0x8u   /* `twosided` adapter: the diffuse lobe reflects on both sides (light tracing) */
 #define VRLB_SURF_INTERIOR(m)    ((((uint32_t)(m)) + 1u) << 8)   /* medium id m on the -n side  */
 #define VRLB_SURF_EXTERIOR(m)    ((((uint32_t)(m)) + 1u) << 16)  /* medium id m on the +n side  */
 #define VRLB_SURF_EMITTER_ID(e)  (((uint32_t)(e)) << 24)
@@ -96,6 +97,11 @@ typedef struct vrlb_scene_desc {
     uint32_t           n_media;
     const vrlb_emitter*emitters;
     uint32_t           n_emitters;
+    /* ABI 3.  Diffuse reflectance of the SMOOTH surfaces, n_tris * 3 floats, or NULL.  Only the light tracer reads it
+     * (vrlb_vrls_generate / vrlb_photons_generate): a particle that meets a smooth surface is reflected with
+     * SmoothDiffuse::sample (src/bsdfs/diffuse.cpp: cosine lobe on the side of the normal the particle arrived on,
+     * weight = reflectance) and carries on, as vrl.cpp:307-358 does.  NULL = reflectance 0: particles end there. */
+    const float       *tri_reflectance;
 } vrlb_scene_desc;
 
 /* ---- sensor ------------------------------------------------------------ */

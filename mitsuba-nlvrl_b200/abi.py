@@ -4,7 +4,7 @@ import ctypes as C
 COMM_ID_BYTES = 128
 OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CANCELLED, ERR_NOMEM = 0, -1, -2, -3, -4, -5
 
-SURF_BSDF_SMOOTH, SURF_BSDF_NULL, SURF_EMITTER = 0x0, 0x1, 0x4
+SURF_BSDF_SMOOTH, SURF_BSDF_NULL, SURF_EMITTER, SURF_TWOSIDED = 0x0, 0x1, 0x4, 0x8
 MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_NONLINEAR = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_HG = 0, 1
 
@@ -30,7 +30,8 @@ class Emitter(C.Structure):
 class SceneDesc(C.Structure):
     _fields_ = [("tri_verts", C.POINTER(C.c_float)), ("tri_flags", C.POINTER(C.c_uint32)), ("n_tris", C.c_uint32),
                 ("media", C.POINTER(Medium)), ("n_media", C.c_uint32),
-                ("emitters", C.POINTER(Emitter)), ("n_emitters", C.c_uint32)]
+                ("emitters", C.POINTER(Emitter)), ("n_emitters", C.c_uint32),
+                ("tri_reflectance", C.POINTER(C.c_float))]
 
 
 class Camera(C.Structure):

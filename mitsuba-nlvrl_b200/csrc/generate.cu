@@ -14,7 +14,12 @@
 // Events (vrl.cpp:180-357): Russian roulette after rr_depth; free-flight distance t = -log(1 - u) / sigma_maj with the
 // grey majorant (medium.cpp:36-75; tr/pdf cancels for a homogeneous extinction); real scatter: throughput *= albedo,
 // new direction from the phase function (isotropic.cpp / hg.cpp); null-BSDF surfaces are crossed and switch the
-// medium; other surfaces END the particle (surface BSDF sampling is outside the hot path).
+// medium; a smooth surface reflects the particle diffusely (SmoothDiffuse::sample: cosine lobe, weight = the
+// triangle's reflectance from vrlb_scene_desc::tri_reflectance; without that table particles end there); an emitter
+// surface ends it before the VRL in flight is stored (vrl.cpp:309-310).  A VRL carries the flux and depth it was
+// created with, so a roulette survival boosts the VRLs created afterwards, not the one in flight -- and a roulette
+// death drops the VRL in flight (vrl.cpp:181-185 runs before :283/:313): the reference's set is reproduced, energy loss
+// included.
 // Flux: laser = power; area emitter = Le * pi * area * pi (the second pi is vrl.cpp:151-152).
 //
 // Output is deterministic for a given (seed, particle count): pass 1 counts the VRLs of every particle, an exclusive
@@ -108,34 +113,41 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
     const uint64_t slot_end = WRITE ? p.offsets[pi + 1] : 0;
 
     Emit e = emit_particle(p, rng);
+    (void) rng.next_f32();                                                 // channel draw, once per particle (vrl.cpp:172-176)
     V3 pos = e.o, dir = e.d, throughput(1.f);
-    int medium = e.medium, depth = 0;
-    V3 vrl_o = pos, vrl_d0 = dir; bool vrl_open = medium >= 0;
-    auto push = [&](V3 end, int med, V3 flux) {                             // VRL::setEndPoint + VRLMap::push_back
+    // depth counts real events (medium scatterings + reflections) = the reference's `depth` - 1 (it starts at 1,
+    // vrl.cpp:171); medium_depth is its mediumDepth (vrl.cpp:164)
+    int medium = e.medium, depth = 0, medium_depth = 0;
+    // a VRL keeps the flux and depth it was created with (VRL(ray.o, medium, throughput * flux, depth ...), vrl.cpp:178,
+    // 283, 354): the roulette's 1/q of a later iteration does not reach the VRL already in flight
+    V3 vrl_o = pos, vrl_d0 = dir, vrl_flux = throughput * e.flux; int vrl_depth = 0; bool vrl_open = medium >= 0;
+    auto open_vrl = [&](V3 at, V3 d0) { vrl_o = at; vrl_d0 = d0; vrl_flux = throughput * e.flux; vrl_depth = depth; vrl_open = medium >= 0; };
+    auto push = [&](V3 end) {                                               // VRL::setEndPoint + VRLMap::push_back
         V3 dd = end - vrl_o; float len = norm(dd);
-        if (!(len > 0.f) || med < 0 || (flux.x == 0.f && flux.y == 0.f && flux.z == 0.f)) return;
+        if (!(len > 0.f) || medium < 0 || (vrl_flux.x == 0.f && vrl_flux.y == 0.f && vrl_flux.z == 0.f)) return;
         if (WRITE && slot < slot_end) {
             DVrl v; V3 dn = dd / len;
             v.ox = vrl_o.x; v.oy = vrl_o.y; v.oz = vrl_o.z; v.length = len;
-            v.dx = dn.x; v.dy = dn.y; v.dz = dn.z; v.medium = (uint32_t) med;
-            v.fr = flux.x; v.fg = flux.y; v.fb = flux.z; v.pad = __int_as_float(depth);
+            v.dx = dn.x; v.dy = dn.y; v.dz = dn.z; v.medium = (uint32_t) medium;
+            v.fr = vrl_flux.x; v.fg = vrl_flux.y; v.fb = vrl_flux.z; v.pad = __int_as_float(vrl_depth);
             p.out[slot++] = v;
         }
         ++count;
     };
 
-    for (int bounce = 0; bounce < p.max_depth && count < p.max_per_particle; ++bounce) {
-        if (depth > p.rr_depth) {                                          // Russian roulette, vrl.cpp:181-185
-            float q = fminf(fmaxf(throughput.x, fmaxf(throughput.y, throughput.z)), 0.95f);
-            if (rng.next_f32() >= q) break;
-            throughput = throughput * (1.f / q);
+    for (int bounce = 0; bounce < 100000 && count < p.max_per_particle; ++bounce) {
+        if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+        {                                                                  // Russian roulette, vrl.cpp:181-185: the draw is
+            float q = fminf(fmaxf(throughput.x, fmaxf(throughput.y, throughput.z)), 0.95f);   // taken every iteration
+            const float u = rng.next_f32();
+            if (depth + 1 > p.rr_depth) { if (!(u < q)) break; throughput = throughput * (1.f / q); }
         }
+        if (depth + 1 >= p.max_depth) break;                               // vrl.cpp:187-189
         // distance to the next medium event
         float t_event = VRLB_INF;
         const DMedium *m = medium >= 0 ? &s.media[medium] : nullptr;
         if (m) {
-            (void) rng.next_f32();                                         // channel draw (grey majorant)
-            float u = rng.next_f32();
+            float u = rng.next_f32();                                      // sample_interaction(ray, next_1d, channel), vrl.cpp:206
             t_event = m->max_density > 0.f ? -logf(1.f - u) / m->max_density : VRLB_INF;
         }
         const bool curved = m && m->kind == VRLB_MEDIUM_NONLINEAR && m->nl_step > 0.f && p.use_non_linear;
@@ -158,8 +170,8 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
                 V3 nd = eikonal_bend(*m, pos, dir, ds);
                 // cut a VRL when the direction has changed and the piece is long enough (vrl.cpp:215-223)
                 if (vrl_open && dot(nd, vrl_d0) < 1.f - 1e-7f && norm(pos - vrl_o) > p.min_vrl_length) {
-                    push(pos, medium, throughput * e.flux);
-                    vrl_o = pos; vrl_d0 = nd;
+                    push(pos);
+                    open_vrl(pos, nd);
                 }
                 dir = nd;
             }
@@ -167,30 +179,63 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
         }
         if (surface) {
             const DTri &tr = s.tris[si.tri];
-            if (vrl_open) push(pos, medium, throughput * e.flux);          // vrl.cpp:313-314
-            if ((tr.flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL) break;   // opaque surface: particle ends
-            (void) rng.next_f32(); (void) rng.next_f32(); (void) rng.next_f32();  // bsdf->sample draws, vrl.cpp:318
-            if (VRLB_SURF_GET_EXTERIOR(tr.flags) >= 0 || VRLB_SURF_GET_INTERIOR(tr.flags) >= 0) medium = target_medium(tr, dir);
-            pos = pos + dir * ((1.f + hmax_abs(pos)) * kRayEpsilon);        // spawn_ray offset
-            vrl_o = pos; vrl_d0 = dir; vrl_open = medium >= 0;
+            if (tr.flags & VRLB_SURF_EMITTER) break;                        // si.shape->is_emitter(): vrl.cpp:309-310, before the VRL is stored
+            if (vrl_open) push(pos);                                        // vrl.cpp:312-313
+            // handleSurfaceInteraction (vrl.cpp:315) would store a surface photon here: the surface maps are not built
+            const float u1 = rng.next_f32(), u2 = rng.next_f32(), u3 = rng.next_f32();     // bsdf->sample(ctx, si, next_1d, next_2d), vrl.cpp:320
+            (void) u1;
+            if ((tr.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_NULL) {
+                if (VRLB_SURF_GET_EXTERIOR(tr.flags) >= 0 || VRLB_SURF_GET_INTERIOR(tr.flags) >= 0) medium = target_medium(tr, dir);
+                pos = pos + dir * ((1.f + hmax_abs(pos)) * kRayEpsilon);    // spawn_ray offset
+                open_vrl(pos, dir);
+                continue;
+            }
+            // SmoothDiffuse::sample (src/bsdfs/diffuse.cpp): nothing behind a one-sided surface, else a cosine-distributed
+            // direction about the normal (warp::square_to_cosine_hemisphere) with weight = reflectance
+            V3 n = tri_normal(tr);
+            float cos_i = -dot(dir, n);
+            if (cos_i < 0.f && (tr.flags & VRLB_SURF_TWOSIDED)) { n = -n; cos_i = -cos_i; }
+            if (!(cos_i > 0.f) || !p.tri_refl) break;
+            const float *rf = p.tri_refl + (size_t) tr.prim * 3;
+            throughput = throughput * V3(__ldg(rf), __ldg(rf + 1), __ldg(rf + 2));
+            if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+            float dx, dy;                                                   // warp::square_to_uniform_disk_concentric
+            {
+                const float x = 2.f * u2 - 1.f, y = 2.f * u3 - 1.f;
+                const bool quad = fabsf(x) < fabsf(y);
+                const float r = quad ? y : x, rp = quad ? x : y;
+                float phi = 0.25f * kPi * (r != 0.f ? rp / r : 0.f);
+                if (quad) phi = 0.5f * kPi - phi;
+                float sn, cs; sincosf(phi, &sn, &cs);
+                dx = r * cs; dy = r * sn;
+            }
+            const float dz = sqrtf(fmaxf(1.f - dx * dx - dy * dy, 0.f));
+            V3 a, b; frame(n, a, b);
+            dir = normalize(a * dx + b * dy + n * dz);
+            ++depth;                                                        // non-null BSDF, vrl.cpp:336-337
+            if (VRLB_SURF_GET_EXTERIOR(tr.flags) >= 0 || VRLB_SURF_GET_INTERIOR(tr.flags) >= 0) medium = target_medium(tr, dir);   // vrl.cpp:351-353
+            pos = pos + dir * ((1.f + hmax_abs(pos)) * kRayEpsilon);
+            open_vrl(pos, dir);                                             // vrl.cpp:354
             continue;
         }
         // real scattering event (homogeneous extinction: no null collisions), vrl.cpp:246-294
-        push(pos, medium, throughput * e.flux);
+        (void) rng.next_f32();                                             // the null-scatter decision's draw, vrl.cpp:246
+        ++depth;                                                           // vrl.cpp:254
+        if (depth + 1 >= p.max_depth) break;                               // vrl.cpp:257-258: the scattering is dropped
         throughput = throughput * V3(m->albedo[0], m->albedo[1], m->albedo[2]);
-        if (!WRITE && p.photon_out && depth == 0) {                        // mediumDepth == 0: handleMediumInteraction, vrl.cpp:278-281, 785
+        if (!WRITE && p.photon_out && medium_depth == 0) {                 // handleMediumInteraction, vrl.cpp:276-281, 785
             const V3 w = throughput * e.flux;                              // flux * throughput after the albedo
             p.photon_out[pi] = DPhoton{ pos.x, pos.y, pos.z, 0.f, dir.x, dir.y, dir.z, 0.f, w.x, w.y, w.z, 0.f };
             p.photon_flag[pi] = 1u;
         }
-        ++depth;
+        ++medium_depth;
+        push(pos);                                                         // vrl.cpp:283-288
         float u1 = rng.next_f32(), u2 = rng.next_f32();
         dir = sample_phase(*m, dir, u1, u2);
-        vrl_o = pos; vrl_d0 = dir; vrl_open = true;
-        if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+        open_vrl(pos, dir);
     }
     if (!WRITE) p.counts[pi] = count;
-    if (!WRITE && p.photon_out && depth == 0) p.photon_flag[pi] = 0u;      // never scattered in a medium
+    if (!WRITE && p.photon_out && medium_depth == 0) p.photon_flag[pi] = 0u;   // never scattered in a medium
 }
 
 cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream) {

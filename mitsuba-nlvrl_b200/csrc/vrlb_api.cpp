@@ -49,7 +49,7 @@ struct vrlb_context {
     std::atomic<int> cancel{ 0 };
 
     // scene
-    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters; DevBuf<float> grids; bool any_grid = false; DevBuf<DSolid> solids;
+    DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters; DevBuf<float> tri_refl; bool have_refl = false; DevBuf<float> grids; bool any_grid = false; DevBuf<DSolid> solids;
     DScene scene{};
     bool have_scene = false;
     std::vector<vrlb_medium> host_media;
@@ -311,6 +311,13 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     ctx->any_grid = !grid_off.empty();
     CU(ctx, cudaMemcpy(ctx->media.ptr, dm.data(), dm.size() * sizeof(DMedium), cudaMemcpyHostToDevice));
     if (sc->n_emitters) CU(ctx, cudaMemcpy(ctx->emitters.ptr, sc->emitters, (size_t) sc->n_emitters * sizeof(vrlb_emitter), cudaMemcpyHostToDevice));
+    ctx->have_refl = sc->tri_reflectance != nullptr && sc->n_tris > 0;      // read by the light tracer only (generate.cu)
+    if (ctx->have_refl) {
+        for (size_t i = 0; i < (size_t) sc->n_tris * 3; ++i)
+            if (!(sc->tri_reflectance[i] >= 0.f)) return fail(ctx, VRLB_ERR_INVALID, "tri_reflectance[%zu] is negative or NaN", i);
+        CU(ctx, ctx->tri_refl.reserve((size_t) sc->n_tris * 3));
+        CU(ctx, cudaMemcpy(ctx->tri_refl.ptr, sc->tri_reflectance, (size_t) sc->n_tris * 3 * sizeof(float), cudaMemcpyHostToDevice));
+    }
     ctx->scene.tris = ctx->tris.ptr; ctx->scene.verts = ctx->verts.ptr; ctx->scene.nodes = ctx->nodes.ptr;
     ctx->scene.wnodes = ctx->wnodes.ptr; ctx->scene.stris = ctx->stris.ptr; ctx->scene.main_root = sa.main_root;
     for (int k = 0; k < 3; ++k) { ctx->scene.main_lo[k] = sa.main_lo[k]; ctx->scene.main_hi[k] = sa.main_hi[k]; }
@@ -422,6 +429,7 @@ static int setup_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, GenP
     p.max_per_particle = 4096; p.min_vrl_length = gen->min_vrl_length;
     for (int k = 0; k < 3; ++k) { p.laser_o[k] = gen->laser_origin[k]; p.laser_d[k] = gen->laser_direction[k]; p.laser_power[k] = gen->laser_power[k]; }
     p.emit_tris = d_etris.ptr; p.emit_cdf = d_ecdf.ptr; p.n_emit_tris = (int32_t) etris.size(); p.emit_area = (float) area;
+    p.tri_refl = ctx->have_refl ? ctx->tri_refl.ptr : nullptr;
 
     return VRLB_OK;
 }

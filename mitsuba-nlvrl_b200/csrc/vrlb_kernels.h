@@ -74,6 +74,7 @@ struct GenParams {
     DVrl     *out;                // device, VRL records
     DPhoton  *photon_out;     // device or null (count pass only): one slot per particle of the wave, the volume photon of
     uint32_t *photon_flag;        //   its FIRST medium scattering (vrl.cpp:278-281) and whether it deposited one
+    const float *tri_refl;        // device or null: n_tris * 3 diffuse reflectance, ORIGINAL triangle order (DTri::prim)
 };
 cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream);
 

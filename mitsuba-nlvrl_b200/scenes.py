@@ -148,11 +148,17 @@ class Scene:
 
     def __init__(self):
         self._tris, self._flags, self.media, self.emitters, self._grids = [], [], [], [], []
+        self._refl, self._any_refl = [], False
 
-    def add_tris(self, tris, flags):
+    def add_tris(self, tris, flags, reflectance=None):
+        """`reflectance` (grey or RGB): diffuse reflectance of a smooth surface, read by the light tracer only
+        (vrlb_scene_desc::tri_reflectance); None = 0, particles end on the surface."""
         tris = np.asarray(tris, np.float32).reshape(-1, 3, 3)
         self._tris.append(tris)
         self._flags.append(np.full(len(tris), flags, np.uint32))
+        r = np.zeros(3, np.float32) if reflectance is None else np.broadcast_to(np.asarray(reflectance, np.float32), (3,))
+        self._refl.append(np.tile(r, (len(tris), 1)))
+        self._any_refl = self._any_refl or reflectance is not None
         return self
 
     def add_medium(self, medium, grid=None):
@@ -189,6 +195,9 @@ class Scene:
         d.n_tris = len(self._f)
         d.media, d.n_media = self._m, len(self.media)
         d.emitters, d.n_emitters = self._e, len(self.emitters)
+        if self._any_refl:
+            self._r = np.ascontiguousarray(np.concatenate(self._refl), np.float32)
+            d.tri_reflectance = abi.fptr(self._r)
         return d
 
 

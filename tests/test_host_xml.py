@@ -117,6 +117,11 @@ def test_synthetic_scene_loads(host, tmp_path):
     assert np.allclose(s["sample_to_camera"], list(cam.sample_to_camera), rtol=2e-6, atol=1e-7)
     assert np.allclose(s["to_world"], list(cam.to_world), rtol=2e-6, atol=1e-7)
     assert "tessellated" in err                                         # the analytic sphere is reported
+    # what the light tracer reads of the BSDFs: the obj triangle is "white" (0.8), the sphere a default diffuse (0.5), the
+    # emitter rectangle and the null cube reflect nothing
+    n_sphere = (2 * 32 - 2) * 64
+    assert info["reflecting_triangles"] == 1 + n_sphere and info["twosided_triangles"] == 0
+    assert np.allclose(info["mean_reflectance"], [(0.8 + 0.5 * n_sphere) / (1 + n_sphere)] * 3, rtol=1e-6)
     # <default> can be overridden from the command line (-Dname=value, mitsuba.cpp:137-146)
     rc, info, err = _info(host, path, "-Dres=128", "-Dspp=5")
     assert rc == 0 and info["sensor"]["width"] == 128 and info["sensor"]["spp"] == 5 and info["sensor"]["height"] == 48
@@ -134,6 +139,26 @@ def test_transform_order_and_rectangle(host, tmp_path):
     rc, info, err = _info(host, p2)
     assert rc == 0, err
     assert info["triangles"] == 2 and np.allclose(info["bbox"], [-2, 6.5, -2, 2, 6.5, 2], atol=1e-6)
+
+
+def test_bsdf_reflectance_forms(host, tmp_path):
+    """twosided adapter, rgb reflectance, wavelength table (band means), delta BSDF (no reflection), nested by reference."""
+    xml = """<scene version="2.0.0">
+    <sensor type="perspective"><float name="fov" value="40"/><film type="hdrfilm"/></sensor>
+    <medium id="m" type="homogeneous"/>
+    <bsdf type="diffuse" id="inner"><rgb name="reflectance" value="0.1, 0.2, 0.3"/></bsdf>
+    <bsdf type="twosided" id="both"><ref id="inner"/></bsdf>
+    <shape type="rectangle"><ref id="both"/></shape>
+    <shape type="rectangle"><bsdf type="diffuse"><spectrum name="reflectance" value="400:0.2, 450:0.4, 500:0.6, 550:0.6, 600:0.9, 700:0.7"/></bsdf></shape>
+    <shape type="rectangle"><bsdf type="dielectric"/></shape>
+    </scene>"""
+    p = os.path.join(str(tmp_path), "bsdfs.xml")
+    open(p, "w").write(xml)
+    rc, info, err = _info(host, p)
+    assert rc == 0, err
+    assert info["triangles"] == 6 and info["reflecting_triangles"] == 4 and info["twosided_triangles"] == 2
+    assert np.allclose(info["mean_reflectance"], [(0.1 + 0.8) / 2, (0.2 + 0.6) / 2, (0.3 + 0.3) / 2], rtol=1e-6)
+    assert "wavelength table" in err and "dielectric" in err
 
 
 def test_property_and_schema_errors(host, tmp_path):

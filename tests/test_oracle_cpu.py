@@ -292,7 +292,7 @@ def test_library_exports_every_declared_symbol():
     missing = [s for s in sorted(declared) if not hasattr(lib, s)]
     assert not missing, missing
     assert declared == set(api.EXPORTS), declared ^ set(api.EXPORTS)
-    assert lib.vrlb_abi_version() == 2
+    assert lib.vrlb_abi_version() == 3
 
 
 def test_pod_layouts_match_header(tmp_path):
