@@ -269,6 +269,34 @@ int  vrlb_photons_download(vrlb_context *ctx, float *pos, float *dir, float *pow
 /* Test/diagnostic entry: the direct term per resident camera segment (throughput included), host buffer n_segs*3. */
 int  vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *direct_out);
 
+/* ---- surface photon maps: the radiance the camera path collects at its first smooth surface (vrl.cpp:671-680) --------
+ * radiance += throughput * (causticMap.estimateCausticRadiance(si, r_c, k_c) + globalMap.estimateRadiance(si, r_g, k_g)),
+ * photonmap.h:131-211: the k nearest photons within the lookup radius (kd-tree nnSearch, kdtree.h:319-400: when more than
+ * k lie inside, the radius shrinks to the k-th nearest), each weighted with bsdf->eval(si, wo = -photon direction)
+ * (SmoothDiffuse::eval = reflectance / pi * cos_theta_o where both cosines are positive), times scale / (pi r^2); the
+ * caustic estimate adds the cone filter max(0, 1 - d / r) and a factor 3.  Photons are what the light tracer stores at
+ * every smooth surface a particle meets (handleSurfaceInteraction, vrl.cpp:315, 772-782): position, travel direction,
+ * flux * throughput before the reflection; caustic = arrived through a transmission (no such BSDF on this path yet, so
+ * the light tracer here only fills the global map).  scale = 1 / surfacePathCount (vrl.cpp:379-383). */
+enum { VRLB_PHOTONMAP_GLOBAL = 0, VRLB_PHOTONMAP_CAUSTIC = 1 };
+/* set->lookup_radius = {global,caustic}_lookup_radius_relative * scene radius (vrl.cpp:448-450); lookup_size =
+ * {global,caustic}_lookup_size (1 .. 1024).  n = 0 clears the map. */
+int  vrlb_surface_photons_upload(vrlb_context *ctx, int which, const vrlb_photonset_desc *set, int32_t lookup_size);
+uint64_t vrlb_surface_photons_count(const vrlb_context *ctx, int which);
+int  vrlb_surface_photons_download(vrlb_context *ctx, int which, float *pos, float *dir, float *power, uint64_t cap, float *scale_out);
+/* One surface query = the end of a camera path on a smooth surface; vrlb_gather adds weight * estimate to the film. */
+typedef struct vrlb_surface_query {
+    float    p[3];   uint32_t pixel;      /* si.p; y*width + x                                                   */
+    float    n[3];   uint32_t flags;      /* geometric normal (= shading frame here); VRLB_SURF_TWOSIDED or 0     */
+    float    wi[3];  float    pad0;       /* world direction towards the camera, -ray.d                           */
+    float    reflectance[3]; float pad1;  /* of the surface's diffuse BSDF                                        */
+    float    weight[3]; float pad2;       /* path throughput                                                      */
+} vrlb_surface_query;
+int  vrlb_surface_queries_upload(vrlb_context *ctx, const vrlb_surface_query *q, uint64_t n, int32_t width, int32_t height);
+int  vrlb_surface_queries_download(vrlb_context *ctx, vrlb_surface_query *q, uint64_t cap, uint64_t *n_out);
+/* Test/diagnostic entry: caustic + global estimate per resident query BEFORE the weight, host buffer n*3. */
+int  vrlb_surface_gather_queries(vrlb_context *ctx, float *radiance_out);
+
 /* ---- camera segments: replaces the medium branch of VRLIntegrator::sample up to the query
  *      (vrl.cpp:443-631) driven by SamplingIntegrator::render_block/render_sample
  *      (integrator.cpp:187-297) ----------------------------------------------------------------- */

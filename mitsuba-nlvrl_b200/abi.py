@@ -71,6 +71,15 @@ class Segment(C.Structure):
                 ("sample", C.c_uint32), ("part", C.c_uint32)]
 
 
+class SurfaceQuery(C.Structure):
+    _fields_ = [("p", C.c_float * 3), ("pixel", C.c_uint32), ("n", C.c_float * 3), ("flags", C.c_uint32),
+                ("wi", C.c_float * 3), ("pad0", C.c_float), ("reflectance", C.c_float * 3), ("pad1", C.c_float),
+                ("weight", C.c_float * 3), ("pad2", C.c_float)]
+
+
+PHOTONMAP_GLOBAL, PHOTONMAP_CAUSTIC = 0, 1
+
+
 class Timing(C.Structure):
     _fields_ = [("ms_upload", C.c_float), ("ms_segments", C.c_float), ("ms_gather", C.c_float), ("ms_film", C.c_float),
                 ("ms_download", C.c_float), ("gather_launches", C.c_uint32), ("total_launches", C.c_uint32),
@@ -85,6 +94,9 @@ SEGMENT_DTYPE = _np.dtype([("o", "<f4", 3), ("maxt", "<f4"), ("d", "<f4", 3), ("
                            ("weight", "<f4", 3), ("medium", "<i4"), ("rng_state", "<u8"),
                            ("sample", "<u4"), ("part", "<u4")])
 assert SEGMENT_DTYPE.itemsize == 64
+SURFACE_QUERY_DTYPE = _np.dtype([("p", "<f4", 3), ("pixel", "<u4"), ("n", "<f4", 3), ("flags", "<u4"), ("wi", "<f4", 3), ("pad0", "<f4"),
+                                 ("reflectance", "<f4", 3), ("pad1", "<f4"), ("weight", "<f4", 3), ("pad2", "<f4")])
+assert SURFACE_QUERY_DTYPE.itemsize == C.sizeof(SurfaceQuery) == 80
 
 
 def fptr(a):

@@ -21,6 +21,8 @@ EXPORTS = [
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
     "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice",
+    "vrlb_surface_photons_upload", "vrlb_surface_photons_count", "vrlb_surface_photons_download",
+    "vrlb_surface_queries_upload", "vrlb_surface_queries_download", "vrlb_surface_gather_queries",
     "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments", "vrlb_photons_generate", "vrlb_photons_download",
 ]
 
@@ -105,6 +107,13 @@ def load_library():
     L.vrlb_vrls_scale.argtypes = [vp]
     L.vrlb_vrls_scale.restype = C.c_float
     L.vrlb_vrls_download_depth.argtypes = [vp, C.POINTER(C.c_int32), C.c_uint64]
+    L.vrlb_surface_photons_upload.argtypes = [vp, C.c_int, C.POINTER(abi.PhotonSetDesc), C.c_int32]
+    L.vrlb_surface_photons_count.argtypes = [vp, C.c_int]
+    L.vrlb_surface_photons_count.restype = C.c_uint64
+    L.vrlb_surface_photons_download.argtypes = [vp, C.c_int, f32p, f32p, f32p, C.c_uint64, f32p]
+    L.vrlb_surface_queries_upload.argtypes = [vp, vp, C.c_uint64, C.c_int32, C.c_int32]
+    L.vrlb_surface_queries_download.argtypes = [vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
+    L.vrlb_surface_gather_queries.argtypes = [vp, f32p]
     L.vrlb_shadow_proxies.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     _lib = L
     return L
@@ -199,6 +208,42 @@ class Context:
         out = np.zeros((max(n, 1), 3), np.float32)
         self._check(self.lib.vrlb_photon_gather_segments(self.h, C.byref(opt), abi.fptr(out)))
         return out[:n]
+
+    # ---- surface photon maps (vrl.cpp:671-680) ----
+    def upload_surface_photons(self, which, photon_desc, lookup_size):
+        self._check(self.lib.vrlb_surface_photons_upload(self.h, which, C.byref(photon_desc), lookup_size))
+
+    def clear_surface_photons(self, which):
+        self._check(self.lib.vrlb_surface_photons_upload(self.h, which, C.byref(abi.PhotonSetDesc()), 0))
+
+    def surface_photons_count(self, which):
+        return int(self.lib.vrlb_surface_photons_count(self.h, which))
+
+    def download_surface_photons(self, which):
+        n = self.surface_photons_count(which)
+        pos, d, pw = (np.zeros((n, 3), np.float32) for _ in range(3))
+        scale = C.c_float()
+        self._check(self.lib.vrlb_surface_photons_download(self.h, which, abi.fptr(pos), abi.fptr(d), abi.fptr(pw), n, C.byref(scale)))
+        return pos, d, pw, scale.value
+
+    def upload_surface_queries(self, queries, width, height):
+        q = np.ascontiguousarray(queries, abi.SURFACE_QUERY_DTYPE)
+        self._check(self.lib.vrlb_surface_queries_upload(self.h, q.ctypes.data, len(q), width, height))
+
+    def download_surface_queries(self):
+        n = C.c_uint64()
+        self._check(self.lib.vrlb_surface_queries_download(self.h, None, 0, C.byref(n)))
+        q = np.zeros(n.value, abi.SURFACE_QUERY_DTYPE)
+        self._check(self.lib.vrlb_surface_queries_download(self.h, q.ctypes.data, len(q), C.byref(n)))
+        return q
+
+    def surface_gather_queries(self):
+        """caustic + global estimate per resident surface query, before the weight."""
+        n = C.c_uint64()
+        self._check(self.lib.vrlb_surface_queries_download(self.h, None, 0, C.byref(n)))
+        out = np.zeros((n.value, 3), np.float32)
+        self._check(self.lib.vrlb_surface_gather_queries(self.h, abi.fptr(out)))
+        return out
 
     def vrls_scale(self):
         return float(self.lib.vrlb_vrls_scale(self.h))

@@ -61,8 +61,13 @@ struct vrlb_context {
     uint64_t n_vrls = 0, vrl_first = 0, vrl_total = 0; float vrl_scale = 1.f;
 
     // volume photon map (photons.cu): sorted by grid cell
-    DevBuf<DPhoton> photons; DevBuf<uint32_t> photon_cells; uint64_t n_photons = 0;
-    float photon_scale = 0.f, photon_radius = 0.f, photon_lo[3] = { 0, 0, 0 }, photon_inv_cell = 0.f; int32_t photon_res[3] = { 1, 1, 1 };
+    struct PhotonMapRes {
+        DevBuf<DPhoton> photons; DevBuf<uint32_t> cells; uint64_t n = 0;
+        float scale = 0.f, radius = 0.f, lo[3] = { 0, 0, 0 }, inv_cell = 0.f; int32_t res[3] = { 1, 1, 1 }; int32_t lookup_size = 0;
+    };
+    PhotonMapRes vol;                 // volume photon map (photons.cu)
+    PhotonMapRes surf[2];             // global / caustic surface maps (surface_photons.cu), VRLB_PHOTONMAP_*
+    DevBuf<vrlb_surface_query> squeries; uint64_t n_squeries = 0;   // camera paths that end on a reflecting surface
 
     // segments
     DevBuf<vrlb_segment> segs; uint64_t n_segs = 0;
@@ -678,17 +683,19 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     return VRLB_OK;
 }
 
+static int surface_gather_impl(vrlb_context *ctx, float *out_dev);
+
 // direct term from the resident photon set (no-op without one); film path when seg_out_dev is null
 static int photon_gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_out_dev) {
-    if (ctx->n_photons == 0 && !seg_out_dev) return VRLB_OK;
+    if (ctx->vol.n == 0 && !seg_out_dev) return VRLB_OK;
     if (!seg_out_dev && ctx->n_ranks > 1 && ctx->rank != 0) return VRLB_OK;   // VRL shards: the films are summed, the direct term is rank 0's
     if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "no scene resident");
     if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no camera segments resident");
     PhotonGatherParams p{};
     p.scene = ctx->scene; p.segs = ctx->segs.ptr; p.n_segs = ctx->n_segs;
-    p.photons = ctx->photons.ptr; p.cell_start = ctx->photon_cells.ptr; p.n_photons = ctx->n_photons;
-    for (int k = 0; k < 3; ++k) { p.grid_lo[k] = ctx->photon_lo[k]; p.grid_res[k] = ctx->photon_res[k]; }
-    p.inv_cell = ctx->photon_inv_cell; p.lookup_radius = ctx->photon_radius; p.scale = ctx->photon_scale;
+    p.photons = ctx->vol.photons.ptr; p.cell_start = ctx->vol.cells.ptr; p.n_photons = ctx->vol.n;
+    for (int k = 0; k < 3; ++k) { p.grid_lo[k] = ctx->vol.lo[k]; p.grid_res[k] = ctx->vol.res[k]; }
+    p.inv_cell = ctx->vol.inv_cell; p.lookup_radius = ctx->vol.radius; p.scale = ctx->vol.scale;
     p.nl_camera = opt->use_non_linear_camera;
     p.film_rgb = seg_out_dev ? nullptr : ctx->film_rgb.ptr; p.seg_out = seg_out_dev;
     CU(ctx, launch_photon_gather(p, ctx->stream));
@@ -701,13 +708,14 @@ int vrlb_gather(vrlb_context *ctx, const vrlb_options *opt) {
     cudaSetDevice(ctx->device);
     int rc = gather_impl(ctx, opt, nullptr);
     if (rc == VRLB_OK) rc = photon_gather_impl(ctx, opt, nullptr);
+    if (rc == VRLB_OK) rc = surface_gather_impl(ctx, nullptr);
     return rc;
 }
 
-int vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set) {
-    if (!ctx || !set) return VRLB_ERR_INVALID;
-    cudaSetDevice(ctx->device);
-    if (set->n == 0) { ctx->n_photons = 0; return VRLB_OK; }
+// Photon set -> resident map: uniform grid over the photons' bounds, counting sort by cell (set order inside a cell, so
+// the sums over a cell are deterministic)
+static int bin_photons(vrlb_context *ctx, const vrlb_photonset_desc *set, vrlb_context::PhotonMapRes &m) {
+    if (set->n == 0) { m.n = 0; return VRLB_OK; }
     if (!set->pos || !set->dir || !set->power) return fail(ctx, VRLB_ERR_INVALID, "photon arrays missing");
     if (!(set->lookup_radius > 0.f)) return fail(ctx, VRLB_ERR_INVALID, "lookup_radius must be > 0");
     if (set->n > 0xfffffff0ull) return fail(ctx, VRLB_ERR_INVALID, "too many photons");
@@ -718,17 +726,17 @@ int vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set) {
     float cell = 2.5f * set->lookup_radius;
     for (;;) {
         double cells = 1;
-        for (int k = 0; k < 3; ++k) { ctx->photon_res[k] = std::max(1, (int) std::floor((hi[k] - lo[k]) / cell) + 1); cells *= ctx->photon_res[k]; }
+        for (int k = 0; k < 3; ++k) { m.res[k] = std::max(1, (int) std::floor((hi[k] - lo[k]) / cell) + 1); cells *= m.res[k]; }
         if (cells <= 16.0e6) break;
         cell *= 1.5f;
     }
-    const size_t n_cells = (size_t) ctx->photon_res[0] * ctx->photon_res[1] * ctx->photon_res[2];
+    const size_t n_cells = (size_t) m.res[0] * m.res[1] * m.res[2];
     const float inv_cell = 1.0f / cell;
     std::vector<uint32_t> cell_of((size_t) n), order((size_t) n), start(n_cells + 1, 0);
     for (uint64_t i = 0; i < n; ++i) {
         uint32_t c[3];
-        for (int k = 0; k < 3; ++k) c[k] = (uint32_t) std::min(ctx->photon_res[k] - 1, std::max(0, (int) std::floor((set->pos[i * 3 + k] - lo[k]) * inv_cell)));
-        cell_of[i] = (c[2] * (uint32_t) ctx->photon_res[1] + c[1]) * (uint32_t) ctx->photon_res[0] + c[0];
+        for (int k = 0; k < 3; ++k) c[k] = (uint32_t) std::min(m.res[k] - 1, std::max(0, (int) std::floor((set->pos[i * 3 + k] - lo[k]) * inv_cell)));
+        cell_of[i] = (c[2] * (uint32_t) m.res[1] + c[1]) * (uint32_t) m.res[0] + c[0];
         start[cell_of[i] + 1] += 1;
     }
     for (size_t c = 0; c < n_cells; ++c) start[c + 1] += start[c];
@@ -740,13 +748,19 @@ int vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set) {
         sorted[k] = DPhoton{ set->pos[i * 3], set->pos[i * 3 + 1], set->pos[i * 3 + 2], 0.f, set->dir[i * 3], set->dir[i * 3 + 1], set->dir[i * 3 + 2], 0.f,
                              set->power[i * 3], set->power[i * 3 + 1], set->power[i * 3 + 2], 0.f };
     }
-    CU(ctx, ctx->photons.reserve(n)); CU(ctx, ctx->photon_cells.reserve(n_cells + 1));
-    CU(ctx, cudaMemcpyAsync(ctx->photons.ptr, sorted.data(), n * sizeof(DPhoton), cudaMemcpyHostToDevice, ctx->stream));
-    CU(ctx, cudaMemcpyAsync(ctx->photon_cells.ptr, start.data(), (n_cells + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, m.photons.reserve(n)); CU(ctx, m.cells.reserve(n_cells + 1));
+    CU(ctx, cudaMemcpyAsync(m.photons.ptr, sorted.data(), n * sizeof(DPhoton), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaMemcpyAsync(m.cells.ptr, start.data(), (n_cells + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
-    for (int k = 0; k < 3; ++k) ctx->photon_lo[k] = lo[k];
-    ctx->photon_inv_cell = inv_cell; ctx->photon_scale = set->scale; ctx->photon_radius = set->lookup_radius; ctx->n_photons = n;
+    for (int k = 0; k < 3; ++k) m.lo[k] = lo[k];
+    m.inv_cell = inv_cell; m.scale = set->scale; m.radius = set->lookup_radius; m.n = n;
     return VRLB_OK;
+}
+
+int vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set) {
+    if (!ctx || !set) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    return bin_photons(ctx, set, ctx->vol);
 }
 
 // Volume photons by light tracing: the same particles as vrlb_vrls_generate (particle i = PCG32 seed(seed + i)), one
@@ -761,7 +775,7 @@ int vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint
     if (gen->start_medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "start_medium out of range");
     if (n_photons_out) *n_photons_out = 0;
     if (n_particles_out) *n_particles_out = 0;
-    if (capacity == 0) { ctx->n_photons = 0; return VRLB_OK; }            // PhotonMap(m_useDirectIllum ? m_volumePhotons : 0), vrl.cpp:79
+    if (capacity == 0) { ctx->vol.n = 0; return VRLB_OK; }            // PhotonMap(m_useDirectIllum ? m_volumePhotons : 0), vrl.cpp:79
     DevBuf<int32_t> d_etris; DevBuf<float> d_ecdf; DevBuf<uint32_t> d_counts, d_flags; DevBuf<DPhoton> d_ph;
     GenParams p{};
     { int rc = setup_generate(ctx, gen, p, d_etris, d_ecdf); if (rc) return rc; }
@@ -793,7 +807,7 @@ int vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint
     d_etris.release(); d_ecdf.release(); d_counts.release(); d_flags.release(); d_ph.release();
     if (n_photons_out) *n_photons_out = have;
     if (n_particles_out) *n_particles_out = particles;
-    if (have == 0) { ctx->n_photons = 0; return VRLB_OK; }
+    if (have == 0) { ctx->vol.n = 0; return VRLB_OK; }
     const uint64_t counted = have == capacity ? capacity - 1 : have;     // paths counted while the map was not full
     vrlb_photonset_desc d{};
     d.pos = pos.data(); d.dir = dir.data(); d.power = power.data(); d.n = have;
@@ -801,23 +815,27 @@ int vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint
     return vrlb_photons_upload(ctx, &d);
 }
 
-uint64_t vrlb_photons_count(const vrlb_context *ctx) { return ctx ? ctx->n_photons : 0; }
+uint64_t vrlb_photons_count(const vrlb_context *ctx) { return ctx ? ctx->vol.n : 0; }
 
-int vrlb_photons_download(vrlb_context *ctx, float *pos, float *dir, float *power, uint64_t cap, float *scale_out) {
-    if (!ctx) return VRLB_ERR_INVALID;
-    cudaSetDevice(ctx->device);
-    if (scale_out) *scale_out = ctx->photon_scale;
-    const uint64_t n = ctx->n_photons;
+static int download_photons(vrlb_context *ctx, const vrlb_context::PhotonMapRes &m, float *pos, float *dir, float *power, uint64_t cap, float *scale_out) {
+    if (scale_out) *scale_out = m.scale;
+    const uint64_t n = m.n;
     if (cap < n) return fail(ctx, VRLB_ERR_INVALID, "capacity %llu < %llu photons", (unsigned long long) cap, (unsigned long long) n);
     if (n == 0) return VRLB_OK;
     std::vector<DPhoton> tmp((size_t) n);
-    CU(ctx, cudaMemcpy(tmp.data(), ctx->photons.ptr, n * sizeof(DPhoton), cudaMemcpyDeviceToHost));
+    CU(ctx, cudaMemcpy(tmp.data(), m.photons.ptr, n * sizeof(DPhoton), cudaMemcpyDeviceToHost));
     for (uint64_t i = 0; i < n; ++i) {
         if (pos)   { pos[i * 3] = tmp[i].px; pos[i * 3 + 1] = tmp[i].py; pos[i * 3 + 2] = tmp[i].pz; }
         if (dir)   { dir[i * 3] = tmp[i].dx; dir[i * 3 + 1] = tmp[i].dy; dir[i * 3 + 2] = tmp[i].dz; }
         if (power) { power[i * 3] = tmp[i].wr; power[i * 3 + 1] = tmp[i].wg; power[i * 3 + 2] = tmp[i].wb; }
     }
     return VRLB_OK;
+}
+
+int vrlb_photons_download(vrlb_context *ctx, float *pos, float *dir, float *power, uint64_t cap, float *scale_out) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    return download_photons(ctx, ctx->vol, pos, dir, power, cap, scale_out);
 }
 
 int vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *direct_out) {
@@ -830,6 +848,86 @@ int vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, floa
     if (rc == VRLB_OK) {
         cudaError_t e = cudaMemcpyAsync(direct_out, tmp.ptr, ctx->n_segs * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = fail(ctx, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
+    }
+    tmp.release();
+    return rc;
+}
+
+// ---- surface photon maps (surface_photons.cu) ------------------------------------------------------
+int vrlb_surface_photons_upload(vrlb_context *ctx, int which, const vrlb_photonset_desc *set, int32_t lookup_size) {
+    if (!ctx || !set) return VRLB_ERR_INVALID;
+    if (which != VRLB_PHOTONMAP_GLOBAL && which != VRLB_PHOTONMAP_CAUSTIC) return fail(ctx, VRLB_ERR_INVALID, "unknown photon map %d", which);
+    if (set->n && (lookup_size < 1 || lookup_size > VRLB_MAX_LOOKUP)) return fail(ctx, VRLB_ERR_INVALID, "lookup_size must lie in 1 .. %d", VRLB_MAX_LOOKUP);
+    cudaSetDevice(ctx->device);
+    int rc = bin_photons(ctx, set, ctx->surf[which]);
+    if (rc == VRLB_OK) ctx->surf[which].lookup_size = lookup_size;
+    return rc;
+}
+uint64_t vrlb_surface_photons_count(const vrlb_context *ctx, int which) {
+    return (ctx && (which == VRLB_PHOTONMAP_GLOBAL || which == VRLB_PHOTONMAP_CAUSTIC)) ? ctx->surf[which].n : 0;
+}
+int vrlb_surface_photons_download(vrlb_context *ctx, int which, float *pos, float *dir, float *power, uint64_t cap, float *scale_out) {
+    if (!ctx || (which != VRLB_PHOTONMAP_GLOBAL && which != VRLB_PHOTONMAP_CAUSTIC)) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    return download_photons(ctx, ctx->surf[which], pos, dir, power, cap, scale_out);
+}
+int vrlb_surface_queries_upload(vrlb_context *ctx, const vrlb_surface_query *q, uint64_t n, int32_t width, int32_t height) {
+    if (!ctx || (n && !q) || width <= 0 || height <= 0) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    for (uint64_t i = 0; i < n; ++i) if (q[i].pixel >= (uint64_t) width * (uint64_t) height) return fail(ctx, VRLB_ERR_INVALID, "surface query %llu: pixel out of range", (unsigned long long) i);
+    { int rc = ensure_film(ctx, width, height); if (rc) return rc; }
+    CU(ctx, ctx->squeries.reserve(std::max<uint64_t>(n, 1)));
+    if (n) CU(ctx, cudaMemcpyAsync(ctx->squeries.ptr, q, n * sizeof(vrlb_surface_query), cudaMemcpyHostToDevice, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->n_squeries = n;
+    return VRLB_OK;
+}
+int vrlb_surface_queries_download(vrlb_context *ctx, vrlb_surface_query *q, uint64_t cap, uint64_t *n_out) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (n_out) *n_out = ctx->n_squeries;
+    if (!q) return VRLB_OK;
+    if (cap < ctx->n_squeries) return fail(ctx, VRLB_ERR_INVALID, "capacity %llu < %llu surface queries", (unsigned long long) cap, (unsigned long long) ctx->n_squeries);
+    if (ctx->n_squeries) CU(ctx, cudaMemcpy(q, ctx->squeries.ptr, ctx->n_squeries * sizeof(vrlb_surface_query), cudaMemcpyDeviceToHost));
+    return VRLB_OK;
+}
+static void fill_grid(const vrlb_context::PhotonMapRes &m, PhotonGridDev &g) {
+    g.photons = m.photons.ptr; g.cell_start = m.cells.ptr; g.n = m.n;
+    for (int k = 0; k < 3; ++k) { g.grid_lo[k] = m.lo[k]; g.grid_res[k] = m.res[k]; }
+    g.inv_cell = m.inv_cell; g.lookup_radius = m.radius; g.scale = m.scale; g.lookup_size = m.lookup_size;
+}
+// surface term from the resident maps (no-op without photons or queries); film path when out_dev is null
+static int surface_gather_impl(vrlb_context *ctx, float *out_dev) {
+    const bool have_maps = ctx->surf[0].n || ctx->surf[1].n;
+    if (ctx->n_squeries == 0 || (!have_maps && !out_dev)) return VRLB_OK;
+    if (!out_dev && ctx->n_ranks > 1 && ctx->rank != 0) return VRLB_OK;       // VRL shards: the films are summed, this term is rank 0's
+    SurfaceGatherParams p{};
+    fill_grid(ctx->surf[VRLB_PHOTONMAP_GLOBAL], p.global); fill_grid(ctx->surf[VRLB_PHOTONMAP_CAUSTIC], p.caustic);
+    p.heap_stride = std::max(1, std::max(ctx->surf[0].n ? ctx->surf[0].lookup_size : 0, ctx->surf[1].n ? ctx->surf[1].lookup_size : 0));
+    // queries in batches so that the k-nearest scratch stays small (batch * k floats)
+    const uint64_t batch = 1u << 18;
+    DevBuf<float> heap; CU(ctx, heap.reserve(std::min<uint64_t>(batch, ctx->n_squeries) * (uint64_t) p.heap_stride));
+    p.heap = heap.ptr;
+    for (uint64_t first = 0; first < ctx->n_squeries; first += batch) {
+        p.queries = ctx->squeries.ptr + first; p.n_queries = std::min<uint64_t>(batch, ctx->n_squeries - first);
+        p.film_rgb = out_dev ? nullptr : ctx->film_rgb.ptr; p.query_out = out_dev ? out_dev + first * 3 : nullptr;
+        CU(ctx, launch_surface_gather(p, ctx->stream));
+        ctx->timing.total_launches += 1; ctx->launches += 1;
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    heap.release();
+    return VRLB_OK;
+}
+int vrlb_surface_gather_queries(vrlb_context *ctx, float *radiance_out) {
+    if (!ctx || !radiance_out) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    DevBuf<float> tmp;
+    CU(ctx, tmp.reserve(ctx->n_squeries * 3 + 1));
+    CU(ctx, cudaMemsetAsync(tmp.ptr, 0, (ctx->n_squeries * 3 + 1) * sizeof(float), ctx->stream));
+    int rc = surface_gather_impl(ctx, tmp.ptr);
+    if (rc == VRLB_OK && ctx->n_squeries) {
+        cudaError_t e = cudaMemcpy(radiance_out, tmp.ptr, ctx->n_squeries * 3 * sizeof(float), cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) rc = fail(ctx, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
     }
     tmp.release();

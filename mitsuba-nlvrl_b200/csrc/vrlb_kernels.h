@@ -102,6 +102,22 @@ struct PhotonGatherParams {
 };
 cudaError_t launch_photon_gather(const PhotonGatherParams &p, cudaStream_t stream);
 
+// Surface photon maps (surface_photons.cu; vrl.cpp:671-680, photonmap.h:131-211)
+struct PhotonGridDev {                // one resident photon map, binned like the volume map
+    const DPhoton  *photons; const uint32_t *cell_start; uint64_t n;
+    float grid_lo[3], inv_cell; int32_t grid_res[3];
+    float lookup_radius, scale; int32_t lookup_size;
+};
+constexpr int VRLB_MAX_LOOKUP = 1024;
+struct SurfaceGatherParams {
+    const vrlb_surface_query *queries; uint64_t n_queries;
+    PhotonGridDev global, caustic;
+    float *film_rgb, *query_out;      // film: weight * estimate by atomicAdd; query_out: estimate per query (n * 3)
+    float *heap;                      // n_queries * heap_stride floats of scratch (k-nearest squared distances)
+    int32_t heap_stride;
+};
+cudaError_t launch_surface_gather(const SurfaceGatherParams &p, cudaStream_t stream);
+
 // FFMA-saturating microkernel (peak.cu)
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int iters, cudaStream_t stream);
 

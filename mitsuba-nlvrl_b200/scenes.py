@@ -383,6 +383,38 @@ def synthetic_photons(n, seed=9, box=BOX, albedo=0.909):
     return pos, direction, power
 
 
+def synthetic_surface_photons(n, seed=21, half=5.0, z=0.0):
+    """Seeded surface photons on the plane z = const over [-half, half]^2: three in four arrive from above (direction
+    z < 0), every fourth from below; RGB power."""
+    u = _seeded_floats(seed, n * 6).reshape(n, 6)
+    pos = np.stack([(u[:, 0] * 2.0 - 1.0) * half, (u[:, 1] * 2.0 - 1.0) * half, np.full(n, z)], 1).astype(np.float32)
+    cz = -np.sqrt(u[:, 2])                                   # cosine-distributed arrival
+    r = np.sqrt(np.maximum(0.0, 1.0 - cz * cz))
+    phi = u[:, 3] * (2.0 * math.pi)
+    cz[::4] *= -1.0
+    direction = np.stack([r * np.cos(phi), r * np.sin(phi), cz], 1).astype(np.float32)
+    power = ((0.5 + u[:, 4:5]) * np.array([[1.0, 0.8, 0.6]])).astype(np.float32)
+    return pos, direction, power
+
+
+def synthetic_surface_queries(n, width, height, seed=22, half=4.0, z=0.0, twosided_every=0):
+    """Seeded surface queries on the same plane (normal +z): random camera-side directions, most above the plane."""
+    u = _seeded_floats(seed, n * 8).reshape(n, 8)
+    q = np.zeros(n, abi.SURFACE_QUERY_DTYPE)
+    q["p"] = np.stack([(u[:, 0] * 2.0 - 1.0) * half, (u[:, 1] * 2.0 - 1.0) * half, np.full(n, z)], 1)
+    q["n"] = (0.0, 0.0, 1.0)
+    cz = u[:, 2] * 1.2 - 0.2                                 # one in six looks at the back of the surface
+    r = np.sqrt(np.maximum(0.0, 1.0 - cz * cz))
+    phi = u[:, 3] * (2.0 * math.pi)
+    q["wi"] = np.stack([r * np.cos(phi), r * np.sin(phi), cz], 1)
+    q["reflectance"] = 0.2 + 0.7 * u[:, 4:7]
+    q["weight"] = (0.25 + 0.75 * u[:, 7:8]) * np.array([[1.0, 1.0, 1.0]])
+    q["pixel"] = (np.arange(n) * 7919) % (width * height)
+    if twosided_every:
+        q["flags"][::twosided_every] = abi.SURF_TWOSIDED
+    return q
+
+
 # --------------------------------------------------------------------------- files (INTEGRATION.md "File formats")
 def save_vrlb(path, soa10, scale=None, medium=None):
     """Exported VRL set: "VRLB" | u32 version | u64 n | f32 scale | u32 pad | 10*n f32 (SoA) | n u16 medium ids."""

@@ -969,6 +969,54 @@ void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc 
     }
 }
 
+/* The surface radiance of VRLIntegrator::sample at the first smooth surface of the camera path (vrl.cpp:671-680):
+ *   estimateCausticRadiance(si, r_c, k_c) + estimateRadiance(si, r_g, k_g)           (photonmap.h:131-211)
+ * nnSearch (kdtree.h:319-400) = the k nearest photons with d^2 < R^2; when more than k lie inside, the search radius
+ * shrinks to the k-th nearest distance, and THAT radius is what invSquaredRadius is computed from afterwards.  Here: all
+ * in-range distances, sorted (the kd-tree's visiting order only permutes the sum).  bsdf->eval is SmoothDiffuse::eval
+ * (diffuse.cpp): reflectance * INV_PI * cos_theta_o where cos_theta_i > 0 and cos_theta_o > 0, si.wi the camera side,
+ * wo = to_local(-photon.direction); `twosided` flips the frame to the side si.wi lies on.  Either set may be NULL / empty. */
+static V3 surface_estimate(const vrlb_photonset_desc *set, int32_t k, bool caustic, const vrlb_surface_query &q) {
+    V3 result(0.f);
+    if (!set || set->n == 0 || k < 1) return result;
+    const V3 p(q.p);
+    float squaredRadius = set->lookup_radius * set->lookup_radius;
+    std::vector<std::pair<float, uint64_t>> found;
+    for (uint64_t i = 0; i < set->n; ++i) {
+        const float d2 = squared_norm(V3(set->pos + i * 3) - p);
+        if (d2 < squaredRadius) found.push_back({ d2, i });
+    }
+    if (found.size() > (size_t) k) {
+        std::sort(found.begin(), found.end());
+        found.resize((size_t) k);
+        squaredRadius = found.back().first;
+    }
+    std::sort(found.begin(), found.end(), [](auto &a, auto &b) { return a.second < b.second; });
+    const float invSquaredRadius = 1.0f / squaredRadius;
+    V3 n(q.n);
+    float cos_i = dot(V3(q.wi), n);
+    if (cos_i < 0.f && (q.flags & VRLB_SURF_TWOSIDED)) { n = -n; cos_i = -cos_i; }
+    if (!(cos_i > 0.f)) return result;
+    const V3 reflectance(q.reflectance);
+    for (auto &f : found) {
+        const V3 pd(set->dir + f.second * 3), pw(set->power + f.second * 3);
+        const float cos_o = -dot(pd, n);
+        if (!(cos_o > 0.f)) continue;
+        float bs = 0.31830988618379067154f * cos_o;
+        if (caustic) bs = bs * std::max(0.f, 1.0f - std::sqrt(f.first * invSquaredRadius));
+        result = result + pw * (reflectance * bs);
+    }
+    return result * ((caustic ? 3.0f : 1.0f) * set->scale * 0.31830988618379067154f * invSquaredRadius);
+}
+void vrlo_surface_gather_queries(const vrlb_photonset_desc *global, int32_t k_global, const vrlb_photonset_desc *caustic, int32_t k_caustic,
+                                 const vrlb_surface_query *queries, uint64_t n, float *out_rgb) {
+    for (uint64_t i = 0; i < n; ++i) {
+        const V3 c = surface_estimate(caustic, k_caustic, true, queries[i]), g = surface_estimate(global, k_global, false, queries[i]);
+        const V3 r = c + g;
+        out_rgb[i * 3] = r.x; out_rgb[i * 3 + 1] = r.y; out_rgb[i * 3 + 2] = r.z;
+    }
+}
+
 /* VRLMap::toLong -> VRL::convertToLong (vrl_map.h:56-62, vrl_struct.h:146-154): Ray3f r(origin, direction, 0) keeps the
  * default [RayEpsilon, inf) interval; length = si.t of the closest surface; a miss is Log(Error) = throw in the reference */
 uint64_t vrlo_vrls_to_long(const vrlo_scene *s, const float *soa10, uint64_t n, float *length_out) {

@@ -68,6 +68,9 @@ void  vrlo_eval_transmittance(const vrlo_scene *s, const float p1[3], const floa
 /* -- direct in-scattering term from the volume photon map (vrl.cpp:523-611, photonmap.h:216-271), per segment, throughput included -- */
 void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc *set, const vrlb_segment *segs, uint64_t n_segs,
                                  const vrlb_options *opt, float *out_rgb);
+/* caustic + global surface estimate per query (vrl.cpp:671-680, photonmap.h:131-211); either set may be NULL */
+void vrlo_surface_gather_queries(const vrlb_photonset_desc *global, int32_t k_global, const vrlb_photonset_desc *caustic, int32_t k_caustic,
+                                 const vrlb_surface_query *queries, uint64_t n, float *out_rgb);
 
 /* -- VRL-set transforms of VRLIntegrator::preprocess (vrl.cpp:408-415) -- */
 /* VRLMap::toLong (vrl_map.h:56-62): new lengths; returns the number of VRLs that see no surface (the reference throws) */

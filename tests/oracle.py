@@ -55,6 +55,7 @@ def lib():
         L.vrlo_grid_transmittance.argtypes = [C.c_void_p, C.c_int, f3, f3, C.c_float, C.c_uint64]
         L.vrlo_grid_transmittance.restype = C.c_float
         L.vrlo_photon_gather_segments.argtypes = [C.c_void_p, C.POINTER(abi.PhotonSetDesc), C.c_void_p, C.c_uint64, C.POINTER(abi.Options), f3]
+        L.vrlo_surface_gather_queries.argtypes = [C.POINTER(abi.PhotonSetDesc), C.c_int32, C.POINTER(abi.PhotonSetDesc), C.c_int32, C.c_void_p, C.c_uint64, f3]
         L.vrlo_vrls_to_long.argtypes = [C.c_void_p, f3, C.c_uint64, f3]
         L.vrlo_vrls_to_long.restype = C.c_uint64
         L.vrlo_vrls_dice.argtypes = [C.c_void_p, f3, C.POINTER(C.c_uint16), C.c_uint64, C.c_uint32, f3, C.POINTER(C.c_uint16), C.c_uint64]
@@ -163,3 +164,13 @@ class OracleScene:
         ev = lib().vrlo_render(self.h, C.byref(cam), C.byref(opt), C.byref(vrl_desc), rng_mode,
                                n_threads or os.cpu_count(), cr, fp(xyzaw), fp(rgb))
         return xyzaw, rgb, ev
+
+
+def surface_gather(queries, global_desc=None, k_global=0, caustic_desc=None, k_caustic=0):
+    """caustic + global surface estimate per query (vrl.cpp:671-680, photonmap.h:131-211), before the path weight."""
+    q = np.ascontiguousarray(queries, abi.SURFACE_QUERY_DTYPE)
+    out = np.zeros((len(q), 3), np.float32)
+    lib().vrlo_surface_gather_queries(C.byref(global_desc) if global_desc is not None else None, k_global,
+                                      C.byref(caustic_desc) if caustic_desc is not None else None, k_caustic,
+                                      q.ctypes.data, len(q), fp(out))
+    return out

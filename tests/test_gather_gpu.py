@@ -335,3 +335,48 @@ def test_photon_direct_term_on_curved_paths_matches_oracle(ctx, atomic):
     np.add.at(want, segs["pixel"], ref)
     assert rel_err(with_direct, want).max() <= REL_TOL
     assert with_direct.sum() > 1.05 * vrl_only.sum()
+
+
+@pytest.mark.parametrize("radius,k", [(0.5, 50), (0.2, 120), (0.6, 1), (0.35, 1024)])
+def test_surface_photon_estimates_match_oracle(ctx, radius, k):
+    """Global + caustic surface estimates (vrl.cpp:671-680, photonmap.h:131-211) through vrlb_surface_gather_queries: grid
+    binned k-nearest with the shrinking radius against the oracle's sort over all photons; ~157 / 25 / 226 / 77 photons in
+    range for the four cases (so: shrunk, not shrunk, k = 1, k never reached); then the film."""
+    w, h = 48, 32
+    pos, pdir, power = scenes.synthetic_surface_photons(20000, seed=21)
+    cpos, cdir, cpower = scenes.synthetic_surface_photons(5000, seed=23)
+    g = scenes.photonset_desc(pos, pdir, power, scale=1.0 / 812, lookup_radius=radius)
+    c = scenes.photonset_desc(cpos, cdir, cpower, scale=1.0 / 377, lookup_radius=0.5 * radius)
+    q = scenes.synthetic_surface_queries(3000, w, h, seed=22, twosided_every=5)
+    # the film below needs a resident scene / VRL set / segments
+    sc = scenes.box_fog_scene(occluders=False)
+    cam = scenes.box_fog_camera(w, h)
+    opt = scenes.default_options(visibility=0)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(scenes.vrlset_desc(scenes.synthetic_vrls(100, seed=3)))
+    ctx.build_segments(cam, opt)
+    ctx.upload_surface_queries(q, w, h)
+    ctx.upload_surface_photons(abi.PHOTONMAP_GLOBAL, g, k)
+    ctx.clear_surface_photons(abi.PHOTONMAP_CAUSTIC)
+    assert ctx.surface_photons_count(abi.PHOTONMAP_GLOBAL) == 20000 and ctx.surface_photons_count(abi.PHOTONMAP_CAUSTIC) == 0
+    got = ctx.surface_gather_queries().astype(np.float64)
+    ref = oracle.surface_gather(q, global_desc=g, k_global=k).astype(np.float64)
+    front = (q["wi"][:, 2] > 0) | (q["flags"] != 0)
+    assert np.all(ref[~front] == 0) and np.all(got[~front] == 0)          # the back of a one-sided surface
+    assert (ref[front] > 0).mean() > 0.6 and (ref[q["wi"][:, 2] < 0] > 0).sum() > 20   # twosided: seen from below too
+    assert rel_err(got, ref).max() <= 2e-5
+    kc = max(2, k // 2)                                                 # (k = 1 puts the cone filter at its zero)
+    ctx.upload_surface_photons(abi.PHOTONMAP_CAUSTIC, c, kc)
+    got2 = ctx.surface_gather_queries().astype(np.float64)
+    ref2 = oracle.surface_gather(q, global_desc=g, k_global=k, caustic_desc=c, k_caustic=kc).astype(np.float64)
+    assert (ref2.sum() > 1.05 * ref.sum()) and rel_err(got2, ref2).max() <= 2e-5
+    # film = VRL term + weight * estimate at the query's pixel; without maps it is the VRL term alone
+    ctx.clear_film(); ctx.gather(opt)
+    with_surface = ctx.film_rgb(w, h).reshape(-1, 3).astype(np.float64)
+    ctx.clear_surface_photons(abi.PHOTONMAP_GLOBAL); ctx.clear_surface_photons(abi.PHOTONMAP_CAUSTIC)
+    ctx.clear_film(); ctx.gather(opt)
+    vrl_only = ctx.film_rgb(w, h).reshape(-1, 3).astype(np.float64)
+    want = vrl_only.copy()
+    np.add.at(want, q["pixel"], ref2 * q["weight"])
+    assert rel_err(with_surface, want).max() <= REL_TOL
+    ctx.upload_surface_queries(q[:0], w, h)                              # leave no queries behind for the other tests

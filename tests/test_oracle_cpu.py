@@ -412,3 +412,48 @@ def test_photon_direct_term_carries_step_phase_across_parts():
     pf = (1 - g * g) / (4 * math.pi) / (1 + g * g + 2 * g * cos_theta) ** 1.5
     want = math.exp(-0.6 * (r + math.sqrt(2.0) * r)) * pf * 3 / (math.pi * r * r)
     assert np.allclose(got, want, rtol=1e-5)
+
+
+def _sq(p=(0, 0, 0), n=(0, 0, 1), wi=(0, 0, 1), refl=(0.5, 0.6, 0.7), flags=0):
+    q = np.zeros(1, abi.SURFACE_QUERY_DTYPE)
+    q["p"], q["n"], q["wi"], q["reflectance"], q["weight"], q["flags"] = p, n, wi, refl, 1.0, flags
+    return q
+
+
+def test_surface_photon_estimates_closed_form():
+    """photonmap.h:131-211 over kdtree.h:319-400: k nearest inside R; the radius of the density estimate shrinks to the
+    k-th nearest when more than k lie inside; SmoothDiffuse::eval = reflectance / pi * cos_theta_o on the front side."""
+    refl = np.array([0.5, 0.6, 0.7])
+    R = 1.0
+    # one photon, straight down, 0.3 away: N = 1 <= k, the radius stays R
+    one = scenes.photonset_desc([[0.3, 0, 0]], [[0, 0, -1]], [[2.0, 3.0, 4.0]], scale=0.5, lookup_radius=R)
+    got = oracle.surface_gather(_sq(), global_desc=one, k_global=10)[0]
+    want = np.array([2.0, 3.0, 4.0]) * refl / math.pi * 1.0 * 0.5 / (math.pi * R * R)
+    assert np.allclose(got, want, rtol=2e-6)
+    # arriving at 60 degrees: cos_theta_o = 0.5
+    tilt = scenes.photonset_desc([[0.3, 0, 0]], [[math.sin(math.pi / 3), 0, -0.5]], [[2.0, 3.0, 4.0]], scale=0.5, lookup_radius=R)
+    assert np.allclose(oracle.surface_gather(_sq(), global_desc=tilt, k_global=10)[0], 0.5 * want, rtol=2e-6)
+    # from behind the surface, or seen from behind a one-sided surface: nothing; twosided flips the frame
+    back = scenes.photonset_desc([[0.3, 0, 0]], [[0, 0, 1]], [[2.0, 3.0, 4.0]], scale=0.5, lookup_radius=R)
+    assert np.all(oracle.surface_gather(_sq(), global_desc=back, k_global=10) == 0)
+    assert np.all(oracle.surface_gather(_sq(wi=(0, 0, -1)), global_desc=back, k_global=10) == 0)
+    assert np.allclose(oracle.surface_gather(_sq(wi=(0, 0, -1), flags=abi.SURF_TWOSIDED), global_desc=back, k_global=10)[0], want, rtol=2e-6)
+    # outside R: nothing
+    far = scenes.photonset_desc([[1.0001, 0, 0]], [[0, 0, -1]], [[2.0, 3.0, 4.0]], scale=0.5, lookup_radius=R)
+    assert np.all(oracle.surface_gather(_sq(), global_desc=far, k_global=10) == 0)
+    # five photons at 0.1 .. 0.5, k = 3: the three nearest count and the estimate divides by pi * 0.3^2
+    d = np.array([0.4, 0.1, 0.5, 0.3, 0.2], np.float32)
+    pos = np.stack([d, np.zeros(5), np.zeros(5)], 1)
+    pw = np.stack([np.arange(1, 6)] * 3, 1).astype(np.float32)            # power 1..5 in file order
+    five = scenes.photonset_desc(pos, [[0, 0, -1]] * 5, pw, scale=1.0, lookup_radius=R)
+    got = oracle.surface_gather(_sq(), global_desc=five, k_global=3)[0]
+    r2 = float(np.float32(0.3) * np.float32(0.3))
+    want3 = (2 + 4 + 5) * refl / math.pi / (math.pi * r2)                 # photons at 0.1, 0.3, 0.2
+    assert np.allclose(got, want3, rtol=1e-5)
+    # caustic estimate: cone filter (1 - d / r) with the shrunk r, factor 3
+    got_c = oracle.surface_gather(_sq(), caustic_desc=five, k_caustic=3)[0]
+    wsum = 2 * (1 - 0.1 / 0.3) + 4 * (1 - 0.3 / 0.3) + 5 * (1 - 0.2 / 0.3)
+    assert np.allclose(got_c, 3 * wsum * refl / math.pi / (math.pi * r2), rtol=2e-5)
+    # both maps: the sum
+    both = oracle.surface_gather(_sq(), global_desc=five, k_global=3, caustic_desc=five, k_caustic=3)[0]
+    assert np.allclose(both, got + got_c, rtol=1e-6)
