@@ -191,10 +191,24 @@ void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
         m_have_vrls = true;
         // the volume photon map of the direct in-scattering term (vrl.cpp:79: capacity volume_photons iff use_direct_illum;
         // lookup radius = volume_lookup_radius_relative * |bbox.center - bbox.max|, vrl.cpp:449-451).  Same particles as above.
-        if (m_useDirectIllum && m_volumePhotons > 0 && !scene.tri_verts.empty()) {
+        double radius = 0.0;                                                       // sceneRadius = |bbox.center - bbox.max|, vrl.cpp:447
+        if (!scene.tri_verts.empty()) {
             double lo[3] = { 1e300, 1e300, 1e300 }, hi[3] = { -1e300, -1e300, -1e300 };
             for (size_t i = 0; i < scene.tri_verts.size(); ++i) { lo[i % 3] = std::min(lo[i % 3], (double) scene.tri_verts[i]); hi[i % 3] = std::max(hi[i % 3], (double) scene.tri_verts[i]); }
-            const double radius = 0.5 * std::sqrt((hi[0] - lo[0]) * (hi[0] - lo[0]) + (hi[1] - lo[1]) * (hi[1] - lo[1]) + (hi[2] - lo[2]) * (hi[2] - lo[2]));
+            radius = 0.5 * std::sqrt((hi[0] - lo[0]) * (hi[0] - lo[0]) + (hi[1] - lo[1]) * (hi[1] - lo[1]) + (hi[2] - lo[2]) * (hi[2] - lo[2]));
+        }
+        // the global surface map (vrl.cpp:76, 379-390): photons at every smooth surface the same particles meet; the camera
+        // path collects it at its first smooth surface (vrl.cpp:671-680).  The caustic map stays empty: no transmissive
+        // BSDF is on this path, so no particle is ever `wasTransmitted` (vrl.cpp:345, 776-780).
+        if (m_globalPhotons > 0 && radius > 0.0 && sd.tri_reflectance) {
+            uint64_t np = 0, paths = 0;
+            check(vrlb_surface_photons_generate(m_ctx, &g, (uint64_t) m_globalPhotons, (float) (m_globalLookupRadiusRelative * radius),
+                                                (int32_t) m_globalLookupSize, &np, &paths), "vrlb_surface_photons_generate");
+            if (np) std::fprintf(stderr, "[VRLIntegrator] Building global PM, size: %llu (%llu particles), lookup radius %g\n",
+                                 (unsigned long long) np, (unsigned long long) paths, m_globalLookupRadiusRelative * radius);
+            else std::fprintf(stderr, "[VRLIntegrator] No global photons\n");
+        }
+        if (m_useDirectIllum && m_volumePhotons > 0 && radius > 0.0) {
             uint64_t np = 0, paths = 0;
             check(vrlb_photons_generate(m_ctx, &g, (uint64_t) m_volumePhotons, (float) (m_volumeLookupRadiusRelative * radius), &np, &paths), "vrlb_photons_generate");
             std::fprintf(stderr, "[VRLIntegrator] Building volume PM, size: %llu (%llu particles), lookup radius %g\n",

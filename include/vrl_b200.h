@@ -261,7 +261,8 @@ int  vrlb_photons_upload(vrlb_context *ctx, const vrlb_photonset_desc *set);   /
 uint64_t vrlb_photons_count(const vrlb_context *ctx);
 /* Light tracing on the device for the photon set (generate.cu, the same particles as vrlb_vrls_generate): one photon at each
  * particle's first medium scattering, in particle order, until `capacity` (`volume_photons`) are stored; scale as the reference
- * counts its paths (vrl.cpp:372-373, 431).  capacity = 0 or a scene where nothing scatters leaves no set (term off). */
+ * counts its paths (vrl.cpp:124, 372-373, 431: every particle traced while the map was not full, except the one that fills
+ * it).  capacity = 0 or a scene where nothing scatters leaves no set (term off). */
 int  vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
                            uint64_t *n_photons_out, uint64_t *n_particles_out);
 /* pos / dir / power (n x 3 each, any may be NULL) of the resident set in grid order, and its scale */
@@ -283,6 +284,12 @@ enum { VRLB_PHOTONMAP_GLOBAL = 0, VRLB_PHOTONMAP_CAUSTIC = 1 };
  * {global,caustic}_lookup_size (1 .. 1024).  n = 0 clears the map. */
 int  vrlb_surface_photons_upload(vrlb_context *ctx, int which, const vrlb_photonset_desc *set, int32_t lookup_size);
 uint64_t vrlb_surface_photons_count(const vrlb_context *ctx, int which);
+/* Light tracing for the global map (the same particles as vrlb_vrls_generate): one photon per smooth-surface hit (needs
+ * vrlb_scene_desc::tri_reflectance; a zero reflectance stands for a BSDF without a smooth lobe and stores nothing), in
+ * particle order, until `capacity` (`global_photons`) are stored; scale = 1 / (particles traced while the map was not
+ * full, the one that fills it not counted) as vrl.cpp:124, 368-369, 379 count surfacePathCount. */
+int  vrlb_surface_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
+                                   int32_t lookup_size, uint64_t *n_photons_out, uint64_t *n_particles_out);
 int  vrlb_surface_photons_download(vrlb_context *ctx, int which, float *pos, float *dir, float *power, uint64_t cap, float *scale_out);
 /* One surface query = the end of a camera path on a smooth surface; vrlb_gather adds weight * estimate to the film. */
 typedef struct vrlb_surface_query {

@@ -21,7 +21,7 @@ EXPORTS = [
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
     "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice",
-    "vrlb_surface_photons_upload", "vrlb_surface_photons_count", "vrlb_surface_photons_download",
+    "vrlb_surface_photons_upload", "vrlb_surface_photons_generate", "vrlb_surface_photons_count", "vrlb_surface_photons_download",
     "vrlb_surface_queries_upload", "vrlb_surface_queries_download", "vrlb_surface_gather_queries",
     "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments", "vrlb_photons_generate", "vrlb_photons_download",
 ]
@@ -108,6 +108,7 @@ def load_library():
     L.vrlb_vrls_scale.restype = C.c_float
     L.vrlb_vrls_download_depth.argtypes = [vp, C.POINTER(C.c_int32), C.c_uint64]
     L.vrlb_surface_photons_upload.argtypes = [vp, C.c_int, C.POINTER(abi.PhotonSetDesc), C.c_int32]
+    L.vrlb_surface_photons_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.c_uint64, C.c_float, C.c_int32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.vrlb_surface_photons_count.argtypes = [vp, C.c_int]
     L.vrlb_surface_photons_count.restype = C.c_uint64
     L.vrlb_surface_photons_download.argtypes = [vp, C.c_int, f32p, f32p, f32p, C.c_uint64, f32p]
@@ -212,6 +213,13 @@ class Context:
     # ---- surface photon maps (vrl.cpp:671-680) ----
     def upload_surface_photons(self, which, photon_desc, lookup_size):
         self._check(self.lib.vrlb_surface_photons_upload(self.h, which, C.byref(photon_desc), lookup_size))
+
+    def generate_surface_photons(self, gen, capacity, lookup_radius, lookup_size):
+        """Global surface photons by light tracing on the device; returns (n_photons, n_particles)."""
+        n, pcount = C.c_uint64(), C.c_uint64()
+        self._check(self.lib.vrlb_surface_photons_generate(self.h, C.byref(gen), int(capacity), float(lookup_radius), int(lookup_size),
+                                                           C.byref(n), C.byref(pcount)))
+        return int(n.value), int(pcount.value)
 
     def clear_surface_photons(self, which):
         self._check(self.lib.vrlb_surface_photons_upload(self.h, which, C.byref(abi.PhotonSetDesc()), 0))

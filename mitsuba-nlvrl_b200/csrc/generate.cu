@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
     V3 vrl_o = pos, vrl_d0 = dir, vrl_flux = throughput * e.flux; int vrl_depth = 0; bool vrl_open = medium >= 0;
     auto open_vrl = [&](V3 at, V3 d0) { vrl_o = at; vrl_d0 = d0; vrl_flux = throughput * e.flux; vrl_depth = depth; vrl_open = medium >= 0; };
     auto push = [&](V3 end) {                                               // VRL::setEndPoint + VRLMap::push_back
+        if (p.collect_surface) return;
         V3 dd = end - vrl_o; float len = norm(dd);
         if (!(len > 0.f) || medium < 0 || (vrl_flux.x == 0.f && vrl_flux.y == 0.f && vrl_flux.z == 0.f)) return;
         if (WRITE && slot < slot_end) {
@@ -181,7 +182,18 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
             const DTri &tr = s.tris[si.tri];
             if (tr.flags & VRLB_SURF_EMITTER) break;                        // si.shape->is_emitter(): vrl.cpp:309-310, before the VRL is stored
             if (vrl_open) push(pos);                                        // vrl.cpp:312-313
-            // handleSurfaceInteraction (vrl.cpp:315) would store a surface photon here: the surface maps are not built
+            // handleSurfaceInteraction (vrl.cpp:315, 772-782): a smooth BSDF stores a photon (position, travel direction,
+            // flux * throughput before the reflection) whichever side it is met from; !wasTransmitted -> the global map
+            if (p.collect_surface && p.tri_refl && (tr.flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL) {
+                const float *rf0 = p.tri_refl + (size_t) tr.prim * 3;
+                if (__ldg(rf0) != 0.f || __ldg(rf0 + 1) != 0.f || __ldg(rf0 + 2) != 0.f) {   // reflectance 0 stands for a BSDF without a smooth lobe
+                    if (WRITE && slot < slot_end) {
+                        const V3 w = throughput * e.flux;
+                        p.surf_out[slot++] = DPhoton{ pos.x, pos.y, pos.z, 0.f, dir.x, dir.y, dir.z, 0.f, w.x, w.y, w.z, 0.f };
+                    }
+                    ++count;
+                }
+            }
             const float u1 = rng.next_f32(), u2 = rng.next_f32(), u3 = rng.next_f32();     // bsdf->sample(ctx, si, next_1d, next_2d), vrl.cpp:320
             (void) u1;
             if ((tr.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_NULL) {

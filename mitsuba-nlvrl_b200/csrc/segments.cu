@@ -222,7 +222,30 @@ __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
                 const DTri &tr = s.tris[si.tri];
                 if (tr.flags & VRLB_SURF_EMITTER) break;                              // vrl.cpp:664-665
                 valid_ray = true;
-                if ((tr.flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL) break;  // smooth BSDF: vrl.cpp:671-680
+                if ((tr.flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL) {       // smooth BSDF: vrl.cpp:671-680
+                    // radiance += (caustic + global photon estimate at si) * throughput: handed to surface_photons.cu
+                    if (p.squeries && on_film) {
+                        const float *rf = p.tri_refl + (size_t) tr.prim * 3;
+                        const float r0 = __ldg(rf), r1 = __ldg(rf + 1), r2 = __ldg(rf + 2);
+                        if (r0 != 0.f || r1 != 0.f || r2 != 0.f) {
+                            unsigned long long slot = atomicAdd(p.sq_counter, 1ull);
+                            if (slot < p.sq_cap) {
+                                const float *vp = s.verts + (size_t) tr.prim * 9;             // si.p, mesh.cpp:467-484
+                                const float b1 = si.u, b2 = si.v, b0 = 1.f - b1 - b2;
+                                const V3 pnt = V3(vp[0], vp[1], vp[2]) * b0 + V3(vp[3], vp[4], vp[5]) * b1 + V3(vp[6], vp[7], vp[8]) * b2;
+                                const V3 n = tri_normal(tr);
+                                vrlb_surface_query q;
+                                q.p[0] = pnt.x; q.p[1] = pnt.y; q.p[2] = pnt.z; q.pixel = film_pixel;
+                                q.n[0] = n.x; q.n[1] = n.y; q.n[2] = n.z; q.flags = tr.flags & VRLB_SURF_TWOSIDED;
+                                q.wi[0] = -rd.x; q.wi[1] = -rd.y; q.wi[2] = -rd.z; q.pad0 = 0.f;
+                                q.reflectance[0] = r0; q.reflectance[1] = r1; q.reflectance[2] = r2; q.pad1 = 0.f;
+                                q.weight[0] = throughput.x; q.weight[1] = throughput.y; q.weight[2] = throughput.z; q.pad2 = 0.f;
+                                p.squeries[slot] = q;
+                            }
+                        }
+                    }
+                    break;
+                }
                 (void) rng.next_f32(); (void) rng.next_f32(); (void) rng.next_f32();  // Null::sample draws, vrl.cpp:682
                 const float *vp = s.verts + (size_t) tr.prim * 9;                     // si.p, mesh.cpp:467-484
                 float b1 = si.u, b2 = si.v, b0 = 1.f - b1 - b2;

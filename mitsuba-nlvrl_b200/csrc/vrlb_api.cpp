@@ -183,7 +183,7 @@ int vrlb_create(int device, vrlb_context **out) {
         delete ctx; return fail(nullptr, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
-    cudaMalloc((void **) &ctx->counter.ptr, sizeof(unsigned long long)); ctx->counter.cap = 1;
+    cudaMalloc((void **) &ctx->counter.ptr, 2 * sizeof(unsigned long long)); ctx->counter.cap = 2;   // [0] segments, [1] surface queries
     *out = ctx;
     return VRLB_OK;
 }
@@ -586,16 +586,22 @@ int vrlb_segments_build(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_op
         p.n_vrls_total = ctx->vrl_total; p.segs = ctx->segs.ptr; p.cap = ctx->segs.cap; p.counter = ctx->counter.ptr;
         p.film_rgb = ctx->film_rgb.ptr; p.film_aw = ctx->film_aw.ptr;
         p.add_direct = ctx->rank == 0 ? 1 : 0;   // emitter radiance is counted once across VRL shards
+        if (ctx->have_refl) {                    // at most one surface query per camera sample
+            CU(ctx, ctx->squeries.reserve(samples));
+            p.squeries = ctx->squeries.ptr; p.sq_cap = samples; p.sq_counter = ctx->counter.ptr + 1; p.tri_refl = ctx->tri_refl.ptr;
+        }
         size_t np = (size_t) cam->width * cam->height;
         cudaEventRecord(ctx->ev[0], ctx->stream);
-        CU(ctx, cudaMemsetAsync(ctx->counter.ptr, 0, sizeof(unsigned long long), ctx->stream));
+        CU(ctx, cudaMemsetAsync(ctx->counter.ptr, 0, 2 * sizeof(unsigned long long), ctx->stream));
         CU(ctx, cudaMemsetAsync(ctx->film_rgb.ptr, 0, np * 3 * sizeof(float), ctx->stream));
         CU(ctx, cudaMemsetAsync(ctx->film_aw.ptr, 0, np * 2 * sizeof(float), ctx->stream));
         CU(ctx, launch_segments(p, ctx->stream));
         cudaEventRecord(ctx->ev[1], ctx->stream);
-        unsigned long long n = 0;
-        CU(ctx, cudaMemcpyAsync(&n, ctx->counter.ptr, sizeof n, cudaMemcpyDeviceToHost, ctx->stream));
+        unsigned long long n2[2] = { 0, 0 };
+        CU(ctx, cudaMemcpyAsync(n2, ctx->counter.ptr, sizeof n2, cudaMemcpyDeviceToHost, ctx->stream));
         CU(ctx, cudaStreamSynchronize(ctx->stream));
+        const unsigned long long n = n2[0];
+        ctx->n_squeries = ctx->have_refl ? std::min<uint64_t>(n2[1], samples) : 0;
         ctx->timing.ms_segments = elapsed(ctx->ev[0], ctx->ev[1]);
         ctx->timing.total_launches += 1; ctx->launches += 1;
         if (n <= ctx->segs.cap) { ctx->n_segs = n; ctx->timing.n_segments = n; return VRLB_OK; }
@@ -808,11 +814,85 @@ int vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint
     if (n_photons_out) *n_photons_out = have;
     if (n_particles_out) *n_particles_out = particles;
     if (have == 0) { ctx->vol.n = 0; return VRLB_OK; }
-    const uint64_t counted = have == capacity ? capacity - 1 : have;     // paths counted while the map was not full
+    // directVolumePath starts out true for every particle traced while the map is not full and is counted when the map is
+    // still not full after it (vrl.cpp:124, 372-373): every such particle counts, scattered or not, but not the one that fills the map
+    const uint64_t counted = done ? particles - 1 : particles;
     vrlb_photonset_desc d{};
     d.pos = pos.data(); d.dir = dir.data(); d.power = power.data(); d.n = have;
     d.scale = counted ? 1.0f / (float) counted : 1.0f; d.lookup_radius = lookup_radius;
     return vrlb_photons_upload(ctx, &d);
+}
+
+// Global surface photons by light tracing: the same particles again, one photon per smooth-surface hit (several per
+// particle: count pass, host scan, write pass like the VRLs), in particle order until `capacity` are stored.
+// Scale = 1 / surfacePathCount: every particle traced while the map was not full counts, except the one that fills it
+// (vrl.cpp:124, 368-369, 379).
+int vrlb_surface_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
+                                  int32_t lookup_size, uint64_t *n_photons_out, uint64_t *n_particles_out) {
+    if (!ctx || !gen) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_surface_photons_generate");
+    if (gen->start_medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "start_medium out of range");
+    if (n_photons_out) *n_photons_out = 0;
+    if (n_particles_out) *n_particles_out = 0;
+    vrlb_context::PhotonMapRes &map = ctx->surf[VRLB_PHOTONMAP_GLOBAL];
+    if (capacity == 0 || !ctx->have_refl) { map.n = 0; return VRLB_OK; }      // no reflecting surface: nothing to store
+    if (lookup_size < 1 || lookup_size > VRLB_MAX_LOOKUP) return fail(ctx, VRLB_ERR_INVALID, "lookup_size must lie in 1 .. %d", VRLB_MAX_LOOKUP);
+    DevBuf<int32_t> d_etris; DevBuf<float> d_ecdf; DevBuf<uint32_t> d_counts; DevBuf<uint64_t> d_offsets; DevBuf<DPhoton> d_ph;
+    GenParams p{};
+    { int rc = setup_generate(ctx, gen, p, d_etris, d_ecdf); if (rc) return rc; }
+    p.collect_surface = 1;
+    std::vector<DPhoton> all; std::vector<DPhoton> ph;
+    std::vector<uint32_t> counts; std::vector<uint64_t> offsets;
+    uint64_t particles = 0;
+    const uint64_t wave = std::min<uint64_t>(std::max<uint64_t>(capacity / 2, 4096), 1u << 20);
+    bool done = false;
+    for (int iter = 0; iter < 256 && !done; ++iter) {
+        if (ctx->cancel.exchange(0)) return fail(ctx, VRLB_ERR_CANCELLED, "cancelled");
+        CU(ctx, d_counts.reserve(wave)); CU(ctx, d_offsets.reserve(wave + 1));
+        p.n_particles = wave; p.first_particle = particles; p.counts = d_counts.ptr; p.offsets = nullptr; p.surf_out = nullptr;
+        CU(ctx, launch_generate(p, false, ctx->stream)); ctx->launches += 1;
+        counts.resize(wave);
+        CU(ctx, cudaMemcpyAsync(counts.data(), d_counts.ptr, wave * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        offsets.assign(wave + 1, 0);
+        uint64_t used = wave;
+        for (uint64_t i = 0; i < wave; ++i) {
+            offsets[i + 1] = offsets[i] + counts[i];
+            if (all.size() + offsets[i + 1] >= capacity) { used = i + 1; done = true; break; }   // this particle fills the map
+        }
+        const uint64_t add = offsets[used];
+        if (add) {
+            CU(ctx, d_ph.reserve(add));
+            CU(ctx, cudaMemcpyAsync(d_offsets.ptr, offsets.data(), (used + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+            p.n_particles = used; p.offsets = d_offsets.ptr; p.surf_out = d_ph.ptr;
+            CU(ctx, launch_generate(p, true, ctx->stream)); ctx->launches += 1;
+            ph.resize(add);
+            CU(ctx, cudaMemcpyAsync(ph.data(), d_ph.ptr, add * sizeof(DPhoton), cudaMemcpyDeviceToHost, ctx->stream));
+            CU(ctx, cudaStreamSynchronize(ctx->stream));
+            all.insert(all.end(), ph.begin(), ph.end());
+        }
+        particles += used;
+        if (!done && all.empty() && iter >= 3) break;                       // no particle ever meets a reflecting surface
+    }
+    d_etris.release(); d_ecdf.release(); d_counts.release(); d_offsets.release(); d_ph.release();
+    if (all.size() > capacity) all.resize(capacity);                        // PhotonMap::insert refuses once full
+    if (n_photons_out) *n_photons_out = all.size();
+    if (n_particles_out) *n_particles_out = particles;
+    if (all.empty()) { map.n = 0; return VRLB_OK; }
+    const uint64_t counted = done ? particles - 1 : particles;
+    std::vector<float> pos(all.size() * 3), dir(all.size() * 3), power(all.size() * 3);
+    for (size_t i = 0; i < all.size(); ++i) {
+        pos[i * 3] = all[i].px; pos[i * 3 + 1] = all[i].py; pos[i * 3 + 2] = all[i].pz;
+        dir[i * 3] = all[i].dx; dir[i * 3 + 1] = all[i].dy; dir[i * 3 + 2] = all[i].dz;
+        power[i * 3] = all[i].wr; power[i * 3 + 1] = all[i].wg; power[i * 3 + 2] = all[i].wb;
+    }
+    vrlb_photonset_desc d{};
+    d.pos = pos.data(); d.dir = dir.data(); d.power = power.data(); d.n = all.size();
+    d.scale = counted ? 1.0f / (float) counted : 1.0f; d.lookup_radius = lookup_radius;
+    int rc = bin_photons(ctx, &d, map);
+    if (rc == VRLB_OK) map.lookup_size = lookup_size;
+    return rc;
 }
 
 uint64_t vrlb_photons_count(const vrlb_context *ctx) { return ctx ? ctx->vol.n : 0; }

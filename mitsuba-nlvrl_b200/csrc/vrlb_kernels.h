@@ -47,6 +47,9 @@ struct SegmentParams {
     float        *film_rgb;      // device: emitter radiance seen directly is added here
     float        *film_aw;       // device: width*height*2: sum(alpha), sum(weight)
     int32_t       add_direct;    // 0 on ranks > 0 of a VRL-sharded render: emitter radiance is counted once
+    // camera paths that end on a smooth surface (vrl.cpp:671-680): one query each, when the scene carries reflectances
+    vrlb_surface_query *squeries; uint64_t sq_cap; unsigned long long *sq_counter;   // null = not collected
+    const float  *tri_refl;      // n_tris * 3, original triangle order
 };
 cudaError_t launch_segments(const SegmentParams &p, cudaStream_t stream);
 
@@ -75,6 +78,10 @@ struct GenParams {
     DPhoton  *photon_out;     // device or null (count pass only): one slot per particle of the wave, the volume photon of
     uint32_t *photon_flag;        //   its FIRST medium scattering (vrl.cpp:278-281) and whether it deposited one
     const float *tri_refl;        // device or null: n_tris * 3 diffuse reflectance, ORIGINAL triangle order (DTri::prim)
+    // surface photon collection (handleSurfaceInteraction, vrl.cpp:315, 772-782): counts / offsets / the two passes then
+    // refer to surface photons instead of VRLs, and no VRL is written
+    int32_t   collect_surface;
+    DPhoton  *surf_out;
 };
 cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream);
 

@@ -239,7 +239,7 @@ def make_nonlinear_medium(lo, hi, res_y, bottom_ior=1.0, top_ior=0.95, **kw):
 BOX = 10.0
 
 
-def box_fog_scene(occluders=True, phase=abi.PHASE_ISOTROPIC, g=0.8, sigma_s=0.1, sigma_a=0.01):
+def box_fog_scene(occluders=True, phase=abi.PHASE_ISOTROPIC, g=0.8, sigma_s=0.1, sigma_a=0.01, wall_reflectance=None):
     """Fog box [-10.01,10.01]^3 (null BSDF, interior medium 0) around five diffuse walls at +-10 (front
     face open towards the camera), optional sphere r=4 and rotated cuboid as occluders inside."""
     sc = Scene()
@@ -247,7 +247,7 @@ def box_fog_scene(occluders=True, phase=abi.PHASE_ISOTROPIC, g=0.8, sigma_s=0.1,
     med = sc.add_medium(make_medium(sigma_t=(st,) * 3, albedo=(sigma_s / st,) * 3, scale=1.0, phase=phase, g=g))
     e = BOX + 0.01
     sc.add_tris(box_tris((-e,) * 3, (e,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(med))
-    sc.add_tris(box_tris((-BOX,) * 3, (BOX,) * 3, faces="xXyYZ", inward=True), abi.SURF_BSDF_SMOOTH)
+    sc.add_tris(box_tris((-BOX,) * 3, (BOX,) * 3, faces="xXyYZ", inward=True), abi.SURF_BSDF_SMOOTH, reflectance=wall_reflectance)
     if occluders:
         sc.add_tris(sphere_tris((4.5, -2.0, -1.0), 4.0), abi.SURF_BSDF_SMOOTH)
         cub = box_tris((-2.0, -3.0, -1.5), (2.0, 3.0, 1.5))

@@ -380,3 +380,54 @@ def test_surface_photon_estimates_match_oracle(ctx, radius, k):
     np.add.at(want, q["pixel"], ref2 * q["weight"])
     assert rel_err(with_surface, want).max() <= REL_TOL
     ctx.upload_surface_queries(q[:0], w, h)                              # leave no queries behind for the other tests
+
+
+def test_camera_paths_hand_their_first_smooth_surface_to_the_photon_maps(ctx):
+    """vrl.cpp:671-680: where a camera path ends on a smooth surface, radiance += (caustic + global estimate) * throughput.
+    vrlb_segments_build writes one surface query per such path (position, normal, -ray.d, reflectance, throughput) when the
+    scene carries reflectances; vrlb_gather adds weight * estimate to the film."""
+    w, h = 64, 36
+    refl = (0.7, 0.6, 0.5)
+    sc = scenes.box_fog_scene(occluders=True, wall_reflectance=refl)     # sphere / cuboid carry no reflectance: no query there
+    cam = scenes.box_fog_camera(w, h)
+    opt = scenes.default_options(visibility=1)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(scenes.vrlset_desc(scenes.synthetic_vrls(200, seed=3)))
+    ctx.build_segments(cam, opt)
+    segs = ctx.download_segments()
+    q = ctx.download_surface_queries()
+    assert len(q) > 0.5 * w * h and len(np.unique(q["pixel"])) == len(q)  # one path per pixel at spp 1
+    # the paths that end on a wall are those whose in-medium segment ends there
+    end = segs["o"] + segs["d"] * segs["maxt"][:, None]
+    on_wall = np.abs(end).max(axis=1) > scenes.BOX - 1e-3
+    assert set(segs["pixel"][on_wall]) == set(q["pixel"])
+    p = q["p"].astype(np.float64)
+    assert np.allclose(np.abs(p).max(axis=1), scenes.BOX, atol=1e-3)
+    assert np.allclose(q["reflectance"], np.array(refl, np.float32)[None, :]) and np.all(q["flags"] == 0)
+    assert ((q["wi"] * q["n"]).sum(1) > 0).all()                           # inward walls seen from inside
+    # throughput = transmittance over the stretch inside the fog box [-10.01, 10.01]^3 (camera at z = -40 outside it)
+    o = np.array([0.0, 0.0, -40.0])
+    d = p - o
+    dist = np.linalg.norm(d, axis=1)
+    t_in = (-(scenes.BOX + 0.01) - o[2]) / (d[:, 2] / dist)
+    assert np.allclose(q["weight"][:, 0], np.exp(-0.11 * (dist - t_in)), rtol=2e-4)
+    assert np.allclose(q["wi"], -d / dist[:, None], atol=2e-5)
+    # film: a global map on the back wall (photons travelling +z arrive on its front)
+    pos, pdir, power = scenes.synthetic_surface_photons(20000, seed=31, half=10.0, z=10.0)
+    g = scenes.photonset_desc(pos, pdir, power, scale=1.0 / 5000, lookup_radius=0.8)
+    ref = oracle.surface_gather(q, global_desc=g, k_global=60).astype(np.float64)
+    assert (ref.sum(1) > 0).sum() > 0.1 * len(q)
+    ctx.upload_surface_photons(abi.PHOTONMAP_GLOBAL, g, 60)
+    assert rel_err(ctx.surface_gather_queries().astype(np.float64), ref).max() <= 2e-5
+    ctx.clear_film(); ctx.gather(opt)
+    with_surface = ctx.film_rgb(w, h).reshape(-1, 3).astype(np.float64)
+    ctx.clear_surface_photons(abi.PHOTONMAP_GLOBAL)
+    ctx.clear_film(); ctx.gather(opt)
+    vrl_only = ctx.film_rgb(w, h).reshape(-1, 3).astype(np.float64)
+    want = vrl_only.copy()
+    np.add.at(want, q["pixel"], ref * q["weight"])
+    assert rel_err(with_surface, want).max() <= REL_TOL and with_surface.sum() > 1.05 * vrl_only.sum()
+    # a scene without reflectances collects no queries
+    ctx.set_scene(scenes.box_fog_scene(occluders=True))
+    ctx.build_segments(cam, opt)
+    assert len(ctx.download_surface_queries()) == 0

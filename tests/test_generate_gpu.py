@@ -338,3 +338,37 @@ def test_particles_end_on_emitter_surfaces_without_storing_the_flight(ctx):
     assert n >= 60 and particles > 1000 * n                                         # only the rare scattered particles store anything
     soa, _ = ctx.download_vrls()
     assert np.abs((soa[0:3] + soa[3:6] * soa[6])).max() < 5 - 1e-3                  # every stored VRL ends inside, at a scattering
+
+
+def test_global_photons_are_the_surface_hits_of_the_same_particles(ctx):
+    """handleSurfaceInteraction (vrl.cpp:315, 772-782): every smooth surface a particle meets stores a photon (position,
+    travel direction, flux * throughput before the reflection) until the map is full; scale = 1 / surfacePathCount where
+    every particle traced while the map was not full counts, except the one that fills it (vrl.cpp:124, 368-369, 379)."""
+    size, refl, power = 5.0, (0.6, 0.5, 0.4), (2.0, 1.0, 0.5)
+    ctx.set_scene(_bounce_box(size, 0.02, refl))
+    gen = scenes.generate_desc(60000, seed=5, laser=((0, 0, 0), (0.3, 0.2, 1.0), power), start_medium=0)
+    n, particles = ctx.generate_surface_photons(gen, 5000, 0.4, 50)
+    assert n == 5000 and 500 < particles < 5000                           # several bounces per particle
+    assert ctx.surface_photons_count(abi.PHOTONMAP_GLOBAL) == 5000
+    pos, pdir, pw, scale = ctx.download_surface_photons(abi.PHOTONMAP_GLOBAL)
+    assert scale == pytest.approx(1.0 / (particles - 1))
+    assert np.allclose(np.abs(pos).max(axis=1), size, atol=1e-3)          # on the walls
+    ax = np.abs(pos).argmax(axis=1)
+    idx = np.arange(len(pos))
+    assert (pdir[idx, ax] * np.sign(pos[idx, ax]) > 0).all()              # travelling into the wall
+    # the unscattered laser flight: full power, all at the spot the laser hits on the z = +size wall
+    direct = np.isclose(pw, np.array(power, np.float32)[None, :], rtol=1e-6).all(axis=1)
+    assert direct.sum() > 0.5 * particles
+    assert np.allclose(pos[direct], [[1.5, 1.0, 5.0]], atol=1e-4)
+    # below the roulette depth: power = laser power * albedo^a * reflectance^r (red channel, up to two events)
+    ratio = pw[:, 0].astype(np.float64) / power[0]
+    allowed = np.array([1.0, 0.9, 0.6, 0.81, 0.54, 0.36])
+    assert (np.abs(ratio[:, None] - allowed[None, :]).min(axis=1) < 1e-5).mean() > 0.5
+    # no reflectance table or capacity 0: no map
+    assert ctx.generate_surface_photons(gen, 0, 0.4, 50) == (0, 0) and ctx.surface_photons_count(abi.PHOTONMAP_GLOBAL) == 0
+    ctx.set_scene(_bounce_box(size, 0.02, refl, with_table=False))
+    assert ctx.generate_surface_photons(gen, 5000, 0.4, 50)[0] == 0
+    # the volume map counts its paths the same way: here most particles end on a wall without scattering, and count
+    n_v, p_v = ctx.generate_photons(gen, 500, 0.5)
+    assert n_v == 500 and p_v > 3 * n_v
+    assert ctx.download_photons()[3] == pytest.approx(1.0 / (p_v - 1))

@@ -317,6 +317,25 @@ def test_render_xml_legacy_schema_renders_the_same_film(host, tmp_path):
 
 
 @pytest.mark.gpu
+def test_render_xml_global_photon_map(host, tmp_path):
+    """The plugin builds the global surface map from the same light tracing (global_photons, global_lookup_radius_relative,
+    global_lookup_size) and the camera paths that end on a diffuse surface collect it; global_photons=0 switches it off."""
+    path = _write_scene(str(tmp_path))
+    txt = open(path).read().replace('<medium id="fog" type="nonlinear">', '<medium id="fog" type="homogeneous">')
+    open(path, "w").write(txt)
+    films = {}
+    for n in ("20000", "0"):
+        out = os.path.join(str(tmp_path), f"film_g{n}.f32")
+        r = subprocess.run([host, "render-xml", path, out, "-Dspp=1", "use_direct_illum=false", f"global_photons={n}",
+                            "global_lookup_size=40"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert ("Building global PM, size: 20000" in r.stderr) == (n == "20000"), r.stderr
+        films[n] = np.fromfile(out, np.float32).reshape(48, 64, 5)
+    a, b = films["20000"][..., 1], films["0"][..., 1]
+    assert np.isfinite(a).all() and np.all(a >= b - 1e-7) and (a > b + 1e-9).sum() > 20 and a.sum() > b.sum()
+
+
+@pytest.mark.gpu
 def test_render_xml_direct_term_switch(host, tmp_path):
     """use_direct_illum (default true, vrl.cpp:57): the plugin builds the volume photon map from the same light tracing and
     adds the direct in-scattering term; with use_direct_illum=false the film holds the VRL term only and is darker."""
