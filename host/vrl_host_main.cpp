@@ -119,10 +119,11 @@ int main(int argc, char **argv) {
                 {   // what the light tracer sees of the BSDFs: triangles that reflect particles, their mean reflectance
                     size_t n_refl = 0; double mean[3] = { 0, 0, 0 };
                     const auto &rf = ls.scene.tri_reflectance;
-                    for (size_t i = 0; i + 2 < rf.size(); i += 3) if (rf[i] > 0 || rf[i + 1] > 0 || rf[i + 2] > 0) { ++n_refl; for (int k = 0; k < 3; ++k) mean[k] += rf[i + (size_t) k]; }
+                    for (size_t i = 0; i + 2 < rf.size(); i += 3) if ((ls.scene.tri_flags[i / 3] & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_SMOOTH && (rf[i] > 0 || rf[i + 1] > 0 || rf[i + 2] > 0)) { ++n_refl; for (int k = 0; k < 3; ++k) mean[k] += rf[i + (size_t) k]; }
                     for (int k = 0; k < 3; ++k) mean[k] = n_refl ? mean[k] / (double) n_refl : 0.0;
-                    size_t n_two = 0; for (uint32_t f : ls.scene.tri_flags) n_two += (f & VRLB_SURF_TWOSIDED) != 0;
-                    std::printf(" \"reflecting_triangles\": %zu, \"twosided_triangles\": %zu, \"mean_reflectance\": [%.9g, %.9g, %.9g],\n", n_refl, n_two, mean[0], mean[1], mean[2]);
+                    size_t n_two = 0, n_mirror = 0, n_glass = 0;
+                    for (uint32_t f : ls.scene.tri_flags) { n_two += (f & VRLB_SURF_TWOSIDED) != 0; n_mirror += (f & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_MIRROR; n_glass += (f & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_DIELECTRIC; }
+                    std::printf(" \"reflecting_triangles\": %zu, \"twosided_triangles\": %zu, \"mirror_triangles\": %zu, \"dielectric_triangles\": %zu, \"mean_reflectance\": [%.9g, %.9g, %.9g],\n", n_refl, n_two, n_mirror, n_glass, mean[0], mean[1], mean[2]);
                 }
                 std::printf(" \"media\": [");
                 for (size_t i = 0; i < ls.scene.media.size(); ++i) {

@@ -198,15 +198,24 @@ void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
             radius = 0.5 * std::sqrt((hi[0] - lo[0]) * (hi[0] - lo[0]) + (hi[1] - lo[1]) * (hi[1] - lo[1]) + (hi[2] - lo[2]) * (hi[2] - lo[2]));
         }
         // the global surface map (vrl.cpp:76, 379-390): photons at every smooth surface the same particles meet; the camera
-        // path collects it at its first smooth surface (vrl.cpp:671-680).  The caustic map stays empty: no transmissive
-        // BSDF is on this path, so no particle is ever `wasTransmitted` (vrl.cpp:345, 776-780).
+        // path collects it at its first smooth surface (vrl.cpp:671-680); the caustic map likewise when the scene has a
+        // dielectric (a caustic photon needs `wasTransmitted`, vrl.cpp:345, 776-780).
         if (m_globalPhotons > 0 && radius > 0.0 && sd.tri_reflectance) {
             uint64_t np = 0, paths = 0;
-            check(vrlb_surface_photons_generate(m_ctx, &g, (uint64_t) m_globalPhotons, (float) (m_globalLookupRadiusRelative * radius),
+            check(vrlb_surface_photons_generate(m_ctx, VRLB_PHOTONMAP_GLOBAL, &g, (uint64_t) m_globalPhotons, (float) (m_globalLookupRadiusRelative * radius),
                                                 (int32_t) m_globalLookupSize, &np, &paths), "vrlb_surface_photons_generate");
             if (np) std::fprintf(stderr, "[VRLIntegrator] Building global PM, size: %llu (%llu particles), lookup radius %g\n",
                                  (unsigned long long) np, (unsigned long long) paths, m_globalLookupRadiusRelative * radius);
             else std::fprintf(stderr, "[VRLIntegrator] No global photons\n");
+            bool any_dielectric = false;
+            for (uint32_t f : scene.tri_flags) any_dielectric = any_dielectric || (f & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_DIELECTRIC;
+            if (m_causticPhotons > 0 && any_dielectric) {                   // only a transmission makes a caustic photon (vrl.cpp:345, 776-780)
+                check(vrlb_surface_photons_generate(m_ctx, VRLB_PHOTONMAP_CAUSTIC, &g, (uint64_t) m_causticPhotons, (float) (m_causticLookupRadiusRelative * radius),
+                                                    (int32_t) m_causticLookupSize, &np, &paths), "vrlb_surface_photons_generate");
+                if (np) std::fprintf(stderr, "[VRLIntegrator] Building caustic PM, size: %llu (%llu particles), lookup radius %g\n",
+                                     (unsigned long long) np, (unsigned long long) paths, m_causticLookupRadiusRelative * radius);
+                else std::fprintf(stderr, "[VRLIntegrator] No caustic photons\n");
+            }
         }
         if (m_useDirectIllum && m_volumePhotons > 0 && radius > 0.0) {
             uint64_t np = 0, paths = 0;

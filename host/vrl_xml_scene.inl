@@ -96,8 +96,19 @@ struct Builder {
     }
 
     // ---- shapes ----
-    static bool is_delta(const std::string &t) {
-        return t == "dielectric" || t == "thindielectric" || t == "conductor" || t == "roughdielectric" || t == "roughconductor" || t == "plastic";
+    // named indices of refraction, src/libcore/... ior.h (the entries the fixture scenes can name)
+    double ior_of(const Node &b, const char *name, const char *def) {
+        const Node *p = prop(b, name);
+        if (p && (p->name == "float" || p->name == "integer")) return to_double(*p, p->get("value"));
+        const std::string v = p ? p->get("value") : std::string(def);
+        static const std::pair<const char *, double> table[] = {
+            { "vacuum", 1.0 }, { "helium", 1.000036 }, { "hydrogen", 1.000132 }, { "air", 1.000277 }, { "carbon dioxide", 1.00045 },
+            { "water", 1.3330 }, { "acetone", 1.36 }, { "ethanol", 1.361 }, { "carbon tetrachloride", 1.461 }, { "glycerol", 1.4729 },
+            { "benzene", 1.501 }, { "silicone oil", 1.52045 }, { "bromine", 1.661 }, { "water ice", 1.31 }, { "fused quartz", 1.458 },
+            { "pyrex", 1.470 }, { "acrylic glass", 1.49 }, { "polypropylene", 1.49 }, { "bk7", 1.5046 }, { "sodium chloride", 1.544 },
+            { "amber", 1.55 }, { "pet", 1.5750 }, { "diamond", 2.419 } };
+        for (auto &e : table) if (v == e.first) return e.second;
+        fail("Error while loading \"" + b.file + "\": unknown index of refraction \"" + v + "\"");
     }
     void add_tri(const double a[3], const double b[3], const double c[3], uint32_t flags, std::vector<float> &v) {
         for (const double *p : { a, b, c }) for (int k = 0; k < 3; ++k) v.push_back((float) p[k]);
@@ -157,8 +168,32 @@ struct Builder {
                 b = in; t = b->get("type");
             }
             if (t == "null") { flags = (flags & ~VRLB_SURF_BSDF_MASK) | VRLB_SURF_BSDF_NULL; return; }
-            if (is_delta(t)) {
-                warn("bsdf type=\"" + t + "\": specular chains are not on the VRL path yet; the surface loads as an occluder");
+            if (t == "conductor") {
+                // SmoothConductor (conductor.cpp): delta reflection, weight = specular_reflectance x Fresnel.  The descriptor
+                // carries one RGB weight: exact for the default eta = 0, k = 1 (Fresnel = 1); a named material or an explicit
+                // eta / k is reduced to its normal-incidence value where given as numbers
+                flags = (flags & ~VRLB_SURF_BSDF_MASK) | VRLB_SURF_BSDF_MIRROR;
+                refl[0] = refl[1] = refl[2] = 1.f;
+                prop_rgb(*b, "specular_reflectance", refl);
+                float eta[3] = { 0.f, 0.f, 0.f }, k[3] = { 1.f, 1.f, 1.f };
+                const bool have = prop_rgb(*b, "eta", eta) | prop_rgb(*b, "k", k);
+                if (have) { for (int c = 0; c < 3; ++c) refl[c] *= ((eta[c] - 1) * (eta[c] - 1) + k[c] * k[c]) / ((eta[c] + 1) * (eta[c] + 1) + k[c] * k[c]);
+                            warn("bsdf type=\"conductor\": Fresnel term taken at normal incidence"); }
+                if (prop(*b, "material") && prop_string(*b, "material", "none") != "none")
+                    warn("bsdf type=\"conductor\": material \"" + prop_string(*b, "material", "") + "\" has no spectral table here; Fresnel term taken as 1");
+                return;
+            }
+            if (t == "dielectric") {
+                // SmoothDielectric (dielectric.cpp:  int_ior default bk7, ext_ior default air)
+                flags = (flags & ~VRLB_SURF_BSDF_MASK) | VRLB_SURF_BSDF_DIELECTRIC;
+                float sr[3] = { 1.f, 1.f, 1.f }, st[3] = { 1.f, 1.f, 1.f };
+                prop_rgb(*b, "specular_reflectance", sr); prop_rgb(*b, "specular_transmittance", st);
+                if (sr[0] != sr[1] || sr[0] != sr[2] || st[0] != st[1] || st[0] != st[2]) warn("bsdf type=\"dielectric\": coloured specular_reflectance / transmittance reduced to the red channel");
+                refl[0] = (float) (ior_of(*b, "int_ior", "bk7") / ior_of(*b, "ext_ior", "air")); refl[1] = sr[0]; refl[2] = st[0];
+                return;
+            }
+            if (t == "thindielectric") {
+                warn("bsdf type=\"thindielectric\" is not on the VRL path; the surface loads as an occluder");
                 refl[0] = refl[1] = refl[2] = 0.f;              // light-tracing particles end there
                 return;
             }
@@ -201,7 +236,7 @@ struct Builder {
         // Emitter::medium() is the exterior medium of the shape the emitter sits on (shape.cpp: the area emitter inherits
         // it); particles start there (vrl.cpp:152)
         if ((flags & VRLB_SURF_EMITTER) && VRLB_SURF_GET_EXTERIOR(flags) >= 0) out.scene.emission_medium = VRLB_SURF_GET_EXTERIOR(flags);
-        const bool reflects = (flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_SMOOTH && !(flags & VRLB_SURF_EMITTER);
+        const bool reflects = (flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL && !((flags & VRLB_SURF_EMITTER) && (flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_SMOOTH);
         for (size_t i = 0; i < v.size() / 9; ++i) {
             out.scene.tri_flags.push_back(flags);
             for (int k = 0; k < 3; ++k) out.scene.tri_reflectance.push_back(reflects ? refl[k] : 0.f);

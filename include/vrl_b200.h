@@ -44,7 +44,13 @@ enum {
  * (vrl_struct.h:552-557, vrl.cpp:713-714). */
 #define VRLB_SURF_BSDF_MASK      0x3u
 #define VRLB_SURF_BSDF_SMOOTH    0x0u   /* diffuse & co: ends the camera path, occludes          */
+/* The delta classes below continue the camera path and the light-tracing particle (specular chains, vrl.cpp:318-358,
+ * 682-716); towards shadow segments they occlude like every other surface (vrl_struct.h:529). */
 #define VRLB_SURF_BSDF_NULL      0x1u   /* index-matched boundary: passed through                */
+#define VRLB_SURF_BSDF_MIRROR    0x2u   /* smooth conductor (src/bsdfs/conductor.cpp): delta reflection, weight =
+                                         * tri_reflectance (specular_reflectance x Fresnel, taken angle-independent) */
+#define VRLB_SURF_BSDF_DIELECTRIC 0x3u  /* smooth dielectric (src/bsdfs/dielectric.cpp): tri_reflectance holds
+                                         * { eta = int_ior / ext_ior, specular_reflectance, specular_transmittance } */
 #define VRLB_SURF_EMITTER        0x4u   /* area emitter attached                                 */
 #define VRLB_SURF_TWOSIDED       0x8u   /* `twosided` adapter: the diffuse lobe reflects on both sides (light tracing) */
 #define VRLB_SURF_INTERIOR(m)    ((((uint32_t)(m)) + 1u) << 8)   /* medium id m on the -n side  */
@@ -277,18 +283,20 @@ int  vrlb_photon_gather_segments(vrlb_context *ctx, const vrlb_options *opt, flo
  * (SmoothDiffuse::eval = reflectance / pi * cos_theta_o where both cosines are positive), times scale / (pi r^2); the
  * caustic estimate adds the cone filter max(0, 1 - d / r) and a factor 3.  Photons are what the light tracer stores at
  * every smooth surface a particle meets (handleSurfaceInteraction, vrl.cpp:315, 772-782): position, travel direction,
- * flux * throughput before the reflection; caustic = arrived through a transmission (no such BSDF on this path yet, so
- * the light tracer here only fills the global map).  scale = 1 / surfacePathCount (vrl.cpp:379-383). */
+ * flux * throughput before the reflection; caustic = the last surface event before it was a transmission.
+ * scale = 1 / surfacePathCount for both maps (vrl.cpp:379-399). */
 enum { VRLB_PHOTONMAP_GLOBAL = 0, VRLB_PHOTONMAP_CAUSTIC = 1 };
 /* set->lookup_radius = {global,caustic}_lookup_radius_relative * scene radius (vrl.cpp:448-450); lookup_size =
  * {global,caustic}_lookup_size (1 .. 1024).  n = 0 clears the map. */
 int  vrlb_surface_photons_upload(vrlb_context *ctx, int which, const vrlb_photonset_desc *set, int32_t lookup_size);
 uint64_t vrlb_surface_photons_count(const vrlb_context *ctx, int which);
-/* Light tracing for the global map (the same particles as vrlb_vrls_generate): one photon per smooth-surface hit (needs
+/* Light tracing for the global or the caustic map (the same particles as vrlb_vrls_generate): one photon per smooth-surface
+ * hit -- caustic when the particle's last surface event was a transmission through a dielectric, global otherwise
+ * (wasTransmitted, vrl.cpp:345, 776-780) -- (needs
  * vrlb_scene_desc::tri_reflectance; a zero reflectance stands for a BSDF without a smooth lobe and stores nothing), in
  * particle order, until `capacity` (`global_photons`) are stored; scale = 1 / (particles traced while the map was not
  * full, the one that fills it not counted) as vrl.cpp:124, 368-369, 379 count surfacePathCount. */
-int  vrlb_surface_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
+int  vrlb_surface_photons_generate(vrlb_context *ctx, int which, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
                                    int32_t lookup_size, uint64_t *n_photons_out, uint64_t *n_particles_out);
 int  vrlb_surface_photons_download(vrlb_context *ctx, int which, float *pos, float *dir, float *power, uint64_t cap, float *scale_out);
 /* One surface query = the end of a camera path on a smooth surface; vrlb_gather adds weight * estimate to the film. */

@@ -5,6 +5,7 @@ COMM_ID_BYTES = 128
 OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CANCELLED, ERR_NOMEM = 0, -1, -2, -3, -4, -5
 
 SURF_BSDF_SMOOTH, SURF_BSDF_NULL, SURF_EMITTER, SURF_TWOSIDED = 0x0, 0x1, 0x4, 0x8
+SURF_BSDF_MIRROR, SURF_BSDF_DIELECTRIC = 0x2, 0x3
 MEDIUM_HOMOGENEOUS, MEDIUM_GRID, MEDIUM_NONLINEAR = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_HG = 0, 1
 

@@ -108,7 +108,7 @@ def load_library():
     L.vrlb_vrls_scale.restype = C.c_float
     L.vrlb_vrls_download_depth.argtypes = [vp, C.POINTER(C.c_int32), C.c_uint64]
     L.vrlb_surface_photons_upload.argtypes = [vp, C.c_int, C.POINTER(abi.PhotonSetDesc), C.c_int32]
-    L.vrlb_surface_photons_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.c_uint64, C.c_float, C.c_int32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    L.vrlb_surface_photons_generate.argtypes = [vp, C.c_int, C.POINTER(abi.GenerateDesc), C.c_uint64, C.c_float, C.c_int32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.vrlb_surface_photons_count.argtypes = [vp, C.c_int]
     L.vrlb_surface_photons_count.restype = C.c_uint64
     L.vrlb_surface_photons_download.argtypes = [vp, C.c_int, f32p, f32p, f32p, C.c_uint64, f32p]
@@ -214,10 +214,10 @@ class Context:
     def upload_surface_photons(self, which, photon_desc, lookup_size):
         self._check(self.lib.vrlb_surface_photons_upload(self.h, which, C.byref(photon_desc), lookup_size))
 
-    def generate_surface_photons(self, gen, capacity, lookup_radius, lookup_size):
-        """Global surface photons by light tracing on the device; returns (n_photons, n_particles)."""
+    def generate_surface_photons(self, gen, capacity, lookup_radius, lookup_size, which=abi.PHOTONMAP_GLOBAL):
+        """Global / caustic surface photons by light tracing on the device; returns (n_photons, n_particles)."""
         n, pcount = C.c_uint64(), C.c_uint64()
-        self._check(self.lib.vrlb_surface_photons_generate(self.h, C.byref(gen), int(capacity), float(lookup_radius), int(lookup_size),
+        self._check(self.lib.vrlb_surface_photons_generate(self.h, which, C.byref(gen), int(capacity), float(lookup_radius), int(lookup_size),
                                                            C.byref(n), C.byref(pcount)))
         return int(n.value), int(pcount.value)
 

@@ -118,6 +118,7 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
     // depth counts real events (medium scatterings + reflections) = the reference's `depth` - 1 (it starts at 1,
     // vrl.cpp:171); medium_depth is its mediumDepth (vrl.cpp:164)
     int medium = e.medium, depth = 0, medium_depth = 0;
+    bool was_transmitted = false;                                          // vrl.cpp:165, 345: the last surface event was a transmission
     // a VRL keeps the flux and depth it was created with (VRL(ray.o, medium, throughput * flux, depth ...), vrl.cpp:178,
     // 283, 354): the roulette's 1/q of a later iteration does not reach the VRL already in flight
     V3 vrl_o = pos, vrl_d0 = dir, vrl_flux = throughput * e.flux; int vrl_depth = 0; bool vrl_open = medium >= 0;
@@ -184,7 +185,9 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
             if (vrl_open) push(pos);                                        // vrl.cpp:312-313
             // handleSurfaceInteraction (vrl.cpp:315, 772-782): a smooth BSDF stores a photon (position, travel direction,
             // flux * throughput before the reflection) whichever side it is met from; !wasTransmitted -> the global map
-            if (p.collect_surface && p.tri_refl && (tr.flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL) {
+            const uint32_t bsdf_kind = tr.flags & VRLB_SURF_BSDF_MASK;
+            // collect_surface 1 = the global map (!wasTransmitted), 2 = the caustic map (wasTransmitted), vrl.cpp:776-780
+            if (p.collect_surface && p.tri_refl && bsdf_kind == VRLB_SURF_BSDF_SMOOTH && was_transmitted == (p.collect_surface == 2)) {
                 const float *rf0 = p.tri_refl + (size_t) tr.prim * 3;
                 if (__ldg(rf0) != 0.f || __ldg(rf0 + 1) != 0.f || __ldg(rf0 + 2) != 0.f) {   // reflectance 0 stands for a BSDF without a smooth lobe
                     if (WRITE && slot < slot_end) {
@@ -195,13 +198,32 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
                 }
             }
             const float u1 = rng.next_f32(), u2 = rng.next_f32(), u3 = rng.next_f32();     // bsdf->sample(ctx, si, next_1d, next_2d), vrl.cpp:320
-            (void) u1;
-            if ((tr.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_NULL) {
+            if (bsdf_kind == VRLB_SURF_BSDF_NULL) {
+                was_transmitted = false;                                    // non_null_bsdf && Transmission, vrl.cpp:345
                 if (VRLB_SURF_GET_EXTERIOR(tr.flags) >= 0 || VRLB_SURF_GET_INTERIOR(tr.flags) >= 0) medium = target_medium(tr, dir);
                 pos = pos + dir * ((1.f + hmax_abs(pos)) * kRayEpsilon);    // spawn_ray offset
                 open_vrl(pos, dir);
                 continue;
             }
+            if (bsdf_kind != VRLB_SURF_BSDF_SMOOTH) {
+                // specular chain on the light side (vrl.cpp:318-358): SmoothConductor / SmoothDielectric::sample
+                if (!p.tri_refl) break;
+                const float *rf = p.tri_refl + (size_t) tr.prim * 3;
+                const DeltaSample ds = sample_delta(bsdf_kind, __ldg(rf), __ldg(rf + 1), __ldg(rf + 2), (tr.flags & VRLB_SURF_TWOSIDED) != 0u,
+                                                    tri_normal(tr), dir, u1);
+                if (!ds.valid) break;
+                throughput = throughput * ds.weight;
+                if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+                dir = ds.wo;
+                ++depth;
+                was_transmitted = ds.transmitted;
+                if (was_transmitted) medium_depth = 0;                      // vrl.cpp:346-347
+                if (VRLB_SURF_GET_EXTERIOR(tr.flags) >= 0 || VRLB_SURF_GET_INTERIOR(tr.flags) >= 0) medium = target_medium(tr, dir);
+                pos = pos + dir * ((1.f + hmax_abs(pos)) * kRayEpsilon);
+                open_vrl(pos, dir);
+                continue;
+            }
+            was_transmitted = false;
             // SmoothDiffuse::sample (src/bsdfs/diffuse.cpp): nothing behind a one-sided surface, else a cosine-distributed
             // direction about the normal (warp::square_to_cosine_hemisphere) with weight = reflectance
             V3 n = tri_normal(tr);
@@ -235,7 +257,8 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
         ++depth;                                                           // vrl.cpp:254
         if (depth + 1 >= p.max_depth) break;                               // vrl.cpp:257-258: the scattering is dropped
         throughput = throughput * V3(m->albedo[0], m->albedo[1], m->albedo[2]);
-        if (!WRITE && p.photon_out && medium_depth == 0) {                 // handleMediumInteraction, vrl.cpp:276-281, 785
+        if (!WRITE && p.photon_out && medium_depth == 0 && !p.photon_flag[pi]) {   // handleMediumInteraction, vrl.cpp:276-281, 785 (one slot per
+                                                                           // particle: a second direct scattering after a transmission is not stored)
             const V3 w = throughput * e.flux;                              // flux * throughput after the albedo
             p.photon_out[pi] = DPhoton{ pos.x, pos.y, pos.z, 0.f, dir.x, dir.y, dir.z, 0.f, w.x, w.y, w.z, 0.f };
             p.photon_flag[pi] = 1u;
@@ -247,7 +270,7 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
         open_vrl(pos, dir);
     }
     if (!WRITE) p.counts[pi] = count;
-    if (!WRITE && p.photon_out && medium_depth == 0) p.photon_flag[pi] = 0u;   // never scattered in a medium
+
 }
 
 cudaError_t launch_generate(const GenParams &p, bool write, cudaStream_t stream) {

@@ -222,7 +222,8 @@ __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
                 const DTri &tr = s.tris[si.tri];
                 if (tr.flags & VRLB_SURF_EMITTER) break;                              // vrl.cpp:664-665
                 valid_ray = true;
-                if ((tr.flags & VRLB_SURF_BSDF_MASK) != VRLB_SURF_BSDF_NULL) {       // smooth BSDF: vrl.cpp:671-680
+                const uint32_t bsdf_kind = tr.flags & VRLB_SURF_BSDF_MASK;
+                if (bsdf_kind == VRLB_SURF_BSDF_SMOOTH) {                              // smooth BSDF: vrl.cpp:671-680
                     // radiance += (caustic + global photon estimate at si) * throughput: handed to surface_photons.cu
                     if (p.squeries && on_film) {
                         const float *rf = p.tri_refl + (size_t) tr.prim * 3;
@@ -246,7 +247,20 @@ __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
                     }
                     break;
                 }
-                (void) rng.next_f32(); (void) rng.next_f32(); (void) rng.next_f32();  // Null::sample draws, vrl.cpp:682
+                const float sample1 = rng.next_f32(); (void) rng.next_f32(); (void) rng.next_f32();  // bsdf->sample(ctx, si, next_1d, next_2d), vrl.cpp:682
+                if (bsdf_kind != VRLB_SURF_BSDF_NULL) {
+                    // specular chain (vrl.cpp:682-705): delta reflection / refraction, throughput *= weight, depth += 1
+                    if (!p.tri_refl) break;
+                    const float *rf = p.tri_refl + (size_t) tr.prim * 3;
+                    const DeltaSample ds = sample_delta(bsdf_kind, __ldg(rf), __ldg(rf + 1), __ldg(rf + 2), (tr.flags & VRLB_SURF_TWOSIDED) != 0u,
+                                                        tri_normal(tr), rd, sample1);
+                    if (!ds.valid) break;
+                    throughput = throughput * ds.weight;
+                    if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+                    rd = ds.wo;
+                    depth += 1u;
+                    specular_chain = true;                                            // vrl.cpp:700-701
+                }
                 const float *vp = s.verts + (size_t) tr.prim * 9;                     // si.p, mesh.cpp:467-484
                 float b1 = si.u, b2 = si.v, b0 = 1.f - b1 - b2;
                 V3 pnt = V3(vp[0], vp[1], vp[2]) * b0 + V3(vp[3], vp[4], vp[5]) * b1 + V3(vp[6], vp[7], vp[8]) * b2;

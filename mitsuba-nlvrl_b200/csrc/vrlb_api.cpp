@@ -256,8 +256,10 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
         uint32_t f = sc->tri_flags ? sc->tri_flags[i] : 0u;
         if (VRLB_SURF_GET_INTERIOR(f) >= (int) sc->n_media || VRLB_SURF_GET_EXTERIOR(f) >= (int) sc->n_media)
             return fail(ctx, VRLB_ERR_INVALID, "triangle %u references medium out of range", i);
-        if ((f & VRLB_SURF_BSDF_MASK) > VRLB_SURF_BSDF_NULL)
-            return fail(ctx, VRLB_ERR_INVALID, "triangle %u: BSDF class %u not supported on this path", i, f & VRLB_SURF_BSDF_MASK);
+        if ((f & VRLB_SURF_BSDF_MASK) > VRLB_SURF_BSDF_NULL && !sc->tri_reflectance)
+            return fail(ctx, VRLB_ERR_INVALID, "triangle %u: BSDF class %u needs its parameters in tri_reflectance", i, f & VRLB_SURF_BSDF_MASK);
+        if ((f & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_DIELECTRIC && !(sc->tri_reflectance[(size_t) i * 3] > 0.f))
+            return fail(ctx, VRLB_ERR_INVALID, "triangle %u: dielectric eta must be > 0", i);
     }
     std::vector<DMedium> dm(sc->n_media);
     std::vector<float> grid_host; std::vector<std::pair<uint32_t, size_t>> grid_off;
@@ -588,7 +590,7 @@ int vrlb_segments_build(vrlb_context *ctx, const vrlb_camera *cam, const vrlb_op
         p.add_direct = ctx->rank == 0 ? 1 : 0;   // emitter radiance is counted once across VRL shards
         if (ctx->have_refl) {                    // at most one surface query per camera sample
             CU(ctx, ctx->squeries.reserve(samples));
-            p.squeries = ctx->squeries.ptr; p.sq_cap = samples; p.sq_counter = ctx->counter.ptr + 1; p.tri_refl = ctx->tri_refl.ptr;
+            p.squeries = ctx->squeries.ptr; p.sq_cap = samples; p.sq_counter = ctx->counter.ptr + 1; p.tri_refl = ctx->tri_refl.ptr;   // (also the delta BSDFs' parameters)
         }
         size_t np = (size_t) cam->width * cam->height;
         cudaEventRecord(ctx->ev[0], ctx->stream);
@@ -823,25 +825,27 @@ int vrlb_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint
     return vrlb_photons_upload(ctx, &d);
 }
 
-// Global surface photons by light tracing: the same particles again, one photon per smooth-surface hit (several per
+// Global / caustic surface photons by light tracing: the same particles again, one photon per smooth-surface hit that
+// was (caustic) or was not (global) preceded by a transmission as the last surface event (vrl.cpp:776-780) (several per
 // particle: count pass, host scan, write pass like the VRLs), in particle order until `capacity` are stored.
 // Scale = 1 / surfacePathCount: every particle traced while the map was not full counts, except the one that fills it
 // (vrl.cpp:124, 368-369, 379).
-int vrlb_surface_photons_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
+int vrlb_surface_photons_generate(vrlb_context *ctx, int which, const vrlb_generate_desc *gen, uint64_t capacity, float lookup_radius,
                                   int32_t lookup_size, uint64_t *n_photons_out, uint64_t *n_particles_out) {
     if (!ctx || !gen) return VRLB_ERR_INVALID;
+    if (which != VRLB_PHOTONMAP_GLOBAL && which != VRLB_PHOTONMAP_CAUSTIC) return fail(ctx, VRLB_ERR_INVALID, "unknown photon map %d", which);
     cudaSetDevice(ctx->device);
     if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "vrlb_scene_set must precede vrlb_surface_photons_generate");
     if (gen->start_medium >= ctx->scene.n_media) return fail(ctx, VRLB_ERR_INVALID, "start_medium out of range");
     if (n_photons_out) *n_photons_out = 0;
     if (n_particles_out) *n_particles_out = 0;
-    vrlb_context::PhotonMapRes &map = ctx->surf[VRLB_PHOTONMAP_GLOBAL];
+    vrlb_context::PhotonMapRes &map = ctx->surf[which];
     if (capacity == 0 || !ctx->have_refl) { map.n = 0; return VRLB_OK; }      // no reflecting surface: nothing to store
     if (lookup_size < 1 || lookup_size > VRLB_MAX_LOOKUP) return fail(ctx, VRLB_ERR_INVALID, "lookup_size must lie in 1 .. %d", VRLB_MAX_LOOKUP);
     DevBuf<int32_t> d_etris; DevBuf<float> d_ecdf; DevBuf<uint32_t> d_counts; DevBuf<uint64_t> d_offsets; DevBuf<DPhoton> d_ph;
     GenParams p{};
     { int rc = setup_generate(ctx, gen, p, d_etris, d_ecdf); if (rc) return rc; }
-    p.collect_surface = 1;
+    p.collect_surface = which == VRLB_PHOTONMAP_CAUSTIC ? 2 : 1;
     std::vector<DPhoton> all; std::vector<DPhoton> ph;
     std::vector<uint32_t> counts; std::vector<uint64_t> offsets;
     uint64_t particles = 0;

@@ -178,6 +178,52 @@ struct DScene {
     int32_t      n_emitters;
 };
 
+// ---- delta BSDFs of the specular chains (vrl.cpp:318-358 light side, 682-716 camera side) ----
+// The translation units are built with -fmad=false -prec-div=true -prec-sqrt=true, so the plain expressions below are
+// one IEEE operation per written operation, like the oracle's.
+__device__ inline void coordinate_system(V3 n, V3 &s, V3 &t) {            // core/vector.h (Duff et al.)
+    float sign = copysignf(1.f, n.z), a = -1.f / (sign + n.z), b = n.x * n.y * a;
+    s = V3(1.f + sign * n.x * n.x * a, sign * b, -sign * n.x);
+    t = V3(b, sign + n.y * n.y * a, -n.y);
+}
+struct DeltaSample { V3 wo; V3 weight; bool valid, transmitted; };
+// bsdf->sample(ctx, si, sample1, sample2) of SmoothConductor / SmoothDielectric with the default BSDFContext
+// (TransportMode::Radiance on both the camera and the light side, as vrl.cpp constructs it).  `rd` = ray direction,
+// `n` = geometric normal = shading frame, prm = the triangle's three tri_reflectance floats.
+__device__ inline DeltaSample sample_delta(uint32_t kind, float p0, float p1, float p2, bool twosided, V3 n, V3 rd, float sample1) {
+    DeltaSample r; r.valid = false; r.transmitted = false; r.weight = V3(0.f); r.wo = rd;
+    V3 s, t; coordinate_system(n, s, t);
+    const V3 w = -rd;
+    const V3 wi(dot(w, s), dot(w, t), dot(w, n));                          // si.wi = to_local(-ray.d)
+    V3 wo;
+    if (kind == VRLB_SURF_BSDF_MIRROR) {                                   // conductor.cpp: active &= cos_theta_i > 0; wo = reflect(wi)
+        if (!(wi.z > 0.f) && !(twosided && wi.z < 0.f)) return r;
+        wo = V3(-wi.x, -wi.y, wi.z);
+        r.weight = V3(p0, p1, p2);
+    } else {                                                               // dielectric.cpp + fresnel(), core/fresnel.h
+        const float eta = p0, cos_i = wi.z;
+        const bool outside = cos_i >= 0.f;
+        const float rcp_eta = 1.f / eta, eta_it = outside ? eta : rcp_eta, eta_ti = outside ? rcp_eta : eta;
+        const float cos_t_sqr = 1.f - (1.f - cos_i * cos_i) * (eta_ti * eta_ti);
+        const float cos_i_abs = fabsf(cos_i), cos_t_abs = sqrtf(fmaxf(cos_t_sqr, 0.f));
+        const bool special = eta == 1.f || cos_i_abs == 0.f;
+        const float a_s = (cos_i_abs - eta_it * cos_t_abs) / (cos_i_abs + eta_it * cos_t_abs);
+        const float a_p = (cos_t_abs - eta_it * cos_i_abs) / (cos_t_abs + eta_it * cos_i_abs);
+        float r_i = 0.5f * (a_s * a_s + a_p * a_p);
+        if (special) r_i = eta == 1.f ? 0.f : 1.f;
+        const float cos_t = cos_i >= 0.f ? -cos_t_abs : cos_t_abs;         // mulsign_neg(cos_theta_t_abs, cos_theta_i)
+        if (sample1 <= r_i) { wo = V3(-wi.x, -wi.y, wi.z); r.weight = V3(p1); }
+        else {
+            wo = V3(-eta_ti * wi.x, -eta_ti * wi.y, cos_t);                // refract(wi, cos_theta_t, eta_ti)
+            r.weight = V3(p2 * (eta_ti * eta_ti));                         // radiance scaling, dielectric.cpp (mode == Radiance)
+            r.transmitted = true;
+        }
+    }
+    r.wo = s * wo.x + t * wo.y + n * wo.z;                                 // si.to_world(bs.wo)
+    r.valid = true;
+    return r;
+}
+
 // Exactly-rounded fp32 building blocks: one IEEE operation each, immune to FMA contraction whatever the
 // translation unit's -fmad setting.  Hit / no-hit decisions (and the exact-mode gather) are built from these so
 // they agree with the oracle's -ffp-contract=off arithmetic.

@@ -256,6 +256,21 @@ def box_fog_scene(occluders=True, phase=abi.PHASE_ISOTROPIC, g=0.8, sigma_s=0.1,
     return sc
 
 
+def specular_fog_scene(mirror=(0.9, 0.8, 0.7), eta=1.5, wall_reflectance=(0.7, 0.6, 0.5)):
+    """box-fog with a mirror sphere (smooth conductor) and a glass cuboid (smooth dielectric, fog on both sides of its
+    faces): camera paths carry on after them (specular chains, vrl.cpp:682-716)."""
+    sc = Scene()
+    med = sc.add_medium(make_medium(sigma_t=(0.11,) * 3, albedo=(0.1 / 0.11,) * 3, scale=1.0))
+    e = BOX + 0.01
+    sc.add_tris(box_tris((-e,) * 3, (e,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(med))
+    sc.add_tris(box_tris((-BOX,) * 3, (BOX,) * 3, faces="xXyYZ", inward=True), abi.SURF_BSDF_SMOOTH, reflectance=wall_reflectance)
+    sc.add_tris(sphere_tris((4.5, -2.0, -1.0), 4.0)[:, ::-1], abi.SURF_BSDF_MIRROR, reflectance=mirror)   # outward normals: a conductor is one-sided
+    cub = box_tris((-2.0, -3.0, -1.5), (2.0, 3.0, 1.5))
+    m = _translate(-4.0, -1.0, 2.0) @ rotation((0.3, 1.0, 0.2), 35.0)
+    sc.add_tris(transform_tris(cub, m), abi.SURF_BSDF_DIELECTRIC, reflectance=(eta, 1.0, 1.0))
+    return sc
+
+
 def nl_fog_scene(occluders=True, res_y=320, bottom_ior=1.0, top_ior=0.95, sigma_s=0.1, sigma_a=0.01):
     """box-fog variant V4: the fog is a graded-IOR `nonlinear` medium, IOR(y) = lerp(bottom, top) over the
     box height in res_y layers (cbox-nonlinear-homo.xml uses 640), so camera paths are curved."""

@@ -199,7 +199,7 @@ namespace {
 /*  Scene: triangle soup + a conservative BVH (stands in for ShapeKDTree, kdtree.h:2069-2172;  */
 /*  only the set of triangle hits matters, and that is decided by the exact test below).      */
 /* ------------------------------------------------------------------------------------------ */
-struct Tri { V3 p0, p1, p2; uint32_t flags; };
+struct Tri { V3 p0, p1, p2; uint32_t flags; float prm[3]; };   /* prm = the triangle's tri_reflectance entry (0 when absent) */
 
 struct BvhNode { float lo[3], hi[3]; int left, right, first, count, axis; };
 
@@ -378,6 +378,52 @@ inline bool is_medium_transition(const Tri &t) {
     return VRLB_SURF_GET_EXTERIOR(t.flags) >= 0 || VRLB_SURF_GET_INTERIOR(t.flags) >= 0;
 }
 inline bool is_null(const Tri &t) { return (t.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_NULL; }
+
+/* coordinate_system, include/mitsuba/core/vector.h (Duff et al.) */
+inline void coordinate_system(V3 n, V3 &s, V3 &t) {
+    float sign = std::copysign(1.f, n.z), a = -1.f / (sign + n.z), b = n.x * n.y * a;
+    s = V3(1.f + sign * n.x * n.x * a, sign * b, -sign * n.x);
+    t = V3(b, sign + n.y * n.y * a, -n.y);
+}
+/* bsdf->sample(ctx, si, sample1, sample2) for the two delta BSDFs of the specular chains, default BSDFContext
+ * (TransportMode::Radiance): SmoothConductor::sample (src/bsdfs/conductor.cpp: one-sided, wo = reflect(wi), weight =
+ * specular_reflectance x Fresnel -- the descriptor carries the product, taken angle-independent) and
+ * SmoothDielectric::sample (src/bsdfs/dielectric.cpp with fresnel() of include/mitsuba/core/fresnel.h: reflect when
+ * sample1 <= r_i, else refract with the eta_ti^2 radiance scaling).  Returns false when the lobe is inactive. */
+inline bool sample_delta(const Tri &tr, V3 n, V3 rd, float sample1, V3 &wo_world, V3 &weight, bool &transmitted) {
+    const uint32_t kind = tr.flags & VRLB_SURF_BSDF_MASK;
+    const bool twosided = (tr.flags & VRLB_SURF_TWOSIDED) != 0;
+    transmitted = false;
+    V3 s, t; coordinate_system(n, s, t);
+    const V3 w = -rd;
+    const V3 wi(dot(w, s), dot(w, t), dot(w, n));
+    V3 wo;
+    if (kind == VRLB_SURF_BSDF_MIRROR) {
+        if (!(wi.z > 0.f) && !(twosided && wi.z < 0.f)) return false;
+        wo = V3(-wi.x, -wi.y, wi.z);
+        weight = V3(tr.prm[0], tr.prm[1], tr.prm[2]);
+    } else {
+        const float eta = tr.prm[0], cos_theta_i = wi.z;
+        const bool outside_mask = cos_theta_i >= 0.f;
+        const float rcp_eta = 1.f / eta, eta_it = outside_mask ? eta : rcp_eta, eta_ti = outside_mask ? rcp_eta : eta;
+        const float cos_theta_t_sqr = 1.f - (1.f - cos_theta_i * cos_theta_i) * (eta_ti * eta_ti);
+        const float cos_theta_i_abs = std::fabs(cos_theta_i), cos_theta_t_abs = std::sqrt(std::max(cos_theta_t_sqr, 0.f));
+        const bool special_case = eta == 1.f || cos_theta_i_abs == 0.f;
+        const float a_s = (cos_theta_i_abs - eta_it * cos_theta_t_abs) / (cos_theta_i_abs + eta_it * cos_theta_t_abs);
+        const float a_p = (cos_theta_t_abs - eta_it * cos_theta_i_abs) / (cos_theta_t_abs + eta_it * cos_theta_i_abs);
+        float r_i = 0.5f * (a_s * a_s + a_p * a_p);
+        if (special_case) r_i = eta == 1.f ? 0.f : 1.f;
+        const float cos_theta_t = cos_theta_i >= 0.f ? -cos_theta_t_abs : cos_theta_t_abs;
+        if (sample1 <= r_i) { wo = V3(-wi.x, -wi.y, wi.z); weight = V3(tr.prm[1]); }
+        else {
+            wo = V3(-eta_ti * wi.x, -eta_ti * wi.y, cos_theta_t);
+            weight = V3(tr.prm[2] * (eta_ti * eta_ti));
+            transmitted = true;
+        }
+    }
+    wo_world = s * wo.x + t * wo.y + n * wo.z;
+    return true;
+}
 
 /* ------------------------------------------------------------------------------------------ */
 /*  Media and phase functions                                                                 */
@@ -875,7 +921,8 @@ vrlo_scene *vrlo_scene_create(const vrlb_scene_desc *desc) {
     s->tris.resize(desc->n_tris);
     for (uint32_t i = 0; i < desc->n_tris; ++i) {
         const float *p = desc->tri_verts + (size_t) i * 9;
-        s->tris[i] = Tri{ V3(p), V3(p + 3), V3(p + 6), desc->tri_flags ? desc->tri_flags[i] : 0u };
+        const float *r = desc->tri_reflectance ? desc->tri_reflectance + (size_t) i * 3 : nullptr;
+        s->tris[i] = Tri{ V3(p), V3(p + 3), V3(p + 6), desc->tri_flags ? desc->tri_flags[i] : 0u, { r ? r[0] : 0.f, r ? r[1] : 0.f, r ? r[2] : 0.f } };
     }
     s->media.assign(desc->media, desc->media + desc->n_media);
     s->grids.resize(desc->n_media);
@@ -904,6 +951,15 @@ void vrlo_eval_transmittance(const vrlo_scene *s, const float p1[3], const float
     Pcg32 sub; sub.seed(0, PCG32_DEFAULT_STREAM + 1);
     float tr = eval_transmittance(*s, true, V3(p1), V3(p2), medium, &sub);
     out_rgb[0] = out_rgb[1] = out_rgb[2] = tr;
+}
+
+/* probe for the delta BSDFs of the specular chains (tests/test_oracle_cpu.py): returns 0 when the lobe is inactive */
+int vrlo_sample_delta(uint32_t flags, const float prm[3], const float n[3], const float rd[3], float sample1, float wo[3], float weight[3], int *transmitted) {
+    Tri tr{ V3(0.f), V3(0.f), V3(0.f), flags, { prm[0], prm[1], prm[2] } };
+    V3 w, wt; bool tt = false;
+    if (!sample_delta(tr, V3(n), V3(rd), sample1, w, wt, tt)) return 0;
+    wo[0] = w.x; wo[1] = w.y; wo[2] = w.z; weight[0] = wt.x; weight[1] = wt.y; weight[2] = wt.z; *transmitted = tt ? 1 : 0;
+    return 1;
 }
 
 /* probes for the grid medium (tests/test_oracle_cpu.py) */
@@ -1310,9 +1366,19 @@ SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler 
             const Tri &tr = s.tris[(size_t) si.prim];
             if (tr.flags & VRLB_SURF_EMITTER) break;            /* vrl.cpp:664-665 */
             valid_ray = true;
-            if (!is_null(tr)) break;                            /* smooth BSDF: photon-map estimates, then break (vrl.cpp:671-680) */
-            /* Null::sample (null.cpp:38-52): consumes next_1d + next_2d, weight 1, wo = -wi */
-            (void) sampler.next_1d(); (void) sampler.next_1d(); (void) sampler.next_1d();
+            if ((tr.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_SMOOTH) break;   /* smooth BSDF: photon-map estimates, then break (vrl.cpp:671-680) */
+            /* bsdf->sample consumes next_1d + next_2d (vrl.cpp:682).  Null::sample (null.cpp:38-52): weight 1, wo = -wi */
+            const float sample1 = sampler.next_1d(); (void) sampler.next_1d(); (void) sampler.next_1d();
+            if (!is_null(tr)) {
+                /* specular chain, vrl.cpp:682-705 */
+                V3 wo, weight; bool transmitted;
+                if (!sample_delta(tr, tri_normal(tr), rd, sample1, wo, weight, transmitted)) break;
+                throughput = throughput * weight;
+                if (throughput.x == 0.f && throughput.y == 0.f && throughput.z == 0.f) break;
+                rd = wo;
+                depth += 1;
+                specular_chain = true;
+            }
             V3 p  = tri_point(tr, si.u, si.v);
             ro    = p;                                          /* si.spawn_ray, interaction.h:58-61 */
             rmint = (1.f + hmax_abs(p)) * kRayEpsilon;

@@ -71,6 +71,8 @@ void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc 
 /* caustic + global surface estimate per query (vrl.cpp:671-680, photonmap.h:131-211); either set may be NULL */
 void vrlo_surface_gather_queries(const vrlb_photonset_desc *global, int32_t k_global, const vrlb_photonset_desc *caustic, int32_t k_caustic,
                                  const vrlb_surface_query *queries, uint64_t n, float *out_rgb);
+/* SmoothConductor / SmoothDielectric::sample as the specular chains call it (vrl.cpp:320, 682); 0 = inactive lobe */
+int vrlo_sample_delta(uint32_t flags, const float prm[3], const float n[3], const float rd[3], float sample1, float wo[3], float weight[3], int *transmitted);
 
 /* -- VRL-set transforms of VRLIntegrator::preprocess (vrl.cpp:408-415) -- */
 /* VRLMap::toLong (vrl_map.h:56-62): new lengths; returns the number of VRLs that see no surface (the reference throws) */

@@ -56,6 +56,8 @@ def lib():
         L.vrlo_grid_transmittance.restype = C.c_float
         L.vrlo_photon_gather_segments.argtypes = [C.c_void_p, C.POINTER(abi.PhotonSetDesc), C.c_void_p, C.c_uint64, C.POINTER(abi.Options), f3]
         L.vrlo_surface_gather_queries.argtypes = [C.POINTER(abi.PhotonSetDesc), C.c_int32, C.POINTER(abi.PhotonSetDesc), C.c_int32, C.c_void_p, C.c_uint64, f3]
+        L.vrlo_sample_delta.argtypes = [C.c_uint32, f3, f3, f3, C.c_float, f3, f3, C.POINTER(C.c_int)]
+        L.vrlo_sample_delta.restype = C.c_int
         L.vrlo_vrls_to_long.argtypes = [C.c_void_p, f3, C.c_uint64, f3]
         L.vrlo_vrls_to_long.restype = C.c_uint64
         L.vrlo_vrls_dice.argtypes = [C.c_void_p, f3, C.POINTER(C.c_uint16), C.c_uint64, C.c_uint32, f3, C.POINTER(C.c_uint16), C.c_uint64]
@@ -174,3 +176,13 @@ def surface_gather(queries, global_desc=None, k_global=0, caustic_desc=None, k_c
                                       C.byref(caustic_desc) if caustic_desc is not None else None, k_caustic,
                                       q.ctypes.data, len(q), fp(out))
     return out
+
+
+def sample_delta(flags, prm, n, rd, sample1):
+    """(wo, weight, transmitted) of the delta BSDF sample, or None when the lobe is inactive."""
+    prm, n, rd = f32(prm), f32(n), f32(rd)
+    wo, wt = np.zeros(3, np.float32), np.zeros(3, np.float32)
+    t = C.c_int()
+    if not lib().vrlo_sample_delta(flags, fp(prm), fp(n), fp(rd), sample1, fp(wo), fp(wt), C.byref(t)):
+        return None
+    return wo, wt, bool(t.value)

@@ -431,3 +431,41 @@ def test_camera_paths_hand_their_first_smooth_surface_to_the_photon_maps(ctx):
     ctx.set_scene(scenes.box_fog_scene(occluders=True))
     ctx.build_segments(cam, opt)
     assert len(ctx.download_surface_queries()) == 0
+
+
+def test_specular_chains_on_the_camera_path_match_oracle(ctx):
+    """vrl.cpp:682-716: a camera path that meets a delta BSDF (mirror sphere, glass cuboid) is reflected / refracted with
+    bsdf->sample, multiplies its throughput and carries on through the fog: more in-medium segments per pixel, each with
+    its own query.  Segments bit-exact against the oracle's restatement, then the gather per pixel."""
+    w, h = 64, 36
+    sc = scenes.specular_fog_scene()
+    cam = scenes.box_fog_camera(w, h)
+    opt = scenes.default_options(visibility=1)
+    soa = scenes.synthetic_vrls(400, seed=3)
+    vd = scenes.vrlset_desc(soa)
+    osc = oracle.OracleScene(sc)
+    ref_segs, ref_direct, ref_aw = osc.build_segments(cam, opt, soa.shape[1], cap=w * h * 40)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(vd)
+    n = ctx.build_segments(cam, opt)
+    assert n == len(ref_segs) and n > 1.3 * w * h                         # the chains add segments
+    segs = ctx.download_segments()
+    end = lambda s: np.round((s["o"] + s["d"] * s["maxt"][:, None]).astype(np.float64).sum(1) * 1e3)
+    key = lambda s: np.lexsort((s["rng_state"], s["pixel"]))              # a pixel's segments in path order: stream position
+    a, b = segs[key(segs)], ref_segs[key(ref_segs)]
+    for f in ("pixel", "sample", "part", "medium", "rng_state", "o", "d", "maxt"):
+        assert np.array_equal(a[f], b[f]), f
+    assert np.allclose(a["weight"], b["weight"], rtol=2e-6, atol=0)
+    # tinted mirror: some segments carry an RGB-distinct throughput; the glass scales by eta^-2 / eta^2
+    assert (np.abs(a["weight"][:, 0] - a["weight"][:, 2]) > 1e-3).sum() > 100
+    per_pixel = np.bincount(segs["pixel"], minlength=w * h)
+    assert per_pixel.max() >= 3
+    li = ctx.gather_segments(opt).astype(np.float64)
+    o32, o64, ev = osc.gather(vd, segs, opt)
+    got, ref = np.zeros((w * h, 3)), np.zeros((w * h, 3))
+    np.add.at(got, segs["pixel"], li * segs["weight"])
+    np.add.at(ref, segs["pixel"], o64 * segs["weight"])
+    assert rel_err(got, ref).max() <= REL_TOL
+    # the paths still end on diffuse walls: surface queries carry the chain's throughput
+    q = ctx.download_surface_queries()
+    assert len(q) > 0.8 * w * h and (np.abs(q["weight"][:, 0] - q["weight"][:, 2]) > 1e-3).sum() > 50

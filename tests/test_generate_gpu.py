@@ -372,3 +372,41 @@ def test_global_photons_are_the_surface_hits_of_the_same_particles(ctx):
     n_v, p_v = ctx.generate_photons(gen, 500, 0.5)
     assert n_v == 500 and p_v > 3 * n_v
     assert ctx.download_photons()[3] == pytest.approx(1.0 / (p_v - 1))
+
+
+def test_light_side_specular_chain_and_caustic_photons(ctx):
+    """vrl.cpp:318-358 with SmoothDielectric::sample: a particle is refracted through a glass slab (Snell twice: the spot on
+    the far wall shifts by the slab's lateral offset), keeps its power (eta^-2 in, eta^2 out), and the photon it stores on
+    the next diffuse surface goes to the caustic map (wasTransmitted, vrl.cpp:345, 776-780); the 4 % reflected at the slab
+    end up in the global map."""
+    size, refl, power, eta = 5.0, (0.6, 0.5, 0.4), (2.0, 1.0, 0.5), 1.5
+    sc = scenes.Scene()
+    sc.add_medium(scenes.make_medium(sigma_t=(0.002,) * 3, albedo=(0.9,) * 3))
+    sc.add_tris(scenes.box_tris((-size,) * 3, (size,) * 3, inward=True), abi.SURF_BSDF_SMOOTH, reflectance=refl)
+    sc.add_tris(scenes.box_tris((-4.9, -4.9, 2.0), (4.9, 4.9, 3.0)), abi.SURF_BSDF_DIELECTRIC, reflectance=(eta, 1.0, 1.0))
+    ctx.set_scene(sc)
+    gen = scenes.generate_desc(20000, seed=8, laser=((0, 0, 0), (0.3, 0.0, 1.0), power), start_medium=0)
+    n_c, p_c = ctx.generate_surface_photons(gen, 4000, 0.4, 50, which=abi.PHOTONMAP_CAUSTIC)
+    assert n_c == 4000
+    pos, pdir, pw, scale = ctx.download_surface_photons(abi.PHOTONMAP_CAUSTIC)
+    assert scale == pytest.approx(1.0 / (p_c - 1))
+    direct = np.isclose(pw, np.array(power, np.float32)[None, :], rtol=2e-5).all(axis=1)
+    assert direct.sum() > 0.8 * 4000                                     # straight through the slab onto the z = +size wall
+    sin_i = 0.3 / math.sqrt(1.09)
+    tan_t = (sin_i / eta) / math.sqrt(1 - (sin_i / eta) ** 2)
+    x_spot = 0.3 * 2.0 + tan_t * 1.0 + 0.3 * 2.0
+    assert np.allclose(pos[direct], [[x_spot, 0.0, size]], atol=2e-3)
+    assert np.allclose(pdir[direct], np.array([[0.3, 0.0, 1.0]]) / math.sqrt(1.09), atol=1e-5)   # the exit restores the direction
+    # the global map: photons whose last surface event was not a transmission -- the slab's reflection lands on z = -size
+    n_g, p_g = ctx.generate_surface_photons(gen, 4000, 0.4, 50, which=abi.PHOTONMAP_GLOBAL)
+    gpos, gdir, gpw, _ = ctx.download_surface_photons(abi.PHOTONMAP_GLOBAL)
+    mirrored = np.isclose(gpw, np.array(power, np.float32)[None, :], rtol=2e-5).all(axis=1)
+    assert mirrored.sum() > 10 and np.allclose(gpos[mirrored][:, 2], -size, atol=1e-3)
+    assert mirrored.sum() < 0.2 * max(p_g, 1)                            # Fresnel: ~4 % at this angle (twice: both faces)
+    # no caustic photon is also a global one: full-power photons on the far wall are all in the caustic map
+    assert not (mirrored & (gpos[:, 2] > size - 1e-3)).any()
+    # VRLs: the flight continues behind the slab with the entry direction
+    ctx.generate_vrls(gen)
+    soa, _ = ctx.download_vrls()
+    behind = (soa[2] > 3.0) & np.isclose(soa[7], power[0], rtol=2e-5)
+    assert behind.sum() > 1000 and np.allclose(soa[3:6, behind].T, np.array([[0.3, 0.0, 1.0]]) / math.sqrt(1.09), atol=1e-5)

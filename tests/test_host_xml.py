@@ -150,15 +150,16 @@ def test_bsdf_reflectance_forms(host, tmp_path):
     <bsdf type="twosided" id="both"><ref id="inner"/></bsdf>
     <shape type="rectangle"><ref id="both"/></shape>
     <shape type="rectangle"><bsdf type="diffuse"><spectrum name="reflectance" value="400:0.2, 450:0.4, 500:0.6, 550:0.6, 600:0.9, 700:0.7"/></bsdf></shape>
-    <shape type="rectangle"><bsdf type="dielectric"/></shape>
+    <shape type="rectangle"><bsdf type="dielectric"><string name="int_ior" value="water"/><float name="ext_ior" value="1.0"/></bsdf></shape>
+    <shape type="rectangle"><bsdf type="conductor"><rgb name="specular_reflectance" value="0.9, 0.8, 0.7"/></bsdf></shape>
     </scene>"""
     p = os.path.join(str(tmp_path), "bsdfs.xml")
     open(p, "w").write(xml)
     rc, info, err = _info(host, p)
     assert rc == 0, err
-    assert info["triangles"] == 6 and info["reflecting_triangles"] == 4 and info["twosided_triangles"] == 2
+    assert info["triangles"] == 8 and info["reflecting_triangles"] == 4 and info["twosided_triangles"] == 2
     assert np.allclose(info["mean_reflectance"], [(0.1 + 0.8) / 2, (0.2 + 0.6) / 2, (0.3 + 0.3) / 2], rtol=1e-6)
-    assert "wavelength table" in err and "dielectric" in err
+    assert "wavelength table" in err and info["dielectric_triangles"] == 2 and info["mirror_triangles"] == 2
 
 
 def test_property_and_schema_errors(host, tmp_path):
@@ -242,11 +243,12 @@ def test_fbd15_benchmark_scenes_load(host):
     cam = scenes.make_camera(256, 256, (0, 0, -40), (0, 0, -39), fov=36, fov_axis="x", near_clip=0.1, far_clip=100)
     assert np.allclose(s["sample_to_camera"], list(cam.sample_to_camera), rtol=2e-6, atol=1e-7)
     assert np.allclose(s["to_world"], list(cam.to_world), rtol=2e-6, atol=1e-7)
-    assert "max_passes" in err and "conductor" in err
+    assert "max_passes" in err and info["mirror_triangles"] == (2 * 32 - 2) * 64       # the conductor sphere: specular chains
     rc, info, err = _info(host, os.path.join(FBD15, "glass", "glass.xml"))
     assert rc == 0, err
     assert [m["id"] for m in info["media"]] == ["grapefruitJuiceIsotropic", "absorbingGlass"]
     assert np.allclose(info["media"][0]["sigma_t"], [0.86, 1.27, 4.96], rtol=1e-6) and "envmap" in err
+    assert info["dielectric_triangles"] == info["triangles"] > 10000                     # glass, liquid surface, interface: all dielectric
 
 
 @pytest.mark.skipif(not os.path.isdir(REF_SCENES), reason="reference fixtures not mounted")

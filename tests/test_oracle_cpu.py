@@ -457,3 +457,46 @@ def test_surface_photon_estimates_closed_form():
     # both maps: the sum
     both = oracle.surface_gather(_sq(), global_desc=five, k_global=3, caustic_desc=five, k_caustic=3)[0]
     assert np.allclose(both, got + got_c, rtol=1e-6)
+
+
+def test_delta_bsdf_samples_closed_form():
+    """SmoothConductor / SmoothDielectric::sample of the specular chains (vrl.cpp:320, 682): mirror direction
+    d - 2 (d.n) n whatever the frame, Snell's law, Fresnel at normal incidence, the radiance scaling eta_ti^2, total
+    internal reflection, one-sided conductor."""
+    rng = np.random.default_rng(3)
+    for _ in range(50):
+        n = rng.normal(size=3); n /= np.linalg.norm(n)
+        d = rng.normal(size=3); d /= np.linalg.norm(d)
+        if d @ n > 0:
+            d = -d                                                       # arrive on the front side
+        wo, wt, tr = oracle.sample_delta(abi.SURF_BSDF_MIRROR, (0.9, 0.8, 0.7), n, d, 0.5)
+        assert np.allclose(wo, d - 2 * (d @ n) * n, atol=2e-6) and np.allclose(wt, (0.9, 0.8, 0.7)) and not tr
+        # the back of a one-sided conductor reflects nothing; the twosided adapter does
+        assert oracle.sample_delta(abi.SURF_BSDF_MIRROR, (0.9, 0.8, 0.7), n, -d, 0.5) is None
+        wo2, _, _ = oracle.sample_delta(abi.SURF_BSDF_MIRROR | abi.SURF_TWOSIDED, (0.9, 0.8, 0.7), n, -d, 0.5)
+        assert np.allclose(wo2, -d + 2 * (d @ n) * n, atol=2e-6)
+        # dielectric, entering (eta = 1.5): refraction obeys Snell, weight = T / eta^2; reflection weight = R
+        eta = 1.5
+        cos_i = -(d @ n)
+        wo_t, wt_t, tr_t = oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, (eta, 0.8, 0.6), n, d, 1.0)
+        assert tr_t and np.isclose(np.linalg.norm(wo_t), 1.0, atol=1e-5)
+        sin_i, sin_t = math.sqrt(max(0.0, 1 - cos_i ** 2)), np.linalg.norm(np.cross(wo_t, n))
+        assert np.isclose(sin_t, sin_i / eta, atol=1e-5) and wo_t @ n < 0
+        assert np.allclose(wt_t, 0.6 / eta ** 2, rtol=1e-6)
+        tang_in, tang_out = d - (d @ n) * n, wo_t - (wo_t @ n) * n       # same plane of incidence, same side
+        assert np.allclose(tang_out, tang_in / eta, atol=1e-5)
+        wo_r, wt_r, tr_r = oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, (eta, 0.8, 0.6), n, d, 0.0)
+        assert not tr_r and np.allclose(wo_r, d - 2 * (d @ n) * n, atol=2e-6) and np.allclose(wt_r, 0.8)
+        # leaving: weight = T * eta^2, or total internal reflection beyond the critical angle
+        wo_l, wt_l, tr_l = oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, (eta, 0.8, 0.6), n, -d, 0.999999)
+        if sin_i * eta >= 1.0:
+            assert not tr_l and np.allclose(wt_l, 0.8)
+        else:
+            assert tr_l and np.allclose(wt_l, 0.6 * eta ** 2, rtol=1e-6) and wo_l @ n > 0
+    # Fresnel reflectance at normal incidence: ((eta - 1) / (eta + 1))^2 = 0.04 for 1.5 -- the switch point of sample1
+    n, d = np.array([0, 0, 1.0]), np.array([0, 0, -1.0])
+    assert not oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, (1.5, 1, 1), n, d, 0.0399)[2]
+    assert oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, (1.5, 1, 1), n, d, 0.0401)[2]
+    # index-matched: r_i = 0, straight through with weight T (sample1 == 0 itself still satisfies `sample1 <= r_i`)
+    wo, wt, tr = oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, (1.0, 1, 0.5), n, np.array([0.6, 0, -0.8]), 1e-6)
+    assert tr and np.allclose(wo, (0.6, 0, -0.8), atol=1e-6) and np.allclose(wt, 0.5)
