@@ -11,8 +11,9 @@
 //            shapes it is interior to, nonlinear.cpp:62-89); phase isotropic / hg
 //   integrator   type "vrl": every child becomes a property of vrlhost::Properties, so the unqueried-property and
 //            wrong-type errors are those of VRLIntegrator's constructor
-// What the hot path asks of a BSDF is one bit (BSDFFlags::Null or not, vrl_struct.h:529); delta BSDFs (dielectric,
-// conductor ...) have no specular chain on this path yet: they load as occluders and are listed in `warnings`.
+// What the gather asks of a BSDF is one bit (BSDFFlags::Null or not, vrl_struct.h:529); the camera path and the light
+// tracer additionally read the diffuse reflectance, and `conductor` / `dielectric` load as the delta classes of the
+// specular chains (VRLB_SURF_BSDF_MIRROR / _DIELECTRIC).  Anything else is reduced as listed in `warnings`.
 // Scene versions before 2.0 get the reference's in-memory upgrade (xml.cpp:350-392: camelCase -> underscore_case names,
 // lookAt) and, for the 0.x scenes of data/FBD15ALVRL_scenes, the schema translation of SURVEY.md 8c (sigma_s/sigma_a ->
 // sigma_t/albedo, medium boundary without BSDF -> null BSDF, the other implementation's integrator properties dropped);
