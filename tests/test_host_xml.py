@@ -338,6 +338,29 @@ def test_render_xml_global_photon_map(host, tmp_path):
 
 
 @pytest.mark.gpu
+def test_render_xml_with_delta_bsdfs(host, tmp_path):
+    """A glass sphere and a mirror triangle in the XML: the scene renders through the specular chains (camera paths carry on
+    behind the sphere) and the plugin traces the caustic map because a dielectric is present."""
+    path = _write_scene(str(tmp_path))
+    txt = open(path).read().replace('<medium id="fog" type="nonlinear">', '<medium id="fog" type="homogeneous">')
+    open(path, "w").write(txt)
+    glass = txt.replace('<bsdf type="diffuse"/>', '<bsdf type="dielectric"><string name="int_ior" value="water"/></bsdf>')
+    assert glass != txt
+    p2 = os.path.join(str(tmp_path), "glass.xml")
+    open(p2, "w").write(glass)
+    films = []
+    for p in (path, p2):
+        out = p + ".f32"
+        r = subprocess.run([host, "render-xml", p, out, "-Dspp=1", "global_photons=20000", "caustic_photons=2000"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert ("caustic" in r.stderr) == (p == p2), r.stderr
+        films.append(np.fromfile(out, np.float32).reshape(48, 64, 5))
+    a, b = films
+    assert np.isfinite(b).all() and (b[..., :3] >= 0).all() and b[..., 1].mean() > 0
+    assert (np.abs(a[..., 1] - b[..., 1]) > 1e-6).sum() > 20             # the pixels that see the sphere changed
+
+
+@pytest.mark.gpu
 def test_render_xml_direct_term_switch(host, tmp_path):
     """use_direct_illum (default true, vrl.cpp:57): the plugin builds the volume photon map from the same light tracing and
     adds the direct in-scattering term; with use_direct_illum=false the film holds the VRL term only and is darker."""
