@@ -1256,7 +1256,10 @@ inline V3 nl_bend(const vrlb_medium &m, V3 p, V3 dir, float ds) {
 /* What one camera sample hands to the VRL query */
 struct PartOut { Ray ray; V3 weight; int medium; uint32_t part; const Ray *all = nullptr; int n_all = 0; };   /* n_all > 0: one query over the whole NLRay (use_nl_atomic_query) */
 
-struct SampleResult { V3 radiance; bool valid_ray; };
+struct SampleResult { V3 radiance; bool valid_ray; bool has_sq = false; vrlb_surface_query sq{}; };
+
+/* test hook: where vrlo_build_surface_queries collects the surface queries of the paths render_pixel traces */
+thread_local std::vector<vrlb_surface_query> *g_surface_queries = nullptr;
 
 /* VRLIntegrator::sample, src/integrators/vrl/vrl.cpp:443-732, for the surface classes of the
  * ABI (null / smooth / emitter).  Photon-map terms (vrl.cpp:600-611, 671-680) are SURVEY 8f rank 3
@@ -1267,6 +1270,7 @@ template <typename OnQuery>
 SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler &sampler, V3 ro, V3 rd,
                           float rmint, float rmaxt, int sensor_medium, OnQuery &&on_query) {
     V3 radiance(0.f), throughput(1.f);
+    bool has_sq = false; vrlb_surface_query sq{};
     int medium = sensor_medium;
     Hit si{ kInf, 0, 0, -1 };
     bool valid_ray = false;                         /* no environment emitter in the ABI */
@@ -1366,7 +1370,18 @@ SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler 
             const Tri &tr = s.tris[(size_t) si.prim];
             if (tr.flags & VRLB_SURF_EMITTER) break;            /* vrl.cpp:664-665 */
             valid_ray = true;
-            if ((tr.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_SMOOTH) break;   /* smooth BSDF: photon-map estimates, then break (vrl.cpp:671-680) */
+            if ((tr.flags & VRLB_SURF_BSDF_MASK) == VRLB_SURF_BSDF_SMOOTH) {        /* smooth BSDF: photon-map estimates, then break (vrl.cpp:671-680) */
+                if (tr.prm[0] != 0.f || tr.prm[1] != 0.f || tr.prm[2] != 0.f) {     /* what the estimates read of si and the path */
+                    const V3 p = tri_point(tr, si.u, si.v), n = tri_normal(tr);
+                    sq.p[0] = p.x; sq.p[1] = p.y; sq.p[2] = p.z; sq.n[0] = n.x; sq.n[1] = n.y; sq.n[2] = n.z;
+                    sq.flags = tr.flags & VRLB_SURF_TWOSIDED;
+                    sq.wi[0] = -rd.x; sq.wi[1] = -rd.y; sq.wi[2] = -rd.z;
+                    for (int k = 0; k < 3; ++k) sq.reflectance[k] = tr.prm[k];
+                    sq.weight[0] = throughput.x; sq.weight[1] = throughput.y; sq.weight[2] = throughput.z;
+                    has_sq = true;
+                }
+                break;
+            }
             /* bsdf->sample consumes next_1d + next_2d (vrl.cpp:682).  Null::sample (null.cpp:38-52): weight 1, wo = -wi */
             const float sample1 = sampler.next_1d(); (void) sampler.next_1d(); (void) sampler.next_1d();
             if (!is_null(tr)) {
@@ -1390,7 +1405,9 @@ SampleResult trace_sample(const vrlo_scene &s, const vrlb_options &opt, Sampler 
         }
         if (!(active_surface || active_medium)) break;          /* vrl.cpp:719 */
     }
-    return SampleResult{ radiance, valid_ray };
+    SampleResult res{ radiance, valid_ray };
+    res.has_sq = has_sq; res.sq = sq;
+    return res;
 }
 
 /* srgb_to_xyz, include/mitsuba/core/spectrum.h:221-227 */
@@ -1423,8 +1440,10 @@ void render_pixel(const vrlo_scene &s, const vrlb_camera &cam, const vrlb_option
         SampleResult r = trace_sample(s, opt, sampler, o, d, mint, maxt, cam.medium, q);
         /* ImageBlock::put, box filter branch (imageblock.cpp:162-169): pixel = ceil(pos - 1) inside the block */
         int fx = (int) std::ceil(posx - (float) bx0 - 1.0f), fy = (int) std::ceil(posy - (float) by0 - 1.0f);
-        if (fx >= 0 && fy >= 0 && fx < bw && fy < bh)
+        if (fx >= 0 && fy >= 0 && fx < bw && fy < bh) {
             put(bx0 + fx, by0 + fy, r.radiance, r.valid_ray ? 1.f : 0.f);
+            if (r.has_sq && g_surface_queries) { r.sq.pixel = (uint32_t) ((by0 + fy) * cam.width + bx0 + fx); g_surface_queries->push_back(r.sq); }
+        }
     }
 }
 
@@ -1502,6 +1521,18 @@ uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const 
         }
     }
     return n;
+}
+
+/* The surface queries of the camera paths (one per path that ends on a smooth surface with a non-zero reflectance), in the
+ * order vrlo_build_segments walks the film; returns the count (may exceed cap). */
+uint64_t vrlo_build_surface_queries(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt, uint64_t n_vrls_total,
+                                    vrlb_surface_query *out, uint64_t cap) {
+    std::vector<vrlb_surface_query> found;
+    g_surface_queries = &found;
+    vrlo_build_segments(s, cam, opt, n_vrls_total, VRLO_RNG_ADDRESSED, nullptr, 0, nullptr, nullptr);
+    g_surface_queries = nullptr;
+    for (uint64_t i = 0; i < std::min<uint64_t>(cap, found.size()); ++i) out[i] = found[i];
+    return found.size();
 }
 
 uint64_t vrlo_render(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt,

@@ -73,6 +73,9 @@ void vrlo_surface_gather_queries(const vrlb_photonset_desc *global, int32_t k_gl
                                  const vrlb_surface_query *queries, uint64_t n, float *out_rgb);
 /* SmoothConductor / SmoothDielectric::sample as the specular chains call it (vrl.cpp:320, 682); 0 = inactive lobe */
 int vrlo_sample_delta(uint32_t flags, const float prm[3], const float n[3], const float rd[3], float sample1, float wo[3], float weight[3], int *transmitted);
+/* surface queries of the camera paths (vrl.cpp:671-680), film order of vrlo_build_segments; returns the count */
+uint64_t vrlo_build_surface_queries(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt, uint64_t n_vrls_total,
+                                    vrlb_surface_query *out, uint64_t cap);
 
 /* -- VRL-set transforms of VRLIntegrator::preprocess (vrl.cpp:408-415) -- */
 /* VRLMap::toLong (vrl_map.h:56-62): new lengths; returns the number of VRLs that see no surface (the reference throws) */

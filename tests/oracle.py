@@ -56,6 +56,8 @@ def lib():
         L.vrlo_grid_transmittance.restype = C.c_float
         L.vrlo_photon_gather_segments.argtypes = [C.c_void_p, C.POINTER(abi.PhotonSetDesc), C.c_void_p, C.c_uint64, C.POINTER(abi.Options), f3]
         L.vrlo_surface_gather_queries.argtypes = [C.POINTER(abi.PhotonSetDesc), C.c_int32, C.POINTER(abi.PhotonSetDesc), C.c_int32, C.c_void_p, C.c_uint64, f3]
+        L.vrlo_build_surface_queries.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.c_uint64, C.c_void_p, C.c_uint64]
+        L.vrlo_build_surface_queries.restype = C.c_uint64
         L.vrlo_sample_delta.argtypes = [C.c_uint32, f3, f3, f3, C.c_float, f3, f3, C.POINTER(C.c_int)]
         L.vrlo_sample_delta.restype = C.c_int
         L.vrlo_vrls_to_long.argtypes = [C.c_void_p, f3, C.c_uint64, f3]
@@ -112,6 +114,13 @@ class OracleScene:
     def grid_transmittance(self, o, d, maxt, seed, medium=0):
         o, d = f32(o), f32(d)
         return lib().vrlo_grid_transmittance(self.h, medium, fp(o), fp(d), maxt, seed)
+
+    def build_surface_queries(self, cam, opt, n_vrls_total):
+        """Surface queries of the camera paths (vrl.cpp:671-680)."""
+        cap = cam.width * cam.height * max(opt.spp, 1)
+        q = np.zeros(cap, abi.SURFACE_QUERY_DTYPE)
+        n = lib().vrlo_build_surface_queries(self.h, C.byref(cam), C.byref(opt), n_vrls_total, q.ctypes.data, cap)
+        return q[:n]
 
     def photon_gather(self, photon_desc, segs, opt):
         """Direct in-scattering term per segment (vrl.cpp:523-611), throughput included."""

@@ -382,6 +382,16 @@ def test_surface_photon_estimates_match_oracle(ctx, radius, k):
     ctx.upload_surface_queries(q[:0], w, h)                              # leave no queries behind for the other tests
 
 
+def _same_queries(got, ref):
+    """GPU surface queries against the oracle's: one per pixel at spp 1, same IEEE operations -> position, normal,
+    direction bit-exact; the throughput is a product of exp() (CUDA expf vs glibc: ulps)."""
+    assert len(got) == len(ref)
+    a, b = got[np.argsort(got["pixel"])], ref[np.argsort(ref["pixel"])]
+    for f in ("pixel", "flags", "p", "n", "wi", "reflectance"):
+        assert np.array_equal(a[f], b[f]), f
+    assert np.allclose(a["weight"], b["weight"], rtol=2e-6, atol=0)
+
+
 def test_camera_paths_hand_their_first_smooth_surface_to_the_photon_maps(ctx):
     """vrl.cpp:671-680: where a camera path ends on a smooth surface, radiance += (caustic + global estimate) * throughput.
     vrlb_segments_build writes one surface query per such path (position, normal, -ray.d, reflectance, throughput) when the
@@ -401,6 +411,7 @@ def test_camera_paths_hand_their_first_smooth_surface_to_the_photon_maps(ctx):
     end = segs["o"] + segs["d"] * segs["maxt"][:, None]
     on_wall = np.abs(end).max(axis=1) > scenes.BOX - 1e-3
     assert set(segs["pixel"][on_wall]) == set(q["pixel"])
+    _same_queries(q, oracle.OracleScene(sc).build_surface_queries(cam, opt, 200))
     p = q["p"].astype(np.float64)
     assert np.allclose(np.abs(p).max(axis=1), scenes.BOX, atol=1e-3)
     assert np.allclose(q["reflectance"], np.array(refl, np.float32)[None, :]) and np.all(q["flags"] == 0)
@@ -466,6 +477,7 @@ def test_specular_chains_on_the_camera_path_match_oracle(ctx):
     np.add.at(got, segs["pixel"], li * segs["weight"])
     np.add.at(ref, segs["pixel"], o64 * segs["weight"])
     assert rel_err(got, ref).max() <= REL_TOL
-    # the paths still end on diffuse walls: surface queries carry the chain's throughput
+    # the paths still end on diffuse walls: surface queries carry the chain's throughput; bit-exact against the oracle's
     q = ctx.download_surface_queries()
     assert len(q) > 0.8 * w * h and (np.abs(q["weight"][:, 0] - q["weight"][:, 2]) > 1e-3).sum() > 50
+    _same_queries(q, osc.build_surface_queries(cam, opt, soa.shape[1]))
