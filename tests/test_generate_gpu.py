@@ -398,9 +398,9 @@ def test_light_side_specular_chain_and_caustic_photons(ctx):
     sin_i = 0.3 / math.sqrt(1.09)
     tan_t = (sin_i / eta) / math.sqrt(1 - (sin_i / eta) ** 2)
     x_spot = 0.3 * 2.0 + tan_t * 1.0 + 0.3 * 2.0
-    # (a fraction of a percent keeps its full power through two internal reflections and lands elsewhere)
-    assert (np.abs(pos[direct] - np.array([[x_spot, 0.0, size]])).max(axis=1) < 2e-3).mean() > 0.98
-    assert (np.abs(pdir[direct] - np.array([[0.3, 0.0, 1.0]]) / math.sqrt(1.09)).max(axis=1) < 1e-5).mean() > 0.98   # the exit restores the direction
+    # (the 4 % reflected inside the slab leave through its lower face with their full power: caustic photons on z = -size)
+    assert (np.abs(pos[direct] - np.array([[x_spot, 0.0, size]])).max(axis=1) < 2e-3).mean() > 0.9
+    assert (np.abs(pdir[direct] - np.array([[0.3, 0.0, 1.0]]) / math.sqrt(1.09)).max(axis=1) < 1e-5).mean() > 0.9   # the exit restores the direction
     # the global map: photons whose last surface event was not a transmission -- the slab's reflection lands on z = -size
     n_g, p_g = ctx.generate_surface_photons(gen, 4000, 0.4, 50, which=abi.PHOTONMAP_GLOBAL)
     gpos, gdir, gpw, _ = ctx.download_surface_photons(abi.PHOTONMAP_GLOBAL)
@@ -414,4 +414,4 @@ def test_light_side_specular_chain_and_caustic_photons(ctx):
     soa, _ = ctx.download_vrls()
     behind = (soa[2] > 3.0) & np.isclose(soa[7], power[0], rtol=2e-5)
     assert behind.sum() > 1000
-    assert (np.abs(soa[3:6, behind].T - np.array([[0.3, 0.0, 1.0]]) / math.sqrt(1.09)).max(axis=1) < 1e-5).mean() > 0.98
+    assert (np.abs(soa[3:6, behind].T - np.array([[0.3, 0.0, 1.0]]) / math.sqrt(1.09)).max(axis=1) < 1e-5).mean() > 0.9
