@@ -21,6 +21,12 @@ def main():
         with open(os.path.join(GOLD, "ref_vrl_struct.json"), "w") as f:
             json.dump(data, f)
         print("wrote ref_vrl_struct.json:", {k: (len(v) if hasattr(v, "__len__") else v) for k, v in data.items()})
+    probe = os.path.join(HERE, "_ref", "refprobe_pm")
+    if os.path.exists(probe):
+        data = json.loads(subprocess.check_output([probe]))
+        with open(os.path.join(GOLD, "ref_photonmap.json"), "w") as f:
+            json.dump(data, f)
+        print("wrote ref_photonmap.json:", {k: (len(v) if hasattr(v, "__len__") else v) for k, v in data.items()})
 
 if __name__ == "__main__":
     sys.exit(main())

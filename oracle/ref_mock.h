@@ -69,6 +69,7 @@ inline std::ostream &operator<<(std::ostream &os, const MockRay &r) { return os 
 
 struct MockFrame {
     MockVec3 s, t, n;
+    MockFrame() : s(1, 0, 0), t(0, 1, 0), n(0, 0, 1) {}
     explicit MockFrame(const MockVec3 &n_) : n(n_) {
         /* any orthonormal completion: evalTransmittance only feeds wo to a BSDF eval that the
            mock answers with 0 (Null::eval) or never reaches */
@@ -81,25 +82,39 @@ struct MockFrame {
 enum class BSDFFlags : uint32_t { None = 0, Null = 0x1, DiffuseReflection = 0x2 };
 inline bool has_flag(uint32_t flags, BSDFFlags f) { return (flags & (uint32_t) f) != 0; }
 enum class TransportMode { Radiance, Importance };
-struct MockBSDFContext { MockBSDFContext(TransportMode, uint32_t, int) {} };
+struct MockBSDFContext { MockBSDFContext(TransportMode, uint32_t, int) {} explicit MockBSDFContext(TransportMode) {} };
 
 struct MockMedium;
 struct MockSI;
 struct MockBSDF {
     uint32_t m_flags = (uint32_t) BSDFFlags::DiffuseReflection;
+    /* diffuse = false: what evalTransmittance meets (Null::eval = 0, or a value never read).  diffuse = true:
+       SmoothDiffuse::eval (src/bsdfs/diffuse.cpp), for the photon-map probe */
+    bool diffuse = false;
+    MockVec3 reflectance = MockVec3(0.5f);
     uint32_t flags() const { return m_flags; }
-    MockVec3 eval(const MockBSDFContext &, const MockSI &, const MockVec3 &) const { return MockVec3(0.f); }
+    inline MockVec3 eval(const MockBSDFContext &, const MockSI &si, const MockVec3 &wo) const;
 };
 struct MockSI {
     float t = math::Infinity<float>;
     MockVec3 p, n;
+    MockVec3 wi = MockVec3(0.f, 0.f, 1.f);      /* local */
+    MockFrame sh_frame;
     MockVec2 duv_dx, duv_dy;
     const MockBSDF *m_bsdf = nullptr;
+    MockVec3 to_local(const MockVec3 &v) const { return sh_frame.to_local(v); }
+    MockVec3 to_world_mueller(const MockVec3 &value, const MockVec3 &, const MockVec3 &) const { return value; }
     bool is_valid() const { return t != math::Infinity<float>; }
     const MockBSDF *bsdf() const { return m_bsdf; }
     bool is_medium_transition() const { return false; }
     const MockMedium *target_medium(const MockVec3 &) const { return nullptr; }
 };
+inline MockVec3 MockBSDF::eval(const MockBSDFContext &, const MockSI &si, const MockVec3 &wo) const {
+    if (!diffuse) return MockVec3(0.f);
+    float cos_theta_i = si.wi.z(), cos_theta_o = wo.z();
+    bool active = cos_theta_i > 0.f && cos_theta_o > 0.f;
+    return active ? reflectance * (0.31830988618379067154f * cos_theta_o) : MockVec3(0.f);
+}
 struct MockMI {
     MockVec3 p, wi;
     float t = 0.f;
@@ -172,9 +187,18 @@ struct MockScene {
 };
 } // namespace mitsuba
 
+/* REF_MOCK_MSVC_TYPENAME: photonmapper/kdtree.h writes `typedef typename Point3f PointType;` (accepted by MSVC only).
+   With Point3f / Vector3f as macros for a qualified name the line is standard C++; the aliases are then left out here. */
+#ifdef REF_MOCK_MSVC_TYPENAME
+#define Point3f ::mitsuba::MockVec3
+#define Vector3f ::mitsuba::MockVec3
+#define REF_MOCK_POINT_ALIASES
+#else
+#define REF_MOCK_POINT_ALIASES using Point3f = mitsuba::MockVec3; using Vector3f = mitsuba::MockVec3;
+#endif
 #define MTS_IMPORT_TYPES(...)                                                                      \
     using Mask = bool; using UInt32 = uint32_t; using Int32 = int32_t;                             \
-    using Point3f = mitsuba::MockVec3; using Vector3f = mitsuba::MockVec3;                         \
+    REF_MOCK_POINT_ALIASES                                                                         \
     using Normal3f = mitsuba::MockVec3; using Ray3f = mitsuba::MockRay;                            \
     using Frame3f = mitsuba::MockFrame; using UnpolarizedSpectrum = mitsuba::MockVec3;             \
     using SurfaceInteraction3f = mitsuba::MockSI; using MediumInteraction3f = mitsuba::MockMI;     \

@@ -974,6 +974,27 @@ float vrlo_grid_transmittance(const vrlo_scene *s, int medium, const float o[3],
  * from the previous gather point (homoEvalTransmittance, medium.h:103-107), PhotonMap::estimateRadianceVolume with the
  * RadianceQueryVolume functor (photonmap.h:216-271) -- here a plain loop over the photon set, the reference's kd-tree
  * only changes the visiting order -- and the map's scale factor (vrl.cpp:610). */
+/* PhotonMap::estimateRadianceVolume with the RadianceQueryVolume functor (photonmap.h:216-271): a plain loop over the
+ * photon set, the reference's kd-tree range query only changes the visiting order */
+static V3 estimate_radiance_volume(const vrlb_medium &m, const vrlb_photonset_desc &set, V3 gp, V3 wo, float radius) {
+    V3 result(0.f);
+    const float radiusSqr = radius * radius;
+    for (uint64_t q = 0; q < set.n; ++q) {
+        const V3 pp(set.pos + q * 3), pd(set.dir + q * 3), pw(set.power + q * 3);
+        const float lengthSqr = squared_norm(gp - pp);
+        if ((radiusSqr - lengthSqr) < 0) continue;
+        const float photonPF = phase_eval(m, -pd, wo);
+        const float q1 = 1.0f - lengthSqr / radiusSqr;
+        result = result + pw * photonPF * (q1 * q1) / radiusSqr * 0.31830988618379067154f * 3.0f;
+    }
+    return result;
+}
+/* probe (tests/test_ref_golden_cpu.py): one estimateRadianceVolume call */
+void vrlo_estimate_radiance_volume(const vrlb_medium *m, const vrlb_photonset_desc *set, const float gp[3], const float wo[3], float radius, float out[3]) {
+    const V3 r = estimate_radiance_volume(*m, *set, V3(gp), V3(wo), radius);
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+
 void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc *set, const vrlb_segment *segs, uint64_t n_segs,
                                  const vrlb_options *opt, float *out_rgb) {
     (void) opt;
@@ -1005,16 +1026,7 @@ void vrlo_photon_gather_segments(const vrlo_scene *s, const vrlb_photonset_desc 
                 stepSize = radius * 2;
                 const float val = std::exp(md * -norm(gp - last));
                 tr = tr * (md != 0.f ? val : 1.0f);
-                V3 result(0.f);
-                const float radiusSqr = radius * radius;
-                for (uint64_t q = 0; q < set->n; ++q) {
-                    const V3 pp(set->pos + q * 3), pd(set->dir + q * 3), pw(set->power + q * 3);
-                    const float lengthSqr = squared_norm(gp - pp);
-                    if ((radiusSqr - lengthSqr) < 0) continue;
-                    const float photonPF = phase_eval(m, -pd, d0);
-                    const float q1 = 1.0f - lengthSqr / radiusSqr;
-                    result = result + pw * photonPF * (q1 * q1) / radiusSqr * 0.31830988618379067154f * 3.0f;
-                }
+                const V3 result = estimate_radiance_volume(m, *set, gp, d0, radius);
                 direct = direct + tr * result;
                 last = gp;
             }

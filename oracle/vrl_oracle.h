@@ -10,9 +10,11 @@
  * for findClosetPoint / samplingVRL / evalTransmittance / getContrib / sequential-stream query sums are the
  * fixture tests/golden/ref_vrl_struct.json, which tests/test_ref_golden_cpu.py holds this file to (closest
  * point bit-exact, getContrib within 3.5e-7).  The PCG32 stream is pinned by tests/golden/enoki_pcg32.json
- * (Enoki's random.h compiled into oracle/_ref/enoki_probe).  "Parity unpinned" still applies to the grid-medium
- * stochastic transmittance, the camera-segment construction and VRL generation: no reference code could be
- * run for those.
+ * (Enoki's random.h compiled into oracle/_ref/enoki_probe).  The photon-map estimates (estimateRadiance,
+ * estimateCausticRadiance, estimateRadianceVolume) are pinned the same way: photonmapper/photonmap.h + kdtree.h
+ * compiled in place (oracle/ref_probe_pm.cpp -> tests/golden/ref_photonmap.json), agreement 2e-7.  "Parity unpinned"
+ * still applies to the grid-medium stochastic transmittance, the camera-segment construction, the delta BSDF samples
+ * and VRL generation: no reference code could be run for those.
  *
  * Input structs are the public ABI PODs of include/vrl_b200.h (interface only).
  */
@@ -73,6 +75,8 @@ void vrlo_surface_gather_queries(const vrlb_photonset_desc *global, int32_t k_gl
                                  const vrlb_surface_query *queries, uint64_t n, float *out_rgb);
 /* SmoothConductor / SmoothDielectric::sample as the specular chains call it (vrl.cpp:320, 682); 0 = inactive lobe */
 int vrlo_sample_delta(uint32_t flags, const float prm[3], const float n[3], const float rd[3], float sample1, float wo[3], float weight[3], int *transmitted);
+/* PhotonMap::estimateRadianceVolume (photonmap.h:216-271) at one gather point */
+void vrlo_estimate_radiance_volume(const vrlb_medium *m, const vrlb_photonset_desc *set, const float gp[3], const float wo[3], float radius, float out[3]);
 /* surface queries of the camera paths (vrl.cpp:671-680), film order of vrlo_build_segments; returns the count */
 uint64_t vrlo_build_surface_queries(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt, uint64_t n_vrls_total,
                                     vrlb_surface_query *out, uint64_t cap);

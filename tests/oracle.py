@@ -58,6 +58,7 @@ def lib():
         L.vrlo_surface_gather_queries.argtypes = [C.POINTER(abi.PhotonSetDesc), C.c_int32, C.POINTER(abi.PhotonSetDesc), C.c_int32, C.c_void_p, C.c_uint64, f3]
         L.vrlo_build_surface_queries.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.c_uint64, C.c_void_p, C.c_uint64]
         L.vrlo_build_surface_queries.restype = C.c_uint64
+        L.vrlo_estimate_radiance_volume.argtypes = [C.POINTER(abi.Medium), C.POINTER(abi.PhotonSetDesc), f3, f3, C.c_float, f3]
         L.vrlo_sample_delta.argtypes = [C.c_uint32, f3, f3, f3, C.c_float, f3, f3, C.POINTER(C.c_int)]
         L.vrlo_sample_delta.restype = C.c_int
         L.vrlo_vrls_to_long.argtypes = [C.c_void_p, f3, C.c_uint64, f3]
@@ -195,3 +196,11 @@ def sample_delta(flags, prm, n, rd, sample1):
     if not lib().vrlo_sample_delta(flags, fp(prm), fp(n), fp(rd), sample1, fp(wo), fp(wt), C.byref(t)):
         return None
     return wo, wt, bool(t.value)
+
+
+def estimate_radiance_volume(medium, photon_desc, gp, wo, radius):
+    """PhotonMap::estimateRadianceVolume at one gather point (photonmap.h:216-271)."""
+    gp, wo = f32(gp), f32(wo)
+    out = np.zeros(3, np.float32)
+    lib().vrlo_estimate_radiance_volume(C.byref(medium), C.byref(photon_desc), fp(gp), fp(wo), radius, fp(out))
+    return out

@@ -9,6 +9,9 @@ reference's vendored Enoki; generator oracle/ref_probe.cpp + oracle/make_golden.
   contrib        VRL::getContrib           vrl_struct.h:584-662
   query          getContrib summed over a VRL list on one sequential stream (vrl_map.h:151-169)
 
+tests/golden/ref_photonmap.json comes from oracle/_ref/refprobe_pm = the reference's photonmapper/photonmap.h + kdtree.h
+compiled the same way (oracle/ref_probe_pm.cpp): estimateRadiance / estimateCausticRadiance / estimateRadianceVolume.
+
 Tolerances: findClosetPoint is pure +,*,/ in the same order -> bit-exact.  Everything that goes through
 log/sinh/atan/tan/exp is compared at 2e-5 relative: the reference evaluates Enoki's polynomial approximations,
 the oracle glibc's correctly-rounded-ish libm, and the inverse CDFs amplify an ulp of difference (the north-star
@@ -181,3 +184,56 @@ def test_to_long_matches_reference(gold):
     got, missed = oracle.OracleScene(sc).vrls_to_long(src)
     assert missed == 0
     assert _close(got, np.array(gold["long"], np.float32), rtol=2e-6)
+
+
+# ---- the reference's photon map (photonmapper/photonmap.h + kdtree.h compiled in place, oracle/ref_probe_pm.cpp) ----
+PM_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_photonmap.json")
+
+
+@pytest.fixture(scope="module")
+def pm_gold():
+    with open(PM_GOLD) as f:
+        return json.load(f)
+
+
+def _rel(got, want):
+    want = np.asarray(want, np.float64)
+    scale = np.abs(want).max()
+    return np.abs(np.asarray(got, np.float64) - want).max() / scale if scale > 0 else np.abs(got).max()
+
+
+def test_surface_estimates_match_reference_compiled_photonmap(pm_gold):
+    """PhotonMap::estimateRadiance / estimateCausticRadiance over the reference's own PointKDTree::build + nnSearch, on
+    1500 photons and 120 queries (k nearest with the radius shrunk to the k-th, not shrunk, k = 2; arbitrary surface
+    normals; photons and camera on either side).  Same fp32 arithmetic, only the summation order differs: 2e-6."""
+    ph = np.array(pm_gold["surface_photons"], np.float32)
+    every = pm_gold["caustic_every"]
+    n_lit = n_shrunk = 0
+    for c in pm_gold["surface"]:
+        q = np.zeros(1, abi.SURFACE_QUERY_DTYPE)
+        q["p"], q["n"], q["wi"], q["reflectance"], q["weight"] = c["p"], c["n"], c["wi"], c["reflectance"], 1.0
+        g = scenes.photonset_desc(ph[:, 0], ph[:, 1], ph[:, 2], scale=pm_gold["global_scale"], lookup_radius=c["radius"])
+        got = oracle.surface_gather(q, global_desc=g, k_global=c["k"])[0]
+        assert _rel(got, c["global"]) <= 2e-6, c
+        cs = ph[::every]
+        cd = scenes.photonset_desc(cs[:, 0], cs[:, 1], cs[:, 2], scale=pm_gold["caustic_scale"],
+                                   lookup_radius=float(np.float32(0.8) * np.float32(c["radius"])))
+        got_c = oracle.surface_gather(q, caustic_desc=cd, k_caustic=c["k"])[0]
+        assert _rel(got_c, c["caustic"]) <= 2e-6, c
+        n_lit += max(c["global"]) > 0
+        d2 = ((ph[:, 0] - np.array(c["p"], np.float32)) ** 2).sum(1)
+        n_shrunk += (d2 < np.float32(c["radius"]) ** 2).sum() > c["k"]
+    assert n_lit >= 30 and 40 <= n_shrunk <= 100          # lit and unlit sides, shrunk and unshrunk radii all occur
+
+
+def test_volume_estimate_matches_reference_compiled_photonmap(pm_gold):
+    """PhotonMap::estimateRadianceVolume over the reference's PointKDTree::executeQuery, isotropic and HG (g = 0.6)."""
+    vp = np.array(pm_gold["volume_photons"], np.float32)
+    seen = 0
+    for c in pm_gold["volume"]:
+        med = scenes.make_medium(sigma_t=(1, 1, 1), albedo=(0.5,) * 3, phase=abi.PHASE_HG if c["hg"] else abi.PHASE_ISOTROPIC, g=pm_gold["hg_g"])
+        pd = scenes.photonset_desc(vp[:, 0], vp[:, 1], vp[:, 2], scale=1.0, lookup_radius=c["radius"])
+        got = oracle.estimate_radiance_volume(med, pd, c["p"], c["wo"], c["radius"])
+        assert _rel(got, c["out"]) <= 2e-6, c
+        seen += c["M"] > 0
+    assert seen >= 40
