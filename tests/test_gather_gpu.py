@@ -481,3 +481,35 @@ def test_specular_chains_on_the_camera_path_match_oracle(ctx):
     q = ctx.download_surface_queries()
     assert len(q) > 0.8 * w * h and (np.abs(q["weight"][:, 0] - q["weight"][:, 2]) > 1e-3).sum() > 50
     _same_queries(q, osc.build_surface_queries(cam, opt, soa.shape[1]))
+
+
+def test_surface_estimates_match_reference_compiled_photonmap(ctx):
+    """The CUDA surface estimates through the C ABI against outputs of the REFERENCE'S OWN PhotonMap (photonmap.h + kdtree.h
+    compiled in place, tests/golden/ref_photonmap.json): global and caustic estimates of 120 queries, three (radius, k)."""
+    import json
+    import os
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_photonmap.json")))
+    ph = np.array(gold["surface_photons"], np.float32)
+    cs = ph[::gold["caustic_every"]]
+    cases = {}
+    for c in gold["surface"]:
+        cases.setdefault((c["radius"], c["k"]), []).append(c)
+    assert len(cases) == 3
+    for (radius, k), cs_ in cases.items():
+        q = np.zeros(len(cs_), abi.SURFACE_QUERY_DTYPE)
+        for i, c in enumerate(cs_):
+            q["p"][i], q["n"][i], q["wi"][i], q["reflectance"][i] = c["p"], c["n"], c["wi"], c["reflectance"]
+        q["weight"] = 1.0
+        ctx.upload_surface_queries(q, 4, 4)
+        want_g = np.array([c["global"] for c in cs_], np.float64)
+        want_c = np.array([c["caustic"] for c in cs_], np.float64)
+        g = scenes.photonset_desc(ph[:, 0], ph[:, 1], ph[:, 2], scale=gold["global_scale"], lookup_radius=radius)
+        cd = scenes.photonset_desc(cs[:, 0], cs[:, 1], cs[:, 2], scale=gold["caustic_scale"], lookup_radius=float(np.float32(0.8) * np.float32(radius)))
+        ctx.upload_surface_photons(abi.PHOTONMAP_GLOBAL, g, k)
+        ctx.clear_surface_photons(abi.PHOTONMAP_CAUSTIC)
+        assert rel_err(ctx.surface_gather_queries().astype(np.float64), want_g).max() <= 2e-5
+        ctx.clear_surface_photons(abi.PHOTONMAP_GLOBAL)
+        ctx.upload_surface_photons(abi.PHOTONMAP_CAUSTIC, cd, k)
+        assert rel_err(ctx.surface_gather_queries().astype(np.float64), want_c).max() <= 2e-5
+    ctx.clear_surface_photons(abi.PHOTONMAP_CAUSTIC)
+    ctx.upload_surface_queries(q[:0], 4, 4)
