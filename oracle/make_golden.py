@@ -27,6 +27,12 @@ def main():
         with open(os.path.join(GOLD, "ref_photonmap.json"), "w") as f:
             json.dump(data, f)
         print("wrote ref_photonmap.json:", {k: (len(v) if hasattr(v, "__len__") else v) for k, v in data.items()})
+    probe = os.path.join(HERE, "_ref", "refprobe_fresnel")
+    if os.path.exists(probe):
+        data = json.loads(subprocess.check_output([probe]))
+        with open(os.path.join(GOLD, "ref_fresnel.json"), "w") as f:
+            json.dump(data, f)
+        print("wrote ref_fresnel.json:", {k: len(v) for k, v in data.items()})
 
 if __name__ == "__main__":
     sys.exit(main())

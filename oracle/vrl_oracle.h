@@ -13,8 +13,9 @@
  * (Enoki's random.h compiled into oracle/_ref/enoki_probe).  The photon-map estimates (estimateRadiance,
  * estimateCausticRadiance, estimateRadianceVolume) are pinned the same way: photonmapper/photonmap.h + kdtree.h
  * compiled in place (oracle/ref_probe_pm.cpp -> tests/golden/ref_photonmap.json), agreement 2e-7.  "Parity unpinned"
- * still applies to the grid-medium stochastic transmittance, the camera-segment construction, the delta BSDF samples
- * and VRL generation: no reference code could be run for those.
+ * still applies to the grid-medium stochastic transmittance, the camera-segment construction and VRL generation: no
+ * reference code could be run for those (the delta BSDF samples inside them are pinned bit-exact through the reference's
+ * fresnel.h, oracle/ref_probe_fresnel.cpp).
  *
  * Input structs are the public ABI PODs of include/vrl_b200.h (interface only).
  */

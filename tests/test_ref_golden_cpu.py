@@ -237,3 +237,31 @@ def test_volume_estimate_matches_reference_compiled_photonmap(pm_gold):
         assert _rel(got, c["out"]) <= 2e-6, c
         seen += c["M"] > 0
     assert seen >= 40
+
+
+def test_delta_bsdf_samples_match_reference_compiled_fresnel():
+    """include/mitsuba/render/fresnel.h compiled in place (oracle/ref_probe_fresnel.cpp -> tests/golden/ref_fresnel.json):
+    fresnel(), reflect(), refract() as SmoothDielectric::sample calls them, 300 directions x 5 indices (both sides, normal
+    and grazing incidence, total internal reflection, index-matched).  The oracle's sample_delta reproduces them BIT-EXACT:
+    the reflect / refract decision flips between r and the next float above it, the directions and the eta_ti^2 radiance
+    scaling are identical.  The default conductor's Fresnel term (eta = 0, k = 1) is exactly 1 at every angle, which is
+    what the surface word's MIRROR class assumes."""
+    with open(os.path.join(os.path.dirname(GOLD), "ref_fresnel.json")) as f:
+        gold = json.load(f)
+    n_r = n_t = n_tir = 0
+    for c in gold["dielectric"]:
+        wi, r = np.array(c["wi"], np.float32), np.float32(c["r"])
+        prm = (c["eta"], 1.0, 1.0)
+        if r > 0:
+            wo, wt, transmitted = oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, prm, (0, 0, 1), -wi, float(r))
+            assert not transmitted and np.array_equal(wo, np.array(c["reflect"], np.float32)) and np.all(wt == 1.0), c
+            n_r += 1
+        if r < 1:
+            above = float(np.nextafter(r, np.float32(2)))
+            wo, wt, transmitted = oracle.sample_delta(abi.SURF_BSDF_DIELECTRIC, prm, (0, 0, 1), -wi, above)
+            assert transmitted and np.array_equal(wo, np.array(c["refract"], np.float32)), c
+            assert np.all(wt == np.float32(c["eta_ti"]) * np.float32(c["eta_ti"])), c
+            n_t += 1
+        n_tir += r == 1 and wi[2] != 0
+    assert n_r >= 200 and n_t >= 200 and n_tir >= 10
+    assert all(f == 1.0 for _, f in gold["conductor_default"])
