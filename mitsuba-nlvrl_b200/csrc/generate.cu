@@ -53,11 +53,6 @@ __device__ inline V3 sample_uniform_sphere(float u1, float u2) {         // warp
     float s, c; sincosf(2.f * kPi * u1, &s, &c);
     return V3(r * c, r * s, z);
 }
-__device__ inline void frame(V3 n, V3 &s, V3 &t) {                        // coordinate_system, core/vector.h
-    float sign = copysignf(1.f, n.z), a = -1.f / (sign + n.z), b = n.x * n.y * a;
-    s = V3(1.f + sign * n.x * n.x * a, sign * b, -sign * n.x);
-    t = V3(b, sign + n.y * n.y * a, -n.y);
-}
 __device__ inline V3 sample_phase(const DMedium &m, V3 wi /* direction of travel */, float u1, float u2) {
     if (m.phase == VRLB_PHASE_ISOTROPIC) return sample_uniform_sphere(u1, u2);
     // Henyey-Greenstein about the direction of travel (hg.cpp:56-75: cos_theta relative to -wi = travel direction)
@@ -66,7 +61,7 @@ __device__ inline V3 sample_phase(const DMedium &m, V3 wi /* direction of travel
     else { float sq = (1.f - g * g) / (1.f - g + 2.f * g * u1); cos_theta = (1.f + g * g - sq * sq) / (2.f * g); }
     float sin_theta = sqrtf(fmaxf(1.f - cos_theta * cos_theta, 0.f));
     float s, c; sincosf(2.f * kPi * u2, &s, &c);
-    V3 a, b; frame(wi, a, b);
+    V3 a, b; coordinate_system(wi, a, b);
     return normalize(a * (sin_theta * c) + b * (sin_theta * s) + wi * cos_theta);
 }
 
@@ -93,7 +88,7 @@ __device__ inline Emit emit_particle(const GenParams &p, Pcg32 &rng) {
     V3 n = tri_normal(t);
     e.o = p0 + e1 * b1 + e2 * (1.f - b0 - b1);
     float r = sqrtf(u3), s, c; sincosf(2.f * kPi * u4, &s, &c);           // cosine hemisphere
-    V3 a, b; frame(n, a, b);
+    V3 a, b; coordinate_system(n, a, b);
     e.d = normalize(a * (r * c) + b * (r * s) + n * sqrtf(fmaxf(1.f - u3, 0.f)));
     int id = VRLB_SURF_GET_EMITTER(t.flags);
     V3 Le(p.scene.emitters[id * 4], p.scene.emitters[id * 4 + 1], p.scene.emitters[id * 4 + 2]);
@@ -244,7 +239,7 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
                 dx = r * cs; dy = r * sn;
             }
             const float dz = sqrtf(fmaxf(1.f - dx * dx - dy * dy, 0.f));
-            V3 a, b; frame(n, a, b);
+            V3 a, b; coordinate_system(n, a, b);
             dir = normalize(a * dx + b * dy + n * dz);
             ++depth;                                                        // non-null BSDF, vrl.cpp:336-337
             if (VRLB_SURF_GET_EXTERIOR(tr.flags) >= 0 || VRLB_SURF_GET_INTERIOR(tr.flags) >= 0) medium = target_medium(tr, dir);   // vrl.cpp:351-353
