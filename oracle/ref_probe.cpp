@@ -181,6 +181,36 @@ int main() {
     }
     printf(" ],\n");
 
+    /* ---- query_rr: the same loop with the distance Russian roulette of vrl_map.h:171-190 (EDistanceRoulette): the
+     *      roulette draw comes first, a survivor's contribution is divided by its survival weight ---- */
+    printf(" \"query_rr\": [\n");
+    for (int k = 0; k < 8; ++k) {
+        Pair p = make_pair(0);
+        int uniform = (k % 3) == 2, vis = (k % 2), samples = 1 + (k % 2);
+        const float scaleRR = k < 4 ? 0.5f : 2.0f;
+        NLf nl = make_ray(p);
+        auto ray = nl.first();
+        MockSampler s; s.seed(0, 30000 + k);
+        V3 Li(0.f); int nb = 0, pruned = 0;
+        for (int smp = 0; smp < samples; ++smp)
+            for (int j = 0; j < NV; ++j) {
+                VRLf v = make_vrl(vp[j], &med);
+                auto res = v.findClosetPoint(ray);
+                float min_distance_sqr = sqrt(enoki::squared_norm((ray.o + ray.d * res.tCam) - (v.origin + v.direction * res.tVRL)));
+                float rrWeight = min(1 / (min_distance_sqr * scaleRR), 1.0);
+                if (rrWeight > s.next_1d()) {
+                    V3 c = (v.getContrib(vis ? &occl : &empty, uniform != 0, nl, &s, 0) / rrWeight) * m_scale;
+                    if (std::isnan(c[0]) || std::isnan(c[1]) || std::isnan(c[2]) || std::isinf(c[0]) || std::isinf(c[1]) || std::isinf(c[2])) continue;
+                    Li += c; nb++;
+                } else pruned++;
+            }
+        if (samples > 1) Li /= (float) samples;
+        printf("  {\"ray\": ["); p3(p.ro); printf(", "); p3(p.rd); printf(", %.9g], \"uniform\": %d, \"vis\": %d, \"samples\": %d, \"seed\": %d, \"scale_rr\": %.9g, \"draws\": %d, \"nb\": %d, \"pruned\": %d, \"out\": [",
+               (double) p.rmaxt, uniform, vis, samples, 30000 + k, (double) scaleRR, (int) s.draws, nb, pruned);
+        p3n(Li); printf("]}%s\n", k + 1 < 8 ? "," : "");
+    }
+    printf(" ],\n");
+
     /* ---- dice: VRL::dice (vrl_struct.h:88-128) with the dice length VRLMap::dicingVRL derives (vrl_map.h:104-118,
      *      double mean of the lengths / avgNumberDice, passed as a Float); long: VRL::convertToLong (146-154) ---- */
     {

@@ -158,6 +158,30 @@ def test_query_sum_matches_reference_sequential_stream(gold):
         assert _close(o32[0], want, rtol=5e-6), (c, o32[0])
 
 
+def test_distance_roulette_query_matches_reference_sequential_stream(gold):
+    """VRLMap::query with EDistanceRoulette (vrl_map.h:171-190) on the reference's sequential stream: the roulette draw
+    comes before the eval's draws, rrWeight = min(1 / (distance * scale_rr), 1), survivors are divided by it."""
+    soa = np.ascontiguousarray(np.array(gold["query_vrls"], np.float32).T)
+    vd = scenes.vrlset_desc(soa, scale=gold["query_scale"])
+    L = oracle.lib()
+    n_pruned = 0
+    for c in gold["query_rr"]:
+        sc = oracle.OracleScene(_scene(gold, bool(c["vis"])))
+        opt = scenes.default_options(samples_per_query=c["samples"], use_uniform_sampling=c["uniform"], visibility=c["vis"],
+                                     math_mode=0, rr_vrl=1, scale_rr=c["scale_rr"])
+        st, inc = C.c_uint64(), C.c_uint64()
+        L.vrlo_pcg32_seed(c["seed"], 0xda3e39cb94b95bdb, C.byref(st), C.byref(inc))
+        seg = np.zeros(1, abi.SEGMENT_DTYPE)
+        r = oracle.f32(c["ray"])
+        seg["o"][0], seg["d"][0], seg["maxt"][0] = r[0:3], r[3:6], r[6]
+        seg["weight"][0] = 1.0
+        seg["rng_state"][0] = st.value
+        o32, o64, ev = sc.gather(vd, seg, opt, rng_mode=oracle.RNG_SEQUENTIAL, n_threads=1)
+        assert _close(o32[0], _arr(c["out"]), rtol=5e-6), (c, o32[0])
+        n_pruned += c["pruned"]
+    assert n_pruned > 500                                  # the roulette does prune
+
+
 def test_dice_matches_reference(gold):
     """VRL::dice compiled from the reference (pieces of mean length / 3, flux attenuated by the medium transmittance):
     piece count, origins and lengths bit-exact (fp64 position arithmetic rounded once), flux to 1e-6 (Enoki exp vs libm)."""
