@@ -307,6 +307,7 @@ typedef struct vrlb_surface_query {
     float    reflectance[3]; float pad1;  /* of the surface's diffuse BSDF                                        */
     float    weight[3]; float pad2;       /* path throughput                                                      */
 } vrlb_surface_query;
+/* (vrlb_segments_build replaces the resident queries with those of the paths it traces; vrlb_segments_upload drops them.) */
 int  vrlb_surface_queries_upload(vrlb_context *ctx, const vrlb_surface_query *q, uint64_t n, int32_t width, int32_t height);
 int  vrlb_surface_queries_download(vrlb_context *ctx, vrlb_surface_query *q, uint64_t cap, uint64_t *n_out);
 /* Test/diagnostic entry: caustic + global estimate per resident query BEFORE the weight, host buffer n*3. */

@@ -624,6 +624,7 @@ int vrlb_segments_upload(vrlb_context *ctx, const vrlb_segment *segs, uint64_t n
     if (n) CU(ctx, cudaMemcpyAsync(ctx->segs.ptr, segs, n * sizeof(vrlb_segment), cudaMemcpyHostToDevice, ctx->stream));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->n_segs = n; ctx->timing.n_segments = n;
+    ctx->n_squeries = 0;                         // the surface queries belonged to the camera paths just replaced
     return VRLB_OK;
 }
 
