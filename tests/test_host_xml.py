@@ -162,6 +162,22 @@ def test_bsdf_reflectance_forms(host, tmp_path):
     assert "wavelength table" in err and info["dielectric_triangles"] == 2 and info["mirror_triangles"] == 2
 
 
+def test_bsdf_parameter_errors(host, tmp_path):
+    """An index of refraction is a number or one of Mitsuba's material names; anything else fails like the reference's lookup."""
+    xml = """<scene version="2.0.0">
+    <sensor type="perspective"><float name="fov" value="40"/><film type="hdrfilm"/></sensor>
+    <medium id="m" type="homogeneous"/>
+    <shape type="rectangle"><bsdf type="dielectric"><string name="int_ior" value="{ior}"/></bsdf></shape>
+    </scene>"""
+    p = os.path.join(str(tmp_path), "ior.xml")
+    open(p, "w").write(xml.format(ior="unobtainium"))
+    rc, info, err = _info(host, p)
+    assert rc != 0 and "unknown index of refraction" in err and "unobtainium" in err
+    open(p, "w").write(xml.format(ior="diamond"))
+    rc, info, err = _info(host, p)
+    assert rc == 0 and info["dielectric_triangles"] == 2, err
+
+
 def test_property_and_schema_errors(host, tmp_path):
     path = _write_scene(str(tmp_path), extra='<integer name="vrlTargetNum" value="5"/>')
     rc, info, err = _info(host, path)
