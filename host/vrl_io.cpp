@@ -137,4 +137,60 @@ void write_pfm(const std::string &path, const std::vector<float> &rgb, int width
         f.write(reinterpret_cast<const char *>(&rgb[(size_t) y * width * 3]), (std::streamsize) ((size_t) width * 3 * sizeof(float)));
 }
 
+namespace {
+void put_i32(std::string &b, int32_t v) { b.append(reinterpret_cast<const char *>(&v), 4); }
+void put_f32(std::string &b, float v) { b.append(reinterpret_cast<const char *>(&v), 4); }
+void put_str(std::string &b, const char *s) { b.append(s); b.push_back('\0'); }
+void attr(std::string &b, const char *name, const char *type, const std::string &value) {
+    put_str(b, name); put_str(b, type); put_i32(b, (int32_t) value.size()); b.append(value);
+}
+}  // namespace
+
+// OpenEXR 2 single-part scan-line layout: magic, version, attributes (name, type, size, value), a zero byte, one 64-bit
+// file offset per scan line, then per line { y, byte count, the line's channels in alphabetical order, each `width` floats }
+void write_exr(const std::string &path, const std::vector<float> &xyzaw, int width, int height) {
+    if (xyzaw.size() != (size_t) width * height * 5) throw std::runtime_error("write_exr: XYZAW buffer size mismatch");
+    const std::vector<float> rgb = develop_rgb(xyzaw, width, height);
+    std::string h;
+    put_i32(h, 20000630); put_i32(h, 2);
+    { std::string v; const char *names[4] = { "A", "B", "G", "R" };
+      for (const char *n : names) { put_str(v, n); put_i32(v, 2 /* FLOAT */); v.append(4, '\0'); put_i32(v, 1); put_i32(v, 1); }
+      v.push_back('\0'); attr(h, "channels", "chlist", v); }
+    attr(h, "compression", "compression", std::string(1, '\0'));
+    { std::string v; put_i32(v, 0); put_i32(v, 0); put_i32(v, width - 1); put_i32(v, height - 1);
+      attr(h, "dataWindow", "box2i", v); attr(h, "displayWindow", "box2i", v); }
+    attr(h, "lineOrder", "lineOrder", std::string(1, '\0'));
+    { std::string v; put_f32(v, 1.f); attr(h, "pixelAspectRatio", "float", v); }
+    { std::string v; put_f32(v, 0.f); put_f32(v, 0.f); attr(h, "screenWindowCenter", "v2f", v); }
+    { std::string v; put_f32(v, 1.f); attr(h, "screenWindowWidth", "float", v); }
+    h.push_back('\0');
+    const uint64_t line_bytes = (uint64_t) width * 4 * sizeof(float), block = 8 + line_bytes;
+    std::ofstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("cannot write " + path);
+    f.write(h.data(), (std::streamsize) h.size());
+    for (int y = 0; y < height; ++y) { const uint64_t off = h.size() + (uint64_t) height * 8 + (uint64_t) y * block; f.write(reinterpret_cast<const char *>(&off), 8); }
+    std::vector<float> line((size_t) width * 4);
+    for (int y = 0; y < height; ++y) {
+        for (int x = 0; x < width; ++x) {
+            const size_t i = (size_t) y * width + x;
+            const float w = xyzaw[i * 5 + 4];
+            line[(size_t) x] = w != 0.f ? xyzaw[i * 5 + 3] / w : 0.f;                         // A
+            line[(size_t) width + x] = rgb[i * 3 + 2];                                           // B
+            line[(size_t) 2 * width + x] = rgb[i * 3 + 1];                                       // G
+            line[(size_t) 3 * width + x] = rgb[i * 3 + 0];                                       // R
+        }
+        const int32_t yy = y, n = (int32_t) line_bytes;
+        f.write(reinterpret_cast<const char *>(&yy), 4); f.write(reinterpret_cast<const char *>(&n), 4);
+        f.write(reinterpret_cast<const char *>(line.data()), (std::streamsize) line_bytes);
+    }
+}
+
+void write_film(const std::string &out, const std::vector<float> &xyzaw, int width, int height) {
+    const std::string ext = out.size() > 4 ? out.substr(out.size() - 4) : std::string();
+    if (ext == ".exr") write_exr(out, xyzaw, width, height);
+    else if (ext == ".pfm") write_pfm(out, develop_rgb(xyzaw, width, height), width, height);
+    else { std::ofstream o(out, std::ios::binary); if (!o) throw std::runtime_error("cannot write " + out);
+           o.write(reinterpret_cast<const char *>(xyzaw.data()), (std::streamsize) (xyzaw.size() * sizeof(float))); }
+}
+
 }  // namespace vrlhost

@@ -4,7 +4,7 @@
 //   * Wavefront OBJ meshes as the fixtures use them (v / f records, polygons fanned, negative indices; normals and
 //     texture coordinates are parsed past -- the gather only needs positions, src/shapes/obj.cpp);
 //   * the developed film: HDRFilm::develop divides XYZ by W and converts XYZ -> linear sRGB (hdrfilm.cpp:259-262,
-//     include/mitsuba/core/spectrum.h:229-235); written as a PFM image (the EXR container stays with the host film).
+//     include/mitsuba/core/spectrum.h:229-235); written as a PFM image or as an uncompressed float OpenEXR file.
 #pragma once
 #include <cstdint>
 #include <string>
@@ -28,5 +28,11 @@ std::vector<float> read_obj(const std::string &path, const float *to_world = nul
 // XYZAW (5 floats / pixel) -> linear sRGB (3 floats / pixel); pixels with W = 0 stay black
 std::vector<float> develop_rgb(const std::vector<float> &xyzaw, int width, int height);
 void write_pfm(const std::string &path, const std::vector<float> &rgb, int width, int height);   // top row first in `rgb`
+// The developed film as the reference's HDRFilm writes it (hdrfilm.cpp:254-349, pixel_format "rgba"): an OpenEXR scan-line
+// file with R, G, B = xyz_to_srgb(XYZ / W) and A = A / W.  Written uncompressed with 32-bit float channels (the reference's
+// default is half floats + ZIP through the OpenEXR library, which is not in this image; any EXR reader takes both).
+void write_exr(const std::string &path, const std::vector<float> &xyzaw, int width, int height);
+// `out` by extension: .exr -> write_exr, .pfm -> develop_rgb + write_pfm, anything else -> the raw XYZAW floats
+void write_film(const std::string &out, const std::vector<float> &xyzaw, int width, int height);
 
 }  // namespace vrlhost

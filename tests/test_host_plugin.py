@@ -113,3 +113,84 @@ def test_host_render_matches_oracle(tmp_path):
     a, b = film[..., :3].astype(np.float64), ref[..., :3].astype(np.float64)
     err = np.abs(a - b) / np.maximum(np.abs(b), 1e-6 * np.abs(b).max())
     assert err.max() <= 2e-4, err.max()       # fp32-sequential oracle film vs compensated GPU sums
+
+
+def _read_exr(path):
+    """Minimal reader for the files write_exr produces: single-part, scan-line, uncompressed, FLOAT channels."""
+    import struct
+    b = open(path, "rb").read()
+    assert struct.unpack_from("<ii", b, 0) == (20000630, 2)
+    pos, attrs = 8, {}
+    while b[pos] != 0:
+        e = b.index(b"\0", pos); name = b[pos:e].decode(); pos = e + 1
+        e = b.index(b"\0", pos); typ = b[pos:e].decode(); pos = e + 1
+        n, = struct.unpack_from("<i", b, pos); pos += 4
+        attrs[name] = (typ, b[pos:pos + n]); pos += n
+    pos += 1
+    chans, v, p = [], attrs["channels"][1], 0
+    while v[p] != 0:
+        e = v.index(b"\0", p); chans.append(v[p:e].decode()); p = e + 1
+        ptype, _, xs, ys = struct.unpack_from("<i4sii", v, p); p += 16
+        assert (ptype, xs, ys) == (2, 1, 1)
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    w, h = x1 - x0 + 1, y1 - y0 + 1
+    assert attrs["compression"][1] == b"\0" and attrs["lineOrder"][1] == b"\0" and chans == sorted(chans)
+    offsets = struct.unpack_from(f"<{h}Q", b, pos)
+    img = np.zeros((h, w, len(chans)), np.float32)
+    for row, off in enumerate(offsets):
+        y, nbytes = struct.unpack_from("<ii", b, off)
+        assert y == row and nbytes == w * len(chans) * 4
+        img[row] = np.frombuffer(b, np.float32, w * len(chans), off + 8).reshape(len(chans), w).T
+    assert offsets[-1] + 8 + w * len(chans) * 4 == len(b)
+    return chans, img, attrs
+
+
+def test_developed_film_as_exr_and_pfm(tmp_path):
+    """HDRFilm::develop (hdrfilm.cpp:254-349): XYZ / W -> linear sRGB, alpha = A / W, written as an OpenEXR scan-line file
+    (uncompressed float channels A, B, G, R) or a PFM; both from the same raw XYZAW film."""
+    host = _build()
+    rng = np.random.default_rng(5)
+    w, h = 7, 5
+    film = rng.uniform(0.1, 2.0, (h, w, 5)).astype(np.float32)
+    film[..., 4] = rng.integers(1, 4, (h, w))
+    film[0, 0] = 0                                                       # a pixel without samples develops to black
+    raw = os.path.join(str(tmp_path), "film.f32")
+    film.tofile(raw)
+    exr, pfm = os.path.join(str(tmp_path), "film.exr"), os.path.join(str(tmp_path), "film.pfm")
+    for out in (exr, pfm):
+        subprocess.check_call([host, "convert-film", raw, str(w), str(h), out])
+    chans, img, attrs = _read_exr(exr)
+    assert chans == ["A", "B", "G", "R"] and img.shape == (h, w, 4)
+    W = np.where(film[..., 4] > 0, film[..., 4], 1.0)
+    xyz = film[..., :3] / W[..., None]
+    m = np.array([[3.240479, -1.537150, -0.498535], [-0.969256, 1.875991, 0.041556], [0.055648, -0.204043, 1.057311]], np.float32)
+    rgb = xyz @ m.T
+    assert np.allclose(img[..., 3], rgb[..., 0], rtol=1e-5, atol=1e-6) and np.allclose(img[..., 2], rgb[..., 1], rtol=1e-5, atol=1e-6)
+    assert np.allclose(img[..., 1], rgb[..., 2], rtol=1e-5, atol=1e-6) and np.allclose(img[..., 0], film[..., 3] / W, rtol=1e-6)
+    assert np.all(img[0, 0] == 0)
+    assert struct_box(attrs["displayWindow"][1]) == (0, 0, w - 1, h - 1)
+    # an independent decoder where the image has one: OpenCV's OpenEXR reader (BGRA)
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    try:
+        import cv2
+        dec = cv2.imread(exr, cv2.IMREAD_UNCHANGED)
+    except Exception:
+        dec = None
+    if dec is not None:
+        assert dec.shape == (h, w, 4) and dec.dtype == np.float32
+        assert np.array_equal(dec[..., 2], img[..., 3]) and np.array_equal(dec[..., 1], img[..., 2])
+        assert np.array_equal(dec[..., 0], img[..., 1]) and np.array_equal(dec[..., 3], img[..., 0])
+    # the PFM holds the same RGB, bottom row first
+    b = open(pfm, "rb").read()
+    head = b"PF\n%d %d\n-1.0\n" % (w, h)
+    assert b.startswith(head)
+    p = np.frombuffer(b, np.float32, w * h * 3, len(head)).reshape(h, w, 3)[::-1]
+    assert np.array_equal(p[..., 0], img[..., 3]) and np.array_equal(p[..., 2], img[..., 1])
+    # wrong size: loud
+    r = subprocess.run([host, "convert-film", raw, str(w + 1), str(h), exr], capture_output=True, text=True)
+    assert r.returncode != 0 and "cannot read" in r.stderr
+
+
+def struct_box(b):
+    import struct
+    return struct.unpack("<4i", b)
