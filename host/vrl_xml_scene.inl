@@ -253,8 +253,9 @@ struct Builder {
         if (s.get("type") != "perspective") fail("Error while loading \"" + s.file + "\": sensor type \"" + s.get("type") + "\" is not on the VRL path (perspective is)");
         const Node *film = child_named(s, "film", nullptr), *sampler = child_named(s, "sampler", nullptr);
         const int w = film ? (int) prop_int(*film, "width", 768) : 768, h = film ? (int) prop_int(*film, "height", 576) : 576;   // film.cpp:15-16
-        if (film) { const Node *rf = child_named(*film, "rfilter", nullptr);
-                    if (rf && rf->get("type") != "box") warn("rfilter type=\"" + rf->get("type") + "\": the device film splats with the box filter (imageblock.cpp:162-169 fast path)"); }
+        { const Node *rf = film ? child_named(*film, "rfilter", nullptr) : nullptr;                          // film.cpp:36-48: no <rfilter> = gaussian
+          const std::string rt = rf ? rf->get("type") : std::string("gaussian");
+          if (rt != "box") warn("rfilter type=\"" + rt + "\"" + (rf ? "" : " (the film's default)") + ": the device film splats with the box filter (imageblock.cpp:162-169 fast path)"); }
         out.sensor.spp = sampler ? (int32_t) prop_int(*sampler, "sample_count", 4) : 4;                      // sampler.cpp:11
         out.sensor.sampler_seed = sampler ? (uint64_t) prop_int(*sampler, "seed", 0) : 0;
         if (sampler && sampler->get("type") != "independent") warn("sampler type=\"" + sampler->get("type") + "\": the path addresses independent PCG32 streams");

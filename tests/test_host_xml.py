@@ -159,6 +159,7 @@ def test_bsdf_reflectance_forms(host, tmp_path):
     assert rc == 0, err
     assert info["triangles"] == 8 and info["reflecting_triangles"] == 4 and info["twosided_triangles"] == 2
     assert np.allclose(info["mean_reflectance"], [(0.1 + 0.8) / 2, (0.2 + 0.6) / 2, (0.3 + 0.3) / 2], rtol=1e-6)
+    assert "rfilter type=\"gaussian\" (the film's default)" in err         # no <rfilter> in this film: Mitsuba would filter with a gaussian
     assert "wavelength table" in err and info["dielectric_triangles"] == 2 and info["mirror_triangles"] == 2
 
 
