@@ -96,7 +96,7 @@ struct Builder {
     }
 
     // ---- shapes ----
-    // named indices of refraction, src/libcore/... ior.h (the entries the fixture scenes can name)
+    // named indices of refraction: the table of include/mitsuba/render/ior.h:23-47
     double ior_of(const Node &b, const char *name, const char *def) {
         const Node *p = prop(b, name);
         if (p && (p->name == "float" || p->name == "integer")) return to_double(*p, p->get("value"));
@@ -189,7 +189,7 @@ struct Builder {
                 float sr[3] = { 1.f, 1.f, 1.f }, st[3] = { 1.f, 1.f, 1.f };
                 prop_rgb(*b, "specular_reflectance", sr); prop_rgb(*b, "specular_transmittance", st);
                 if (sr[0] != sr[1] || sr[0] != sr[2] || st[0] != st[1] || st[0] != st[2]) warn("bsdf type=\"dielectric\": coloured specular_reflectance / transmittance reduced to the red channel");
-                refl[0] = (float) (ior_of(*b, "int_ior", "bk7") / ior_of(*b, "ext_ior", "air")); refl[1] = sr[0]; refl[2] = st[0];
+                refl[0] = (float) ior_of(*b, "int_ior", "bk7") / (float) ior_of(*b, "ext_ior", "air");   /* m_eta = int_ior / ext_ior in ScalarFloat, dielectric.cpp */ refl[1] = sr[0]; refl[2] = st[0];
                 return;
             }
             if (t == "thindielectric") {
