@@ -166,6 +166,7 @@ void expand(Node &n, Params &params, const std::string &base_dir, int depth, std
 // ("reusable after schema translation"), each reported in `notes`:
 //   medium sigma_s + sigma_a            -> sigma_t = sigma_s + sigma_a, albedo = sigma_s / sigma_t
 //   shape with a medium and no BSDF     -> index-matched boundary (0.x Shape::configure), i.e. <bsdf type="null"/>
+//   gridvolume without a to_world       -> use_grid_bbox = true (the 0.x plugin places the grid by the file's bounding box)
 //   <integrator type="vrl"> properties  -> those of the LightSlice implementation these scenes were written for are dropped;
 //                                          VRLIntegrator then runs on its defaults (or the caller's overrides)
 int version_major(const Node &root, const std::string &path) {
@@ -247,6 +248,12 @@ void translate_legacy(Node &n, std::vector<std::string> &notes) {
             n.children.push_back(std::move(b));
             notes.push_back("0.x shape with a medium and no BSDF: loaded as an index-matched boundary (null BSDF), as 0.x Shape::configure did");
         }
+    }
+    if (n.name == "volume" && n.get("type", "") == "gridvolume" && !find("use_grid_bbox") && !find("to_world")) {
+        // a 0.x gridvolume sits where its file's bounding box says (0.x gridvolume.cpp); Mitsuba 2 asks for use_grid_bbox
+        Node b; b.name = "boolean"; b.file = n.file; b.attrs = { { "name", "use_grid_bbox" }, { "value", "true" } };
+        n.children.push_back(std::move(b));
+        notes.push_back("0.x gridvolume: placed by the bounding box stored in its file (use_grid_bbox = true)");
     }
     if (n.name == "integrator" && n.get("type", "") == "vrl") {
         std::vector<Node> kept;

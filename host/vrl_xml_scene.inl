@@ -42,8 +42,12 @@ struct Builder {
             else fail("Error while loading \"" + m.file + "\": phase function \"" + pt + "\" is not on the VRL path");
         }
         for (int k = 0; k < 3; ++k) { d.albedo[k] = 0.75f; d.sigma_t[k] = 1.f; }                             // homogeneous.cpp:23-24
-        if (prop(m, "albedo") && !prop_rgb(m, "albedo", d.albedo))
-            fail("Error while loading \"" + m.file + "\": medium \"" + id + "\": only a constant albedo is supported");
+        if (const Node *al = prop(m, "albedo")) {
+            // a constant: <rgb|spectrum|float name="albedo">, or <volume name="albedo" type="constvolume"> with its `color` / `value`
+            bool ok = prop_rgb(m, "albedo", d.albedo);
+            if (!ok && al->name == "volume" && al->get("type", "") == "constvolume") ok = prop_rgb(*al, "color", d.albedo) || prop_rgb(*al, "value", d.albedo);
+            if (!ok) fail("Error while loading \"" + m.file + "\": medium \"" + id + "\": only a constant albedo is supported");
+        }
         if (type == "homogeneous" || type == "nonlinear") {
             d.kind = type == "homogeneous" ? VRLB_MEDIUM_HOMOGENEOUS : VRLB_MEDIUM_NONLINEAR;
             if (prop(m, "sigma_t") && !prop_rgb(m, "sigma_t", d.sigma_t))

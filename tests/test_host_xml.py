@@ -268,6 +268,23 @@ def test_fbd15_benchmark_scenes_load(host):
     assert info["dielectric_triangles"] == info["triangles"] > 10000                     # glass, liquid surface, interface: all dielectric
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference/data/hetvol"), reason="reference fixtures not mounted")
+def test_hetvol_scene_loads(host):
+    """BASELINE config "data/hetvol": a Mitsuba-0.4 scene (volpath, constvolume albedo, gridvolume placed by the file's
+    bounding box, ldsampler, gaussian filter).  After the upgrade + translation the smoke grid sits exactly in bounds.obj."""
+    rc, info, err = _info(host, "/root/reference/data/hetvol/hetvol.xml")
+    assert rc == 0, err
+    m = info["media"][0]
+    assert (m["id"], m["kind"], m["phase"]) == ("smoke", abi.MEDIUM_GRID, abi.PHASE_HG) and m["scale"] == 100.0
+    assert m["grid_res"] == [128, 128, 50] and np.allclose(m["albedo"], [0.9] * 3)
+    assert np.allclose(m["grid_bbox"], [-0.5, -0.5, -0.1953125, 0.5, 0.5, 0.1953125], atol=1e-6)
+    assert info["null_triangles"] == 12 and info["interior_triangles"] == 12 and info["emitters"] == [[400.0, 400.0, 400.0]]
+    assert info["sensor"]["width"] == 768 and info["sensor"]["spp"] == 64 and info["integrator"] == "volpath"
+    assert np.allclose(info["mean_reflectance"], [0.2, 0.2, 0.3])      # diffuseReflectance -> diffuse_reflectance -> reflectance
+    for w in ("v0.4.0", "use_grid_bbox", "ldsampler", "gaussian"):
+        assert w in err, w
+
+
 @pytest.mark.skipif(not os.path.isdir(REF_SCENES), reason="reference fixtures not mounted")
 def test_reference_fixture_scenes_load(host):
     rc, info, err = _info(host, os.path.join(REF_SCENES, "cbox-volume-vrl.xml"), "use_light_cut=false")
