@@ -407,6 +407,21 @@ bool prop_rgb(const Node &n, const char *name, float out[3]) {
     const Node *p = prop(n, name);
     if (!p) return false;
     if (p->name != "rgb" && p->name != "spectrum" && p->name != "float" && p->name != "color") return false;
+    if (p->get("value").find(':') != std::string::npos) {
+        // wavelength:value table (the 0.x scenes and data/cbox): mean over the red / green / blue thirds of the visible range
+        // (no CIE integration; callers report it in `warnings`)
+        double sum[3] = { 0, 0, 0 }; int cnt[3] = { 0, 0, 0 }; std::string tok;
+        for (char ch : p->get("value") + ",") {
+            if (ch != ',') { tok += ch; continue; }
+            const size_t c = tok.find(':');
+            if (c != std::string::npos) { const double wl = to_double(*p, tok.substr(0, c)), val = to_double(*p, tok.substr(c + 1));
+                                          const int band = wl < 490 ? 2 : wl < 580 ? 1 : 0; sum[band] += val; ++cnt[band]; }
+            tok.clear();
+        }
+        const double all = (sum[0] + sum[1] + sum[2]) / std::max(1, cnt[0] + cnt[1] + cnt[2]);
+        for (int k = 0; k < 3; ++k) out[k] = (float) (cnt[k] ? sum[k] / cnt[k] : all);
+        return true;
+    }
     auto l = to_list(*p, p->get("value"));
     if (l.size() == 1) out[0] = out[1] = out[2] = (float) l[0];
     else if (l.size() == 3) for (int i = 0; i < 3; ++i) out[i] = (float) l[(size_t) i];

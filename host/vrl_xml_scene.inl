@@ -92,6 +92,8 @@ struct Builder {
         vrlb_emitter d{};
         d.radiance[0] = d.radiance[1] = d.radiance[2] = 1.f;                                                  // area.cpp:32
         prop_rgb(e, "radiance", d.radiance);
+        if (const Node *r = prop(e, "radiance")) if (r->get("value", "").find(':') != std::string::npos)
+            warn("radiance given as a wavelength table: reduced to RGB by band means (no CIE integration)");
         const int idx = (int) out.scene.emitters.size();
         if (idx >= 255) fail("too many emitters");
         out.scene.emitters.push_back(d);
@@ -210,16 +212,7 @@ struct Builder {
             const std::string v = r->get("value", "");
             if ((r->name == "rgb" || r->name == "spectrum" || r->name == "float" || r->name == "color") && v.find(':') == std::string::npos && !v.empty()) prop_rgb(*b, r->get("name").c_str(), refl);
             else if (r->name == "spectrum" && v.find(':') != std::string::npos) {
-                // wavelength:value table (the 0.x scenes): mean over the blue / green / red thirds of the visible range
-                double sum[3] = { 0, 0, 0 }; int cnt[3] = { 0, 0, 0 }; std::string tok;
-                for (char ch : v + ",") {
-                    if (ch != ',') { tok += ch; continue; }
-                    const size_t c = tok.find(':');
-                    if (c != std::string::npos) { const double wl = to_double(*r, tok.substr(0, c)), val = to_double(*r, tok.substr(c + 1));
-                                                  const int band = wl < 490 ? 2 : wl < 580 ? 1 : 0; sum[band] += val; ++cnt[band]; }
-                    tok.clear();
-                }
-                for (int k = 0; k < 3; ++k) refl[k] = cnt[k] ? (float) (sum[k] / cnt[k]) : 0.5f;
+                prop_rgb(*b, r->get("name").c_str(), refl);
                 warn("reflectance given as a wavelength table: reduced to RGB by band means (no CIE integration)");
             } else warn("bsdf \"" + b->get("id", t.c_str()) + "\": textured reflectance; light-tracing particles see the default 0.5");
         };

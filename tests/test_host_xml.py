@@ -285,6 +285,16 @@ def test_hetvol_scene_loads(host):
         assert w in err, w
 
 
+@pytest.mark.skipif(not os.path.isfile("/root/reference/data/cbox/cbox.xml"), reason="reference fixtures not mounted")
+def test_data_cbox_scene_loads(host):
+    """BASELINE config "data/cbox": the Mitsuba-0.4 Cornell box (surface only; spectra as wavelength tables)."""
+    rc, info, err = _info(host, "/root/reference/data/cbox/cbox.xml")
+    assert rc == 0, err
+    assert info["triangles"] == 38 and info["emitter_triangles"] == 2 and info["media"] == []
+    assert np.allclose(info["emitters"], [[17.0, 8.0, 0.0]])          # 400:0, 500:8, 600:15.6, 700:18.4 by band means
+    assert "wavelength table" in err and info["reflecting_triangles"] == 36
+
+
 @pytest.mark.skipif(not os.path.isdir(REF_SCENES), reason="reference fixtures not mounted")
 def test_reference_fixture_scenes_load(host):
     rc, info, err = _info(host, os.path.join(REF_SCENES, "cbox-volume-vrl.xml"), "use_light_cut=false")
