@@ -4,7 +4,7 @@
 //   vrl_host selftest                                                     property / error behaviour, no GPU needed
 //   vrl_host vol-info <file.vol> | obj-info <file.obj>                     the loaders of vrl_io.h (no GPU needed)
 //   vrl_host xml-info <scene.xml> [-Dname=value ...]                       what the scene loader of vrl_xml.h sees (no GPU needed)
-//   vrl_host convert-film <in.f32> <width> <height> <out.exr|out.pfm>     raw XYZAW film -> developed image
+//   vrl_host convert-film <in.f32> <width> <height> <out.exr|out.pfm> [float16]   raw XYZAW film -> developed image
 //   vrl_host render-xml <scene.xml> <out.exr|out.pfm|out.f32> [-Dname=value ...] [key=value ...]
 //                                                                         the role of `mitsuba scene.xml`: load -> VRLIntegrator ->
 //                                                                         preprocess (light tracing on the device) -> render -> film;
@@ -91,13 +91,13 @@ int main(int argc, char **argv) {
                         g.bbox_min[0], g.bbox_min[1], g.bbox_min[2], g.bbox_max[0], g.bbox_max[1], g.bbox_max[2], g.max, g.mean);
             return 0;
         }
-        if (argc == 6 && std::string(argv[1]) == "convert-film") {         // raw XYZAW floats -> .exr / .pfm (HDRFilm::develop)
+        if ((argc == 6 || (argc == 7 && std::string(argv[6]) == "float16")) && std::string(argv[1]) == "convert-film") {   // raw XYZAW floats -> .exr / .pfm (HDRFilm::develop)
             const int w = std::atoi(argv[3]), h = std::atoi(argv[4]);
             std::ifstream f(argv[2], std::ios::binary);
             std::vector<float> film((size_t) std::max(w, 0) * (size_t) std::max(h, 0) * 5);
             if (!f || film.empty() || !f.read((char *) film.data(), (std::streamsize) (film.size() * 4)))
                 throw std::runtime_error(std::string("cannot read ") + argv[3] + " x " + argv[4] + " XYZAW pixels from " + argv[2]);
-            write_film(argv[5], film, w, h);
+            write_film(argv[5], film, w, h, argc == 7);
             return 0;
         }
         if (argc == 3 && std::string(argv[1]) == "obj-info") {
@@ -170,7 +170,7 @@ int main(int argc, char **argv) {
             std::vector<float> film;
             bool ok = integrator.render(ls.scene, ls.sensor, film);
             std::string out = argv[3];
-            write_film(out, film, ls.sensor.camera.width, ls.sensor.camera.height);
+            write_film(out, film, ls.sensor.camera.width, ls.sensor.camera.height, ls.film_half);
             return ok ? 0 : 3;
         }
         if (argc < 5 || std::string(argv[1]) != "render") { std::fprintf(stderr, "usage: vrl_host render scene.vrls set.vrlb out.f32 [k=v ...] | selftest\n"); return 2; }

@@ -141,6 +141,25 @@ namespace {
 void put_i32(std::string &b, int32_t v) { b.append(reinterpret_cast<const char *>(&v), 4); }
 void put_f32(std::string &b, float v) { b.append(reinterpret_cast<const char *>(&v), 4); }
 void put_str(std::string &b, const char *s) { b.append(s); b.push_back('\0'); }
+// IEEE binary32 -> binary16, round to nearest even (what OpenEXR's `half` does)
+uint16_t to_half(float f) {
+    uint32_t x; std::memcpy(&x, &f, 4);
+    const uint32_t sign = (x >> 16) & 0x8000u, mant = x & 0x7fffffu;
+    const int32_t e = (int32_t) ((x >> 23) & 0xffu) - 127 + 15;
+    if (((x >> 23) & 0xffu) == 0xffu) return (uint16_t) (sign | 0x7c00u | (mant ? 0x200u : 0u));     // inf / nan
+    if (e >= 31) return (uint16_t) (sign | 0x7c00u);                                                    // overflow -> inf
+    if (e <= 0) {                                                                                        // subnormal half or zero
+        if (e < -10) return (uint16_t) sign;
+        const uint32_t m = mant | 0x800000u; const int shift = 14 - e;
+        uint32_t h = m >> shift; const uint32_t rem = m & ((1u << shift) - 1u), halfway = 1u << (shift - 1);
+        if (rem > halfway || (rem == halfway && (h & 1u))) ++h;
+        return (uint16_t) (sign | h);
+    }
+    uint32_t h = ((uint32_t) e << 10) | (mant >> 13);
+    const uint32_t rem = mant & 0x1fffu;
+    if (rem > 0x1000u || (rem == 0x1000u && (h & 1u))) ++h;                                              // may carry into the exponent: still correct
+    return (uint16_t) (sign | h);
+}
 void attr(std::string &b, const char *name, const char *type, const std::string &value) {
     put_str(b, name); put_str(b, type); put_i32(b, (int32_t) value.size()); b.append(value);
 }
@@ -148,13 +167,13 @@ void attr(std::string &b, const char *name, const char *type, const std::string 
 
 // OpenEXR 2 single-part scan-line layout: magic, version, attributes (name, type, size, value), a zero byte, one 64-bit
 // file offset per scan line, then per line { y, byte count, the line's channels in alphabetical order, each `width` floats }
-void write_exr(const std::string &path, const std::vector<float> &xyzaw, int width, int height) {
+void write_exr(const std::string &path, const std::vector<float> &xyzaw, int width, int height, bool half) {
     if (xyzaw.size() != (size_t) width * height * 5) throw std::runtime_error("write_exr: XYZAW buffer size mismatch");
     const std::vector<float> rgb = develop_rgb(xyzaw, width, height);
     std::string h;
     put_i32(h, 20000630); put_i32(h, 2);
     { std::string v; const char *names[4] = { "A", "B", "G", "R" };
-      for (const char *n : names) { put_str(v, n); put_i32(v, 2 /* FLOAT */); v.append(4, '\0'); put_i32(v, 1); put_i32(v, 1); }
+      for (const char *n : names) { put_str(v, n); put_i32(v, half ? 1 /* HALF */ : 2 /* FLOAT */); v.append(4, '\0'); put_i32(v, 1); put_i32(v, 1); }
       v.push_back('\0'); attr(h, "channels", "chlist", v); }
     attr(h, "compression", "compression", std::string(1, '\0'));
     { std::string v; put_i32(v, 0); put_i32(v, 0); put_i32(v, width - 1); put_i32(v, height - 1);
@@ -164,7 +183,7 @@ void write_exr(const std::string &path, const std::vector<float> &xyzaw, int wid
     { std::string v; put_f32(v, 0.f); put_f32(v, 0.f); attr(h, "screenWindowCenter", "v2f", v); }
     { std::string v; put_f32(v, 1.f); attr(h, "screenWindowWidth", "float", v); }
     h.push_back('\0');
-    const uint64_t line_bytes = (uint64_t) width * 4 * sizeof(float), block = 8 + line_bytes;
+    const uint64_t line_bytes = (uint64_t) width * 4 * (half ? 2 : 4), block = 8 + line_bytes;
     std::ofstream f(path, std::ios::binary);
     if (!f) throw std::runtime_error("cannot write " + path);
     f.write(h.data(), (std::streamsize) h.size());
@@ -181,13 +200,17 @@ void write_exr(const std::string &path, const std::vector<float> &xyzaw, int wid
         }
         const int32_t yy = y, n = (int32_t) line_bytes;
         f.write(reinterpret_cast<const char *>(&yy), 4); f.write(reinterpret_cast<const char *>(&n), 4);
-        f.write(reinterpret_cast<const char *>(line.data()), (std::streamsize) line_bytes);
+        if (half) {
+            std::vector<uint16_t> hl(line.size());
+            for (size_t k = 0; k < line.size(); ++k) hl[k] = to_half(line[k]);
+            f.write(reinterpret_cast<const char *>(hl.data()), (std::streamsize) line_bytes);
+        } else f.write(reinterpret_cast<const char *>(line.data()), (std::streamsize) line_bytes);
     }
 }
 
-void write_film(const std::string &out, const std::vector<float> &xyzaw, int width, int height) {
+void write_film(const std::string &out, const std::vector<float> &xyzaw, int width, int height, bool half) {
     const std::string ext = out.size() > 4 ? out.substr(out.size() - 4) : std::string();
-    if (ext == ".exr") write_exr(out, xyzaw, width, height);
+    if (ext == ".exr") write_exr(out, xyzaw, width, height, half);
     else if (ext == ".pfm") write_pfm(out, develop_rgb(xyzaw, width, height), width, height);
     else { std::ofstream o(out, std::ios::binary); if (!o) throw std::runtime_error("cannot write " + out);
            o.write(reinterpret_cast<const char *>(xyzaw.data()), (std::streamsize) (xyzaw.size() * sizeof(float))); }

@@ -31,8 +31,8 @@ void write_pfm(const std::string &path, const std::vector<float> &rgb, int width
 // The developed film as the reference's HDRFilm writes it (hdrfilm.cpp:254-349, pixel_format "rgba"): an OpenEXR scan-line
 // file with R, G, B = xyz_to_srgb(XYZ / W) and A = A / W.  Written uncompressed with 32-bit float channels (the reference's
 // default is half floats + ZIP through the OpenEXR library, which is not in this image; any EXR reader takes both).
-void write_exr(const std::string &path, const std::vector<float> &xyzaw, int width, int height);
+void write_exr(const std::string &path, const std::vector<float> &xyzaw, int width, int height, bool half = false);   // half: 16-bit channels (component_format float16, the film's default)
 // `out` by extension: .exr -> write_exr, .pfm -> develop_rgb + write_pfm, anything else -> the raw XYZAW floats
-void write_film(const std::string &out, const std::vector<float> &xyzaw, int width, int height);
+void write_film(const std::string &out, const std::vector<float> &xyzaw, int width, int height, bool half = false);
 
 }  // namespace vrlhost

@@ -33,6 +33,7 @@ struct LoadedScene {
     HostSensor  sensor;
     Properties  integrator{ "vrl" };
     std::string integrator_type;                 // "" when the file has no <integrator>
+    bool film_half = true;                       // hdrfilm component_format: float16 (the default, hdrfilm.cpp:108-109) or float32
     std::vector<std::string> warnings;
     std::vector<std::string> media_ids;          // XML id of media[i]
     std::vector<std::unique_ptr<std::vector<float>>> grids;   // storage behind vrlb_medium::grid pointers

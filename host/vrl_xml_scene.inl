@@ -253,6 +253,9 @@ struct Builder {
         { const Node *rf = film ? child_named(*film, "rfilter", nullptr) : nullptr;                          // film.cpp:36-48: no <rfilter> = gaussian
           const std::string rt = rf ? rf->get("type") : std::string("gaussian");
           if (rt != "box") warn("rfilter type=\"" + rt + "\"" + (rf ? "" : " (the film's default)") + ": the device film splats with the box filter (imageblock.cpp:162-169 fast path)"); }
+        if (film) { const std::string cf = prop_string(*film, "component_format", "float16");               // hdrfilm.cpp:108-160
+                    out.film_half = cf == "float16";
+                    if (cf != "float16" && cf != "float32") warn("film component_format=\"" + cf + "\": written as float32"); }
         out.sensor.spp = sampler ? (int32_t) prop_int(*sampler, "sample_count", 4) : 4;                      // sampler.cpp:11
         out.sensor.sampler_seed = sampler ? (uint64_t) prop_int(*sampler, "seed", 0) : 0;
         if (sampler && sampler->get("type") != "independent") warn("sampler type=\"" + sampler->get("type") + "\": the path addresses independent PCG32 streams");

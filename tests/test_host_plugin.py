@@ -180,6 +180,14 @@ def test_developed_film_as_exr_and_pfm(tmp_path):
         assert dec.shape == (h, w, 4) and dec.dtype == np.float32
         assert np.array_equal(dec[..., 2], img[..., 3]) and np.array_equal(dec[..., 1], img[..., 2])
         assert np.array_equal(dec[..., 0], img[..., 1]) and np.array_equal(dec[..., 3], img[..., 0])
+    # component_format float16 (the film's default): HALF channels, round to nearest even like numpy's float16
+    exr16 = os.path.join(str(tmp_path), "film16.exr")
+    subprocess.check_call([host, "convert-film", raw, str(w), str(h), exr16, "float16"])
+    b16 = open(exr16, "rb").read()
+    assert len(b16) < len(open(exr, "rb").read())
+    if dec is not None:
+        dec16 = cv2.imread(exr16, cv2.IMREAD_UNCHANGED)
+        assert np.array_equal(dec16, dec.astype(np.float16).astype(np.float32))
     # the PFM holds the same RGB, bottom row first
     b = open(pfm, "rb").read()
     head = b"PF\n%d %d\n-1.0\n" % (w, h)
