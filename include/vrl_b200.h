@@ -247,6 +247,21 @@ int  vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64
  *                      the set keeps VRL-major order and its m_scale.  Homogeneous / nonlinear media only. */
 int  vrlb_vrls_to_long(vrlb_context *ctx);
 int  vrlb_vrls_dice(vrlb_context *ctx, uint32_t avg_number_dice, uint64_t *n_vrls_out);
+/* vrlb_vrls_dice for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same pieces as
+ * vrlb_vrls_dice (VRL::dice arithmetic, VRL-major order) for one homogeneous medium of grey extinction `max_density`
+ * (= scale * mean(sigma_t)), but every buffer is the caller's and lives on `device`: d_soa10 = the 10 columns of the
+ * input set (column c of VRL j at d_soa10[c*n + j]); d_soa10_out = the diced set with column stride cap_out (column c
+ * of piece i at d_soa10_out[c*cap_out + i]); d_n_out = two uint64 on the device: [0] the diced size, [1] a status
+ * (0 ok; 1 the mean length is not positive; 2 the diced size exceeds cap_out -- in both cases nothing is written).
+ * The work is enqueued on `cuda_stream` (cudaStream_t as void*, NULL = the default stream) and the call returns without
+ * synchronising.  It calls no cudaMalloc / cudaFree: the piece counts and offsets live in a static __device__ array
+ * sized for VRLB_NOALLOC_MAX_VRLS input VRLs (~0.75 MB held by every GPU that loads the library, until exit); a larger
+ * n is VRLB_ERR_INVALID (message through vrlb_last_error(NULL)).  All calls on a device share that array: calls that
+ * overlap on the GPU (two streams, two threads) race -- serialise them. */
+#define VRLB_NOALLOC_MAX_VRLS 65536u
+int  vrlb_vrls_dice_noalloc(int device, void *cuda_stream, const float *d_soa10, uint64_t n, float max_density,
+                            uint32_t avg_number_dice, float *d_soa10_out, uint64_t cap_out, uint64_t *d_n_out);
 
 /* ---- volume photon map: the direct in-scattering term of VRLIntegrator::sample (vrl.cpp:523-611) ----------------------
  * A resident photon set switches the term on (`use_direct_illum`): vrlb_gather / vrlb_render then add, for every in-medium

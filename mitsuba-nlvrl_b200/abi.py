@@ -2,6 +2,7 @@
 import ctypes as C
 
 COMM_ID_BYTES = 128
+NOALLOC_MAX_VRLS = 65536
 OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CANCELLED, ERR_NOMEM = 0, -1, -2, -3, -4, -5
 
 SURF_BSDF_SMOOTH, SURF_BSDF_NULL, SURF_EMITTER, SURF_TWOSIDED = 0x0, 0x1, 0x4, 0x8

@@ -20,7 +20,7 @@ EXPORTS = [
     "vrlb_film_device_ptr", "vrlb_film_download_xyzaw", "vrlb_film_download_rgb", "vrlb_render", "vrlb_cancel",
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
-    "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice",
+    "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice", "vrlb_vrls_dice_noalloc",
     "vrlb_surface_photons_upload", "vrlb_surface_photons_generate", "vrlb_surface_photons_count", "vrlb_surface_photons_download",
     "vrlb_surface_queries_upload", "vrlb_surface_queries_download", "vrlb_surface_gather_queries",
     "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments", "vrlb_photons_generate", "vrlb_photons_download",
@@ -98,6 +98,7 @@ def load_library():
     L.vrlb_vrls_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.vrlb_vrls_to_long.argtypes = [vp]
     L.vrlb_vrls_dice.argtypes = [vp, C.c_uint32, C.POINTER(C.c_uint64)]
+    L.vrlb_vrls_dice_noalloc.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_float, C.c_uint32, vp, C.c_uint64, vp]
     L.vrlb_photons_upload.argtypes = [vp, C.POINTER(abi.PhotonSetDesc)]
     L.vrlb_photons_count.argtypes = [vp]
     L.vrlb_photons_generate.argtypes = [vp, C.POINTER(abi.GenerateDesc), C.c_uint64, C.c_float, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]

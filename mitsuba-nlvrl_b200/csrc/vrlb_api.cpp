@@ -160,6 +160,8 @@ float elapsed(cudaEvent_t a, cudaEvent_t b) { float ms = 0.f; cudaEventElapsedTi
 
 }  // namespace
 
+namespace vrlb { void set_global_error(const char *msg) { g_create_error = msg ? msg : ""; } }
+
 extern "C" {
 
 int vrlb_abi_version(void) { return VRLB_ABI_VERSION; }

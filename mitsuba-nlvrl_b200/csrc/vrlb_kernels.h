@@ -125,6 +125,9 @@ struct SurfaceGatherParams {
 };
 cudaError_t launch_surface_gather(const SurfaceGatherParams &p, cudaStream_t stream);
 
+// message returned by vrlb_last_error(NULL), for entry points that take no context (noalloc.cu)
+void set_global_error(const char *msg);
+
 // FFMA-saturating microkernel (peak.cu)
 cudaError_t launch_fp32_peak(float *scratch, int blocks, int iters, cudaStream_t stream);
 
