@@ -10,7 +10,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libvrl_b200.so")
+LIB_PATH = os.environ.get("VRLB_LIB_PATH") or os.path.join(_HERE, "csrc", "libvrl_b200.so")   # the override is for kernel-variant experiments (tools/)
 
 # every symbol include/vrl_b200.h declares
 EXPORTS = [

@@ -204,7 +204,11 @@ void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, S
     for (uint32_t i = 0; i < n; ++i) subsets[subset_of(i)].push_back(i);
     float ext = 0.f;
     for (uint32_t i = 0; i < n * 9; ++i) ext = std::max(ext, std::fabs(verts[i]));
-    const float margin = 1e-3f * ext + 1e-6f;
+    // Safety margin of the shell boxes and the solids' proxies.  It has to cover the fp32 error of the device's tests and of
+    // the fast path's end points (a few 1e-6 * ext) and the graze margins of intersect_tri_graze (2e-4 + 1e-5 * length);
+    // every eval with an end point closer than this to a shell goes to the BVH, and importance sampling puts ~1 % of the
+    // end points within 1e-3 * ext of a wall (VRLs and camera parts END on walls), so it is not chosen any larger.
+    const float margin = 1e-4f * ext + 3e-4f;
     for (size_t s = 0; s < subsets.size(); ++s) {
         const std::vector<uint32_t> &sub = subsets[s];
         uint32_t root_ref = 0x80000000u;          // empty leaf

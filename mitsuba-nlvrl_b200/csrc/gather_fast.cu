@@ -131,10 +131,15 @@ struct Guard { float h2min, zmax; };
 // flux * sigma_s(cam) * sigma_s(vrl) * m_scale BEFORE the shadow test (the segment to trace is returned in so / sd /
 // sdist when VIS), 0 where the reference returns 0.  `slow` is set (and nothing
 // else computed) when the guard wants the exact path.
+// What the visibility kernel needs of an eval's connection segment pCam -> pVRL: its start, the unnormalised direction,
+// |dir|^2 and 1/|dir|, and the two sampled parameters BEFORE the clamp of vrl_struct.h:340-341 (pCam / pVRL are computed
+// from the unclamped values there, so these are the parameters of the segment's end points on the camera part / the VRL).
+struct Conn { V3 pCam, dir; float d2, rd, tCam, tVRL; };
+
 template <bool UNIFORM, bool VIS, bool ISO, bool GUARD, class Seg>
 __device__ __forceinline__ float contrib_fast(const DScene &scene, const Seg &ray, V3 vo, V3 vd, float vlen,
                                               float max_density, float g, float u1, float u2, Guard guard, bool &slow,
-                                              V3 &so, V3 &sd, float &sdist) {
+                                              Conn &cn) {
     V3 pCam, pVRL; float tCam, tVRL, invPDF;
     slow = false;
     if (UNIFORM) {
@@ -143,6 +148,7 @@ __device__ __forceinline__ float contrib_fast(const DScene &scene, const Seg &ra
         pCam = fmad3(ray.o, ray.d, tCam);
         pVRL = fmad3(vo, vd, tVRL);
         invPDF = vlen * ray.maxt;
+        if (VIS) { cn.tCam = tCam; cn.tVRL = tVRL; }
     } else {
         float cpCam, cpVRL;
         closest_fast(vo, vd, vlen, ray, cpCam, cpVRL);
@@ -185,6 +191,7 @@ __device__ __forceinline__ float contrib_fast(const DScene &scene, const Seg &ra
         float invPDF_B = (thetaB - thetaA) * fmaf(uS, uS, hp2) * rhp;
         tCam = uS - u0Hat;
         pCam = fmad3(ray.o, ray.d, tCam);
+        if (VIS) { cn.tCam = tCam; cn.tVRL = tVRL; }
         tCam = fminf(fmaxf(tCam, 0.0f), ray.maxt);               // vrl_struct.h:340-341
         tVRL = fminf(fmaxf(tVRL, 0.0f), vlen);
         invPDF = invPDF_A * invPDF_B;
@@ -203,7 +210,7 @@ __device__ __forceinline__ float contrib_fast(const DScene &scene, const Seg &ra
         pf = rayPF * vrlPF;
         if (pf == 0.f) return 0.f;
     }
-    if (VIS) { so = pCam; sd = dir * rd; sdist = dist; }          // shadow segment, traced by the caller (vrl_struct.h:509-572)
+    if (VIS) { cn.pCam = pCam; cn.dir = dir; cn.d2 = d2; cn.rd = rd; }   // shadow segment, classified by the caller (vrl_struct.h:509-572)
     // three homogeneous transmittances, medium.h:112-117: exp(-sigma (dist + tCam + tVRL)) in one MUFU.EX2
     float tr = f_ex2(-(max_density * kLog2e) * (dist + tCam + tVRL));
     if (tr == 0.f) return 0.f;
@@ -293,8 +300,8 @@ gather_fast_kernel(GatherParams p) {
                 float g = 0.f;
                 if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
                 bool slow;
-                V3 so, sd; float sdist;
-                float f = contrib_fast<UNIFORM, false, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, so, sd, sdist);
+                Conn cn;
+                float f = contrib_fast<UNIFORM, false, ISO, GUARD>(p.scene, ray, vo, vd, vlen, c.w, g, u1, u2, guard, slow, cn);
                 if (GUARD && slow) {                                      // ill-conditioned eval: exactly-rounded path
                     const DMedium &m = media[__float_as_uint(b.w)];
                     SegRegs er; er.o = ray.o; er.d = ray.d; er.maxt = ray.maxt;
@@ -332,33 +339,36 @@ gather_fast_kernel(GatherParams p) {
     }
 }
 
-// ---- shadow phase: in-warp ray queue with persistent lanes ------------------------------------------------
-// The shadow query is the divergent part of an eval (traversal length varies 2..80 node visits per ray).  Done
-// inline, every lane waits for the slowest ray of its warp at every VRL (measured: 9.8 of 32 lanes active,
-// profiles/r01b_gather_v2_fast.txt).  Instead a warp shades NB VRLs for its 32 camera segments in lock step
-// (phase A, fully converged), parks the NB*32 shadow segments in shared memory, and then traces them with
-// persistent lanes: whenever a lane finishes a ray it pulls the next one from the queue (phase B), so lanes stay
-// busy until the queue runs dry.  Phase C adds the surviving contributions in VRL order (lane-private slots,
-// deterministic).  B200 has no RT cores: this is plain SIMT traversal with warp-level ray compaction.
-constexpr int NB    = 4;                 // pending shadow segments a lane may park before the warp traces
-constexpr int VTILE = 64, NBUF = 4;     // VRL ring of the visibility kernel: NBUF tiles of VTILE records
-constexpr int QCAP  = NB * 32;           // shadow-segment slots per warp
-constexpr int QF    = 11;                // floats per slot: o(3) d(3) dist alive r g b
-constexpr float Q_RESOLVED = -1.f, Q_REDO = -2.f, Q_SLOW = -3.f;   // dist markers: no trace needed / re-evaluate exactly / exact eval pending
+// ---- shadow phase: convergent classification + a persistent, compacted trace buffer ------------------------
+// The shadow query is the divergent part of an eval: most connection segments miss every occluder's bounding volume,
+// some need the finer proxies, ~1 % need the BVH (2..80 node visits).  Done inline with per-lane branches, every lane
+// waits for the slowest lane of its warp at every VRL.  Here the VRL loop keeps all 32 lanes on ONE instruction
+// stream: the levels of a solid's proxies are gated by warp votes and evaluated predicated (classify_segment), the
+// shells cost four compares against precomputed parameter intervals, and a segment that is still undecided is
+// appended -- ballot-compacted -- to the warp's TRACE BUFFER together with its contribution.  The buffer persists
+// across VRLs and tiles and is traced through the BVHs only when >= 32 rays are waiting (drain_trace, out of line):
+// persistent lanes, a lane that finishes a ray pulls the next one; node steps and triangle tests are separated, leaf
+// hits go to a leaf queue and are tested 32 at a time.  Contributions are added by their owner lane in buffer order,
+// so the sum of a lane is deterministic.  B200 has no RT cores: plain SIMT traversal with warp-level ray compaction.
+constexpr int VTILE = 64, NBUF = 4;      // VRL ring of the visibility kernel: NBUF tiles of VTILE 64-byte records
+constexpr int DRAIN_WINDOW = 8;          // tiles between forced drains of the trace buffer (512 VRLs)
+constexpr int TCAP  = 64;                // trace buffer: rays waiting for the BVH (traced when >= 32 are pending)
+constexpr int QF    = 11;                // floats per ray: o(3) d(3) dist alive r g b
+constexpr float Q_REDO = -2.f;           // dist marker: hit decision inside the graze margins, re-evaluate exactly
 
-struct WarpQueue {
-    float    v[QF][QCAP];                // SoA: consecutive lanes -> consecutive banks
-    uint16_t roots[QCAP];                // per slot: which roots to visit (roots_mask)
-    uint16_t list[QCAP];                 // compacted slot indices that need tracing
-    uint16_t vj[QCAP];                   // per slot: index of the VRL in the current tile (exact re-evaluation)
-    uint32_t lq[128];                    // pending leaf entries: (first triangle << 12) | (count << 7) | slot
+struct WarpBuf {
+    float    v[QF][TCAP];                // trace buffer, SoA: consecutive rays -> consecutive banks
+    uint32_t jg[TCAP];                   // per ray: index of the VRL in this rank's shard (exact re-evaluation)
+    uint16_t roots[TCAP];                // per ray: which roots to visit
+    uint16_t own[TCAP];                  // per ray: owner lane | query sample index << 5
+    uint32_t lq[128];                    // pending leaf entries: (first triangle << 12) | (count << 7) | ray
 };
 
 struct RayState {
     V3 o, d, inv; float dist;
     uint32_t cur;        // current wide node
     int sp;              // stack pointer
-    uint32_t roots;      // bit 0: main BVH pending, bit 1 + i: shell i pending (decided in phase A)
+    uint32_t roots;      // bit 0: main BVH pending, bit 1 + i: shell i pending, bit 9 + i: solid i pending
 };
 
 __device__ __forceinline__ bool shell_inside(const DShell &sh, V3 o, V3 e) {
@@ -366,70 +376,76 @@ __device__ __forceinline__ bool shell_inside(const DShell &sh, V3 o, V3 e) {
            e.x > sh.lo[0] && e.x < sh.hi[0] && e.y > sh.lo[1] && e.y < sh.hi[1] && e.z > sh.lo[2] && e.z < sh.hi[2];
 }
 
-// One solid against the shadow segment o + t d, t in [0, dist] (d unit, e = end point):
-// 0 = cannot hit it, 1 = undecided (traverse its BVH), 2 = certainly occluded by it.  See occluder_proxies.cpp.
-// Cheapest rejection first: most segments miss the bounding sphere and leave after ~15 instructions.
-__device__ __forceinline__ int solid_test(const DSolid &S, float4 bs, uint32_t flags, V3 o, V3 d, V3 e, float dist) {
-    V3 oc(bs.x - o.x, bs.y - o.y, bs.z - o.z);
-    const float t = fminf(fmaxf(fdot(oc, d), 0.f), dist);        // closest approach of the segment to the centre
-    V3 q = fmad3(oc, d, -t);
-    if (fdot(q, q) > bs.w) return 0;
-    // inner proxies count only for a segment that enters from outside: an end point outside the bounding sphere
-    V3 ec(bs.x - e.x, bs.y - e.y, bs.z - e.z);
-    const bool enters = fdot(oc, oc) > bs.w || fdot(ec, ec) > bs.w;
-    if (enters && (flags & VRLB_SOLID_INNER_SPHERE)) {
-        V3 oi(S.ci[0] - o.x, S.ci[1] - o.y, S.ci[2] - o.z);
-        const float ti = fminf(fmaxf(fdot(oi, d), 0.f), dist);
-        V3 qi = fmad3(oi, d, -ti);
-        if (fdot(qi, qi) <= S.r_in2) return 2;
-    }
-    if (flags & (VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB)) {
-        V3 r(o.x - S.oc[0], o.y - S.oc[1], o.z - S.oc[2]);
-        V3 ol(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), r), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), r), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), r));
-        V3 dl(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), d), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), d), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), d));
-        V3 il(f_rcp(dl.x), f_rcp(dl.y), f_rcp(dl.z));
-        if ((flags & VRLB_SOLID_OUTER_OBB) &&
-            !slab2(-S.h_out[0], -S.h_out[1], -S.h_out[2], S.h_out[0], S.h_out[1], S.h_out[2], il, ol, 0.f, dist)) return 0;
-        if (enters && (flags & VRLB_SOLID_INNER_OBB)) {
-            float ax = (-S.h_in[0] - ol.x) * il.x, bx = (S.h_in[0] - ol.x) * il.x;
-            float ay = (-S.h_in[1] - ol.y) * il.y, by = (S.h_in[1] - ol.y) * il.y;
-            float az = (-S.h_in[2] - ol.z) * il.z, bz = (S.h_in[2] - ol.z) * il.z;
-            float t0 = fmaxf(fmaxf(0.f, fminf(ax, bx)), fmaxf(fminf(ay, by), fminf(az, bz)));
-            float t1 = fminf(fminf(dist, fmaxf(ax, bx)), fminf(fmaxf(ay, by), fmaxf(az, bz)));
-            if (t0 <= t1) return 2;                       // strict: the box is already pulled in by the margin
-        }
-    }
-    return 1;
-}
-
-// which roots the shadow segment has to visit: bit 0 = main BVH (its root box is hit), bit 1 + i = shell i (an end
-// point is not strictly inside it), bit 9 + i = solid i (undecided by its proxies).  `occluded` = a solid's inner proxy
-// already decides the query.  Evaluated in phase A with all lanes converged.
-// `cs` is the scene as the kernel PARAMETER (constant bank: its counts and root box cost no load and no register);
-// `bsph` / `sflags` are the solids' bounding spheres (one LDS.128 each) and their proxy flags, 3 bits per solid.
-__device__ __forceinline__ uint32_t roots_mask(const DScene &cs, const DSolid *solids, const float4 *bsph, uint32_t sflags,
-                                               const float (&safe)[6], V3 o, V3 d, float dist, bool &occluded) {   // safe = p.safe
+// Classification of one connection segment o + t dir, t in [0, 1] (dir NOT normalised, inv_d2 = 1 / |dir|^2), with all
+// lanes of the warp on one instruction stream.  Returns which roots the segment has to visit -- bit 0 = main BVH (its
+// root box is met), bit 1 + i = shell i (an end point is not strictly inside it), bit 9 + i = solid i (undecided by its
+// proxies); `occluded` = a closed solid's inner proxy already decides the query.  Per solid (occluder_proxies.cpp):
+// bounding sphere missed -> cannot hit it; then, only if some lane of the warp got that far (warp vote), the finer
+// proxies the solid carries: inscribed sphere met by a segment that enters from outside -> occluded; outer oriented box
+// missed -> cannot hit; inscribed box met -> occluded.  `cs` is the scene as the kernel PARAMETER (constant bank).
+__device__ __forceinline__ uint32_t classify_segment(const DScene &cs, const DSolid *solids, const float4 *bsph, uint32_t sflags,
+                                                     V3 o, V3 dir, float inv_d2, bool notsafe, bool active, bool &occluded) {
     uint32_t m = 0;
-    occluded = false;
-    V3 e = fmad3(o, d, dist);
+    bool occ = false;
+    const V3 e = o + dir;
     const int n_solids = cs.n_solids;
 #pragma unroll 1
     for (int i = 0; i < n_solids; ++i) {
-        int r = solid_test(solids[i], bsph[i], (sflags >> (3 * i)) & 7u, o, d, e, dist);
-        if (r == 2) { occluded = true; return 0; }
-        if (r == 1) m |= 512u << i;
+        const float4 bs = bsph[i];
+        const V3 oc(bs.x - o.x, bs.y - o.y, bs.z - o.z);
+        const float t = fminf(fmaxf(fdot(oc, dir) * inv_d2, 0.f), 1.f);   // closest approach of the segment to the centre
+        const V3 q = fmad3(oc, dir, -t);
+        const bool touch = active && fdot(q, q) <= bs.w;
+        if (!__any_sync(0xffffffffu, touch)) continue;
+        const uint32_t fl = (sflags >> (3 * i)) & 7u;
+        const DSolid &S = solids[i];
+        // inner proxies count only for a segment that enters from outside: an end point outside the bounding sphere
+        const V3 ec(bs.x - e.x, bs.y - e.y, bs.z - e.z);
+        const bool enters = fdot(oc, oc) > bs.w || fdot(ec, ec) > bs.w;
+        bool und = touch, hit = false;
+        if (fl & VRLB_SOLID_INNER_SPHERE) {
+            const V3 oi(S.ci[0] - o.x, S.ci[1] - o.y, S.ci[2] - o.z);
+            const float ti = fminf(fmaxf(fdot(oi, dir) * inv_d2, 0.f), 1.f);
+            const V3 qi = fmad3(oi, dir, -ti);
+            if (und && enters && fdot(qi, qi) <= S.r_in2) { hit = true; und = false; }
+        }
+        if ((fl & (VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB)) && __any_sync(0xffffffffu, und)) {
+            const V3 r(o.x - S.oc[0], o.y - S.oc[1], o.z - S.oc[2]);
+            const V3 ol(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), r), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), r), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), r));
+            const V3 dl(fdot(V3(S.ax[0], S.ax[1], S.ax[2]), dir), fdot(V3(S.ax[3], S.ax[4], S.ax[5]), dir), fdot(V3(S.ax[6], S.ax[7], S.ax[8]), dir));
+            const V3 il(f_rcp(dl.x), f_rcp(dl.y), f_rcp(dl.z));
+            bool enters_b = enters;
+            if (fl & VRLB_SOLID_OUTER_OBB) {
+                if (!slab2(-S.h_out[0], -S.h_out[1], -S.h_out[2], S.h_out[0], S.h_out[1], S.h_out[2], il, ol, 0.f, 1.f)) und = false;
+                // an end point outside the outer box is outside the solid as well (importance sampling favours short
+                // connections: both ends inside the bounding sphere of a box-like solid is common)
+                const V3 el = ol + dl;
+                enters_b = enters_b || fabsf(ol.x) > S.h_out[0] || fabsf(ol.y) > S.h_out[1] || fabsf(ol.z) > S.h_out[2] ||
+                           fabsf(el.x) > S.h_out[0] || fabsf(el.y) > S.h_out[1] || fabsf(el.z) > S.h_out[2];
+            }
+            if (fl & VRLB_SOLID_INNER_OBB) {
+                const float ax = (-S.h_in[0] - ol.x) * il.x, bx = (S.h_in[0] - ol.x) * il.x;
+                const float ay = (-S.h_in[1] - ol.y) * il.y, by = (S.h_in[1] - ol.y) * il.y;
+                const float az = (-S.h_in[2] - ol.z) * il.z, bz = (S.h_in[2] - ol.z) * il.z;
+                const float t0 = fmaxf(fmaxf(0.f, fminf(ax, bx)), fmaxf(fminf(ay, by), fminf(az, bz)));
+                const float t1 = fminf(fminf(1.f, fmaxf(ax, bx)), fminf(fmaxf(ay, by), fmaxf(az, bz)));
+                if (und && enters_b && t0 <= t1) { hit = true; und = false; }   // strict: the box is already pulled in by the margin
+            }
+        }
+        occ = occ || hit;
+        if (und) m |= 512u << i;
     }
     if (cs.main_root != 0x80000000u) {
-        V3 inv(f_rcp(d.x), f_rcp(d.y), f_rcp(d.z));
-        if (slab2(cs.main_lo[0], cs.main_lo[1], cs.main_lo[2], cs.main_hi[0], cs.main_hi[1], cs.main_hi[2], inv, o, 0.f, dist)) m |= 1u;
+        const V3 inv(f_rcp(dir.x), f_rcp(dir.y), f_rcp(dir.z));
+        if (active && slab2(cs.main_lo[0], cs.main_lo[1], cs.main_lo[2], cs.main_hi[0], cs.main_hi[1], cs.main_hi[2], inv, o, 0.f, 1.f)) m |= 1u;
     }
-    // shells: `safe` is the intersection of all shell boxes (registers); only a segment with an end point outside it
-    // has to look at the individual shells
-    const bool in_safe = o.x > safe[0] && o.x < safe[3] && o.y > safe[1] && o.y < safe[4] && o.z > safe[2] && o.z < safe[5] &&
-                         e.x > safe[0] && e.x < safe[3] && e.y > safe[1] && e.y < safe[4] && e.z > safe[2] && e.z < safe[5];
-    if (!in_safe)
-        for (int i = 0; i < cs.n_shells; ++i) if (!shell_inside(cs.shells[i], o, e)) m |= 2u << i;
-    return m;
+    // shells: only a segment with an end point outside the safe box has to look at the individual shells
+    if (__any_sync(0xffffffffu, notsafe && active)) {
+        if (notsafe && active)
+            for (int i = 0; i < cs.n_shells; ++i) if (!shell_inside(cs.shells[i], o, e)) m |= 2u << i;
+    }
+    occluded = occ;
+    return occ ? 0u : m;
 }
 __device__ __forceinline__ bool next_root(const DScene &s, RayState &r, uint32_t &root) {
     if (r.roots == 0) return false;
@@ -439,12 +455,12 @@ __device__ __forceinline__ bool next_root(const DScene &s, RayState &r, uint32_t
     return true;
 }
 
-// Phase B.  `cnt` listed slots; on return q.v[7][slot] = 0 for occluded segments and q.v[6][slot] = Q_REDO for
+// Tracing.  `cnt` rays in the buffer; on return q.v[7][ray] = 0 for occluded segments and q.v[6][ray] = Q_REDO for
 // segments whose hit decision fell inside the graze margins.  Two kinds of work, each done by all 32 lanes at
-// once: node steps (one DWNode visit per active lane; lanes that finish a ray pull the next from q.list) and
-// leaf entries (slot, leaf) that the node steps append to q.lq -- as soon as 32 are pending every lane tests one
+// once: node steps (one DWNode visit per active lane; lanes that finish a ray pull the next one) and
+// leaf entries (ray, leaf) that the node steps append to q.lq -- as soon as 32 are pending every lane tests one
 // leaf's triangles.  Triangle tests at 1-3 active lanes were what held the inline traversal at 10 of 32 lanes.
-__device__ __forceinline__ void process_leaves(const DScene &s, WarpQueue &q, int first, int n, unsigned lane) {
+__device__ __forceinline__ void process_leaves(const DScene &s, WarpBuf &q, int first, int n, unsigned lane) {
     if ((int) lane < n) {
         uint32_t ent = q.lq[first + lane];
         int slot = (int) (ent & 127u);
@@ -464,15 +480,19 @@ __device__ __forceinline__ void process_leaves(const DScene &s, WarpQueue &q, in
     }
 }
 
-__device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int cnt, uint32_t *wd) {
+// Traversal stack: build_shadow_accel bounds the depth of every BVH it emits (bvh_build.cpp, kMaxShadowDepth) so
+// that depth + the single-leaf roots pushed up front stays below this.
+constexpr int TRACE_STACK = 48;
+template <bool WATCHDOG>
+__device__ __forceinline__ void trace_queue(const DScene &s, WarpBuf &q, int cnt, uint32_t *wd) {
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
     int head = 0, slot = 0, lqn = 0;
     bool active = false;
     RayState r;
-    uint32_t stack[24];
+    uint32_t stack[TRACE_STACK];
     r.sp = 0; r.cur = 0; r.roots = 0; r.dist = 0.f;
     for (uint32_t steps = 0; ; ++steps) {
-        if (steps > (1u << 22)) {                                  // watchdog: a batch takes a few hundred steps
+        if (WATCHDOG && steps > (1u << 22)) {                      // a batch takes a few hundred steps
             if (wd && atomicCAS(wd, 0u, 2u) == 0u) { wd[1] = blockIdx.x; wd[2] = threadIdx.x; wd[3] = (uint32_t) cnt; wd[4] = (uint32_t) head; wd[5] = r.cur; wd[6] = (uint32_t) r.sp; __threadfence_system(); }
             __trap();
         }
@@ -492,7 +512,7 @@ __device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int c
             if (avail > 0) {
                 int rank = __popc(idle & lt);
                 if (!active && rank < avail) {
-                    slot = q.list[head + rank];
+                    slot = head + rank;
                     r.o = V3(q.v[0][slot], q.v[1][slot], q.v[2][slot]);
                     r.d = V3(q.v[3][slot], q.v[4][slot], q.v[5][slot]);
                     r.dist = q.v[6][slot];
@@ -547,7 +567,7 @@ __device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int c
                 active = more;
             }
         }
-        // append leaf entries: leaf reference | slot
+        // append leaf entries: leaf reference | ray
         {
             unsigned m0 = __ballot_sync(0xffffffffu, leaf0 != 0);
             if (leaf0) q.lq[lqn + __popc(m0 & lt)] = leaf0 | (uint32_t) slot;
@@ -561,9 +581,8 @@ __device__ __forceinline__ void trace_queue(const DScene &s, WarpQueue &q, int c
     if (lqn > 0) process_leaves(s, q, 0, lqn, lane);
 }
 
-// the exactly-rounded eval with its inline shadow traversal, out of line: it runs for < 1 % of the evals and would
-// otherwise be inlined twice into the kernel (instruction-cache misses were 2.7 stalled warps per issue)
-// the exactly-rounded eval without its shadow query: seg[0..6] = pCam, direction, length of the connection
+// the exactly-rounded eval, out of line: it runs for < 1 % of the evals (instruction-cache footprint).
+// exact_eval_seg: without the shadow query; seg[0..6] = pCam, direction, length of the connection
 template <bool UNIFORM>
 __device__ __noinline__ float exact_eval_seg(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
                                              float max_density, int phase, float g, float u1, float u2, float *seg) {
@@ -576,8 +595,14 @@ __device__ __noinline__ float exact_eval_vis(const DScene &scene, const SegRegs 
     return eval_contrib<UNIFORM, true>(scene, ray, vo, vd, vlen, max_density, phase, g, u1, u2);
 }
 
-// Watchdog for the ring: a wait that outlasts ~2 s (a tile takes ~0.1 ms) writes the CTA's ring state to pinned host
-// memory and traps, so that a lost hand-over surfaces as an error with evidence instead of a silent hang.
+// Watchdog for the ring (debug builds, -DVRLB_WATCHDOG): a wait that outlasts ~2 s (a tile takes ~0.1 ms) writes the
+// CTA's ring state to pinned host memory and traps, so that a lost hand-over surfaces as an error with evidence
+// instead of a silent hang.  Off in production: the clock reads were 3 % of the issued instructions.
+#ifdef VRLB_WATCHDOG
+constexpr bool kWatchdog = true;
+#else
+constexpr bool kWatchdog = false;
+#endif
 __device__ __noinline__ void ring_watchdog_trip(uint32_t *wd, uint32_t code, uint32_t it, uint32_t buf,
                                                 const uint32_t *warp_it, const uint64_t *bars) {
     if (wd && atomicCAS(wd, 0u, code) == 0u) {
@@ -597,104 +622,148 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t *bar, uint32_t parity, uin
         asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}\n"
                      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(20000u) : "memory");
         if (ok) return;
-        // a warp that ran ahead of the producer waits here for a tile (~0.1 ms of work): sleep instead of spinning, the
-        // spin loop was 5 % of all issued instructions (profiles/r01k_gather_v2_lines.txt)
-        __nanosleep(spins < 4 ? 512u : 4096u);
-        if (spins == 4) t0 = clock64();
-        else if (spins > 4 && (spins & 15u) == 0 && clock64() - t0 > 4000000000LL) ring_watchdog_trip(wd, code, it, buf, warp_it, bars);
+        // a warp that ran ahead of the producer waits here for a tile (~0.1 ms of work): sleep instead of spinning
+        __nanosleep(spins < 2 ? 2000u : 10000u);               // a tile is ~150 us of work for a warp
+        if (kWatchdog) {
+            if (spins == 4) t0 = clock64();
+            else if (spins > 4 && (spins & 15u) == 0 && clock64() - t0 > 4000000000LL) ring_watchdog_trip(wd, code, it, buf, warp_it, bars);
+        }
     }
 }
 
-// Trace what the warp has parked and return the sum of the surviving contributions of this lane (lane-private slots,
-// deterministic order).  Out of line: the flush runs once per few dozen VRLs, and keeping the traversal's registers
-// out of the shading loop is worth a third CTA per SM.
 struct Acc3 { float r, g, b; };
+
+// What a drain needs beyond the warp's buffer, in one struct so the out-of-line call passes one pointer.
+struct DrainCtx {
+    const DScene  *S;
+    const DMedium *media;
+    const DVrlV   *vrls;         // this rank's shard (global memory): exact re-evaluation of traced rays
+    uint64_t first_index, total; // stream addressing (GatherParams)
+    float    scale_rr;
+    uint32_t *wd;
+};
+
+// Trace the n rays waiting in the buffer and let every lane add what survives of its own (buffer order).  Out of
+// line: it runs once per ~100 VRLs and keeps the traversal's registers out of the shading loop.
 template <bool UNIFORM, bool RR>
-__device__ __noinline__ Acc3 flush_queue(const DScene &S, WarpQueue &q, const DVrl *tile_buf, const DMedium *media, int npend,
-                                         uint64_t rng_tile, const SegRegs &er, float scale_rr, uint32_t *wd) {
-    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+__device__ __noinline__ Acc3 drain_trace(const DrainCtx &fc, WarpBuf &q, int n, const SegRegs &er, uint64_t rng0) {
+    const unsigned lane = threadIdx.x & 31u;
     constexpr uint32_t DPE = RR ? 3u : 2u;
     Acc3 acc = { 0.f, 0.f, 0.f };
-    int qn = 0;
-#pragma unroll
-    for (int k = 0; k < NB; ++k) {
-        const bool need = k < npend;
-        const unsigned m = __ballot_sync(0xffffffffu, need);
-        if (need) q.list[qn + __popc(m & lt)] = (uint16_t) (k * 32 + (int) lane);
-        qn += __popc(m);
+    __syncwarp();
+    trace_queue<kWatchdog>(*fc.S, q, n, fc.wd);
+    __syncwarp();
+    // lane-parallel: occluded rays contribute nothing; graze decisions are re-evaluated exactly by their owner below
+    bool any_redo = false;
+    for (int i = (int) lane; i < n; i += 32) {
+        const bool redo = q.v[6][i] == Q_REDO;
+        if (redo || q.v[7][i] == 0.f) { q.v[8][i] = 0.f; q.v[9][i] = 0.f; q.v[10][i] = 0.f; }
+        any_redo = any_redo || redo;
     }
+    any_redo = __any_sync(0xffffffffu, any_redo);
     __syncwarp();
-    trace_queue(S, q, qn, wd);
-    __syncwarp();
-    for (int k = 0; k < npend; ++k) {
-        const int slot = k * 32 + (int) lane;
-        float cr = q.v[8][slot], cg = q.v[9][slot], cb = q.v[10][slot];
-        if (q.v[6][slot] == Q_REDO) {              // graze margin: exactly-rounded eval + exact trace
-            const uint32_t j = q.vj[slot];
-            const float4 *vp = reinterpret_cast<const float4 *>(tile_buf + j);
-            float4 a = vp[0], b = vp[1], c = vp[2];
-            const DMedium &m = media[__float_as_uint(b.w)];
-            Pcg32 rr; rr.state = rng_tile;
-            for (uint32_t d = 0; d < j * DPE + (RR ? 1u : 0u); ++d) rr.next_u32();
+    for (int i = 0; i < n; ++i) {                  // uniform loop, broadcast reads: the owner adds
+        const bool mine = (q.own[i] & 31u) == lane;
+        const float cr = q.v[8][i], cg = q.v[9][i], cb = q.v[10][i];
+        if (mine && fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { acc.r += cr; acc.g += cg; acc.b += cb; }   // vrl_map.h:162
+    }
+    if (any_redo) {
+        for (int i = 0; i < n; ++i) {
+            const uint32_t own = q.own[i];
+            if ((own & 31u) != lane || q.v[6][i] != Q_REDO) continue;
+            // graze margin: exactly-rounded eval + exact trace
+            const uint32_t jg = q.jg[i], s = own >> 5;
+            const float4 *vp = reinterpret_cast<const float4 *>(fc.vrls + jg);
+            float4 a = __ldg(vp), b = __ldg(vp + 1), c = __ldg(vp + 2);
+            const DMedium &m = fc.media[__float_as_uint(b.w)];
+            Pcg32 rr; rr.state = rng0;
+            rr.advance(((uint64_t) s * fc.total + fc.first_index + jg) * DPE + (RR ? 1u : 0u));
             float ru1 = rr.next_f32(), ru2 = rr.next_f32();
-            float fe = exact_eval_vis<UNIFORM>(S, er, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, m.max_density, m.phase, m.g, ru1, ru2);
+            float fe = exact_eval_vis<UNIFORM>(*fc.S, er, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, m.max_density, m.phase, m.g, ru1, ru2);
             if (RR) {
                 FastSegC ray; ray.o = er.o; ray.d = er.d; ray.maxt = er.maxt;
                 float cc, cv;
                 closest_fast(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w, ray, cc, cv);
                 V3 dd = fmad3(ray.o, ray.d, cc) - fmad3(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), cv);
-                fe = fe * f_rcp(fminf(f_rcp(f_sqrt(fdot(dd, dd)) * scale_rr), 1.0f));
+                fe = fe * f_rcp(fminf(f_rcp(f_sqrt(fdot(dd, dd)) * fc.scale_rr), 1.0f));
             }
-            cr = c.x * fe; cg = c.y * fe; cb = c.z * fe;
-        } else if (q.v[7][slot] == 0.f) continue;  // occluded
-        if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { acc.r += cr; acc.g += cg; acc.b += cb; }   // vrl_map.h:162
+            const float cr = c.x * fe, cg = c.y * fe, cb = c.z * fe;
+            if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { acc.r += cr; acc.g += cg; acc.b += cb; }
+        }
     }
     __syncwarp();
     return acc;
 }
 
-// ---- kernel with visibility: phases A (shade NB VRLs) / B (trace the queue) / C (accumulate) per warp ----
+// Parameter interval (lo, hi) of the points o + t d that lie strictly inside the box `safe` (lo[3], hi[3]).
+__device__ __forceinline__ void safe_interval(V3 o, V3 d, const float *safe, float &lo, float &hi) {
+    lo = -VRLB_INF; hi = VRLB_INF;
+    const float oo[3] = { o.x, o.y, o.z }, dd[3] = { d.x, d.y, d.z };
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        if (fabsf(dd[k]) > 1e-12f) {
+            const float inv = 1.0f / dd[k];
+            const float t0 = (safe[k] - oo[k]) * inv, t1 = (safe[3 + k] - oo[k]) * inv;
+            lo = fmaxf(lo, fminf(t0, t1)); hi = fminf(hi, fmaxf(t0, t1));
+        } else if (!(oo[k] > safe[k] && oo[k] < safe[3 + k])) { lo = VRLB_INF; hi = -VRLB_INF; }
+    }
+}
+
+// ---- kernel with visibility ----
+#ifndef VRLB_VIS_THREADS
+#define VRLB_VIS_THREADS 256
+#endif
+#ifndef VRLB_VIS_MINBLOCKS
+#define VRLB_VIS_MINBLOCKS 3
+#endif
+constexpr int VIS_THREADS = VRLB_VIS_THREADS, VIS_MINBLOCKS = VRLB_VIS_MINBLOCKS;
 template <bool UNIFORM, bool RR, bool ISO, bool GUARD>
-__global__ void __launch_bounds__(GATHER_THREADS, 3)
+__global__ void __launch_bounds__(VIS_THREADS, VIS_MINBLOCKS)
 gather_fast_vis_kernel(GatherParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    DVrl (*tile)[VTILE] = reinterpret_cast<DVrl (*)[VTILE]>(smem_raw);                              // [NBUF][VTILE]
-    WarpQueue *queues = reinterpret_cast<WarpQueue *>(smem_raw + NBUF * VTILE * sizeof(DVrl));      // [warps]
+    DVrlV (*tile)[VTILE] = reinterpret_cast<DVrlV (*)[VTILE]>(smem_raw);                             // [NBUF][VTILE]
+    WarpBuf *bufs = reinterpret_cast<WarpBuf *>(smem_raw + NBUF * VTILE * sizeof(DVrlV));           // [warps]
     __shared__ alignas(8) uint64_t ring_bar[2 * NBUF];  // [0, NBUF): "full" (TMA complete_tx); [NBUF, 2 NBUF): "empty" (one arrive per warp)
     uint64_t *full_bar = ring_bar, *empty_bar = ring_bar + NBUF;
-    __shared__ uint32_t warp_it[GATHER_THREADS / 32];   // watchdog evidence: the tile each warp is on
-    __shared__ DSolid sol[VRLB_MAX_SOLIDS];             // the solids' proxies, read by every eval
+    __shared__ uint32_t warp_it[VIS_THREADS / 32];   // watchdog evidence: the tile each warp is on
+    __shared__ DSolid sol[VRLB_MAX_SOLIDS];             // the solids' proxies
     __shared__ float4 bsph[VRLB_MAX_SOLIDS];            // their bounding spheres (centre, r^2): the first test of every eval, one LDS.128
     __shared__ uint32_t s_sflags;                       // proxy flags, 3 bits per solid
     __shared__ DScene s_scene;                          // the out-of-line helpers take the scene by reference: shared, not a local copy
-    if (threadIdx.x == 0) s_scene = p.scene;
+    __shared__ DrainCtx s_dc;
+    if (threadIdx.x == 0) {
+        s_scene = p.scene;
+        s_dc.S = &s_scene; s_dc.media = p.scene.media; s_dc.vrls = p.vrls_vis;
+        s_dc.first_index = p.first_index; s_dc.total = p.total; s_dc.scale_rr = p.scale_rr; s_dc.wd = p.wd;
+    }
     __syncthreads();
     const DScene &S = s_scene;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, lt = (1u << lane) - 1u;
-    WarpQueue &q = queues[tid >> 5];
-    const uint64_t seg_i = (uint64_t) blockIdx.x * GATHER_THREADS + tid;
+    WarpBuf &q = bufs[tid >> 5];
+    const uint64_t seg_i = (uint64_t) blockIdx.x * VIS_THREADS + tid;
     const bool live = seg_i < p.n_segs;
 
-    // Only what every eval needs stays in registers (origin, direction, maxt, the stream); pixel, weight and the
-    // stream's start are re-read from the segment record where they are used (the kernel sits at its register cap).
-    FastSegC ray; uint64_t rng0 = 0;
+    // Only what every eval needs stays in registers (origin, direction, maxt, the safe interval, the stream); pixel,
+    // weight and the stream's start are re-read from the segment record where they are used.
+    FastSegC ray;
     if (live) {
         const float4 *sp = reinterpret_cast<const float4 *>(p.segs + seg_i);
         float4 r0 = __ldg(sp), r1 = __ldg(sp + 1);
         ray.o = V3(r0.x, r0.y, r0.z); ray.maxt = r0.w;
         ray.d = V3(r1.x, r1.y, r1.z);
-        rng0 = __ldg(reinterpret_cast<const ulonglong2 *>(sp + 3)).x;
     } else {
         ray.o = V3(0.f); ray.d = V3(0.f, 0.f, 1.f); ray.maxt = 1.f;
     }
     SegRegs er; er.o = ray.o; er.d = ray.d; er.maxt = ray.maxt;
+    float t_lo, t_hi;                                   // camera-part parameters strictly inside the shells' safe box
+    safe_interval(ray.o, ray.d, p.safe, t_lo, t_hi);
 
     const uint32_t n_tiles = (uint32_t) ((p.n_vrls + VTILE - 1) / VTILE);
     const uint32_t total_tiles = n_tiles * p.q;
     constexpr uint32_t DPE = RR ? 3u : 2u;
 
-    for (uint32_t i = tid; i < (uint32_t) S.n_solids * (sizeof(DSolid) / 4); i += GATHER_THREADS)
+    for (uint32_t i = tid; i < (uint32_t) S.n_solids * (sizeof(DSolid) / 4); i += VIS_THREADS)
         reinterpret_cast<uint32_t *>(sol)[i] = reinterpret_cast<const uint32_t *>(S.solids)[i];
     if (tid < (uint32_t) S.n_solids) bsph[tid] = make_float4(S.solids[tid].c[0], S.solids[tid].c[1], S.solids[tid].c[2], S.solids[tid].r_out2);
     if (tid == 32) {
@@ -703,7 +772,7 @@ gather_fast_vis_kernel(GatherParams p) {
         s_sflags = f;
     }
     if (tid == 0) {
-        for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], GATHER_THREADS / 32); }
+        for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], VIS_THREADS / 32); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -711,9 +780,9 @@ gather_fast_vis_kernel(GatherParams p) {
         uint32_t t = it % n_tiles, buf = it % NBUF;
         uint64_t first = (uint64_t) t * VTILE;
         uint32_t cnt = (uint32_t) min((uint64_t) VTILE, p.n_vrls - first);
-        uint32_t bytes = cnt * (uint32_t) sizeof(DVrl);
+        uint32_t bytes = cnt * (uint32_t) sizeof(DVrlV);
         mbar_expect_tx(&full_bar[buf], bytes);
-        tma_bulk_g2s(&tile[buf][0], p.vrls_fast + first, bytes, &full_bar[buf]);
+        tma_bulk_g2s(&tile[buf][0], p.vrls_vis + first, bytes, &full_bar[buf]);
     };
     if (tid == 0) {
         for (uint32_t b = 0; b < NBUF && b < total_tiles; ++b) issue(b);
@@ -723,15 +792,17 @@ gather_fast_vis_kernel(GatherParams p) {
     const Guard guard = { p.guard_h2, p.guard_z };
     const uint32_t sflags = s_sflags;
     float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
-    Pcg32 rng; rng.state = rng0;
+    Pcg32 rng; rng.state = 0;
+    int tb_n = 0;                                          // rays in the trace buffer (warp-uniform)
+    auto rng_start = [&]() { return live ? __ldg(reinterpret_cast<const ulonglong2 *>(p.segs + seg_i) + 3).x : 0ull; };
 
     for (uint32_t it = 0; it < total_tiles; ++it) {
         const uint32_t t = it % n_tiles, s = it / n_tiles, buf = it % NBUF;
         if (t == 0) {
-            rng.state = live ? __ldg(reinterpret_cast<const ulonglong2 *>(p.segs + seg_i) + 3).x : 0ull;
+            rng.state = rng_start();
             rng.advance(((uint64_t) s * p.total + p.first_index) * DPE);
         }
-        if (lane == 0) warp_it[tid >> 5] = it;
+        if (kWatchdog && lane == 0) warp_it[tid >> 5] = it;
         // producer (thread 0): tile it + 2 goes into the slot that tile it - 2 vacated, once every warp has released it.
         // Warps may drift up to 2 tiles apart in either direction of warp 0 without anyone waiting.
         if (tid == 0 && it >= 2 && it + 2 < total_tiles) {
@@ -742,16 +813,8 @@ gather_fast_vis_kernel(GatherParams p) {
         mbar_wait_wd(&full_bar[buf], (it / NBUF) & 1u, p.wd, 1u, it, buf, warp_it, ring_bar);
         const uint32_t cnt = (uint32_t) min((uint64_t) VTILE, p.n_vrls - (uint64_t) t * VTILE);
         float pr = 0.f, pg = 0.f, pb = 0.f;
-        const uint64_t rng_tile = rng.state;               // to regenerate (u1, u2) of a VRL on the rare re-evaluation
-        int npend = 0;                                     // shadow segments this lane has parked (slot = k * 32 + lane)
-        auto flush = [&]() {
-            Acc3 r = flush_queue<UNIFORM, RR>(S, q, &tile[buf][0], media, npend, rng_tile, er, p.scale_rr, p.wd);
-            pr += r.r; pg += r.g; pb += r.b;
-            npend = 0;
-        };
-        // The (out-of-line) flush is called from the OUTER of two loops: the inner loop shades VRLs until some lane's
-        // slots are full and contains no call, so its state stays in registers instead of being re-read from the
-        // spill area at every VRL (12 LDL per eval before, profiles/r01k_gather_v2_lines.txt).
+        // The (out-of-line) drain is called from the OUTER of two loops: the inner loop shades VRLs until 32 rays wait in the
+        // trace buffer and contains no call except the rare exactly-rounded eval, so its state stays in registers.
         for (uint32_t j = 0; ; ) {
           for (; j < cnt; ++j) {
             // shade VRL j for the warp's 32 camera segments (converged); only undecided shadow segments are parked
@@ -769,43 +832,58 @@ gather_fast_vis_kernel(GatherParams p) {
                 survive  = rrWeight > rng.next_f32();
             }
             float u1 = rng.next_f32(), u2 = rng.next_f32();
-            float f = 0.f; bool pend = false; uint32_t roots = 0; V3 so(0.f), sd(0.f); float dist = 0.f;
+            float f = 0.f; bool notsafe = false; Conn cn;
+            cn.pCam = V3(0.f); cn.dir = V3(0.f, 0.f, 1.f); cn.d2 = 1.f; cn.rd = 1.f; cn.tCam = 0.f; cn.tVRL = 0.f;
             if (survive) {
                 float g = 0.f;
                 if (!ISO) g = media[__float_as_uint(b.w)].phase == VRLB_PHASE_HG ? media[__float_as_uint(b.w)].g : 0.f;
                 bool slow;
-                f = contrib_fast<UNIFORM, true, ISO, GUARD>(S, ray, vo, vd, vlen, max_density, g, u1, u2, guard, slow, so, sd, dist);
+                f = contrib_fast<UNIFORM, true, ISO, GUARD>(S, ray, vo, vd, vlen, max_density, g, u1, u2, guard, slow, cn);
                 if (GUARD && slow) {                              // ill-conditioned eval: exactly-rounded arithmetic; its
-                    const DMedium &m = media[__float_as_uint(b.w)];       // connection segment is traced like any other
+                    const DMedium &m = media[__float_as_uint(b.w)];       // connection segment is classified like any other
                     float seg[7];
                     f = exact_eval_seg<UNIFORM>(S, er, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2, seg);
-                    so = V3(seg[0], seg[1], seg[2]); sd = V3(seg[3], seg[4], seg[5]); dist = seg[6];
+                    const float dist = seg[6];
                     if (!(dist > 0.f)) f = 0.f;
-                }
-                if (f != 0.f) {
-                    bool occluded;
-                    roots = roots_mask(p.scene, sol, bsph, sflags, p.safe, so, sd, dist, occluded);
-                    if (occluded) f = 0.f;                        // an inner proxy of a closed solid decides it
-                    else pend = roots != 0;
+                    cn.pCam = V3(seg[0], seg[1], seg[2]); cn.dir = V3(seg[3], seg[4], seg[5]) * dist;
+                    cn.d2 = dist * dist; cn.rd = f_rcp(dist);
+                    notsafe = true;                               // no parameters: the shells look at the end points
+                } else {
+                    // shells: both end points strictly inside the safe box <=> both parameters inside their intervals
+                    const float2 vi = *reinterpret_cast<const float2 *>(vp + 3);
+                    notsafe = !(cn.tCam > t_lo && cn.tCam < t_hi && cn.tVRL > vi.x && cn.tVRL < vi.y);
                 }
                 if (RR) f = f * f_rcp(rrWeight);
             }
+            bool occluded;
+            const uint32_t roots = classify_segment(p.scene, sol, bsph, sflags, cn.pCam, cn.dir, cn.rd * cn.rd, notsafe, f != 0.f, occluded);
+            if (occluded) f = 0.f;                                // an inner proxy of a closed solid decides it
             float4 c;                                             // flux pre-multiplied by sigma_s^2 * m_scale; read here, not
             asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"    // at the top: four registers fewer across the eval
                          : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w) : "r"(smem_u32(vp + 2)));
             const float cr = c.x * f, cg = c.y * f, cb = c.z * f;
-            if (pend) {
-                const int slot = npend * 32 + (int) lane;
-                q.v[0][slot] = so.x; q.v[1][slot] = so.y; q.v[2][slot] = so.z;
-                q.v[3][slot] = sd.x; q.v[4][slot] = sd.y; q.v[5][slot] = sd.z;
-                q.v[6][slot] = dist; q.v[7][slot] = 1.f;
-                q.v[8][slot] = cr; q.v[9][slot] = cg; q.v[10][slot] = cb;
-                q.roots[slot] = (uint16_t) roots; q.vj[slot] = (uint16_t) j;
-                ++npend;
+            const bool undec = roots != 0;
+            const unsigned um = __ballot_sync(0xffffffffu, undec);
+            if (undec) {                                          // park the segment: compacted, (VRL, lane) order
+                const int r = tb_n + __popc(um & lt);
+                const float dist = cn.d2 * cn.rd;
+                q.v[0][r] = cn.pCam.x; q.v[1][r] = cn.pCam.y; q.v[2][r] = cn.pCam.z;
+                q.v[3][r] = cn.dir.x * cn.rd; q.v[4][r] = cn.dir.y * cn.rd; q.v[5][r] = cn.dir.z * cn.rd;
+                q.v[6][r] = dist; q.v[7][r] = 1.f;
+                q.v[8][r] = cr; q.v[9][r] = cg; q.v[10][r] = cb;
+                q.roots[r] = (uint16_t) roots; q.own[r] = (uint16_t) (lane | (s << 5)); q.jg[r] = t * VTILE + j;
             } else if (fabsf(cr) + fabsf(cg) + fabsf(cb) < VRLB_INF) { pr += cr; pg += cg; pb += cb; }   // vrl_map.h:162
-            if (__any_sync(0xffffffffu, npend == NB)) { ++j; break; }
+            tb_n += __popc(um);
+            if (tb_n >= 32) { ++j; break; }
           }
-          if (__any_sync(0xffffffffu, npend > 0)) flush();
+          // ... and at the end of every DRAIN_WINDOW-th tile (GLOBAL tile index) whatever is waiting: VRL shards cut at
+          // a window boundary then form the same trace batches as the whole set and reproduce its sums bit for bit
+          const bool window_end = j >= cnt && (((p.first_index / VTILE + t + 1) % DRAIN_WINDOW) == 0 || t + 1 == n_tiles);
+          if (tb_n >= 32 || (window_end && tb_n > 0)) {
+              Acc3 r = drain_trace<UNIFORM, RR>(s_dc, q, tb_n, er, rng_start());
+              pr += r.r; pg += r.g; pb += r.b;
+              tb_n = 0;
+          }
           if (j >= cnt) break;
         }
         float part[3] = { pr, pg, pb };
@@ -819,6 +897,18 @@ gather_fast_vis_kernel(GatherParams p) {
         // release the slot (consumer side of the full/empty mbarrier pipeline; no CTA barrier in the loop)
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[buf]);
+    }
+    // rays still waiting in the trace buffer
+    if (tb_n > 0) {
+        Acc3 r = drain_trace<UNIFORM, RR>(s_dc, q, tb_n, er, rng_start());
+        float part[3] = { r.r, r.g, r.b };
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float y = xsub(part[k], comp[k]);
+            float tt = xadd(sum[k], y);
+            comp[k] = xsub(xsub(tt, sum[k]), y);
+            sum[k] = tt;
+        }
     }
 
     if (live) {
@@ -854,6 +944,37 @@ cudaError_t launch_prep_fast_vrls(const DVrl *in, uint64_t n, const DMedium *med
     return cudaGetLastError();
 }
 
+// ---- 64-byte records of the visibility kernel: the same three rows + the VRL's parameter interval inside the shells'
+//      safe box (gather_fast_vis_kernel tests "end point strictly inside every shell" with two compares) ----
+struct SafeBox { float v[6]; };
+__global__ void prep_vis_vrls_kernel(const DVrl *in, uint64_t n, const DMedium *media, float scale, SafeBox safe, DVrlV *out) {
+    uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const DVrl v = in[j];
+    const DMedium m = media[v.medium];
+    DVrlV o;
+    o.ox = v.ox; o.oy = v.oy; o.oz = v.oz; o.length = v.length;
+    o.dx = v.dx; o.dy = v.dy; o.dz = v.dz; o.medium = v.medium;
+    o.fr = v.fr * m.sigma_s[0] * m.sigma_s[0] * scale;      // vrl_struct.h:652-659, vrl_map.h:160
+    o.fg = v.fg * m.sigma_s[1] * m.sigma_s[1] * scale;
+    o.fb = v.fb * m.sigma_s[2] * m.sigma_s[2] * scale;
+    o.ext = m.max_density;
+    safe_interval(V3(v.ox, v.oy, v.oz), V3(v.dx, v.dy, v.dz), safe.v, o.v_lo, o.v_hi);
+    o.pad0 = o.pad1 = 0u;
+    out[j] = o;
+}
+void shell_safe_box(const DScene &scene, float safe[6]) {
+    for (int k = 0; k < 3; ++k) { safe[k] = -INFINITY; safe[3 + k] = INFINITY; }
+    for (int i = 0; i < scene.n_shells; ++i)
+        for (int k = 0; k < 3; ++k) { safe[k] = fmaxf(safe[k], scene.shells[i].lo[k]); safe[3 + k] = fminf(safe[3 + k], scene.shells[i].hi[k]); }
+}
+cudaError_t launch_prep_vis_vrls(const DVrl *in, uint64_t n, const DScene &scene, float scale, DVrlV *out, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    SafeBox sb; shell_safe_box(scene, sb.v);
+    prep_vis_vrls_kernel<<<(uint32_t) ((n + 255) / 256), 256, 0, stream>>>(in, n, scene.media, scale, sb, out);
+    return cudaGetLastError();
+}
+
 template <bool U, bool R, bool I, bool P>
 static cudaError_t launch_f(const GatherParams &p, cudaStream_t stream) {
     uint32_t grid = (uint32_t) ((p.n_segs + GATHER_THREADS - 1) / GATHER_THREADS);
@@ -865,21 +986,16 @@ static cudaError_t launch_f(const GatherParams &p, cudaStream_t stream) {
 }
 template <bool U, bool R, bool I, bool P>
 static cudaError_t launch_fv(const GatherParams &p, cudaStream_t stream) {
-    uint32_t grid = (uint32_t) ((p.n_segs + GATHER_THREADS - 1) / GATHER_THREADS);
+    uint32_t grid = (uint32_t) ((p.n_segs + VIS_THREADS - 1) / VIS_THREADS);
     if (grid == 0 || p.n_vrls == 0) return cudaSuccess;
-    constexpr size_t smem = NBUF * VTILE * sizeof(DVrl) + (GATHER_THREADS / 32) * sizeof(WarpQueue);
+    constexpr size_t smem = NBUF * VTILE * sizeof(DVrlV) + (VIS_THREADS / 32) * sizeof(WarpBuf);
     GatherParams pp = p;                   // intersection of the shell boxes: a segment with both ends strictly inside it meets no shell
     pp.guard_h2 = p.guard_h * p.guard_h;
-    for (int k = 0; k < 3; ++k) { pp.safe[k] = -INFINITY; pp.safe[3 + k] = INFINITY; }
-    for (int i = 0; i < p.scene.n_shells; ++i)
-        for (int k = 0; k < 3; ++k) { pp.safe[k] = fmaxf(pp.safe[k], p.scene.shells[i].lo[k]); pp.safe[3 + k] = fminf(pp.safe[3 + k], p.scene.shells[i].hi[k]); }
-    static bool configured = false;       // per instantiation; the attribute is sticky for the process
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(gather_fast_vis_kernel<U, R, I, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
-    gather_fast_vis_kernel<U, R, I, P><<<grid, GATHER_THREADS, smem, stream>>>(pp);
+    shell_safe_box(p.scene, pp.safe);
+    // per device, so set before every launch (it is cheap): a process may hold contexts on several GPUs
+    cudaError_t e = cudaFuncSetAttribute(gather_fast_vis_kernel<U, R, I, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    if (e != cudaSuccess) return e;
+    gather_fast_vis_kernel<U, R, I, P><<<grid, VIS_THREADS, smem, stream>>>(pp);
     return cudaGetLastError();
 }
 template <bool U, bool R, bool V>

@@ -56,7 +56,7 @@ struct vrlb_context {
     std::vector<DTri> host_tris;      // BVH order, for the emitter table of vrlb_vrls_generate
 
     // VRL set
-    DevBuf<DVrl> vrls, vrls_fast; bool fast_dirty = true; bool all_iso = true;
+    DevBuf<DVrl> vrls, vrls_fast; DevBuf<DVrlV> vrls_vis; bool fast_dirty = true; bool all_iso = true;
     DevBuf<float> stage_soa; DevBuf<uint16_t> stage_med;
     uint64_t n_vrls = 0, vrl_first = 0, vrl_total = 0; float vrl_scale = 1.f;
 
@@ -195,7 +195,7 @@ void vrlb_destroy(vrlb_context *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->wnodes.release(); ctx->stris.release(); ctx->media.release(); ctx->emitters.release(); ctx->grids.release(); ctx->solids.release();
-    ctx->vrls.release(); ctx->vrls_fast.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
+    ctx->vrls.release(); ctx->vrls_fast.release(); ctx->vrls_vis.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
     if (ctx->nccl_comm && g_nccl_destroy) g_nccl_destroy(ctx->nccl_comm);
     ctx->block_ids.release(); ctx->film_rgb.release(); ctx->film_aw.release(); ctx->film_xyzaw.release();
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
@@ -678,9 +678,15 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     if (fast && ctx->fast_dirty && ctx->n_vrls) {
         CU(ctx, ctx->vrls_fast.reserve(ctx->n_vrls));
         CU(ctx, launch_prep_fast_vrls(ctx->vrls.ptr, ctx->n_vrls, ctx->media.ptr, ctx->vrl_scale, ctx->vrls_fast.ptr, ctx->stream));
-        ctx->fast_dirty = false; ctx->timing.total_launches += 1; ctx->launches += 1;
+        ctx->timing.total_launches += 1; ctx->launches += 1;
+        if (ctx->scene.n_tris > 0) {         // the visibility kernel's 64-byte records (safe-box intervals of this scene's shells)
+            CU(ctx, ctx->vrls_vis.reserve(ctx->n_vrls));
+            CU(ctx, launch_prep_vis_vrls(ctx->vrls.ptr, ctx->n_vrls, ctx->scene, ctx->vrl_scale, ctx->vrls_vis.ptr, ctx->stream));
+            ctx->timing.total_launches += 1; ctx->launches += 1;
+        }
+        ctx->fast_dirty = false;
     }
-    p.vrls_fast = ctx->vrls_fast.ptr;
+    p.vrls_fast = ctx->vrls_fast.ptr; p.vrls_vis = ctx->vrls_vis.ptr;
     p.guard_h = opt->reserved[0] ? (float) opt->reserved[0] * 1e-3f : 0.2f;   // dev knobs (milli-units); 0 = shipped defaults
     p.guard_z = opt->reserved[1] ? (float) opt->reserved[1] : 8.0f;
     cudaEventRecord(ctx->ev[2], ctx->stream);

@@ -156,6 +156,12 @@ struct DVrl {            // 48 B record: three 16-byte rows, staged tile-wise in
     float dx, dy, dz; uint32_t medium;
     float fr, fg, fb, pad;
 };
+struct DVrlV {           // 64 B record of the visibility kernel: DVrl rows (flux pre-multiplied, extinction) + the parameter
+    float ox, oy, oz, length;    // interval (v_lo, v_hi) of the VRL's points strictly inside the shells' safe box
+    float dx, dy, dz; uint32_t medium;
+    float fr, fg, fb, ext;
+    float v_lo, v_hi; uint32_t pad0, pad1;
+};
 
 struct DScene {
     const DTri  *tris;

@@ -14,6 +14,7 @@ struct GatherParams {
     uint64_t            n_segs;
     const DVrl         *vrls;        // device, 48 B records (this rank's shard)
     const DVrl         *vrls_fast;   // same records pre-multiplied for the fast kernel (launch_prep_fast_vrls)
+    const DVrlV        *vrls_vis;    // 64-byte records of the fast visibility kernel (launch_prep_vis_vrls)
     uint64_t            n_vrls;
     uint64_t            first_index; // global index of vrls[0] (PCG32 stream addressing)
     uint64_t            total;       // size of the whole exported set
@@ -33,6 +34,8 @@ cudaError_t launch_gather(const GatherParams &p, bool uniform, bool rr, bool vis
 // math_mode 1 / 2 (gather_fast.cu): iso = every medium isotropic, guard = route ill-conditioned evals to the exact path
 cudaError_t launch_gather_fast(const GatherParams &p, bool uniform, bool rr, bool vis, bool iso, bool guard, cudaStream_t stream);
 cudaError_t launch_prep_fast_vrls(const DVrl *in, uint64_t n, const DMedium *media, float scale, DVrl *out, cudaStream_t stream);
+cudaError_t launch_prep_vis_vrls(const DVrl *in, uint64_t n, const DScene &scene, float scale, DVrlV *out, cudaStream_t stream);
+void shell_safe_box(const DScene &scene, float safe[6]);   // intersection of the (shrunk) shell boxes, +-inf without shells
 
 struct SegmentParams {
     DScene        scene;

@@ -9,7 +9,12 @@ def shard_bounds(n_total, rank, world):
     """Rank r owns VRLs [r*N/W, (r+1)*N/W): contiguous, so eval (s, j) keeps its PCG32 offset (s*N + j)*dpe."""
     if not (0 <= rank < world):
         raise ValueError(f"rank {rank} outside [0, {world})")
-    return rank * n_total // world, (rank + 1) * n_total // world
+    # cuts on multiples of 512 VRLs where the set is large enough: the visibility kernel drains its trace buffer at those
+    # GLOBAL boundaries (gather_fast.cu DRAIN_WINDOW), so the shards' partial films are the whole set's partial sums
+    def cut(r):
+        c = r * n_total // world
+        return c if (r == 0 or r == world or n_total < 512 * world * 4) else (c + 256) // 512 * 512
+    return cut(rank), cut(rank + 1)
 
 
 def shard_desc(soa10, rank, world):

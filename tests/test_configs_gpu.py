@@ -115,14 +115,15 @@ def test_config4_bench_frame_1080p_100k(ctx):
     for lo, hi in ((0, 37777), (37777, n)):
         ctx.upload_vrls(scenes.vrlset_desc(np.ascontiguousarray(soa[:, lo:hi]), scale=1.0 / n, first_index=lo, total=n))
         parts += ctx.gather_segments(opt)
-    # Shards cut at a tile boundary reproduce the whole bit for bit (same tiles -> same batches); an unaligned cut
+    # Shards cut at a drain-window boundary (512 VRLs, gather_fast.cu DRAIN_WINDOW) reproduce the whole bit for bit (same
+    # tiles -> same trace batches); an unaligned cut
     # regroups the shadow batches, and an eval whose connection grazes a silhouette edge can then be decided by the
     # exactly-rounded re-evaluation in one grouping and by the fast test in the other ("graze"):
     # measured 3 of 2 073 600 pixels differ by 1-4 average evals (1e-5 each), everything else by fp32 rounding.
     err = rel_err(parts, whole)
     assert err.max() <= REL_TOL and (err > 1e-5).sum() <= 16 and np.median(err) <= 1e-6
     parts = np.zeros_like(whole)
-    for lo, hi in ((0, 37760), (37760, n)):                             # 37760 = 590 tiles of 64
+    for lo, hi in ((0, 37888), (37888, n)):                             # 37888 = 74 windows of 512
         ctx.upload_vrls(scenes.vrlset_desc(np.ascontiguousarray(soa[:, lo:hi]), scale=1.0 / n, first_index=lo, total=n))
         parts += ctx.gather_segments(opt)
     assert rel_err(parts, whole).max() <= 1e-6
