@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--vrls", type=int, default=100000)
     ap.add_argument("--q", type=int, default=1)
     ap.add_argument("--no-occluders", action="store_true")
+    ap.add_argument("--force-vis", action="store_true", help="with --no-occluders: keep the shadow query (shells only)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -60,7 +61,7 @@ def workload(args):
     import mitsuba_nlvrl_b200 as pkg
     sc = pkg.scenes.box_fog_scene(occluders=not args.no_occluders)
     cam = pkg.scenes.box_fog_camera(args.width, args.height)
-    opt = pkg.scenes.default_options(samples_per_query=args.q, visibility=0 if args.no_occluders else 1)
+    opt = pkg.scenes.default_options(samples_per_query=args.q, visibility=0 if (args.no_occluders and not args.force_vis) else 1)
     soa = pkg.scenes.synthetic_vrls(args.vrls, seed=1)
     name = (f"box-fog {'V1 no occluders' if args.no_occluders else 'V2 occluders+BVH visibility'} "
             f"{args.width}x{args.height} spp1 q{args.q} N_vrl={args.vrls} homogeneous isotropic importance-sampled")

@@ -350,8 +350,8 @@ gather_fast_kernel(GatherParams p) {
 // persistent lanes, a lane that finishes a ray pulls the next one; node steps and triangle tests are separated, leaf
 // hits go to a leaf queue and are tested 32 at a time.  Contributions are added by their owner lane in buffer order,
 // so the sum of a lane is deterministic.  B200 has no RT cores: plain SIMT traversal with warp-level ray compaction.
-constexpr int VTILE = 64, NBUF = 4;      // VRL ring of the visibility kernel: NBUF tiles of VTILE 64-byte records
-constexpr int DRAIN_WINDOW = 8;          // tiles between forced drains of the trace buffer (512 VRLs)
+constexpr int VTILE = 32, NBUF = 2;      // VRL staging of the visibility kernel: per WARP, NBUF tiles of VTILE 64-byte records
+constexpr int DRAIN_WINDOW = 16;         // tiles between forced drains of the trace buffer (512 VRLs)
 constexpr int TCAP  = 64;                // trace buffer: rays waiting for the BVH (traced when >= 32 are pending)
 constexpr int QF    = 11;                // floats per ray: o(3) d(3) dist alive r g b
 constexpr float Q_REDO = -2.f;           // dist marker: hit decision inside the graze margins, re-evaluate exactly
@@ -721,10 +721,13 @@ template <bool UNIFORM, bool RR, bool ISO, bool GUARD>
 __global__ void __launch_bounds__(VIS_THREADS, VIS_MINBLOCKS)
 gather_fast_vis_kernel(GatherParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    DVrlV (*tile)[VTILE] = reinterpret_cast<DVrlV (*)[VTILE]>(smem_raw);                             // [NBUF][VTILE]
-    WarpBuf *bufs = reinterpret_cast<WarpBuf *>(smem_raw + NBUF * VTILE * sizeof(DVrlV));           // [warps]
-    __shared__ alignas(8) uint64_t ring_bar[2 * NBUF];  // [0, NBUF): "full" (TMA complete_tx); [NBUF, 2 NBUF): "empty" (one arrive per warp)
-    uint64_t *full_bar = ring_bar, *empty_bar = ring_bar + NBUF;
+    // VRL tiles are staged PER WARP (TMA bulk copies into the warp's own double buffer, completion on the warp's own
+    // mbarriers): warps of a CTA do different amounts of shadow work, and a CTA-wide ring made the fast ones wait for the
+    // slow ones (issue slots 66 % busy on a frame without solids, profiles/r02d); the tiles come from L2 either way.
+    DVrlV (*tile)[VTILE] = reinterpret_cast<DVrlV (*)[VTILE]>(smem_raw) + (threadIdx.x >> 5) * NBUF;  // [warp][NBUF][VTILE]
+    WarpBuf *bufs = reinterpret_cast<WarpBuf *>(smem_raw + (VIS_THREADS / 32) * NBUF * VTILE * sizeof(DVrlV));           // [warps]
+    __shared__ alignas(8) uint64_t ring_bar[(VIS_THREADS / 32) * NBUF];  // per warp: "full" (TMA complete_tx) of its two buffers
+    uint64_t *full_bar = ring_bar + (threadIdx.x >> 5) * NBUF;
     __shared__ uint32_t warp_it[VIS_THREADS / 32];   // watchdog evidence: the tile each warp is on
     __shared__ DSolid sol[VRLB_MAX_SOLIDS];             // the solids' proxies
     __shared__ float4 bsph[VRLB_MAX_SOLIDS];            // their bounding spheres (centre, r^2): the first test of every eval, one LDS.128
@@ -771,8 +774,8 @@ gather_fast_vis_kernel(GatherParams p) {
         for (int i = 0; i < S.n_solids; ++i) f |= (S.solids[i].flags & 7u) << (3 * i);
         s_sflags = f;
     }
-    if (tid == 0) {
-        for (int b = 0; b < NBUF; ++b) { mbar_init(&full_bar[b], 1); mbar_init(&empty_bar[b], VIS_THREADS / 32); }
+    if (lane == 0) {
+        for (int b = 0; b < NBUF; ++b) mbar_init(&full_bar[b], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -784,9 +787,7 @@ gather_fast_vis_kernel(GatherParams p) {
         mbar_expect_tx(&full_bar[buf], bytes);
         tma_bulk_g2s(&tile[buf][0], p.vrls_vis + first, bytes, &full_bar[buf]);
     };
-    if (tid == 0) {
-        for (uint32_t b = 0; b < NBUF && b < total_tiles; ++b) issue(b);
-    }
+    if (lane == 0 && total_tiles > 0) issue(0);
 
     const DMedium *media = S.media;
     const Guard guard = { p.guard_h2, p.guard_z };
@@ -794,6 +795,16 @@ gather_fast_vis_kernel(GatherParams p) {
     float sum[3] = { 0.f, 0.f, 0.f }, comp[3] = { 0.f, 0.f, 0.f };     // Kahan across tiles
     Pcg32 rng; rng.state = 0;
     int tb_n = 0;                                          // rays in the trace buffer (warp-uniform)
+    auto kahan_add = [&](float r, float g, float b) {
+        const float part[3] = { r, g, b };
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float y = xsub(part[k], comp[k]);
+            float tt = xadd(sum[k], y);
+            comp[k] = xsub(xsub(tt, sum[k]), y);
+            sum[k] = tt;
+        }
+    };
     auto rng_start = [&]() { return live ? __ldg(reinterpret_cast<const ulonglong2 *>(p.segs + seg_i) + 3).x : 0ull; };
 
     for (uint32_t it = 0; it < total_tiles; ++it) {
@@ -803,13 +814,9 @@ gather_fast_vis_kernel(GatherParams p) {
             rng.advance(((uint64_t) s * p.total + p.first_index) * DPE);
         }
         if (kWatchdog && lane == 0) warp_it[tid >> 5] = it;
-        // producer (thread 0): tile it + 2 goes into the slot that tile it - 2 vacated, once every warp has released it.
-        // Warps may drift up to 2 tiles apart in either direction of warp 0 without anyone waiting.
-        if (tid == 0 && it >= 2 && it + 2 < total_tiles) {
-            mbar_wait_wd(&empty_bar[(it - 2) % NBUF], ((it - 2) / NBUF) & 1u, p.wd, 3u, it, (it - 2) % NBUF, warp_it, ring_bar);
-            issue(it + 2);
-        }
+        // the next tile goes into the other buffer, which the warp finished reading at the end of the previous iteration
         __syncwarp();
+        if (lane == 0 && it + 1 < total_tiles) issue(it + 1);
         mbar_wait_wd(&full_bar[buf], (it / NBUF) & 1u, p.wd, 1u, it, buf, warp_it, ring_bar);
         const uint32_t cnt = (uint32_t) min((uint64_t) VTILE, p.n_vrls - (uint64_t) t * VTILE);
         float pr = 0.f, pg = 0.f, pb = 0.f;
@@ -880,35 +887,23 @@ gather_fast_vis_kernel(GatherParams p) {
           // a window boundary then form the same trace batches as the whole set and reproduce its sums bit for bit
           const bool window_end = j >= cnt && (((p.first_index / VTILE + t + 1) % DRAIN_WINDOW) == 0 || t + 1 == n_tiles);
           if (tb_n >= 32 || (window_end && tb_n > 0)) {
+              // the tile's partial sums go into the Kahan accumulators first: nothing of the inner loop's state is live
+              // across the call except what the accumulators hold
+              kahan_add(pr, pg, pb);
+              pr = pg = pb = 0.f;
               Acc3 r = drain_trace<UNIFORM, RR>(s_dc, q, tb_n, er, rng_start());
-              pr += r.r; pg += r.g; pb += r.b;
+              kahan_add(r.r, r.g, r.b);
               tb_n = 0;
           }
           if (j >= cnt) break;
         }
-        float part[3] = { pr, pg, pb };
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            float y = xsub(part[k], comp[k]);
-            float tt = xadd(sum[k], y);
-            comp[k] = xsub(xsub(tt, sum[k]), y);
-            sum[k] = tt;
-        }
-        // release the slot (consumer side of the full/empty mbarrier pipeline; no CTA barrier in the loop)
+        kahan_add(pr, pg, pb);
         __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_bar[buf]);
     }
     // rays still waiting in the trace buffer
     if (tb_n > 0) {
         Acc3 r = drain_trace<UNIFORM, RR>(s_dc, q, tb_n, er, rng_start());
-        float part[3] = { r.r, r.g, r.b };
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            float y = xsub(part[k], comp[k]);
-            float tt = xadd(sum[k], y);
-            comp[k] = xsub(xsub(tt, sum[k]), y);
-            sum[k] = tt;
-        }
+        kahan_add(r.r, r.g, r.b);
     }
 
     if (live) {
@@ -988,7 +983,7 @@ template <bool U, bool R, bool I, bool P>
 static cudaError_t launch_fv(const GatherParams &p, cudaStream_t stream) {
     uint32_t grid = (uint32_t) ((p.n_segs + VIS_THREADS - 1) / VIS_THREADS);
     if (grid == 0 || p.n_vrls == 0) return cudaSuccess;
-    constexpr size_t smem = NBUF * VTILE * sizeof(DVrlV) + (VIS_THREADS / 32) * sizeof(WarpBuf);
+    constexpr size_t smem = (VIS_THREADS / 32) * (NBUF * VTILE * sizeof(DVrlV) + sizeof(WarpBuf));
     GatherParams pp = p;                   // intersection of the shell boxes: a segment with both ends strictly inside it meets no shell
     pp.guard_h2 = p.guard_h * p.guard_h;
     shell_safe_box(p.scene, pp.safe);
