@@ -31,22 +31,8 @@ namespace vrlb {
 
 constexpr float kPi = 3.14159265358979323846f;
 
-__device__ inline float ior_at(const DMedium &m, float y) {
-    float h = m.nl_hi[1] - m.nl_lo[1];
-    float t = fminf(fmaxf((y - m.nl_lo[1]) / h, 0.f), 1.f);
-    return m.ior_bottom + (m.ior_top - m.ior_bottom) * t;
-}
-__device__ inline float ior_grad_y(const DMedium &m, V3 p) {
-    bool in = p.x >= m.nl_lo[0] && p.x <= m.nl_hi[0] && p.y >= m.nl_lo[1] && p.y <= m.nl_hi[1] && p.z >= m.nl_lo[2] && p.z <= m.nl_hi[2];
-    return in ? (m.ior_top - m.ior_bottom) / (m.nl_hi[1] - m.nl_lo[1]) : 0.f;
-}
-// one eikonal step of length ds: bends `dir` towards increasing n, returns the new direction (unit)
-__device__ inline V3 eikonal_bend(const DMedium &m, V3 p, V3 dir, float ds) {
-    float n = ior_at(m, p.y);
-    V3 v = dir * n;
-    v.y = v.y + ds * ior_grad_y(m, p);
-    return normalize(v);
-}
+// one eikonal step: nl_bend (vrlb_device.cuh)
+__device__ inline V3 eikonal_bend(const DMedium &m, V3 p, V3 dir, float ds) { return nl_bend(m, p, dir, ds); }
 
 __device__ inline V3 sample_uniform_sphere(float u1, float u2) {         // warp::square_to_uniform_sphere
     float z = 1.f - 2.f * u2, r = sqrtf(fmaxf(1.f - z * z, 0.f));
@@ -247,8 +233,16 @@ __global__ void __launch_bounds__(128) generate_kernel(GenParams p) {
             open_vrl(pos, dir);                                             // vrl.cpp:354
             continue;
         }
-        // real scattering event (homogeneous extinction: no null collisions), vrl.cpp:246-294
-        (void) rng.next_f32();                                             // the null-scatter decision's draw, vrl.cpp:246
+        // tentative collision: null or real scattering (delta tracking), vrl.cpp:246-294.  The free flight was sampled with the
+        // majorant; in a grid medium the collision is real with probability sigma_t(x) / majorant, otherwise the particle
+        // carries on from here -- same direction, VRL in flight not cut, depth untouched (vrl.cpp:259-264; the throughput
+        // factors of the two branches, sigma_n / sigma_n and sigma_s / sigma_t, leave 1 and the albedo).  Constant
+        // extinction: sigma_t = majorant, every collision is real.
+        const float u_null = rng.next_f32();                               // the null-scatter decision's draw, vrl.cpp:246
+        if (m->kind == VRLB_MEDIUM_GRID) {
+            const float sigma_t = m->scale * grid_eval(*m, pos);
+            if (u_null >= sigma_t / m->max_density) continue;
+        }
         ++depth;                                                           // vrl.cpp:254
         if (depth + 1 >= p.max_depth) break;                               // vrl.cpp:257-258: the scattering is dropped
         throughput = throughput * V3(m->albedo[0], m->albedo[1], m->albedo[2]);

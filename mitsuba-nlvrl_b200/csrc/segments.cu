@@ -51,18 +51,6 @@ __device__ inline void camera_ray(const vrlb_camera &c, float sx, float sy, V3 &
 
 // cosine of the turning angle after which a curved camera path starts a new straight part (0.25 degrees)
 constexpr float NL_PART_COS = 0.99999048f;
-// one eikonal step (see generate.cu): v = n dir, v.y += ds * dn/dy inside the IOR box, dir = v / |v|
-__device__ inline V3 nl_bend(const DMedium &m, V3 p, V3 dir, float ds) {
-    float h = m.nl_hi[1] - m.nl_lo[1];
-    float t = fminf(fmaxf((p.y - m.nl_lo[1]) / h, 0.f), 1.f);
-    float n = m.ior_bottom + (m.ior_top - m.ior_bottom) * t;
-    bool in = p.x >= m.nl_lo[0] && p.x <= m.nl_hi[0] && p.y >= m.nl_lo[1] && p.y <= m.nl_hi[1] && p.z >= m.nl_lo[2] && p.z <= m.nl_hi[2];
-    float g = in ? (m.ior_top - m.ior_bottom) / h : 0.f;
-    V3 v = dir * n;
-    v.y = v.y + ds * g;
-    return normalize(v);
-}
-
 __global__ void __launch_bounds__(128) segments_kernel(SegmentParams p) {
     const int bs = p.opt.block_size;
     const uint32_t pixel_count = (uint32_t) (bs * bs);

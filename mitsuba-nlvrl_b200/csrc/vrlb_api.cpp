@@ -288,7 +288,7 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
             grid_host.insert(grid_host.end(), m.grid, m.grid + (size_t) m.grid_res[0] * m.grid_res[1] * m.grid_res[2]);
         }
         for (int k = 0; k < 3; ++k) { d.albedo[k] = m.albedo[k]; d.nl_lo[k] = m.nl_bbox_min[k]; d.nl_hi[k] = m.nl_bbox_max[k]; }
-        d.ior_bottom = m.bottom_ior; d.ior_top = m.top_ior; d.nl_step = 0.f;
+        d.ior_bottom = m.bottom_ior; d.ior_top = m.top_ior; d.nl_step = 0.f; d.from_bottom = m.from_bottom ? 1 : 0;
         if (m.kind == VRLB_MEDIUM_NONLINEAR) {
             if (m.ior_method != 0) return fail(ctx, VRLB_ERR_INVALID, "medium %u: only ior_method 0 (linear in height) is on the path", i);
             if (!(m.nl_bbox_max[1] > m.nl_bbox_min[1]) || m.nl_res[1] < 1) return fail(ctx, VRLB_ERR_INVALID, "medium %u: nonlinear medium needs nl_bbox and nl_res", i);

@@ -138,7 +138,7 @@ struct DMedium {         // what the gather needs of a medium (homogeneous / non
     float g;
     int32_t phase;
     int32_t kind;
-    int32_t pad;
+    int32_t from_bottom; // nonlinear.cpp:149-150: 1 = height measured from the box floor; 0 = n(y) = lerp(bottom, top, max(0, y / (height / 2))), world y
     // graded refractive index (VRLB_MEDIUM_NONLINEAR, nonlinear.cpp:129-153 method 0): n(y) = lerp(bottom, top, (y - y0) / height)
     float nl_lo[3], nl_hi[3];
     float ior_bottom, ior_top;
@@ -183,6 +183,31 @@ struct DScene {
     const float *emitters;   // n_emitters * 4
     int32_t      n_emitters;
 };
+
+// IOR profile of the `nonlinear` medium (nonlinear.cpp:129-153, ior_method 0): the index n at p and its vertical gradient
+// (0 outside the medium's box).  from_bottom = false (mirage.xml): the lower half of the world (y <= 0) has the bottom index.
+__device__ inline void nl_profile(const DMedium &m, V3 p, float &n, float &g) {
+    const float h = m.nl_hi[1] - m.nl_lo[1];
+    const bool in = p.x >= m.nl_lo[0] && p.x <= m.nl_hi[0] && p.y >= m.nl_lo[1] && p.y <= m.nl_hi[1] && p.z >= m.nl_lo[2] && p.z <= m.nl_hi[2];
+    if (m.from_bottom) {
+        const float t = fminf(fmaxf((p.y - m.nl_lo[1]) / h, 0.f), 1.f);
+        n = m.ior_bottom + (m.ior_top - m.ior_bottom) * t;
+        g = in ? (m.ior_top - m.ior_bottom) / h : 0.f;
+    } else {
+        const float hh = h * 0.5f;
+        const float t = fmaxf(0.f, p.y / hh);
+        n = m.ior_bottom + (m.ior_top - m.ior_bottom) * t;
+        g = (in && p.y > 0.f) ? (m.ior_top - m.ior_bottom) / hh : 0.f;
+    }
+}
+// one eikonal step of length ds: v = n dir, v.y += ds * dn/dy, dir = v / |v| (bends `dir` towards increasing n)
+__device__ inline V3 nl_bend(const DMedium &m, V3 p, V3 dir, float ds) {
+    float n, g;
+    nl_profile(m, p, n, g);
+    V3 v = dir * n;
+    v.y = v.y + ds * g;
+    return normalize(v);
+}
 
 // ---- delta BSDFs of the specular chains (vrl.cpp:318-358 light side, 682-716 camera side) ----
 // The translation units are built with -fmad=false -prec-div=true -prec-sqrt=true, so the plain expressions below are

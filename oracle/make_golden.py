@@ -33,6 +33,18 @@ def main():
         with open(os.path.join(GOLD, "ref_fresnel.json"), "w") as f:
             json.dump(data, f)
         print("wrote ref_fresnel.json:", {k: len(v) for k, v in data.items()})
+    probe = os.path.join(HERE, "_ref", "refprobe_nl")
+    if os.path.exists(probe):
+        data = json.loads(subprocess.check_output([probe]))
+        with open(os.path.join(GOLD, "ref_nonlinear.json"), "w") as f:
+            json.dump(data, f)
+        print("wrote ref_nonlinear.json:", {m["name"]: len(m["rays"]) for m in data["media"]}, "warnings", data["warnings"])
+    probe = os.path.join(HERE, "_ref", "refprobe_medium")
+    if os.path.exists(probe):
+        data = json.loads(subprocess.check_output([probe]))
+        with open(os.path.join(GOLD, "ref_medium.json"), "w") as f:
+            json.dump(data, f)
+        print("wrote ref_medium.json:", len(data["cases"]), "cases, warnings", data["warnings"])
 
 if __name__ == "__main__":
     sys.exit(main())

@@ -1253,13 +1253,26 @@ inline float nl_step(const vrlb_medium &m) {
     if (m.kind != VRLB_MEDIUM_NONLINEAR || m.nl_res[1] < 1) return 0.f;
     return (m.nl_bbox_max[1] - m.nl_bbox_min[1]) / (float) m.nl_res[1];
 }
-inline V3 nl_bend(const vrlb_medium &m, V3 p, V3 dir, float ds) {
+/* index and vertical gradient at p; from_bottom = false (mirage.xml): norm = max(0, y / (height / 2)) with the WORLD y,
+ * nonlinear.cpp:149-150 */
+inline void nl_profile(const vrlb_medium &m, V3 p, float &n, float &g) {
     float h = m.nl_bbox_max[1] - m.nl_bbox_min[1];
-    float t = std::fmin(std::fmax((p.y - m.nl_bbox_min[1]) / h, 0.f), 1.f);
-    float n = m.bottom_ior + (m.top_ior - m.bottom_ior) * t;
     bool in = p.x >= m.nl_bbox_min[0] && p.x <= m.nl_bbox_max[0] && p.y >= m.nl_bbox_min[1] && p.y <= m.nl_bbox_max[1] &&
               p.z >= m.nl_bbox_min[2] && p.z <= m.nl_bbox_max[2];
-    float g = in ? (m.top_ior - m.bottom_ior) / h : 0.f;
+    if (m.from_bottom) {
+        float t = std::fmin(std::fmax((p.y - m.nl_bbox_min[1]) / h, 0.f), 1.f);
+        n = m.bottom_ior + (m.top_ior - m.bottom_ior) * t;
+        g = in ? (m.top_ior - m.bottom_ior) / h : 0.f;
+    } else {
+        float hh = h * 0.5f;
+        float t = std::fmax(0.f, p.y / hh);
+        n = m.bottom_ior + (m.top_ior - m.bottom_ior) * t;
+        g = (in && p.y > 0.f) ? (m.top_ior - m.bottom_ior) / hh : 0.f;
+    }
+}
+inline V3 nl_bend(const vrlb_medium &m, V3 p, V3 dir, float ds) {
+    float n, g;
+    nl_profile(m, p, n, g);
     V3 v = dir * n;
     v.y = v.y + ds * g;
     return normalize(v);
@@ -1462,6 +1475,31 @@ void render_pixel(const vrlo_scene &s, const vrlb_camera &cam, const vrlb_option
 }  // namespace
 
 extern "C" {
+
+/* graded-IOR probes: the profile (nonlinear.cpp:129-153) and the fixed-step eikonal march of a ray from o along d through
+ * medium `medium` of the scene until the next surface (the marcher of trace_sample / the light tracer, without the part
+ * cutting): out8 = exit point, exit direction, path length, steps.  Returns 1 if a surface was reached. */
+float vrlo_nl_ior(const vrlb_medium *m, const float p[3]) {
+    float n, g;
+    nl_profile(*m, V3(p), n, g);
+    return n;
+}
+int vrlo_nl_march(const vrlo_scene *s, int medium, const float o[3], const float d[3], float mint, float *out8) {
+    const vrlb_medium &m = s->media[(size_t) medium];
+    V3 pos(o), dir(d);
+    float step_mint = mint, ds = nl_step(m), len = 0.f;
+    int steps = 0; bool found = false;
+    if (!(ds > 0.f)) return 0;
+    for (; steps < 1000000; ++steps) {
+        Hit hit = ray_intersect(*s, pos, dir, step_mint, ds);
+        step_mint = 0.f;
+        if (hit.valid()) { pos = pos + dir * hit.t; len += hit.t; found = true; break; }
+        pos = pos + dir * ds; len += ds;
+        dir = nl_bend(m, pos, dir, ds);
+    }
+    out8[0] = pos.x; out8[1] = pos.y; out8[2] = pos.z; out8[3] = dir.x; out8[4] = dir.y; out8[5] = dir.z; out8[6] = len; out8[7] = (float) steps;
+    return found ? 1 : 0;
+}
 
 uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt,
                              uint64_t n_vrls_total, int rng_mode, vrlb_segment *segs, uint64_t cap,

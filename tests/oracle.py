@@ -61,6 +61,9 @@ def lib():
         L.vrlo_estimate_radiance_volume.argtypes = [C.POINTER(abi.Medium), C.POINTER(abi.PhotonSetDesc), f3, f3, C.c_float, f3]
         L.vrlo_sample_delta.argtypes = [C.c_uint32, f3, f3, f3, C.c_float, f3, f3, C.POINTER(C.c_int)]
         L.vrlo_sample_delta.restype = C.c_int
+        L.vrlo_nl_ior.argtypes = [C.POINTER(abi.Medium), f3]
+        L.vrlo_nl_ior.restype = C.c_float
+        L.vrlo_nl_march.argtypes = [C.c_void_p, C.c_int, f3, f3, C.c_float, f3]
         L.vrlo_vrls_to_long.argtypes = [C.c_void_p, f3, C.c_uint64, f3]
         L.vrlo_vrls_to_long.restype = C.c_uint64
         L.vrlo_vrls_dice.argtypes = [C.c_void_p, f3, C.POINTER(C.c_uint16), C.c_uint64, C.c_uint32, f3, C.POINTER(C.c_uint16), C.c_uint64]
@@ -129,6 +132,12 @@ class OracleScene:
         out = np.zeros((len(segs), 3), np.float32)
         lib().vrlo_photon_gather_segments(self.h, C.byref(photon_desc), segs.ctypes.data, len(segs), C.byref(opt), fp(out))
         return out
+
+    def nl_march(self, o, d, medium=0, mint=0.0):
+        """Fixed-step eikonal march from o along d to the next surface: (found, exit point, exit direction, length, steps)."""
+        out = np.zeros(8, np.float32)
+        ok = lib().vrlo_nl_march(self.h, medium, fp(f32(o)), fp(f32(d)), mint, fp(out))
+        return bool(ok), out[0:3].copy(), out[3:6].copy(), float(out[6]), int(out[7])
 
     def vrls_to_long(self, soa10):
         """VRLMap::toLong: (new lengths, number of VRLs that see no surface)."""

@@ -415,3 +415,41 @@ def test_light_side_specular_chain_and_caustic_photons(ctx):
     behind = (soa[2] > 3.0) & np.isclose(soa[7], power[0], rtol=2e-5)
     assert behind.sum() > 1000
     assert (np.abs(soa[3:6, behind].T - np.array([[0.3, 0.0, 1.0]]) / math.sqrt(1.09)).max(axis=1) < 1e-5).mean() > 0.9
+
+
+def test_grid_medium_light_tracer_takes_null_collisions(ctx):
+    """Delta tracking in the light tracer (vrl.cpp:246-264): free flights are sampled with the majorant and a tentative
+    collision is real with probability sigma_t(x) / majorant.  A laser along +z through a grid whose density steps from
+    rho1 (z < 0) to rho2 (z > 0): the first scatterings (the volume photons) follow sigma(z) exp(-int sigma) -- not the
+    majorant's exponential -- and a VRL runs through null collisions uncut."""
+    L, rho1, rho2, scale = 10.0, 0.25, 1.0, 0.4
+    nz = 80
+    grid = np.empty((nz, 4, 4), np.float32)
+    grid[: nz // 2] = rho1
+    grid[nz // 2:] = rho2
+    m = scenes.make_medium(kind=abi.MEDIUM_GRID, sigma_t=(1, 1, 1), albedo=(0.8,) * 3, scale=scale)
+    m.grid_bbox_min[:] = [-L] * 3
+    m.grid_bbox_max[:] = [L] * 3
+    sc = scenes.Scene()
+    mid = sc.add_medium(m, grid=grid)
+    sc.add_tris(scenes.box_tris((-L,) * 3, (L,) * 3), abi.SURF_BSDF_NULL | abi.surf_interior(mid))
+    ctx.set_scene(sc)
+    gen = scenes.generate_desc(1, seed=5, max_depth=100000, rr_depth=50, laser=((0.1, 0.2, -L + 1e-3), (0, 0, 1), (1, 1, 1)), start_medium=0)
+    n, particles = ctx.generate_photons(gen, 20000, 0.5)
+    pos, pdir, power, pscale = ctx.download_photons()
+    assert n == 20000
+    s1, s2 = scale * rho1, scale * rho2
+    p_first = 1 - np.exp(-s1 * L)                                       # first scattering before the step
+    p_second = np.exp(-s1 * L) * (1 - np.exp(-s2 * L))
+    frac_first = (pos[:, 2] < 0).mean()
+    want = p_first / (p_first + p_second)                               # (particles that cross the box unscattered leave no photon)
+    assert abs(frac_first - want) <= 4 * np.sqrt(want * (1 - want) / n) + 0.01, (frac_first, want)
+    # inside each half the depths are exponential with that half's extinction: mean depth of a truncated exponential
+    mean_trunc = lambda s, ln: 1 / s - ln * np.exp(-s * ln) / (1 - np.exp(-s * ln))
+    z1 = pos[pos[:, 2] < -0.3, 2] + L                                   # (0.3 = more than a voxel away from the trilinear ramp at the step)
+    z2 = pos[pos[:, 2] > 0.3, 2] - 0.3
+    assert z1.mean() == pytest.approx(mean_trunc(s1, L - 0.3), rel=0.04) and z2.mean() == pytest.approx(mean_trunc(s2, L - 0.3), rel=0.04)
+    assert np.allclose(power, 0.8, rtol=1e-5)                            # a null collision leaves the throughput alone
+    # with the majorant's exponential (the behaviour before delta tracking) the first half would hold
+    wrong = (1 - np.exp(-s2 * L))
+    assert abs(frac_first - wrong) > 0.2

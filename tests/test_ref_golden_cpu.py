@@ -289,3 +289,38 @@ def test_delta_bsdf_samples_match_reference_compiled_fresnel():
         n_tir += r == 1 and wi[2] != 0
     assert n_r >= 200 and n_t >= 200 and n_tir >= 10
     assert all(f == 1.0 for _, f in gold["conductor_default"])
+
+
+def test_grid_transmittance_matches_reference_compiled_medium():
+    """Medium::evalTransmittance of the reference (include/mitsuba/render/medium.h:109-155 over src/librender/medium.cpp's
+    sample_interaction / eval_tr_and_pdf, compiled in place by oracle/ref_probe_medium.cpp) for a grid medium, on the same
+    PCG32 sub-streams: the oracle's grid_transmittance gives the same value -- the same number of accepted free-flight steps
+    (the product of exp(-majorant * step) over them) -- for segments inside the grid box, starting outside it, leaving it,
+    axis-parallel and very short; three majorants."""
+    import json, os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_medium.json")) as f:
+        g = json.load(f)
+    worst, n_multi = 0.0, 0
+    by_maj = {}
+    for c in g["cases"]:
+        by_maj.setdefault(round(c["majorant"], 6), []).append(c)
+    assert len(by_maj) == 3
+    for maj, cases in by_maj.items():
+        sc = scenes.Scene()
+        grid = np.full((4, 4, 4), 0.8, np.float32)
+        m = scenes.make_medium(kind=abi.MEDIUM_GRID, sigma_t=(1, 1, 1), albedo=(0.5,) * 3, scale=maj / 0.8)
+        m.grid_bbox_min[:] = g["grid_lo"]
+        m.grid_bbox_max[:] = g["grid_hi"]
+        sc.add_medium(m, grid=grid)
+        osc = oracle.OracleScene(sc)
+        for c in cases:
+            tr = osc.grid_transmittance(c["o"], c["d"], c["maxt"], c["seed"])
+            err = abs(tr - c["tr"]) / max(c["tr"], 1e-30)
+            worst = max(worst, err)
+            assert err <= 3e-6, (c, tr)                      # Enoki's exp / log polynomials against glibc's over <= ~20 factors
+            n_multi += int(c["draws"] >= 4)
+    assert n_multi >= 100                                    # most cases chain several accept steps
+    # homoEvalTransmittance, medium.h:103-107
+    for length, tr in g["homo"]:
+        assert abs(np.exp(np.float32(-g["homo_density"]) * np.float32(length)) - tr) <= 2e-7 * max(tr, 1e-3) + 1e-9
+    print(f"grid transmittance vs reference: max rel err {worst:.2e}")
