@@ -107,6 +107,38 @@ int main(int argc, char **argv) {
             std::printf("triangles %zu bbox %.9g %.9g %.9g %.9g %.9g %.9g checksum %.9g\n", t.size() / 9, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], sum);
             return 0;
         }
+        if (argc >= 4 && std::string(argv[1]) == "dump-xml") {
+            // scene.xml -> the binary scene dump the Python harness reads (scenes.load_scene_dump): what the XML loader hands the
+            // plugin, so that tests can run the SAME loaded fixture through the oracle and through the C ABI
+            std::map<std::string, std::string> defs;
+            for (int i = 4; i < argc; ++i) {
+                std::string a = argv[i];
+                auto eq = a.find('=');
+                if (a.rfind("-D", 0) != 0 || eq == std::string::npos) throw std::runtime_error("expected -Dname=value: " + a);
+                defs[a.substr(2, eq - 2)] = a.substr(eq + 1);
+            }
+            LoadedScene ls = load_scene_xml(argv[2], defs);
+            for (auto &w : ls.warnings) std::fprintf(stderr, "[xml] warning: %s\n", w.c_str());
+            std::ofstream o(argv[3], std::ios::binary);
+            if (!o) throw std::runtime_error(std::string("cannot write ") + argv[3]);
+            auto put = [&](const void *p, size_t n) { o.write((const char *) p, (std::streamsize) n); };
+            auto put_u32 = [&](uint32_t v) { put(&v, 4); };
+            put("VRLD2\0\0\0", 8);
+            put_u32((uint32_t) ls.scene.tri_flags.size());
+            put(ls.scene.tri_verts.data(), ls.scene.tri_verts.size() * 4); put(ls.scene.tri_flags.data(), ls.scene.tri_flags.size() * 4);
+            put_u32((uint32_t) ls.scene.media.size()); put(ls.scene.media.data(), ls.scene.media.size() * sizeof(vrlb_medium));
+            put_u32((uint32_t) ls.scene.emitters.size()); put(ls.scene.emitters.data(), ls.scene.emitters.size() * sizeof(vrlb_emitter));
+            put(&ls.sensor.camera, sizeof(vrlb_camera)); put(&ls.sensor.spp, 4); put(&ls.sensor.sampler_seed, 8);
+            put_u32(ls.scene.tri_reflectance.empty() ? 0u : 1u);
+            put(ls.scene.tri_reflectance.data(), ls.scene.tri_reflectance.size() * 4);
+            for (const vrlb_medium &m : ls.scene.media)
+                if (m.kind == VRLB_MEDIUM_GRID) put(m.grid, (size_t) m.grid_res[0] * m.grid_res[1] * m.grid_res[2] * 4);
+            put(&ls.scene.emission_medium, 4); put(ls.scene.laser_power, 12);
+            if (!o) throw std::runtime_error(std::string("write failed: ") + argv[3]);
+            std::printf("{\"triangles\": %zu, \"media\": %zu, \"emitters\": %zu, \"integrator\": \"%s\"}\n", ls.scene.tri_flags.size(), ls.scene.media.size(),
+                        ls.scene.emitters.size(), ls.integrator_type.c_str());
+            return 0;
+        }
         if (argc >= 3 && (std::string(argv[1]) == "xml-info" || std::string(argv[1]) == "render-xml")) {
             const bool render = std::string(argv[1]) == "render-xml";
             if (render && argc < 4) { std::fprintf(stderr, "usage: vrl_host render-xml scene.xml out.pfm [-Dname=value ...] [key=value ...]\n"); return 2; }

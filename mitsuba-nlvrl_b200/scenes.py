@@ -516,3 +516,51 @@ def save_scene_dump(path, scene, cam, spp=1, seed=0):
         f.write(struct.pack("<I", len(scene.media)) + b"".join(bytes(m) for m in scene.media))
         f.write(struct.pack("<I", len(scene.emitters)) + b"".join(bytes(e) for e in scene.emitters))
         f.write(bytes(cam) + struct.pack("<iQ", spp, seed))
+
+
+def load_scene_dump(path):
+    """The scene dump `vrl_host dump-xml scene.xml out` writes (host/vrl_host_main.cpp): the scene as the C++ XML loader
+    hands it to the plugin.  Returns (Scene, Camera, spp, sampler seed, emission medium)."""
+    import ctypes as C
+    import struct
+    with open(path, "rb") as f:
+        raw = f.read()
+    if raw[:8] != b"VRLD2\0\0\0":
+        raise ValueError(f"{path}: not a VRLD2 scene dump")
+    off = 8
+
+    def take(n):
+        nonlocal off
+        b = raw[off:off + n]
+        if len(b) != n:
+            raise ValueError(f"{path}: truncated")
+        off += n
+        return b
+    n_tris, = struct.unpack("<I", take(4))
+    verts = np.frombuffer(take(n_tris * 36), np.float32).reshape(-1, 3, 3).copy()
+    flags = np.frombuffer(take(n_tris * 4), np.uint32).copy()
+    n_media, = struct.unpack("<I", take(4))
+    media = [abi.Medium.from_buffer_copy(take(C.sizeof(abi.Medium))) for _ in range(n_media)]
+    n_em, = struct.unpack("<I", take(4))
+    emitters = [abi.Emitter.from_buffer_copy(take(C.sizeof(abi.Emitter))) for _ in range(n_em)]
+    cam = abi.Camera.from_buffer_copy(take(C.sizeof(abi.Camera)))
+    spp, seed = struct.unpack("<iQ", take(12))
+    has_refl, = struct.unpack("<I", take(4))
+    refl = np.frombuffer(take(n_tris * 12), np.float32).reshape(-1, 3).copy() if has_refl else None
+    sc = Scene()
+    for m in media:
+        grid, gmax = None, m.grid_max
+        if m.kind == abi.MEDIUM_GRID:
+            nx, ny, nz = m.grid_res
+            grid = np.frombuffer(take(nx * ny * nz * 4), np.float32).reshape(nz, ny, nx).copy()
+        m.grid = None
+        sc.add_medium(m, grid=grid)
+        m.grid_max = gmax                       # the loader's majorant (m_sigmat->max()), not recomputed here
+    for e in emitters:
+        sc.add_emitter(tuple(e.radiance))
+    sc._tris.append(verts)
+    sc._flags.append(flags)
+    sc._refl.append(refl if refl is not None else np.zeros((n_tris, 3), np.float32))
+    sc._any_refl = refl is not None
+    emission_medium, = struct.unpack("<i", take(4))
+    return sc, cam, spp, seed, emission_medium

@@ -1501,6 +1501,13 @@ int vrlo_nl_march(const vrlo_scene *s, int medium, const float o[3], const float
     return found ? 1 : 0;
 }
 
+/* test hook: restrict vrlo_build_segments to the pixels x0 <= x < x1, y0 <= y < y1 (curved paths at 720p are minutes of
+ * single-threaded marching for the whole film); x1 <= x0 resets to the whole film */
+static int g_build_crop[4] = { 0, 0, 1 << 30, 1 << 30 };
+void vrlo_set_build_crop(int x0, int y0, int x1, int y1) {
+    if (x1 <= x0 || y1 <= y0) { g_build_crop[0] = g_build_crop[1] = 0; g_build_crop[2] = g_build_crop[3] = 1 << 30; }
+    else { g_build_crop[0] = x0; g_build_crop[1] = y0; g_build_crop[2] = x1; g_build_crop[3] = y1; }
+}
 uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_options *opt,
                              uint64_t n_vrls_total, int rng_mode, vrlb_segment *segs, uint64_t cap,
                              float *direct_rgb, float *alpha_w) {
@@ -1518,7 +1525,12 @@ uint64_t vrlo_build_segments(const vrlo_scene *s, const vrlb_camera *cam, const 
             int bx0 = bx * opt->block_size, by0 = by * opt->block_size;
             int bw = std::min(opt->block_size, cam->width - bx0), bh = std::min(opt->block_size, cam->height - by0);
             uint32_t bid = ids[(size_t) by * nbx + bx];
+            if (bx0 >= g_build_crop[2] || by0 >= g_build_crop[3] || bx0 + bw <= g_build_crop[0] || by0 + bh <= g_build_crop[1]) continue;
             for (uint32_t i = 0; i < (uint32_t) (opt->block_size * opt->block_size); ++i) {
+                {   /* test hook: only the pixels of the crop window (vrlo_set_build_crop) */
+                    const int cpx = bx0 + (int) compact_bits(i), cpy = by0 + (int) compact_bits(i >> 1);
+                    if (cpx < g_build_crop[0] || cpy < g_build_crop[1] || cpx >= g_build_crop[2] || cpy >= g_build_crop[3]) continue;
+                }
                 auto on_query = [&](const PartOut &p, Sampler &smp, int px, int py, int j) {
                     if (p.n_all > 0) {
                         /* atomic query: the parts as consecutive records sharing the query's stream position;

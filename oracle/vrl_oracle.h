@@ -86,6 +86,7 @@ uint64_t vrlo_build_surface_queries(const vrlo_scene *s, const vrlb_camera *cam,
 /* VRLMap::toLong (vrl_map.h:56-62): new lengths; returns the number of VRLs that see no surface (the reference throws) */
 uint64_t vrlo_vrls_to_long(const vrlo_scene *s, const float *soa10, uint64_t n, float *length_out);
 /* VRLMap::dicingVRL (vrl_map.h:104-128): out_soa10 is [10][cap]; returns the diced count (may exceed cap: nothing lost but the tail) */
+void vrlo_set_build_crop(int x0, int y0, int x1, int y1);
 float vrlo_nl_ior(const vrlb_medium *m, const float p[3]);
 int vrlo_nl_march(const vrlo_scene *s, int medium, const float o[3], const float d[3], float mint, float *out8);
 uint64_t vrlo_vrls_dice(const vrlo_scene *s, const float *soa10, const uint16_t *medium, uint64_t n, uint32_t avg_number_dice,

@@ -61,6 +61,8 @@ def lib():
         L.vrlo_estimate_radiance_volume.argtypes = [C.POINTER(abi.Medium), C.POINTER(abi.PhotonSetDesc), f3, f3, C.c_float, f3]
         L.vrlo_sample_delta.argtypes = [C.c_uint32, f3, f3, f3, C.c_float, f3, f3, C.POINTER(C.c_int)]
         L.vrlo_sample_delta.restype = C.c_int
+        L.vrlo_set_build_crop.argtypes = [C.c_int] * 4
+        L.vrlo_set_build_crop.restype = None
         L.vrlo_nl_ior.argtypes = [C.POINTER(abi.Medium), f3]
         L.vrlo_nl_ior.restype = C.c_float
         L.vrlo_nl_march.argtypes = [C.c_void_p, C.c_int, f3, f3, C.c_float, f3]
@@ -159,7 +161,15 @@ class OracleScene:
         assert m == cap
         return out[:, :m], om[:m]
 
-    def build_segments(self, cam, opt, n_vrls_total, rng_mode=RNG_ADDRESSED, cap=None):
+    def build_segments(self, cam, opt, n_vrls_total, rng_mode=RNG_ADDRESSED, cap=None, crop=None):
+        """crop = (x0, y0, x1, y1): only those pixels' paths (the whole film otherwise)."""
+        lib().vrlo_set_build_crop(*(crop if crop is not None else (0, 0, 0, 0)))
+        try:
+            return self._build_segments(cam, opt, n_vrls_total, rng_mode, cap)
+        finally:
+            lib().vrlo_set_build_crop(0, 0, 0, 0)
+
+    def _build_segments(self, cam, opt, n_vrls_total, rng_mode, cap):
         npix = cam.width * cam.height
         cap = cap or npix * opt.spp * 4
         segs = np.zeros(cap, abi.SEGMENT_DTYPE)
