@@ -48,11 +48,11 @@ def test_config1_cbox_homogeneous_256_1k(ctx):
     li = ctx.gather_segments(opt).astype(np.float64)
     o32, o64, ev = oracle.OracleScene(sc).gather(vd, segs, opt)
     assert ev == 256 * 256 * 1000 * 2
-    err = rel_err(li, o64).max(axis=1)
     # With only 1k VRLs one eval is ~1e-3 of a pixel.  A shadow segment that grazes a triangle edge can be decided
-    # differently when CUDA's sinhf/atanf/tanf and glibc's differ by an ulp in its end points (measured: 3 of 65536
-    # pixels, also on the exactly-rounded kernel); everything else is held to the north-star tolerance.
-    assert (err > REL_TOL).sum() <= 8 and err.max() <= 5e-3, f"{(err > REL_TOL).sum()} pixels, max {err.max():.3e}"
+    # differently when CUDA's sinhf/atanf/tanf and glibc's differ by an ulp in its end points; every segment above the
+    # north-star tolerance has to be explained by such evals (parity_tools.explain), everything else agreeing.
+    import parity_tools
+    err = parity_tools.check_segments(ctx, oracle.OracleScene(sc), segs, np.arange(len(segs)), li, soa, 1.0 / soa.shape[1], opt, "config 1 (256^2 x 1k, q = 2)")
     assert np.quantile(err, 0.999) <= 1e-5
 
 
@@ -68,10 +68,10 @@ def test_config2_grid_volume_512_10k(ctx):
     segs = ctx.download_segments()
     li = ctx.gather_segments(opt).astype(np.float64)
     idx = _band(segs, 512, (254, 256))
-    o32, o64, ev = oracle.OracleScene(sc).gather(vd, segs[idx], opt)
-    err = rel_err(li[idx], o64)
-    # a free-flight accept/reject decided differently by one ulp of logf changes one eval of 10k by a factor (1 - u)
-    assert np.quantile(err, 0.98) <= REL_TOL and err.max() <= 5e-3, f"{err.max():.3e}"
+    # a free-flight accept / reject decided differently by one ulp of logf changes one eval of 10k by a discrete factor:
+    # segments above the tolerance have to be explained by such evals (parity_tools.explain; two of them are re-run)
+    import parity_tools
+    parity_tools.check_segments(ctx, oracle.OracleScene(sc), segs, idx, li, soa, 1.0 / soa.shape[1], opt, "config 2 (512^2 x 10k, grid 128x50x128)", max_explain=2, max_bad=len(idx) // 25)
 
 
 def test_config3_graded_ior_720p(ctx):
@@ -107,7 +107,7 @@ def test_config4_bench_frame_1080p_100k(ctx):
     segs = ctx.download_segments()
     whole = ctx.gather_segments(opt).astype(np.float64)
     y, x = segs["pixel"] // 1920, segs["pixel"] % 1920
-    idx = np.nonzero((y == 540) & (x >= 1100) & (x < 1164))[0]       # 64 pixels through the sphere's silhouette
+    idx = np.nonzero(((y == 540) | (y == 500)) & (x % 2 == 0))[0]    # every other pixel of two full rows: through the sphere's and the cuboid's silhouettes
     o32, o64, ev = oracle.OracleScene(sc).gather(vd, segs[idx], opt)
     err = rel_err(whole[idx], o64)
     assert err.max() <= REL_TOL, f"{err.max():.3e}"

@@ -19,8 +19,6 @@ scenes, api, abi = pkg.scenes, pkg.api, pkg.abi
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 FIX = os.path.join(ROOT, "tests", "golden", "scenes")
-REL_TOL = 1e-4
-
 
 @pytest.fixture(scope="module")
 def host():
@@ -42,46 +40,7 @@ def load_fixture(host, tmp_path, rel, *defs):
     return scenes.load_scene_dump(out)
 
 
-def seg_key(s):
-    return np.lexsort((s["rng_state"], s["part"], s["sample"], s["pixel"]))
-
-
-def rel_err(got, ref):
-    floor = 1e-6 * np.abs(ref).max()
-    return (np.abs(got - ref) / np.maximum(np.abs(ref), floor)).max(axis=-1)
-
-
-def explain(ctx, osc, seg, soa, scale, opt, max_flips=6):
-    """Re-runs one camera segment one VRL at a time on the GPU and on the oracle (global stream addressing keeps every eval
-    on its own draws).  Returns (#evals that differ by a decision, relative error of the sum over all OTHER evals)."""
-    n = soa.shape[1]
-    one = np.ascontiguousarray(seg.reshape(1))
-    ctx.upload_segments(one, 2048, 2048)                       # (pixel index < width * height is all the upload checks)
-    g = np.zeros((n, 3)); o = np.zeros((n, 3))
-    for j in range(n):
-        vd = scenes.vrlset_desc(np.ascontiguousarray(soa[:, j:j + 1]), scale=scale, first_index=j, total=n)
-        ctx.upload_vrls(vd)
-        g[j] = ctx.gather_segments(opt)[0]
-        o[j] = osc.gather(vd, one, opt, n_threads=1)[1][0]
-    mag = np.abs(o).sum(axis=1) + np.abs(g).sum(axis=1)
-    diff = np.abs(g - o).sum(axis=1)
-    flip = diff > 1e-3 * np.maximum(mag, 1e-30)              # one side 0 (shadow decision) or a discrete jump (accept / reject)
-    rest = rel_err(g[~flip].sum(axis=0)[None], o[~flip].sum(axis=0)[None])[0]
-    return int(flip.sum()), float(rest)
-
-
-def check_segments(ctx, osc, segs, idx, li, soa, scale, opt, label, max_explain=6):
-    vd = scenes.vrlset_desc(soa, scale=scale)
-    o32, o64, ev = osc.gather(vd, segs[idx], opt)
-    err = rel_err(li[idx], o64)
-    bad = np.nonzero(err > REL_TOL)[0]
-    print(f"{label}: {len(idx)} segments, {ev:.3g} evals, max rel err {err.max():.2e}, {len(bad)} above 1e-4, median {np.median(err):.1e}")
-    assert len(bad) <= max(8, len(idx) // 2000), (label, len(bad))
-    for k in bad[:max_explain]:
-        flips, rest = explain(ctx, osc, segs[idx[k]], soa, scale, opt)
-        print(f"  segment {idx[k]} (pixel {segs['pixel'][idx[k]]}): rel err {err[k]:.2e} = {flips} decision flips; all other evals agree to {rest:.1e}")
-        assert 1 <= flips <= 12 and rest <= REL_TOL, (label, idx[k], flips, rest)
-    return err
+from parity_tools import REL_TOL, check_segments, explain, rel_err, seg_key
 
 
 def generate_set(ctx, n_target, emission_medium, **kw):
