@@ -68,6 +68,13 @@ def workload(args):
     return sc, cam, opt, soa, name
 
 
+def bench_config(name, n_segs, frame_evals, world):
+    """config of the JSON line; the reference arm prints the same dict key for key."""
+    return {"workload": name, "n_segments": int(n_segs), "evals_per_frame": int(frame_evals),
+            "parallelism": f"vrl-shard x{world} + NCCL fp32 film all-reduce" if world > 1 else "single GPU",
+            "l2": "256 MB flush buffer written between steps; segment buffer 133 MB > L2"}
+
+
 # ------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -171,8 +178,9 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "ms_per_frame_extrapolated": 1e3 * frame_evals / value,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": name, "note": "each step = a bounded crop of the frame on the host cores"},
-            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc},
+            "config": bench_config(name, cam.width * cam.height, frame_evals, args.gpus),     # every pixel of the box-fog frame has one in-medium segment
+            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port",
+                             "sample": desc + "; each step = a bounded crop of the frame on the host cores"},
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -297,30 +305,93 @@ def run_ours(args):
                      "fp32_tflops": ev1 * FLOPS_PER_EVAL / (g1 * 1e-3) * 1e-12,
                      "frac_of_fp32_peak": ev1 * FLOPS_PER_EVAL / (g1 * 1e-3) * 1e-12 / fp32_peak if fp32_peak else None}
 
+    # ---- BASELINE's other workloads on this box, one gather launch each (same sharding; max over ranks) ----------
+    def one_launch(scene_x, cam_x, opt_x, soa_x, label, kernel):
+        shard_x, vd_x = pkg.sharding.shard_desc(soa_x, rank, world)
+        ctx.set_scene(scene_x)
+        ctx.upload_vrls(vd_x)
+        n_x = ctx.build_segments(cam_x, opt_x)
+        ctx.gather(opt_x); ctx.synchronize()                   # warm-up launch (first use of this kernel instantiation)
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        ctx.build_segments(cam_x, opt_x)
+        ctx.gather(opt_x); ctx.synchronize()
+        ms_x = torch.tensor([ctx.timing()["ms_gather"]], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms_x, op=dist.ReduceOp.MAX)
+        ms_x = float(ms_x.item())
+        ev_x = n_x * soa_x.shape[1] * opt_x.samples_per_query
+        return {"workload": label, "n_segments": int(n_x), "evals_per_frame": int(ev_x), "evals_per_s": ev_x / (ms_x * 1e-3),
+                "ms_per_frame_gather": ms_x, "kernel": kernel,
+                "fp32_tflops": ev_x * FLOPS_PER_EVAL / (ms_x * 1e-3) * 1e-12 / world,
+                "frac_of_fp32_peak": (ev_x * FLOPS_PER_EVAL / (ms_x * 1e-3) * 1e-12 / world / fp32_peak) if fp32_peak else None}
+
+    workloads = []
+    if not args.no_occluders and not args.no_secondary:
+        # configs[1] shape (V3): grid medium 128 x 50 x 128, HG phase, 512 x 512, 10k VRLs, shadow rays through the BVH
+        workloads.append(one_launch(scenes.grid_fog_scene(occluders=True, res=(128, 50, 128)), scenes.box_fog_camera(512, 512),
+                                    scenes.default_options(visibility=1), scenes.synthetic_vrls(10000, seed=2),
+                                    "box-fog V3 grid medium 128x50x128 HG, 512x512, N_vrl=10000, BVH visibility",
+                                    "gather_kernel<GRID> (exactly rounded: the stochastic transmittance is a chain of accept / reject decisions)"))
+        note("V3 done")
+        # the north star's target (V4): graded-IOR medium, curved camera paths in straight parts, 1920 x 1080, 100k VRLs
+        workloads.append(one_launch(scenes.nl_fog_scene(occluders=True, res_y=320), scenes.box_fog_camera(args.width, args.height),
+                                    scenes.default_options(visibility=1, use_non_linear_camera=1), soa,
+                                    f"box-fog V4 graded IOR 1.0->0.95 (320 layers), curved camera paths, {args.width}x{args.height}, N_vrl={n_total}, BVH visibility",
+                                    "gather_fast_vis_kernel"))
+        note("V4 done")
+
+    # ---- N > 1: is the sharded, all-reduced film the single-GPU film?  (outside every timed region) ------------------
+    multi_gpu_check = None
+    if world > 1 and not args.no_secondary:
+        n_chk = min(8192, n_total)
+        soa_chk = np.ascontiguousarray(soa[:, :n_chk])
+        ctx.set_scene(sc)
+        _, vd_chk = pkg.sharding.shard_desc(soa_chk, rank, world)
+        ctx.upload_vrls(vd_chk)
+        ctx.build_segments(cam, opt); ctx.gather(opt); ctx.film_allreduce(); ctx.synchronize()
+        sharded = ctx.film_rgb(cam.width, cam.height).astype(np.float64) if rank == 0 else None
+        barrier()
+        if rank == 0:
+            ctx.upload_vrls(scenes.vrlset_desc(soa_chk))
+            ctx.build_segments(cam, opt); ctx.gather(opt); ctx.synchronize()
+            single = ctx.film_rgb(cam.width, cam.height).astype(np.float64)
+            rel = np.abs(sharded - single) / np.maximum(np.abs(single), 1e-6 * np.abs(single).max())
+            multi_gpu_check = {"n_vrls": int(n_chk), "max_rel": float(rel.max()), "pixels_above_1e-5": int((rel.max(axis=-1) > 1e-5).sum()),
+                               "what": f"film of {world} VRL shards summed by NCCL vs the same set on one GPU"}
+            assert rel.max() <= 1e-4, multi_gpu_check
+        barrier()
+
     note("secondary done")
     if rank == 0:
         g_ms = float(np.mean(gather_ms))
         shard_evals = n_segs * (hi - lo) * opt.samples_per_query
         achieved = shard_evals * FLOPS_PER_EVAL / (g_ms * 1e-3) * 1e-12
-        traffic = None
+        # DRAM traffic and pipe utilisation cannot be measured without the profiler: they come from the kept ncu --set full
+        # capture of this kernel on this frame (a 2000-VRL launch; the traffic -- the segment buffer read once, the film
+        # written once -- does not grow with the VRL count), named in traffic_source
+        traffic, kept = None, {}
         tr_file = os.path.join(ROOT, "profiles", "gather_traffic.json")
-        if os.path.exists(tr_file):
+        if os.path.exists(tr_file) and not args.no_occluders:
             try:
-                traffic = json.load(open(tr_file)).get("dram_bytes_per_launch")
+                kept = json.load(open(tr_file))
+                traffic = kept.get("dram_bytes_per_launch")
             except Exception:
-                traffic = None
+                traffic, kept = None, {}
         line = {"metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": total_ms / args.steps, "ms_per_frame": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": name, "n_segments": int(n_segs), "evals_per_frame": int(frame_evals),
-                           "parallelism": f"vrl-shard x{world} + NCCL fp32 film all-reduce" if world > 1 else "single GPU",
-                           "l2": "256 MB flush buffer written between steps; segment buffer 133 MB > L2"},
+                "config": bench_config(name, n_segs, frame_evals, world),
                 "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
                              "frac": achieved / fp32_peak if fp32_peak else None, "traffic": traffic,
                              "kernel": "gather_fast_vis_kernel" if not args.no_occluders else "gather_fast_kernel", "ms_per_launch": g_ms, "flops_per_eval": FLOPS_PER_EVAL,
                              "peak_source": "FFMA microkernel measured in this run (vrlb_measure_fp32_peak); "
-                                            "MEASURED_PEAKS.json has no FP32 entry"},
-                "clocks": clk, "gpu_launches": int(launches), "e2e": e2e, "secondary": secondary}
+                                            "MEASURED_PEAKS.json has no FP32 entry",
+                             "traffic_source": kept.get("source"), "pipe_fma_pct": kept.get("pipe_fma_pct"),
+                             "pipe_alu_pct": kept.get("pipe_alu_pct"), "pipe_xu_pct": kept.get("pipe_xu_pct"),
+                             "issue_active_pct": kept.get("issue_active_pct")},
+                "clocks": clk, "gpu_launches": int(launches), "e2e": e2e, "secondary": secondary, "workloads": workloads,
+                "multi_gpu_check": multi_gpu_check}
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, desc, _, _ = cpu_sample(sc, cam, opt, soa, args.cpu_seconds)
             line["cpu_baseline"] = {"value": rate, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc}
