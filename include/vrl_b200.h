@@ -142,7 +142,7 @@ typedef struct vrlb_options {
     int32_t  hide_emitters;
     int32_t  math_mode;             /* 0: exact (the reference's IEEE operation order, every eval);
                                        1: production: fast arithmetic (FMA, MUFU) with a conditioning guard that
-                                          sends near-singular evals (VRL closer than 0.2 to the camera part, or
+                                          sends near-singular evals (VRL closer than 1 % of the scene's extent to the camera part, or
                                           asinh argument < -8) through the exact path; parity <= 1e-4 per pixel;
                                        2: fast arithmetic without the guard (diagnostic: perf ceiling) */
     int32_t  reserved[2];           /* 0.  (development: override guard thresholds, [0] = h in 1e-3 units, [1] = z) */
@@ -384,6 +384,12 @@ int  vrlb_measure_fp32_peak(vrlb_context *ctx, float *tflops);
  *      counts[2] = triangles left in the main BVH. ---- */
 #define VRLB_SOLID_WORDS 34
 int  vrlb_shadow_proxies(const float *tri_verts, uint32_t n_tris, float *solids_out, uint32_t cap_solids, uint32_t counts[3]);
+
+/* Depth (root = 0) of the closest-hit BVH and of the deepest shadow BVH the library builds for a mesh: the device
+ * traversals use fixed per-lane stacks, so the host build bounds its depth (28; balanced median splits once a binned-SAH
+ * branch would go deeper).  Host only.  Stands where the reference's kd-tree has its own depth limit
+ * (include/mitsuba/render/kdtree.h: max_depth). */
+int  vrlb_bvh_depths(const float *tri_verts, uint32_t n_tris, uint32_t depths[2]);
 
 int  vrlb_cancel(vrlb_context *ctx);
 int  vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out);

@@ -20,7 +20,7 @@ EXPORTS = [
     "vrlb_film_device_ptr", "vrlb_film_download_xyzaw", "vrlb_film_download_rgb", "vrlb_render", "vrlb_cancel",
     "vrlb_get_timing", "vrlb_synchronize", "vrlb_comm_unique_id", "vrlb_comm_init", "vrlb_comm_destroy",
     "vrlb_film_allreduce", "vrlb_film_resolve", "vrlb_measure_fp32_peak", "vrlb_vrls_generate", "vrlb_vrls_scale",
-    "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_vrls_to_long", "vrlb_vrls_dice", "vrlb_vrls_dice_noalloc",
+    "vrlb_vrls_download_depth", "vrlb_shadow_proxies", "vrlb_bvh_depths", "vrlb_vrls_to_long", "vrlb_vrls_dice", "vrlb_vrls_dice_noalloc",
     "vrlb_surface_photons_upload", "vrlb_surface_photons_generate", "vrlb_surface_photons_count", "vrlb_surface_photons_download",
     "vrlb_surface_queries_upload", "vrlb_surface_queries_download", "vrlb_surface_gather_queries",
     "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments", "vrlb_photons_generate", "vrlb_photons_download",
@@ -116,6 +116,7 @@ def load_library():
     L.vrlb_surface_queries_upload.argtypes = [vp, vp, C.c_uint64, C.c_int32, C.c_int32]
     L.vrlb_surface_queries_download.argtypes = [vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.vrlb_surface_gather_queries.argtypes = [vp, f32p]
+    L.vrlb_bvh_depths.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     L.vrlb_shadow_proxies.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     _lib = L
     return L

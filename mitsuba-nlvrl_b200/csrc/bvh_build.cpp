@@ -27,8 +27,20 @@ struct Box {
 };
 }  // namespace
 
+// Depth bound.  The device traversals keep fixed per-lane stacks (vrlb_device.cuh: closest_hit 48 entries, two pushes per
+// level; traverse_any_hit 32, one push per level; gather_fast.cu trace_queue 48 incl. up to 14 pre-pushed single-leaf
+// roots), and a binned-SAH build has no depth bound of its own (a geometric progression of triangle sizes peels one
+// triangle per level).  So the build switches to balanced median splits as soon as the SAH's depth plus the levels a
+// balanced tree still needs for the node's triangles would reach kMaxBvhDepth; 2^19 - 1 triangles need 18 levels.
+constexpr int kMaxBvhDepth = 28;
+static_assert(kMaxBvhDepth + 1 <= 48 && kMaxBvhDepth + 1 <= 32 && kMaxBvhDepth + VRLB_MAX_SHELLS + VRLB_MAX_SOLIDS <= 48,
+              "traversal stacks of vrlb_device.cuh / gather_fast.cu");
+static int g_last_depth = 0;
+int last_bvh_depth() { return g_last_depth; }
+
 void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vector<DNode> &nodes, std::vector<DTri> &tris) {
     nodes.clear(); tris.clear();
+    g_last_depth = 0;
     if (n == 0) return;
     std::vector<Box> tb(n);
     std::vector<float> cen((size_t) n * 3);
@@ -45,10 +57,10 @@ void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vecto
     std::vector<uint32_t> order(n);
     for (uint32_t i = 0; i < n; ++i) order[i] = i;
 
-    struct Item { uint32_t begin, end; int node; };
+    struct Item { uint32_t begin, end; int node; int depth; };
     std::vector<Item> stack;
     nodes.push_back(DNode());
-    stack.push_back({ 0, n, 0 });
+    stack.push_back({ 0, n, 0, 0 });
     constexpr int NB = 16;
     while (!stack.empty()) {
         Item it = stack.back(); stack.pop_back();
@@ -59,7 +71,22 @@ void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vecto
         uint32_t count = it.end - it.begin;
         bool leaf = count <= 4;
         uint32_t mid = 0;
-        if (!leaf) {
+        g_last_depth = std::max(g_last_depth, it.depth);
+        int balanced_levels = 0;                                  // levels a balanced tree needs below this node
+        while ((4u << balanced_levels) < count) ++balanced_levels;
+        const bool force_median = it.depth + balanced_levels + 1 >= kMaxBvhDepth;
+        if (!leaf && force_median) {
+            // object median along the widest centroid axis: the subtree below is balanced, so the bound holds
+            int axis = 0;
+            for (int k = 1; k < 3; ++k) if (cbox.hi[k] - cbox.lo[k] > cbox.hi[axis] - cbox.lo[axis]) axis = k;
+            mid = (it.begin + it.end) / 2;
+            std::nth_element(order.begin() + it.begin, order.begin() + mid, order.begin() + it.end,
+                             [&](uint32_t a, uint32_t b) { return cen[(size_t) a * 3 + axis] < cen[(size_t) b * 3 + axis]; });
+            nd.a = (int32_t) nodes.size(); nodes.push_back(DNode());
+            nd.b = (int32_t) nodes.size(); nodes.push_back(DNode());
+            stack.push_back({ it.begin, mid, nd.a, it.depth + 1 });
+            stack.push_back({ mid, it.end, nd.b, it.depth + 1 });
+        } else if (!leaf) {
             int axis = -1, best_bin = -1; float best = INF;
             for (int k = 0; k < 3; ++k) {
                 float e = cbox.hi[k] - cbox.lo[k];
@@ -93,8 +120,8 @@ void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vecto
             if (count > 16 || axis >= 0) {
                 nd.a = (int32_t) nodes.size(); nodes.push_back(DNode());
                 nd.b = (int32_t) nodes.size(); nodes.push_back(DNode());
-                stack.push_back({ it.begin, mid, nd.a });
-                stack.push_back({ mid, it.end, nd.b });
+                stack.push_back({ it.begin, mid, nd.a, it.depth + 1 });
+                stack.push_back({ mid, it.end, nd.b, it.depth + 1 });
             } else {
                 leaf = true;
             }
@@ -217,6 +244,7 @@ void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, S
             for (size_t i = 0; i < sub.size(); ++i) { std::memcpy(&v[i * 9], verts + (size_t) sub[i] * 9, 36); f[i] = flags ? flags[sub[i]] : 0u; }
             std::vector<DNode> nodes; std::vector<DTri> tris; std::vector<DWNode> w;
             build_bvh(v.data(), f.data(), (uint32_t) sub.size(), nodes, tris);
+            out.max_depth = std::max(out.max_depth, last_bvh_depth());
             build_wide_nodes(nodes, w);
             const uint32_t tri0 = (uint32_t) out.tris.size(), node0 = (uint32_t) out.wnodes.size();
             for (DTri &t : tris) { t.prim = sub[t.prim]; out.tris.push_back(t); }

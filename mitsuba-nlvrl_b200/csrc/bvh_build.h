@@ -9,6 +9,7 @@ namespace vrlb {
 // verts: n*9 floats (p0 p1 p2 per triangle), flags: n surface words (may be null).
 // Produces the flattened binary BVH (root = node 0) and the triangles in leaf order.
 void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vector<DNode> &nodes, std::vector<DTri> &tris);
+int last_bvh_depth();      // depth (root = 0) of the tree the last build_bvh call produced; bounded by kMaxBvhDepth (bvh_build.cpp)
 // Re-packs the binary BVH for the shadow traversal: one DWNode per inner node holding both children's boxes.
 // Empty when the root is a leaf.
 void build_wide_nodes(const std::vector<DNode> &nodes, std::vector<DWNode> &wnodes);
@@ -22,6 +23,7 @@ struct ShadowAccel {
     float    main_lo[3] = { 0, 0, 0 }, main_hi[3] = { 0, 0, 0 };
     bool     has_main = false;
     uint32_t n_main_tris = 0;
+    int      max_depth = 0;        // deepest of the BVHs in here
 };
 // proxies of one component (triangle indices `sub` into verts); fills everything but `root`
 void build_solid_proxies(const float *verts, const std::vector<uint32_t> &sub, float margin, DSolid &out);

@@ -52,6 +52,7 @@ struct vrlb_context {
     DevBuf<DTri> tris; DevBuf<float> verts; DevBuf<DNode> nodes; DevBuf<DWNode> wnodes; DevBuf<DTri> stris; DevBuf<DMedium> media; DevBuf<float> emitters; DevBuf<float> tri_refl; bool have_refl = false; DevBuf<float> grids; bool any_grid = false; DevBuf<DSolid> solids;
     DScene scene{};
     bool have_scene = false;
+    float scene_extent = 20.f;        // largest side of the geometry's bounding box (the conditioning guard scales with it)
     std::vector<vrlb_medium> host_media;
     std::vector<DTri> host_tris;      // BVH order, for the emitter table of vrlb_vrls_generate
 
@@ -195,6 +196,10 @@ void vrlb_destroy(vrlb_context *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->wnodes.release(); ctx->stris.release(); ctx->media.release(); ctx->emitters.release(); ctx->grids.release(); ctx->solids.release();
+    ctx->tri_refl.release(); ctx->squeries.release();
+    ctx->vol.photons.release(); ctx->vol.cells.release();
+    for (auto &m : ctx->surf) { m.photons.release(); m.cells.release(); }
+    if (ctx->wd) cudaFreeHost(ctx->wd);
     ctx->vrls.release(); ctx->vrls_fast.release(); ctx->vrls_vis.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
     if (ctx->nccl_comm && g_nccl_destroy) g_nccl_destroy(ctx->nccl_comm);
     ctx->block_ids.release(); ctx->film_rgb.release(); ctx->film_aw.release(); ctx->film_xyzaw.release();
@@ -232,6 +237,16 @@ int vrlb_shadow_proxies(const float *tri_verts, uint32_t n_tris, float *solids_o
     if (solids_out)
         for (size_t i = 0; i < sa.solids.size() && i < cap_solids; ++i) std::memcpy(solids_out + i * VRLB_SOLID_WORDS, &sa.solids[i], sizeof(DSolid));
     counts[2] = sa.n_main_tris;
+    return VRLB_OK;
+}
+
+int vrlb_bvh_depths(const float *tri_verts, uint32_t n_tris, uint32_t depths[2]) {
+    if ((n_tris && !tri_verts) || !depths) return VRLB_ERR_INVALID;
+    std::vector<DNode> nodes; std::vector<DTri> tris;
+    build_bvh(tri_verts, nullptr, n_tris, nodes, tris);
+    depths[0] = (uint32_t) last_bvh_depth();
+    ShadowAccel sa; build_shadow_accel(tri_verts, nullptr, n_tris, sa);
+    depths[1] = (uint32_t) sa.max_depth;
     return VRLB_OK;
 }
 
@@ -297,6 +312,12 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
         }
         dm[i] = d;
     }
+    if (sc->n_tris) {
+        float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY };
+        for (size_t i = 0; i < (size_t) sc->n_tris * 9; ++i) { lo[i % 3] = std::min(lo[i % 3], sc->tri_verts[i]); hi[i % 3] = std::max(hi[i % 3], sc->tri_verts[i]); }
+        const float ext = std::max(hi[0] - lo[0], std::max(hi[1] - lo[1], hi[2] - lo[2]));
+        ctx->scene_extent = (ext > 0.f && std::isfinite(ext)) ? ext : 20.f;
+    } else ctx->scene_extent = 20.f;
     std::vector<DNode> nodes; std::vector<DTri> tris;
     build_bvh(sc->tri_verts, sc->tri_flags, sc->n_tris, nodes, tris);
     ShadowAccel sa; build_shadow_accel(sc->tri_verts, sc->tri_flags, sc->n_tris, sa);
@@ -453,7 +474,7 @@ int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_
     GenParams p{};
     { int rc = setup_generate(ctx, gen, p, d_etris, d_ecdf); if (rc) return rc; }
     const uint64_t target = gen->target_vrls;
-    uint64_t have = 0, particles = 0;
+    uint64_t have = 0, particles = 0, producing = 0;              // producing: particles that stored at least one VRL (volumePath, vrl.cpp:370)
     uint64_t wave = std::min<uint64_t>(std::max<uint64_t>(target / 4, 4096), 1u << 22);
     std::vector<uint32_t> counts; std::vector<uint64_t> offsets;
     bool done = false;
@@ -469,6 +490,7 @@ int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_
         uint64_t used = wave;
         for (uint64_t i = 0; i < wave; ++i) {
             offsets[i + 1] = offsets[i] + counts[i];
+            if (counts[i]) ++producing;
             if (have + offsets[i + 1] >= target) { used = i + 1; done = true; break; }       // the particle that fills the map is the last one
         }
         const uint64_t add = offsets[used];
@@ -493,7 +515,12 @@ int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_
     }
     d_etris.release(); d_ecdf.release(); d_counts.release(); d_offsets.release();
     if (have == 0) return fail(ctx, VRLB_ERR_STATE, "light tracing produced no VRL (no particle reached a medium)");
-    ctx->n_vrls = have; ctx->vrl_first = 0; ctx->vrl_total = have; ctx->vrl_scale = 1.0f / (float) particles;   // vrl.cpp:404,423
+    // VRLMap::push_back refuses once the map holds target_vrls (vrl_map.h:43-45): the VRLs of the filling particle beyond
+    // the target are dropped.  m_scale = 1 / volumePathCount (vrl.cpp:404, 423), and a particle counts when it stored a VRL
+    // and the map is not full after it (vrl.cpp:370-371): the filling particle does not.
+    if (have > target) have = target;
+    const uint64_t counted = done && producing > 1 ? producing - 1 : producing;
+    ctx->n_vrls = have; ctx->vrl_first = 0; ctx->vrl_total = have; ctx->vrl_scale = 1.0f / (float) std::max<uint64_t>(counted, 1);
     ctx->fast_dirty = true;
     if (n_vrls_out) *n_vrls_out = have;
     if (n_particles_out) *n_particles_out = particles;
@@ -687,7 +714,10 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
         ctx->fast_dirty = false;
     }
     p.vrls_fast = ctx->vrls_fast.ptr; p.vrls_vis = ctx->vrls_vis.ptr;
-    p.guard_h = opt->reserved[0] ? (float) opt->reserved[0] * 1e-3f : 0.2f;   // dev knobs (milli-units); 0 = shipped defaults
+    // Conditioning guard: evals whose VRL passes closer than 1 % of the scene's extent to the camera part take the exactly
+    // rounded path.  The fast path's position error is ~1e-6 of the coordinates' magnitude and the equi-angular pdf amplifies
+    // it by 1 / h, so the threshold has to scale with the scene (0.2 on the +-10 box-fog scene the kernel was tuned on).
+    p.guard_h = opt->reserved[0] ? (float) opt->reserved[0] * 1e-3f : 0.01f * ctx->scene_extent / 1.001f;   // dev knob (milli-units); 0 = shipped default
     p.guard_z = opt->reserved[1] ? (float) opt->reserved[1] : 8.0f;
     cudaEventRecord(ctx->ev[2], ctx->stream);
     if (!fast) CU(ctx, launch_gather(p, uniform, opt->rr_vrl != 0, vis, ctx->any_grid, ctx->stream));

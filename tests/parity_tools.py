@@ -52,3 +52,28 @@ def check_segments(ctx, osc, segs, idx, li, soa, scale, opt, label, max_explain=
     return err
 
 
+
+
+def check_pixels(ctx, osc, segs, idx, li, soa, scale, opt, label, max_explain=4, max_bad=8):
+    """Curved camera paths: the north star's tolerance is per PIXEL -- the sum over a path's parts of weight * Li.  (A single
+    part can be a stub of 1e-5 of its path; the equi-angular pdf of such a part, theta_B - theta_A of two nearly equal
+    arctangents, carries 1e-3 of relative rounding noise in ANY fp32 evaluation, the reference's included, at 1e-8 of the
+    pixel.)  `idx` must hold complete paths.  An offending pixel is explained through its worst part."""
+    vd = scenes.vrlset_desc(soa, scale=scale)
+    o32, o64, ev = osc.gather(vd, segs[idx], opt)
+    pix, inv = np.unique(segs["pixel"][idx], return_inverse=True)
+    got, ref = np.zeros((len(pix), 3)), np.zeros((len(pix), 3))
+    w = segs["weight"][idx].astype(np.float64)
+    np.add.at(got, inv, li[idx] * w)
+    np.add.at(ref, inv, o64 * w)
+    err = rel_err(got, ref)
+    bad = np.nonzero(err > REL_TOL)[0]
+    print(f"{label}: {len(pix)} pixels / {len(idx)} parts, {ev:.3g} evals, max rel err per pixel {err.max():.2e}, {len(bad)} above 1e-4, median {np.median(err):.1e}")
+    assert len(bad) <= max_bad, (label, len(bad))
+    for k in bad[:max_explain]:
+        members = np.nonzero(inv == k)[0]
+        worst = members[np.argmax(np.abs((li[idx][members] - o64[members]) * w[members]).sum(axis=1))]
+        flips, rest = explain(ctx, osc, segs[idx[worst]], soa, scale, opt)
+        print(f"  pixel {pix[k]}: rel err {err[k]:.2e}; its worst part has {flips} decision flips, all its other evals agree to {rest:.1e}")
+        assert 1 <= flips <= 12 and rest <= REL_TOL, (label, pix[k], flips, rest)
+    return err

@@ -561,3 +561,39 @@ def test_spp4_matches_oracle(ctx, math_mode):
     ref_xyzaw, _, _ = osc.render(cam, opt, vd)
     assert np.array_equal(out[..., 3:], ref_xyzaw[..., 3:]) and out[..., 4].min() == 4.0
     assert film_err_fp64(ctx, osc, cam, opt, vd, soa.shape[1]).max() <= 5e-3          # (the per-segment check above carries the tolerance)
+
+
+@pytest.mark.parametrize("scale", [0.05, 50.0])
+def test_fast_path_parity_is_scale_invariant(ctx, scale):
+    """The conditioning guard of math_mode 1 is 1 % of the scene's extent, not an absolute length: the same frame with every
+    length multiplied by 0.05 / 50 (extinction divided accordingly) keeps the per-segment parity, and the share of evals the
+    guard sends to the exactly-rounded path stays what it is on the +-10 box (timing: no 5x slow-down at the small scale)."""
+    sc0, cam0, opt, soa0 = _setup(True, n_vrls=1500, w=48, h=32, visibility=1, math_mode=1)
+    sc = scenes.Scene()
+    m = scenes.make_medium(sigma_t=(0.11 / scale,) * 3, albedo=(0.1 / 0.11,) * 3)
+    sc.add_medium(m)
+    flags = sc0.tri_flags
+    start = 0
+    tv = sc0.tri_verts * np.float32(scale)
+    while start < len(flags):
+        end = start + 1
+        while end < len(flags) and flags[end] == flags[start]:
+            end += 1
+        sc.add_tris(tv[start:end], int(flags[start]))
+        start = end
+    cam = scenes.make_camera(48, 32, origin=(0, 0, -40 * scale), target=(0, 0, -39 * scale), fov=36.0, fov_axis="x",
+                             near_clip=0.1 * scale, far_clip=1000.0 * scale)
+    soa = soa0.copy()
+    soa[0:3] *= np.float32(scale); soa[6] *= np.float32(scale)
+    soa = np.ascontiguousarray(soa)
+    vd = scenes.vrlset_desc(soa)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(vd)
+    n = ctx.build_segments(cam, opt)
+    assert n == 48 * 32
+    segs = ctx.download_segments()
+    li = ctx.gather_segments(opt).astype(np.float64)
+    osc = oracle.OracleScene(sc)
+    import parity_tools
+    err = parity_tools.check_segments(ctx, osc, segs, np.arange(n), li, soa, 1.0 / soa.shape[1], opt, f"box-fog x {scale}", max_explain=3)
+    assert np.quantile(err, 0.99) <= 1e-5

@@ -103,7 +103,7 @@ def test_light_tracer_flights_follow_the_reference_walk(ctx, gold, name):
     for r, reg in zip(m["rays"], regular):
         if not reg or np.sign(r["exit_d"][1]) != np.sign(r["d"][1]):
             continue
-        gen = scenes.generate_desc(1, seed=1, min_vrl_length=0.5, laser=(r["o"], r["d"], (1, 1, 1)), start_medium=0, max_steps=1000000)
+        gen = scenes.generate_desc(1500, seed=1, min_vrl_length=4.0, laser=(r["o"], r["d"], (1, 1, 1)), start_medium=0, max_steps=1000000)
         n, particles = ctx.generate_vrls(gen)
         soa, _ = ctx.download_vrls()
         o, dd, ln = soa[0:3].T.astype(np.float64), soa[3:6].T.astype(np.float64), soa[6].astype(np.float64)

@@ -77,3 +77,24 @@ def test_open_mesh_gets_no_inner_proxy():
     allt = np.concatenate([np.asarray(tris, np.float32).reshape(-1, 9), np.asarray(more, np.float32).reshape(-1, 9)])
     solids, n_shells, n_main = api.shadow_proxies(allt)
     assert len(solids) == 1 and (solids[0]["flags"] & 6) == 0
+
+
+def test_bvh_depth_is_bounded_for_adversarial_meshes():
+    """A strip of triangles whose sizes form a geometric progression makes a binned-SAH build peel one triangle per level;
+    the device traversals have fixed stacks (48 / 32 entries), so the host build must stay below its depth bound (28)."""
+    import ctypes as C
+    n = 400
+    x = np.cumsum(1.5 ** (np.arange(n + 1) * 0.25)) * 1e-6          # 1e-6 .. ~1e11: sizes over 17 decades
+    tris = np.zeros((n, 3, 3), np.float32)
+    tris[:, 0, 0] = x[:-1]; tris[:, 1, 0] = x[1:]; tris[:, 2, 0] = x[:-1]
+    tris[:, 2, 1] = (x[1:] - x[:-1])
+    tris[:, :, 2] = np.linspace(0, 1, n)[:, None]                     # not coplanar: an ordinary component, not a shell
+    lib = api.load_library()
+    d = (C.c_uint32 * 2)()
+    v = np.ascontiguousarray(tris.reshape(-1))
+    assert lib.vrlb_bvh_depths(v.ctypes.data_as(C.POINTER(C.c_float)), n, d) == 0
+    assert 8 <= d[0] <= 28 and d[1] <= 28, list(d)
+    # an ordinary mesh stays shallow
+    sph = np.ascontiguousarray(scenes.sphere_tris((0, 0, 0), 1.0).reshape(-1), np.float32)
+    assert lib.vrlb_bvh_depths(sph.ctypes.data_as(C.POINTER(C.c_float)), len(sph) // 9, d) == 0
+    assert d[0] <= 16 and d[1] <= 16
