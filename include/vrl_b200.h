@@ -34,7 +34,8 @@ enum {
     VRLB_ERR_CUDA      = -2,  /* CUDA runtime failure or no device                                 */
     VRLB_ERR_STATE     = -3,  /* call order violated (e.g. gather before a VRL set is resident)   */
     VRLB_ERR_CANCELLED = -4,  /* vrlb_cancel() observed; mirrors Integrator::cancel, integrator.h:148 */
-    VRLB_ERR_NOMEM     = -5
+    VRLB_ERR_NOMEM     = -5,
+    VRLB_ERR_UNSUPPORTED = -6 /* a combination the reference itself rejects, or one this library does not build (message says which) */
 };
 
 /* ---- surfaces ---------------------------------------------------------- */
@@ -146,6 +147,14 @@ typedef struct vrlb_options {
                                           asinh argument < -8) through the exact path; parity <= 1e-4 per pixel;
                                        2: fast arithmetic without the guard (diagnostic: perf ceiling) */
     int32_t  reserved[2];           /* 0.  (development: override guard thresholds, [0] = h in 1e-3 units, [1] = z) */
+    /* the VRL light cut (vrl_lightcut.h; properties vrl.cpp:66-72) */
+    int32_t  use_light_cut;         /* 1: every query walks the cut of the light tree built by vrlb_lightcut_build
+                                       (VRLMap::query's ELightCutAcceleration branch, vrl_map.h:198-201) */
+    float    threshold_error;       /* m_errorRatio: a cluster is refined while its bound >= threshold_error * hmax(Li) (0.02) */
+    int32_t  threshold_better_dist; /* clusters of at most this many VRLs bound the distance by exact segment-segment
+                                       distances instead of the box (8) */
+    int32_t  lightcut_heap;         /* 0 = default (4096): entries of a query's refinement heap; a query that needs more
+                                       is counted in vrlb_lightcut_stats and finishes with the exact sum over the VRLs */
 } vrlb_options;
 
 /* ---- VRL set ----------------------------------------------------------- */
@@ -344,6 +353,36 @@ int  vrlb_gather(vrlb_context *ctx, const vrlb_options *opt);
 /* Same, and additionally returns Li per resident segment BEFORE the weight (host, n_segments*3 fp32):
  * exactly the `color` VRLMap::query returns (vrl_map.h:210), for per-segment parity checks. */
 int  vrlb_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *li_out);
+
+/* ---- the VRL light cut: replaces VRLLightCut (src/integrators/vrl/vrl_lightcut.h), which VRLMap::build creates when
+ *      use_light_cut is set (vrl_map.h:89-97) and VRLMap::query walks instead of the whole set (vrl_map.h:198-201). ---- */
+/* Builds the reference's light tree (vrl_lightcut.h:196-212 -> buildLightTree :515-627: greedy bottom-up clustering by
+ * Node::dist :101-109, one sampler draw per merge for the representative :137-150) over the resident VRL set -- the same
+ * tree as the reference builds from the same VRLs and the same sampler (sampler.seed(base_seed, seed_offset), the sampler
+ * VRLIntegrator::preprocess hands to VRLMap::build, vrl.cpp:424).  The partner searches run on the device.  A context
+ * holding a shard builds the tree of its shard.  Any call that changes the VRL set drops the tree.
+ * Not built: stochastic_lightcut (shuffleRepresentativeLight re-draws representatives per query on a per-thread copy of
+ * the tree, vrl_lightcut.h:153-193) -> the host mirror reports it as unsupported. */
+int  vrlb_lightcut_build(vrlb_context *ctx, uint64_t base_seed, uint64_t seed_offset);
+/* The tree in preorder, for parity checks: f13[k] = cluster flux(3), addFlux(3), aabb lo(3) hi(3), maxVRLLenght;
+ * i6[k] = is leaf, VRL of the representative, child sharing it (isSame; -1 for a leaf), VRLs in the cluster, id, parent id.
+ * Returns the node count through n_out (2 n - 1); writes at most cap nodes. */
+int  vrlb_lightcut_download(vrlb_context *ctx, float *f13, int32_t *i6, uint64_t cap, uint64_t *n_out);
+typedef struct vrlb_lightcut_stats {
+    uint64_t n_nodes;        /* 2 n - 1                                                              */
+    uint64_t build_searches; /* partner searches of the build (n in one launch + one launch each)     */
+    float    build_ms;       /* wall time of vrlb_lightcut_build                                      */
+    float    pad;
+    uint64_t queries;        /* of the last gather through the cut: queries (segments x samples_per_query ...) */
+    uint64_t evaluations;    /* ... fresh getContrib calls (LCQuery::nb_evaluation summed)            */
+    uint64_t refinements;    /* ... clusters replaced by their children                               */
+    uint64_t overflows;      /* ... queries whose heap outgrew lightcut_heap and were summed exactly   */
+    uint64_t max_heap;       /* ... largest refinement heap                                           */
+} vrlb_lightcut_stats;
+int  vrlb_lightcut_get_stats(const vrlb_context *ctx, vrlb_lightcut_stats *out);
+/* vrlb_gather_segments through the cut (opt->use_light_cut is implied), additionally returning per segment
+ * stats4 = fresh evaluations, refinements, largest heap, 1 if the query overflowed (host, n_segments*4 fp32; may be NULL). */
+int  vrlb_lightcut_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *li_out, float *stats4_out);
 /* Device pointer of the fp32 RGB radiance accumulation buffer (width*height*3 floats) so that a
  * multi-GPU host can sum VRL shards with NCCL without a host round trip. */
 int  vrlb_film_device_ptr(vrlb_context *ctx, void **dev_ptr, uint64_t *n_floats);

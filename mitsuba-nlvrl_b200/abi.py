@@ -3,7 +3,7 @@ import ctypes as C
 
 COMM_ID_BYTES = 128
 NOALLOC_MAX_VRLS = 65536
-OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CANCELLED, ERR_NOMEM = 0, -1, -2, -3, -4, -5
+OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_CANCELLED, ERR_NOMEM, ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6
 
 SURF_BSDF_SMOOTH, SURF_BSDF_NULL, SURF_EMITTER, SURF_TWOSIDED = 0x0, 0x1, 0x4, 0x8
 SURF_BSDF_MIRROR, SURF_BSDF_DIELECTRIC = 0x2, 0x3
@@ -47,7 +47,8 @@ class Options(C.Structure):
                 ("samples_per_query", C.c_int32), ("use_uniform_sampling", C.c_int32), ("rr_vrl", C.c_int32),
                 ("scale_rr", C.c_float), ("max_depth", C.c_int32), ("use_non_linear_camera", C.c_int32),
                 ("use_nl_atomic_query", C.c_int32), ("visibility", C.c_int32), ("hide_emitters", C.c_int32),
-                ("math_mode", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("math_mode", C.c_int32), ("reserved", C.c_int32 * 2),
+                ("use_light_cut", C.c_int32), ("threshold_error", C.c_float), ("threshold_better_dist", C.c_int32), ("lightcut_heap", C.c_int32)]
 
 
 class VrlSetDesc(C.Structure):
@@ -87,6 +88,12 @@ class Timing(C.Structure):
                 ("ms_download", C.c_float), ("gather_launches", C.c_uint32), ("total_launches", C.c_uint32),
                 ("n_evals", C.c_uint64), ("n_segments", C.c_uint64),
                 ("launches_lifetime", C.c_uint64), ("ms_reduce", C.c_float), ("pad", C.c_float)]
+
+
+class LightcutStats(C.Structure):
+    _fields_ = [("n_nodes", C.c_uint64), ("build_searches", C.c_uint64), ("build_ms", C.c_float), ("pad", C.c_float),
+                ("queries", C.c_uint64), ("evaluations", C.c_uint64), ("refinements", C.c_uint64), ("overflows", C.c_uint64),
+                ("max_heap", C.c_uint64)]
 
 
 assert C.sizeof(Segment) == 64

@@ -24,6 +24,7 @@ EXPORTS = [
     "vrlb_surface_photons_upload", "vrlb_surface_photons_generate", "vrlb_surface_photons_count", "vrlb_surface_photons_download",
     "vrlb_surface_queries_upload", "vrlb_surface_queries_download", "vrlb_surface_gather_queries",
     "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments", "vrlb_photons_generate", "vrlb_photons_download",
+    "vrlb_lightcut_build", "vrlb_lightcut_download", "vrlb_lightcut_get_stats", "vrlb_lightcut_gather_segments",
 ]
 
 
@@ -116,6 +117,10 @@ def load_library():
     L.vrlb_surface_queries_upload.argtypes = [vp, vp, C.c_uint64, C.c_int32, C.c_int32]
     L.vrlb_surface_queries_download.argtypes = [vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
     L.vrlb_surface_gather_queries.argtypes = [vp, f32p]
+    L.vrlb_lightcut_build.argtypes = [vp, C.c_uint64, C.c_uint64]
+    L.vrlb_lightcut_download.argtypes = [vp, f32p, C.POINTER(C.c_int32), C.c_uint64, C.POINTER(C.c_uint64)]
+    L.vrlb_lightcut_get_stats.argtypes = [vp, C.POINTER(abi.LightcutStats)]
+    L.vrlb_lightcut_gather_segments.argtypes = [vp, C.POINTER(abi.Options), f32p, f32p]
     L.vrlb_bvh_depths.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     L.vrlb_shadow_proxies.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     _lib = L
@@ -284,6 +289,31 @@ class Context:
 
     def gather(self, opt):
         self._check(self.lib.vrlb_gather(self.h, C.byref(opt)))
+
+    def lightcut_build(self, seed_offset=0, base_seed=0):
+        """VRLLightCut constructor (vrl_lightcut.h:196-212) over the resident VRL set; the sampler is sampler.seed(base_seed, seed_offset)."""
+        self._check(self.lib.vrlb_lightcut_build(self.h, base_seed, seed_offset))
+
+    def lightcut_download(self):
+        """The tree in preorder: (f [n,13] = flux, add_flux, lo, hi, max_len; i [n,6] = leaf, rep VRL, same child, n_leaves, id, parent id)."""
+        n = C.c_uint64()
+        self._check(self.lib.vrlb_lightcut_download(self.h, None, None, 0, C.byref(n)))
+        f, i = np.zeros((n.value, 13), np.float32), np.zeros((n.value, 6), np.int32)
+        self._check(self.lib.vrlb_lightcut_download(self.h, f.ctypes.data_as(C.POINTER(C.c_float)), i.ctypes.data_as(C.POINTER(C.c_int32)), n.value, C.byref(n)))
+        return f, i
+
+    def lightcut_stats(self):
+        st = abi.LightcutStats()
+        self._check(self.lib.vrlb_lightcut_get_stats(self.h, C.byref(st)))
+        return st
+
+    def lightcut_gather_segments(self, opt):
+        """Li per resident segment through the cut + per-segment [fresh evaluations, refinements, largest heap, overflowed]."""
+        n = self.lib.vrlb_segments_count(self.h)
+        out, st = np.zeros((n, 3), np.float32), np.zeros((n, 4), np.float32)
+        self._check(self.lib.vrlb_lightcut_gather_segments(self.h, C.byref(opt), out.ctypes.data_as(C.POINTER(C.c_float)),
+                                                           st.ctypes.data_as(C.POINTER(C.c_float))))
+        return out, st
 
     def gather_segments(self, opt):
         n = int(self.lib.vrlb_segments_count(self.h))

@@ -18,6 +18,7 @@
 #include "../../include/vrl_b200.h"
 #include "bvh_build.h"
 #include "vrlb_kernels.h"
+#include "lightcut.h"
 
 using namespace vrlb;
 
@@ -60,6 +61,11 @@ struct vrlb_context {
     DevBuf<DVrl> vrls, vrls_fast; DevBuf<DVrlV> vrls_vis; bool fast_dirty = true; bool all_iso = true;
     DevBuf<float> stage_soa; DevBuf<uint16_t> stage_med;
     uint64_t n_vrls = 0, vrl_first = 0, vrl_total = 0; float vrl_scale = 1.f;
+    // light cut over the resident set (lightcut.cu); dropped whenever the set changes
+    LightcutTree *lc = nullptr;
+    DevBuf<unsigned long long> lc_heap; DevBuf<float4> lc_slots; DevBuf<unsigned long long> lc_stats; DevBuf<float> lc_seg_stats;
+    vrlb_lightcut_stats lc_last{};
+    void vrls_changed() { fast_dirty = true; if (lc) { lightcut_free(lc); lc = nullptr; } }
 
     // volume photon map (photons.cu): sorted by grid cell
     struct PhotonMapRes {
@@ -200,6 +206,8 @@ void vrlb_destroy(vrlb_context *ctx) {
     ctx->vol.photons.release(); ctx->vol.cells.release();
     for (auto &m : ctx->surf) { m.photons.release(); m.cells.release(); }
     if (ctx->wd) cudaFreeHost(ctx->wd);
+    if (ctx->lc) lightcut_free(ctx->lc);
+    ctx->lc_heap.release(); ctx->lc_slots.release(); ctx->lc_stats.release(); ctx->lc_seg_stats.release();
     ctx->vrls.release(); ctx->vrls_fast.release(); ctx->vrls_vis.release(); ctx->stage_soa.release(); ctx->stage_med.release(); ctx->segs.release(); ctx->counter.release();
     if (ctx->nccl_comm && g_nccl_destroy) g_nccl_destroy(ctx->nccl_comm);
     ctx->block_ids.release(); ctx->film_rgb.release(); ctx->film_aw.release(); ctx->film_xyzaw.release();
@@ -397,7 +405,7 @@ int vrlb_vrls_upload(vrlb_context *ctx, const vrlb_vrlset_desc *set) {
     cudaEventRecord(ctx->ev[1], ctx->stream);
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->timing.ms_upload = elapsed(ctx->ev[0], ctx->ev[1]);
-    ctx->fast_dirty = true;
+    ctx->vrls_changed();
     ctx->n_vrls = n; ctx->vrl_first = set->first_index; ctx->vrl_total = total; ctx->vrl_scale = set->scale;
     return VRLB_OK;
 }
@@ -521,7 +529,7 @@ int vrlb_vrls_generate(vrlb_context *ctx, const vrlb_generate_desc *gen, uint64_
     if (have > target) have = target;
     const uint64_t counted = done && producing > 1 ? producing - 1 : producing;
     ctx->n_vrls = have; ctx->vrl_first = 0; ctx->vrl_total = have; ctx->vrl_scale = 1.0f / (float) std::max<uint64_t>(counted, 1);
-    ctx->fast_dirty = true;
+    ctx->vrls_changed();
     if (n_vrls_out) *n_vrls_out = have;
     if (n_particles_out) *n_particles_out = particles;
     return VRLB_OK;
@@ -539,7 +547,7 @@ int vrlb_vrls_to_long(vrlb_context *ctx) {
     unsigned long long missed = 0;
     CU(ctx, cudaMemcpyAsync(&missed, ctx->counter.ptr, sizeof missed, cudaMemcpyDeviceToHost, ctx->stream));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->fast_dirty = true;
+    ctx->vrls_changed();
     // VRL::convertToLong: Log(Error, ...) throws in the reference
     if (missed) return fail(ctx, VRLB_ERR_STATE, "Impossible to convert to long vrl... (%llu VRLs see no surface)", missed);
     return VRLB_OK;
@@ -581,7 +589,7 @@ int vrlb_vrls_dice(vrlb_context *ctx, uint32_t avg_number_dice, uint64_t *n_out)
     ctx->vrls.release(); ctx->vrls = diced; diced.ptr = nullptr; diced.cap = 0;
     d_counts.release(); d_offsets.release();
     ctx->n_vrls = total; ctx->vrl_first = 0; ctx->vrl_total = total;      // m_scale is untouched (vrl.cpp:412-423)
-    ctx->fast_dirty = true;
+    ctx->vrls_changed();
     if (n_out) *n_out = total;
     return VRLB_OK;
 }
@@ -681,12 +689,52 @@ int vrlb_film_clear(vrlb_context *ctx) {
     return VRLB_OK;
 }
 
+// VRLMap::query's ELightCutAcceleration branch (vrl_map.h:198-201) for every resident segment
+static int lightcut_gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_out_dev, float *seg_stats_dev) {
+    if (!ctx->lc) return fail(ctx, VRLB_ERR_STATE, "use_light_cut: no light tree resident (vrlb_lightcut_build after the VRL set is final)");
+    if (ctx->any_grid) return fail(ctx, VRLB_ERR_UNSUPPORTED, "use_light_cut with a grid medium: the reference raises \"Heterogeneous Lightcut not implemented\" (vrl_lightcut.h:485)");
+    if (opt->use_nl_atomic_query && opt->use_non_linear_camera) return fail(ctx, VRLB_ERR_UNSUPPORTED, "use_light_cut with use_nl_atomic_query: multi-part queries through the cut are not built (queries are per part, vrl.cpp:619-628)");
+    if (!(opt->threshold_error >= 0.f)) return fail(ctx, VRLB_ERR_INVALID, "threshold_error %g", (double) opt->threshold_error);
+    if (lightcut_n_vrls(ctx->lc) != ctx->n_vrls) return fail(ctx, VRLB_ERR_STATE, "light tree is stale");
+    LightcutParams p{};
+    p.scene = ctx->scene; p.segs = ctx->segs.ptr; p.n_segs = ctx->n_segs;
+    p.nodes = lightcut_nodes(ctx->lc); p.leaf_order = lightcut_leaf_order(ctx->lc); p.jump = lightcut_jump(ctx->lc);
+    p.vrls = ctx->vrls.ptr; p.n_vrls = ctx->n_vrls; p.first_index = ctx->vrl_first; p.total = ctx->vrl_total;
+    p.root = lightcut_root(ctx->lc); p.scale = ctx->vrl_scale; p.err = opt->threshold_error; p.better_dist = opt->threshold_better_dist;
+    p.q = (uint32_t) opt->samples_per_query;
+    // a heap never holds more than the tree's inner nodes
+    const uint64_t want = opt->lightcut_heap > 0 ? (uint64_t) opt->lightcut_heap : 16384u;
+    p.cap = (uint32_t) std::max<uint64_t>(2, std::min<uint64_t>(want, ctx->n_vrls));
+    int n_sms = 148; cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    const uint32_t grid = lightcut_grid(p.n_segs, p.cap, n_sms, (size_t) 24 << 30);
+    const size_t entries = (size_t) grid * 128 * p.cap;
+    CU(ctx, ctx->lc_heap.reserve(entries)); CU(ctx, ctx->lc_slots.reserve(entries)); CU(ctx, ctx->lc_stats.reserve(8));
+    CU(ctx, cudaMemsetAsync(ctx->lc_stats.ptr, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    p.heap_key = ctx->lc_heap.ptr; p.slot_est = ctx->lc_slots.ptr; p.stats = ctx->lc_stats.ptr;
+    p.film_rgb = seg_out_dev ? nullptr : ctx->film_rgb.ptr; p.seg_out = seg_out_dev; p.seg_stats = seg_stats_dev;
+    const bool vis = opt->visibility != 0 && ctx->scene.n_tris > 0;
+    cudaEventRecord(ctx->ev[2], ctx->stream);
+    CU(ctx, launch_lightcut_gather(p, grid, opt->use_uniform_sampling != 0, vis, ctx->stream));
+    cudaEventRecord(ctx->ev[3], ctx->stream);
+    unsigned long long st[5] = { 0, 0, 0, 0, 0 };
+    CU(ctx, cudaMemcpyAsync(st, ctx->lc_stats.ptr, sizeof st, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->lc_last.queries = st[0] * p.q; ctx->lc_last.evaluations = st[1]; ctx->lc_last.refinements = st[2]; ctx->lc_last.overflows = st[3]; ctx->lc_last.max_heap = st[4];
+    const bool launched = p.n_segs && p.n_vrls;
+    ctx->timing.gather_launches = launched ? 1 : 0;
+    ctx->timing.total_launches += launched ? 1 : 0; ctx->launches += launched ? 1 : 0;
+    ctx->timing.n_evals = st[1] + st[0] * p.q;           // fresh evaluations + one root evaluation per query sample
+    ctx->timing.ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
+    return VRLB_OK;
+}
+
 static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_out_dev) {
     if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "no scene resident");
     if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no camera segments resident");
     if (opt->samples_per_query < 1) return fail(ctx, VRLB_ERR_INVALID, "samples_per_query must be >= 1");
     if (opt->math_mode < 0 || opt->math_mode > 2) return fail(ctx, VRLB_ERR_INVALID, "math_mode %d unknown (0 exact, 1 fast + conditioning guard, 2 fast unguarded)", opt->math_mode);
     if (ctx->cancel.exchange(0)) return fail(ctx, VRLB_ERR_CANCELLED, "cancelled");
+    if (opt->use_light_cut) return lightcut_gather_impl(ctx, opt, seg_out_dev, nullptr);
     GatherParams p{};
     p.scene = ctx->scene; p.segs = ctx->segs.ptr; p.n_segs = ctx->n_segs;
     p.vrls = ctx->vrls.ptr; p.n_vrls = ctx->n_vrls; p.first_index = ctx->vrl_first; p.total = ctx->vrl_total;
@@ -1070,6 +1118,51 @@ int vrlb_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *li_o
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) rc = fail(ctx, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
         else ctx->timing.ms_gather = elapsed(ctx->ev[2], ctx->ev[3]);
+    }
+    tmp.release();
+    return rc;
+}
+
+int vrlb_lightcut_build(vrlb_context *ctx, uint64_t base_seed, uint64_t seed_offset) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (ctx->lc) { lightcut_free(ctx->lc); ctx->lc = nullptr; }
+    if (ctx->n_vrls == 0) return fail(ctx, VRLB_ERR_STATE, "no VRL set resident");
+    cudaError_t e = lightcut_build(ctx->vrls.ptr, ctx->n_vrls, ctx->vrl_first, base_seed, seed_offset, ctx->stream, &ctx->lc, &ctx->launches);
+    if (e != cudaSuccess) return fail_cuda(ctx, "lightcut_build", e);
+    lightcut_build_stats(ctx->lc, &ctx->lc_last.n_nodes, &ctx->lc_last.build_searches, &ctx->lc_last.build_ms);
+    return VRLB_OK;
+}
+
+int vrlb_lightcut_download(vrlb_context *ctx, float *f13, int32_t *i6, uint64_t cap, uint64_t *n_out) {
+    if (!ctx || !n_out || (cap && (!f13 || !i6))) return VRLB_ERR_INVALID;
+    if (!ctx->lc) return fail(ctx, VRLB_ERR_STATE, "no light tree resident");
+    *n_out = lightcut_dump(ctx->lc, f13, i6, cap);
+    return VRLB_OK;
+}
+
+int vrlb_lightcut_get_stats(const vrlb_context *ctx, vrlb_lightcut_stats *out) {
+    if (!ctx || !out) return VRLB_ERR_INVALID;
+    *out = ctx->lc_last;
+    return VRLB_OK;
+}
+
+int vrlb_lightcut_gather_segments(vrlb_context *ctx, const vrlb_options *opt, float *li_out, float *stats4_out) {
+    if (!ctx || !opt || !li_out) return VRLB_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    if (!ctx->have_scene) return fail(ctx, VRLB_ERR_STATE, "no scene resident");
+    if (ctx->width == 0) return fail(ctx, VRLB_ERR_STATE, "no camera segments resident");
+    if (opt->samples_per_query < 1) return fail(ctx, VRLB_ERR_INVALID, "samples_per_query must be >= 1");
+    DevBuf<float> tmp;
+    CU(ctx, tmp.reserve(ctx->n_segs * 3 + 1)); CU(ctx, ctx->lc_seg_stats.reserve(ctx->n_segs * 4 + 1));
+    CU(ctx, cudaMemsetAsync(tmp.ptr, 0, (ctx->n_segs * 3 + 1) * sizeof(float), ctx->stream));
+    CU(ctx, cudaMemsetAsync(ctx->lc_seg_stats.ptr, 0, (ctx->n_segs * 4 + 1) * sizeof(float), ctx->stream));
+    int rc = lightcut_gather_impl(ctx, opt, tmp.ptr, ctx->lc_seg_stats.ptr);
+    if (rc == VRLB_OK) {
+        cudaError_t e = cudaMemcpyAsync(li_out, tmp.ptr, ctx->n_segs * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess && stats4_out) e = cudaMemcpyAsync(stats4_out, ctx->lc_seg_stats.ptr, ctx->n_segs * 4 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = fail(ctx, VRLB_ERR_CUDA, "%s", cudaGetErrorString(e));
     }
     tmp.release();
     return rc;

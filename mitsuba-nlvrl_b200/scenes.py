@@ -207,6 +207,7 @@ def default_options(**kw):
     o.samples_per_query, o.use_uniform_sampling, o.rr_vrl, o.scale_rr = 1, 0, 0, 0.5
     o.max_depth, o.use_non_linear_camera, o.use_nl_atomic_query = 512, 1, 0
     o.visibility, o.hide_emitters, o.math_mode = 1, 0, 1
+    o.use_light_cut, o.threshold_error, o.threshold_better_dist, o.lightcut_heap = 0, 0.02, 8, 0      # vrl.cpp:66-72
     for k, v in kw.items():
         if not hasattr(o, k):
             raise AttributeError(k)

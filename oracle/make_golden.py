@@ -45,6 +45,12 @@ def main():
         with open(os.path.join(GOLD, "ref_medium.json"), "w") as f:
             json.dump(data, f)
         print("wrote ref_medium.json:", len(data["cases"]), "cases, warnings", data["warnings"])
+    probe = os.path.join(HERE, "_ref", "refprobe_lc")
+    if os.path.exists(probe):
+        data = json.loads(subprocess.check_output([probe]))
+        with open(os.path.join(GOLD, "ref_lightcut.json"), "w") as f:
+            json.dump(data, f)
+        print("wrote ref_lightcut.json:", {k: (len(v) if hasattr(v, "__len__") else v) for k, v in data.items()})
 
 if __name__ == "__main__":
     sys.exit(main())

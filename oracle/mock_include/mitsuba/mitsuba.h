@@ -1,0 +1,1 @@
+/* stub: the mock Mitsuba of oracle/ref_mock.h stands in for <mitsuba/mitsuba.h> (oracle/Makefile, _ref/refprobe_lc) */

@@ -40,9 +40,10 @@ template <typename T> constexpr auto Infinity      = std::numeric_limits<scalar_
 template <typename T> constexpr auto Epsilon       = std::numeric_limits<scalar_t<T>>::epsilon() / 2;
 template <typename T> constexpr auto RayEpsilon    = Epsilon<T> * 1500;
 template <typename T> constexpr auto ShadowEpsilon = RayEpsilon<T> * 10;
+template <typename T> constexpr auto Max           = std::numeric_limits<scalar_t<T>>::max();   /* math.h:30 */
 } // namespace math
 
-enum class LogLevel { Trace, Debug, Info, Warn, Error };
+enum LogLevel : int { Trace = 0, Debug = 100, Info = 200, Warn = 300, Error = 400 };   /* core/logger.h:11-17 (unscoped: the reference writes both Log(Error, ..) and Log(LogLevel::Error, ..)) */
 struct MockLog { static inline int warnings = 0; };
 template <typename... Args> inline void Log(LogLevel level, Args &&...) {
     if (level == LogLevel::Error) throw std::runtime_error("Log(Error)");
@@ -52,15 +53,22 @@ namespace string { template <typename T> const T &indent(const T &v) { return v;
 
 template <typename T> constexpr bool is_rgb_v = true;
 
+#ifdef REF_MOCK_VEC3
+using MockVec3 = REF_MOCK_VEC3;     /* a probe's own 3-vector (ref_probe_lc.cpp: the real bbox.h asks Point::Vector) */
+#else
 using MockVec3 = enoki::Array<float, 3>;
+#endif
 using MockVec2 = enoki::Array<float, 2>;
+#ifndef REF_MOCK_VEC3
 using Vector   = MockVec3; /* names the dead anisotropic branch of samplingVRL uses unqualified */
+#endif
 
 struct MockRay {
     MockVec3 o, d, d_rcp;
     float mint = math::RayEpsilon<float>;
     float maxt = math::Infinity<float>;
     float time = 0.f;
+    using Float = float; using Vector = MockVec3;      /* bbox.h:335-337 reads Ray::Float / Ray::Vector */
     MockRay() = default;
     MockRay(const MockVec3 &o_, const MockVec3 &d_, const float &t) : o(o_), d(d_), time(t) { d_rcp = rcp(d); }
     MockVec3 operator()(float t) const { return fmadd(d, MockVec3(t), o); }
@@ -125,12 +133,17 @@ struct MockSampler {
     uint64_t draws = 0;
     void seed(uint64_t base_seed, uint64_t seed_offset) { rng.seed(base_seed + seed_offset, PCG32_DEFAULT_STREAM); draws = 0; }
     float next_1d(bool = true) { ++draws; return rng.next_float32(); }
+    float next1D() { return next_1d(); }                  /* named by dead code only (vrl_lightcut.h:744) */
+    MockSampler *clone() { return new MockSampler(*this); }
 };
 struct MockPhaseContext { explicit MockPhaseContext(MockSampler *) {} };
 
+enum class PhaseFunctionFlags : uint32_t { None = 0x00, Isotropic = 0x01, Anisotropic = 0x02, Microflake = 0x04 };   /* render/phase.h:17-22 */
+inline bool has_flag(uint32_t flags, PhaseFunctionFlags f) { return (flags & (uint32_t) f) != 0; }                   /* :34-36 */
 struct MockPhase {
     bool hg = false;
     float g = 0.f;
+    uint32_t flags(bool = true) const { return (uint32_t) (hg ? PhaseFunctionFlags::Anisotropic : PhaseFunctionFlags::Isotropic); }   /* isotropic.cpp / hg.cpp constructors */
     float eval(const MockPhaseContext &, const MockMI &mi, const MockVec3 &wo) const {
         const float inv4pi = 0.07957747154594766788f;
         if (!hg) return inv4pi;
@@ -162,6 +175,8 @@ struct MockMedium {
 
 struct MockScene {
     std::vector<MockVec3> tri; /* 3 vertices per triangle */
+    struct BSphere { float radius = 1.f; };
+    BSphere getBSphere() const { return BSphere(); }      /* named by dead code only (vrl_lightcut.h:726) */
     MockBSDF bsdf;
     MockSI ray_intersect(const MockRay &ray, bool = true) const {
         MockSI si;

@@ -26,7 +26,6 @@
 #include "ref_mock.h"
 
 namespace mitsuba {
-constexpr LogLevel Info = LogLevel::Info, Warn = LogLevel::Warn, Error = LogLevel::Error, Debug = LogLevel::Debug;
 template <typename T> struct ref {
     T *p = nullptr;
     ref() = default; ref(T *q) : p(q) {}

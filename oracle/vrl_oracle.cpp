@@ -19,6 +19,7 @@
 #include <cstdio>
 #include <cstring>
 #include <limits>
+#include <queue>
 #include <thread>
 #include <vector>
 
@@ -1646,6 +1647,528 @@ uint64_t vrlo_render(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_opt
         evals += local;
     });
     return evals.load();
+}
+
+}  // extern "C"
+
+/* ========================================================================================== */
+/*  Part 7: the VRL light cut -- src/integrators/vrl/vrl_lightcut.h.            */
+/*  Pinned by tests/golden/ref_lightcut.json: that header compiled in place (ref_probe_lc.cpp) */
+/* ========================================================================================== */
+namespace {
+
+/* ---- BoundingBox::getMinDistanceSqr(ray), include/mitsuba/core/bbox.h:335-816 ---------------------------------------
+ * Squared distance between a box and a ray part.  The fork's routine is the published line / axis-aligned-box distance
+ * query of Eberly ("Distance from a line to a box"): the line is reflected into the octant where its direction is
+ * non-negative, the face (or edge, corner) of the box the line passes closest to is found from sign tests of cross
+ * products, and the line parameter of the closest point decides between the line result and the two end points.
+ * Quirks of the fork kept here because the cut's bound is computed from them:
+ *   - the slab test in front (bbox.h:302-325, :806) is for the whole LINE, both directions: a part whose supporting line
+ *     meets the box is at distance 0 however far the part itself is;
+ *   - the box handed to the line query is given by its FULL extents (bbox.h:349, `box.extents()`) where the algorithm
+ *     expects half extents: the line result is the distance to a box twice as large (the end-point results are not). */
+struct LineBox { float sqr = 0.f, t = 0.f; };
+
+/* the line leaves the reflected box through the face +e[i0] (or passes it beyond an edge / corner of that face) */
+void lb_face(int i0, int i1, int i2, const float *p, const float *d, const float *pme, const float *e, LineBox &r) {
+    float ppe[3] = { 0.f, 0.f, 0.f };
+    ppe[i1] = p[i1] + e[i1];
+    ppe[i2] = p[i2] + e[i2];
+    /* closest box point at offsets (pme[i0], x1, x2) from the line's reference point: bbox.h:460-466 and its siblings */
+    auto close = [&](float len_sqr, float x1, float x2) {
+        float delta = d[i0] * pme[i0] + d[i1] * x1 + d[i2] * x2;
+        float param = -delta / len_sqr;
+        r.sqr += pme[i0] * pme[i0] + x1 * x1 + x2 * x2 + delta * param;
+        r.t = param;
+    };
+    /* the edge of the face that runs along axis ia (ib = the face's other axis); with `only_if_ahead` the edge is taken
+     * only when the projection falls on its positive side (bbox.h:538, :573) */
+    auto edge = [&](int ia, int ib, bool only_if_ahead) -> bool {
+        float len_sqr = d[i0] * d[i0] + d[ib] * d[ib];
+        float tmp = len_sqr * ppe[ia] - d[ia] * (d[i0] * pme[i0] + d[ib] * ppe[ib]);
+        if (only_if_ahead && !(tmp >= 0.f)) return false;
+        float xa;
+        if (tmp <= 2.f * len_sqr * e[ia]) { float t = tmp / len_sqr; len_sqr += d[ia] * d[ia]; xa = ppe[ia] - t; }   /* interior of the edge */
+        else { len_sqr += d[ia] * d[ia]; xa = pme[ia]; }                                                              /* its far vertex       */
+        if (ia == i1) close(len_sqr, xa, ppe[i2]); else close(len_sqr, ppe[i1], xa);
+        return true;
+    };
+    const bool in1 = d[i0] * ppe[i1] >= d[i1] * pme[i0];
+    if (in1) {
+        if (d[i0] * ppe[i2] >= d[i2] * pme[i0]) { float inv = 1.f / d[i0]; r.t = -pme[i0] * inv; return; }   /* crosses the face: distance 0 */
+        edge(i1, i2, false);
+        return;
+    }
+    if (d[i0] * ppe[i2] >= d[i2] * pme[i0]) { edge(i2, i1, false); return; }
+    if (edge(i1, i2, true)) return;
+    if (edge(i2, i1, true)) return;
+    float len_sqr = d[i0] * d[i0] + d[i1] * d[i1];                                                            /* the corner */
+    len_sqr += d[i2] * d[i2];
+    close(len_sqr, ppe[i1], ppe[i2]);
+}
+
+/* no zero direction component: bbox.h:626-657 */
+void lb_general(const float *p, const float *d, const float *e, LineBox &r) {
+    const float pme[3] = { p[0] - e[0], p[1] - e[1], p[2] - e[2] };
+    if (d[1] * pme[0] >= d[0] * pme[1]) {
+        if (d[2] * pme[0] >= d[0] * pme[2]) lb_face(0, 1, 2, p, d, pme, e, r);
+        else lb_face(2, 0, 1, p, d, pme, e, r);
+    } else {
+        if (d[2] * pme[1] >= d[1] * pme[2]) lb_face(1, 2, 0, p, d, pme, e, r);
+        else lb_face(2, 0, 1, p, d, pme, e, r);
+    }
+}
+inline void lb_clamp_axis(int i, const float *p, const float *e, LineBox &r) {       /* the point-box term of one axis */
+    if (p[i] < -e[i]) { float delta = p[i] + e[i]; r.sqr += delta * delta; }
+    else if (p[i] > e[i]) { float delta = p[i] - e[i]; r.sqr += delta * delta; }
+}
+/* d[i2] == 0: a 2-D problem in the (i0, i1) plane plus the point-box term along i2, bbox.h:659-726 */
+void lb_one_zero(int i0, int i1, int i2, const float *p, const float *d, const float *e, LineBox &r) {
+    float pme0 = p[i0] - e[i0], pme1 = p[i1] - e[i1];
+    float prod0 = d[i1] * pme0, prod1 = d[i0] * pme1;
+    if (prod0 >= prod1) {
+        float ppe1 = p[i1] + e[i1];
+        float delta = prod0 - d[i0] * ppe1;
+        if (delta >= 0.f) {
+            float inv_l = 1.f / (d[i0] * d[i0] + d[i1] * d[i1]);
+            r.sqr += delta * delta * inv_l;
+            r.t = -(d[i0] * pme0 + d[i1] * ppe1) * inv_l;
+        } else { float inv = 1.f / d[i0]; r.t = -pme0 * inv; }
+    } else {
+        float ppe0 = p[i0] + e[i0];
+        float delta = prod1 - d[i1] * ppe0;
+        if (delta >= 0.f) {
+            float inv_l = 1.f / (d[i0] * d[i0] + d[i1] * d[i1]);
+            r.sqr += delta * delta * inv_l;
+            r.t = -(d[i0] * ppe0 + d[i1] * pme1) * inv_l;
+        } else { float inv = 1.f / d[i1]; r.t = -pme1 * inv; }
+    }
+    lb_clamp_axis(i2, p, e, r);
+}
+/* only d[i0] != 0: bbox.h:728-761 */
+void lb_two_zeros(int i0, int i1, int i2, const float *p, const float *d, const float *e, LineBox &r) {
+    r.t = (e[i0] - p[i0]) / d[i0];
+    lb_clamp_axis(i1, p, e, r);
+    lb_clamp_axis(i2, p, e, r);
+}
+
+float box_point_sqr(const V3 &lo, const V3 &hi, const V3 &p) {                        /* bbox.h:221-224 */
+    V3 a((p.x < lo.x) ? lo.x - p.x : 0.f, (p.y < lo.y) ? lo.y - p.y : 0.f, (p.z < lo.z) ? lo.z - p.z : 0.f);
+    V3 b((p.x > hi.x) ? p.x - hi.x : 0.f, (p.y > hi.y) ? p.y - hi.y : 0.f, (p.z > hi.z) ? p.z - hi.z : 0.f);
+    return squared_norm(a + b);
+}
+
+float box_ray_sqr(const V3 &lo, const V3 &hi, const Ray &ray) {
+    /* bbox.h:806-808 after :302-325 -- the slab test on the line */
+    {
+        const float o[3] = { ray.o.x, ray.o.y, ray.o.z }, d[3] = { ray.d.x, ray.d.y, ray.d.z };
+        const float l[3] = { lo.x, lo.y, lo.z }, h[3] = { hi.x, hi.y, hi.z };
+        float mint = -kInf, maxt = kInf;
+        bool first = true;
+        for (int i = 0; i < 3; ++i) {
+            float rcp = 1.0f / d[i];
+            float t1 = (l[i] - o[i]) * rcp, t2 = (h[i] - o[i]) * rcp;
+            float a = std::min(t1, t2), b = std::max(t1, t2);
+            if (first) { mint = a; maxt = b; first = false; } else { mint = std::max(mint, a); maxt = std::min(maxt, b); }
+        }
+        if (maxt >= mint) return 0.0f;
+    }
+    /* bbox.h:345-365 */
+    V3 c = (hi + lo) * 0.5f, ext = hi - lo;
+    V3 pt = ray.o - c;
+    float p[3] = { pt.x, pt.y, pt.z }, d[3] = { ray.d.x, ray.d.y, ray.d.z };
+    const float e[3] = { ext.x, ext.y, ext.z };
+    int positive = 0;
+    for (int i = 0; i < 3; ++i) {
+        if (d[i] < 0.f) { p[i] = -p[i]; d[i] = -d[i]; }
+        if (d[i] > 0.f) positive |= 1 << i;
+    }
+    LineBox r;
+    switch (positive) {                                                                 /* bbox.h:389-429 */
+        case 7: lb_general(p, d, e, r); break;
+        case 3: lb_one_zero(0, 1, 2, p, d, e, r); break;
+        case 5: lb_one_zero(0, 2, 1, p, d, e, r); break;
+        case 6: lb_one_zero(1, 2, 0, p, d, e, r); break;
+        case 1: lb_two_zeros(0, 1, 2, p, d, e, r); break;
+        case 2: lb_two_zeros(1, 0, 2, p, d, e, r); break;
+        case 4: lb_two_zeros(2, 0, 1, p, d, e, r); break;
+        default: lb_clamp_axis(0, p, e, r); lb_clamp_axis(1, p, e, r); lb_clamp_axis(2, p, e, r); break;
+    }
+    if (r.t < 0.f) return box_point_sqr(lo, hi, ray.o);
+    if (r.t > ray.maxt) return box_point_sqr(lo, hi, ray.o + ray.d * ray.maxt);        /* line(maxt - mint), mint = 0 */
+    return r.sqr;
+}
+
+/* VRLLightCut::sqrDistanceVRL(Ray3f, VRL), vrl_lightcut.h:772-838: the clamped closest points of two segments
+ * (s on the VRL, t on the camera part), with the reference's 1e-4 absolute thresholds */
+float seg_seg_sqr(const Ray &r, const Vrl &beam) {
+    V3 u = beam.direction * beam.length, v = r.d * r.maxt, w = beam.origin - r.o;
+    float a = dot(u, u), b = dot(u, v), c = dot(v, v), d = dot(u, w), e = dot(v, w);
+    float D = a * c - b * b;
+    float sN, sD = D, tN, tD = D;
+    if ((double) D < 0.0001) { sN = 0.f; sD = 1.f; tN = e; tD = c; }
+    else {
+        sN = b * e - c * d;
+        tN = a * e - b * d;
+        if (sN < 0.f) { sN = 0.f; tN = e; tD = c; }
+        else if (sN > sD) { sN = sD; tN = e + b; tD = c; }
+    }
+    if (tN < 0.f) {
+        tN = 0.f;
+        if (-d < 0.f) sN = 0.f;
+        else if (-d > a) sN = sD;
+        else { sN = -d; sD = a; }
+    } else if (tN > tD) {
+        tN = tD;
+        if ((-d + b) < 0.f) sN = 0.f;
+        else if ((-d + b) > a) sN = sD;
+        else { sN = -d + b; sD = a; }
+    }
+    float sc = ((double) std::fabs(sN) < 0.0001) ? 0.f : sN / sD;
+    float tc = ((double) std::fabs(tN) < 0.0001) ? 0.f : tN / tD;
+    V3 dP = w + (u * sc) - (v * tc);
+    return squared_norm(dP);
+}
+
+/* ---- the light tree ------------------------------------------------------------------------------------------------ */
+struct LcNode {
+    int parent = -1, child[2] = { -1, -1 };
+    bool leaf = true;
+    V3 lo, hi;                       /* aabb of every VRL of the cluster */
+    Vrl rep;                         /* representative, flux = the cluster's */
+    int rep_leaf = -1;               /* index of the VRL the representative's geometry comes from */
+    V3 add_flux = V3(0.f);
+    int same = -1;                   /* the child that shares the representative */
+    float max_len = 0.f;
+    std::vector<int> leaves;         /* Node::nodes: n1's then n2's */
+};
+inline V3 vmin(V3 a, V3 b) { return V3(std::min(a.x, b.x), std::min(a.y, b.y), std::min(a.z, b.z)); }
+inline V3 vmax(V3 a, V3 b) { return V3(std::max(a.x, b.x), std::max(a.y, b.y), std::max(a.z, b.z)); }
+inline float hmax3(V3 a) { return std::max(std::max(a.x, a.y), a.z); }
+
+/* Node(const VRL &), vrl_lightcut.h:56-63 */
+LcNode lc_leaf(const Vrl &v, int index) {
+    LcNode n;
+    V3 end = v.origin + v.direction * v.length;
+    n.lo = vmin(v.origin, end); n.hi = vmax(v.origin, end);
+    n.rep = v; n.rep_leaf = index; n.max_len = v.length;
+    n.leaves.push_back(index);
+    return n;
+}
+/* Node::dist, vrl_lightcut.h:101-109 */
+inline float lc_dist(const LcNode &n1, const LcNode &n2) {
+    float total = hmax3(n1.rep.flux + n2.rep.flux);
+    V3 ext = vmax(n1.hi, n2.hi) - vmin(n1.lo, n2.lo);
+    return squared_norm(ext) * total;
+}
+/* Node(Node *n1, Node *n2, Float v, bool), vrl_lightcut.h:111-151 (children referenced by index) */
+LcNode lc_merge(const LcNode &n1, int i1, const LcNode &n2, int i2, float v) {
+    LcNode m;
+    m.lo = vmin(n1.lo, n2.lo); m.hi = vmax(n1.hi, n2.hi);
+    m.leaf = false;
+    m.max_len = std::max(n1.max_len, n2.max_len);
+    m.child[0] = i1; m.child[1] = i2;
+    m.leaves = n1.leaves;
+    m.leaves.insert(m.leaves.end(), n2.leaves.begin(), n2.leaves.end());
+    float leftWM = hmax3(n1.rep.flux) * n1.rep.length, rightWM = hmax3(n2.rep.flux) * n2.rep.length;
+    float ratio = leftWM / (leftWM + rightWM);
+    const int index = v < ratio ? 0 : 1;
+    const LcNode &keep = index == 0 ? n1 : n2, &other = index == 0 ? n2 : n1;
+    m.rep = keep.rep; m.rep_leaf = keep.rep_leaf;
+    ratio = other.rep.length / keep.rep.length;
+    m.add_flux = other.rep.flux * ratio;
+    m.rep.flux = m.rep.flux + m.add_flux;
+    m.same = index;
+    return m;
+}
+
+}  // namespace
+
+struct vrlo_lightcut {
+    std::vector<LcNode> nodes;       /* leaves 0..n-1 in VRL order, then the merges in creation order */
+    int root = -1;
+    uint64_t n_vrls = 0, build_draws = 0;
+    std::vector<int> preorder;       /* node ids in preorder (what the reference probe prints) */
+};
+
+namespace {
+
+/* buildLightTree, vrl_lightcut.h:515-627: greedy bottom-up clustering.  Each live cluster keeps one queue entry
+ * (itself, its cheapest partner at the time the entry was made); the cheapest entry is popped; it merges when both
+ * ends are still live, else the live end(s) search again.  One sampler draw per merge picks the representative. */
+void lc_build(vrlo_lightcut &lc, const vrlb_vrlset_desc &set, Sampler &sampler, int n_threads) {
+    const size_t n = (size_t) set.n;
+    lc.n_vrls = n;
+    lc.nodes.reserve(2 * n);
+    for (size_t j = 0; j < n; ++j) lc.nodes.push_back(lc_leaf(load_vrl(set, j), (int) j));
+    if (n == 0) return;
+    std::vector<int> slot(n);
+    for (size_t j = 0; j < n; ++j) slot[j] = (int) j;
+    struct QE { size_t id1; int n1; size_t id2; int n2; float distance; bool operator>(const QE &o) const { return distance > o.distance; } };
+    std::priority_queue<QE, std::vector<QE>, std::greater<QE>> pairs;
+    auto min_pair = [&](int node, size_t i) -> std::pair<size_t, float> {
+        size_t o = 0; float best = std::numeric_limits<float>::max();
+        for (size_t j = 0; j < n; ++j) {
+            if (i == j || slot[j] < 0) continue;
+            float d = lc_dist(lc.nodes[(size_t) node], lc.nodes[(size_t) slot[j]]);
+            if (best > d) { o = j; best = d; }
+        }
+        return { o, best };
+    };
+    {
+        std::vector<std::pair<size_t, float>> first(n);
+        parallel_for(n, n_threads, [&](uint64_t i) { first[i] = min_pair(slot[i], (size_t) i); });
+        for (size_t i = 0; i < n; ++i) pairs.push(QE{ i, slot[i], first[i].first, slot[first[i].first], first[i].second });
+    }
+    std::vector<char> has_parent(2 * n, 0);
+    size_t live = n;
+    while (live != 1) {
+        QE p = pairs.top(); pairs.pop();
+        const bool free1 = !has_parent[(size_t) p.n1], free2 = p.n2 >= 0 && !has_parent[(size_t) p.n2];
+        if (free1 && free2) {
+            float v = sampler.next_1d(); ++lc.build_draws;
+            const int id = (int) lc.nodes.size();
+            lc.nodes.push_back(lc_merge(lc.nodes[(size_t) p.n1], p.n1, lc.nodes[(size_t) p.n2], p.n2, v));
+            lc.nodes[(size_t) p.n1].parent = id; lc.nodes[(size_t) p.n2].parent = id;
+            has_parent[(size_t) p.n1] = has_parent[(size_t) p.n2] = 1;
+            slot[p.id1] = id; slot[p.id2] = -1;
+            auto b = min_pair(id, p.id1);
+            pairs.push(QE{ p.id1, id, b.first, slot[b.first], b.second });
+            --live;
+        } else {
+            if (free1) { auto b = min_pair(p.n1, p.id1); pairs.push(QE{ p.id1, p.n1, b.first, slot[b.first], b.second }); }
+            if (free2) { auto b = min_pair(p.n2, p.id2); pairs.push(QE{ p.id2, p.n2, b.first, slot[b.first], b.second }); }
+        }
+    }
+    for (size_t i = 0; i < n; ++i) if (slot[i] >= 0) lc.root = slot[i];
+    /* preorder numbering */
+    std::vector<int> stack{ lc.root };
+    while (!stack.empty()) {
+        int id = stack.back(); stack.pop_back();
+        lc.preorder.push_back(id);
+        const LcNode &nd = lc.nodes[(size_t) id];
+        if (!nd.leaf) { stack.push_back(nd.child[1]); stack.push_back(nd.child[0]); }
+    }
+}
+
+/* getClusterUpperBound, vrl_lightcut.h:429-512 */
+float lc_bound(const vrlo_scene &s, const vrlo_lightcut &lc, const LcNode &cluster, const Ray *parts, int n_parts, float maxt_total, int better_dist, bool *unsupported) {
+    const vrlb_medium &m = s.media[(size_t) cluster.rep.medium];
+    float min_length;
+    if ((int) cluster.leaves.size() > better_dist) {
+        float best = std::numeric_limits<float>::max();
+        for (int j = 0; j < n_parts; ++j) best = std::min(best, box_ray_sqr(cluster.lo, cluster.hi, parts[j]));
+        min_length = safe_sqrt(best);
+    } else {
+        float best = std::numeric_limits<float>::max();
+        for (int leaf : cluster.leaves) {
+            float per = std::numeric_limits<float>::max();
+            for (int j = 0; j < n_parts; ++j) per = std::min(per, seg_seg_sqr(parts[j], lc.nodes[(size_t) leaf].rep));
+            best = std::min(best, per);
+        }
+        min_length = safe_sqrt(best);
+    }
+    if ((double) min_length < 0.0001) return std::numeric_limits<float>::max();
+    if (!is_homogeneous(m)) { if (unsupported) *unsupported = true; return std::numeric_limits<float>::max(); }   /* Log(Error, ...), :485 */
+    float tr = homo_transmittance(m, 0.f, min_length);
+    V3 ss = sigma_s_const(m);
+    V3 material = V3(1.f) * ss;
+    material = material * ss;
+    const double k = (m.phase == VRLB_PHASE_ISOTROPIC ? 1.0 : 2.0) / (16 * M_PI * M_PI);
+    material = V3((float) ((double) material.x * k), (float) ((double) material.y * k), (float) ((double) material.z * k));
+    float invRayPDF = cluster.max_len;
+    float invVRLPDF = (float) (2.0 * std::atan((double) maxt_total * 0.5 / (double) min_length) / (double) min_length);
+    float invPdf = invRayPDF * invVRLPDF;
+    V3 tmp = cluster.rep.flux * invPdf * material * V3(tr);
+    return hmax3(tmp);
+}
+
+/* getContrib on an NLRay (vrl_struct.h:584-662 with samplingVRL :247-360): importance sampling reads the first part
+ * only; uniform sampling walks the parts (NLRay::at) */
+V3 lc_contrib(const vrlo_scene &s, bool trace, const Vrl &vrl, const Ray *parts, int n_parts, float maxt_total, bool uniform, Pcg32 *r, Pcg32 *sub) {
+    if (n_parts == 1 || !uniform) {
+        DrawSrc draws{ r, { 0.f, 0.f }, 0 };
+        return get_contrib(s, trace, vrl, parts[0], uniform, draws, sub);
+    }
+    float u1 = r->next_f32(), u2 = r->next_f32();
+    float tCam = u1 * maxt_total, tVRL = u2 * vrl.length;
+    int hit = n_parts - 1; V3 pCam; bool found = false;
+    float dist = tCam;
+    if (dist < maxt_total)
+        for (int k = 0; k < n_parts; ++k) {
+            if (dist < parts[k].maxt) { hit = k; pCam = parts[k].o + parts[k].d * dist; found = true; break; }
+            dist -= parts[k].maxt;
+        }
+    if (!found) { hit = n_parts - 1; pCam = parts[hit].o + parts[hit].d * tCam; }
+    SamplingInfo si{ pCam, tCam, vrl.origin + vrl.direction * tVRL, tVRL, vrl.length * maxt_total, true };
+    Ray wi_ray{ parts[0].o, parts[hit].d, parts[0].maxt };
+    return get_contrib_sampled(s, trace, vrl, wi_ray, si, sub);
+}
+
+struct LcStats { uint64_t evals = 0, pops = 0, max_heap = 0; float min_margin = std::numeric_limits<float>::max(); bool unsupported = false; };
+
+/* VRLLightCut::query, vrl_lightcut.h:243-393 (stochastic = false), times m_scale and over samples_per_query as
+ * VRLMap::query wraps it (vrl_map.h:143, 198-205).  Addressed draws: the fresh evaluation of a cluster whose
+ * representative is VRL j, in sample i, reads the stream at ((i * total + j) * 2) -- every VRL is the representative of
+ * exactly one chain of clusters and only the top of the chain is evaluated, so no position is read twice. */
+V3 lc_query(const vrlo_scene &s, const vrlo_lightcut &lc, float scale, const Ray *parts, int n_parts, const vrlb_options &opt,
+            int rng_mode, Pcg32 &rng, LcStats &st) {
+    V3 total(0.f);
+    if (lc.root < 0) return total;
+    const bool uniform = opt.use_uniform_sampling != 0, trace = opt.visibility != 0;
+    const uint32_t q = (uint32_t) std::max(opt.samples_per_query, 1);
+    float maxt_total = 0.f;
+    for (int k = 0; k < n_parts; ++k) maxt_total += parts[k].maxt;
+    const Pcg32 base = rng;
+    struct Cut { int node; float bound; V3 est; };
+    auto cmp = [](const Cut &a, const Cut &b) { return a.bound < b.bound; };
+    for (uint32_t i = 0; i < q; ++i) {
+        auto eval = [&](const LcNode &nd) -> V3 {
+            if (rng_mode == VRLO_RNG_ADDRESSED) {
+                Pcg32 r = base;
+                r.advance((int64_t) (((uint64_t) i * lc.n_vrls + (uint64_t) nd.rep_leaf) * 2u));
+                Pcg32 sub; sub.seed(r.state, PCG32_DEFAULT_STREAM + 1);
+                return lc_contrib(s, trace, nd.rep, parts, n_parts, maxt_total, uniform, &r, &sub);
+            }
+            return lc_contrib(s, trace, nd.rep, parts, n_parts, maxt_total, uniform, &rng, &rng);
+        };
+        auto bound = [&](const LcNode &nd) { return lc_bound(s, lc, nd, parts, n_parts, maxt_total, opt.threshold_better_dist, &st.unsupported); };
+        std::priority_queue<Cut, std::vector<Cut>, decltype(cmp)> heap(cmp);
+        const LcNode &root = lc.nodes[(size_t) lc.root];
+        {
+            float b = bound(root);
+            V3 e = eval(root);
+            heap.push(Cut{ lc.root, b, e });
+        }
+        V3 Li = heap.top().est;
+        while (!heap.empty()) {
+            Cut cur = heap.top(); heap.pop();
+            const float thr = hmax3(Li * opt.threshold_error);
+            {
+                float margin = std::fabs(cur.bound - thr) / std::max(std::fabs(thr), 1e-30f);
+                st.min_margin = std::min(st.min_margin, margin);
+            }
+            if (cur.bound < thr) break;
+            ++st.pops;
+            Li = Li - cur.est;
+            const LcNode &cl = lc.nodes[(size_t) cur.node];
+            for (int c = 0; c < 2; ++c) {
+                if (cl.child[c] < 0) continue;
+                const LcNode &ch = lc.nodes[(size_t) cl.child[c]];
+                V3 est = ch.rep.flux;
+                if (cl.same == c) {
+                    V3 div = cl.rep.flux;
+                    if (div.x > 0.0f) est.x /= div.x;
+                    if (div.y > 0.0f) est.y /= div.y;
+                    if (div.z > 0.0f) est.z /= div.z;
+                    est = est * cur.est;
+                    if (std::isnan(est.x) || std::isnan(est.y) || std::isnan(est.z)) est = V3(0.f);
+                } else {
+                    ++st.evals;
+                    est = eval(ch);
+                }
+                Li = Li + est;
+                if (!ch.leaf) heap.push(Cut{ cl.child[c], bound(ch), est });
+            }
+            st.max_heap = std::max<uint64_t>(st.max_heap, heap.size());
+        }
+        Li = V3(std::max(Li.x, 0.f), std::max(Li.y, 0.f), std::max(Li.z, 0.f));
+        total = total + Li * scale;
+    }
+    if (rng_mode == VRLO_RNG_ADDRESSED) { rng = base; rng.advance((int64_t) ((uint64_t) q * lc.n_vrls * 2u)); }
+    if (q > 1) total = total / (float) q;
+    return total;
+}
+
+}  // namespace
+
+extern "C" {
+
+/* sampler.seed(0, seed_offset) supplies the representative draws, one per merge */
+vrlo_lightcut *vrlo_lightcut_build(const vrlb_vrlset_desc *set, uint64_t base_seed, uint64_t seed_offset, int n_threads) {
+    vrlo_lightcut *lc = new vrlo_lightcut();
+    Sampler smp; smp.seed(base_seed, seed_offset);
+    lc_build(*lc, *set, smp, n_threads);
+    return lc;
+}
+void vrlo_lightcut_destroy(vrlo_lightcut *lc) { delete lc; }
+uint64_t vrlo_lightcut_n_nodes(const vrlo_lightcut *lc) { return lc->preorder.size(); }
+uint64_t vrlo_lightcut_build_draws(const vrlo_lightcut *lc) { return lc->build_draws; }
+/* preorder dump.  f13: [n][13] = flux(3) add_flux(3) lo(3) hi(3) max_len; i6: [n][6] = leaf, representative VRL, the child sharing it, n_leaves, creation id, parent's creation id */
+void vrlo_lightcut_nodes(const vrlo_lightcut *lc, float *f13, int32_t *i6) {
+    for (size_t k = 0; k < lc->preorder.size(); ++k) {
+        const LcNode &n = lc->nodes[(size_t) lc->preorder[k]];
+        float *f = f13 + 13 * k; int32_t *i = i6 + 6 * k;
+        f[0] = n.rep.flux.x; f[1] = n.rep.flux.y; f[2] = n.rep.flux.z;
+        f[3] = n.add_flux.x; f[4] = n.add_flux.y; f[5] = n.add_flux.z;
+        f[6] = n.lo.x; f[7] = n.lo.y; f[8] = n.lo.z; f[9] = n.hi.x; f[10] = n.hi.y; f[11] = n.hi.z; f[12] = n.max_len;
+        i[0] = n.leaf ? 1 : 0; i[1] = n.rep_leaf; i[2] = n.same; i[3] = (int32_t) n.leaves.size(); i[4] = lc->preorder[k]; i[5] = n.parent;
+    }
+}
+float vrlo_lc_node_dist(const float a10[10], const float b10[10]) {
+    vrlb_vrlset_desc sa{ a10, nullptr, 1, 0, 1, 1.f, 0.f }, sb{ b10, nullptr, 1, 0, 1, 1.f, 0.f };
+    return lc_dist(lc_leaf(load_vrl(sa, 0), 0), lc_leaf(load_vrl(sb, 0), 1));
+}
+/* out14 = pick, flux(3), add_flux(3), lo(3), hi(3), max_len */
+void vrlo_lc_merge(const float a10[10], const float b10[10], float v, float *out14) {
+    vrlb_vrlset_desc sa{ a10, nullptr, 1, 0, 1, 1.f, 0.f }, sb{ b10, nullptr, 1, 0, 1, 1.f, 0.f };
+    LcNode m = lc_merge(lc_leaf(load_vrl(sa, 0), 0), 0, lc_leaf(load_vrl(sb, 0), 1), 1, v);
+    out14[0] = (float) m.same; out14[1] = m.rep.flux.x; out14[2] = m.rep.flux.y; out14[3] = m.rep.flux.z;
+    out14[4] = m.add_flux.x; out14[5] = m.add_flux.y; out14[6] = m.add_flux.z;
+    out14[7] = m.lo.x; out14[8] = m.lo.y; out14[9] = m.lo.z; out14[10] = m.hi.x; out14[11] = m.hi.y; out14[12] = m.hi.z; out14[13] = m.max_len;
+}
+float vrlo_lc_box_dist(const float lo[3], const float hi[3], const float o[3], const float d[3], float maxt) {
+    return box_ray_sqr(V3(lo), V3(hi), Ray{ V3(o), V3(d), maxt });
+}
+float vrlo_lc_seg_dist(const float vrl10[10], const float o[3], const float d[3], float maxt) {
+    vrlb_vrlset_desc sa{ vrl10, nullptr, 1, 0, 1, 1.f, 0.f };
+    return seg_seg_sqr(Ray{ V3(o), V3(d), maxt }, load_vrl(sa, 0));
+}
+/* parts7: n_parts x (o(3), d(3), maxt); node = preorder index */
+float vrlo_lightcut_bound(const vrlo_scene *s, const vrlo_lightcut *lc, int32_t node, const float *parts7, int n_parts, int better_dist) {
+    std::vector<Ray> parts((size_t) n_parts);
+    float maxt = 0.f;
+    for (int k = 0; k < n_parts; ++k) { parts[(size_t) k] = Ray{ V3(parts7 + 7 * k), V3(parts7 + 7 * k + 3), parts7[7 * k + 6] }; maxt += parts7[7 * k + 6]; }
+    return lc_bound(*s, *lc, lc->nodes[(size_t) lc->preorder[(size_t) node]], parts.data(), n_parts, maxt, better_dist, nullptr);
+}
+/* one query on the stream sampler.seed(0, seed_offset) (sequential mode) / addressed from that position.
+ * stats5 = evals (the reference's nb_evaluation), draws consumed (sequential mode), pops, largest heap, min decision margin */
+void vrlo_lightcut_query(const vrlo_scene *s, const vrlo_lightcut *lc, float scale, const float *parts7, int n_parts, const vrlb_options *opt,
+                         int rng_mode, uint64_t base_seed, uint64_t seed_offset, float out_rgb[3], double *stats5) {
+    std::vector<Ray> parts((size_t) n_parts);
+    for (int k = 0; k < n_parts; ++k) parts[(size_t) k] = Ray{ V3(parts7 + 7 * k), V3(parts7 + 7 * k + 3), parts7[7 * k + 6] };
+    Sampler smp; smp.seed(base_seed, seed_offset);
+    Pcg32 start = smp.rng;
+    LcStats st;
+    V3 li = lc_query(*s, *lc, scale, parts.data(), n_parts, *opt, rng_mode, smp.rng, st);
+    out_rgb[0] = li.x; out_rgb[1] = li.y; out_rgb[2] = li.z;
+    uint64_t draws = 0;
+    if (rng_mode == VRLO_RNG_SEQUENTIAL) { while (start.state != smp.rng.state && draws < (1u << 24)) { start.next_u32(); ++draws; } }
+    if (stats5) { stats5[0] = (double) st.evals; stats5[1] = (double) draws; stats5[2] = (double) st.pops; stats5[3] = (double) st.max_heap; stats5[4] = (double) st.min_margin; }
+}
+/* the gather through the cut over explicit segments (each record one query, or a group of n_parts records when
+ * use_nl_atomic_query): out_rgb32 per segment (groups: on the first record), stats4 per segment = evals, pops, largest
+ * heap, min decision margin.  Returns the fresh evaluations, or UINT64_MAX when a cluster sits in a non-homogeneous medium. */
+uint64_t vrlo_lightcut_gather_segments(const vrlo_scene *s, const vrlo_lightcut *lc, float scale, const vrlb_segment *segs, uint64_t n_segs,
+                                       const vrlb_options *opt, int rng_mode, int n_threads, float *out_rgb32, float *stats4) {
+    std::atomic<uint64_t> evals{ 0 };
+    std::atomic<int> bad{ 0 };
+    parallel_for(n_segs, n_threads, [&](uint64_t i) {
+        const vrlb_segment &sg = segs[i];
+        const uint32_t n_all = sg.sample >> 16;
+        if (n_all > 0 && (sg.part & 0xffffu) != 0) { if (out_rgb32) out_rgb32[i * 3] = out_rgb32[i * 3 + 1] = out_rgb32[i * 3 + 2] = 0.f; return; }
+        const uint32_t n_parts = n_all > 0 ? n_all : 1;
+        std::vector<Ray> parts(n_parts);
+        for (uint32_t k = 0; k < n_parts; ++k) parts[k] = Ray{ V3(segs[i + k].o), V3(segs[i + k].d), segs[i + k].maxt };
+        Pcg32 rng{ sg.rng_state, (PCG32_DEFAULT_STREAM << 1) | 1u };
+        LcStats st;
+        V3 li = lc_query(*s, *lc, scale, parts.data(), (int) n_parts, *opt, rng_mode, rng, st);
+        if (st.unsupported) bad = 1;
+        evals += st.evals;
+        if (out_rgb32) { out_rgb32[i * 3 + 0] = li.x; out_rgb32[i * 3 + 1] = li.y; out_rgb32[i * 3 + 2] = li.z; }
+        if (stats4) { stats4[i * 4 + 0] = (float) st.evals; stats4[i * 4 + 1] = (float) st.pops; stats4[i * 4 + 2] = (float) st.max_heap; stats4[i * 4 + 3] = st.min_margin; }
+    });
+    return bad.load() ? UINT64_MAX : evals.load();
 }
 
 }  // extern "C"

@@ -116,6 +116,23 @@ uint64_t vrlo_render(const vrlo_scene *s, const vrlb_camera *cam, const vrlb_opt
                      const vrlb_vrlset_desc *vrls, int rng_mode, int n_threads,
                      const int32_t *crop, float *xyzaw, float *rgb);
 
+/* -- the VRL light cut (vrl_lightcut.h), pinned by tests/golden/ref_lightcut.json -- */
+typedef struct vrlo_lightcut vrlo_lightcut;
+vrlo_lightcut *vrlo_lightcut_build(const vrlb_vrlset_desc *set, uint64_t base_seed, uint64_t seed_offset, int n_threads);
+void     vrlo_lightcut_destroy(vrlo_lightcut *lc);
+uint64_t vrlo_lightcut_n_nodes(const vrlo_lightcut *lc);
+uint64_t vrlo_lightcut_build_draws(const vrlo_lightcut *lc);
+void     vrlo_lightcut_nodes(const vrlo_lightcut *lc, float *f13, int32_t *i6);
+float    vrlo_lc_node_dist(const float a10[10], const float b10[10]);
+void     vrlo_lc_merge(const float a10[10], const float b10[10], float v, float *out14);
+float    vrlo_lc_box_dist(const float lo[3], const float hi[3], const float o[3], const float d[3], float maxt);
+float    vrlo_lc_seg_dist(const float vrl10[10], const float o[3], const float d[3], float maxt);
+float    vrlo_lightcut_bound(const vrlo_scene *s, const vrlo_lightcut *lc, int32_t node, const float *parts7, int n_parts, int better_dist);
+void     vrlo_lightcut_query(const vrlo_scene *s, const vrlo_lightcut *lc, float scale, const float *parts7, int n_parts, const vrlb_options *opt,
+                             int rng_mode, uint64_t base_seed, uint64_t seed_offset, float out_rgb[3], double *stats5);
+uint64_t vrlo_lightcut_gather_segments(const vrlo_scene *s, const vrlo_lightcut *lc, float scale, const vrlb_segment *segs, uint64_t n_segs,
+                                       const vrlb_options *opt, int rng_mode, int n_threads, float *out_rgb32, float *stats4);
+
 #ifdef __cplusplus
 }
 #endif

@@ -79,6 +79,28 @@ def lib():
         L.vrlo_render.argtypes = [C.c_void_p, C.POINTER(abi.Camera), C.POINTER(abi.Options), C.POINTER(abi.VrlSetDesc),
                                   C.c_int, C.c_int, C.POINTER(C.c_int32), f3, f3]
         L.vrlo_render.restype = C.c_uint64
+        L.vrlo_lightcut_build.argtypes = [C.POINTER(abi.VrlSetDesc), C.c_uint64, C.c_uint64, C.c_int]
+        L.vrlo_lightcut_build.restype = C.c_void_p
+        L.vrlo_lightcut_destroy.argtypes = [C.c_void_p]
+        L.vrlo_lightcut_n_nodes.argtypes = [C.c_void_p]
+        L.vrlo_lightcut_n_nodes.restype = C.c_uint64
+        L.vrlo_lightcut_build_draws.argtypes = [C.c_void_p]
+        L.vrlo_lightcut_build_draws.restype = C.c_uint64
+        L.vrlo_lightcut_nodes.argtypes = [C.c_void_p, f3, C.POINTER(C.c_int32)]
+        L.vrlo_lc_node_dist.argtypes = [f3, f3]
+        L.vrlo_lc_node_dist.restype = C.c_float
+        L.vrlo_lc_merge.argtypes = [f3, f3, C.c_float, f3]
+        L.vrlo_lc_box_dist.argtypes = [f3, f3, f3, f3, C.c_float]
+        L.vrlo_lc_box_dist.restype = C.c_float
+        L.vrlo_lc_seg_dist.argtypes = [f3, f3, f3, C.c_float]
+        L.vrlo_lc_seg_dist.restype = C.c_float
+        L.vrlo_lightcut_bound.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, f3, C.c_int, C.c_int]
+        L.vrlo_lightcut_bound.restype = C.c_float
+        L.vrlo_lightcut_query.argtypes = [C.c_void_p, C.c_void_p, C.c_float, f3, C.c_int, C.POINTER(abi.Options), C.c_int,
+                                          C.c_uint64, C.c_uint64, f3, C.POINTER(C.c_double)]
+        L.vrlo_lightcut_gather_segments.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_uint64, C.POINTER(abi.Options),
+                                                    C.c_int, C.c_int, f3, f3]
+        L.vrlo_lightcut_gather_segments.restype = C.c_uint64
         _lib = L
     return _lib
 
@@ -223,3 +245,72 @@ def estimate_radiance_volume(medium, photon_desc, gp, wo, radius):
     out = np.zeros(3, np.float32)
     lib().vrlo_estimate_radiance_volume(C.byref(medium), C.byref(photon_desc), fp(gp), fp(wo), radius, fp(out))
     return out
+
+
+class OracleLightcut:
+    """The reference's light tree over a VRL set (vrl_lightcut.h:196-212, 515-627) and queries through its cut."""
+
+    def __init__(self, vrl_desc, seed_offset=0, base_seed=0, n_threads=None):
+        self._desc = vrl_desc
+        self.scale = vrl_desc.scale
+        self.h = lib().vrlo_lightcut_build(C.byref(vrl_desc), base_seed, seed_offset, n_threads or os.cpu_count())
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().vrlo_lightcut_destroy(self.h)
+            self.h = None
+
+    @property
+    def build_draws(self):
+        return lib().vrlo_lightcut_build_draws(self.h)
+
+    def nodes(self):
+        """Preorder: (f [n,13] = flux, add_flux, lo, hi, max_len; i [n,6] = leaf, rep VRL, same child, n_leaves, id, parent id)."""
+        n = lib().vrlo_lightcut_n_nodes(self.h)
+        f, i = np.zeros((n, 13), np.float32), np.zeros((n, 6), np.int32)
+        lib().vrlo_lightcut_nodes(self.h, fp(f), i.ctypes.data_as(C.POINTER(C.c_int32)))
+        return f, i
+
+    def bound(self, osc, node, parts, better_dist=8):
+        parts = f32(parts).reshape(-1, 7)
+        return lib().vrlo_lightcut_bound(osc.h, self.h, node, fp(parts), len(parts), better_dist)
+
+    def query(self, osc, parts, opt, seed_offset, rng_mode=RNG_SEQUENTIAL, scale=1.0, base_seed=0):
+        parts = f32(parts).reshape(-1, 7)
+        out, st = np.zeros(3, np.float32), np.zeros(5, np.float64)
+        lib().vrlo_lightcut_query(osc.h, self.h, scale, fp(parts), len(parts), C.byref(opt), rng_mode, base_seed, seed_offset,
+                                  fp(out), st.ctypes.data_as(C.POINTER(C.c_double)))
+        return out, dict(evals=int(st[0]), draws=int(st[1]), pops=int(st[2]), max_heap=int(st[3]), min_margin=float(st[4]))
+
+    def gather(self, osc, segs, opt, rng_mode=RNG_ADDRESSED, n_threads=None):
+        """Per segment: Li (fp32, the reference's arithmetic) and stats [evals, pops, largest heap, min decision margin]."""
+        n = len(segs)
+        segs = np.ascontiguousarray(segs)
+        out, st = np.zeros((n, 3), np.float32), np.zeros((n, 4), np.float32)
+        ev = lib().vrlo_lightcut_gather_segments(osc.h, self.h, self.scale, segs.ctypes.data, n, C.byref(opt), rng_mode,
+                                                 n_threads or os.cpu_count(), fp(out), fp(st))
+        assert ev != 2 ** 64 - 1, "light cut over a non-homogeneous medium (the reference raises Log(Error), vrl_lightcut.h:485)"
+        return out, st, ev
+
+
+def lc_node_dist(a10, b10):
+    a10, b10 = f32(a10), f32(b10)
+    return lib().vrlo_lc_node_dist(fp(a10), fp(b10))
+
+
+def lc_merge(a10, b10, v):
+    a10, b10, out = f32(a10), f32(b10), np.zeros(14, np.float32)
+    lib().vrlo_lc_merge(fp(a10), fp(b10), v, fp(out))
+    return dict(pick=int(out[0]), flux=out[1:4], add_flux=out[4:7], lo=out[7:10], hi=out[10:13], max_len=out[13])
+
+
+def lc_box_dist(lo, hi, ray7):
+    lo, hi, r = f32(lo), f32(hi), f32(ray7)
+    o, d = f32(r[0:3]), f32(r[3:6])
+    return lib().vrlo_lc_box_dist(fp(lo), fp(hi), fp(o), fp(d), float(r[6]))
+
+
+def lc_seg_dist(vrl10, ray7):
+    v, r = f32(vrl10), f32(ray7)
+    o, d = f32(r[0:3]), f32(r[3:6])
+    return lib().vrlo_lc_seg_dist(fp(v), fp(o), fp(d), float(r[6]))

@@ -105,7 +105,11 @@ def test_config4_bench_frame_1080p_100k(ctx):
     ctx.upload_vrls(vd)
     assert ctx.build_segments(cam, opt) == 1920 * 1080
     segs = ctx.download_segments()
-    whole = ctx.gather_segments(opt).astype(np.float64)
+    whole32 = ctx.gather_segments(opt)
+    # run to run bit-exact: the stand-in for racecheck (closed on this pool, profiles/r02_sanitizer_note.txt) -- a race on the
+    # per-warp trace buffers, the TMA double buffer or the queue slots would show here
+    assert np.array_equal(whole32, ctx.gather_segments(opt))
+    whole = whole32.astype(np.float64)
     y, x = segs["pixel"] // 1920, segs["pixel"] % 1920
     idx = np.nonzero(((y == 540) | (y == 500)) & (x % 2 == 0))[0]    # every other pixel of two full rows: through the sphere's and the cuboid's silhouettes
     o32, o64, ev = oracle.OracleScene(sc).gather(vd, segs[idx], opt)
