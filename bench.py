@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--lightcut-1m", action="store_true", help="also time the light cut at 1e6 VRLs (minutes of tree build)")
     return ap.parse_args()
 
 
@@ -340,6 +341,26 @@ def run_ours(args):
                                     f"box-fog V4 graded IOR 1.0->0.95 (320 layers), curved camera paths, {args.width}x{args.height}, N_vrl={n_total}, BVH visibility",
                                     "gather_fast_vis_kernel"))
         note("V4 done")
+        # the bench frame through the VRL light cut (use_light_cut): the reference's tree built on the device, one
+        # cut per camera segment.  N = 1e6 (--lightcut-1m) builds for minutes and is measured once per round (profiles/).
+        if world == 1:
+            for n_lc in ([min(n_total, 100000)] + ([1000000] if args.lightcut_1m else [])):
+                soa_lc = soa if n_lc == n_total else scenes.synthetic_vrls(n_lc, seed=1)
+                ctx.set_scene(sc)
+                ctx.upload_vrls(scenes.vrlset_desc(soa_lc))
+                opt_lc = scenes.default_options(visibility=1, use_light_cut=1, threshold_error=0.02)
+                n_x = ctx.build_segments(cam, opt_lc)
+                ctx.lightcut_build(seed_offset=1)
+                ctx.clear_film(); ctx.gather(opt_lc); ctx.synchronize()
+                st, ms_x = ctx.lightcut_stats(), ctx.timing()["ms_gather"]
+                workloads.append({"workload": f"box-fog V2 {args.width}x{args.height}, N_vrl={n_lc}, use_light_cut threshold_error=0.02 threshold_better_dist=8",
+                                  "kernel": "lightcut_gather_kernel (exactly rounded getContrib; the reference's tree and refinement order)",
+                                  "n_segments": int(n_x), "tree_nodes": int(st.n_nodes), "build_ms": float(st.build_ms), "build_partner_searches": int(st.build_searches),
+                                  "ms_per_frame_gather": float(ms_x), "evaluations_per_query": st.evaluations / max(st.queries, 1),
+                                  "fraction_of_set_evaluated": st.evaluations / max(st.queries, 1) / n_lc, "largest_heap": int(st.max_heap),
+                                  "overflowed_queries": int(st.overflows), "cut_evals_per_s": (st.evaluations + st.queries) / (ms_x * 1e-3),
+                                  "full_gather_equivalent_evals_per_s": n_x * n_lc / (ms_x * 1e-3)})
+                note(f"light cut N={n_lc} done")
 
     # ---- N > 1: is the sharded, all-reduced film the single-GPU film?  (outside every timed region) ------------------
     multi_gpu_check = None

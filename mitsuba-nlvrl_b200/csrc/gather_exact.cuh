@@ -47,8 +47,9 @@ struct SegRegs { V3 o, d; float maxt; };
 //      GRID: the VRL's medium may be a grid medium; then `sub_seed` keys the eval's transmittance sub-stream and
 //      `st2` receives sigma_t(pCam) * sigma_t(pVRL) (the caller multiplies albedo^2; heterogeneous.cpp:43-51). ----
 //      `seg_out` (3 + 3 + 1 floats), when given, receives the connection segment pCam, direction, length and the
-//      shadow query is left to the caller (the fast kernel parks it in its warp queue). ----
-template <bool UNIFORM, bool VIS, bool GRID = false>
+//      shadow query is left to the caller (the fast kernel parks it in its warp queue).  PROXIED: the shadow query
+//      goes through the solids' conservative proxies first (any_hit_proxied: same answer, fewer BVH walks). ----
+template <bool UNIFORM, bool VIS, bool GRID = false, bool PROXIED = false>
 __device__ inline float eval_contrib(const DScene &scene, const SegRegs &ray, V3 vo, V3 vd, float vlen,
                                      float max_density, int phase, float g, float u1, float u2,
                                      const DMedium *gm = nullptr, uint64_t sub_seed = 0, float *st2 = nullptr, float *seg_out = nullptr,
@@ -123,7 +124,7 @@ __device__ inline float eval_contrib(const DScene &scene, const SegRegs &ray, V3
     float remaining = norm(dd);
     dd = normalize(dd);
     if (seg_out) { seg_out[0] = pCam.x; seg_out[1] = pCam.y; seg_out[2] = pCam.z; seg_out[3] = dd.x; seg_out[4] = dd.y; seg_out[5] = dd.z; seg_out[6] = remaining; }
-    if (VIS && remaining > 0 && any_hit(scene, pCam, dd, 0.f, remaining)) return 0.f;
+    if (VIS && remaining > 0 && (PROXIED ? any_hit_proxied(scene, pCam, dd, 0.f, remaining) : any_hit(scene, pCam, dd, 0.f, remaining))) return 0.f;
     if (GRID && gm->kind == VRLB_MEDIUM_GRID) {
         // get_scattering_coefficients at both points (vrl_struct.h:616, 624), then the three stochastic
         // transmittances in the reference's call order (:632, :641, :647) on the eval's sub-stream

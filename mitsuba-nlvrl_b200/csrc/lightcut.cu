@@ -18,8 +18,9 @@
 // estimate, so it is kept sequential per query and parallel across queries (32 neighbouring segments per warp walk
 // similar cuts).  Each step pops the cluster with the largest bound, evaluates the child that does not share the parent's
 // representative (getContrib in the reference's operation order, gather_exact.cuh), scales the parent's estimate for the
-// one that does, bounds both.  The heap lives in global memory, interleaved across threads (entry e of thread t at
-// e * T + t): keys are (bound bits << 32 | slot), payloads (estimate, node) sit in slots recycled through a free list.
+// one that does, bounds both.  The heap is 4-ary: its first three levels sit in shared memory, the rest in the thread's own
+// run of global memory where four siblings are one 32-byte sector; keys are (bound bits << 32 | slot), payloads (estimate,
+// node) sit in slots recycled through a free list.
 // PCG32 addressing: the evaluation of a cluster whose representative is VRL j, in query sample s, reads the two uniforms
 // at ((s * total + first_index + j) * 2) -- every VRL represents exactly one chain of clusters and only the top of a chain
 // is evaluated, so no position is read twice; the jump (multiplier, increment) per VRL is tabulated at build time.
@@ -189,7 +190,7 @@ struct HostPcg {             // the sampler handed to VRLMap::build (Independent
 struct LightcutTree {
     std::vector<HNode> nodes;        // leaves 0..n-1 in VRL order, then the merges in creation order; root = last
     int32_t root = -1;
-    DLcNode *d_nodes = nullptr; uint32_t *d_leaf_order = nullptr; ulonglong2 *d_jump = nullptr;
+    DLcNode *d_nodes = nullptr; uint32_t *d_leaf_order = nullptr; ulonglong2 *d_jump = nullptr; float4 *d_leaf_geom = nullptr;
     uint64_t n_vrls = 0, searches = 0, merges = 0;
     float build_ms = 0.f;
 };
@@ -199,6 +200,7 @@ void lightcut_free(LightcutTree *t) {
     if (t->d_nodes) cudaFree(t->d_nodes);
     if (t->d_leaf_order) cudaFree(t->d_leaf_order);
     if (t->d_jump) cudaFree(t->d_jump);
+    if (t->d_leaf_geom) cudaFree(t->d_leaf_geom);
     delete t;
 }
 
@@ -326,6 +328,17 @@ cudaError_t lightcut_build(const DVrl *d_vrls, uint64_t n64, uint64_t first_inde
         LC_CU(cudaMalloc((void **) &tree->d_nodes, dn.size() * sizeof(DLcNode)));
         LC_CU(cudaMalloc((void **) &tree->d_leaf_order, (size_t) n * sizeof(uint32_t)));
         LC_CU(cudaMalloc((void **) &tree->d_jump, (size_t) n * sizeof(ulonglong2)));
+        LC_CU(cudaMalloc((void **) &tree->d_leaf_geom, (size_t) n * 2 * sizeof(float4)));
+        {   // the VRLs' geometry in leaf order: the exact-distance bound of a small cluster reads a contiguous run
+            std::vector<float4> geom((size_t) n * 2);
+            for (uint32_t k = 0; k < n; ++k) {
+                const HNode &h = tree->nodes[(size_t) leaf_order[k]];
+                geom[2 * (size_t) k] = make_float4(h.o[0], h.o[1], h.o[2], h.len);
+                geom[2 * (size_t) k + 1] = make_float4(h.d[0], h.d[1], h.d[2], 0.f);
+            }
+            LC_CU(cudaMemcpyAsync(tree->d_leaf_geom, geom.data(), geom.size() * sizeof(float4), cudaMemcpyHostToDevice, stream));
+            LC_CU(cudaStreamSynchronize(stream));
+        }
         LC_CU(cudaMemcpyAsync(tree->d_nodes, dn.data(), dn.size() * sizeof(DLcNode), cudaMemcpyHostToDevice, stream));
         LC_CU(cudaMemcpyAsync(tree->d_leaf_order, leaf_order.data(), (size_t) n * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
         lc_jump_kernel<<<(n + 255) / 256, 256, 0, stream>>>(tree->d_jump, n, first_index);
@@ -349,6 +362,7 @@ done:
 const DLcNode *lightcut_nodes(const LightcutTree *t) { return t->d_nodes; }
 const uint32_t *lightcut_leaf_order(const LightcutTree *t) { return t->d_leaf_order; }
 const ulonglong2 *lightcut_jump(const LightcutTree *t) { return t->d_jump; }
+const float4 *lightcut_leaf_geom(const LightcutTree *t) { return t->d_leaf_geom; }
 uint32_t lightcut_root(const LightcutTree *t) { return (uint32_t) t->root; }
 uint64_t lightcut_n_vrls(const LightcutTree *t) { return t->n_vrls; }
 void lightcut_build_stats(const LightcutTree *t, uint64_t *n_nodes, uint64_t *searches, float *ms) {
@@ -536,7 +550,7 @@ __device__ __noinline__ float seg_seg_sqr(V3 ro, V3 rd, float rmaxt, V3 vo, V3 v
 }
 
 // getClusterUpperBound, vrl_lightcut.h:429-512
-__device__ inline float lc_bound(const LightcutParams &p, const DLcNode *nd, const SegRegs &ray) {
+__device__ __noinline__ float lc_bound(const LightcutParams &p, const DLcNode *nd, const SegRegs &ray) {
     const float4 *row = reinterpret_cast<const float4 *>(nd);
     const float4 r3 = __ldg(row + 3), r4 = __ldg(row + 4);
     const uint32_t n_leaves = __float_as_uint(r4.w);
@@ -546,10 +560,13 @@ __device__ inline float lc_bound(const LightcutParams &p, const DLcNode *nd, con
     } else {
         const uint32_t first = __ldg(&nd->first_leaf);
         best = FLT_MAX;
-        for (uint32_t k = 0; k < n_leaves; ++k) {
-            const float4 *lf = reinterpret_cast<const float4 *>(p.nodes + __ldg(p.leaf_order + first + k));
-            const float4 a = __ldg(lf), b = __ldg(lf + 1);
-            best = fminf(best, seg_seg_sqr(ray.o, ray.d, ray.maxt, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w));
+        const float4 *lf = p.leaf_geom + 2 * (size_t) first;
+        for (uint32_t k0 = 0; k0 < n_leaves; k0 += 4) {                          // four records in flight per round
+            float4 a[4], b[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (k0 + k < n_leaves) { a[k] = __ldg(lf + 2 * (k0 + k)); b[k] = __ldg(lf + 2 * (k0 + k) + 1); }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (k0 + k < n_leaves) best = fminf(best, seg_seg_sqr(ray.o, ray.d, ray.maxt, V3(a[k].x, a[k].y, a[k].z), V3(b[k].x, b[k].y, b[k].z), a[k].w));
         }
     }
     const float min_length = safe_sqrt(best);
@@ -571,14 +588,100 @@ __device__ inline float lc_bound(const LightcutParams &p, const DLcNode *nd, con
 //  Query: VRLLightCut::query, vrl_lightcut.h:243-393 (stochastic = false), wrapped as VRLMap::query does (vrl_map.h:143, 198-205)
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int LC_THREADS = 128;
+constexpr int LC_BLOCKS_PER_SM = 5;      // 640 resident queries per SM (<= 102 registers)
+constexpr uint32_t LC_SMEM_TOP = 21;     // levels 0-2 of the 4-ary heap live in shared memory (21 KB per block)
+
+// getContrib of a cluster's representative carrying the cluster's flux, on the uniforms addressed by the representative's VRL
+template <bool UNIFORM, bool VIS>
+__device__ __noinline__ void lc_eval(const LightcutParams &p, const DLcNode *nd, const SegRegs &ray, uint64_t base_state, float *est) {
+    const float4 *row = reinterpret_cast<const float4 *>(nd);
+    const float4 a = __ldg(row), b = __ldg(row + 1), c = __ldg(row + 2);
+    const ulonglong2 j = __ldg(p.jump + __float_as_uint(c.w));
+    Pcg32 r; r.state = j.x * base_state + j.y;
+    const float u1 = r.next_f32(), u2 = r.next_f32();
+    const DMedium &m = p.scene.media[__float_as_uint(b.w)];
+    const float f = eval_contrib<UNIFORM, VIS, false, true>(p.scene, ray, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w,
+                                                      m.max_density, m.phase, m.g, u1, u2, &m);
+    est[0] = c.x * f * m.sigma_s[0] * m.sigma_s[0];
+    est[1] = c.y * f * m.sigma_s[1] * m.sigma_s[1];
+    est[2] = c.z * f * m.sigma_s[2] * m.sigma_s[2];
+}
+// the exact sum over the set, as the no-acceleration branch (vrl_map.h:151-169) with its stream addressing
+template <bool UNIFORM, bool VIS>
+__device__ __noinline__ void lc_exact_sum(const LightcutParams &p, const SegRegs &ray, uint64_t base_state, float *Li) {
+    Pcg32 r; r.state = base_state;
+    r.advance(p.first_index * 2u);
+    Li[0] = Li[1] = Li[2] = 0.f;
+    for (uint64_t j = 0; j < p.n_vrls; ++j) {
+        const float4 *vp = reinterpret_cast<const float4 *>(p.vrls + j);
+        const float4 a = __ldg(vp), b = __ldg(vp + 1), c = __ldg(vp + 2);
+        const DMedium &m = p.scene.media[__float_as_uint(b.w)];
+        const float u1 = r.next_f32(), u2 = r.next_f32();
+        const float f = eval_contrib<UNIFORM, VIS, false, true>(p.scene, ray, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w,
+                                                          m.max_density, m.phase, m.g, u1, u2, &m);
+        const float cr = c.x * f * m.sigma_s[0] * m.sigma_s[0], cg = c.y * f * m.sigma_s[1] * m.sigma_s[1], cb = c.z * f * m.sigma_s[2] * m.sigma_s[2];
+        if (isfinite(cr) && isfinite(cg) && isfinite(cb)) { Li[0] += cr; Li[1] += cg; Li[2] += cb; }
+    }
+}
+
+// Per-thread refinement heap: a 4-ary max-heap of keys (bound bits << 32 | slot).  Entry i's children are 4i+1 .. 4i+4;
+// entries 0-20 (three levels) sit in shared memory, the rest in the thread's own contiguous run of global memory where every
+// group of four siblings is one aligned 32-byte sector (entry i >= 21 at word i - 21: 4i + 1 - 21 is a multiple of 4).
+struct LcHeap {
+    unsigned long long *g;       // thread's global run
+    unsigned long long *s;       // thread's column of the block's shared array (stride LC_THREADS)
+    uint32_t n;
+    __device__ __forceinline__ unsigned long long load(uint32_t i) const { return i < LC_SMEM_TOP ? s[i * LC_THREADS] : g[i - LC_SMEM_TOP]; }
+    __device__ __forceinline__ void store(uint32_t i, unsigned long long v) { if (i < LC_SMEM_TOP) s[i * LC_THREADS] = v; else g[i - LC_SMEM_TOP] = v; }
+    __device__ inline void push(unsigned long long key) {
+        uint32_t i = n++;
+        while (i > 0) {
+            const uint32_t parent = (i - 1) >> 2;
+            const unsigned long long pk = load(parent);
+            if (pk >= key) break;
+            store(i, pk);
+            i = parent;
+        }
+        store(i, key);
+    }
+    __device__ inline unsigned long long pop() {
+        const unsigned long long top = load(0);
+        const unsigned long long last = load(--n);
+        uint32_t i = 0;
+        while (true) {
+            const uint32_t c0 = 4 * i + 1;
+            if (c0 >= n) break;
+            unsigned long long k0, k1, k2, k3;
+            if (c0 < LC_SMEM_TOP) { k0 = s[c0 * LC_THREADS]; k1 = s[(c0 + 1) * LC_THREADS]; k2 = s[(c0 + 2) * LC_THREADS]; k3 = s[(c0 + 3) * LC_THREADS]; }
+            else {
+                const ulonglong2 *q = reinterpret_cast<const ulonglong2 *>(g + (c0 - LC_SMEM_TOP));
+                const ulonglong2 lo = q[0], hi = q[1];
+                k0 = lo.x; k1 = lo.y; k2 = hi.x; k3 = hi.y;
+            }
+            // entries at or beyond n are stale: masked to 0, which no live key is below
+            if (c0 + 1 >= n) k1 = 0;
+            if (c0 + 2 >= n) k2 = 0;
+            if (c0 + 3 >= n) k3 = 0;
+            unsigned long long mk = k0; uint32_t mi = c0;
+            if (k1 > mk) { mk = k1; mi = c0 + 1; }
+            if (k2 > mk) { mk = k2; mi = c0 + 2; }
+            if (k3 > mk) { mk = k3; mi = c0 + 3; }
+            if (mk <= last) break;
+            store(i, mk);
+            i = mi;
+        }
+        if (n) store(i, last);
+        return top;
+    }
+};
 
 template <bool UNIFORM, bool VIS>
-__global__ void __launch_bounds__(LC_THREADS)
-lightcut_gather_kernel(LightcutParams p) {
+__global__ void __launch_bounds__(LC_THREADS, LC_BLOCKS_PER_SM)
+lightcut_gather_kernel(const __grid_constant__ LightcutParams p) {
+    __shared__ unsigned long long top_keys[LC_SMEM_TOP * LC_THREADS];
     const uint32_t T = gridDim.x * LC_THREADS, t = blockIdx.x * LC_THREADS + threadIdx.x;
-    unsigned long long *hk = p.heap_key + t;         // entry e at hk[e * T]
-    float4 *sl = p.slot_est + t;
-    const DMedium *media = p.scene.media;
+    LcHeap heap; heap.g = p.heap_key + (size_t) t * p.cap; heap.s = top_keys + threadIdx.x; heap.n = 0;
+    float4 *sl = p.slot_est + (size_t) t * p.cap;    // payload slots: estimate + node (while live) / next free slot
     unsigned long long n_evals = 0, n_pops = 0, n_over = 0, n_queries = 0; uint32_t max_heap = 0;
 
     for (uint64_t seg_i = t; seg_i < p.n_segs; seg_i += T) {
@@ -597,74 +700,33 @@ lightcut_gather_kernel(LightcutParams p) {
         for (uint32_t s = 0; s < p.q; ++s) {
             Pcg32 base; base.state = rng0;
             if (s) base.advance((uint64_t) s * p.total * 2u);
-            // getContrib of a cluster's representative carrying the cluster's flux
-            auto eval = [&](const DLcNode *nd, float *est) {
-                const float4 *row = reinterpret_cast<const float4 *>(nd);
-                const float4 a = __ldg(row), b = __ldg(row + 1), c = __ldg(row + 2);
-                const ulonglong2 j = __ldg(p.jump + __float_as_uint(c.w));
-                Pcg32 r; r.state = j.x * base.state + j.y;
-                const float u1 = r.next_f32(), u2 = r.next_f32();
-                const DMedium &m = media[__float_as_uint(b.w)];
-                const float f = eval_contrib<UNIFORM, VIS, false>(p.scene, ray, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w,
-                                                                  m.max_density, m.phase, m.g, u1, u2, &m);
-                est[0] = c.x * f * m.sigma_s[0] * m.sigma_s[0];
-                est[1] = c.y * f * m.sigma_s[1] * m.sigma_s[1];
-                est[2] = c.z * f * m.sigma_s[2] * m.sigma_s[2];
-            };
-            uint32_t heap_n = 0, bump = 0; int32_t free_head = -1;
-            auto alloc_slot = [&]() -> int32_t {
-                if (free_head >= 0) { int32_t s_ = free_head; free_head = __float_as_int(sl[(size_t) s_ * T].w); return s_; }
-                if (bump < p.cap) return (int32_t) bump++;
-                return -1;
-            };
+            heap.n = 0;
+            uint32_t bump = 0; int32_t free_head = -1;
+            // payload slot + key; false when the thread's run is full
             auto push = [&](float bound, uint32_t node, const float *est) -> bool {
-                const int32_t slot = alloc_slot();
-                if (slot < 0) return false;
-                sl[(size_t) slot * T] = make_float4(est[0], est[1], est[2], __uint_as_float(node));
-                const unsigned long long key = ((unsigned long long) __float_as_uint(bound) << 32) | (uint32_t) slot;
-                uint32_t i = heap_n++;
-                while (i > 0) {
-                    const uint32_t parent = (i - 1) >> 1;
-                    const unsigned long long pk = hk[(size_t) parent * T];
-                    if (pk >= key) break;
-                    hk[(size_t) i * T] = pk;
-                    i = parent;
-                }
-                hk[(size_t) i * T] = key;
+                int32_t slot;
+                if (free_head >= 0) { slot = free_head; free_head = __float_as_int(sl[slot].w); }
+                else if (bump < p.cap) slot = (int32_t) bump++;
+                else return false;
+                sl[slot] = make_float4(est[0], est[1], est[2], __uint_as_float(node));
+                heap.push(((unsigned long long) __float_as_uint(bound) << 32) | (uint32_t) slot);
                 return true;
             };
-            auto pop = [&]() -> unsigned long long {
-                const unsigned long long top = hk[0];
-                const unsigned long long last = hk[(size_t) (--heap_n) * T];
-                uint32_t i = 0;
-                while (true) {
-                    uint32_t l = 2 * i + 1;
-                    if (l >= heap_n) break;
-                    unsigned long long lk = hk[(size_t) l * T];
-                    if (l + 1 < heap_n) { const unsigned long long rk = hk[(size_t) (l + 1) * T]; if (rk > lk) { lk = rk; ++l; } }
-                    if (lk <= last) break;
-                    hk[(size_t) i * T] = lk;
-                    i = l;
-                }
-                if (heap_n) hk[(size_t) i * T] = last;
-                return top;
-            };
-
             float Li[3];
             bool overflow = false;
             {
                 const DLcNode *root = p.nodes + p.root;
                 const float b = lc_bound(p, root, ray);
-                float e[3]; eval(root, e);
+                float e[3]; lc_eval<UNIFORM, VIS>(p, root, ray, base.state, e);
                 push(b, p.root, e);
                 Li[0] = e[0]; Li[1] = e[1]; Li[2] = e[2];
             }
-            while (heap_n > 0) {
-                const unsigned long long top = pop();
+            while (heap.n > 0) {
+                const unsigned long long top = heap.pop();
                 const float bound = __uint_as_float((uint32_t) (top >> 32));
                 const int32_t slot = (int32_t) (top & 0xffffffffu);
-                const float4 pay = sl[(size_t) slot * T];
-                sl[(size_t) slot * T].w = __int_as_float(free_head); free_head = slot;
+                const float4 pay = sl[slot];
+                sl[slot].w = __int_as_float(free_head); free_head = slot;
                 const float thr = fmaxf(fmaxf(Li[0] * p.err, Li[1] * p.err), Li[2] * p.err);
                 if (bound < thr) break;
                 ++q_pops;
@@ -672,49 +734,39 @@ lightcut_gather_kernel(LightcutParams p) {
                 const DLcNode *cl = p.nodes + __float_as_uint(pay.w);
                 const float4 c2 = __ldg(reinterpret_cast<const float4 *>(cl) + 2);
                 const int4 topo = __ldg(reinterpret_cast<const int4 *>(cl) + 5);       // child0, child1, same, first_leaf
-                const DLcNode *ch[2] = { p.nodes + topo.x, p.nodes + topo.y };
                 if (topo.x < 0) continue;                                             // a one-VRL tree: the root has no children (:309-310)
-                const int same = topo.z, fresh = 1 - same;
-                float est[2][3];
+                const int same = topo.z;
+                const DLcNode *ch_same = p.nodes + (same == 0 ? topo.x : topo.y), *ch_fresh = p.nodes + (same == 0 ? topo.y : topo.x);
+                float es[3], ef[3];
                 {   // the child that keeps the representative: the parent's estimate scaled by the flux ratio (:320-339)
-                    const float4 f = __ldg(reinterpret_cast<const float4 *>(ch[same]) + 2);
+                    const float4 f = __ldg(reinterpret_cast<const float4 *>(ch_same) + 2);
                     float ex = f.x, ey = f.y, ez = f.z;
                     if (c2.x > 0.0f) ex /= c2.x;
                     if (c2.y > 0.0f) ey /= c2.y;
                     if (c2.z > 0.0f) ez /= c2.z;
                     ex *= pay.x; ey *= pay.y; ez *= pay.z;
                     if (isnan(ex) || isnan(ey) || isnan(ez)) { ex = ey = ez = 0.f; }
-                    est[same][0] = ex; est[same][1] = ey; est[same][2] = ez;
+                    es[0] = ex; es[1] = ey; es[2] = ez;
                 }
-                eval(ch[fresh], est[fresh]);
+                lc_eval<UNIFORM, VIS>(p, ch_fresh, ray, base.state, ef);
                 ++q_evals;
-#pragma unroll
+                // children in the reference's order (0 then 1): Li += estimate; an inner child enters the heap with its bound
+#pragma unroll 1
                 for (int c = 0; c < 2; ++c) {
-                    Li[0] = Li[0] + est[c][0]; Li[1] = Li[1] + est[c][1]; Li[2] = Li[2] + est[c][2];
-                    const int32_t id = c == 0 ? topo.x : topo.y;
-                    if (__ldg(&ch[c]->child0) >= 0) {
-                        if (!push(lc_bound(p, ch[c], ray), (uint32_t) id, est[c])) { overflow = true; break; }
+                    const bool is_same = c == same;
+                    const float *e = is_same ? es : ef;
+                    const DLcNode *ch = is_same ? ch_same : ch_fresh;
+                    Li[0] = Li[0] + e[0]; Li[1] = Li[1] + e[1]; Li[2] = Li[2] + e[2];
+                    if (__ldg(&ch->child0) >= 0) {
+                        if (!push(lc_bound(p, ch, ray), (uint32_t) (c == 0 ? topo.x : topo.y), e)) { overflow = true; break; }
                     }
                 }
                 if (overflow) break;
-                q_heap = max(q_heap, heap_n);
+                q_heap = max(q_heap, heap.n);
             }
             if (overflow) {
-                // the exact sum over the set, as the no-acceleration branch (vrl_map.h:151-169) with its stream addressing
                 q_over = true;
-                Pcg32 r = base;
-                r.advance(p.first_index * 2u);
-                Li[0] = Li[1] = Li[2] = 0.f;
-                for (uint64_t j = 0; j < p.n_vrls; ++j) {
-                    const float4 *vp = reinterpret_cast<const float4 *>(p.vrls + j);
-                    const float4 a = __ldg(vp), b = __ldg(vp + 1), c = __ldg(vp + 2);
-                    const DMedium &m = media[__float_as_uint(b.w)];
-                    const float u1 = r.next_f32(), u2 = r.next_f32();
-                    const float f = eval_contrib<UNIFORM, VIS, false>(p.scene, ray, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), a.w,
-                                                                      m.max_density, m.phase, m.g, u1, u2, &m);
-                    const float cr = c.x * f * m.sigma_s[0] * m.sigma_s[0], cg = c.y * f * m.sigma_s[1] * m.sigma_s[1], cb = c.z * f * m.sigma_s[2] * m.sigma_s[2];
-                    if (isfinite(cr) && isfinite(cg) && isfinite(cb)) { Li[0] += cr; Li[1] += cg; Li[2] += cb; }
-                }
+                lc_exact_sum<UNIFORM, VIS>(p, ray, base.state, Li);
                 q_evals += (uint32_t) p.n_vrls;
             }
             tot[0] = tot[0] + fmaxf(Li[0], 0.f) * p.scale;
@@ -744,8 +796,8 @@ lightcut_gather_kernel(LightcutParams p) {
 }
 
 uint32_t lightcut_grid(uint64_t n_segs, uint32_t cap, int n_sms, size_t budget_bytes) {
-    uint32_t per_sm = 4;
-    while (per_sm > 1 && (size_t) n_sms * per_sm * LC_THREADS * cap * 24ull > budget_bytes) per_sm >>= 1;
+    uint32_t per_sm = LC_BLOCKS_PER_SM;
+    while (per_sm > 1 && (size_t) n_sms * per_sm * LC_THREADS * cap * 24ull > budget_bytes) --per_sm;
     uint64_t want = (n_segs + LC_THREADS - 1) / LC_THREADS;
     return (uint32_t) std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t) n_sms * per_sm));
 }

@@ -25,6 +25,7 @@ void lightcut_free(LightcutTree *t);
 const DLcNode *lightcut_nodes(const LightcutTree *t);
 const uint32_t *lightcut_leaf_order(const LightcutTree *t);
 const ulonglong2 *lightcut_jump(const LightcutTree *t);
+const float4 *lightcut_leaf_geom(const LightcutTree *t);
 uint32_t lightcut_root(const LightcutTree *t);
 uint64_t lightcut_n_vrls(const LightcutTree *t);
 void lightcut_build_stats(const LightcutTree *t, uint64_t *n_nodes, uint64_t *searches, float *ms);
@@ -34,6 +35,7 @@ struct LightcutParams {
     DScene              scene;
     const vrlb_segment *segs; uint64_t n_segs;
     const DLcNode      *nodes; const uint32_t *leaf_order; const ulonglong2 *jump;
+    const float4       *leaf_geom;       // (o, length), (d, -) of the VRLs in leaf order
     const DVrl         *vrls;            // the set itself: the exact sum of a query whose heap overflows
     uint64_t            n_vrls, first_index, total;
     uint32_t            root;
@@ -42,7 +44,7 @@ struct LightcutParams {
     uint32_t            q;               // samples_per_query
     unsigned long long *heap_key; float4 *slot_est; uint32_t cap;     // per-thread refinement heaps, interleaved across the grid's threads
     float              *film_rgb, *seg_out, *seg_stats;               // seg_stats: n_segs * 4 = evaluations, refinements, largest heap, overflowed
-    unsigned long long *stats;           // 5 words: queries, fresh evaluations, refinements, overflowed queries, largest heap
+    unsigned long long *stats;           // 8 words, zeroed before the launch: queries, fresh evaluations, refinements, overflowed queries, largest heap, next query
 };
 // blocks of the query kernel such that its heaps fit `budget_bytes`
 uint32_t lightcut_grid(uint64_t n_segs, uint32_t cap, int n_sms, size_t budget_bytes);

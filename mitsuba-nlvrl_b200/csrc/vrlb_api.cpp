@@ -698,15 +698,15 @@ static int lightcut_gather_impl(vrlb_context *ctx, const vrlb_options *opt, floa
     if (lightcut_n_vrls(ctx->lc) != ctx->n_vrls) return fail(ctx, VRLB_ERR_STATE, "light tree is stale");
     LightcutParams p{};
     p.scene = ctx->scene; p.segs = ctx->segs.ptr; p.n_segs = ctx->n_segs;
-    p.nodes = lightcut_nodes(ctx->lc); p.leaf_order = lightcut_leaf_order(ctx->lc); p.jump = lightcut_jump(ctx->lc);
+    p.nodes = lightcut_nodes(ctx->lc); p.leaf_order = lightcut_leaf_order(ctx->lc); p.jump = lightcut_jump(ctx->lc); p.leaf_geom = lightcut_leaf_geom(ctx->lc);
     p.vrls = ctx->vrls.ptr; p.n_vrls = ctx->n_vrls; p.first_index = ctx->vrl_first; p.total = ctx->vrl_total;
     p.root = lightcut_root(ctx->lc); p.scale = ctx->vrl_scale; p.err = opt->threshold_error; p.better_dist = opt->threshold_better_dist;
     p.q = (uint32_t) opt->samples_per_query;
     // a heap never holds more than the tree's inner nodes
-    const uint64_t want = opt->lightcut_heap > 0 ? (uint64_t) opt->lightcut_heap : 16384u;
-    p.cap = (uint32_t) std::max<uint64_t>(2, std::min<uint64_t>(want, ctx->n_vrls));
+    const uint64_t want = opt->lightcut_heap > 0 ? (uint64_t) opt->lightcut_heap : 12288u;
+    p.cap = (uint32_t) ((std::max<uint64_t>(2, std::min<uint64_t>(want, ctx->n_vrls)) + 3) & ~3ull);      // runs of whole 32-byte sectors
     int n_sms = 148; cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    const uint32_t grid = lightcut_grid(p.n_segs, p.cap, n_sms, (size_t) 24 << 30);
+    const uint32_t grid = lightcut_grid(p.n_segs, p.cap, n_sms, (size_t) 40 << 30);
     const size_t entries = (size_t) grid * 128 * p.cap;
     CU(ctx, ctx->lc_heap.reserve(entries)); CU(ctx, ctx->lc_slots.reserve(entries)); CU(ctx, ctx->lc_stats.reserve(8));
     CU(ctx, cudaMemsetAsync(ctx->lc_stats.ptr, 0, 8 * sizeof(unsigned long long), ctx->stream));

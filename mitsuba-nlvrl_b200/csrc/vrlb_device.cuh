@@ -405,6 +405,66 @@ __device__ inline bool any_hit(const DScene &s, V3 o, V3 d, float mint, float ma
     return false;
 }
 
+// any_hit with the solids' conservative proxies in front of their BVHs (occluder_proxies.cpp): a segment that misses a
+// solid's bounding sphere or outer oriented box cannot hit it; a segment that enters from outside and meets the inscribed
+// sphere or box of a CLOSED solid is occluded.  The proxies carry the build's safety margin, so the answer is any_hit's;
+// only segments between the inner and the outer proxies walk the triangles.  For callers whose lanes trace unrelated
+// segments (the light cut's per-query refinement), where a BVH walk runs one or two lanes wide.
+__device__ inline bool any_hit_proxied(const DScene &s, V3 o, V3 d, float mint, float maxt) {
+    if (s.n_tris == 0) return false;
+    V3 inv(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    if (s.main_root != 0x80000000u && traverse_any_hit(s, s.main_root, o, d, inv, mint, maxt)) return true;
+    const V3 a = o + d * mint, e = o + d * maxt;
+    for (int i = 0; i < s.n_shells; ++i) {
+        const DShell &sh = s.shells[i];
+        bool inside = o.x > sh.lo[0] && o.x < sh.hi[0] && o.y > sh.lo[1] && o.y < sh.hi[1] && o.z > sh.lo[2] && o.z < sh.hi[2] &&
+                      e.x > sh.lo[0] && e.x < sh.hi[0] && e.y > sh.lo[1] && e.y < sh.hi[1] && e.z > sh.lo[2] && e.z < sh.hi[2];
+        if (!inside && traverse_any_hit(s, sh.root, o, d, inv, mint, maxt)) return true;
+    }
+    const V3 dir = e - a;                                      // the segment a + t dir, t in [0, 1]
+    const float inv_d2 = 1.0f / dot(dir, dir);
+    for (int i = 0; i < s.n_solids; ++i) {
+        const DSolid &so = s.solids[i];
+        if (!slab(make_float4(so.lo[0], so.lo[1], so.lo[2], 0.f), make_float4(so.hi[0], so.hi[1], so.hi[2], 0.f), o, inv, mint, maxt)) continue;
+        const V3 oc(so.c[0] - a.x, so.c[1] - a.y, so.c[2] - a.z);
+        {
+            const float t = fminf(fmaxf(dot(oc, dir) * inv_d2, 0.f), 1.f);
+            const V3 q = oc - dir * t;
+            if (dot(q, q) > so.r_out2) continue;                                    // misses the bounding sphere
+        }
+        const V3 ec(so.c[0] - e.x, so.c[1] - e.y, so.c[2] - e.z);
+        bool enters = dot(oc, oc) > so.r_out2 || dot(ec, ec) > so.r_out2;          // an end point outside the solid
+        if ((so.flags & VRLB_SOLID_INNER_SPHERE) && enters) {
+            const V3 oi(so.ci[0] - a.x, so.ci[1] - a.y, so.ci[2] - a.z);
+            const float t = fminf(fmaxf(dot(oi, dir) * inv_d2, 0.f), 1.f);
+            const V3 q = oi - dir * t;
+            if (dot(q, q) <= so.r_in2) return true;
+        }
+        if (so.flags & (VRLB_SOLID_OUTER_OBB | VRLB_SOLID_INNER_OBB)) {
+            const V3 r(a.x - so.oc[0], a.y - so.oc[1], a.z - so.oc[2]);
+            const V3 ol(dot(V3(so.ax[0], so.ax[1], so.ax[2]), r), dot(V3(so.ax[3], so.ax[4], so.ax[5]), r), dot(V3(so.ax[6], so.ax[7], so.ax[8]), r));
+            const V3 dl(dot(V3(so.ax[0], so.ax[1], so.ax[2]), dir), dot(V3(so.ax[3], so.ax[4], so.ax[5]), dir), dot(V3(so.ax[6], so.ax[7], so.ax[8]), dir));
+            const V3 il(1.0f / dl.x, 1.0f / dl.y, 1.0f / dl.z);
+            if (so.flags & VRLB_SOLID_OUTER_OBB) {
+                if (!slab2(-so.h_out[0], -so.h_out[1], -so.h_out[2], so.h_out[0], so.h_out[1], so.h_out[2], il, ol, 0.f, 1.f)) continue;
+                const V3 el = ol + dl;
+                enters = enters || fabsf(ol.x) > so.h_out[0] || fabsf(ol.y) > so.h_out[1] || fabsf(ol.z) > so.h_out[2] ||
+                         fabsf(el.x) > so.h_out[0] || fabsf(el.y) > so.h_out[1] || fabsf(el.z) > so.h_out[2];
+            }
+            if ((so.flags & VRLB_SOLID_INNER_OBB) && enters) {
+                const float ax = (-so.h_in[0] - ol.x) * il.x, bx = (so.h_in[0] - ol.x) * il.x;
+                const float ay = (-so.h_in[1] - ol.y) * il.y, by = (so.h_in[1] - ol.y) * il.y;
+                const float az = (-so.h_in[2] - ol.z) * il.z, bz = (so.h_in[2] - ol.z) * il.z;
+                const float t0 = fmaxf(fmaxf(0.f, fminf(ax, bx)), fmaxf(fminf(ay, by), fminf(az, bz)));
+                const float t1 = fminf(fminf(1.f, fmaxf(ax, bx)), fminf(fmaxf(ay, by), fmaxf(az, bz)));
+                if (t0 <= t1) return true;
+            }
+        }
+        if (traverse_any_hit(s, so.root, o, d, inv, mint, maxt)) return true;
+    }
+    return false;
+}
+
 __device__ inline V3 tri_normal(const DTri &t) {
     return normalize(cross(V3(t.e1[0], t.e1[1], t.e1[2]), V3(t.e2[0], t.e2[1], t.e2[2])));
 }
