@@ -56,8 +56,9 @@ static int selftest() {
     expect_throw("unreferenced property", [] { Properties p; p.set_int("vrlTargetNum", 5); VRLIntegrator it(p); }, "unreferenced property");
     expect_throw("wrong type", [] { Properties p; p.set_string("target_vrls", "many"); VRLIntegrator it(p); }, "wrong type");
     expect_throw("sample() has no CPU path", [] { Properties p; VRLIntegrator it(p); it.sample(); }, "no CPU fallback");
-    { Properties p; p.set_bool("use_light_cut", true); p.set_bool("stochastic_lightcut", true); p.set_int("lightcut_samples", 4); VRLIntegrator it(p);
-      std::printf("ok   use_light_cut is accepted (the gather is exact)\n"); }
+    { Properties p; p.set_bool("use_light_cut", true); p.set_float("threshold_error", 0.05); p.set_int("threshold_better_dist", 4); VRLIntegrator it(p);
+      std::printf("ok   use_light_cut is accepted (the cut is walked on the device)\n"); }
+    expect_throw("stochastic_lightcut", [] { Properties p; p.set_bool("use_light_cut", true); p.set_bool("stochastic_lightcut", true); VRLIntegrator it(p); }, "not supported");
     { VrlSet s; s.n = 3; s.scale = 0.25f; s.soa10.resize(30); for (int i = 0; i < 30; ++i) s.soa10[i] = (float) i; s.medium = { 0, 1, 0 };
       s.save("/tmp/_vrlb_selftest.vrlb"); VrlSet t; t.load("/tmp/_vrlb_selftest.vrlb");
       bool ok = t.n == 3 && t.scale == 0.25f && t.soa10 == s.soa10 && t.medium == s.medium;

@@ -124,12 +124,13 @@ VRLIntegrator::VRLIntegrator(const Properties &props) {
         for (size_t i = 0; i < rest.size(); ++i) msg += (i ? ", \"" : "\"") + rest[i] + "\"";
         Throw(msg);
     }
-    // The lightcut (vrl_lightcut.h) is the reference's way to make 32k-128k VRLs affordable on CPU cores: it replaces
-    // clusters of VRLs by a representative whenever a bound on the cluster's error is below `threshold_error`.  The B200
-    // gather evaluates every VRL (error 0 <= any threshold), so the option is accepted and the cut parameters are
-    // unused; images differ from the reference's lightcut images by the reference's own clustering error.
-    if (m_useLightCut)
-        std::fprintf(stderr, "[VRLIntegrator] use_light_cut: the B200 gather evaluates the full VRL set (exact; threshold_error = %g is met trivially)\n", m_thresholdError);
+    // The light cut (vrl_lightcut.h): the library builds the reference's tree over the final VRL set (vrlb_lightcut_build in
+    // preprocess / set_vrls) and every query walks its cut (vrl_map.h:198-201).  stochastic_lightcut re-draws the
+    // representatives per query on a per-thread copy of the tree (vrl_lightcut.h:153-193, 257-261): not built.
+    if (m_useLightCut && m_stochasticLightcut)
+        Throw("\"stochastic_lightcut\" is not supported by the B200 light cut (deterministic representatives only)");
+    if (m_useLightCut && m_useNLAtomicQuery && m_useNonLinearCameraRays)
+        Throw("\"use_light_cut\" with \"use_nl_atomic_query\": multi-part queries through the cut are not supported");
     if (m_samplesPerQuery < 1) Throw("\"samples_per_query\" must be >= 1");
 }
 
@@ -156,6 +157,7 @@ vrlb_options VRLIntegrator::make_options(const HostSensor &sensor) const {
     o.max_depth = (int32_t) m_maxDepth;
     o.use_non_linear_camera = m_useNonLinearCameraRays; o.use_nl_atomic_query = m_useNLAtomicQuery;
     o.visibility = 1; o.hide_emitters = m_hideEmitters; o.math_mode = (int32_t) m_mathMode;
+    o.use_light_cut = m_useLightCut; o.threshold_error = (float) m_thresholdError; o.threshold_better_dist = (int32_t) m_thresholdBetterDist;
     return o;
 }
 
@@ -166,9 +168,10 @@ void VRLIntegrator::set_vrls(const VrlSet &set) {
     d.n = set.n; d.first_index = 0; d.total = set.n; d.scale = set.scale;
     check(vrlb_vrls_upload(m_ctx, &d), "vrlb_vrls_upload");
     m_have_vrls = true;
+    if (m_useLightCut) build_lightcut(0);
 }
 
-void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
+void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &sensor) {
     if (!m_ctx) check(vrlb_create((int) m_device, &m_ctx), "vrlb_create");
     vrlb_scene_desc sd{};
     sd.tri_verts = scene.tri_verts.data(); sd.tri_flags = scene.tri_flags.data(); sd.n_tris = (uint32_t) scene.tri_flags.size();
@@ -231,7 +234,18 @@ void VRLIntegrator::preprocess(const HostScene &scene, const HostSensor &) {
         check(vrlb_vrls_dice(m_ctx, (uint32_t) m_diceVRL, &n), "vrlb_vrls_dice");
         std::fprintf(stderr, "[VRLIntegrator] Dicing the VRL... Number of VRLs: %llu\n", (unsigned long long) n);
     }
+    if (m_useLightCut && (!m_lightcutBuilt || m_longVRL || m_diceVRL > 1)) build_lightcut(sensor.sampler_seed);
     m_preprocessed = true;
+}
+
+// VRLMap::build's ELightCutAcceleration branch (vrl_map.h:89-97, called from vrl.cpp:424 with the preprocess sampler)
+void VRLIntegrator::build_lightcut(uint64_t base_seed) {
+    check(vrlb_lightcut_build(m_ctx, base_seed, 0), "vrlb_lightcut_build");
+    vrlb_lightcut_stats st{};
+    vrlb_lightcut_get_stats(m_ctx, &st);
+    std::fprintf(stderr, "[VRLIntegrator] Building VRL lightcut acceleration: %llu nodes, %llu partner searches, %.0f ms\n",
+                 (unsigned long long) st.n_nodes, (unsigned long long) st.build_searches, st.build_ms);
+    m_lightcutBuilt = true;
 }
 
 bool VRLIntegrator::render(const HostScene &scene, const HostSensor &sensor, std::vector<float> &xyzaw) {
@@ -260,7 +274,9 @@ std::string VRLIntegrator::to_string() const {
     std::ostringstream o;
     o << "VRLIntegrator[\n  max_depth = " << m_maxDepth << ",\n  rr_depth = " << m_rrDepth << ",\n  target_vrls = " << m_targetVRLs
       << ",\n  samples_per_query = " << m_samplesPerQuery << ",\n  use_uniform_sampling = " << m_useUniformSampling
-      << ",\n  rr_vrl = " << m_RRVRL << ",\n  backend = libvrl_b200 (sm_100a), math_mode = " << m_mathMode << "\n]";
+      << ",\n  rr_vrl = " << m_RRVRL << ",\n  use_light_cut = " << m_useLightCut << " (threshold_error = " << m_thresholdError
+      << ", threshold_better_dist = " << m_thresholdBetterDist << ")"
+      << ",\n  backend = libvrl_b200 (sm_100a), math_mode = " << m_mathMode << "\n]";
     return o.str();
 }
 

@@ -113,7 +113,8 @@ private:
     vrlb_options make_options(const HostSensor &sensor) const;
     void check(int rc, const char *what) const;
     vrlb_context *m_ctx = nullptr;
-    bool m_preprocessed = false, m_have_vrls = false;
+    bool m_preprocessed = false, m_have_vrls = false, m_lightcutBuilt = false;
+    void build_lightcut(uint64_t base_seed);
     vrlb_timing m_timing{};
 };
 

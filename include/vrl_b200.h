@@ -153,8 +153,9 @@ typedef struct vrlb_options {
     float    threshold_error;       /* m_errorRatio: a cluster is refined while its bound >= threshold_error * hmax(Li) (0.02) */
     int32_t  threshold_better_dist; /* clusters of at most this many VRLs bound the distance by exact segment-segment
                                        distances instead of the box (8) */
-    int32_t  lightcut_heap;         /* 0 = default (4096): entries of a query's refinement heap; a query that needs more
-                                       is counted in vrlb_lightcut_stats and finishes with the exact sum over the VRLs */
+    int32_t  lightcut_heap;         /* entries of a query's refinement heap; 0 = default max(4096, 4 N^(2/3)), four times the
+                                       largest heap measured on the bench frame.  A query that needs more is counted in
+                                       vrlb_lightcut_stats and finishes with the exact sum over the VRLs (slow: N evals on one lane) */
 } vrlb_options;
 
 /* ---- VRL set ----------------------------------------------------------- */
