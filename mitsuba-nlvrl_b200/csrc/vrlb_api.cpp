@@ -89,7 +89,7 @@ struct vrlb_context {
     void *pinned = nullptr; size_t pinned_cap = 0;
     uint32_t *wd = nullptr;           // pinned, 32 words: in-kernel watchdog record (gather_fast.cu)
 
-    cudaEvent_t ev[8] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
+    cudaEvent_t ev[10] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };   // [8], [9]: the gather's launch pacing
     vrlb_timing timing{};
     uint64_t launches = 0;       // lifetime kernel-launch count of this library
 
@@ -770,14 +770,42 @@ static int gather_impl(vrlb_context *ctx, const vrlb_options *opt, float *seg_ou
     // it by 1 / h, so the threshold has to scale with the scene (0.2 on the +-10 box-fog scene the kernel was tuned on).
     p.guard_h = opt->reserved[0] ? (float) opt->reserved[0] * 1e-3f : 0.01f * ctx->scene_extent / 1.001f;   // dev knob (milli-units); 0 = shipped default
     p.guard_z = opt->reserved[1] ? (float) opt->reserved[1] : 8.0f;
+    // The film path cuts the sum over the VRLs into launches of ~1/4 s so that vrlb_cancel has the latency of the
+    // reference's per-block should_stop() (integrator.cpp:124): the host keeps one launch queued ahead of the running one
+    // and looks at the flag before every launch.  Cuts sit on multiples of 512 VRLs, the visibility kernel's trace-batch
+    // window, so a chunked gather adds the same per-eval values as one launch would (the film sums them by fp32 RED
+    // either way).  Per-segment output (tests) stays one launch: seg_out is assigned, not accumulated.
+    const double rate = !fast ? (ctx->any_grid ? 2e9 : 2e10) : 4e10;                 // evals / s, low estimates per kernel
+    uint64_t chunk = p.n_vrls;
+    if (!seg_out_dev && p.n_segs) {
+        const double per_launch = 0.25 * rate / ((double) p.n_segs * p.q);
+        chunk = std::max<uint64_t>(512, (uint64_t) per_launch / 512 * 512);
+        if (chunk * 5 / 4 >= p.n_vrls) chunk = p.n_vrls;                                 // a short tail is not worth a launch
+    }
+    const DVrl *v0 = p.vrls, *vf0 = p.vrls_fast; const DVrlV *vv0 = p.vrls_vis;
+    const uint64_t n_all = p.n_vrls, first_all = p.first_index;
+    uint32_t n_launch = 0;
     cudaEventRecord(ctx->ev[2], ctx->stream);
-    if (!fast) CU(ctx, launch_gather(p, uniform, opt->rr_vrl != 0, vis, ctx->any_grid, ctx->stream));
-    else CU(ctx, launch_gather_fast(p, uniform, opt->rr_vrl != 0, vis, ctx->all_iso, opt->math_mode == 1, ctx->stream));
+    for (uint64_t lo = 0; lo < n_all; lo += chunk) {
+        if (n_launch && ctx->cancel.exchange(0)) {
+            cudaStreamSynchronize(ctx->stream);
+            return fail(ctx, VRLB_ERR_CANCELLED, "cancelled after %llu of %llu VRLs", (unsigned long long) lo, (unsigned long long) n_all);
+        }
+        p.n_vrls = std::min<uint64_t>(chunk, n_all - lo); p.first_index = first_all + lo;
+        p.vrls = v0 + lo; p.vrls_fast = vf0 ? vf0 + lo : nullptr; p.vrls_vis = vv0 ? vv0 + lo : nullptr;
+        if (!fast) CU(ctx, launch_gather(p, uniform, opt->rr_vrl != 0, vis, ctx->any_grid, ctx->stream));
+        else CU(ctx, launch_gather_fast(p, uniform, opt->rr_vrl != 0, vis, ctx->all_iso, opt->math_mode == 1, ctx->stream));
+        if (chunk < n_all) {                     // wait for the launch BEFORE this one: one stays queued behind the running one
+            if (n_launch) CU(ctx, cudaEventSynchronize(ctx->ev[8 + ((n_launch - 1) & 1)]));
+            cudaEventRecord(ctx->ev[8 + (n_launch & 1)], ctx->stream);
+        }
+        ++n_launch;
+    }
     cudaEventRecord(ctx->ev[3], ctx->stream);
-    bool launched = p.n_segs && p.n_vrls;
-    ctx->timing.gather_launches = launched ? 1 : 0;
-    ctx->timing.total_launches += launched ? 1 : 0; ctx->launches += launched ? 1 : 0;
-    ctx->timing.n_evals = p.n_segs * p.n_vrls * p.q;
+    if (!p.n_segs) n_launch = 0;
+    ctx->timing.gather_launches = n_launch;
+    ctx->timing.total_launches += n_launch; ctx->launches += n_launch;
+    ctx->timing.n_evals = p.n_segs * n_all * p.q;
     return VRLB_OK;
 }
 

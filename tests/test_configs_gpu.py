@@ -131,3 +131,42 @@ def test_config4_bench_frame_1080p_100k(ctx):
         ctx.upload_vrls(scenes.vrlset_desc(np.ascontiguousarray(soa[:, lo:hi]), scale=1.0 / n, first_index=lo, total=n))
         parts += ctx.gather_segments(opt)
     assert rel_err(parts, whole).max() <= 1e-6
+
+
+def test_cancel_stops_a_long_gather_within_a_second(ctx):
+    """vrlb_cancel from another thread (Integrator::cancel, integrator.h:148; the reference polls should_stop() per block,
+    integrator.cpp:124): the film gather runs as launches of ~1/4 s and stops between two of them; the chunked sum is the
+    single launch's sum (cuts on the visibility kernel's 512-VRL windows)."""
+    import threading
+    import time
+    sc, cam = scenes.box_fog_scene(occluders=True), scenes.box_fog_camera(1920, 1080)
+    opt = scenes.default_options(visibility=1)
+    n = 60000
+    soa = scenes.synthetic_vrls(n, seed=3)
+    ctx.set_scene(sc)
+    ctx.upload_vrls(scenes.vrlset_desc(soa))
+    ctx.build_segments(cam, opt)
+    ctx.clear_film()
+    t0 = time.time()
+    ctx.gather(opt); ctx.synchronize()
+    full_s = time.time() - t0
+    assert ctx.timing()["gather_launches"] >= 8                      # ~2.6 s of work in quarter-second launches
+    film = ctx.film_rgb(cam.width, cam.height).astype(np.float64)
+    # the same frame as ONE launch: per-segment output, accumulated here
+    segs = ctx.download_segments()
+    li = ctx.gather_segments(opt).astype(np.float64)
+    acc = np.zeros((cam.width * cam.height, 3))
+    np.add.at(acc, segs["pixel"], li * segs["weight"])
+    assert rel_err(film.reshape(-1, 3), acc).max() <= 2e-6
+    # cancel 0.3 s into the next gather
+    ctx.clear_film()
+    threading.Timer(0.3, ctx.cancel).start()
+    t0 = time.time()
+    with pytest.raises(api.VrlbError) as e:
+        ctx.gather(opt)
+    stopped_s = time.time() - t0
+    assert e.value.code == abi.ERR_CANCELLED
+    assert stopped_s <= 1.1 and stopped_s < 0.6 * full_s, (stopped_s, full_s)
+    ctx.clear_film()
+    ctx.gather(opt); ctx.synchronize()                                # the context is usable afterwards, same film
+    assert rel_err(ctx.film_rgb(cam.width, cam.height).astype(np.float64).reshape(-1, 3), film.reshape(-1, 3)).max() <= 2e-6
