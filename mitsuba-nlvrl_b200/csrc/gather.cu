@@ -122,7 +122,7 @@ gather_kernel(GatherParams p) {
                 float u1 = rng.next_f32(), u2 = rng.next_f32();
                 if (!survive) continue;
                 float st2 = 0.f;
-                float f = eval_contrib<UNIFORM, VIS, GRID>(p.scene, ray, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2,
+                float f = eval_contrib<UNIFORM, VIS, GRID, true>(p.scene, ray, vo, vd, vlen, m.max_density, m.phase, m.g, u1, u2,
                                                            &m, eval_state, &st2, nullptr, nla_off, nla_total);
                 if (RR) f = f / rrWeight;
                 // flux * f * sigma_s(cam) * sigma_s(vrl) * m_scale (vrl_struct.h:652-659, vrl_map.h:160)

@@ -532,14 +532,43 @@ __device__ inline float grid_transmittance(const DMedium &m, V3 o_, V3 d, float 
     const float majorant = m.max_density;
     (void) sub.next_u32();                             // channel draw; the majorant is grey
     float si_t = maxt_;
-    float throughput = 1.0f;
+    float optical = 0.f;                               // sum of the accepted steps' majorant depths: ONE exp at the end (each
+                                                       // factor exp(-tt * majorant) of the reference rounds separately; the
+                                                       // decisions below -- what the estimator's value hangs on -- are untouched)
     V3 ro = o_; float rmint = 0.f, rmaxt = maxt_;
+    // BoundingBox::ray_intersect per step (bbox.h:302-325): the direction does not change, its reciprocals are hoisted
+    const float dd[3] = { d.x, d.y, d.z };
+    const float rcp[3] = { __fdiv_rn(1.0f, d.x), __fdiv_rn(1.0f, d.y), __fdiv_rn(1.0f, d.z) };
+    // A segment whose end points both lie inside the grid's box by a margin (1e-4 of the box + 1e-5; positions along it
+    // carry ~1e-6 of rounding) keeps every step's origin inside and every step's exit distance beyond the remaining
+    // length: the box test returns active with bmin <= 0 <= mint and bmax >= rmaxt, i.e. it changes nothing and is skipped.
+    bool well_inside;
+    {
+        const V3 e = o_ + d * maxt_;
+        const float mg[3] = { 1e-4f * (m.g_hi[0] - m.g_lo[0]) + 1e-5f, 1e-4f * (m.g_hi[1] - m.g_lo[1]) + 1e-5f, 1e-4f * (m.g_hi[2] - m.g_lo[2]) + 1e-5f };
+        well_inside = fminf(o_.x, e.x) > m.g_lo[0] + mg[0] && fmaxf(o_.x, e.x) < m.g_hi[0] - mg[0] &&
+                      fminf(o_.y, e.y) > m.g_lo[1] + mg[1] && fmaxf(o_.y, e.y) < m.g_hi[1] - mg[1] &&
+                      fminf(o_.z, e.z) > m.g_lo[2] + mg[2] && fmaxf(o_.z, e.z) < m.g_hi[2] - mg[2];
+    }
     while (t < maxt) {
         float sample = sub.next_f32();
-        float bmin, bmax;
-        bool active = bbox_ray_intersect(m.g_lo, m.g_hi, ro, d, bmin, bmax);
-        active = active && (isfinite(bmin) || isfinite(bmax));
-        if (!active) { bmin = 0.f; bmax = kInfF; }
+        float bmin = -1.f, bmax = kInfF;
+        bool active = true;
+        if (!well_inside) {
+            const float oo[3] = { ro.x, ro.y, ro.z };
+            float t1p[3], t2p[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                active = active && ((dd[k] != 0.f) || ((oo[k] > m.g_lo[k]) || (oo[k] < m.g_hi[k])));
+                float t1 = __fmul_rn(__fsub_rn(m.g_lo[k], oo[k]), rcp[k]), t2 = __fmul_rn(__fsub_rn(m.g_hi[k], oo[k]), rcp[k]);
+                t1p[k] = fminf(t1, t2); t2p[k] = fmaxf(t1, t2);
+            }
+            bmin = fmaxf(t1p[0], fmaxf(t1p[1], t1p[2]));
+            bmax = fminf(t2p[0], fminf(t2p[1], t2p[2]));
+            active = active && bmax >= bmin;
+            active = active && (isfinite(bmin) || isfinite(bmax));
+            if (!active) { bmin = 0.f; bmax = kInfF; }
+        }
         float mint = fmaxf(rmint, bmin), mx = fminf(rmaxt, bmax);
         float sampled_t = __fadd_rn(mint, __fdiv_rn(-logf(__fsub_rn(1.f, sample)), majorant));
         bool valid_mi   = active && (sampled_t <= mx);
@@ -548,14 +577,14 @@ __device__ inline float grid_transmittance(const DMedium &m, V3 o_, V3 d, float 
         if (!(mi_t < kInfF)) break;                    // !mi.is_valid()
         if (si_t < mi_t) mi_t = kInfF;
         float tt = __fsub_rn(fminf(mi_t, si_t), mint);
-        throughput = __fmul_rn(throughput, expf(__fmul_rn(-tt, majorant)));
+        optical = __fadd_rn(optical, __fmul_rn(tt, majorant));
         t = __fadd_rn(t, mi_t);
         si_t = __fsub_rn(si_t, mi_t);
         ro    = mi_p;                                  // mi.spawn_ray(_ray.d), interaction.h:58-61
         rmint = __fmul_rn(__fadd_rn(1.f, fmaxf(fabsf(mi_p.x), fmaxf(fabsf(mi_p.y), fabsf(mi_p.z)))), kRayEpsilon);
         rmaxt = fmaxf(0.0f, __fsub_rn(maxt, t));
     }
-    return throughput;
+    return expf(-optical);
 }
 
 // IsotropicPhaseFunction::eval (src/phase/isotropic.cpp:40-44) / HGPhaseFunction::eval (src/phase/hg.cpp:51-54,77-81)
