@@ -365,9 +365,17 @@ def run_ours(args):
     # ---- N > 1: is the sharded, all-reduced film the single-GPU film?  (outside every timed region) ------------------
     multi_gpu_check = None
     if world > 1 and not args.no_secondary:
+        # the bench scene plus what only rank 0 may add (the films are SUMMED): an area light the camera sees directly
+        # (segments.cu add_direct) and a volume photon map (the direct in-scattering term, photon_gather_impl)
         n_chk = min(8192, n_total)
         soa_chk = np.ascontiguousarray(soa[:, :n_chk])
-        ctx.set_scene(sc)
+        sc_chk = scenes.box_fog_scene(occluders=True)
+        e_id = sc_chk.add_emitter((4.0, 3.0, 2.0))
+        quad = np.array([[[-2, 6, -3], [2, 6, -3], [2, 9, -3]], [[-2, 6, -3], [2, 9, -3], [-2, 9, -3]]], np.float32)
+        sc_chk.add_tris(quad[:, ::-1], pkg.abi.SURF_BSDF_SMOOTH | pkg.abi.SURF_EMITTER | pkg.abi.surf_emitter_id(e_id))
+        ph = scenes.photonset_desc(*scenes.synthetic_photons(2000, seed=9), scale=1.0 / 2000, lookup_radius=0.6)
+        ctx.set_scene(sc_chk)
+        ctx.upload_photons(ph)
         _, vd_chk = pkg.sharding.shard_desc(soa_chk, rank, world)
         ctx.upload_vrls(vd_chk)
         ctx.build_segments(cam, opt); ctx.gather(opt); ctx.film_allreduce(); ctx.synchronize()
@@ -378,9 +386,12 @@ def run_ours(args):
             ctx.build_segments(cam, opt); ctx.gather(opt); ctx.synchronize()
             single = ctx.film_rgb(cam.width, cam.height).astype(np.float64)
             rel = np.abs(sharded - single) / np.maximum(np.abs(single), 1e-6 * np.abs(single).max())
+            lit = single.reshape(-1, 3).max(axis=1) > 3.0     # pixels that see the light: 4, 3, 2 of radiance added once
             multi_gpu_check = {"n_vrls": int(n_chk), "max_rel": float(rel.max()), "pixels_above_1e-5": int((rel.max(axis=-1) > 1e-5).sum()),
-                               "what": f"film of {world} VRL shards summed by NCCL vs the same set on one GPU"}
-            assert rel.max() <= 1e-4, multi_gpu_check
+                               "pixels_seeing_the_emitter": int(lit.sum()), "volume_photons": 2000,
+                               "what": f"film of {world} VRL shards summed by NCCL (emitter radiance and the photon term added by rank 0 only) vs the same frame on one GPU"}
+            assert rel.max() <= 1e-4 and lit.sum() > 100, multi_gpu_check
+        ctx.clear_photons()
         barrier()
 
     note("secondary done")
