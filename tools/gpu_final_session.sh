@@ -1,8 +1,11 @@
-TAG=r01o
+#!/bin/bash
+# Round-end measurement set on one B200: smoke, bench (both arms), the ncu launch list of the bench command.
+TAG=${1:-r02i}
 OUT=/tmp/prof_$TAG; mkdir -p $OUT gpurun_out
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
-timeout 400 python bench.py > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err; echo "bench rc=$?"
-timeout 200 python bench.py --impl reference > $OUT/bench_ref_$TAG.json 2> $OUT/bench_ref_$TAG.err; echo "ref rc=$?"
-timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $OUT/${TAG}_launches.csv python bench.py --vrls 2000 --steps 2 --warmup 1 --no-cpu-baseline > $OUT/ncu_launch.log 2>&1; echo "launch list rc=$?"
+timeout 600 python bench.py > $OUT/${TAG}_bench_n1.json 2> $OUT/${TAG}_bench_n1.err; echo "bench rc=$?"
+timeout 300 python bench.py --impl reference > $OUT/${TAG}_bench_ref.json 2> $OUT/${TAG}_bench_ref.err; echo "ref rc=$?"
+# launch list of the SAME command at a reduced VRL count (ncu serialises and replays; the kernel's share of the step is what must agree)
+timeout 400 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv python bench.py --vrls 8000 --steps 2 --warmup 1 --no-cpu-baseline --no-secondary > $OUT/ncu_launch.log 2>&1; echo "launch list rc=$?"
 cp $OUT/* gpurun_out/ 2>/dev/null
-tail -c 2500 $OUT/bench_$TAG.json
+tail -c 3000 $OUT/${TAG}_bench_n1.json
