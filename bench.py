@@ -202,7 +202,9 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the VRL gather has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # a rank that dies must not leave the others in a barrier for the driver's whole time limit
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=240))
     sc, cam, opt, soa, name = workload(args)
     n_total = soa.shape[1]
     lo, hi = pkg.sharding.shard_bounds(n_total, rank, world)
@@ -386,11 +388,12 @@ def run_ours(args):
             ctx.build_segments(cam, opt); ctx.gather(opt); ctx.synchronize()
             single = ctx.film_rgb(cam.width, cam.height).astype(np.float64)
             rel = np.abs(sharded - single) / np.maximum(np.abs(single), 1e-6 * np.abs(single).max())
-            lit = single.reshape(-1, 3).max(axis=1) > 3.0     # pixels that see the light: 4, 3, 2 of radiance added once
+            lit = single.reshape(-1, 3).max(axis=1) > 1.0     # pixels that see the light: (4, 3, 2) x the fog's transmittance (0.46), added once
             multi_gpu_check = {"n_vrls": int(n_chk), "max_rel": float(rel.max()), "pixels_above_1e-5": int((rel.max(axis=-1) > 1e-5).sum()),
                                "pixels_seeing_the_emitter": int(lit.sum()), "volume_photons": 2000,
                                "what": f"film of {world} VRL shards summed by NCCL (emitter radiance and the photon term added by rank 0 only) vs the same frame on one GPU"}
-            assert rel.max() <= 1e-4 and lit.sum() > 100, multi_gpu_check
+            # no assert here: the other ranks wait in the barrier below; the verdict is raised after the line is printed
+            multi_gpu_check["ok"] = bool(rel.max() <= 1e-4 and lit.sum() > 100)
         ctx.clear_photons()
         barrier()
 
@@ -427,10 +430,13 @@ def run_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, desc, _, _ = cpu_sample(sc, cam, opt, soa, args.cpu_seconds)
             line["cpu_baseline"] = {"value": rate, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc}
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+    if rank == 0 and multi_gpu_check is not None and not multi_gpu_check.get("ok", False):
+        print(f"[bench] multi_gpu_check FAILED: {multi_gpu_check}", file=sys.stderr)
+        return 3
     return 0
 
 
