@@ -299,7 +299,8 @@ def test_pod_layouts_match_header(tmp_path):
     """sizeof of every POD as the C compiler lays out include/vrl_b200.h == the ctypes mirror."""
     import subprocess
     names = {"vrlb_segment": abi.Segment, "vrlb_options": abi.Options, "vrlb_camera": abi.Camera, "vrlb_vrlset_desc": abi.VrlSetDesc,
-             "vrlb_timing": abi.Timing, "vrlb_medium": abi.Medium, "vrlb_scene_desc": abi.SceneDesc, "vrlb_emitter": abi.Emitter}
+             "vrlb_timing": abi.Timing, "vrlb_medium": abi.Medium, "vrlb_scene_desc": abi.SceneDesc, "vrlb_emitter": abi.Emitter,
+             "vrlb_lightcut_stats": abi.LightcutStats, "vrlb_generate_desc": abi.GenerateDesc, "vrlb_photonset_desc": abi.PhotonSetDesc}
     src = tmp_path / "sz.c"
     body = "".join(f'printf("{n} %zu\\n", sizeof({n}));' for n in names)
     src.write_text('#include <stdio.h>\n#include "vrl_b200.h"\nint main(void){' + body + "return 0;}")
