@@ -96,3 +96,36 @@ def test_laser_single_scattering_image_converges_to_the_closed_form():
     assert abs(z.mean()) <= 0.6
     assert abs(np.mean(ratio) - 1.0) <= 0.015
     ctx.close()
+
+
+def test_gpu_frame_against_independent_oracle_frames():
+    """The recipe of test_renders.py:64-81 with the CPU oracle as the reference renderer: K independent oracle frames (own
+    sampler seeds, so own jitter and own sampling draws) give a per-pixel mean and variance; one GPU frame rendered with
+    yet another seed must be a draw from that distribution (Z-test per pixel, Bonferroni-sized bound), and its mean over
+    the image must agree to a fraction of a percent.  Same exported VRL set on both sides; nothing else is shared -- so
+    this catches what a same-stream comparison cannot see (a mistake both sides make at a fixed stream position)."""
+    import oracle
+    sc, cam = scenes.box_fog_scene(occluders=True), scenes.box_fog_camera(48, 27)
+    soa = scenes.synthetic_vrls(256, seed=8)
+    vd = scenes.vrlset_desc(soa)
+    osc = oracle.OracleScene(sc)
+    K, spp = 16, 4
+    frames = []
+    for k in range(K):
+        opt = scenes.default_options(visibility=1, math_mode=0, spp=spp, base_seed=1000 + 7919 * k)
+        xyzaw, rgb, _ = osc.render(cam, opt, vd)
+        frames.append((xyzaw[..., :3] / np.maximum(xyzaw[..., 4:5], 1e-30)).reshape(-1, 3).astype(np.float64))     # XYZ / W, what the film develops
+    frames = np.array(frames)
+    mean, var = frames.mean(axis=0), frames.var(axis=0, ddof=1)                # var of ONE spp-sample frame
+    ctx = api.Context(0)
+    ctx.set_scene(sc)
+    gopt = scenes.default_options(visibility=1, math_mode=1, spp=spp, base_seed=424242)
+    out = ctx.render(cam, gopt, vd)
+    ctx.close()
+    gpu = (out[..., :3] / np.maximum(out[..., 4:5], 1e-30)).reshape(-1, 3).astype(np.float64)
+    lit = mean.max(axis=1) > 0.05 * mean.max()
+    z = (gpu - mean)[lit] / np.sqrt(var[lit] * (1.0 + 1.0 / K) + 1e-30)       # Student t, K - 1 degrees of freedom
+    print(f"{lit.sum()} pixels, K = {K} oracle frames at {spp} spp: max |Z| {np.abs(z).max():.2f}, |Z| > 3 in {100 * (np.abs(z) > 3).mean():.2f} %, "
+          f"mean Z {z.mean():+.3f}, image mean GPU / oracle {gpu[lit].sum() / mean[lit].sum():.4f}")
+    assert np.abs(z).max() <= 8.0 and (np.abs(z) > 3).mean() <= 0.03 and abs(z.mean()) <= 0.25
+    assert abs(gpu[lit].sum() / mean[lit].sum() - 1.0) <= 0.01
