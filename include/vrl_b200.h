@@ -348,7 +348,11 @@ uint64_t vrlb_segments_count(const vrlb_context *ctx);
 
 /* ---- gather: replaces VRLMap::query -> VRL::getContrib (vrl_map.h:133-211, vrl_struct.h:584-662)
  *      for every resident camera segment against every resident VRL.  Accumulates
- *      weight * Li into the device radiance buffer (fp32 RGB, width*height*3). ----------------- */
+ *      weight * Li into the device radiance buffer (fp32 RGB, width*height*3).
+ *      A long gather is issued as launches of about a quarter of a second over consecutive VRL ranges (multiples of 512,
+ *      so the film receives the values one launch would add); the call then paces them -- it returns when all but the
+ *      last are done -- and looks at the cancel flag between two launches.  With opt->use_light_cut the queries walk
+ *      the cut of the resident light tree instead (vrlb_lightcut_build). ----------------- */
 int  vrlb_film_clear(vrlb_context *ctx);
 int  vrlb_gather(vrlb_context *ctx, const vrlb_options *opt);
 /* Same, and additionally returns Li per resident segment BEFORE the weight (host, n_segments*3 fp32):
@@ -431,6 +435,8 @@ int  vrlb_shadow_proxies(const float *tri_verts, uint32_t n_tris, float *solids_
  * (include/mitsuba/render/kdtree.h: max_depth). */
 int  vrlb_bvh_depths(const float *tri_verts, uint32_t n_tris, uint32_t depths[2]);
 
+/* Integrator::cancel (integrator.h:148-151).  Thread-safe against a running vrlb_gather / vrlb_render of the same context:
+ * the gather stops between two of its launches (< 1 s) and returns VRLB_ERR_CANCELLED; the film then holds a partial sum. */
 int  vrlb_cancel(vrlb_context *ctx);
 int  vrlb_get_timing(const vrlb_context *ctx, vrlb_timing *out);
 int  vrlb_synchronize(vrlb_context *ctx);
