@@ -434,6 +434,14 @@ int  vrlb_shadow_proxies(const float *tri_verts, uint32_t n_tris, float *solids_
  * branch would go deeper).  Host only.  Stands where the reference's kd-tree has its own depth limit
  * (include/mitsuba/render/kdtree.h: max_depth). */
 int  vrlb_bvh_depths(const float *tri_verts, uint32_t n_tris, uint32_t depths[2]);
+/* Which builder the NEXT vrlb_scene_set uses for the closest-hit tree (the one the camera paths and the light tracer
+ * walk, Scene::ray_intersect -> ShapeKDTree, scene.cpp:114-131, kdtree.h:2069-2172): 0 = binned SAH on the host (default),
+ * 1 = LBVH on the device (Morton sort + parallel hierarchy + bottom-up fit, bvh_lbvh.cu).  Hits do not depend on the tree.
+ * A device tree deeper than the traversal stack allows falls back to the host build.  The shadow structure (shells,
+ * solids with their proxies) is built on the host either way. */
+int  vrlb_set_bvh_builder(vrlb_context *ctx, int builder);
+/* info = builder used by the last vrlb_scene_set (0 / 1), depth of the tree (root = 0), nodes, build time in microseconds */
+int  vrlb_bvh_info(const vrlb_context *ctx, uint32_t info[4]);
 
 /* Integrator::cancel (integrator.h:148-151).  Thread-safe against a running vrlb_gather / vrlb_render of the same context:
  * the gather stops between two of its launches (< 1 s) and returns VRLB_ERR_CANCELLED; the film then holds a partial sum. */

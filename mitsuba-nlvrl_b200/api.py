@@ -25,6 +25,7 @@ EXPORTS = [
     "vrlb_surface_queries_upload", "vrlb_surface_queries_download", "vrlb_surface_gather_queries",
     "vrlb_photons_upload", "vrlb_photons_count", "vrlb_photon_gather_segments", "vrlb_photons_generate", "vrlb_photons_download",
     "vrlb_lightcut_build", "vrlb_lightcut_download", "vrlb_lightcut_get_stats", "vrlb_lightcut_gather_segments",
+    "vrlb_set_bvh_builder", "vrlb_bvh_info",
 ]
 
 
@@ -121,6 +122,8 @@ def load_library():
     L.vrlb_lightcut_download.argtypes = [vp, f32p, C.POINTER(C.c_int32), C.c_uint64, C.POINTER(C.c_uint64)]
     L.vrlb_lightcut_get_stats.argtypes = [vp, C.POINTER(abi.LightcutStats)]
     L.vrlb_lightcut_gather_segments.argtypes = [vp, C.POINTER(abi.Options), f32p, f32p]
+    L.vrlb_set_bvh_builder.argtypes = [vp, C.c_int]
+    L.vrlb_bvh_info.argtypes = [vp, C.POINTER(C.c_uint32)]
     L.vrlb_bvh_depths.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     L.vrlb_shadow_proxies.argtypes = [C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_float), C.c_uint32, C.POINTER(C.c_uint32)]
     _lib = L
@@ -289,6 +292,15 @@ class Context:
 
     def gather(self, opt):
         self._check(self.lib.vrlb_gather(self.h, C.byref(opt)))
+
+    def set_bvh_builder(self, builder):
+        """0 = host binned SAH (default), 1 = device LBVH, for the closest-hit tree of the next set_scene."""
+        self._check(self.lib.vrlb_set_bvh_builder(self.h, builder))
+
+    def bvh_info(self):
+        info = (C.c_uint32 * 4)()
+        self._check(self.lib.vrlb_bvh_info(self.h, info))
+        return dict(builder=int(info[0]), depth=int(info[1]), nodes=int(info[2]), build_us=int(info[3]))
 
     def lightcut_build(self, seed_offset=0, base_seed=0):
         """VRLLightCut constructor (vrl_lightcut.h:196-212) over the resident VRL set; the sampler is sampler.seed(base_seed, seed_offset)."""

@@ -1,5 +1,6 @@
 // bvh_build.h -- host BVH builder interface (internal).
 #pragma once
+#include <cuda_runtime.h>
 #include <stdint.h>
 #include <vector>
 
@@ -9,6 +10,11 @@ namespace vrlb {
 // verts: n*9 floats (p0 p1 p2 per triangle), flags: n surface words (may be null).
 // Produces the flattened binary BVH (root = node 0) and the triangles in leaf order.
 void build_bvh(const float *verts, const uint32_t *flags, uint32_t n, std::vector<DNode> &nodes, std::vector<DTri> &tris);
+// The same tree layout built on the device (bvh_lbvh.cu, LBVH): d_verts / d_flags are device arrays in ORIGINAL triangle
+// order, lo / hi the geometry's bounding box, pad the host build's box margin; writes 2n - 1 nodes and n triangles.
+// *max_depth = depth of the tree (root = 0).
+cudaError_t build_bvh_device(const float *d_verts, const uint32_t *d_flags, uint32_t n, float pad, const float lo[3], const float hi[3],
+                             DNode *d_nodes, DTri *d_tris, int *max_depth, uint64_t *launches, cudaStream_t stream);
 int last_bvh_depth();      // depth (root = 0) of the tree the last build_bvh call produced; bounded by kMaxBvhDepth (bvh_build.cpp)
 // Re-packs the binary BVH for the shadow traversal: one DWNode per inner node holding both children's boxes.
 // Empty when the root is a leaf.

@@ -8,6 +8,7 @@
 #include <dlfcn.h>
 
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -54,6 +55,9 @@ struct vrlb_context {
     DScene scene{};
     bool have_scene = false;
     float scene_extent = 20.f;        // largest side of the geometry's bounding box (the conditioning guard scales with it)
+    int bvh_builder = 0;              // vrlb_set_bvh_builder: 0 = host binned SAH, 1 = device LBVH (closest-hit tree)
+    uint32_t bvh_info[4] = { 0, 0, 0, 0 };   // builder used, depth, nodes, build time in microseconds
+    DevBuf<uint32_t> flags_dev;
     std::vector<vrlb_medium> host_media;
     std::vector<DTri> host_tris;      // BVH order, for the emitter table of vrlb_vrls_generate
 
@@ -202,7 +206,7 @@ void vrlb_destroy(vrlb_context *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     ctx->tris.release(); ctx->verts.release(); ctx->nodes.release(); ctx->wnodes.release(); ctx->stris.release(); ctx->media.release(); ctx->emitters.release(); ctx->grids.release(); ctx->solids.release();
-    ctx->tri_refl.release(); ctx->squeries.release();
+    ctx->tri_refl.release(); ctx->squeries.release(); ctx->flags_dev.release();
     ctx->vol.photons.release(); ctx->vol.cells.release();
     for (auto &m : ctx->surf) { m.photons.release(); m.cells.release(); }
     if (ctx->wd) cudaFreeHost(ctx->wd);
@@ -255,6 +259,18 @@ int vrlb_bvh_depths(const float *tri_verts, uint32_t n_tris, uint32_t depths[2])
     depths[0] = (uint32_t) last_bvh_depth();
     ShadowAccel sa; build_shadow_accel(tri_verts, nullptr, n_tris, sa);
     depths[1] = (uint32_t) sa.max_depth;
+    return VRLB_OK;
+}
+
+int vrlb_set_bvh_builder(vrlb_context *ctx, int builder) {
+    if (!ctx) return VRLB_ERR_INVALID;
+    if (builder != 0 && builder != 1) return fail(ctx, VRLB_ERR_INVALID, "bvh builder %d unknown (0 host binned SAH, 1 device LBVH)", builder);
+    ctx->bvh_builder = builder;
+    return VRLB_OK;
+}
+int vrlb_bvh_info(const vrlb_context *ctx, uint32_t info[4]) {
+    if (!ctx || !info) return VRLB_ERR_INVALID;
+    for (int k = 0; k < 4; ++k) info[k] = ctx->bvh_info[k];
     return VRLB_OK;
 }
 
@@ -327,7 +343,38 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
         ctx->scene_extent = (ext > 0.f && std::isfinite(ext)) ? ext : 20.f;
     } else ctx->scene_extent = 20.f;
     std::vector<DNode> nodes; std::vector<DTri> tris;
-    build_bvh(sc->tri_verts, sc->tri_flags, sc->n_tris, nodes, tris);
+    bool device_tree = false;
+    const auto t_bvh = std::chrono::steady_clock::now();
+    if (ctx->bvh_builder == 1 && sc->n_tris > 0) {
+        // closest-hit tree on the device (bvh_lbvh.cu): same layout, same triangle arithmetic; the host build's margin
+        float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY }, mx = 0.f;
+        for (size_t i = 0; i < (size_t) sc->n_tris * 9; ++i) {
+            lo[i % 3] = std::min(lo[i % 3], sc->tri_verts[i]); hi[i % 3] = std::max(hi[i % 3], sc->tri_verts[i]);
+            mx = std::max(mx, std::fabs(sc->tri_verts[i]));
+        }
+        const float pad = 1e-4f * mx + 1e-6f;
+        const uint32_t n = sc->n_tris;
+        CU(ctx, ctx->verts.reserve((size_t) n * 9)); CU(ctx, ctx->flags_dev.reserve(n));
+        CU(ctx, ctx->tris.reserve(n)); CU(ctx, ctx->nodes.reserve((size_t) 2 * n));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        CU(ctx, cudaMemcpy(ctx->verts.ptr, sc->tri_verts, (size_t) n * 9 * sizeof(float), cudaMemcpyHostToDevice));
+        CU(ctx, cudaMemcpy(ctx->flags_dev.ptr, sc->tri_flags, (size_t) n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        int depth = 0;
+        CU(ctx, build_bvh_device(ctx->verts.ptr, ctx->flags_dev.ptr, n, pad, lo, hi, ctx->nodes.ptr, ctx->tris.ptr, &depth, &ctx->launches, ctx->stream));
+        if (depth <= 44) {                       // closest_hit's stack holds depth + 1 entries of its 48
+            device_tree = true;
+            tris.resize(n); nodes.resize((size_t) 2 * n - 1);
+            CU(ctx, cudaMemcpy(tris.data(), ctx->tris.ptr, (size_t) n * sizeof(DTri), cudaMemcpyDeviceToHost));      // the emitter table reads them
+            CU(ctx, cudaMemcpy(nodes.data(), ctx->nodes.ptr, nodes.size() * sizeof(DNode), cudaMemcpyDeviceToHost));
+            ctx->bvh_info[0] = 1; ctx->bvh_info[1] = (uint32_t) depth;
+        }
+    }
+    if (!device_tree) {
+        build_bvh(sc->tri_verts, sc->tri_flags, sc->n_tris, nodes, tris);
+        ctx->bvh_info[0] = 0; ctx->bvh_info[1] = (uint32_t) last_bvh_depth();
+    }
+    ctx->bvh_info[2] = (uint32_t) nodes.size();
+    ctx->bvh_info[3] = (uint32_t) std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_bvh).count();
     ShadowAccel sa; build_shadow_accel(sc->tri_verts, sc->tri_flags, sc->n_tris, sa);
     CU(ctx, ctx->wnodes.reserve(sa.wnodes.size())); CU(ctx, ctx->stris.reserve(sa.tris.size()));
     CU(ctx, ctx->tris.reserve(tris.size())); CU(ctx, ctx->nodes.reserve(nodes.size()));
@@ -335,8 +382,10 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     CU(ctx, ctx->emitters.reserve((size_t) sc->n_emitters * 4));
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     if (!tris.empty()) {
-        CU(ctx, cudaMemcpy(ctx->tris.ptr, tris.data(), tris.size() * sizeof(DTri), cudaMemcpyHostToDevice));
-        CU(ctx, cudaMemcpy(ctx->nodes.ptr, nodes.data(), nodes.size() * sizeof(DNode), cudaMemcpyHostToDevice));
+        if (!device_tree) {
+            CU(ctx, cudaMemcpy(ctx->tris.ptr, tris.data(), tris.size() * sizeof(DTri), cudaMemcpyHostToDevice));
+            CU(ctx, cudaMemcpy(ctx->nodes.ptr, nodes.data(), nodes.size() * sizeof(DNode), cudaMemcpyHostToDevice));
+        }
         if (!sa.wnodes.empty()) CU(ctx, cudaMemcpy(ctx->wnodes.ptr, sa.wnodes.data(), sa.wnodes.size() * sizeof(DWNode), cudaMemcpyHostToDevice));
         CU(ctx, cudaMemcpy(ctx->stris.ptr, sa.tris.data(), sa.tris.size() * sizeof(DTri), cudaMemcpyHostToDevice));
         CU(ctx, cudaMemcpy(ctx->verts.ptr, sc->tri_verts, (size_t) sc->n_tris * 9 * sizeof(float), cudaMemcpyHostToDevice));
