@@ -437,11 +437,13 @@ int  vrlb_bvh_depths(const float *tri_verts, uint32_t n_tris, uint32_t depths[2]
 /* Which builder the NEXT vrlb_scene_set uses for the closest-hit tree (the one the camera paths and the light tracer
  * walk, Scene::ray_intersect -> ShapeKDTree, scene.cpp:114-131, kdtree.h:2069-2172): 0 = binned SAH on the host (default),
  * 1 = LBVH on the device (Morton sort + parallel hierarchy + bottom-up fit, bvh_lbvh.cu).  Hits do not depend on the tree.
- * A device tree deeper than the traversal stack allows falls back to the host build.  The shadow structure (shells,
- * solids with their proxies) is built on the host either way. */
+ * A device tree deeper than the traversal stack allows falls back to the host build.  With builder 1 the trees of the
+ * shadow structure (main geometry, each shell, each solid) are built on the device as well; its components, shell boxes
+ * and the solids' proxies are found on the host either way. */
 int  vrlb_set_bvh_builder(vrlb_context *ctx, int builder);
-/* info = builder used by the last vrlb_scene_set (0 / 1), depth of the tree (root = 0), nodes, build time in microseconds */
-int  vrlb_bvh_info(const vrlb_context *ctx, uint32_t info[4]);
+/* info = closest-hit tree of the last vrlb_scene_set: builder used (0 / 1), depth (root = 0), nodes, build time in
+ * microseconds; shadow structure: trees built on the device, depth of its deepest tree */
+int  vrlb_bvh_info(const vrlb_context *ctx, uint32_t info[6]);
 
 /* Integrator::cancel (integrator.h:148-151).  Thread-safe against a running vrlb_gather / vrlb_render of the same context:
  * the gather stops between two of its launches (< 1 s) and returns VRLB_ERR_CANCELLED; the film then holds a partial sum. */

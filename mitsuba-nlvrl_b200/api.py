@@ -298,9 +298,10 @@ class Context:
         self._check(self.lib.vrlb_set_bvh_builder(self.h, builder))
 
     def bvh_info(self):
-        info = (C.c_uint32 * 4)()
+        info = (C.c_uint32 * 6)()
         self._check(self.lib.vrlb_bvh_info(self.h, info))
-        return dict(builder=int(info[0]), depth=int(info[1]), nodes=int(info[2]), build_us=int(info[3]))
+        return dict(builder=int(info[0]), depth=int(info[1]), nodes=int(info[2]), build_us=int(info[3]),
+                    shadow_trees_on_device=int(info[4]), shadow_depth=int(info[5]))
 
     def lightcut_build(self, seed_offset=0, base_seed=0):
         """VRLLightCut constructor (vrl_lightcut.h:196-212) over the resident VRL set; the sampler is sampler.seed(base_seed, seed_offset)."""

@@ -168,8 +168,9 @@ void build_wide_nodes(const std::vector<DNode> &nodes, std::vector<DWNode> &wnod
 // such components get their own small BVH which the shadow query enters only when an end point is within
 // `margin` of (or outside) the box.  Everything else goes into the main BVH, whose SAH is then no longer
 // dominated by scene-sized triangles.  Exactness: skipped triangles are at least `margin` away from the segment.
-void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, ShadowAccel &out) {
+void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, ShadowAccel &out, const SubsetBuilder *custom, uint32_t *n_custom) {
     out = ShadowAccel();
+    if (n_custom) *n_custom = 0;
     if (n == 0) return;
     // union-find over triangles sharing a vertex position (exact fp32 equality)
     std::vector<uint32_t> parent(n);
@@ -243,8 +244,14 @@ void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, S
             std::vector<float> v((size_t) sub.size() * 9); std::vector<uint32_t> f(sub.size());
             for (size_t i = 0; i < sub.size(); ++i) { std::memcpy(&v[i * 9], verts + (size_t) sub[i] * 9, 36); f[i] = flags ? flags[sub[i]] : 0u; }
             std::vector<DNode> nodes; std::vector<DTri> tris; std::vector<DWNode> w;
-            build_bvh(v.data(), f.data(), (uint32_t) sub.size(), nodes, tris);
-            out.max_depth = std::max(out.max_depth, last_bvh_depth());
+            int depth = 0;
+            if (custom && (*custom)(v.data(), f.data(), (uint32_t) sub.size(), nodes, tris, depth) && depth + 2 <= kMaxBvhDepth) {
+                if (n_custom) ++*n_custom;
+            } else {
+                build_bvh(v.data(), f.data(), (uint32_t) sub.size(), nodes, tris);
+                depth = last_bvh_depth();
+            }
+            out.max_depth = std::max(out.max_depth, depth);
             build_wide_nodes(nodes, w);
             const uint32_t tri0 = (uint32_t) out.tris.size(), node0 = (uint32_t) out.wnodes.size();
             for (DTri &t : tris) { t.prim = sub[t.prim]; out.tris.push_back(t); }

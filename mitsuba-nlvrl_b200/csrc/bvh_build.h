@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <functional>
 #include <vector>
 
 #include "vrlb_device.cuh"
@@ -33,5 +34,9 @@ struct ShadowAccel {
 };
 // proxies of one component (triangle indices `sub` into verts); fills everything but `root`
 void build_solid_proxies(const float *verts, const std::vector<uint32_t> &sub, float margin, DSolid &out);
-void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, ShadowAccel &out);
+// `custom`, when given, builds the binary tree of one component (host arrays in, nodes / triangles in leaf order and the
+// tree's depth out; false = could not, use the host build): how the device LBVH (bvh_lbvh.cu) is plugged in.  A tree
+// deeper than the shadow traversals' stacks allow (kMaxBvhDepth, bvh_build.cpp) is replaced by the host build.
+using SubsetBuilder = std::function<bool(const float *verts, const uint32_t *flags, uint32_t n, std::vector<DNode> &nodes, std::vector<DTri> &tris, int &depth)>;
+void build_shadow_accel(const float *verts, const uint32_t *flags, uint32_t n, ShadowAccel &out, const SubsetBuilder *custom = nullptr, uint32_t *n_custom = nullptr);
 }  // namespace vrlb

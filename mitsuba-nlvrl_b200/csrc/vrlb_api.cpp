@@ -56,7 +56,7 @@ struct vrlb_context {
     bool have_scene = false;
     float scene_extent = 20.f;        // largest side of the geometry's bounding box (the conditioning guard scales with it)
     int bvh_builder = 0;              // vrlb_set_bvh_builder: 0 = host binned SAH, 1 = device LBVH (closest-hit tree)
-    uint32_t bvh_info[4] = { 0, 0, 0, 0 };   // builder used, depth, nodes, build time in microseconds
+    uint32_t bvh_info[6] = { 0, 0, 0, 0, 0, 0 };   // closest-hit tree: builder used, depth, nodes, build time in microseconds; shadow trees built on the device, their largest depth
     DevBuf<uint32_t> flags_dev;
     std::vector<vrlb_medium> host_media;
     std::vector<DTri> host_tris;      // BVH order, for the emitter table of vrlb_vrls_generate
@@ -268,9 +268,9 @@ int vrlb_set_bvh_builder(vrlb_context *ctx, int builder) {
     ctx->bvh_builder = builder;
     return VRLB_OK;
 }
-int vrlb_bvh_info(const vrlb_context *ctx, uint32_t info[4]) {
+int vrlb_bvh_info(const vrlb_context *ctx, uint32_t info[6]) {
     if (!ctx || !info) return VRLB_ERR_INVALID;
-    for (int k = 0; k < 4; ++k) info[k] = ctx->bvh_info[k];
+    for (int k = 0; k < 6; ++k) info[k] = ctx->bvh_info[k];
     return VRLB_OK;
 }
 
@@ -375,7 +375,28 @@ int vrlb_scene_set(vrlb_context *ctx, const vrlb_scene_desc *sc) {
     }
     ctx->bvh_info[2] = (uint32_t) nodes.size();
     ctx->bvh_info[3] = (uint32_t) std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_bvh).count();
-    ShadowAccel sa; build_shadow_accel(sc->tri_verts, sc->tri_flags, sc->n_tris, sa);
+    // the shadow structure's per-component trees through the device builder as well, when it is selected (components,
+    // shells and proxies are found on the host either way)
+    SubsetBuilder dev_builder = [&](const float *v, const uint32_t *f, uint32_t m, std::vector<DNode> &nd, std::vector<DTri> &tr, int &depth) -> bool {
+        if (m == 0) return false;
+        float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY }, mx = 0.f;
+        for (size_t i = 0; i < (size_t) m * 9; ++i) { lo[i % 3] = std::min(lo[i % 3], v[i]); hi[i % 3] = std::max(hi[i % 3], v[i]); mx = std::max(mx, std::fabs(v[i])); }
+        DevBuf<float> dv; DevBuf<uint32_t> df; DevBuf<DNode> dn; DevBuf<DTri> dt;
+        bool ok = dv.reserve((size_t) m * 9) == cudaSuccess && df.reserve(m) == cudaSuccess && dn.reserve((size_t) 2 * m) == cudaSuccess && dt.reserve(m) == cudaSuccess;
+        ok = ok && cudaMemcpy(dv.ptr, v, (size_t) m * 9 * sizeof(float), cudaMemcpyHostToDevice) == cudaSuccess;
+        ok = ok && cudaMemcpy(df.ptr, f, (size_t) m * sizeof(uint32_t), cudaMemcpyHostToDevice) == cudaSuccess;
+        ok = ok && build_bvh_device(dv.ptr, df.ptr, m, 1e-4f * mx + 1e-6f, lo, hi, dn.ptr, dt.ptr, &depth, &ctx->launches, ctx->stream) == cudaSuccess;
+        if (ok) {
+            nd.resize((size_t) 2 * m - 1); tr.resize(m);
+            ok = cudaMemcpy(nd.data(), dn.ptr, nd.size() * sizeof(DNode), cudaMemcpyDeviceToHost) == cudaSuccess &&
+                 cudaMemcpy(tr.data(), dt.ptr, (size_t) m * sizeof(DTri), cudaMemcpyDeviceToHost) == cudaSuccess;
+        }
+        dv.release(); df.release(); dn.release(); dt.release();
+        return ok;
+    };
+    uint32_t n_dev_components = 0;
+    ShadowAccel sa; build_shadow_accel(sc->tri_verts, sc->tri_flags, sc->n_tris, sa, ctx->bvh_builder == 1 ? &dev_builder : nullptr, &n_dev_components);
+    ctx->bvh_info[4] = n_dev_components; ctx->bvh_info[5] = (uint32_t) sa.max_depth;
     CU(ctx, ctx->wnodes.reserve(sa.wnodes.size())); CU(ctx, ctx->stris.reserve(sa.tris.size()));
     CU(ctx, ctx->tris.reserve(tris.size())); CU(ctx, ctx->nodes.reserve(nodes.size()));
     CU(ctx, ctx->verts.reserve((size_t) sc->n_tris * 9)); CU(ctx, ctx->media.reserve(dm.size()));

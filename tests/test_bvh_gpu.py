@@ -64,3 +64,35 @@ def test_random_triangle_soup_is_walked_identically():
     assert di["builder"] == 1
     _same(host_segs, dev_segs)
     assert len(host_segs) > 30000 and host_segs["maxt"].std() > 1.0          # the paths do end on the soup
+
+
+@pytest.mark.parametrize("math_mode", [0, 1])
+def test_shadow_trees_from_the_device_give_the_same_film(math_mode):
+    """With builder 1 the trees of the shadow structure (main geometry, shells, solids) come from the device as well.  A shadow
+    query is a yes / no: the exactly rounded kernel must produce a bit-identical film; the fast kernel may meet a grazing
+    triangle before or after a certain hit depending on the tree, and then re-evaluates that one eval exactly (1e-5 of it)."""
+    from parity_tools import rel_err
+    sc, cam = scenes.box_fog_scene(occluders=True), scenes.box_fog_camera(320, 180)
+    opt = scenes.default_options(visibility=1, math_mode=math_mode)
+    vd = scenes.vrlset_desc(scenes.synthetic_vrls(2048, seed=6))
+    films, infos = [], []
+    for builder in (0, 1):
+        ctx = api.Context(0)
+        ctx.set_bvh_builder(builder)
+        ctx.set_scene(sc)
+        infos.append(ctx.bvh_info())
+        ctx.upload_vrls(vd)
+        ctx.build_segments(cam, opt)
+        ctx.clear_film(); ctx.gather(opt)
+        films.append(ctx.film_rgb(cam.width, cam.height).reshape(-1, 3).astype(np.float64))
+        ctx.close()
+    print(f"shadow structure: host depth {infos[0]['shadow_depth']}; device: {infos[1]['shadow_trees_on_device']} trees, depth {infos[1]['shadow_depth']}")
+    assert infos[0]["shadow_trees_on_device"] == 0 and infos[1]["shadow_trees_on_device"] >= 3
+    differing = (films[0] != films[1]).any(axis=1)
+    if math_mode == 0:
+        assert not differing.any(), differing.sum()
+    else:
+        # measured: 1 of 57 600 pixels differs, by 1.03e-4 (one eval of 2048 decided by the exact re-evaluation instead of the
+        # fast test, DESIGN.md section 5 kernel 4 "graze"); every other pixel is bit-identical
+        err = rel_err(films[1], films[0])
+        assert err.max() <= 2e-3 and (err > 1e-4).sum() <= 3 and differing.mean() <= 0.002, (err.max(), differing.sum())
